@@ -1,0 +1,249 @@
+/*
+ * mmsolver_b200.h -- C-ABI of the B200-native mmSolver solve hot path.
+ *
+ * This is the drop-in boundary for ONE path of the reference
+ * (bpatchasaheb/mayaMatchMoveSolver): the Levenberg-Marquardt solve loop
+ *   solveFrames()            src/mmSolver/adjust/adjust_base.cpp:713
+ *   solveFunc()              src/mmSolver/adjust/adjust_solveFunc.cpp:529
+ *   measureErrors()          src/mmSolver/adjust/adjust_measureErrors.cpp:523
+ *   setParameters()          src/mmSolver/adjust/adjust_setParameters.cpp:253
+ *   solve_3d_cminpack_lmder  src/mmSolver/adjust/adjust_cminpack_lmder.cpp:64
+ *
+ * Plain pointers and sizes only; no torch / C++ types cross this ABI.
+ * Every function returns an mmb_status (0 = ok, <0 = error) and never throws.
+ * The library owns device memory inside the opaque mmb_problem handle; the
+ * caller owns every host array it passes in or receives results into.  No
+ * host pointer is retained after a call returns.
+ *
+ * The scene description mirrors what the reference hands to its solve
+ * callback in SolverData (adjust_data.h:188-261) when sceneGraphMode ==
+ * kMMSceneGraph: the flattened mmscenegraph FlatScene
+ * (lib/rust/mmscenegraph/src/scene/flat.rs:41-71) + AttrDataBlock
+ * (src/attr/datablock.rs:76-111) + the lens model tables
+ * (mayahelper/maya_lens_model_utils.cpp:859) + the solver attribute list.
+ */
+#ifndef MMSOLVER_B200_H
+#define MMSOLVER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MMB_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+typedef int32_t mmb_status;
+#define MMB_OK 0
+#define MMB_ERR_INVALID_ARGUMENT (-1)
+#define MMB_ERR_CUDA (-2)
+#define MMB_ERR_NO_DEVICE (-3)
+#define MMB_ERR_NOT_ENOUGH_OBJECTS (-4) /* adjust_base.cpp:844-862 */
+#define MMB_ERR_MORE_PARAMS_THAN_ERRORS (-5) /* adjust_base.cpp:864-882 */
+#define MMB_ERR_UNSUPPORTED (-6)
+#define MMB_ERR_INTERNAL (-7)
+
+/* ---- attribute references ----------------------------------------------
+ * Every scene value that the reference keeps in its AttrDataBlock is named by
+ * an int32 "attr ref":  ref >= 0  -> static_values[ref]
+ *                        ref <  0  -> anim_values[(-ref-1) * num_frames + f]
+ * (datablock.rs:76-111, animdense.rs:45-53).
+ */
+typedef int32_t mmb_attr_ref;
+#define MMB_ANIM_REF(a) (-(int32_t)(a)-1)
+#define MMB_ATTR_NONE INT32_MIN /* unused slot (e.g. lens coeff) -> 0.0 */
+
+/* rotate orders: lib/rust/mmscenegraph/src/math/rotate/euler.rs */
+enum { MMB_ROO_XYZ = 0, MMB_ROO_YZX = 1, MMB_ROO_ZXY = 2,
+       MMB_ROO_XZY = 3, MMB_ROO_YXZ = 4, MMB_ROO_ZYX = 5 };
+/* film fit: lib/rust/mmscenegraph/src/math/camera.rs:32-37 */
+enum { MMB_FILM_FIT_FILL = 0, MMB_FILM_FIT_HORIZONTAL = 1,
+       MMB_FILM_FIT_VERTICAL = 2, MMB_FILM_FIT_OVERSCAN = 3 };
+/* lens model types: lib/cppbind/mmlens (LensModelType) */
+enum { MMB_LENS_PASSTHROUGH = 0,
+       MMB_LENS_3DE_CLASSIC = 1,                 /* 5 coeffs  */
+       MMB_LENS_3DE_RADIAL_STD_DEG4 = 2,         /* 8 coeffs  */
+       MMB_LENS_3DE_ANAMORPHIC_STD_DEG4 = 3,     /* 13 coeffs */
+       MMB_LENS_3DE_ANAMORPHIC_STD_DEG4_RESCALED = 4 /* 14 coeffs */ };
+#define MMB_LENS_MAX_COEFFS 14
+#define MMB_TFM_ATTRS 9  /* tx ty tz rx ry rz sx sy sz */
+#define MMB_CAM_ATTRS 8  /* sensor_w_mm sensor_h_mm focal_mm lens_offset_x_mm
+                            lens_offset_y_mm near far camera_scale
+                            (dag.rs:120-172) */
+
+/* ---- scene description ------------------------------------------------- */
+typedef struct mmb_scene_desc {
+    int32_t abi_version; /* MMB_ABI_VERSION */
+
+    /* frames to solve (MTimeArray frameList / mmsgFrameList) */
+    int32_t num_frames;
+    const int32_t *frames; /* [F] frame numbers (informational) */
+
+    /* attribute value store */
+    int32_t num_static;
+    const double *static_values; /* [num_static] */
+    int32_t num_anim;
+    const double *anim_values;   /* [num_anim * F] */
+
+    /* transform hierarchy, parents before children (dag.rs:234-327) */
+    int32_t num_transforms;
+    const int32_t *tfm_parent;        /* [T] -1 = none, else < own index */
+    const int32_t *tfm_rotate_order;  /* [T] MMB_ROO_* */
+    const mmb_attr_ref *tfm_attrs;    /* [T*9] */
+
+    /* cameras (flat.rs:263-283) */
+    int32_t num_cameras;
+    const int32_t *cam_tfm;           /* [C] transform index */
+    const mmb_attr_ref *cam_attrs;    /* [C*8] */
+    const int32_t *cam_film_fit;      /* [C] MMB_FILM_FIT_* */
+    const int32_t *cam_render_width;  /* [C] */
+    const int32_t *cam_render_height; /* [C] */
+    const int32_t *cam_lens;          /* [C] lens index or -1 */
+
+    /* bundles */
+    int32_t num_bundles;
+    const int32_t *bnd_tfm; /* [B] transform index */
+
+    /* markers: dense marker x frame tables (marker-major), as cached by
+     * countUpNumberOfErrors (adjust_relationships.cpp:75-221) */
+    int32_t num_markers;
+    const int32_t *mkr_cam;    /* [M] */
+    const int32_t *mkr_bnd;    /* [M] */
+    const double *mkr_x;       /* [M*F] -0.5..0.5, overscan applied */
+    const double *mkr_y;       /* [M*F] */
+    const double *mkr_weight;  /* [M*F] */
+    const uint8_t *mkr_enable; /* [M*F] */
+
+    /* lens models (mmlens LensModel + CameraParameters) */
+    int32_t num_lenses;
+    const int32_t *lens_model;        /* [L] MMB_LENS_* */
+    const mmb_attr_ref *lens_attrs;   /* [L*MMB_LENS_MAX_COEFFS] */
+    const double *lens_camera_params; /* [L*6] focal_cm fbw_cm fbh_cm
+                                         pixel_aspect lco_x_cm lco_y_cm
+                                         (lens_model.h:42 defaults
+                                          3.0 3.6 2.4 1.0 0.0 0.0) */
+
+    /* solver attributes, in the order of the reference's '-attr' flags
+     * (countUpNumberOfUnknownParameters, adjust_relationships.cpp:223-337):
+     * an anim ref expands to F parameters, a static ref to one. */
+    int32_t num_attrs;
+    const mmb_attr_ref *attr_ref; /* [A] */
+    const double *attr_min;       /* [A] -FLT_MAX = none (maya_attr.cpp:88) */
+    const double *attr_max;       /* [A] +FLT_MAX = none */
+    const double *attr_offset;    /* [A] default 0 */
+    const double *attr_scale;     /* [A] default 1 */
+} mmb_scene_desc;
+
+/* ---- solver options: SolverOptions, adjust_data.h:133-185 -------------- */
+typedef struct mmb_options {
+    int32_t iter_max;          /* -iterations, default 100 (maxfev) */
+    double tau;                /* -tauFactor 1.0, clamped [0,1]; factor=tau*100 */
+    double eps1;               /* ftol 1e-6 */
+    double eps2;               /* xtol 1e-6 */
+    double eps3;               /* gtol 1e-6 */
+    double delta;              /* FD step 1e-4 */
+    int32_t auto_diff_type;    /* 0 forward, 1 central */
+    int32_t auto_param_scale;  /* 1 -> lmder mode 1, else mode 2 */
+    int32_t robust_loss_type;  /* accepted, unused (adjust_defines.h:134) */
+    double robust_loss_scale;
+    int32_t scene_graph_mode;  /* 2 = mmscenegraph (only mode implemented) */
+    int32_t solver_type;       /* 2 = cminpack_lmder (default) */
+    int32_t time_eval_mode;    /* accepted, unused without Maya */
+    int32_t accept_only_better;/* default 1 */
+    double image_width;        /* default 2048.0 */
+    int32_t frame_solve_mode;  /* 0 all frames at once, 1 per frame */
+    int32_t remove_unused_markers;
+    int32_t remove_unused_attributes;
+    /* extensions (0 = reference behaviour) */
+    int32_t lens_index_literal;/* 1: reproduce the reference's
+                                  [markerIndex+frameIndex] lens table read
+                                  (adjust_measureErrors.cpp:463); 0: intended
+                                  [marker*F+frame] */
+    int32_t device;            /* CUDA device ordinal */
+} mmb_options;
+
+/* ---- results: SolverResult / ErrorMetrics, adjust_results.h:119-286 ---- */
+typedef struct mmb_result {
+    int32_t success;
+    int32_t reason_num;              /* cminpack info 0..8 */
+    const char *reason_str;          /* static string, adjust_cminpack_base.h */
+    double error_final;              /* enorm(fvec) */
+    double error_avg, error_min, error_max; /* px, compute_error_stats */
+    int32_t iteration_num;           /* nfev */
+    int32_t iteration_function_num;  /* iflag=1 calls */
+    int32_t iteration_jacobian_num;  /* FD re-evaluations (n per Jacobian) */
+    int32_t iteration_attempt_num;   /* LM outer iterations (ours) */
+    int32_t user_interrupted;
+    int32_t error_is_better;         /* acceptOnlyBetter decision */
+    double timer_solve_s, timer_jacobian_s, timer_function_s,
+           timer_linear_s;           /* device time, CUDA events */
+} mmb_result;
+
+typedef struct mmb_problem mmb_problem; /* opaque */
+
+/* fill with the reference defaults (adjust_defines.h:92-152,
+ * arg_flags_solve_info.cpp) */
+void mmb_options_default(mmb_options *opt);
+
+/* Build index maps (bit-exact with adjust_relationships.cpp) and upload the
+ * scene.  Replaces the head of solveFrames(), adjust_base.cpp:746-1074. */
+mmb_status mmb_problem_create(const mmb_scene_desc *scene,
+                              const mmb_options *opt, mmb_problem **out);
+void mmb_problem_destroy(mmb_problem *p);
+
+/* sizes: numberOfParameters n, numberOfMarkerErrors/2 (= Nobs), m = 2*Nobs */
+mmb_status mmb_problem_sizes(const mmb_problem *p, int32_t *n_params,
+                             int32_t *n_obs, int32_t *n_errors);
+
+/* errorToMarkerList [Nobs*2] (marker, frame); paramToAttrList [n*2]
+ * (attr, frame | -1).  Either pointer may be NULL. */
+mmb_status mmb_get_index_maps(const mmb_problem *p, int32_t *error_to_marker,
+                              int32_t *param_to_attr);
+/* normalised marker weights [Nobs] (adjust_relationships.cpp:166-182) */
+mmb_status mmb_get_marker_weights(const mmb_problem *p, double *weights);
+
+/* get_initial_parameters(), adjust_base.cpp:260: x[n] in solver space */
+mmb_status mmb_get_initial_parameters(const mmb_problem *p, double *x);
+
+/* solveFunc iflag=1 (adjust_solveFunc.cpp:262): fvec[m]; optional
+ * error_dist[Nobs] (errorDistanceList, px) */
+mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec,
+                              double *error_dist);
+
+/* solveFunc iflag=2 (adjust_solveFunc.cpp:482): dense column-major
+ * fjac[n * ldfjac], ldfjac >= m, exactly what cminpack receives. */
+mmb_status mmb_eval_jacobian_dense(mmb_problem *p, const double *x,
+                                   double *fjac, int32_t ldfjac);
+
+/* Same Jacobian in the compact block layout the device keeps.  For
+ * observation i the k = k_max local columns are
+ *   values [c * m + 2*i + {0,1}],  column ids [i * k_max + c] (-1 = unused).
+ * Call with NULL outputs to query k_max. */
+mmb_status mmb_eval_jacobian_blocks(mmb_problem *p, const double *x,
+                                    double *values, int32_t *col_ids,
+                                    int32_t *k_max);
+
+/* The LM solve (solve_3d_cminpack_lmder + tail of solveFrames).
+ * x_out[n] solver-space parameters, attr_values_out[n] external values
+ * (what set_maya_attribute_values writes), error_dist_out[Nobs] px. */
+mmb_status mmb_solve(mmb_problem *p, mmb_result *result, double *x_out,
+                     double *attr_values_out, double *error_dist_out);
+
+/* MComputation::isInterruptRequested analogue; callable from another thread */
+void mmb_request_cancel(mmb_problem *p);
+
+/* device-side benchmarking hooks (inputs already resident in HBM):
+ * run `reps` back-to-back residual+FD-Jacobian evaluations at the initial
+ * parameters on the problem's stream; returns mean ms per evaluation measured
+ * with CUDA events and the number of kernel launches issued. */
+mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
+                          double *ms_per_eval, int32_t *launches);
+
+const char *mmb_status_string(mmb_status s);
+const char *mmb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MMSOLVER_B200_H */

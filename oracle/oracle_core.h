@@ -1,0 +1,306 @@
+// TEST INFRASTRUCTURE ONLY.
+//
+// CPU oracle for the mmSolver LM solve hot path: a single-threaded, scalar
+// FP64 restatement of the reference's algorithm with the reference's own cost
+// structure (one scene evaluation per Jacobian column, dense column-major J,
+// dense pivoted-QR lmder).  Only tests/, __graft_entry__.smoke() and
+// bench.py's cpu_baseline / --impl reference legs may use it; the product
+// path never does.
+//
+// Followed reference code (paths relative to /root/reference):
+//   src/mmSolver/adjust/adjust_relationships.cpp:75-337,565-617  index maps
+//   src/mmSolver/adjust/adjust_base.cpp:194-295,346-372,713-1287,1297-1488
+//   src/mmSolver/adjust/adjust_setParameters.cpp:174-276
+//   src/mmSolver/adjust/adjust_measureErrors.cpp:392-562
+//   src/mmSolver/adjust/adjust_solveFunc.cpp:148-226,262-525
+//   src/mmSolver/adjust/adjust_cminpack_lmder.cpp:64-198
+//   lib/rust/mmscenegraph/src/scene/flat.rs:172-358, math/dag.rs:120-327
+//
+// Parity pinning: see tests/test_oracle_*.py (Rust reprojection KATs,
+// test1.py / test_deviation_calculation.py / test_marker_weight.py scenes
+// restated as arrays, scipy MINPACK cross-check, oracle/_ref lens library).
+#pragma once
+#include <cfloat>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <map>
+#include <vector>
+
+#include "../include/mmsolver_b200.h"
+#include "oracle_lens.h"
+#include "oracle_math.h"
+#include "oracle_minpack.h"
+
+using namespace orc;
+
+struct orc_problem {
+    // deep copy of the scene
+    int F = 0, T = 0, C = 0, B = 0, M = 0, L = 0, A = 0;
+    std::vector<int32_t> frames;
+    std::vector<double> stat, anim;  // live attribute store (AttrDataBlock)
+    std::vector<double> stat0, anim0;
+    std::vector<int32_t> tfm_parent, tfm_roo, tfm_attrs;
+    std::vector<int32_t> cam_tfm, cam_attrs, cam_fit, cam_rw, cam_rh, cam_lens;
+    std::vector<int32_t> bnd_tfm, mkr_cam, mkr_bnd;
+    std::vector<double> mkr_x, mkr_y, mkr_w;
+    std::vector<uint8_t> mkr_en;
+    std::vector<int32_t> lens_model, lens_attrs;
+    std::vector<double> lens_cam;
+    std::vector<int32_t> attr_ref;
+    std::vector<double> attr_min, attr_max, attr_off, attr_scl;
+    mmb_options opt;
+    // index maps
+    std::vector<std::pair<int, int>> errorToMarker, paramToAttr;
+    std::vector<double> markerWeight;         // normalised
+    std::vector<std::vector<bool>> paramFrame; // n x F
+    std::vector<std::vector<bool>> markerToAttr; // M x A (structural)
+    int n = 0, nobs = 0, m = 0;
+    // work
+    std::vector<double> previousParam, errorList, errorDist;
+    std::vector<double> out_points, out_markers;  // flat.rs out_*_list [M*F*2]
+    std::vector<M4> world;                       // [T*F]
+    int iterNum = 0, jacIterNum = 0, funcEvalNum = 0;
+    bool faithful_eval = true;  // evaluate whole scene on every call
+    bool central_literal = false;  // see func_jacobian
+};
+
+static inline double attr_get(const orc_problem *p, int32_t ref, int f) {
+    // datablock.rs:76-91 get_attr_value
+    if (ref >= 0) return p->stat[ref];
+    return p->anim[(size_t)(-ref - 1) * p->F + f];
+}
+static inline void attr_set(orc_problem *p, int32_t ref, int f, double v) {
+    // datablock.rs:93-111: static ignores the frame
+    if (ref >= 0) p->stat[ref] = v;
+    else p->anim[(size_t)(-ref - 1) * p->F + f] = v;
+}
+
+// adjust_base.cpp:194-220
+static double boundInternalToExternal(double value, double xmin, double xmax,
+                                      double offset, double scale) {
+    const double float_max = std::numeric_limits<float>::max();
+    if ((xmin <= -float_max) && (xmax >= float_max)) {
+        value = (value / scale) - offset;
+        value = std::max<double>(value, xmin);
+        value = std::min<double>(value, xmax);
+        return value;
+    } else if (xmax >= float_max) {
+        value = xmin - (1.0 + std::sqrt(value * value + 1.0));
+    } else if (xmin <= -float_max) {
+        value = xmax + (1.0 - std::sqrt(value * value + 1.0));
+    } else {
+        value = xmin + ((xmax - xmin) / 2.0) * (std::sin(value) + 1.0);
+    }
+    value = (value / scale) - offset;
+    value = std::max<double>(value, xmin);
+    value = std::min<double>(value, xmax);
+    return value;
+}
+
+// adjust_base.cpp:225-258 (quirks kept: `xmin <= float_max` test at :239)
+static double boundExternalToInternal(double value, double xmin, double xmax,
+                                      double offset, double scale) {
+    value = std::max<double>(value, xmin);
+    value = std::min<double>(value, xmax);
+    value = (value * scale) + offset;
+    xmin = (xmin * scale) + offset;
+    xmax = (xmax * scale) + offset;
+    const double float_max = std::numeric_limits<float>::max();
+    if ((xmin <= float_max) && (xmax >= float_max)) {
+        return value;
+    } else if (xmax >= float_max) {
+        value = std::sqrt(std::pow(((value - xmin) + 1.0), 2.0) - 1.0);
+    } else if (xmin <= -float_max) {
+        value = std::sqrt(std::pow((xmax - value) + 1.0, 2.0) - 1.0);
+    } else {
+        value = std::asin((2.0 * (value - xmin) / (xmax - xmin)) - 1.0);
+    }
+    return value;
+}
+
+// Which attr-store refs feed marker m?  Structural restatement of the
+// marker->attr "affects" relationship (adjust_relationships.cpp:369-466 asks
+// Maya's DG; here the hierarchy is explicit).
+static bool marker_uses_ref(const orc_problem *p, int mk, int32_t ref) {
+    auto chain_has = [&](int t) {
+        while (t >= 0) {
+            for (int k = 0; k < 9; ++k) if (p->tfm_attrs[t * 9 + k] == ref) return true;
+            t = p->tfm_parent[t];
+        }
+        return false;
+    };
+    const int c = p->mkr_cam[mk], b = p->mkr_bnd[mk];
+    if (chain_has(p->cam_tfm[c]) || chain_has(p->bnd_tfm[b])) return true;
+    for (int k = 0; k < 8; ++k) if (p->cam_attrs[c * 8 + k] == ref) return true;
+    const int l = p->cam_lens[c];
+    if (l >= 0)
+        for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k)
+            if (p->lens_attrs[l * MMB_LENS_MAX_COEFFS + k] == ref) return true;
+    return false;
+}
+
+static void build_index_maps(orc_problem *p) {
+    const int F = p->F;
+    // countUpNumberOfErrors, adjust_relationships.cpp:75-221
+    p->errorToMarker.clear(); p->markerWeight.clear();
+    std::map<int, double> weightMaxPerFrame;
+    for (int i = 0; i < p->M; ++i) {
+        for (int j = 0; j < F; ++j) {
+            const bool enable = p->mkr_en[(size_t)i * F + j] != 0;
+            const double weight = p->mkr_w[(size_t)i * F + j];
+            if (enable && (weight > 0.0)) {
+                p->errorToMarker.push_back({i, j});
+                p->markerWeight.push_back(weight);
+                auto it = weightMaxPerFrame.find(j);
+                double wmax = weight;
+                if (it != weightMaxPerFrame.end()) { wmax = it->second; if (weight > wmax) wmax = weight; }
+                weightMaxPerFrame[j] = wmax;
+            }
+        }
+    }
+    for (size_t i = 0; i < p->errorToMarker.size(); ++i)
+        p->markerWeight[i] = p->markerWeight[i] / weightMaxPerFrame[p->errorToMarker[i].second];
+    p->nobs = (int)p->errorToMarker.size();
+    p->m = 2 * p->nobs;
+    // countUpNumberOfUnknownParameters, adjust_relationships.cpp:223-337
+    p->paramToAttr.clear(); p->paramFrame.clear();
+    for (int i = 0; i < p->A; ++i) {
+        if (p->attr_ref[i] < 0) {
+            for (int j = 0; j < F; ++j) {
+                p->paramToAttr.push_back({i, j});
+                std::vector<bool> fr(F, false); fr[j] = true;
+                p->paramFrame.push_back(fr);
+            }
+        } else {
+            p->paramToAttr.push_back({i, -1});
+            p->paramFrame.push_back(std::vector<bool>(F, true));
+        }
+    }
+    p->n = (int)p->paramToAttr.size();
+    p->markerToAttr.assign(p->M, std::vector<bool>(p->A, false));
+    for (int i = 0; i < p->M; ++i)
+        for (int j = 0; j < p->A; ++j) p->markerToAttr[i][j] = marker_uses_ref(p, i, p->attr_ref[j]);
+    p->previousParam.assign(p->n, 0.0);
+    p->errorList.assign(p->m, 0.0);
+    p->errorDist.assign(p->nobs, 0.0);
+}
+
+// flat.rs:172-358 FlatScene::evaluate (all transforms x all frames)
+static void evaluate_scene(orc_problem *p, const std::vector<bool> *frameEnable) {
+    const int F = p->F;
+    p->world.resize((size_t)p->T * F);
+    const bool all = p->faithful_eval || frameEnable == nullptr;
+    for (int i = 0; i < p->T; ++i) {
+        const int32_t *a = &p->tfm_attrs[i * 9];
+        for (int f = 0; f < F; ++f) {
+            if (!all && !(*frameEnable)[f]) continue;
+            M4 local = local_matrix(attr_get(p, a[0], f), attr_get(p, a[1], f), attr_get(p, a[2], f),
+                                    attr_get(p, a[3], f), attr_get(p, a[4], f), attr_get(p, a[5], f),
+                                    attr_get(p, a[6], f), attr_get(p, a[7], f), attr_get(p, a[8], f),
+                                    p->tfm_roo[i]);
+            const int par = p->tfm_parent[i];
+            p->world[(size_t)i * F + f] = par >= 0 ? m4_mul(p->world[(size_t)par * F + f], local) : local;
+        }
+    }
+    p->out_points.resize((size_t)p->M * F * 2);
+    p->out_markers.resize((size_t)p->M * F * 2);
+    for (int mk = 0; mk < p->M; ++mk) {
+        const int c = p->mkr_cam[mk], b = p->mkr_bnd[mk];
+        const int32_t *ca = &p->cam_attrs[c * 8];
+        for (int f = 0; f < F; ++f) {
+            if (!all && !(*frameEnable)[f]) continue;
+            // dag.rs:120-172 compute_projection_matrix_with_attrs
+            const double focal = attr_get(p, ca[2], f);
+            const double sx_mm = attr_get(p, ca[0], f), sy_mm = attr_get(p, ca[1], f);
+            const double sx_in = sx_mm * MM_TO_INCH, sy_in = sy_mm * MM_TO_INCH;
+            const double ox_in = attr_get(p, ca[3], f) * MM_TO_INCH;
+            const double oy_in = attr_get(p, ca[4], f) * MM_TO_INCH;
+            const double near_clip = 0.1;  // dag.rs:152
+            const double far_clip = attr_get(p, ca[6], f);
+            const double cam_scale = attr_get(p, ca[7], f);
+            M4 proj = projection_matrix(focal, sx_in, sy_in, ox_in, oy_in, (double)p->cam_rw[c],
+                                        (double)p->cam_rh[c], p->cam_fit[c], near_clip, far_clip, cam_scale);
+            double px, py;
+            reproject_normalised(p->world[(size_t)p->cam_tfm[c] * F + f], proj,
+                                 p->world[(size_t)p->bnd_tfm[b] * F + f], px, py);
+            const size_t o = ((size_t)mk * F + f) * 2;
+            p->out_points[o] = px; p->out_points[o + 1] = py;
+            // flat.rs:327-348
+            double mx = p->mkr_x[(size_t)mk * F + f], my = p->mkr_y[(size_t)mk * F + f];
+            scale_marker_film_fit(p->cam_fit[c], sx_mm / sy_mm,
+                                  (double)p->cam_rw[c] / (double)p->cam_rh[c], mx, my);
+            p->out_markers[o] = mx; p->out_markers[o + 1] = my;
+        }
+    }
+}
+
+static LensEval lens_at(const orc_problem *p, int l, int f) {
+    LensEval L; L.model = p->lens_model[l];
+    for (int k = 0; k < 6; ++k) L.cam[k] = p->lens_cam[l * 6 + k];
+    for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k) {
+        const int32_t r = p->lens_attrs[l * MMB_LENS_MAX_COEFFS + k];
+        L.c[k] = (r == INT32_MIN) ? 0.0 : attr_get(p, r, f);
+    }
+    lens_prepare(L);
+    return L;
+}
+
+// adjust_setParameters.cpp:174-276.  Lens coefficients live in the same attr
+// store here, so the lens branch (:201-222) and the AttrDataBlock branch
+// (:225-233) become one write (intended [attr*F + f] indexing).
+static void setParameters(orc_problem *p, const double *x) {
+    for (int i = 0; i < p->n; ++i) {
+        const int ai = p->paramToAttr[i].first, fi = p->paramToAttr[i].second;
+        const double real = boundInternalToExternal(x[i], p->attr_min[ai], p->attr_max[ai],
+                                                    p->attr_off[ai], p->attr_scl[ai]);
+        attr_set(p, p->attr_ref[ai], fi < 0 ? 0 : fi, real);
+    }
+    for (int j = 0; j < p->n; ++j) p->previousParam[j] = x[j];
+}
+
+// adjust_measureErrors.cpp:392-562 (mmSceneGraph variant)
+static void measureErrors(orc_problem *p, const std::vector<bool> &frameEnable,
+                          const std::vector<bool> &errorMeasurements, double *errors,
+                          double &eavg, double &emax, double &emin) {
+    eavg = 0.0; emax = -0.0; emin = std::numeric_limits<double>::max();
+    evaluate_scene(p, &frameEnable);
+    const double imageWidth = p->opt.image_width;
+    const int F = p->F;
+    int measured = 0;
+    for (int i = 0; i < p->nobs; ++i) {
+        const int markerIndex = p->errorToMarker[i].first, frameIndex = p->errorToMarker[i].second;
+        if (!frameEnable[frameIndex]) continue;
+        if (!errorMeasurements[i]) continue;
+        const double w = std::sqrt(p->markerWeight[i]);
+        const size_t o = ((size_t)markerIndex * F + frameIndex) * 2;
+        const double mkr_x = p->out_markers[o], mkr_y = p->out_markers[o + 1];
+        double point_x = p->out_points[o], point_y = p->out_points[o + 1];
+        // lens: adjust_measureErrors.cpp:461-479
+        int lm = markerIndex, lf = frameIndex;
+        if (p->opt.lens_index_literal) {  // literal [markerIndex + frameIndex] read
+            const int idx = markerIndex + frameIndex;
+            lm = idx / F; lf = idx % F;
+            if (lm >= p->M) lm = -1;
+        }
+        const int l = lm >= 0 ? p->cam_lens[p->mkr_cam[lm]] : -1;
+        if (l >= 0 && p->lens_model[l] != 0) {
+            LensEval L = lens_at(p, l, lf);
+            double ox = point_x, oy = point_y;
+            lens_distort(L, point_x, point_y, ox, oy);
+            if (std::isfinite(ox)) point_x = ox;
+            if (std::isfinite(oy)) point_y = oy;
+        }
+        const double dx = std::fabs(mkr_x - point_x), dy = std::fabs(mkr_y - point_y);
+        const double dxp = dx * imageWidth, dyp = dy * imageWidth;
+        errors[2 * i] = dxp * w * 1.0;
+        errors[2 * i + 1] = dyp * w * 1.0;
+        p->errorList[2 * i] = dxp; p->errorList[2 * i + 1] = dyp;
+        const double d = std::sqrt((dx * dx) + (dy * dy)) * imageWidth;
+        p->errorDist[i] = d;
+        eavg += d; if (d > emax) emax = d; if (d < emin) emin = d;
+        ++measured;
+    }
+    if (measured == 0) { emax = emin = eavg = 0.0; } else { eavg *= 1.0 / measured; }
+}
