@@ -241,6 +241,8 @@ mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
                           double *ms_per_eval, int32_t *launches);
 
 const char *mmb_status_string(mmb_status s);
+/* detail of the last failing call on this thread (static storage) */
+const char *mmb_last_error(void);
 const char *mmb_version(void);
 
 #ifdef __cplusplus

@@ -1,0 +1,258 @@
+// extern "C" surface declared in include/mmsolver_b200.h.
+#include <cstring>
+#include <new>
+
+#include "device_problem.h"
+#include "lm.h"
+
+using namespace mmb;
+
+struct mmb_problem {
+    DeviceProblem *dp;
+};
+
+static const char *k_reasons[9] = {
+    // adjust_cminpack_base.h:51-83
+    "Improper input parameters",
+    "Both actual and predicted relative reductions in the sum of squares are at most ftol.",
+    "Relative error between two consecutive iterates is at most xtol.",
+    "Conditions for info = 1 and info = 2 both hold.",
+    "The cosine of the angle between fvec and any column of the Jacobian is at most gtol in absolute value.",
+    "Number of calls to fcn has reached or exceeded maxfev.",
+    "'ftol' is too small. No further reduction in the sum of squares is possible.",
+    "'xtol' is too small. No further improvement in the approximate solution x is possible.",
+    "'gtol' is too small. fvec is orthogonal to the columns of the Jacobian to machine precision."};
+
+const char *mmb_reason_string(int info) { return (info >= 0 && info < 9) ? k_reasons[info] : "User interrupted or solver error."; }
+
+extern "C" {
+
+void mmb_options_default(mmb_options *o) {
+    if (!o) return;
+    std::memset(o, 0, sizeof(*o));
+    o->iter_max = 100;        // arg_flags_solve_info.h ITERATIONS_DEFAULT_VALUE
+    o->tau = 1.0;
+    o->eps1 = 1e-6; o->eps2 = 1e-6; o->eps3 = 1e-6;
+    o->delta = 1e-4;
+    o->auto_diff_type = 0;
+    o->auto_param_scale = 1;
+    o->robust_loss_type = 0;
+    o->robust_loss_scale = 1.0;
+    o->scene_graph_mode = 2;
+    o->solver_type = 2;
+    o->time_eval_mode = 0;
+    o->accept_only_better = 1;
+    o->image_width = 2048.0;
+    o->frame_solve_mode = 0;
+    o->remove_unused_markers = 1;
+    o->remove_unused_attributes = 1;
+    o->lens_index_literal = 0;
+    o->device = 0;
+}
+
+mmb_status mmb_problem_create(const mmb_scene_desc *scene, const mmb_options *opt, mmb_problem **out) {
+    if (!scene || !opt || !out) return MMB_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    try {
+        DeviceProblem *dp = nullptr;
+        mmb_status st = device_problem_create(scene, opt, &dp);
+        if (st != MMB_OK) return st;
+        mmb_problem *p = new mmb_problem{dp};
+        *out = p;
+        return MMB_OK;
+    } catch (const std::bad_alloc &) {
+        set_last_error("host allocation failed");
+        return MMB_ERR_INTERNAL;
+    } catch (...) {
+        set_last_error("unexpected exception");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+void mmb_problem_destroy(mmb_problem *p) {
+    if (!p) return;
+    delete p->dp;
+    delete p;
+}
+
+mmb_status mmb_problem_sizes(const mmb_problem *p, int32_t *n, int32_t *nobs, int32_t *m) {
+    if (!p) return MMB_ERR_INVALID_ARGUMENT;
+    if (n) *n = p->dp->hp.n;
+    if (nobs) *nobs = p->dp->hp.nobs;
+    if (m) *m = p->dp->hp.m;
+    return MMB_OK;
+}
+
+mmb_status mmb_get_index_maps(const mmb_problem *p, int32_t *e2m, int32_t *p2a) {
+    if (!p) return MMB_ERR_INVALID_ARGUMENT;
+    const HostProblem &hp = p->dp->hp;
+    if (e2m) for (int i = 0; i < hp.nobs; ++i) { e2m[2 * i] = hp.err_marker[i]; e2m[2 * i + 1] = hp.err_frame[i]; }
+    if (p2a) for (int i = 0; i < hp.n; ++i) { p2a[2 * i] = hp.par_attr[i]; p2a[2 * i + 1] = hp.par_frame[i]; }
+    return MMB_OK;
+}
+
+mmb_status mmb_get_marker_weights(const mmb_problem *p, double *w) {
+    if (!p || !w) return MMB_ERR_INVALID_ARGUMENT;
+    const HostProblem &hp = p->dp->hp;
+    for (int i = 0; i < hp.nobs; ++i) w[i] = hp.obs_w[i];
+    return MMB_OK;
+}
+
+mmb_status mmb_get_initial_parameters(const mmb_problem *p, double *x) {
+    if (!p || !x) return MMB_ERR_INVALID_ARGUMENT;
+    const HostProblem &hp = p->dp->hp;
+    for (int i = 0; i < hp.n; ++i) {
+        const int a = hp.par_attr[i], f = hp.par_frame[i];
+        const int32_t ref = hp.attr_ref[a];
+        const double v = ref >= 0 ? hp.stat0[ref] : hp.anim0[(size_t)(-ref - 1) * hp.F + f];
+        x[i] = bound_external_to_internal(v, hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
+    }
+    return MMB_OK;
+}
+
+static mmb_status upload_x(DeviceProblem *dp, const double *x) {
+    MMB_CUDA_CHECK(cudaSetDevice(dp->device));
+    if (dp->hp.n)
+        MMB_CUDA_CHECK(cudaMemcpyAsync(dp->d_x, x, sizeof(double) * dp->hp.n, cudaMemcpyHostToDevice, dp->stream));
+    return MMB_OK;
+}
+
+mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec, double *error_dist) {
+    if (!p || !x || !fvec) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    mmb_status st;
+    if ((st = upload_x(dp, x)) != MMB_OK) return st;
+    if ((st = launch_reset_store(dp)) != MMB_OK) return st;
+    if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
+    if ((st = launch_variants(dp, dp->d_x, false)) != MMB_OK) return st;
+    if ((st = launch_residuals(dp, dp->d_fvec, dp->d_dist)) != MMB_OK) return st;
+    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
+    if (error_dist)
+        MMB_CUDA_CHECK(cudaMemcpyAsync(error_dist, dp->d_dist, sizeof(double) * dp->hp.nobs, cudaMemcpyDeviceToHost, dp->stream));
+    MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
+    return MMB_OK;
+}
+
+static mmb_status run_jacobian(DeviceProblem *dp, const double *x) {
+    mmb_status st;
+    if ((st = ensure_jacobian_buffers(dp)) != MMB_OK) return st;
+    if ((st = upload_x(dp, x)) != MMB_OK) return st;
+    if ((st = launch_reset_store(dp)) != MMB_OK) return st;
+    if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
+    if ((st = launch_variants(dp, dp->d_x, true)) != MMB_OK) return st;
+    if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, dp->d_cols)) != MMB_OK) return st;
+    return MMB_OK;
+}
+
+mmb_status mmb_eval_jacobian_blocks(mmb_problem *p, const double *x, double *values, int32_t *col_ids,
+                                    int32_t *k_max) {
+    if (!p) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    if (k_max) *k_max = dp->ds.kmax;
+    if (!values && !col_ids) return MMB_OK;
+    if (!x) return MMB_ERR_INVALID_ARGUMENT;
+    mmb_status st = run_jacobian(dp, x);
+    if (st != MMB_OK) return st;
+    const size_t k = dp->ds.kmax;
+    if (values)
+        MMB_CUDA_CHECK(cudaMemcpyAsync(values, dp->d_jac, sizeof(double) * k * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
+    if (col_ids)
+        MMB_CUDA_CHECK(cudaMemcpyAsync(col_ids, dp->d_cols, sizeof(int32_t) * k * dp->hp.nobs, cudaMemcpyDeviceToHost, dp->stream));
+    MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
+    return MMB_OK;
+}
+
+mmb_status mmb_eval_jacobian_dense(mmb_problem *p, const double *x, double *fjac, int32_t ldfjac) {
+    if (!p || !x || !fjac) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    const HostProblem &hp = dp->hp;
+    if (ldfjac < hp.m) return MMB_ERR_INVALID_ARGUMENT;
+    const size_t k = dp->ds.kmax;
+    std::vector<double> vals(k * (size_t)hp.m);
+    std::vector<int32_t> cols(k * (size_t)hp.nobs);
+    int32_t kk = 0;
+    mmb_status st = mmb_eval_jacobian_blocks(p, x, vals.data(), cols.data(), &kk);
+    if (st != MMB_OK) return st;
+    // layout conversion only: block columns -> cminpack's dense column-major
+    for (size_t j = 0; j < (size_t)hp.n; ++j) std::memset(&fjac[j * ldfjac], 0, sizeof(double) * hp.m);
+    for (size_t i = 0; i < (size_t)hp.nobs; ++i)
+        for (size_t c = 0; c < k; ++c) {
+            const int32_t pid = cols[i * k + c];
+            if (pid < 0) continue;
+            fjac[(size_t)pid * ldfjac + 2 * i] = vals[c * hp.m + 2 * i];
+            fjac[(size_t)pid * ldfjac + 2 * i + 1] = vals[c * hp.m + 2 * i + 1];
+        }
+    return MMB_OK;
+}
+
+mmb_status mmb_solve(mmb_problem *p, mmb_result *result, double *x_out, double *attr_values_out,
+                     double *error_dist_out) {
+    if (!p || !result) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        mmb_status st = lm_solve(p->dp, result, x_out, attr_values_out, error_dist_out);
+        result->reason_str = mmb_reason_string(result->reason_num);
+        return st;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_solve");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+void mmb_request_cancel(mmb_problem *p) {
+    if (p) p->dp->cancel = 1;
+}
+
+mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2, double *ms_per_eval, int32_t *launches) {
+    if (!p || reps <= 0) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    const HostProblem &hp = dp->hp;
+    std::vector<double> x(hp.n);
+    mmb_get_initial_parameters(p, x.data());
+    mmb_status st = run_jacobian(dp, x.data());  // warm-up + buffers
+    if (st != MMB_OK) return st;
+    double *flush = nullptr;
+    const size_t flush_n = (size_t)256 << 20 >> 3;  // 256 MiB > 126 MB L2
+    if (flush_l2) MMB_CUDA_CHECK(cudaMalloc(&flush, flush_n * sizeof(double)));
+    cudaEvent_t e0, e1;
+    MMB_CUDA_CHECK(cudaEventCreate(&e0));
+    MMB_CUDA_CHECK(cudaEventCreate(&e1));
+    double total_ms = 0.0;
+    const long long l0 = dp->launches;
+    for (int r = 0; r < reps; ++r) {
+        if (flush) MMB_CUDA_CHECK(cudaMemsetAsync(flush, r & 0xff, flush_n * sizeof(double), dp->stream));
+        MMB_CUDA_CHECK(cudaEventRecord(e0, dp->stream));
+        if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
+        if ((st = launch_variants(dp, dp->d_x, true)) != MMB_OK) return st;
+        if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, nullptr)) != MMB_OK) return st;
+        MMB_CUDA_CHECK(cudaEventRecord(e1, dp->stream));
+        MMB_CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        MMB_CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        total_ms += ms;
+    }
+    if (ms_per_eval) *ms_per_eval = total_ms / reps;
+    if (launches) *launches = (int32_t)(dp->launches - l0);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (flush) cudaFree(flush);
+    return MMB_OK;
+}
+
+const char *mmb_status_string(mmb_status s) {
+    switch (s) {
+        case MMB_OK: return "ok";
+        case MMB_ERR_INVALID_ARGUMENT: return "invalid argument";
+        case MMB_ERR_CUDA: return "CUDA error";
+        case MMB_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU path)";
+        case MMB_ERR_NOT_ENOUGH_OBJECTS: return "not enough markers/attributes to solve";
+        case MMB_ERR_MORE_PARAMS_THAN_ERRORS: return "more unknown parameters than error measurements";
+        case MMB_ERR_UNSUPPORTED: return "unsupported option";
+        case MMB_ERR_INTERNAL: return "internal error";
+        default: return "unknown status";
+    }
+}
+
+const char *mmb_last_error(void) { return get_last_error().c_str(); }
+
+const char *mmb_version(void) { return "mmsolver_b200 0.1.0 (sm_100a)"; }
+
+}  // extern "C"

@@ -1,0 +1,89 @@
+// Device-resident problem: owns every HBM buffer of one solve handle.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "eval_bodies.cuh"
+#include "problem.h"
+
+namespace mmb {
+
+#define MMB_CUDA_CHECK(expr)                                                      \
+    do {                                                                          \
+        cudaError_t _e = (expr);                                                  \
+        if (_e != cudaSuccess) {                                                  \
+            set_last_error(std::string(#expr) + ": " + cudaGetErrorString(_e));   \
+            return MMB_ERR_CUDA;                                                  \
+        }                                                                         \
+    } while (0)
+
+void set_last_error(const std::string &msg);
+const std::string &get_last_error();
+
+// Simple arena of device allocations freed together.
+struct DeviceArena {
+    std::vector<void *> ptrs;
+    size_t bytes = 0;
+    ~DeviceArena() { release(); }
+    void release() {
+        for (void *p : ptrs) cudaFree(p);
+        ptrs.clear();
+        bytes = 0;
+    }
+    template <typename T>
+    cudaError_t alloc(T **out, size_t count) {
+        *out = nullptr;
+        if (count == 0) count = 1;
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+        if (e != cudaSuccess) return e;
+        ptrs.push_back(p);
+        bytes += count * sizeof(T);
+        *out = (T *)p;
+        return cudaSuccess;
+    }
+    template <typename T>
+    cudaError_t upload(T **out, const std::vector<T> &v) {
+        cudaError_t e = alloc(out, v.size());
+        if (e != cudaSuccess) return e;
+        if (!v.empty()) e = cudaMemcpy(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+        return e;
+    }
+};
+
+struct LmWorkspace;  // lm_global.cu
+
+struct DeviceProblem {
+    HostProblem hp;
+    DevScene ds;        // device pointers (passed by value to kernels)
+    DeviceArena arena;
+    cudaStream_t stream = nullptr;
+    int device = 0;
+    // work vectors
+    double *d_x = nullptr;      // [n] parameters (reference order)
+    double *d_fvec = nullptr;   // [m]
+    double *d_dist = nullptr;   // [nobs]
+    double *d_jac = nullptr;    // [kmax * m] block Jacobian (lazy)
+    int32_t *d_cols = nullptr;  // [nobs * kmax] (lazy)
+    double *d_stat0 = nullptr, *d_anim0 = nullptr;  // pristine attribute store
+    LmWorkspace *lm = nullptr;
+    volatile int cancel = 0;
+    long long launches = 0;     // kernels launched by this handle
+
+    ~DeviceProblem();
+};
+
+mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt, DeviceProblem **out);
+mmb_status ensure_jacobian_buffers(DeviceProblem *p);
+
+// kernel launchers (kernels.cu); all asynchronous on p->stream
+mmb_status launch_reset_store(DeviceProblem *p);                 // attribute store <- pristine
+mmb_status launch_set_parameters(DeviceProblem *p, const double *d_x);
+mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed);
+mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist);
+mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols);
+
+}  // namespace mmb

@@ -1,0 +1,340 @@
+// Per-thread bodies of the scene / residual / FD-Jacobian kernels.
+//
+// Path replaced (reference):
+//   setParameters_mmSceneGraph          adjust_setParameters.cpp:174-250
+//   FlatScene::evaluate                 lib/rust/mmscenegraph/src/scene/flat.rs:172-358
+//   measureErrors_mmSceneGraph          adjust_measureErrors.cpp:392-521
+//   solveFunc_calculateJacobianMatrix*  adjust_solveFunc.cpp:305-525
+//
+// The reference re-evaluates the whole scene once per Jacobian column.  Here
+// every (entity, frame, perturbed parameter) "variant" is evaluated once in a
+// tiny launch, and a single streaming launch over observations combines them.
+#pragma once
+#include "device_math.cuh"
+
+namespace mmb {
+
+struct PlanEntryD {
+    int32_t attr;
+    int16_t cam_var, bnd_var, lens_var, pad;
+};
+
+// Everything the kernels read; plain device pointers.
+struct DevScene {
+    int F, T, C, B, M, L, A, n, nobs, kmax;
+    int central;        // autoDiffType == 1
+    int dense_grid;     // obs i == marker*F + frame
+    int any_lens;
+    int lens_literal;   // reference's [markerIndex + frameIndex] lens read
+    double delta;       // SolverOptions.delta
+    double image_width;
+    // attribute store (AttrDataBlock): live values
+    double *stat;       // [num_static]
+    double *anim;       // [num_anim * F]
+    // scene
+    const int32_t *tfm_parent, *tfm_roo, *tfm_attrs;
+    const int32_t *cam_tfm, *cam_attrs, *cam_fit, *cam_rw, *cam_rh, *cam_lens;
+    const int32_t *bnd_tfm, *mkr_cam, *mkr_bnd;
+    const int32_t *lens_model, *lens_attrs;
+    const double *lens_cam;
+    // solver attrs / params
+    const int32_t *attr_ref, *attr_param_base;
+    const uint8_t *attr_anim;
+    const double *attr_min, *attr_max, *attr_off, *attr_scl;
+    const int32_t *par_attr, *par_frame;
+    // observations (errorToMarkerList order)
+    const int32_t *err_marker, *err_frame;
+    const double *obs_mx, *obs_my, *obs_w;
+    // variant tables
+    double *cam_tab, *bnd_tab, *lens_tab;
+    const int64_t *cam_off, *bnd_off, *lens_off;
+    const int32_t *cam_fs, *bnd_fs, *lens_fs;
+    const int32_t *cam_ndep, *bnd_ndep, *lens_ndep;  // number of deps
+    // variant jobs
+    const int32_t *cam_job_ent, *cam_job_var, *cam_job_attr;
+    const int64_t *cam_job_start;
+    int cam_njobs; long long cam_jobs_total;
+    const int32_t *bnd_job_ent, *bnd_job_var, *bnd_job_attr;
+    const int64_t *bnd_job_start;
+    int bnd_njobs; long long bnd_jobs_total;
+    const int32_t *lens_job_ent, *lens_job_var, *lens_job_attr;
+    const int64_t *lens_job_start;
+    int lens_njobs; long long lens_jobs_total;
+    // plan
+    const PlanEntryD *plan;  // [M*kmax]
+    const int32_t *mkr_k;    // [M]
+    // per-parameter FD step actually used (deltaA, deltaB) for x
+    double *par_delta_a, *par_delta_b;  // [n]
+};
+
+// ---- setParameters: scatter x into the attribute store --------------------
+// adjust_setParameters.cpp:174-250.  One thread per parameter.
+MMB_HD void set_parameter_thread(const DevScene &s, const double *x, int i) {
+    const int a = s.par_attr[i], f = s.par_frame[i];
+    const double real = bound_int_to_ext(x[i], s.attr_min[a], s.attr_max[a], s.attr_off[a], s.attr_scl[a]);
+    const int32_t ref = s.attr_ref[a];
+    if (ref >= 0) s.stat[ref] = real;
+    else s.anim[(size_t)(-ref - 1) * s.F + f] = real;
+    // FD steps for this x (calculateParameterDelta, adjust_solveFunc.cpp:148)
+    const double da = parameter_delta(x[i], s.delta, 1.0, s.attr_min[a], s.attr_max[a]);
+    s.par_delta_a[i] = da;
+    s.par_delta_b[i] = parameter_delta(x[i], s.delta, -1.0, s.attr_min[a], s.attr_max[a]);
+}
+
+// Attribute read with one overridden ref (the perturbed parameter).
+struct AttrView {
+    const double *stat, *anim;
+    int F, f;
+    int32_t ovr_ref;
+    double ovr_val;
+    MMB_HD double get(int32_t ref) const {
+        if (ref == ovr_ref) return ovr_val;
+        if (ref >= 0) return stat[ref];
+        return anim[(size_t)(-ref - 1) * F + f];
+    }
+};
+
+// Which job / frame does flat thread index t belong to? (binary search)
+MMB_HD int find_job(const int64_t *start, int njobs, long long t) {
+    int lo = 0, hi = njobs;  // start[lo] <= t < start[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (start[mid] <= t) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// The perturbed external value of solver attr `a` at frame f for variant v.
+MMB_HD AttrView make_view(const DevScene &s, const double *x, int f, int attr, int var, int ndep) {
+    AttrView v;
+    v.stat = s.stat; v.anim = s.anim; v.F = s.F; v.f = f;
+    v.ovr_ref = INT32_MIN + 1;  // matches no ref (MMB_ATTR_NONE is INT32_MIN)
+    v.ovr_val = 0.0;
+    if (var > 0) {
+        const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
+        const bool second = var > ndep;  // central: variants ndep+1.. use deltaB
+        const double d = second ? s.par_delta_b[p] : s.par_delta_a[p];
+        v.ovr_ref = s.attr_ref[attr];
+        v.ovr_val = bound_int_to_ext(x[p] + d, s.attr_min[attr], s.attr_max[attr], s.attr_off[attr], s.attr_scl[attr]);
+    }
+    return v;
+}
+
+MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
+    // dag.rs:234-327: world = parent_world * local, accumulated leaf -> root
+    Aff w;
+    bool first = true;
+    while (t >= 0) {
+        const int32_t *a = &s.tfm_attrs[t * 9];
+        const Aff l = local_matrix(av.get(a[0]), av.get(a[1]), av.get(a[2]), av.get(a[3]), av.get(a[4]),
+                                   av.get(a[5]), av.get(a[6]), av.get(a[7]), av.get(a[8]), s.tfm_roo[t]);
+        w = first ? l : aff_mul(l, w);
+        first = false;
+        t = s.tfm_parent[t];
+    }
+    return w;
+}
+
+// One thread per (camera, variant, frame): 14 doubles
+//   [0..11] rows 0,1,3 of P*inv(W);  [12],[13] marker film-fit scale
+// table layout: cam_off[c] + ((v*14 + j) * fs + f)
+MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
+    const int job = find_job(s.cam_job_start, s.cam_njobs, t);
+    const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
+    const int f = (int)(t - s.cam_job_start[job]);
+    const int fs = s.cam_fs[c];
+    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c]);
+    const Aff w = world_matrix(s, av, s.cam_tfm[c]);
+    const int32_t *ca = &s.cam_attrs[c * 8];
+    const double sw = av.get(ca[0]), sh = av.get(ca[1]);
+    const Proj p = projection_entries(av.get(ca[2]), sw, sh, av.get(ca[3]), av.get(ca[4]),
+                                      (double)s.cam_rw[c], (double)s.cam_rh[c], s.cam_fit[c],
+                                      0.1 /* dag.rs:152 */, av.get(ca[7]));
+    double out[14];
+    camera_rows(w, p, out);
+    marker_film_fit_scale(s.cam_fit[c], sw / sh, (double)s.cam_rw[c] / (double)s.cam_rh[c], out[12], out[13]);
+    double *dst = s.cam_tab + s.cam_off[c];
+#pragma unroll
+    for (int j = 0; j < 14; ++j) dst[((size_t)v * 14 + j) * fs + f] = out[j];
+}
+
+// One thread per (bundle, variant, frame): world position (3 doubles)
+MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long t) {
+    const int job = find_job(s.bnd_job_start, s.bnd_njobs, t);
+    const int b = s.bnd_job_ent[job], v = s.bnd_job_var[job], attr = s.bnd_job_attr[job];
+    const int f = (int)(t - s.bnd_job_start[job]);
+    const int fs = s.bnd_fs[b];
+    const AttrView av = make_view(s, x, f, attr, v, s.bnd_ndep[b]);
+    const Aff w = world_matrix(s, av, s.bnd_tfm[b]);
+    double *dst = s.bnd_tab + s.bnd_off[b];
+    dst[((size_t)v * 3 + 0) * fs + f] = w.m[3];
+    dst[((size_t)v * 3 + 1) * fs + f] = w.m[7];
+    dst[((size_t)v * 3 + 2) * fs + f] = w.m[11];
+}
+
+// One thread per (lens, variant, frame): prepared lens record (24 doubles)
+MMB_HD void lens_variant_thread(const DevScene &s, const double *x, long long t) {
+    const int job = find_job(s.lens_job_start, s.lens_njobs, t);
+    const int l = s.lens_job_ent[job], v = s.lens_job_var[job], attr = s.lens_job_attr[job];
+    const int f = (int)(t - s.lens_job_start[job]);
+    const int fs = s.lens_fs[l];
+    const AttrView av = make_view(s, x, f, attr, v, s.lens_ndep[l]);
+    double c[14], rec[kLensRec];
+    for (int k = 0; k < 14; ++k) {
+        const int32_t r = s.lens_attrs[l * 14 + k];
+        c[k] = (r == INT32_MIN) ? 0.0 : av.get(r);
+    }
+    lens_prepare(s.lens_model[l], c, &s.lens_cam[l * 6], rec);
+    double *dst = s.lens_tab + s.lens_off[l];
+    for (int j = 0; j < kLensRec; ++j) dst[((size_t)v * kLensRec + j) * fs + f] = rec[j];
+}
+
+// ---- observation evaluation ------------------------------------------------
+struct ObsCtx {
+    int marker, frame, cam, bnd, lens, lens_frame;
+    double mx, my, w;       // raw marker, sqrt(weight)
+};
+
+MMB_HD void load_cam(const DevScene &s, int c, int v, int f, double *cm /*14*/) {
+    const int fs = s.cam_fs[c];
+    const int ff = fs == 1 ? 0 : f;
+    const double *src = s.cam_tab + s.cam_off[c] + (size_t)v * 14 * fs + ff;
+#pragma unroll
+    for (int j = 0; j < 14; ++j) cm[j] = src[(size_t)j * fs];
+}
+MMB_HD void load_bnd(const DevScene &s, int b, int v, int f, double *bp /*3*/) {
+    const int fs = s.bnd_fs[b];
+    const int ff = fs == 1 ? 0 : f;
+    const double *src = s.bnd_tab + s.bnd_off[b] + (size_t)v * 3 * fs + ff;
+    bp[0] = src[0]; bp[1] = src[fs]; bp[2] = src[2 * (size_t)fs];
+}
+MMB_HD void load_lens(const DevScene &s, int l, int v, int f, double *rec /*24*/) {
+    const int fs = s.lens_fs[l];
+    const int ff = fs == 1 ? 0 : f;
+    const double *src = s.lens_tab + s.lens_off[l] + (size_t)v * kLensRec * fs + ff;
+    for (int j = 0; j < kLensRec; ++j) rec[j] = src[(size_t)j * fs];
+}
+
+// reprojection.rs:27-62 on the reduced rows; then the residual pair
+// (adjust_measureErrors.cpp:481-499).  ex, ey are the weighted residuals.
+MMB_HD void project_point(const double *cm, const double *bp, double &px, double &py) {
+    const double sx = cm[0] * bp[0] + cm[1] * bp[1] + cm[2] * bp[2] + cm[3];
+    const double sy = cm[4] * bp[0] + cm[5] * bp[1] + cm[6] * bp[2] + cm[7];
+    const double sw = cm[8] * bp[0] + cm[9] * bp[1] + cm[10] * bp[2] + cm[11];
+    px = sx / sw * 0.5;
+    py = sy / sw * 0.5;
+}
+
+MMB_HD ObsCtx make_obs(const DevScene &s, int i) {
+    ObsCtx o;
+    if (s.dense_grid) { o.marker = i / s.F; o.frame = i - o.marker * s.F; }
+    else { o.marker = s.err_marker[i]; o.frame = s.err_frame[i]; }
+    o.cam = s.mkr_cam[o.marker]; o.bnd = s.mkr_bnd[o.marker];
+    o.mx = s.obs_mx[i]; o.my = s.obs_my[i]; o.w = sqrt(s.obs_w[i]);
+    o.lens = -1; o.lens_frame = o.frame;
+    if (s.any_lens) {
+        int lm = o.marker;
+        if (s.lens_literal) {  // adjust_measureErrors.cpp:463 literal index
+            const int idx = o.marker + o.frame;
+            lm = idx / s.F; o.lens_frame = idx - lm * s.F;
+            if (lm >= s.M) lm = -1;
+        }
+        if (lm >= 0) {
+            const int l = s.cam_lens[s.mkr_cam[lm]];
+            if (l >= 0 && s.lens_model[l] != 0) o.lens = l;
+        }
+    }
+    return o;
+}
+
+MMB_HD void residual_from(const DevScene &s, const ObsCtx &o, const double *cm, const double *bp,
+                          const double *lens_rec, double &ex, double &ey, double &dist) {
+    double px, py;
+    project_point(cm, bp, px, py);
+    if (lens_rec) {
+        double ox, oy;
+        lens_distort(lens_rec, px, py, ox, oy);
+        px = ox; py = oy;
+    }
+    const double mkx = o.mx * cm[12], mky = o.my * cm[13];
+    const double dx = fabs(mkx - px), dy = fabs(mky - py);
+    const double dxp = dx * s.image_width, dyp = dy * s.image_width;
+    ex = dxp * o.w;
+    ey = dyp * o.w;
+    dist = sqrt((dx * dx) + (dy * dy)) * s.image_width;
+}
+
+// Residuals only (solveFunc iflag=1).  fvec[2i], fvec[2i+1], dist[i].
+MMB_HD void residual_thread(const DevScene &s, int i, double *fvec, double *dist) {
+    const ObsCtx o = make_obs(s, i);
+    double cm[14], bp[3], rec[kLensRec];
+    load_cam(s, o.cam, 0, o.frame, cm);
+    load_bnd(s, o.bnd, 0, o.frame, bp);
+    if (o.lens >= 0) load_lens(s, o.lens, 0, o.lens_frame, rec);
+    double ex, ey, d;
+    residual_from(s, o, cm, bp, o.lens >= 0 ? rec : nullptr, ex, ey, d);
+    fvec[2 * (size_t)i] = ex;
+    fvec[2 * (size_t)i + 1] = ey;
+    if (dist) dist[i] = d;
+}
+
+// Residuals + block Jacobian (solveFunc iflag=1 and iflag=2 fused).
+//   jac[c * m + 2i + {0,1}], col_ids[i * kmax + c] = parameter index or -1
+MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist, double *jac,
+                            int32_t *col_ids) {
+    const ObsCtx o = make_obs(s, i);
+    const size_t m = 2 * (size_t)s.nobs;
+    double cm[14], bp[3], rec[kLensRec];
+    load_cam(s, o.cam, 0, o.frame, cm);
+    load_bnd(s, o.bnd, 0, o.frame, bp);
+    const bool has_lens = o.lens >= 0;
+    if (has_lens) load_lens(s, o.lens, 0, o.lens_frame, rec);
+    double ex, ey, d;
+    residual_from(s, o, cm, bp, has_lens ? rec : nullptr, ex, ey, d);
+    if (fvec) { fvec[2 * (size_t)i] = ex; fvec[2 * (size_t)i + 1] = ey; }
+    if (dist) dist[i] = d;
+    const int k = s.mkr_k[o.marker];
+    const PlanEntryD *pl = s.plan + (size_t)o.marker * s.kmax;
+    const int cnd = s.cam_ndep[o.cam], bnd_nd = s.bnd_ndep[o.bnd];
+    const int lnd = has_lens ? s.lens_ndep[o.lens] : 0;
+    for (int c = 0; c < s.kmax; ++c) {
+        double jx = 0.0, jy = 0.0;
+        int32_t pid = -1;
+        if (c < k) {
+            const PlanEntryD e = pl[c];
+            pid = s.attr_param_base[e.attr] + (s.attr_anim[e.attr] ? o.frame : 0);
+            double cmv[14], bpv[3], recv[kLensRec];
+            const double *pcm = cm, *pbp = bp, *prec = has_lens ? rec : nullptr;
+            if (e.cam_var) { load_cam(s, o.cam, e.cam_var, o.frame, cmv); pcm = cmv; }
+            if (e.bnd_var) { load_bnd(s, o.bnd, e.bnd_var, o.frame, bpv); pbp = bpv; }
+            if (e.lens_var && has_lens) { load_lens(s, o.lens, e.lens_var, o.lens_frame, recv); prec = recv; }
+            double ax, ay, ad;
+            residual_from(s, o, pcm, pbp, prec, ax, ay, ad);
+            const double da = s.par_delta_a[pid];
+            bool forward = !s.central;
+            double db = 0.0;
+            if (!forward) { db = s.par_delta_b[pid]; if (da == db) forward = true; }
+            if (forward) {
+                const double inv_delta = 1.0 / da;
+                jx = (ax - ex) * inv_delta;
+                jy = (ay - ey) * inv_delta;
+            } else {
+                pcm = cm; pbp = bp; prec = has_lens ? rec : nullptr;
+                if (e.cam_var) { load_cam(s, o.cam, e.cam_var + cnd, o.frame, cmv); pcm = cmv; }
+                if (e.bnd_var) { load_bnd(s, o.bnd, e.bnd_var + bnd_nd, o.frame, bpv); pbp = bpv; }
+                if (e.lens_var && has_lens) { load_lens(s, o.lens, e.lens_var + lnd, o.lens_frame, recv); prec = recv; }
+                double bx, by, bd;
+                residual_from(s, o, pcm, pbp, prec, bx, by, bd);
+                // adjust_solveFunc.cpp:468 (0.5/(|dA|+|dB|), as written)
+                const double inv_delta = 0.5 / (fabs(da) + fabs(db));
+                jx = (ax - bx) * inv_delta;
+                jy = (ay - by) * inv_delta;
+            }
+        }
+        jac[(size_t)c * m + 2 * (size_t)i] = jx;
+        jac[(size_t)c * m + 2 * (size_t)i + 1] = jy;
+        if (col_ids) col_ids[(size_t)i * s.kmax + c] = pid;
+    }
+}
+
+}  // namespace mmb

@@ -1,0 +1,219 @@
+// CUDA kernels (sm_100a) of the residual / FD-Jacobian path and the handle
+// that owns their HBM buffers.  Per-thread bodies live in eval_bodies.cuh.
+#include "device_problem.h"
+
+namespace mmb {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string &msg) { g_last_error = msg; }
+const std::string &get_last_error() { return g_last_error; }
+
+// ---- kernels ---------------------------------------------------------------
+__global__ void k_copy(double *dst, const double *src, size_t n) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[i];
+}
+
+__global__ void k_set_parameters(DevScene s, const double *x) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < s.n) set_parameter_thread(s, x, i);
+}
+
+// kind 0 camera, 1 bundle, 2 lens; base_only skips perturbed variants
+__global__ void k_variants(DevScene s, const double *x, int base_only) {
+    const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long nc = s.cam_jobs_total, nb = s.bnd_jobs_total, nl = s.lens_jobs_total;
+    if (t < nc) {
+        if (base_only && s.cam_job_var[find_job(s.cam_job_start, s.cam_njobs, t)] != 0) return;
+        camera_variant_thread(s, x, t);
+    } else if (t < nc + nb) {
+        const long long u = t - nc;
+        if (base_only && s.bnd_job_var[find_job(s.bnd_job_start, s.bnd_njobs, u)] != 0) return;
+        bundle_variant_thread(s, x, u);
+    } else if (t < nc + nb + nl) {
+        const long long u = t - nc - nb;
+        if (base_only && s.lens_job_var[find_job(s.lens_job_start, s.lens_njobs, u)] != 0) return;
+        lens_variant_thread(s, x, u);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_residuals(DevScene s, double *fvec, double *dist) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < s.nobs) residual_thread(s, i, fvec, dist);
+}
+
+__global__ void __launch_bounds__(256) k_jacobian(DevScene s, double *fvec, double *dist, double *jac,
+                                                  int32_t *cols) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < s.nobs) jacobian_thread(s, i, fvec, dist, jac, cols);
+}
+
+// ---- launchers -------------------------------------------------------------
+static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+mmb_status launch_reset_store(DeviceProblem *p) {
+    const HostProblem &hp = p->hp;
+    if (hp.num_static) {
+        k_copy<<<blocks_for(hp.num_static, 256), 256, 0, p->stream>>>(p->ds.stat, p->d_stat0, hp.num_static);
+        ++p->launches;
+    }
+    if (hp.num_anim) {
+        const size_t n = (size_t)hp.num_anim * hp.F;
+        k_copy<<<blocks_for(n, 256), 256, 0, p->stream>>>(p->ds.anim, p->d_anim0, n);
+        ++p->launches;
+    }
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
+mmb_status launch_set_parameters(DeviceProblem *p, const double *d_x) {
+    if (p->hp.n == 0) return MMB_OK;
+    k_set_parameters<<<blocks_for(p->hp.n, 128), 128, 0, p->stream>>>(p->ds, d_x);
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
+mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed) {
+    const long long total = p->ds.cam_jobs_total + p->ds.bnd_jobs_total + p->ds.lens_jobs_total;
+    k_variants<<<blocks_for(total, 128), 128, 0, p->stream>>>(p->ds, d_x, with_perturbed ? 0 : 1);
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
+mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist) {
+    k_residuals<<<blocks_for(p->hp.nobs, 256), 256, 0, p->stream>>>(p->ds, d_fvec, d_dist);
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
+mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols) {
+    k_jacobian<<<blocks_for(p->hp.nobs, 256), 256, 0, p->stream>>>(p->ds, d_fvec, d_dist, d_jac, d_cols);
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
+// ---- handle ----------------------------------------------------------------
+void lm_workspace_destroy(LmWorkspace *w);
+
+DeviceProblem::~DeviceProblem() {
+    cudaSetDevice(device);
+    if (lm) lm_workspace_destroy(lm);
+    if (stream) cudaStreamDestroy(stream);
+    arena.release();
+}
+
+mmb_status ensure_jacobian_buffers(DeviceProblem *p) {
+    if (p->d_jac) return MMB_OK;
+    const size_t k = (size_t)std::max(p->hp.kmax, 1);
+    MMB_CUDA_CHECK(p->arena.alloc(&p->d_jac, k * (size_t)p->hp.m));
+    MMB_CUDA_CHECK(p->arena.alloc(&p->d_cols, k * (size_t)p->hp.nobs));
+    return MMB_OK;
+}
+
+mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt, DeviceProblem **out) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_last_error("no CUDA device: this library has no CPU path");
+        return MMB_ERR_NO_DEVICE;
+    }
+    if (opt->device < 0 || opt->device >= ndev) {
+        set_last_error("device ordinal out of range");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    DeviceProblem *p = new DeviceProblem();
+    mmb_status st = build_host_problem(s, opt, &p->hp);
+    if (st != MMB_OK) {
+        set_last_error(p->hp.error);
+        delete p;
+        return st;
+    }
+    p->device = opt->device;
+#define CK(expr)                                                               \
+    do {                                                                       \
+        cudaError_t _e = (expr);                                               \
+        if (_e != cudaSuccess) {                                               \
+            set_last_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+            delete p;                                                          \
+            return MMB_ERR_CUDA;                                               \
+        }                                                                      \
+    } while (0)
+    CK(cudaSetDevice(p->device));
+    CK(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    HostProblem &hp = p->hp;
+    DevScene &d = p->ds;
+    DeviceArena &A = p->arena;
+    d.F = hp.F; d.T = hp.T; d.C = hp.C; d.B = hp.B; d.M = hp.M; d.L = hp.L; d.A = hp.A;
+    d.n = hp.n; d.nobs = hp.nobs; d.kmax = std::max(hp.kmax, 1);
+    d.central = opt->auto_diff_type == 1;
+    d.dense_grid = hp.dense_grid;
+    d.any_lens = hp.any_lens;
+    d.lens_literal = opt->lens_index_literal;
+    d.delta = opt->delta;
+    d.image_width = opt->image_width;
+    CK(A.upload(&p->d_stat0, hp.stat0));
+    CK(A.upload(&p->d_anim0, hp.anim0));
+    CK(A.upload(&d.stat, hp.stat0));
+    CK(A.upload(&d.anim, hp.anim0));
+    int32_t *tmp_i = nullptr; double *tmp_d = nullptr; uint8_t *tmp_b = nullptr; int64_t *tmp_l = nullptr;
+#define UP_I(field, vec) CK(A.upload(&tmp_i, vec)); d.field = tmp_i
+#define UP_D(field, vec) CK(A.upload(&tmp_d, vec)); d.field = tmp_d
+#define UP_L(field, vec) CK(A.upload(&tmp_l, vec)); d.field = tmp_l
+    UP_I(tfm_parent, hp.tfm_parent); UP_I(tfm_roo, hp.tfm_roo); UP_I(tfm_attrs, hp.tfm_attrs);
+    UP_I(cam_tfm, hp.cam_tfm); UP_I(cam_attrs, hp.cam_attrs); UP_I(cam_fit, hp.cam_fit);
+    UP_I(cam_rw, hp.cam_rw); UP_I(cam_rh, hp.cam_rh); UP_I(cam_lens, hp.cam_lens);
+    UP_I(bnd_tfm, hp.bnd_tfm); UP_I(mkr_cam, hp.mkr_cam); UP_I(mkr_bnd, hp.mkr_bnd);
+    UP_I(lens_model, hp.lens_model); UP_I(lens_attrs, hp.lens_attrs); UP_D(lens_cam, hp.lens_cam);
+    UP_I(attr_ref, hp.attr_ref); UP_I(attr_param_base, hp.attr_param_base);
+    CK(A.upload(&tmp_b, hp.attr_anim)); d.attr_anim = tmp_b;
+    UP_D(attr_min, hp.attr_min); UP_D(attr_max, hp.attr_max);
+    UP_D(attr_off, hp.attr_off); UP_D(attr_scl, hp.attr_scl);
+    UP_I(par_attr, hp.par_attr); UP_I(par_frame, hp.par_frame);
+    if (hp.dense_grid) { d.err_marker = nullptr; d.err_frame = nullptr; }
+    else { UP_I(err_marker, hp.err_marker); UP_I(err_frame, hp.err_frame); }
+    UP_D(obs_mx, hp.obs_mx); UP_D(obs_my, hp.obs_my); UP_D(obs_w, hp.obs_w);
+    CK(A.alloc(&d.cam_tab, (size_t)hp.cam_tab_size));
+    CK(A.alloc(&d.bnd_tab, (size_t)hp.bnd_tab_size));
+    CK(A.alloc(&d.lens_tab, (size_t)hp.lens_tab_size));
+    UP_L(cam_off, hp.cam_off); UP_L(bnd_off, hp.bnd_off); UP_L(lens_off, hp.lens_off);
+    UP_I(cam_fs, hp.cam_fs); UP_I(bnd_fs, hp.bnd_fs); UP_I(lens_fs, hp.lens_fs);
+    std::vector<int32_t> cnd(hp.C), bnd(hp.B), lnd(hp.L);
+    for (int c = 0; c < hp.C; ++c) cnd[c] = (int32_t)hp.cam_deps[c].size();
+    for (int b = 0; b < hp.B; ++b) bnd[b] = (int32_t)hp.bnd_deps[b].size();
+    for (int l = 0; l < hp.L; ++l) lnd[l] = (int32_t)hp.lens_deps[l].size();
+    UP_I(cam_ndep, cnd); UP_I(bnd_ndep, bnd); UP_I(lens_ndep, lnd);
+    UP_I(cam_job_ent, hp.cam_job_ent); UP_I(cam_job_var, hp.cam_job_var); UP_I(cam_job_attr, hp.cam_job_attr);
+    UP_L(cam_job_start, hp.cam_job_start);
+    d.cam_njobs = (int)hp.cam_job_ent.size(); d.cam_jobs_total = hp.cam_jobs_total;
+    UP_I(bnd_job_ent, hp.bnd_job_ent); UP_I(bnd_job_var, hp.bnd_job_var); UP_I(bnd_job_attr, hp.bnd_job_attr);
+    UP_L(bnd_job_start, hp.bnd_job_start);
+    d.bnd_njobs = (int)hp.bnd_job_ent.size(); d.bnd_jobs_total = hp.bnd_jobs_total;
+    UP_I(lens_job_ent, hp.lens_job_ent); UP_I(lens_job_var, hp.lens_job_var); UP_I(lens_job_attr, hp.lens_job_attr);
+    UP_L(lens_job_start, hp.lens_job_start);
+    d.lens_njobs = (int)hp.lens_job_ent.size(); d.lens_jobs_total = hp.lens_jobs_total;
+    {
+        static_assert(sizeof(PlanEntry) == sizeof(PlanEntryD), "plan entry layout");
+        PlanEntryD *dp = nullptr;
+        CK(A.alloc(&dp, hp.plan.size()));
+        if (!hp.plan.empty())
+            CK(cudaMemcpy(dp, hp.plan.data(), hp.plan.size() * sizeof(PlanEntry), cudaMemcpyHostToDevice));
+        d.plan = dp;
+    }
+    UP_I(mkr_k, hp.mkr_k);
+    CK(A.alloc(&d.par_delta_a, (size_t)hp.n));
+    CK(A.alloc(&d.par_delta_b, (size_t)hp.n));
+    CK(A.alloc(&p->d_x, (size_t)hp.n));
+    CK(A.alloc(&p->d_fvec, (size_t)hp.m));
+    CK(A.alloc(&p->d_dist, (size_t)hp.nobs));
+#undef CK
+#undef UP_I
+#undef UP_D
+#undef UP_L
+    *out = p;
+    return MMB_OK;
+}
+
+}  // namespace mmb

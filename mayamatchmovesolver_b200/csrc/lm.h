@@ -1,0 +1,8 @@
+// Levenberg-Marquardt driver on the device (lm_global.cu).
+#pragma once
+#include "device_problem.h"
+
+namespace mmb {
+mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out);
+void lm_workspace_destroy(LmWorkspace *w);
+}  // namespace mmb

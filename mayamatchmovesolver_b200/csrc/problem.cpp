@@ -1,0 +1,314 @@
+// Host C++: scene validation, reference index maps, variant plan.
+// See problem.h.  Reference functions restated here:
+//   countUpNumberOfErrors            adjust_relationships.cpp:75-221
+//   countUpNumberOfUnknownParameters adjust_relationships.cpp:223-337
+//   findErrorToParameterRelationship adjust_relationships.cpp:565-617
+//     (kept implicit: the relationship is the per-marker column plan)
+//   parameterBoundFromInternalToExternal / ExternalToInternal
+//                                    adjust_base.cpp:194-258
+#include "problem.h"
+
+#include <algorithm>
+#include <cmath>
+#include <limits>
+#include <set>
+
+namespace mmb {
+
+double bound_internal_to_external(double value, double xmin, double xmax,
+                                  double offset, double scale) {
+    const double float_max = std::numeric_limits<float>::max();
+    if ((xmin <= -float_max) && (xmax >= float_max)) {
+        value = (value / scale) - offset;
+        value = std::max(value, xmin);
+        value = std::min(value, xmax);
+        return value;
+    } else if (xmax >= float_max) {
+        // lower bound only (formula as written at adjust_base.cpp:207)
+        value = xmin - (1.0 + std::sqrt(value * value + 1.0));
+    } else if (xmin <= -float_max) {
+        value = xmax + (1.0 - std::sqrt(value * value + 1.0));
+    } else {
+        value = xmin + ((xmax - xmin) / 2.0) * (std::sin(value) + 1.0);
+    }
+    value = (value / scale) - offset;
+    value = std::max(value, xmin);
+    value = std::min(value, xmax);
+    return value;
+}
+
+double bound_external_to_internal(double value, double xmin, double xmax,
+                                  double offset, double scale) {
+    value = std::max(value, xmin);
+    value = std::min(value, xmax);
+    value = (value * scale) + offset;
+    xmin = (xmin * scale) + offset;
+    xmax = (xmax * scale) + offset;
+    const double float_max = std::numeric_limits<float>::max();
+    // adjust_base.cpp:239 tests `xmin <= float_max` (sic); kept.
+    if ((xmin <= float_max) && (xmax >= float_max)) {
+        return value;
+    } else if (xmax >= float_max) {
+        value = std::sqrt(std::pow(((value - xmin) + 1.0), 2.0) - 1.0);
+    } else if (xmin <= -float_max) {
+        value = std::sqrt(std::pow((xmax - value) + 1.0, 2.0) - 1.0);
+    } else {
+        value = std::asin((2.0 * (value - xmin) / (xmax - xmin)) - 1.0);
+    }
+    return value;
+}
+
+static bool ref_ok(int32_t r, int ns, int na, bool allow_none) {
+    if (r == MMB_ATTR_NONE) return allow_none;
+    if (r >= 0) return r < ns;
+    return (-(int64_t)r - 1) < na;
+}
+
+// refs read by a transform chain (leaf -> root)
+static void chain_refs(const HostProblem &hp, int t, std::vector<int32_t> &out) {
+    while (t >= 0) {
+        for (int k = 0; k < MMB_TFM_ATTRS; ++k) out.push_back(hp.tfm_attrs[t * MMB_TFM_ATTRS + k]);
+        t = hp.tfm_parent[t];
+    }
+}
+
+static void deps_from_refs(const HostProblem &hp, const std::vector<int32_t> &refs,
+                           std::vector<int32_t> &deps, uint8_t &varies) {
+    std::set<int32_t> rs(refs.begin(), refs.end());
+    deps.clear();
+    varies = 0;
+    for (int32_t r : rs)
+        if (r != MMB_ATTR_NONE && r < 0) varies = 1;
+    for (int a = 0; a < hp.A; ++a)
+        if (rs.count(hp.attr_ref[a])) deps.push_back(a);
+}
+
+mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
+                              HostProblem *hpp) {
+    HostProblem &hp = *hpp;
+    if (!s || !opt) return MMB_ERR_INVALID_ARGUMENT;
+    if (s->abi_version != MMB_ABI_VERSION) {
+        hp.error = "abi_version mismatch";
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    hp.opt = *opt;
+    hp.F = s->num_frames; hp.T = s->num_transforms; hp.C = s->num_cameras;
+    hp.B = s->num_bundles; hp.M = s->num_markers; hp.L = s->num_lenses;
+    hp.A = s->num_attrs;
+    hp.num_static = s->num_static; hp.num_anim = s->num_anim;
+    if (hp.F <= 0 || hp.T <= 0 || hp.C <= 0 || hp.B <= 0 || hp.M <= 0 || hp.A < 0 ||
+        hp.L < 0 || hp.num_static < 0 || hp.num_anim < 0) {
+        // flat.rs:186-190 asserts the same counts are > 0
+        hp.error = "scene needs >=1 frame, transform, camera, bundle and marker";
+        return MMB_ERR_NOT_ENOUGH_OBJECTS;
+    }
+    if (opt->scene_graph_mode != 2) {
+        hp.error = "only sceneGraphMode=2 (mmscenegraph) is implemented; the Maya DAG mode needs Maya";
+        return MMB_ERR_UNSUPPORTED;
+    }
+    if (opt->solver_type != 2) {
+        hp.error = "only solverType=2 (cminpack_lmder) is implemented";
+        return MMB_ERR_UNSUPPORTED;
+    }
+    const size_t F = hp.F;
+    if (s->frames) hp.frames.assign(s->frames, s->frames + F);
+    else { hp.frames.resize(F); for (size_t f = 0; f < F; ++f) hp.frames[f] = (int32_t)f; }
+    if (hp.num_static) hp.stat0.assign(s->static_values, s->static_values + hp.num_static);
+    if (hp.num_anim) hp.anim0.assign(s->anim_values, s->anim_values + (size_t)hp.num_anim * F);
+    hp.tfm_parent.assign(s->tfm_parent, s->tfm_parent + hp.T);
+    hp.tfm_roo.assign(s->tfm_rotate_order, s->tfm_rotate_order + hp.T);
+    hp.tfm_attrs.assign(s->tfm_attrs, s->tfm_attrs + hp.T * MMB_TFM_ATTRS);
+    hp.cam_tfm.assign(s->cam_tfm, s->cam_tfm + hp.C);
+    hp.cam_attrs.assign(s->cam_attrs, s->cam_attrs + hp.C * MMB_CAM_ATTRS);
+    hp.cam_fit.assign(s->cam_film_fit, s->cam_film_fit + hp.C);
+    hp.cam_rw.assign(s->cam_render_width, s->cam_render_width + hp.C);
+    hp.cam_rh.assign(s->cam_render_height, s->cam_render_height + hp.C);
+    hp.cam_lens.assign(hp.C, -1);
+    if (s->cam_lens) hp.cam_lens.assign(s->cam_lens, s->cam_lens + hp.C);
+    hp.bnd_tfm.assign(s->bnd_tfm, s->bnd_tfm + hp.B);
+    hp.mkr_cam.assign(s->mkr_cam, s->mkr_cam + hp.M);
+    hp.mkr_bnd.assign(s->mkr_bnd, s->mkr_bnd + hp.M);
+    if (hp.L > 0) {
+        hp.lens_model.assign(s->lens_model, s->lens_model + hp.L);
+        hp.lens_attrs.assign(s->lens_attrs, s->lens_attrs + hp.L * MMB_LENS_MAX_COEFFS);
+        hp.lens_cam.assign(s->lens_camera_params, s->lens_camera_params + hp.L * 6);
+    }
+    if (hp.A) {
+        hp.attr_ref.assign(s->attr_ref, s->attr_ref + hp.A);
+        hp.attr_min.assign(s->attr_min, s->attr_min + hp.A);
+        hp.attr_max.assign(s->attr_max, s->attr_max + hp.A);
+        hp.attr_off.assign(s->attr_offset, s->attr_offset + hp.A);
+        hp.attr_scl.assign(s->attr_scale, s->attr_scale + hp.A);
+    }
+    // ---- validation ------------------------------------------------------
+    for (int t = 0; t < hp.T; ++t) {
+        if (hp.tfm_parent[t] >= t || hp.tfm_parent[t] < -1) { hp.error = "tfm_parent must precede child"; return MMB_ERR_INVALID_ARGUMENT; }
+        if (hp.tfm_roo[t] < 0 || hp.tfm_roo[t] > 5) { hp.error = "bad rotate order"; return MMB_ERR_INVALID_ARGUMENT; }
+        for (int k = 0; k < MMB_TFM_ATTRS; ++k)
+            if (!ref_ok(hp.tfm_attrs[t * MMB_TFM_ATTRS + k], hp.num_static, hp.num_anim, false)) { hp.error = "bad transform attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
+    }
+    for (int c = 0; c < hp.C; ++c) {
+        if (hp.cam_tfm[c] < 0 || hp.cam_tfm[c] >= hp.T) { hp.error = "bad cam_tfm"; return MMB_ERR_INVALID_ARGUMENT; }
+        if (hp.cam_lens[c] >= hp.L) { hp.error = "bad cam_lens"; return MMB_ERR_INVALID_ARGUMENT; }
+        if (hp.cam_fit[c] < 0 || hp.cam_fit[c] > 3) { hp.error = "bad film fit"; return MMB_ERR_INVALID_ARGUMENT; }
+        for (int k = 0; k < MMB_CAM_ATTRS; ++k)
+            if (!ref_ok(hp.cam_attrs[c * MMB_CAM_ATTRS + k], hp.num_static, hp.num_anim, false)) { hp.error = "bad camera attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
+    }
+    for (int b = 0; b < hp.B; ++b)
+        if (hp.bnd_tfm[b] < 0 || hp.bnd_tfm[b] >= hp.T) { hp.error = "bad bnd_tfm"; return MMB_ERR_INVALID_ARGUMENT; }
+    for (int m = 0; m < hp.M; ++m)
+        if (hp.mkr_cam[m] < 0 || hp.mkr_cam[m] >= hp.C || hp.mkr_bnd[m] < 0 || hp.mkr_bnd[m] >= hp.B) { hp.error = "bad marker camera/bundle index"; return MMB_ERR_INVALID_ARGUMENT; }
+    for (int l = 0; l < hp.L; ++l) {
+        if (hp.lens_model[l] < 0 || hp.lens_model[l] > 4) { hp.error = "bad lens model"; return MMB_ERR_INVALID_ARGUMENT; }
+        for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k)
+            if (!ref_ok(hp.lens_attrs[l * MMB_LENS_MAX_COEFFS + k], hp.num_static, hp.num_anim, true)) { hp.error = "bad lens attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
+    }
+    for (int a = 0; a < hp.A; ++a)
+        if (!ref_ok(hp.attr_ref[a], hp.num_static, hp.num_anim, false)) { hp.error = "bad solver attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
+
+    // ---- countUpNumberOfErrors (marker-major, frame-minor) ---------------
+    std::vector<double> wmax(F, 0.0);
+    std::vector<uint8_t> wseen(F, 0);
+    hp.err_marker.clear(); hp.err_frame.clear();
+    hp.obs_mx.clear(); hp.obs_my.clear(); hp.obs_w.clear();
+    for (int i = 0; i < hp.M; ++i) {
+        for (size_t j = 0; j < F; ++j) {
+            const size_t o = (size_t)i * F + j;
+            const bool enable = s->mkr_enable[o] != 0;
+            const double weight = s->mkr_weight[o];
+            if (enable && (weight > 0.0)) {
+                hp.err_marker.push_back(i);
+                hp.err_frame.push_back((int32_t)j);
+                hp.obs_w.push_back(weight);
+                hp.obs_mx.push_back(s->mkr_x[o]);
+                hp.obs_my.push_back(s->mkr_y[o]);
+                if (!wseen[j] || weight > wmax[j]) wmax[j] = weight;
+                wseen[j] = 1;
+            }
+        }
+    }
+    hp.nobs = (int)hp.err_marker.size();
+    hp.m = 2 * hp.nobs;
+    for (int i = 0; i < hp.nobs; ++i) hp.obs_w[i] = hp.obs_w[i] / wmax[hp.err_frame[i]];
+    hp.dense_grid = ((size_t)hp.nobs == (size_t)hp.M * F);
+
+    // ---- countUpNumberOfUnknownParameters (attr-major, frame-minor) -------
+    hp.par_attr.clear(); hp.par_frame.clear();
+    hp.attr_param_base.assign(hp.A, 0);
+    hp.attr_anim.assign(hp.A, 0);
+    hp.attr_slot.assign(hp.A, 0);
+    hp.na = 0; hp.ns = 0;
+    for (int a = 0; a < hp.A; ++a) {
+        hp.attr_param_base[a] = (int32_t)hp.par_attr.size();
+        if (hp.attr_ref[a] < 0) {
+            hp.attr_anim[a] = 1;
+            hp.attr_slot[a] = hp.na++;
+            for (size_t j = 0; j < F; ++j) { hp.par_attr.push_back(a); hp.par_frame.push_back((int32_t)j); }
+        } else {
+            hp.attr_slot[a] = hp.ns++;
+            hp.par_attr.push_back(a); hp.par_frame.push_back(-1);
+        }
+    }
+    hp.n = (int)hp.par_attr.size();
+    hp.par_to_int.assign(hp.n, 0); hp.int_to_par.assign(hp.n, 0);
+    for (int p = 0; p < hp.n; ++p) {
+        const int a = hp.par_attr[p];
+        const int q = hp.attr_anim[a] ? hp.par_frame[p] * hp.na + hp.attr_slot[a]
+                                      : (int)F * hp.na + hp.attr_slot[a];
+        hp.par_to_int[p] = q; hp.int_to_par[q] = p;
+    }
+
+    // ---- entity dependencies ---------------------------------------------
+    hp.cam_deps.assign(hp.C, {}); hp.bnd_deps.assign(hp.B, {}); hp.lens_deps.assign(hp.L, {});
+    hp.cam_varies.assign(hp.C, 0); hp.bnd_varies.assign(hp.B, 0); hp.lens_varies.assign(hp.L, 0);
+    hp.cam_mscale_varies.assign(hp.C, 0);
+    for (int c = 0; c < hp.C; ++c) {
+        std::vector<int32_t> refs;
+        chain_refs(hp, hp.cam_tfm[c], refs);
+        for (int k = 0; k < MMB_CAM_ATTRS; ++k) refs.push_back(hp.cam_attrs[c * MMB_CAM_ATTRS + k]);
+        deps_from_refs(hp, refs, hp.cam_deps[c], hp.cam_varies[c]);
+        for (int a : hp.cam_deps[c])
+            if (hp.attr_ref[a] == hp.cam_attrs[c * MMB_CAM_ATTRS + 0] || hp.attr_ref[a] == hp.cam_attrs[c * MMB_CAM_ATTRS + 1])
+                hp.cam_mscale_varies[c] = 1;
+    }
+    for (int b = 0; b < hp.B; ++b) {
+        std::vector<int32_t> refs;
+        chain_refs(hp, hp.bnd_tfm[b], refs);
+        deps_from_refs(hp, refs, hp.bnd_deps[b], hp.bnd_varies[b]);
+    }
+    hp.any_lens = false;
+    for (int l = 0; l < hp.L; ++l) {
+        std::vector<int32_t> refs;
+        for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k) refs.push_back(hp.lens_attrs[l * MMB_LENS_MAX_COEFFS + k]);
+        deps_from_refs(hp, refs, hp.lens_deps[l], hp.lens_varies[l]);
+    }
+    for (int c = 0; c < hp.C; ++c)
+        if (hp.cam_lens[c] >= 0 && hp.lens_model[hp.cam_lens[c]] != MMB_LENS_PASSTHROUGH) hp.any_lens = true;
+
+    // ---- variant tables ---------------------------------------------------
+    const int vmul = (opt->auto_diff_type == 1) ? 2 : 1;
+    auto layout = [&](const std::vector<std::vector<int32_t>> &deps, const std::vector<uint8_t> &varies,
+                      int width, std::vector<int64_t> &off, std::vector<int32_t> &fs,
+                      std::vector<int32_t> &nvar, int64_t &total, std::vector<int32_t> &job_ent,
+                      std::vector<int32_t> &job_var, std::vector<int32_t> &job_attr,
+                      std::vector<int64_t> &job_start, int64_t &jobs_total) {
+        const int E = (int)deps.size();
+        off.assign(E, 0); fs.assign(E, 1); nvar.assign(E, 1);
+        job_ent.clear(); job_var.clear(); job_attr.clear(); job_start.clear();
+        total = 0; jobs_total = 0;
+        for (int e = 0; e < E; ++e) {
+            // a variant of a static entity perturbed by an animated param
+            // would differ per frame; `varies` already covers that because an
+            // animated solver attr is an animated ref in the chain.
+            fs[e] = varies[e] ? (int32_t)F : 1;
+            nvar[e] = 1 + vmul * (int)deps[e].size();
+            off[e] = total;
+            total += (int64_t)nvar[e] * width * fs[e];
+            for (int v = 0; v < nvar[e]; ++v) {
+                job_ent.push_back(e); job_var.push_back(v);
+                job_attr.push_back(v == 0 ? -1 : deps[e][(v - 1) % deps[e].size()]);
+                job_start.push_back(jobs_total);
+                jobs_total += fs[e];
+            }
+        }
+        job_start.push_back(jobs_total);
+    };
+    layout(hp.cam_deps, hp.cam_varies, 14, hp.cam_off, hp.cam_fs, hp.cam_nvar, hp.cam_tab_size,
+           hp.cam_job_ent, hp.cam_job_var, hp.cam_job_attr, hp.cam_job_start, hp.cam_jobs_total);
+    layout(hp.bnd_deps, hp.bnd_varies, 3, hp.bnd_off, hp.bnd_fs, hp.bnd_nvar, hp.bnd_tab_size,
+           hp.bnd_job_ent, hp.bnd_job_var, hp.bnd_job_attr, hp.bnd_job_start, hp.bnd_jobs_total);
+    layout(hp.lens_deps, hp.lens_varies, 24, hp.lens_off, hp.lens_fs, hp.lens_nvar, hp.lens_tab_size,
+           hp.lens_job_ent, hp.lens_job_var, hp.lens_job_attr, hp.lens_job_start, hp.lens_jobs_total);
+
+    // ---- per-marker column plan -------------------------------------------
+    hp.mkr_k.assign(hp.M, 0);
+    std::vector<std::vector<PlanEntry>> plans(hp.M);
+    hp.kmax = 0;
+    for (int mk = 0; mk < hp.M; ++mk) {
+        const int c = hp.mkr_cam[mk], b = hp.mkr_bnd[mk], l = hp.cam_lens[c];
+        std::set<int32_t> cols(hp.cam_deps[c].begin(), hp.cam_deps[c].end());
+        cols.insert(hp.bnd_deps[b].begin(), hp.bnd_deps[b].end());
+        if (l >= 0) cols.insert(hp.lens_deps[l].begin(), hp.lens_deps[l].end());
+        auto find1 = [](const std::vector<int32_t> &v, int32_t a) -> int16_t {
+            auto it = std::lower_bound(v.begin(), v.end(), a);
+            return (it != v.end() && *it == a) ? (int16_t)(it - v.begin() + 1) : (int16_t)0;
+        };
+        for (int32_t a : cols) {
+            PlanEntry e;
+            e.attr = a;
+            e.cam_var = find1(hp.cam_deps[c], a);
+            e.bnd_var = find1(hp.bnd_deps[b], a);
+            e.lens_var = l >= 0 ? find1(hp.lens_deps[l], a) : (int16_t)0;
+            e.pad = 0;
+            plans[mk].push_back(e);
+        }
+        hp.mkr_k[mk] = (int32_t)plans[mk].size();
+        hp.kmax = std::max(hp.kmax, hp.mkr_k[mk]);
+    }
+    hp.plan.assign((size_t)hp.M * std::max(hp.kmax, 1), PlanEntry{-1, 0, 0, 0, 0});
+    for (int mk = 0; mk < hp.M; ++mk)
+        for (size_t c = 0; c < plans[mk].size(); ++c) hp.plan[(size_t)mk * hp.kmax + c] = plans[mk][c];
+    return MMB_OK;
+}
+
+}  // namespace mmb

@@ -1,0 +1,101 @@
+// Host-side problem description of the B200 mmSolver solve path.
+//
+// Replaces the head of solveFrames() (adjust_base.cpp:746-1074): the index
+// maps of adjust_relationships.cpp are rebuilt bit-exactly on plain arrays
+// and then compiled into the "variant plan" the CUDA kernels consume.
+//
+// Variant plan (ours, not in the reference): an observation (marker, frame)
+// depends on its camera's 3x4 world-projection rows, its bundle's world
+// position and its lens coefficients.  Every solver parameter perturbs one
+// (or more) of those three *entities*, never the observation directly, so the
+// finite-difference Jacobian (adjust_solveFunc.cpp:305-479) becomes
+//   1. one small launch that evaluates every entity at x and at x + delta*e_p
+//      for each parameter p it depends on ("variants"), and
+//   2. one streaming launch over observations that combines variants.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/mmsolver_b200.h"
+
+namespace mmb {
+
+// per-marker plan entry: column c of marker m
+struct PlanEntry {
+    int32_t attr;      // solver attribute index (or -1 unused)
+    int16_t cam_var;   // 0 = base, else 1-based index into camera dep list
+    int16_t bnd_var;   // same for bundle
+    int16_t lens_var;  // same for lens
+    int16_t pad;
+};
+
+struct HostProblem {
+    mmb_options opt;
+    int F = 0, T = 0, C = 0, B = 0, M = 0, L = 0, A = 0;
+    int num_static = 0, num_anim = 0;
+    // deep copies of the scene
+    std::vector<int32_t> frames;
+    std::vector<double> stat0, anim0;
+    std::vector<int32_t> tfm_parent, tfm_roo, tfm_attrs;
+    std::vector<int32_t> cam_tfm, cam_attrs, cam_fit, cam_rw, cam_rh, cam_lens;
+    std::vector<int32_t> bnd_tfm, mkr_cam, mkr_bnd;
+    std::vector<int32_t> lens_model, lens_attrs;
+    std::vector<double> lens_cam;
+    std::vector<int32_t> attr_ref;
+    std::vector<double> attr_min, attr_max, attr_off, attr_scl;
+
+    // ---- index maps (adjust_relationships.cpp) --------------------------
+    int n = 0, nobs = 0, m = 0;
+    std::vector<int32_t> err_marker, err_frame;   // errorToMarkerList
+    std::vector<double> obs_mx, obs_my, obs_w;    // markerPosList / weights
+    std::vector<int32_t> par_attr, par_frame;     // paramToAttrList
+    std::vector<int32_t> attr_param_base;         // first param of attr a
+    std::vector<uint8_t> attr_anim;               // attr expands per frame
+    bool dense_grid = false;                      // nobs == M*F, i = m*F+f
+
+    // ---- entity dependency lists ---------------------------------------
+    // solver attrs each entity depends on (sorted attr indices)
+    std::vector<std::vector<int32_t>> cam_deps, bnd_deps, lens_deps;
+    // does the entity vary per frame (any animated ref in its chain)?
+    std::vector<uint8_t> cam_varies, bnd_varies, lens_varies;
+    std::vector<uint8_t> cam_mscale_varies;  // sensor w/h is a solver attr
+    // variant table offsets (in doubles) and frame strides
+    std::vector<int64_t> cam_off, bnd_off, lens_off;
+    std::vector<int32_t> cam_fs, bnd_fs, lens_fs;      // F or 1
+    std::vector<int32_t> cam_nvar, bnd_nvar, lens_nvar;  // 1 + deps (*2 central)
+    int64_t cam_tab_size = 0, bnd_tab_size = 0, lens_tab_size = 0;
+    // flattened (entity, variant) work lists for the variant kernel
+    std::vector<int32_t> cam_job_ent, cam_job_var, cam_job_attr;
+    std::vector<int32_t> bnd_job_ent, bnd_job_var, bnd_job_attr;
+    std::vector<int32_t> lens_job_ent, lens_job_var, lens_job_attr;
+    int64_t cam_jobs_total = 0, bnd_jobs_total = 0, lens_jobs_total = 0;
+    std::vector<int64_t> cam_job_start, bnd_job_start, lens_job_start;  // prefix (threads)
+
+    // ---- per-marker column plan ---------------------------------------
+    int kmax = 0;
+    std::vector<PlanEntry> plan;  // [M * kmax]
+    std::vector<int32_t> mkr_k;   // [M]
+    bool any_lens = false;
+
+    // ---- normal-equation partition (LM) --------------------------------
+    // eliminated side: animated attrs grouped by frame; reduced side: static
+    int na = 0;   // animated solver attrs (block size per frame)
+    int ns = 0;   // static solver params (reduced system dimension)
+    std::vector<int32_t> attr_slot;  // attr -> index within its class
+    // solver param (reference order) <-> internal order
+    // internal: [F*na eliminated (frame-major)] [ns reduced]
+    std::vector<int32_t> par_to_int, int_to_par;
+
+    std::string error;
+};
+
+// Build everything above from a scene description. Returns MMB_OK or error.
+mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
+                              HostProblem *hp);
+
+// adjust_base.cpp:194-258 on the host (used for initial parameters / output)
+double bound_internal_to_external(double v, double mn, double mx, double off, double scl);
+double bound_external_to_internal(double v, double mn, double mx, double off, double scl);
+
+}  // namespace mmb

@@ -1,0 +1,143 @@
+"""Python handle over the C-ABI (`mmb_problem`): what the reference's Python
+API reaches through `maya.cmds.mmSolver` (solverstep.py:505-738), minus Maya.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+from ._capi import Options, Result, c_f64p, c_i32p, check
+
+
+def default_options(**overrides):
+    lib = _capi.load()
+    o = Options()
+    lib.mmb_options_default(C.byref(o))
+    for k, v in overrides.items():
+        if not hasattr(o, k):
+            raise TypeError("unknown option %r" % k)
+        setattr(o, k, v)
+    return o
+
+
+class SolveResult:
+    """Field names follow SolverResult / ErrorMetricsResult (adjust_results.h:119-286)."""
+
+    def __init__(self, r, x, attr_values, error_dist):
+        self.success = bool(r.success)
+        self.reason_num = r.reason_num
+        self.reason_string = (r.reason_str or b"").decode()
+        self.error_final = r.error_final
+        self.error_avg, self.error_min, self.error_max = r.error_avg, r.error_min, r.error_max
+        self.iteration_num = r.iteration_num
+        self.iteration_function_num = r.iteration_function_num
+        self.iteration_jacobian_num = r.iteration_jacobian_num
+        self.iteration_attempt_num = r.iteration_attempt_num
+        self.user_interrupted = bool(r.user_interrupted)
+        self.error_is_better = bool(r.error_is_better)
+        self.timer_solve_s = r.timer_solve_s
+        self.timer_jacobian_s = r.timer_jacobian_s
+        self.timer_function_s = r.timer_function_s
+        self.timer_linear_s = r.timer_linear_s
+        self.x = x
+        self.attr_values = attr_values
+        self.error_dist = error_dist
+
+    def __repr__(self):
+        return ("SolveResult(success=%s reason=%d nfev=%d err_final=%.6g avg=%.6g max=%.6g)" %
+                (self.success, self.reason_num, self.iteration_num, self.error_final, self.error_avg,
+                 self.error_max))
+
+
+class Problem:
+    def __init__(self, scene, options=None, **opt_overrides):
+        self._lib = _capi.load()
+        self.options = options if options is not None else default_options(**opt_overrides)
+        desc, keep = scene.desc()
+        self._h = C.c_void_p()
+        check(self._lib.mmb_problem_create(C.byref(desc), C.byref(self.options), C.byref(self._h)),
+              "mmb_problem_create")
+        n, nobs, m = C.c_int32(), C.c_int32(), C.c_int32()
+        check(self._lib.mmb_problem_sizes(self._h, C.byref(n), C.byref(nobs), C.byref(m)), "mmb_problem_sizes")
+        self.n, self.nobs, self.m = n.value, nobs.value, m.value
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.mmb_problem_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def index_maps(self):
+        e2m = np.zeros((self.nobs, 2), np.int32)
+        p2a = np.zeros((self.n, 2), np.int32)
+        check(self._lib.mmb_get_index_maps(self._h, e2m.ctypes.data_as(c_i32p), p2a.ctypes.data_as(c_i32p)),
+              "mmb_get_index_maps")
+        return e2m, p2a
+
+    def marker_weights(self):
+        w = np.zeros(self.nobs)
+        check(self._lib.mmb_get_marker_weights(self._h, w.ctypes.data_as(c_f64p)), "mmb_get_marker_weights")
+        return w
+
+    def initial_parameters(self):
+        x = np.zeros(self.n)
+        check(self._lib.mmb_get_initial_parameters(self._h, x.ctypes.data_as(c_f64p)), "mmb_get_initial_parameters")
+        return x
+
+    def eval_residuals(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        fvec = np.zeros(self.m)
+        dist = np.zeros(self.nobs)
+        check(self._lib.mmb_eval_residuals(self._h, x.ctypes.data_as(c_f64p), fvec.ctypes.data_as(c_f64p),
+                                           dist.ctypes.data_as(c_f64p)), "mmb_eval_residuals")
+        return fvec, dist
+
+    def eval_jacobian_dense(self, x):
+        """column-major fjac as cminpack receives it, returned as (m, n) array"""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        ld = max(self.m, 1)
+        fjac = np.zeros((self.n, ld))
+        check(self._lib.mmb_eval_jacobian_dense(self._h, x.ctypes.data_as(c_f64p), fjac.ctypes.data_as(c_f64p), ld),
+              "mmb_eval_jacobian_dense")
+        return fjac.T
+
+    def jacobian_kmax(self):
+        k = C.c_int32()
+        check(self._lib.mmb_eval_jacobian_blocks(self._h, None, None, None, C.byref(k)), "mmb_eval_jacobian_blocks")
+        return k.value
+
+    def eval_jacobian_blocks(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        k = self.jacobian_kmax()
+        vals = np.zeros((k, self.m))
+        cols = np.zeros((self.nobs, k), np.int32)
+        kk = C.c_int32()
+        check(self._lib.mmb_eval_jacobian_blocks(self._h, x.ctypes.data_as(c_f64p), vals.ctypes.data_as(c_f64p),
+                                                 cols.ctypes.data_as(c_i32p), C.byref(kk)), "mmb_eval_jacobian_blocks")
+        return vals, cols
+
+    def solve(self):
+        r = Result()
+        x = np.zeros(self.n)
+        av = np.zeros(self.n)
+        dist = np.zeros(self.nobs)
+        check(self._lib.mmb_solve(self._h, C.byref(r), x.ctypes.data_as(c_f64p), av.ctypes.data_as(c_f64p),
+                                  dist.ctypes.data_as(c_f64p)), "mmb_solve")
+        return SolveResult(r, x, av, dist)
+
+    def request_cancel(self):
+        self._lib.mmb_request_cancel(self._h)
+
+    def bench_eval(self, reps=10, flush_l2=True):
+        ms = C.c_double()
+        launches = C.c_int32()
+        check(self._lib.mmb_bench_eval(self._h, reps, 1 if flush_l2 else 0, C.byref(ms), C.byref(launches)),
+              "mmb_bench_eval")
+        return ms.value, launches.value

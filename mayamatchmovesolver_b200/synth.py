@@ -1,0 +1,146 @@
+"""Deterministic synthetic scenes of the BASELINE.json config shapes
+(SURVEY.md section 8d).  numpy only; used by bench.py and tests/.
+
+The scene mathematics used to *generate* ground-truth markers is a small numpy
+restatement of SURVEY appendix B (projection of the truth bundles through the
+truth camera); it is data generation, not the solve path.
+"""
+import numpy as np
+
+from .scene import SceneBuilder
+
+DEG = np.pi / 180.0
+
+
+def _rot(rx, ry, rz):
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    X = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Y = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Z = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Z @ Y @ X  # rotate order XYZ (transform.rs:433)
+
+
+def project_truth(cam_t, cam_r_deg, pts, focal_mm, sensor_w_mm, sensor_h_mm, render_w, render_h):
+    """Horizontal film fit (camera.rs:183-242).  Returns marker x,y in the
+    -0.5..0.5 units the markers are stored in (before flat.rs film-fit scale)."""
+    R = _rot(*(np.asarray(cam_r_deg) * DEG))
+    pc = (pts - np.asarray(cam_t)) @ R  # inv(R) = R^T applied to column vectors
+    size_x = 0.1 / focal_mm * sensor_w_mm
+    image_aspect = render_w / render_h
+    size_y = size_x / image_aspect
+    p00 = 1.0 / (size_x * 0.5) * 0.1
+    p11 = 1.0 / (size_y * 0.5) * 0.1
+    x = p00 * pc[:, 0] / (-pc[:, 2]) * 0.5
+    y = p11 * pc[:, 1] / (-pc[:, 2]) * 0.5
+    # measureErrors compares against marker * film-fit scale; invert it here
+    film_aspect = sensor_w_mm / sensor_h_mm
+    y = y / (image_aspect / film_aspect)
+    return x, y
+
+
+def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
+    f = np.arange(F)
+    ph = rng.uniform(0, 2 * np.pi, 5)
+    t = np.stack([amp_t * np.sin(2 * np.pi * f / period + ph[0]),
+                  amp_t * np.sin(2 * np.pi * f / period + ph[1]),
+                  amp_t * np.sin(2 * np.pi * f / period + ph[2])], 1)
+    r = np.stack([amp_r * np.sin(2 * np.pi * f / period + ph[3]),
+                  amp_r * np.sin(2 * np.pi * f / period + ph[4]),
+                  np.zeros(F)], 1)
+    return t, r
+
+
+def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, init_noise_t=0.1,
+               init_noise_r=0.5, init_noise_b=0.05, fixed_bundles=0, lens=None, solve_focal=False,
+               solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False):
+    """One animated camera, B static bundles, full (or thinned) visibility.
+
+    cfg2: make_scene(240, 50, 2, solve_bundles=False)
+    cfg3: make_scene(1000, 500, 3)
+    cfg4: make_scene(1000, 500, 4, lens={...}, solve_focal=True, solve_lens=(...))
+    `fixed_bundles` bundles are left out of the attr list (removes the gauge
+    freedom so solved values are comparable between solvers).
+    Returns (SceneBuilder, info dict).
+    """
+    rng = np.random.default_rng(seed)
+    sensor_w, sensor_h, rw, rh = 36.0, 24.0, 2048, 1556
+    pts = np.stack([rng.uniform(-10, 10, B), rng.uniform(-10, 10, B), rng.uniform(-30, -10, B)], 1)
+    cam_t, cam_r = camera_path(F, rng)
+    sb = SceneBuilder(frames=np.arange(1, F + 1))
+    lens_node = None
+    if lens is not None:
+        # truth coefficients are only used to make the markers; the scene
+        # starts from zero coefficients when they are solved
+        init = {k: (0.0 if k in solve_lens else v) for k, v in lens.items()}
+        lens_node = sb.add_lens("3de_radial_std_deg4", camera_params=(focal_truth * 0.1, sensor_w * 0.1, sensor_h * 0.1, 1.0, 0.0, 0.0), **init)
+    t0 = cam_t + rng.normal(0, init_noise_t, cam_t.shape) if solve_camera else cam_t
+    r0 = cam_r + rng.normal(0, init_noise_r, cam_r.shape) if solve_camera else cam_r
+    r0[:, 2] = cam_r[:, 2] + (rng.normal(0, init_noise_r, F) if solve_camera else 0.0)
+    cam_tfm = sb.add_transform(tx=t0[:, 0], ty=t0[:, 1], tz=t0[:, 2], rx=r0[:, 0], ry=r0[:, 1], rz=r0[:, 2])
+    f_init = focal_truth if focal_init is None else focal_init
+    cam = sb.add_camera(cam_tfm, film_fit="horizontal", render_width=rw, render_height=rh, lens=lens_node,
+                        sensor_width_mm=sensor_w, sensor_height_mm=sensor_h, focal_length_mm=f_init)
+    b0 = pts + (rng.normal(0, init_noise_b, pts.shape) if solve_bundles else 0.0)
+    if fixed_bundles:
+        b0[:fixed_bundles] = pts[:fixed_bundles]
+    bnd_tfms = []
+    mx = np.zeros((B, F))
+    my = np.zeros((B, F))
+    for f in range(F):
+        x, y = project_truth(cam_t[f], cam_r[f], pts, focal_truth, sensor_w, sensor_h, rw, rh)
+        mx[:, f] = x
+        my[:, f] = y
+    if lens is not None:
+        mx, my = _distort_markers(mx, my, lens, (focal_truth * 0.1, sensor_w * 0.1, sensor_h * 0.1, 1.0, 0.0, 0.0), rw / rh, sensor_w / sensor_h)
+    mx = mx + rng.normal(0, noise_px / 2048.0, mx.shape)
+    my = my + rng.normal(0, noise_px / 2048.0, my.shape)
+    enable = np.ones((B, F), np.uint8)
+    if drop_fraction > 0:
+        enable = (rng.uniform(size=(B, F)) >= drop_fraction).astype(np.uint8)
+    w = rng.uniform(0.5, 1.0, (B, F)) if weights else np.ones((B, F))
+    for b in range(B):
+        t = sb.add_transform(tx=b0[b, 0], ty=b0[b, 1], tz=b0[b, 2])
+        bnd_tfms.append(t)
+        bn = sb.add_bundle(t)
+        sb.add_marker(cam, bn, mx[b], my[b], weight=w[b], enable=enable[b])
+    if solve_camera:
+        for k in ("tx", "ty", "tz", "rx", "ry", "rz"):
+            sb.add_attr(cam_tfm[k])
+    if solve_focal:
+        sb.add_attr(cam["focal_length_mm"])
+    for k in solve_lens:
+        sb.add_attr(lens_node[k])
+    if solve_bundles:
+        for b in range(fixed_bundles, B):
+            for k in ("tx", "ty", "tz"):
+                sb.add_attr(bnd_tfms[b][k])
+    info = dict(F=F, B=B, seed=seed, truth_points=pts, truth_cam_t=cam_t, truth_cam_r=cam_r,
+                cam_tfm=cam_tfm, cam=cam, bnd_tfms=bnd_tfms, lens=lens_node)
+    return sb, info
+
+
+def _lens_radial_core(x, y, c):
+    c2, u2, v2, c4, u4, v4 = (c.get(k, 0.0) for k in ("degree2_distortion", "degree2_u", "degree2_v",
+                                                      "degree4_distortion", "degree4_u", "degree4_v"))
+    r2 = x * x + y * y
+    rad = 1 + c2 * r2 + c4 * r2 * r2
+    return (x * rad + (r2 + 2 * x * x) * (u2 + u4 * r2) + 2 * x * y * (v2 + v4 * r2),
+            y * rad + (r2 + 2 * y * y) * (v2 + v4 * r2) + 2 * x * y * (u2 + u4 * r2))
+
+
+def _distort_markers(mx, my, lens, cam6, render_aspect, sensor_aspect):
+    """Markers of a distorted plate: apply the lens *distort* direction (the
+    fixed-point inverse the solver applies to projected points) to the ideal
+    marker positions.  Data generation only (cylindric terms must be 0)."""
+    assert lens.get("cylindric_bending", 0.0) == 0.0
+    scale_y = render_aspect / sensor_aspect  # flat.rs Horizontal: residual space is (mx, my*scale)
+    w, h = cam6[1], cam6[2]
+    radius = np.sqrt(w * w + h * h) / 2
+    qx = (mx * w) / radius
+    qy = (my * scale_y * h) / radius
+    px, py = qx.copy(), qy.copy()
+    for _ in range(60):
+        fx, fy = _lens_radial_core(px, py, lens)
+        px = px + qx - fx
+        py = py + qy - fy
+    return px * radius / w, py * radius / h / scale_y
