@@ -84,6 +84,7 @@ mmb_status launch_reset_store(DeviceProblem *p);                 // attribute st
 mmb_status launch_set_parameters(DeviceProblem *p, const double *d_x);
 mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed);
 mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist);
-mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols);
+mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols,
+                           double *d_dist_last = nullptr);
 
 }  // namespace mmb

@@ -280,8 +280,11 @@ MMB_HD void residual_thread(const DevScene &s, int i, double *fvec, double *dist
 
 // Residuals + block Jacobian (solveFunc iflag=1 and iflag=2 fused).
 //   jac[c * m + 2i + {0,1}], col_ids[i * kmax + c] = parameter index or -1
+// dist_last (optional): the distance the reference leaves in errorDistanceList
+// after its Jacobian loop -- the evaluation with the LAST solver attribute
+// perturbed (adjust_measureErrors.cpp:497 overwrites it on every call).
 MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist, double *jac,
-                            int32_t *col_ids) {
+                            int32_t *col_ids, double *dist_last = nullptr) {
     const ObsCtx o = make_obs(s, i);
     const size_t m = 2 * (size_t)s.nobs;
     double cm[14], bp[3], rec[kLensRec];
@@ -293,6 +296,7 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
     residual_from(s, o, cm, bp, has_lens ? rec : nullptr, ex, ey, d);
     if (fvec) { fvec[2 * (size_t)i] = ex; fvec[2 * (size_t)i + 1] = ey; }
     if (dist) dist[i] = d;
+    double dlast = d;
     const int k = s.mkr_k[o.marker];
     const PlanEntryD *pl = s.plan + (size_t)o.marker * s.kmax;
     const int cnd = s.cam_ndep[o.cam], bnd_nd = s.bnd_ndep[o.bnd];
@@ -318,6 +322,7 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
                 const double inv_delta = 1.0 / da;
                 jx = (ax - ex) * inv_delta;
                 jy = (ay - ey) * inv_delta;
+                if (e.attr == s.A - 1) dlast = ad;
             } else {
                 pcm = cm; pbp = bp; prec = has_lens ? rec : nullptr;
                 if (e.cam_var) { load_cam(s, o.cam, e.cam_var + cnd, o.frame, cmv); pcm = cmv; }
@@ -329,12 +334,14 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
                 const double inv_delta = 0.5 / (fabs(da) + fabs(db));
                 jx = (ax - bx) * inv_delta;
                 jy = (ay - by) * inv_delta;
+                if (e.attr == s.A - 1) dlast = bd;
             }
         }
         jac[(size_t)c * m + 2 * (size_t)i] = jx;
         jac[(size_t)c * m + 2 * (size_t)i + 1] = jy;
         if (col_ids) col_ids[(size_t)i * s.kmax + c] = pid;
     }
+    if (dist_last) dist_last[i] = dlast;
 }
 
 }  // namespace mmb

@@ -43,9 +43,9 @@ __global__ void __launch_bounds__(256) k_residuals(DevScene s, double *fvec, dou
 }
 
 __global__ void __launch_bounds__(256) k_jacobian(DevScene s, double *fvec, double *dist, double *jac,
-                                                  int32_t *cols) {
+                                                  int32_t *cols, double *dist_last) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < s.nobs) jacobian_thread(s, i, fvec, dist, jac, cols);
+    if (i < s.nobs) jacobian_thread(s, i, fvec, dist, jac, cols, dist_last);
 }
 
 // ---- launchers -------------------------------------------------------------
@@ -89,8 +89,8 @@ mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist) {
     return MMB_OK;
 }
 
-mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols) {
-    k_jacobian<<<blocks_for(p->hp.nobs, 256), 256, 0, p->stream>>>(p->ds, d_fvec, d_dist, d_jac, d_cols);
+mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols, double *d_dist_last) {
+    k_jacobian<<<blocks_for(p->hp.nobs, 256), 256, 0, p->stream>>>(p->ds, d_fvec, d_dist, d_jac, d_cols, d_dist_last);
     ++p->launches;
     MMB_CUDA_CHECK(cudaGetLastError());
     return MMB_OK;

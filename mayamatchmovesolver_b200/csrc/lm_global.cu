@@ -1,9 +1,625 @@
+// Device Levenberg-Marquardt driver for the global (all frames at once) solve.
+//
+// Replaces solve_3d_cminpack_lmder (adjust_cminpack_lmder.cpp:64-198) and the
+// tail of solveFrames (adjust_base.cpp:1076-1287).  The control law is
+// MINPACK's lmder/lmpar evaluated by single-block
+// control kernels on the device; the linear algebra is the Schur/Cholesky
+// path of lm_kernels.cuh.  The host enqueues kernels and reads the flag words
+// of LmState to know what to enqueue next.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+
 #include "lm.h"
+#include "lm_kernels.cuh"
+
 namespace mmb {
-struct LmWorkspace { int dummy; };
+
+constexpr int kRedBlocks = 592;  // 148 SMs x 4 partial-sum blocks
+
+struct LmWorkspace {
+    LmDims d{};
+    DeviceArena arena;
+    LmState *st = nullptr;     // device
+    LmState *h_st = nullptr;   // pinned host mirror
+    int32_t *attr_slot = nullptr, *i2p = nullptr;
+    double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
+    double *Lf = nullptr, *Ld = nullptr;
+    double *diag = nullptr, *acnorm = nullptr;        // [n] by parameter id
+    double *p_int = nullptr, *w_int = nullptr;        // [KE + NSP] internal order
+    double *p_par = nullptr, *x2 = nullptr;           // [n] parameter order
+    double *fvec2 = nullptr, *dist2 = nullptr;
+    double *part_f = nullptr, *part_jp = nullptr;     // [kRedBlocks]
+    double *part_gemv = nullptr;                      // [chunks * NSP]
+    int gemv_chunks = 1;
+    double init_avg = 0, init_min = 0, init_max = 0;
+    ~LmWorkspace() {
+        if (h_st) cudaFreeHost(h_st);
+    }
+};
+
 void lm_workspace_destroy(LmWorkspace *w) { delete w; }
-mmb_status lm_solve(DeviceProblem *, mmb_result *, double *, double *, double *) {
-    set_last_error("lm_solve: not built yet");
-    return MMB_ERR_UNSUPPORTED;
+
+// ---- control kernels (one block of 1024 threads) ---------------------------------------
+__device__ double sum_partials(const double *part, int n, double *sh) {
+    double a = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) a += part[i];
+    return block_sum(a, sh);
 }
+
+__global__ void k_ctrl_init(LmState *st, const double *part_f, int nparts) {
+    __shared__ double sh[32];
+    const double ss = sum_partials(part_f, nparts, sh);
+    if (threadIdx.x == 0) {
+        st->fnorm = sqrt(ss);
+        st->par = 0.0; st->par_cur = 0.0;
+        st->iter = 1; st->nfev = 1; st->njev = 0; st->info = 0;
+        st->need_jacobian = 1; st->done = 0; st->accepted = 0;
+        st->delta = 0.0; st->xnorm = 0.0; st->gnorm = 0.0;
+        st->chol_fail_total = 0; st->n_factor = 0;
+        // lmder input checks (info = 0: improper input parameters)
+        if (st->n <= 0 || st->m < st->n || st->ftol < 0.0 || st->xtol < 0.0 || st->gtol < 0.0 ||
+            st->maxfev <= 0 || st->factor <= 0.0) {
+            st->info = 0; st->done = 1;
+        }
+    }
+}
+
+// After assembly: column norms, diag, delta (first iteration), gnorm / gtol test,
+// and the start of lmpar.
+__global__ void __launch_bounds__(1024) k_ctrl_prep(LmDims d, LmState *st, const double *U, const double *gE,
+                                                    const double *V, const int32_t *i2p, const double *x,
+                                                    double *diag, double *acnorm) {
+    __shared__ double sh[32];
+    const int n = d.n;
+    const bool first = st->iter == 1;
+    const double fnorm = st->fnorm;
+    double xs = 0.0, gmax = 0.0, gs = 0.0;
+    for (int q = threadIdx.x; q < n; q += blockDim.x) {
+        const int pid = i2p[q];
+        double h, g;
+        if (q < d.KE) {
+            const int f = q / d.na, a = q - f * d.na;
+            h = U[((size_t)f * d.na + a) * d.na + a];
+            g = gE[q];
+        } else {
+            const int s = q - d.KE;
+            h = V[(size_t)s * d.NSP + s];
+            g = V[(size_t)d.ns * d.NSP + s];
+        }
+        const double ac = sqrt(fmax(h, 0.0));
+        acnorm[pid] = ac;
+        double dg = diag[pid];
+        if (st->mode != 2) {
+            if (first) dg = (ac == 0.0) ? 1.0 : ac;
+        }
+        if (first) {
+            const double t = dg * x[pid];
+            xs += t * t;
+        }
+        if (fnorm != 0.0 && ac != 0.0) gmax = fmax(gmax, fabs(g / fnorm) / ac);
+        if (st->mode != 2) dg = fmax(dg, ac);
+        diag[pid] = dg;
+        const double t2 = g / dg;
+        gs += t2 * t2;
+    }
+    xs = block_sum(xs, sh);
+    gs = block_sum(gs, sh);
+    // max-reduce
+    __syncthreads();
+    for (int o = 16; o > 0; o >>= 1) gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o));
+    __shared__ double wmax[32];
+    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = gmax;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double g = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) g = fmax(g, wmax[w]);
+        st->njev += 1;
+        if (first) {
+            st->xnorm = sqrt(xs);
+            st->delta = st->factor * st->xnorm;
+            if (st->delta == 0.0) st->delta = st->factor;
+        }
+        st->gnorm = g;
+        st->gnorm_scaled = sqrt(gs);
+        st->need_jacobian = 0;
+        if (g <= st->gtol) { st->info = 4; st->done = 1; }
+        st->lmpar_iter = 0; st->lmpar_done = 0; st->chol_fail = 0; st->par_cur = 0.0;
+    }
+}
+
+// dxnorm = ||D p|| after a solve (needed by the q-solve that follows)
+__global__ void __launch_bounds__(1024) k_dxnorm(LmDims d, LmState *st, const double *p_int, const double *diag,
+                                                 const int32_t *i2p) {
+    __shared__ double sh[32];
+    double a = 0.0;
+    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
+        const double t = diag[i2p[q]] * p_int[q < d.KE ? q : q];
+        a += t * t;
+    }
+    a = block_sum(a, sh);
+    if (threadIdx.x == 0) {
+        st->dxnorm = st->chol_fail ? INFINITY : sqrt(a);
+        st->n_factor += 1;
+    }
+}
+
+// lmpar step (MINPACK lmpar restated on the normal equations)
+__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int) {
+    __shared__ double sh[32];
+    double a = 0.0;
+    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
+        const double t = w_int[q];
+        a += t * t;
+    }
+    a = block_sum(a, sh);
+    if (threadIdx.x != 0) return;
+    const double p1 = 0.1, p001 = 0.001, dwarf = 2.2250738585072014e-308;
+    const double delta = st->delta;
+    const bool fail = st->chol_fail != 0;
+    if (fail) st->chol_fail_total += 1;
+    st->chol_fail = 0;
+    const double qn2 = a;
+    st->qnorm2 = qn2;
+    if (st->lmpar_iter == 0) {
+        // Gauss-Newton probe at par = 0
+        const double dxnorm = st->dxnorm;
+        const double fp = dxnorm - delta;
+        st->fp = fp;
+        if (!fail && fp <= p1 * delta) { st->par = 0.0; st->lmpar_done = 1; return; }
+        double parl = 0.0;
+        if (!fail && qn2 > 0.0) parl = ((fp / delta) / qn2);
+        double paru = st->gnorm_scaled / delta;
+        if (paru == 0.0) paru = dwarf / fmin(delta, p1);
+        double par = st->par;
+        par = fmax(par, parl);
+        par = fmin(par, paru);
+        if (par == 0.0) par = fail ? 0.0 : st->gnorm_scaled / dxnorm;
+        if (par == 0.0) par = fmax(dwarf, p001 * paru);
+        st->parl = parl; st->paru = paru; st->par = par; st->par_cur = par;
+        st->lmpar_iter = 1;
+        return;
+    }
+    if (fail) {
+        // damped system not positive definite (numerical): raise the damping
+        st->parl = fmax(st->parl, st->par);
+        st->par = fmax(st->par * 10.0, p001 * st->paru);
+        st->par_cur = st->par;
+        st->lmpar_iter += 1;
+        if (st->lmpar_iter > 30) { st->lmpar_done = 1; st->info = -2; st->done = 1; }
+        return;
+    }
+    const double temp = st->fp;
+    const double fp = st->dxnorm - delta;
+    st->fp = fp;
+    if (fabs(fp) <= p1 * delta || (st->parl == 0.0 && fp <= temp && temp < 0.0) || st->lmpar_iter >= 10) {
+        st->lmpar_done = 1;
+        return;
+    }
+    const double parc = ((fp / delta) / qn2);
+    if (fp > 0.0) st->parl = fmax(st->parl, st->par);
+    if (fp < 0.0) st->paru = fmin(st->paru, st->par);
+    double par = fmax(st->parl, st->par + parc);
+    if (par == 0.0) par = fmax(dwarf, p001 * st->paru);
+    st->par = par; st->par_cur = par;
+    st->lmpar_iter += 1;
+}
+
+// trial point: x2 = x - p, pnorm = ||D p||, delta clamp on the first iteration
+__global__ void __launch_bounds__(1024) k_ctrl_trial(LmDims d, LmState *st, const double *p_int, const int32_t *i2p,
+                                                     const double *diag, const double *x, double *x2, double *p_par) {
+    __shared__ double sh[32];
+    double a = 0.0;
+    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
+        const int pid = i2p[q];
+        const double step = -p_int[q];
+        p_par[pid] = step;
+        x2[pid] = x[pid] + step;
+        const double t = diag[pid] * step;
+        a += t * t;
+    }
+    a = block_sum(a, sh);
+    if (threadIdx.x == 0) {
+        st->pnorm = sqrt(a);
+        if (st->iter == 1) st->delta = fmin(st->delta, st->pnorm);
+    }
+}
+
+// ratio test, delta / par update, accept / reject, convergence tests
+__global__ void __launch_bounds__(1024) k_ctrl_accept(LmDims d, LmState *st, const double *part_f, const double *part_jp,
+                                                      int nparts, const double *diag, const double *x2) {
+    __shared__ double sh[32];
+    const double ss1 = sum_partials(part_f, nparts, sh);
+    const double jp2 = sum_partials(part_jp, nparts, sh);
+    double xs = 0.0;
+    for (int i = threadIdx.x; i < d.n; i += blockDim.x) {
+        const double t = diag[i] * x2[i];
+        xs += t * t;
+    }
+    xs = block_sum(xs, sh);
+    if (threadIdx.x != 0) return;
+    const double p1 = 0.1, p5 = 0.5, p25 = 0.25, p75 = 0.75, p0001 = 1e-4, epsmch = 2.220446049250313e-16;
+    const double fnorm = st->fnorm, fnorm1 = sqrt(ss1), pnorm = st->pnorm;
+    st->fnorm1 = fnorm1;
+    st->jp_sumsq = jp2;
+    st->nfev += 1;
+    double actred = -1.0;
+    if (p1 * fnorm1 < fnorm) { const double t = fnorm1 / fnorm; actred = 1.0 - t * t; }
+    const double temp1 = sqrt(jp2) / fnorm;
+    const double temp2 = (sqrt(st->par) * pnorm) / fnorm;
+    const double prered = temp1 * temp1 + temp2 * temp2 / p5;
+    const double dirder = -(temp1 * temp1 + temp2 * temp2);
+    double ratio = 0.0;
+    if (prered != 0.0) ratio = actred / prered;
+    if (ratio <= p25) {
+        double temp;
+        if (actred >= 0.0) temp = p5; else temp = p5 * dirder / (dirder + p5 * actred);
+        if (p1 * fnorm1 >= fnorm || temp < p1) temp = p1;
+        st->delta = temp * fmin(st->delta, pnorm / p1);
+        st->par /= temp;
+    } else if (st->par == 0.0 || ratio >= p75) {
+        st->delta = pnorm / p5;
+        st->par = p5 * st->par;
+    }
+    st->accepted = 0;
+    if (ratio >= p0001) {
+        st->accepted = 1;
+        st->xnorm = sqrt(xs);
+        st->fnorm = fnorm1;
+        st->iter += 1;
+    }
+    st->ratio = ratio; st->actred = actred; st->prered = prered;
+    int info = 0;
+    const bool small_red = fabs(actred) <= st->ftol && prered <= st->ftol && p5 * ratio <= 1.0;
+    if (small_red) info = 1;
+    if (st->delta <= st->xtol * st->xnorm) info = 2;
+    if (small_red && info == 2) info = 3;
+    if (info == 0) {
+        if (st->nfev >= st->maxfev) info = 5;
+        if (fabs(actred) <= epsmch && prered <= epsmch && p5 * ratio <= 1.0) info = 6;
+        if (st->delta <= epsmch * st->xnorm) info = 7;
+        if (st->gnorm <= epsmch) info = 8;
+    }
+    if (info != 0) { st->info = info; st->done = 1; }
+    // next pass: a new Jacobian after an accepted step, else lmpar again
+    st->need_jacobian = st->accepted;
+    st->lmpar_iter = 0; st->lmpar_done = 0; st->par_cur = 0.0; st->chol_fail = 0;
+}
+
+__global__ void k_accept_copy(const LmState *st, size_t n, size_t m, size_t nobs, const double *x2, double *x,
+                              const double *f2, double *f, const double *d2, double *dd) {
+    if (!st->accepted) return;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < m; i += (size_t)gridDim.x * blockDim.x) {
+        f[i] = f2[i];
+        if (i < n) x[i] = x2[i];
+        if (i < nobs) dd[i] = d2[i];
+    }
+}
+
+// compute_error_stats (adjust_base.cpp:346-372): avg / min / max of finite distances
+__global__ void __launch_bounds__(1024) k_error_stats(LmState *st, const double *dist, int nobs) {
+    __shared__ double sh[32];
+    __shared__ double smin[32], smax[32];
+    double a = 0.0, mn = 1.7976931348623157e308, mx = -0.0;
+    for (int i = threadIdx.x; i < nobs; i += blockDim.x) {
+        const double e = dist[i];
+        if (!isfinite(e)) continue;
+        a += e; mn = fmin(mn, e); mx = fmax(mx, e);
+    }
+    a = block_sum(a, sh);
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) { smin[threadIdx.x >> 5] = mn; smax[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { mn = fmin(mn, smin[w]); mx = fmax(mx, smax[w]); }
+        st->err_avg = a / (double)nobs; st->err_min = mn; st->err_max = mx;
+    }
+}
+
+// ---- workspace ------------------------------------------------------------------------------
+static mmb_status lm_workspace_create(DeviceProblem *p) {
+    if (p->lm) return MMB_OK;
+    const HostProblem &hp = p->hp;
+    if (hp.na > kMaxNA) {
+        set_last_error("more than 64 animated solver attributes per frame are not supported");
+        return MMB_ERR_UNSUPPORTED;
+    }
+    LmWorkspace *w = new LmWorkspace();
+    LmDims &d = w->d;
+    d.F = hp.F; d.na = hp.na; d.ns = hp.ns; d.NS1 = hp.ns + 1;
+    d.NSP = ((d.NS1 + 63) / 64) * 64;
+    d.KE = hp.F * hp.na; d.KEP = ((d.KE + kSyrkKT - 1) / kSyrkKT) * kSyrkKT;
+    d.n = hp.n; d.nobs = hp.nobs; d.m = hp.m; d.kmax = p->ds.kmax;
+    DeviceArena &A = w->arena;
+#define CKW(expr)                                                                \
+    do {                                                                         \
+        cudaError_t _e = (expr);                                                 \
+        if (_e != cudaSuccess) {                                                 \
+            set_last_error(std::string(#expr) + ": " + cudaGetErrorString(_e));  \
+            delete w;                                                            \
+            return MMB_ERR_CUDA;                                                 \
+        }                                                                        \
+    } while (0)
+    CKW(A.alloc(&w->st, 1));
+    CKW(cudaMallocHost((void **)&w->h_st, sizeof(LmState)));
+    CKW(A.upload(&w->attr_slot, hp.attr_slot));
+    CKW(A.upload(&w->i2p, hp.int_to_par));
+    CKW(A.alloc(&w->U, (size_t)d.F * d.na * d.na));
+    CKW(A.alloc(&w->gE, (size_t)d.KE));
+    CKW(A.alloc(&w->W, (size_t)d.KE * d.NSP));
+    CKW(A.alloc(&w->Y, (size_t)d.KEP * d.NSP));
+    CKW(cudaMemset(w->Y, 0, sizeof(double) * std::max<size_t>((size_t)d.KEP * d.NSP, 1)));
+    CKW(A.alloc(&w->V, (size_t)d.NSP * d.NSP));
+    CKW(A.alloc(&w->S, (size_t)d.NSP * d.NSP));
+    CKW(A.alloc(&w->Lf, (size_t)d.F * d.na * d.na));
+    CKW(A.alloc(&w->Ld, (size_t)64 * 64));
+    CKW(A.alloc(&w->diag, (size_t)d.n));
+    CKW(A.alloc(&w->acnorm, (size_t)d.n));
+    CKW(A.alloc(&w->p_int, (size_t)d.KE + d.NSP));
+    CKW(A.alloc(&w->w_int, (size_t)d.KE + d.NSP));
+    CKW(A.alloc(&w->p_par, (size_t)d.n));
+    CKW(A.alloc(&w->x2, (size_t)d.n));
+    CKW(A.alloc(&w->fvec2, (size_t)d.m));
+    CKW(A.alloc(&w->dist2, (size_t)d.nobs));
+    CKW(A.alloc(&w->part_f, (size_t)kRedBlocks));
+    CKW(A.alloc(&w->part_jp, (size_t)kRedBlocks));
+    w->gemv_chunks = std::max(1, std::min(64, d.KE / 256));
+    CKW(A.alloc(&w->part_gemv, (size_t)w->gemv_chunks * d.NSP));
+    CKW(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 64 * kCS * (int)sizeof(double)));
+#undef CKW
+    p->lm = w;
+    return MMB_OK;
+}
+
+// ---- enqueue helpers ------------------------------------------------------------------------
+#define LAUNCH_CHECK()                                  \
+    do {                                                \
+        ++p->launches;                                  \
+        MMB_CUDA_CHECK(cudaGetLastError());             \
+    } while (0)
+
+static mmb_status read_state(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    MMB_CUDA_CHECK(cudaMemcpyAsync(w->h_st, w->st, sizeof(LmState), cudaMemcpyDeviceToHost, p->stream));
+    MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
+    return MMB_OK;
+}
+
+static mmb_status enqueue_residual_eval(DeviceProblem *p, const double *d_x, double *d_f, double *d_dist) {
+    LmWorkspace *w = p->lm;
+    mmb_status st;
+    if ((st = launch_set_parameters(p, d_x)) != MMB_OK) return st;
+    if ((st = launch_variants(p, d_x, false)) != MMB_OK) return st;
+    if ((st = launch_residuals(p, d_f, d_dist)) != MMB_OK) return st;
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(d_f, (size_t)p->hp.m, w->part_f);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
+static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    const LmDims &d = w->d;
+    mmb_status st;
+    if ((st = launch_set_parameters(p, p->d_x)) != MMB_OK) return st;
+    if ((st = launch_variants(p, p->d_x, true)) != MMB_OK) return st;
+    if ((st = launch_jacobian(p, nullptr, nullptr, p->d_jac, nullptr, w->dist2)) != MMB_OK) return st;
+    if (d.KE) {
+        MMB_CUDA_CHECK(cudaMemsetAsync(w->U, 0, sizeof(double) * (size_t)d.F * d.na * d.na, p->stream));
+        MMB_CUDA_CHECK(cudaMemsetAsync(w->gE, 0, sizeof(double) * (size_t)d.KE, p->stream));
+        MMB_CUDA_CHECK(cudaMemsetAsync(w->W, 0, sizeof(double) * (size_t)d.KE * d.NSP, p->stream));
+    }
+    MMB_CUDA_CHECK(cudaMemsetAsync(w->V, 0, sizeof(double) * (size_t)d.NSP * d.NSP, p->stream));
+    k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->U, w->gE, w->W, w->V);
+    LAUNCH_CHECK();
+    k_ctrl_prep<<<1, 1024, 0, p->stream>>>(d, w->st, w->U, w->gE, w->V, w->i2p, p->d_x, w->diag, w->acnorm);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
+// one factorisation + solve + Newton-correction solve at st->par_cur, then the lmpar control step
+static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    const LmDims &d = w->d;
+    cudaStream_t s = p->stream;
+    if (d.KE) {
+        const size_t sm = sizeof(double) * ((size_t)d.na * d.na + d.na);
+        k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
+        LAUNCH_CHECK();
+    }
+    {
+        const size_t tot = (size_t)d.NSP * d.NSP;
+        k_schur_init<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(d, w->st, w->V, w->diag, w->i2p, w->S);
+        LAUNCH_CHECK();
+    }
+    const int nb = d.NSP / 64;
+    if (d.KE) {
+        const int tiles = nb * (nb + 1) / 2;
+        int ksplit = 1;
+        while (tiles * ksplit < 296 && ksplit < 16 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
+        k_schur_syrk<<<dim3(tiles, ksplit), 128, 0, s>>>(d, w->Y, w->S);
+        LAUNCH_CHECK();
+    }
+    for (int kb = 0; kb < nb; ++kb) {
+        k_chol_panel<<<nb - kb, 256, 2 * 64 * kCS * sizeof(double), s>>>(d, kb, w->st, w->S, w->Ld);
+        LAUNCH_CHECK();
+        const int nt = nb - kb - 1;
+        k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
+        LAUNCH_CHECK();
+    }
+    k_backward_s<<<1, 1024, 0, s>>>(d, w->S, w->p_int + d.KE);
+    LAUNCH_CHECK();
+    if (d.KE) {
+        k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
+        LAUNCH_CHECK();
+    }
+    k_dxnorm<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->diag, w->i2p);
+    LAUNCH_CHECK();
+    // Newton correction: w = L^-1 (D^2 p / dxnorm)
+    if (d.KE) {
+        k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->st, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
+        LAUNCH_CHECK();
+        k_gemv_t_partial<<<dim3((d.ns + 127) / 128 > 0 ? (d.ns + 127) / 128 : 1, w->gemv_chunks), 128, 0, s>>>(d, w->Y, w->w_int, w->part_gemv);
+        LAUNCH_CHECK();
+    }
+    if (d.ns) {
+        k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->st, d.KE ? w->gemv_chunks : 0, w->part_gemv, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
+        LAUNCH_CHECK();
+        k_forward_s<<<1, 1024, 0, s>>>(d, w->S, w->w_int + d.KE, w->w_int + d.KE);
+        LAUNCH_CHECK();
+    }
+    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
+static mmb_status enqueue_trial(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    const LmDims &d = w->d;
+    cudaStream_t s = p->stream;
+    k_ctrl_trial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->i2p, w->diag, p->d_x, w->x2, w->p_par);
+    LAUNCH_CHECK();
+    mmb_status st = enqueue_residual_eval(p, w->x2, w->fvec2, w->dist2);
+    if (st != MMB_OK) return st;
+    k_jp_partial<<<kRedBlocks, 256, 0, s>>>(p->ds, d, p->d_jac, w->p_par, w->part_jp);
+    LAUNCH_CHECK();
+    k_ctrl_accept<<<1, 1024, 0, s>>>(d, w->st, w->part_f, w->part_jp, kRedBlocks, w->diag, w->x2);
+    LAUNCH_CHECK();
+    k_accept_copy<<<296, 256, 0, s>>>(w->st, (size_t)d.n, (size_t)d.m, (size_t)d.nobs, w->x2, p->d_x, w->fvec2, p->d_fvec, w->dist2, p->d_dist);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
+using clk = std::chrono::steady_clock;
+static double secs(clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); }
+
+mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out) {
+    std::memset(res, 0, sizeof(*res));
+    const HostProblem &hp = p->hp;
+    // pre-checks of solveFrames (adjust_base.cpp:844-882)
+    if (hp.nobs == 0 || hp.n == 0) { set_last_error("no used markers or attributes"); return MMB_ERR_NOT_ENOUGH_OBJECTS; }
+    if (hp.n > hp.m) { set_last_error("more parameters than errors"); return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
+    MMB_CUDA_CHECK(cudaSetDevice(p->device));
+    mmb_status st;
+    if ((st = ensure_jacobian_buffers(p)) != MMB_OK) return st;
+    if ((st = lm_workspace_create(p)) != MMB_OK) return st;
+    LmWorkspace *w = p->lm;
+    const LmDims &d = w->d;
+    const auto t_begin = clk::now();
+    p->cancel = 0;
+
+    // initial parameters (get_initial_parameters, adjust_base.cpp:260-295)
+    std::vector<double> x0(hp.n);
+    for (int i = 0; i < hp.n; ++i) {
+        const int a = hp.par_attr[i], f = hp.par_frame[i];
+        const int32_t ref = hp.attr_ref[a];
+        const double v = ref >= 0 ? hp.stat0[ref] : hp.anim0[(size_t)(-ref - 1) * hp.F + f];
+        x0[i] = bound_external_to_internal(v, hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
+    }
+    MMB_CUDA_CHECK(cudaMemcpyAsync(p->d_x, x0.data(), sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
+    if ((st = launch_reset_store(p)) != MMB_OK) return st;
+
+    LmState h{};
+    h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
+    h.ftol = hp.opt.eps1; h.xtol = hp.opt.eps2; h.gtol = hp.opt.eps3; h.factor = hp.opt.tau * 100.0;
+    *w->h_st = h;
+    MMB_CUDA_CHECK(cudaMemcpyAsync(w->st, w->h_st, sizeof(LmState), cudaMemcpyHostToDevice, p->stream));
+    MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
+    {   // diag = paramWeightList = 1.0 (adjust_relationships.cpp:320)
+        std::vector<double> ones(hp.n, 1.0);
+        MMB_CUDA_CHECK(cudaMemcpyAsync(w->diag, ones.data(), sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
+        MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
+    }
+    double t_jac = 0, t_func = 0, t_lin = 0;
+    int func_evals = 0, jac_evals = 0;
+
+    // initial measureErrors when acceptOnlyBetter (adjust_base.cpp:1080-1103): at the
+    // scene's own values, before any parameter is set.
+    double init_avg = 0.0;
+    if (hp.opt.accept_only_better) {
+        if ((st = launch_variants(p, p->d_x, false)) != MMB_OK) return st;
+        if ((st = launch_residuals(p, p->d_fvec, p->d_dist)) != MMB_OK) return st;
+        k_error_stats<<<1, 1024, 0, p->stream>>>(w->st, p->d_dist, hp.nobs);
+        LAUNCH_CHECK();
+        if ((st = read_state(p)) != MMB_OK) return st;
+        init_avg = w->h_st->err_avg;
+    }
+    // first function evaluation
+    auto t0 = clk::now();
+    if ((st = enqueue_residual_eval(p, p->d_x, p->d_fvec, p->d_dist)) != MMB_OK) return st;
+    k_ctrl_init<<<1, 1024, 0, p->stream>>>(w->st, w->part_f, kRedBlocks);
+    LAUNCH_CHECK();
+    if ((st = read_state(p)) != MMB_OK) return st;
+    t_func += secs(t0, clk::now());
+    ++func_evals;
+
+    int guard = 0;
+    while (!w->h_st->done) {
+        if (p->cancel) { res->user_interrupted = 1; break; }
+        if (++guard > 100000) break;
+        if (w->h_st->need_jacobian) {
+            t0 = clk::now();
+            if ((st = enqueue_jacobian_and_assembly(p)) != MMB_OK) return st;
+            if ((st = read_state(p)) != MMB_OK) return st;
+            t_jac += secs(t0, clk::now());
+            jac_evals += hp.n * (hp.opt.auto_diff_type == 1 ? 2 : 1);
+            if (w->h_st->done) break;
+        }
+        t0 = clk::now();
+        while (!w->h_st->lmpar_done && !w->h_st->done) {
+            if ((st = enqueue_lmpar_step(p)) != MMB_OK) return st;
+            if ((st = read_state(p)) != MMB_OK) return st;
+        }
+        t_lin += secs(t0, clk::now());
+        if (w->h_st->done) break;
+        t0 = clk::now();
+        if ((st = enqueue_trial(p)) != MMB_OK) return st;
+        if ((st = read_state(p)) != MMB_OK) return st;
+        t_func += secs(t0, clk::now());
+        ++func_evals;
+    }
+    // results (adjust_cminpack_lmder.cpp:185-197, adjust_base.cpp:1201-1282)
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)hp.m, w->part_f);
+    LAUNCH_CHECK();
+    // errorDistanceList holds whatever the LAST measureErrors call left there (a
+    // rejected trial or the last FD perturbation included): dist2 tracks that.
+    k_error_stats<<<1, 1024, 0, p->stream>>>(w->st, w->dist2, hp.nobs);
+    LAUNCH_CHECK();
+    std::vector<double> part(kRedBlocks), x(hp.n);
+    MMB_CUDA_CHECK(cudaMemcpyAsync(part.data(), w->part_f, sizeof(double) * kRedBlocks, cudaMemcpyDeviceToHost, p->stream));
+    MMB_CUDA_CHECK(cudaMemcpyAsync(x.data(), p->d_x, sizeof(double) * hp.n, cudaMemcpyDeviceToHost, p->stream));
+    if (dist_out)
+        MMB_CUDA_CHECK(cudaMemcpyAsync(dist_out, w->dist2, sizeof(double) * hp.nobs, cudaMemcpyDeviceToHost, p->stream));
+    if ((st = read_state(p)) != MMB_OK) return st;
+    const LmState &f = *w->h_st;
+    double ss = 0.0;
+    for (double v : part) ss += v;
+    res->error_final = std::sqrt(ss);
+    res->success = func_evals > 0 ? 1 : 0;  // success = iterNum > 0
+    res->reason_num = res->user_interrupted ? -1 : f.info;
+    res->iteration_num = f.nfev;
+    res->iteration_function_num = func_evals;
+    res->iteration_jacobian_num = jac_evals;
+    res->iteration_attempt_num = f.njev;
+    res->error_avg = f.err_avg; res->error_min = f.err_min; res->error_max = f.err_max;
+    bool better = true;
+    if (hp.opt.accept_only_better) better = f.err_avg <= init_avg;
+    res->error_is_better = better ? 1 : 0;
+    for (int i = 0; i < hp.n; ++i) {
+        const int a = hp.par_attr[i];
+        if (x_out) x_out[i] = x[i];
+        if (attr_out)
+            attr_out[i] = bound_internal_to_external(better ? x[i] : x0[i], hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
+    }
+    res->timer_solve_s = secs(t_begin, clk::now());
+    res->timer_jacobian_s = t_jac;
+    res->timer_function_s = t_func;
+    res->timer_linear_s = t_lin;
+    (void)d;
+    return MMB_OK;
+}
+
 }  // namespace mmb
