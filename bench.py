@@ -1,0 +1,259 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 mmSolver solve hot path.
+
+Metric (BASELINE.json): marker-frame residual+FD-Jacobian evals/s.
+One *eval* = one observation (marker x frame) producing its 2 residuals and its
+whole block-Jacobian row pair (all 1+k perturbed re-evaluations count as that
+one eval).
+
+A *step* = one residual+FD-Jacobian evaluation of the whole workload scene
+(setParameters + entity variants + the residual/Jacobian kernel), inputs
+resident in HBM.  L2 is flushed (256 MiB memset, outside the event brackets)
+before every step.  `value` = evals of all ranks / max-over-ranks device time.
+`e2e` = the same metric through the public C-ABI solve call (mmb_problem_create
++ mmb_solve + destroy) with HOST buffers: evals done by the solve / wall time.
+Extra keys report LM iterations/s and solved frames/s of the global solve and
+of the per-frame (batched) solve.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "cfg3: global camera+bundle solve, 1000 frames x 500 bundles (n=7500, 500000 observations per GPU)"
+CPU_SAMPLE = dict(F=40, B=40, seed=3)   # bounded sample of the same workload for the CPU legs
+
+
+def _peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            return json.load(fh), "measured (MEASURED_PEAKS.json)"
+    return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self._halt = threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [t.strip() for t in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._halt.wait(0.1)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=5)
+        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.samples)}
+
+
+def cpu_reference_leg(steps=1, warmup=0):
+    """The reference's own CPU cost structure for this path, restated (oracle/):
+    one whole-scene evaluation per Jacobian column, dense column-major J, dense
+    pivoted-QR lmder, single thread (the reference has no threads under
+    src/mmSolver/adjust).  Bounded sample of the workload; returns evals/s."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from oraclelib import OracleProblem
+    from mayamatchmovesolver_b200 import synth
+    sb, _ = synth.make_scene(fixed_bundles=3, **CPU_SAMPLE)
+    times, evals, iters = [], 0, 0
+    for i in range(warmup + steps):
+        o = OracleProblem(sb, faithful=True, iter_max=12)
+        t0 = time.perf_counter()
+        r = o.solve(structural_skip=False)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+            evals += o.nobs * r.iteration_attempt_num
+            iters += r.iteration_attempt_num
+    total = sum(times)
+    sample = ("scaled cfg3 (F=%d, B=%d: n=%d, m=%d), oracle/ faithful dense path, %d LM iterations per solve"
+              % (CPU_SAMPLE["F"], CPU_SAMPLE["B"], o.n, o.m, iters // max(1, steps)))
+    return dict(value=evals / total, seconds=total, lm_iters_per_s=iters / total,
+                frames_per_s=CPU_SAMPLE["F"] * steps / total, sample=sample, ms_per_step=1e3 * total / steps)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    leg = cpu_reference_leg(steps=max(1, min(args.steps, 3)), warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": "marker-frame residual+FD-Jacobian evals/s", "value": leg["value"],
+        "unit": "evals/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": leg["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": leg["sample"]},
+        "cpu_baseline": {"value": leg["value"], "unit": "evals/s", "cores": 1, "kind": "port", "sample": leg["sample"]},
+        "e2e": {"value": leg["value"], "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "lm_iters_per_s": leg["lm_iters_per_s"], "solved_frames_per_s": leg["frames_per_s"],
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def run_own(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from mayamatchmovesolver_b200 import synth
+    from mayamatchmovesolver_b200.problem import Problem
+
+    F, B = 1000, 500
+    sb, _ = synth.make_scene(F, B, 3 + rank)
+    p = Problem(sb, device=local)
+    k = p.jacobian_kmax()
+    bytes_per_obs = 48 + 16 * k  # marker 24 B + residuals 16 B + distance 8 B + 2*k*8 B block J
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    sampler = ClockSampler(local)
+    for _ in range(args.warmup):
+        p.bench_eval(1, True)
+    barrier()
+    sampler.start()
+    l0 = p.launch_count()
+    tot_ms = jac_ms = 0.0
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        ms, msj, _ = p.bench_eval(1, True)
+        tot_ms += ms
+        jac_ms += msj
+    t_wall = time.perf_counter() - t_wall0
+    launches = p.launch_count() - l0
+    barrier()
+    clocks = sampler.stop()
+    if dist is not None:
+        import torch
+        t = torch.tensor([tot_ms, jac_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tot_ms, jac_ms = float(t[0]), float(t[1])
+        lt = torch.tensor([launches], device="cuda", dtype=torch.int64)
+        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
+        launches = int(lt[0])
+    evals_all = world * p.nobs * args.steps
+    value = evals_all / (tot_ms * 1e-3)
+    ms_per_step = tot_ms / args.steps
+
+    # ---- end to end through the public solve call, host buffers ----------
+    def e2e_once(seed):
+        sb2, _ = synth.make_scene(F, B, seed, noise_px=0.5)
+        arrays = sb2.arrays()
+        h2d = sum(a.nbytes for a in arrays.values())
+        t0 = time.perf_counter()
+        with Problem(sb2, device=local, iter_max=20) as q:
+            r = q.solve()
+            d2h = 8 * (2 * q.n + q.nobs) + 160
+            nobs = q.nobs
+        dt = time.perf_counter() - t0
+        return r, dt, h2d, d2h, nobs
+    e2e_once(100 + rank)  # warm-up (module load, allocations)
+    barrier()
+    r, dt, h2d, d2h, nobs = e2e_once(200 + rank)
+    e2e_evals = nobs * r.iteration_attempt_num
+    stats = np.array([dt, r.timer_solve_s], dtype=np.float64)
+    if dist is not None:
+        import torch
+        t = torch.tensor(stats, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        stats = t.cpu().numpy()
+    e2e_value = world * e2e_evals / stats[0]
+    lm_iters_per_s = r.iteration_attempt_num / stats[1]
+    frames_per_s = world * F / stats[0]
+
+    if rank != 0:
+        return
+    peaks, peaks_src = _peaks()
+    algo_bytes = p.nobs * bytes_per_obs
+    achieved = algo_bytes / (jac_ms / args.steps * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic_k_jacobian.json")
+    if os.path.exists(tp):
+        with open(tp) as fh:
+            traffic = json.load(fh).get("dram_bytes_per_launch")
+    line = {
+        "metric": "marker-frame residual+FD-Jacobian evals/s", "value": value, "unit": "evals/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames": F, "bundles": B, "params": p.n, "observations_per_gpu": p.nobs,
+                   "local_params_per_obs_k": k, "l2": "flushed before every step (256 MiB memset outside the event brackets)",
+                   "sharding": "independent frame-range shards per GPU, no data-path collective"},
+        "clocks": clocks,
+        "gpu_launches": launches,
+        "wall_s_timed_region": t_wall,
+        "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "what": "mmb_problem_create + mmb_solve (iter_max=20) + destroy with host buffers; evals = observations x Jacobian evaluations",
+                "seconds": float(stats[0]), "lm_outer_iterations": r.iteration_attempt_num, "nfev": r.iteration_num,
+                "reason_num": r.reason_num, "error_avg_px": r.error_avg},
+        "lm_iters_per_s": lm_iters_per_s,
+        "solved_frames_per_s": frames_per_s,
+        "roofline": {"bound": "hbm", "kernel": "k_jacobian", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes,
+                     "peak_source": peaks_src, "kernel_ms": jac_ms / args.steps},
+    }
+    if world == 1 and not args.no_cpu:
+        leg = cpu_reference_leg(steps=1)
+        line["cpu_baseline"] = {"value": leg["value"], "unit": "evals/s", "cores": 1, "kind": "port",
+                                "sample": leg["sample"], "seconds": leg["seconds"]}
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_own(args)
+
+
+if __name__ == "__main__":
+    main()

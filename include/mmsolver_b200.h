@@ -236,9 +236,15 @@ void mmb_request_cancel(mmb_problem *p);
 /* device-side benchmarking hooks (inputs already resident in HBM):
  * run `reps` back-to-back residual+FD-Jacobian evaluations at the initial
  * parameters on the problem's stream; returns mean ms per evaluation measured
- * with CUDA events and the number of kernel launches issued. */
+ * with CUDA events (whole evaluation = setParameters + entity variants +
+ * the residual/Jacobian kernel; and that last kernel alone) and the number of
+ * kernel launches issued.  The L2 flush, when asked for, is outside the
+ * timed brackets. */
 mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
-                          double *ms_per_eval, int32_t *launches);
+                          double *ms_per_eval, double *ms_jacobian_kernel,
+                          int32_t *launches);
+/* kernels launched by this handle so far (bench.py's gpu_launches) */
+int64_t mmb_launch_count(const mmb_problem *p);
 
 const char *mmb_status_string(mmb_status s);
 /* detail of the last failing call on this thread (static storage) */

@@ -69,6 +69,7 @@ struct DeviceProblem {
     double *d_jac = nullptr;    // [kmax * m] block Jacobian (lazy)
     int32_t *d_cols = nullptr;  // [nobs * kmax] (lazy)
     double *d_stat0 = nullptr, *d_anim0 = nullptr;  // pristine attribute store
+    double *d_flush = nullptr;  // L2 flush scratch (bench only)
     LmWorkspace *lm = nullptr;
     volatile int cancel = 0;
     long long launches = 0;     // kernels launched by this handle

@@ -136,8 +136,13 @@ class Problem:
         self._lib.mmb_request_cancel(self._h)
 
     def bench_eval(self, reps=10, flush_l2=True):
+        """-> (ms per whole evaluation, ms of the residual/Jacobian kernel alone, launches)"""
         ms = C.c_double()
+        msj = C.c_double()
         launches = C.c_int32()
-        check(self._lib.mmb_bench_eval(self._h, reps, 1 if flush_l2 else 0, C.byref(ms), C.byref(launches)),
-              "mmb_bench_eval")
-        return ms.value, launches.value
+        check(self._lib.mmb_bench_eval(self._h, reps, 1 if flush_l2 else 0, C.byref(ms), C.byref(msj),
+                                       C.byref(launches)), "mmb_bench_eval")
+        return ms.value, msj.value, launches.value
+
+    def launch_count(self):
+        return int(self._lib.mmb_launch_count(self._h))

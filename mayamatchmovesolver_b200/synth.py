@@ -52,7 +52,7 @@ def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
 
 def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, init_noise_t=0.1,
                init_noise_r=0.5, init_noise_b=0.05, fixed_bundles=0, lens=None, solve_focal=False,
-               solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False):
+               solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False, period=120.0):
     """One animated camera, B static bundles, full (or thinned) visibility.
 
     cfg2: make_scene(240, 50, 2, solve_bundles=False)
@@ -65,7 +65,7 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
     rng = np.random.default_rng(seed)
     sensor_w, sensor_h, rw, rh = 36.0, 24.0, 2048, 1556
     pts = np.stack([rng.uniform(-10, 10, B), rng.uniform(-10, 10, B), rng.uniform(-30, -10, B)], 1)
-    cam_t, cam_r = camera_path(F, rng)
+    cam_t, cam_r = camera_path(F, rng, period=period)
     sb = SceneBuilder(frames=np.arange(1, F + 1))
     lens_node = None
     if lens is not None:
