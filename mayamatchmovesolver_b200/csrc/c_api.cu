@@ -133,14 +133,14 @@ mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec, dou
     return MMB_OK;
 }
 
-static mmb_status run_jacobian(DeviceProblem *dp, const double *x) {
+static mmb_status run_jacobian(DeviceProblem *dp, const double *x, bool want_cols = true) {
     mmb_status st;
     if ((st = ensure_jacobian_buffers(dp)) != MMB_OK) return st;
     if ((st = upload_x(dp, x)) != MMB_OK) return st;
     if ((st = launch_reset_store(dp)) != MMB_OK) return st;
     if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
     if ((st = launch_variants(dp, dp->d_x, true)) != MMB_OK) return st;
-    if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, dp->d_cols)) != MMB_OK) return st;
+    if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, want_cols ? dp->d_cols : nullptr)) != MMB_OK) return st;
     return MMB_OK;
 }
 
@@ -151,7 +151,7 @@ mmb_status mmb_eval_jacobian_blocks(mmb_problem *p, const double *x, double *val
     if (k_max) *k_max = dp->ds.kmax;
     if (!values && !col_ids) return MMB_OK;
     if (!x) return MMB_ERR_INVALID_ARGUMENT;
-    mmb_status st = run_jacobian(dp, x);
+    mmb_status st = run_jacobian(dp, x, col_ids != nullptr);
     if (st != MMB_OK) return st;
     const size_t k = dp->ds.kmax;
     if (values)

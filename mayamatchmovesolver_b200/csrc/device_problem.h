@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "eval_bodies.cuh"
+#include "jacobian_tiled.cuh"
 #include "problem.h"
 
 namespace mmb {
@@ -70,6 +71,8 @@ struct DeviceProblem {
     int32_t *d_cols = nullptr;  // [nobs * kmax] (lazy)
     double *d_stat0 = nullptr, *d_anim0 = nullptr;  // pristine attribute store
     double *d_flush = nullptr;  // L2 flush scratch (bench only)
+    bool tiled_ok = false;      // register-tiled Jacobian kernel applies
+    TiledPlan tiled{};
     LmWorkspace *lm = nullptr;
     volatile int cancel = 0;
     long long launches = 0;     // kernels launched by this handle

@@ -120,6 +120,17 @@ MMB_HD AttrView make_view(const DevScene &s, const double *x, int f, int attr, i
     return v;
 }
 
+constexpr int kCamRec = 16;  // doubles per camera variant record
+constexpr int kBndRec = 4;   // doubles per bundle variant record
+
+// 1/deltaA of the parameter a variant perturbs (forward differences), stored
+// next to the variant so the Jacobian kernel needs no per-parameter lookups.
+MMB_HD double variant_inv_delta(const DevScene &s, int f, int attr, int var) {
+    if (var == 0) return 0.0;
+    const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
+    return 1.0 / s.par_delta_a[p];
+}
+
 MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
     // dag.rs:234-327: world = parent_world * local, accumulated leaf -> root
     Aff w;
@@ -135,9 +146,10 @@ MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
     return w;
 }
 
-// One thread per (camera, variant, frame): 14 doubles
-//   [0..11] rows 0,1,3 of P*inv(W);  [12],[13] marker film-fit scale
-// table layout: cam_off[c] + ((v*14 + j) * fs + f)
+// One thread per (camera, variant, frame): kCamRec doubles
+//   [0..11] rows 0,1,3 of P*inv(W);  [12],[13] marker film-fit scale;
+//   [14] 1/deltaA of the perturbed parameter (variants only)
+// table layout: cam_off[c] + ((v*kCamRec + j) * fs + f)
 MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
     const int job = find_job(s.cam_job_start, s.cam_njobs, t);
     const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
@@ -155,10 +167,11 @@ MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long 
     marker_film_fit_scale(s.cam_fit[c], sw / sh, (double)s.cam_rw[c] / (double)s.cam_rh[c], out[12], out[13]);
     double *dst = s.cam_tab + s.cam_off[c];
 #pragma unroll
-    for (int j = 0; j < 14; ++j) dst[((size_t)v * 14 + j) * fs + f] = out[j];
+    for (int j = 0; j < 14; ++j) dst[((size_t)v * kCamRec + j) * fs + f] = out[j];
+    dst[((size_t)v * kCamRec + 14) * fs + f] = variant_inv_delta(s, f, attr, v);
 }
 
-// One thread per (bundle, variant, frame): world position (3 doubles)
+// One thread per (bundle, variant, frame): world position + 1/deltaA (kBndRec doubles)
 MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long t) {
     const int job = find_job(s.bnd_job_start, s.bnd_njobs, t);
     const int b = s.bnd_job_ent[job], v = s.bnd_job_var[job], attr = s.bnd_job_attr[job];
@@ -167,9 +180,10 @@ MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long 
     const AttrView av = make_view(s, x, f, attr, v, s.bnd_ndep[b]);
     const Aff w = world_matrix(s, av, s.bnd_tfm[b]);
     double *dst = s.bnd_tab + s.bnd_off[b];
-    dst[((size_t)v * 3 + 0) * fs + f] = w.m[3];
-    dst[((size_t)v * 3 + 1) * fs + f] = w.m[7];
-    dst[((size_t)v * 3 + 2) * fs + f] = w.m[11];
+    dst[((size_t)v * kBndRec + 0) * fs + f] = w.m[3];
+    dst[((size_t)v * kBndRec + 1) * fs + f] = w.m[7];
+    dst[((size_t)v * kBndRec + 2) * fs + f] = w.m[11];
+    dst[((size_t)v * kBndRec + 3) * fs + f] = variant_inv_delta(s, f, attr, v);
 }
 
 // One thread per (lens, variant, frame): prepared lens record (24 doubles)
@@ -198,14 +212,14 @@ struct ObsCtx {
 MMB_HD void load_cam(const DevScene &s, int c, int v, int f, double *cm /*14*/) {
     const int fs = s.cam_fs[c];
     const int ff = fs == 1 ? 0 : f;
-    const double *src = s.cam_tab + s.cam_off[c] + (size_t)v * 14 * fs + ff;
+    const double *src = s.cam_tab + s.cam_off[c] + (size_t)v * kCamRec * fs + ff;
 #pragma unroll
     for (int j = 0; j < 14; ++j) cm[j] = src[(size_t)j * fs];
 }
 MMB_HD void load_bnd(const DevScene &s, int b, int v, int f, double *bp /*3*/) {
     const int fs = s.bnd_fs[b];
     const int ff = fs == 1 ? 0 : f;
-    const double *src = s.bnd_tab + s.bnd_off[b] + (size_t)v * 3 * fs + ff;
+    const double *src = s.bnd_tab + s.bnd_off[b] + (size_t)v * kBndRec * fs + ff;
     bp[0] = src[0]; bp[1] = src[fs]; bp[2] = src[2 * (size_t)fs];
 }
 MMB_HD void load_lens(const DevScene &s, int l, int v, int f, double *rec /*24*/) {

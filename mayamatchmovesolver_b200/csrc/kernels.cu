@@ -1,5 +1,8 @@
 // CUDA kernels (sm_100a) of the residual / FD-Jacobian path and the handle
 // that owns their HBM buffers.  Per-thread bodies live in eval_bodies.cuh.
+#include <cstdlib>
+#include <cstring>
+
 #include "device_problem.h"
 
 namespace mmb {
@@ -90,6 +93,46 @@ mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist) {
 }
 
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols, double *d_dist_last) {
+    if (p->tiled_ok) {
+        static int variant = -1;
+        if (variant < 0) { const char *e = getenv("MMB_TILE"); variant = e ? atoi(e) : 0; }
+        const int fblocks = (p->hp.F + kTileFrames - 1) / kTileFrames;
+        int m_done = 0;
+        // full tiles of a uniform-layout scene: fast instance
+        if (p->tiled.uniform && !d_cols) {
+#define MMB_FAST(MPC, MINB)                                                                                          \
+    {                                                                                                                \
+        const int tiles = p->hp.M / MPC;                                                                             \
+        if (tiles > 0) {                                                                                             \
+            if (d_dist_last)                                                                                         \
+                k_jacobian_tiled_fast<MPC, MINB, true><<<dim3(fblocks, tiles), kTileFrames, 0, p->stream>>>(         \
+                    p->ds, p->tiled, d_fvec, d_dist, d_jac, d_dist_last);                                            \
+            else                                                                                                     \
+                k_jacobian_tiled_fast<MPC, MINB, false><<<dim3(fblocks, tiles), kTileFrames, 0, p->stream>>>(        \
+                    p->ds, p->tiled, d_fvec, d_dist, d_jac, d_dist_last);                                            \
+            ++p->launches;                                                                                           \
+        }                                                                                                            \
+        m_done = tiles * MPC;                                                                                        \
+    }
+            switch (variant) {
+                case 1: MMB_FAST(1, 6) break;
+                case 2: MMB_FAST(3, 4) break;
+                case 3: MMB_FAST(4, 3) break;
+                case 4: MMB_FAST(4, 4) break;
+                default: MMB_FAST(2, 4) break;
+            }
+#undef MMB_FAST
+        }
+        if (m_done < p->hp.M) {  // tail markers, non-uniform layouts, column-id output
+            constexpr int MPC = 2;
+            const dim3 grid(fblocks, (p->hp.M - m_done + MPC - 1) / MPC);
+            k_jacobian_tiled<MPC, 4><<<grid, kTileFrames, 0, p->stream>>>(p->ds, p->tiled, d_fvec, d_dist, d_jac, d_cols,
+                                                                          d_dist_last, m_done);
+            ++p->launches;
+        }
+        MMB_CUDA_CHECK(cudaGetLastError());
+        return MMB_OK;
+    }
     k_jacobian<<<blocks_for(p->hp.nobs, 256), 256, 0, p->stream>>>(p->ds, d_fvec, d_dist, d_jac, d_cols, d_dist_last);
     ++p->launches;
     MMB_CUDA_CHECK(cudaGetLastError());
@@ -111,6 +154,9 @@ mmb_status ensure_jacobian_buffers(DeviceProblem *p) {
     const size_t k = (size_t)std::max(p->hp.kmax, 1);
     MMB_CUDA_CHECK(p->arena.alloc(&p->d_jac, k * (size_t)p->hp.m));
     MMB_CUDA_CHECK(p->arena.alloc(&p->d_cols, k * (size_t)p->hp.nobs));
+    // the tiled kernel never touches unused columns: they stay 0 / -1
+    MMB_CUDA_CHECK(cudaMemset(p->d_jac, 0, sizeof(double) * k * (size_t)p->hp.m));
+    MMB_CUDA_CHECK(cudaMemset(p->d_cols, 0xff, sizeof(int32_t) * k * (size_t)p->hp.nobs));
     return MMB_OK;
 }
 
@@ -205,6 +251,62 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     UP_I(mkr_k, hp.mkr_k);
     CK(A.alloc(&d.par_delta_a, (size_t)hp.n));
     CK(A.alloc(&d.par_delta_b, (size_t)hp.n));
+    // ---- register-tiled Jacobian fast path (jacobian_tiled.cuh) ---------------
+    {
+        size_t VB = 0;
+        bool bundles_static = true;
+        for (int b = 0; b < hp.B; ++b) {
+            VB = std::max(VB, hp.bnd_deps[b].size());
+            if (hp.bnd_fs[b] != 1) bundles_static = false;
+        }
+        const size_t VC = hp.cam_deps[0].size();
+        bool eligible = hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && hp.C == 1 &&
+                        !hp.cam_mscale_varies[0] && bundles_static && VC <= (size_t)kTileMaxVC &&
+                        VB <= (size_t)kTileMaxVB && hp.kmax <= 127;
+        for (int mk = 0; eligible && mk < hp.M; ++mk)
+            for (int c = 0; c < hp.mkr_k[mk]; ++c) {
+                const PlanEntry &e = hp.plan[(size_t)mk * hp.kmax + c];
+                if ((e.cam_var != 0) == (e.bnd_var != 0) || e.lens_var != 0) eligible = false;
+            }
+        bool ok = eligible && hp.F >= 32;
+        const char *force = getenv("MMB_JACOBIAN_PATH");
+        if (force && !strcmp(force, "generic")) ok = false;
+        if (force && !strcmp(force, "tiled")) ok = eligible;
+        if (ok) {
+            std::vector<int8_t> ccol((size_t)hp.M * std::max<size_t>(VC, 1), -1), bcol((size_t)hp.M * std::max<size_t>(VB, 1), -1);
+            std::vector<int32_t> battr((size_t)hp.M * std::max<size_t>(VB, 1), -1);
+            for (int mk = 0; mk < hp.M; ++mk)
+                for (int c = 0; c < hp.mkr_k[mk]; ++c) {
+                    const PlanEntry &e = hp.plan[(size_t)mk * hp.kmax + c];
+                    if (e.cam_var) ccol[(size_t)mk * VC + (e.cam_var - 1)] = (int8_t)c;
+                    else { bcol[(size_t)mk * VB + (e.bnd_var - 1)] = (int8_t)c; battr[(size_t)mk * VB + (e.bnd_var - 1)] = e.attr; }
+                }
+            TiledPlan &t = p->tiled;
+            t.cam = 0; t.VC = (int)VC; t.VB = (int)VB;
+            t.uniform = 1;
+            for (int mk = 1; mk < hp.M && t.uniform; ++mk) {
+                for (size_t v = 0; v < VC; ++v) if (ccol[(size_t)mk * VC + v] != ccol[v]) t.uniform = 0;
+                for (size_t v = 0; v < VB; ++v) if (bcol[(size_t)mk * VB + v] != bcol[v]) t.uniform = 0;
+            }
+            for (int v = 0; v < kTileMaxVC; ++v) t.cam_col_u[v] = (size_t)v < VC ? ccol[v] : (int8_t)-1;
+            for (int v = 0; v <= kTileMaxVB; ++v) t.bnd_col_u[v] = (size_t)v < VB ? bcol[v] : (int8_t)-1;
+            for (int v = 0; v < kTileMaxVC; ++v) t.cam_coloff_u[v] = (long long)std::max<int>(t.cam_col_u[v], 0) * hp.nobs;
+            for (int v = 0; v <= kTileMaxVB; ++v) t.bnd_coloff_u[v] = (long long)std::max<int>(t.bnd_col_u[v], 0) * hp.nobs;
+            // uniform layout also needs every marker to own all VC / VB columns
+            for (size_t v = 0; v < VC; ++v) if (ccol[v] < 0) t.uniform = 0;
+            for (size_t v = 0; v < VB; ++v) if (bcol[v] < 0) t.uniform = 0;
+            std::vector<int32_t> cattr(hp.cam_deps[0].begin(), hp.cam_deps[0].end());
+            if (cattr.empty()) cattr.push_back(0);
+            int8_t *d8 = nullptr;
+            CK(A.upload(&tmp_i, cattr)); t.cam_dep_attr = tmp_i;
+            CK(A.upload(&d8, ccol)); t.mkr_cam_col = d8;
+            CK(A.upload(&d8, bcol)); t.mkr_bnd_col = d8;
+            CK(A.upload(&tmp_i, battr)); t.mkr_bnd_attr = tmp_i;
+            t.last_attr_cam_var = -1;
+            for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
+            p->tiled_ok = true;
+        }
+    }
     CK(A.alloc(&p->d_x, (size_t)hp.n));
     CK(A.alloc(&p->d_fvec, (size_t)hp.m));
     CK(A.alloc(&p->d_dist, (size_t)hp.nobs));

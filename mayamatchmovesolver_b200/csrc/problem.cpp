@@ -273,9 +273,9 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         }
         job_start.push_back(jobs_total);
     };
-    layout(hp.cam_deps, hp.cam_varies, 14, hp.cam_off, hp.cam_fs, hp.cam_nvar, hp.cam_tab_size,
+    layout(hp.cam_deps, hp.cam_varies, 16, hp.cam_off, hp.cam_fs, hp.cam_nvar, hp.cam_tab_size,
            hp.cam_job_ent, hp.cam_job_var, hp.cam_job_attr, hp.cam_job_start, hp.cam_jobs_total);
-    layout(hp.bnd_deps, hp.bnd_varies, 3, hp.bnd_off, hp.bnd_fs, hp.bnd_nvar, hp.bnd_tab_size,
+    layout(hp.bnd_deps, hp.bnd_varies, 4, hp.bnd_off, hp.bnd_fs, hp.bnd_nvar, hp.bnd_tab_size,
            hp.bnd_job_ent, hp.bnd_job_var, hp.bnd_job_attr, hp.bnd_job_start, hp.bnd_jobs_total);
     layout(hp.lens_deps, hp.lens_varies, 24, hp.lens_off, hp.lens_fs, hp.lens_nvar, hp.lens_tab_size,
            hp.lens_job_ent, hp.lens_job_var, hp.lens_job_attr, hp.lens_job_start, hp.lens_jobs_total);

@@ -113,15 +113,16 @@ class Problem:
         check(self._lib.mmb_eval_jacobian_blocks(self._h, None, None, None, C.byref(k)), "mmb_eval_jacobian_blocks")
         return k.value
 
-    def eval_jacobian_blocks(self, x):
+    def eval_jacobian_blocks(self, x, want_cols=True):
         x = np.ascontiguousarray(x, dtype=np.float64)
         k = self.jacobian_kmax()
         vals = np.zeros((k, self.m))
-        cols = np.zeros((self.nobs, k), np.int32)
+        cols = np.zeros((self.nobs, k), np.int32) if want_cols else None
         kk = C.c_int32()
         check(self._lib.mmb_eval_jacobian_blocks(self._h, x.ctypes.data_as(c_f64p), vals.ctypes.data_as(c_f64p),
-                                                 cols.ctypes.data_as(c_i32p), C.byref(kk)), "mmb_eval_jacobian_blocks")
-        return vals, cols
+                                                 cols.ctypes.data_as(c_i32p) if want_cols else None, C.byref(kk)),
+              "mmb_eval_jacobian_blocks")
+        return (vals, cols) if want_cols else vals
 
     def solve(self):
         r = Result()

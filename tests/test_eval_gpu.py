@@ -25,7 +25,11 @@ CASES = [
 
 @pytest.mark.parametrize("case", CASES)
 @pytest.mark.parametrize("adt", [0, 1])
-def test_residuals_and_jacobian_match_oracle(case, adt):
+@pytest.mark.parametrize("path", ["generic", "tiled"])
+def test_residuals_and_jacobian_match_oracle(case, adt, path, monkeypatch):
+    # both Jacobian kernels: the generic per-observation one and the register-tiled fast
+    # path (which only engages for the shapes it supports; others fall back to generic)
+    monkeypatch.setenv("MMB_JACOBIAN_PATH", path)
     sb, _ = synth.make_scene(**case)
     o = OracleProblem(sb, auto_diff_type=adt)
     with Problem(sb, auto_diff_type=adt) as p:
@@ -50,6 +54,8 @@ def test_residuals_and_jacobian_match_oracle(case, adt):
             assert np.abs(J - Jo).max() <= 1e-9 * np.abs(Jo).max()
             vals, cols = p.eval_jacobian_blocks(xt)
             assert np.array_equal(blocks_to_dense(vals, cols, p.n), J)
+            # values-only call: the kernel instance the LM loop and bench use (no column ids)
+            assert np.array_equal(p.eval_jacobian_blocks(xt, want_cols=False), vals)
 
 
 def test_full_size_properties():
