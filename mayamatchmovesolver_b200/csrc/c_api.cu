@@ -122,8 +122,6 @@ mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec, dou
     DeviceProblem *dp = p->dp;
     mmb_status st;
     if ((st = upload_x(dp, x)) != MMB_OK) return st;
-    if ((st = launch_reset_store(dp)) != MMB_OK) return st;
-    if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
     if ((st = launch_variants(dp, dp->d_x, false)) != MMB_OK) return st;
     if ((st = launch_residuals(dp, dp->d_fvec, dp->d_dist)) != MMB_OK) return st;
     MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
@@ -137,8 +135,6 @@ static mmb_status run_jacobian(DeviceProblem *dp, const double *x, bool want_col
     mmb_status st;
     if ((st = ensure_jacobian_buffers(dp)) != MMB_OK) return st;
     if ((st = upload_x(dp, x)) != MMB_OK) return st;
-    if ((st = launch_reset_store(dp)) != MMB_OK) return st;
-    if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
     if ((st = launch_variants(dp, dp->d_x, true)) != MMB_OK) return st;
     if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, want_cols ? dp->d_cols : nullptr)) != MMB_OK) return st;
     return MMB_OK;
@@ -231,7 +227,6 @@ mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2, double
     for (int r = 0; r < reps; ++r) {
         if (flush) MMB_CUDA_CHECK(cudaMemsetAsync(flush, r & 0xff, flush_n * sizeof(double), dp->stream));
         MMB_CUDA_CHECK(cudaEventRecord(e0, dp->stream));
-        if ((st = launch_set_parameters(dp, dp->d_x)) != MMB_OK) return st;
         if ((st = launch_variants(dp, dp->d_x, true)) != MMB_OK) return st;
         MMB_CUDA_CHECK(cudaEventRecord(ej, dp->stream));
         if ((st = launch_jacobian(dp, dp->d_fvec, dp->d_dist, dp->d_jac, nullptr)) != MMB_OK) return st;

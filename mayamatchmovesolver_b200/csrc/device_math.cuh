@@ -53,6 +53,20 @@ MMB_HD Aff aff_mul(const Aff &a, const Aff &b) {
     return r;
 }
 
+MMB_HD void mul3x3x3(const double *A, const double *B, const double *C, double *R) {
+    double AB[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            AB[i * 3 + j] = A[i * 3 + 0] * B[0 * 3 + j] + A[i * 3 + 1] * B[1 * 3 + j] + A[i * 3 + 2] * B[2 * 3 + j];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            R[i * 3 + j] = AB[i * 3 + 0] * C[0 * 3 + j] + AB[i * 3 + 1] * C[1 * 3 + j] + AB[i * 3 + 2] * C[2 * 3 + j];
+}
+
 // transform.rs:338-453: T * R * S with R from the rotate order table :433-440
 MMB_HD Aff local_matrix(double tx, double ty, double tz, double rx, double ry, double rz,
                         double sx, double sy, double sz, int roo) {
@@ -61,29 +75,18 @@ MMB_HD Aff local_matrix(double tx, double ty, double tz, double rx, double ry, d
     sincos(ry * kDeg2Rad, &sry, &cry);
     sincos(rz * kDeg2Rad, &srz, &crz);
     // 3x3 factors
-    double X[9] = {1, 0, 0, 0, crx, -srx, 0, srx, crx};
-    double Y[9] = {cry, 0, sry, 0, 1, 0, -sry, 0, cry};
-    double Z[9] = {crz, -srz, 0, srz, crz, 0, 0, 0, 1};
-    const double *A, *Bm, *Cm;  // R = A * B * C
-    switch (roo) {
-        case 0: A = Z; Bm = Y; Cm = X; break;  // XYZ
-        case 1: A = X; Bm = Z; Cm = Y; break;  // YZX
-        case 2: A = Y; Bm = X; Cm = Z; break;  // ZXY
-        case 3: A = Y; Bm = Z; Cm = X; break;  // XZY
-        case 4: A = Z; Bm = X; Cm = Y; break;  // YXZ
-        default: A = X; Bm = Y; Cm = Z; break; // ZYX
+    const double X[9] = {1, 0, 0, 0, crx, -srx, 0, srx, crx};
+    const double Y[9] = {cry, 0, sry, 0, 1, 0, -sry, 0, cry};
+    const double Z[9] = {crz, -srz, 0, srz, crz, 0, 0, 0, 1};
+    double R[9];
+    switch (roo) {  // R = A * B * C (transform.rs:433-440)
+        case 0: mul3x3x3(Z, Y, X, R); break;  // XYZ
+        case 1: mul3x3x3(X, Z, Y, R); break;  // YZX
+        case 2: mul3x3x3(Y, X, Z, R); break;  // ZXY
+        case 3: mul3x3x3(Y, Z, X, R); break;  // XZY
+        case 4: mul3x3x3(Z, X, Y, R); break;  // YXZ
+        default: mul3x3x3(X, Y, Z, R); break; // ZYX
     }
-    double AB[9], R[9];
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-            AB[i * 3 + j] = A[i * 3 + 0] * Bm[0 * 3 + j] + A[i * 3 + 1] * Bm[1 * 3 + j] + A[i * 3 + 2] * Bm[2 * 3 + j];
-#pragma unroll
-    for (int i = 0; i < 3; ++i)
-#pragma unroll
-        for (int j = 0; j < 3; ++j)
-            R[i * 3 + j] = AB[i * 3 + 0] * Cm[0 * 3 + j] + AB[i * 3 + 1] * Cm[1 * 3 + j] + AB[i * 3 + 2] * Cm[2 * 3 + j];
     Aff o;
     o.m[0] = R[0] * sx; o.m[1] = R[1] * sy; o.m[2] = R[2] * sz; o.m[3] = tx;
     o.m[4] = R[3] * sx; o.m[5] = R[4] * sy; o.m[6] = R[5] * sz; o.m[7] = ty;

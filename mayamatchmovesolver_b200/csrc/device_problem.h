@@ -84,8 +84,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
 mmb_status ensure_jacobian_buffers(DeviceProblem *p);
 
 // kernel launchers (kernels.cu); all asynchronous on p->stream
-mmb_status launch_reset_store(DeviceProblem *p);                 // attribute store <- pristine
-mmb_status launch_set_parameters(DeviceProblem *p, const double *d_x);
+// d_x == nullptr evaluates the scene at its own attribute values (no parameters applied)
 mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed);
 mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist);
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols,

@@ -29,8 +29,8 @@ struct DevScene {
     double delta;       // SolverOptions.delta
     double image_width;
     // attribute store (AttrDataBlock): live values
-    double *stat;       // [num_static]
-    double *anim;       // [num_anim * F]
+    const double *stat; // [num_static]  read-only: solved values come from x
+    const double *anim; // [num_anim * F]
     // scene
     const int32_t *tfm_parent, *tfm_roo, *tfm_attrs;
     const int32_t *cam_tfm, *cam_attrs, *cam_fit, *cam_rw, *cam_rh, *cam_lens;
@@ -39,7 +39,9 @@ struct DevScene {
     const double *lens_cam;
     // solver attrs / params
     const int32_t *attr_ref, *attr_param_base;
+    const int32_t *stat_attr, *anim_attr;  // attribute-store slot -> solver attr (or -1)
     const uint8_t *attr_anim;
+    const uint8_t *attr_plain;  // unbounded, scale 1, offset 0
     const double *attr_min, *attr_max, *attr_off, *attr_scl;
     const int32_t *par_attr, *par_frame;
     // observations (errorToMarkerList order)
@@ -53,6 +55,7 @@ struct DevScene {
     // variant jobs
     const int32_t *cam_job_ent, *cam_job_var, *cam_job_attr;
     const int64_t *cam_job_start;
+    const int32_t *cam_thread_job, *bnd_thread_job, *lens_thread_job;  // thread -> job
     int cam_njobs; long long cam_jobs_total;
     const int32_t *bnd_job_ent, *bnd_job_var, *bnd_job_attr;
     const int64_t *bnd_job_start;
@@ -67,30 +70,30 @@ struct DevScene {
     double *par_delta_a, *par_delta_b;  // [n]
 };
 
-// ---- setParameters: scatter x into the attribute store --------------------
-// adjust_setParameters.cpp:174-250.  One thread per parameter.
-MMB_HD void set_parameter_thread(const DevScene &s, const double *x, int i) {
-    const int a = s.par_attr[i], f = s.par_frame[i];
-    const double real = bound_int_to_ext(x[i], s.attr_min[a], s.attr_max[a], s.attr_off[a], s.attr_scl[a]);
-    const int32_t ref = s.attr_ref[a];
-    if (ref >= 0) s.stat[ref] = real;
-    else s.anim[(size_t)(-ref - 1) * s.F + f] = real;
-    // FD steps for this x (calculateParameterDelta, adjust_solveFunc.cpp:148)
-    const double da = parameter_delta(x[i], s.delta, 1.0, s.attr_min[a], s.attr_max[a]);
-    s.par_delta_a[i] = da;
-    s.par_delta_b[i] = parameter_delta(x[i], s.delta, -1.0, s.attr_min[a], s.attr_max[a]);
-}
-
-// Attribute read with one overridden ref (the perturbed parameter).
+// ---- attribute values --------------------------------------------------------
+// setParameters (adjust_setParameters.cpp:174-250) never materialises here: a
+// solved attribute is read straight from the parameter vector through
+// parameterBoundFromInternalToExternal, an unsolved one from the (read-only)
+// attribute store.  One attribute may be overridden by x[p] + delta (the
+// perturbed parameter of a Jacobian column).
 struct AttrView {
-    const double *stat, *anim;
-    int F, f;
-    int32_t ovr_ref;
-    double ovr_val;
+    const DevScene *s;
+    const double *x;  // nullptr: the scene's own values (before any setParameters)
+    int f;
+    int ovr_attr;
+    double ovr_delta;
     MMB_HD double get(int32_t ref) const {
-        if (ref == ovr_ref) return ovr_val;
-        if (ref >= 0) return stat[ref];
-        return anim[(size_t)(-ref - 1) * F + f];
+        const int a = x ? (ref >= 0 ? s->stat_attr[ref] : s->anim_attr[-ref - 1]) : -1;
+        if (a < 0) {
+            if (ref >= 0) return s->stat[ref];
+            return s->anim[(size_t)(-ref - 1) * s->F + f];
+        }
+        const int p = s->attr_param_base[a] + (s->attr_anim[a] ? f : 0);
+        double xv = x[p];
+        if (a == ovr_attr) xv += ovr_delta;
+        // no bounds, scale 1, offset 0: (x / 1) - 0 clamped to +-FLT_MAX is x itself
+        if (s->attr_plain[a]) return fmin(fmax(xv, -3.40282346638528859811704183484516925e+38), 3.40282346638528859811704183484516925e+38);
+        return bound_int_to_ext(xv, s->attr_min[a], s->attr_max[a], s->attr_off[a], s->attr_scl[a]);
     }
 };
 
@@ -104,31 +107,30 @@ MMB_HD int find_job(const int64_t *start, int njobs, long long t) {
     return lo;
 }
 
-// The perturbed external value of solver attr `a` at frame f for variant v.
-MMB_HD AttrView make_view(const DevScene &s, const double *x, int f, int attr, int var, int ndep) {
-    AttrView v;
-    v.stat = s.stat; v.anim = s.anim; v.F = s.F; v.f = f;
-    v.ovr_ref = INT32_MIN + 1;  // matches no ref (MMB_ATTR_NONE is INT32_MIN)
-    v.ovr_val = 0.0;
-    if (var > 0) {
-        const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
-        const bool second = var > ndep;  // central: variants ndep+1.. use deltaB
-        const double d = second ? s.par_delta_b[p] : s.par_delta_a[p];
-        v.ovr_ref = s.attr_ref[attr];
-        v.ovr_val = bound_int_to_ext(x[p] + d, s.attr_min[attr], s.attr_max[attr], s.attr_off[attr], s.attr_scl[attr]);
-    }
-    return v;
-}
-
 constexpr int kCamRec = 16;  // doubles per camera variant record
 constexpr int kBndRec = 4;   // doubles per bundle variant record
 
-// 1/deltaA of the parameter a variant perturbs (forward differences), stored
-// next to the variant so the Jacobian kernel needs no per-parameter lookups.
-MMB_HD double variant_inv_delta(const DevScene &s, int f, int attr, int var) {
-    if (var == 0) return 0.0;
-    const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
-    return 1.0 / s.par_delta_a[p];
+// View for variant `var` of an entity with `ndep` dependencies at frame f.
+// calculateParameterDelta (adjust_solveFunc.cpp:148-180) is evaluated here; the
+// steps are also published per parameter for the generic Jacobian kernel.
+MMB_HD AttrView make_view(const DevScene &s, const double *x, int f, int attr, int var, int ndep,
+                          double &inv_delta_a) {
+    AttrView v;
+    v.s = &s; v.x = x; v.f = f;
+    v.ovr_attr = -1;
+    v.ovr_delta = 0.0;
+    inv_delta_a = 0.0;
+    if (var > 0) {
+        const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
+        const double da = parameter_delta(x[p], s.delta, 1.0, s.attr_min[attr], s.attr_max[attr]);
+        const double db = parameter_delta(x[p], s.delta, -1.0, s.attr_min[attr], s.attr_max[attr]);
+        s.par_delta_a[p] = da;  // same value from every entity that depends on p
+        s.par_delta_b[p] = db;
+        inv_delta_a = 1.0 / da;
+        v.ovr_attr = attr;
+        v.ovr_delta = var > ndep ? db : da;  // central: variants ndep+1.. use deltaB
+    }
+    return v;
 }
 
 MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
@@ -151,11 +153,12 @@ MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
 //   [14] 1/deltaA of the perturbed parameter (variants only)
 // table layout: cam_off[c] + ((v*kCamRec + j) * fs + f)
 MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
-    const int job = find_job(s.cam_job_start, s.cam_njobs, t);
+    const int job = s.cam_thread_job[t];
     const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
     const int f = (int)(t - s.cam_job_start[job]);
     const int fs = s.cam_fs[c];
-    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c]);
+    double inv_da;
+    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
     const Aff w = world_matrix(s, av, s.cam_tfm[c]);
     const int32_t *ca = &s.cam_attrs[c * 8];
     const double sw = av.get(ca[0]), sh = av.get(ca[1]);
@@ -168,31 +171,33 @@ MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long 
     double *dst = s.cam_tab + s.cam_off[c];
 #pragma unroll
     for (int j = 0; j < 14; ++j) dst[((size_t)v * kCamRec + j) * fs + f] = out[j];
-    dst[((size_t)v * kCamRec + 14) * fs + f] = variant_inv_delta(s, f, attr, v);
+    dst[((size_t)v * kCamRec + 14) * fs + f] = inv_da;
 }
 
 // One thread per (bundle, variant, frame): world position + 1/deltaA (kBndRec doubles)
 MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long t) {
-    const int job = find_job(s.bnd_job_start, s.bnd_njobs, t);
+    const int job = s.bnd_thread_job[t];
     const int b = s.bnd_job_ent[job], v = s.bnd_job_var[job], attr = s.bnd_job_attr[job];
     const int f = (int)(t - s.bnd_job_start[job]);
     const int fs = s.bnd_fs[b];
-    const AttrView av = make_view(s, x, f, attr, v, s.bnd_ndep[b]);
+    double inv_da;
+    const AttrView av = make_view(s, x, f, attr, v, s.bnd_ndep[b], inv_da);
     const Aff w = world_matrix(s, av, s.bnd_tfm[b]);
     double *dst = s.bnd_tab + s.bnd_off[b];
     dst[((size_t)v * kBndRec + 0) * fs + f] = w.m[3];
     dst[((size_t)v * kBndRec + 1) * fs + f] = w.m[7];
     dst[((size_t)v * kBndRec + 2) * fs + f] = w.m[11];
-    dst[((size_t)v * kBndRec + 3) * fs + f] = variant_inv_delta(s, f, attr, v);
+    dst[((size_t)v * kBndRec + 3) * fs + f] = inv_da;
 }
 
 // One thread per (lens, variant, frame): prepared lens record (24 doubles)
 MMB_HD void lens_variant_thread(const DevScene &s, const double *x, long long t) {
-    const int job = find_job(s.lens_job_start, s.lens_njobs, t);
+    const int job = s.lens_thread_job[t];
     const int l = s.lens_job_ent[job], v = s.lens_job_var[job], attr = s.lens_job_attr[job];
     const int f = (int)(t - s.lens_job_start[job]);
     const int fs = s.lens_fs[l];
-    const AttrView av = make_view(s, x, f, attr, v, s.lens_ndep[l]);
+    double inv_da;
+    const AttrView av = make_view(s, x, f, attr, v, s.lens_ndep[l], inv_da);
     double c[14], rec[kLensRec];
     for (int k = 0; k < 14; ++k) {
         const int32_t r = s.lens_attrs[l * 14 + k];

@@ -12,30 +12,20 @@ void set_last_error(const std::string &msg) { g_last_error = msg; }
 const std::string &get_last_error() { return g_last_error; }
 
 // ---- kernels ---------------------------------------------------------------
-__global__ void k_copy(double *dst, const double *src, size_t n) {
-    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = src[i];
-}
-
-__global__ void k_set_parameters(DevScene s, const double *x) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < s.n) set_parameter_thread(s, x, i);
-}
-
 // kind 0 camera, 1 bundle, 2 lens; base_only skips perturbed variants
 __global__ void k_variants(DevScene s, const double *x, int base_only) {
     const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long nc = s.cam_jobs_total, nb = s.bnd_jobs_total, nl = s.lens_jobs_total;
     if (t < nc) {
-        if (base_only && s.cam_job_var[find_job(s.cam_job_start, s.cam_njobs, t)] != 0) return;
+        if (base_only && s.cam_job_var[s.cam_thread_job[t]] != 0) return;
         camera_variant_thread(s, x, t);
     } else if (t < nc + nb) {
         const long long u = t - nc;
-        if (base_only && s.bnd_job_var[find_job(s.bnd_job_start, s.bnd_njobs, u)] != 0) return;
+        if (base_only && s.bnd_job_var[s.bnd_thread_job[u]] != 0) return;
         bundle_variant_thread(s, x, u);
     } else if (t < nc + nb + nl) {
         const long long u = t - nc - nb;
-        if (base_only && s.lens_job_var[find_job(s.lens_job_start, s.lens_njobs, u)] != 0) return;
+        if (base_only && s.lens_job_var[s.lens_thread_job[u]] != 0) return;
         lens_variant_thread(s, x, u);
     }
 }
@@ -53,29 +43,6 @@ __global__ void __launch_bounds__(256) k_jacobian(DevScene s, double *fvec, doub
 
 // ---- launchers -------------------------------------------------------------
 static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
-
-mmb_status launch_reset_store(DeviceProblem *p) {
-    const HostProblem &hp = p->hp;
-    if (hp.num_static) {
-        k_copy<<<blocks_for(hp.num_static, 256), 256, 0, p->stream>>>(p->ds.stat, p->d_stat0, hp.num_static);
-        ++p->launches;
-    }
-    if (hp.num_anim) {
-        const size_t n = (size_t)hp.num_anim * hp.F;
-        k_copy<<<blocks_for(n, 256), 256, 0, p->stream>>>(p->ds.anim, p->d_anim0, n);
-        ++p->launches;
-    }
-    MMB_CUDA_CHECK(cudaGetLastError());
-    return MMB_OK;
-}
-
-mmb_status launch_set_parameters(DeviceProblem *p, const double *d_x) {
-    if (p->hp.n == 0) return MMB_OK;
-    k_set_parameters<<<blocks_for(p->hp.n, 128), 128, 0, p->stream>>>(p->ds, d_x);
-    ++p->launches;
-    MMB_CUDA_CHECK(cudaGetLastError());
-    return MMB_OK;
-}
 
 mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed) {
     const long long total = p->ds.cam_jobs_total + p->ds.bnd_jobs_total + p->ds.lens_jobs_total;
@@ -202,8 +169,8 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     d.image_width = opt->image_width;
     CK(A.upload(&p->d_stat0, hp.stat0));
     CK(A.upload(&p->d_anim0, hp.anim0));
-    CK(A.upload(&d.stat, hp.stat0));
-    CK(A.upload(&d.anim, hp.anim0));
+    d.stat = p->d_stat0;  // the attribute store is read-only: solved values come from x
+    d.anim = p->d_anim0;
     int32_t *tmp_i = nullptr; double *tmp_d = nullptr; uint8_t *tmp_b = nullptr; int64_t *tmp_l = nullptr;
 #define UP_I(field, vec) CK(A.upload(&tmp_i, vec)); d.field = tmp_i
 #define UP_D(field, vec) CK(A.upload(&tmp_d, vec)); d.field = tmp_d
@@ -214,7 +181,15 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     UP_I(bnd_tfm, hp.bnd_tfm); UP_I(mkr_cam, hp.mkr_cam); UP_I(mkr_bnd, hp.mkr_bnd);
     UP_I(lens_model, hp.lens_model); UP_I(lens_attrs, hp.lens_attrs); UP_D(lens_cam, hp.lens_cam);
     UP_I(attr_ref, hp.attr_ref); UP_I(attr_param_base, hp.attr_param_base);
+    UP_I(stat_attr, hp.stat_attr); UP_I(anim_attr, hp.anim_attr);
     CK(A.upload(&tmp_b, hp.attr_anim)); d.attr_anim = tmp_b;
+    {
+        std::vector<uint8_t> plain(std::max(hp.A, 1), 0);
+        const double fm = 3.40282346638528859811704183484516925e+38;
+        for (int a = 0; a < hp.A; ++a)
+            plain[a] = hp.attr_min[a] <= -fm && hp.attr_max[a] >= fm && hp.attr_scl[a] == 1.0 && hp.attr_off[a] == 0.0;
+        CK(A.upload(&tmp_b, plain)); d.attr_plain = tmp_b;
+    }
     UP_D(attr_min, hp.attr_min); UP_D(attr_max, hp.attr_max);
     UP_D(attr_off, hp.attr_off); UP_D(attr_scl, hp.attr_scl);
     UP_I(par_attr, hp.par_attr); UP_I(par_frame, hp.par_frame);
@@ -233,6 +208,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     UP_I(cam_ndep, cnd); UP_I(bnd_ndep, bnd); UP_I(lens_ndep, lnd);
     UP_I(cam_job_ent, hp.cam_job_ent); UP_I(cam_job_var, hp.cam_job_var); UP_I(cam_job_attr, hp.cam_job_attr);
     UP_L(cam_job_start, hp.cam_job_start);
+    UP_I(cam_thread_job, hp.cam_thread_job); UP_I(bnd_thread_job, hp.bnd_thread_job); UP_I(lens_thread_job, hp.lens_thread_job);
     d.cam_njobs = (int)hp.cam_job_ent.size(); d.cam_jobs_total = hp.cam_jobs_total;
     UP_I(bnd_job_ent, hp.bnd_job_ent); UP_I(bnd_job_var, hp.bnd_job_var); UP_I(bnd_job_attr, hp.bnd_job_attr);
     UP_L(bnd_job_start, hp.bnd_job_start);

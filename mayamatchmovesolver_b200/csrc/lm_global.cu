@@ -9,6 +9,8 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "lm.h"
@@ -34,6 +36,11 @@ struct LmWorkspace {
     double *part_gemv = nullptr;                      // [chunks * NSP]
     int gemv_chunks = 1;
     double init_avg = 0, init_min = 0, init_max = 0;
+    // optional phase timing (MMB_LM_PROFILE=1): schur, cholesky, back-substitution, q-solve
+    bool profile = false;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    double phase_ms[4] = {0, 0, 0, 0};
+    int phase_n = 0;
     ~LmWorkspace() {
         if (h_st) cudaFreeHost(h_st);
     }
@@ -369,8 +376,11 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.alloc(&w->part_jp, (size_t)kRedBlocks));
     w->gemv_chunks = std::max(1, std::min(64, d.KE / 256));
     CKW(A.alloc(&w->part_gemv, (size_t)w->gemv_chunks * d.NSP));
+    CKW(cudaFuncSetAttribute(k_backward_s, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * (64 * kDS + 64 + 32 * 64)));
     CKW(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 64 * kCS * (int)sizeof(double)));
 #undef CKW
+    w->profile = getenv("MMB_LM_PROFILE") != nullptr;
+    if (w->profile) for (auto &e : w->ev) cudaEventCreate(&e);
     p->lm = w;
     return MMB_OK;
 }
@@ -392,7 +402,6 @@ static mmb_status read_state(DeviceProblem *p) {
 static mmb_status enqueue_residual_eval(DeviceProblem *p, const double *d_x, double *d_f, double *d_dist) {
     LmWorkspace *w = p->lm;
     mmb_status st;
-    if ((st = launch_set_parameters(p, d_x)) != MMB_OK) return st;
     if ((st = launch_variants(p, d_x, false)) != MMB_OK) return st;
     if ((st = launch_residuals(p, d_f, d_dist)) != MMB_OK) return st;
     k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(d_f, (size_t)p->hp.m, w->part_f);
@@ -404,7 +413,6 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     const LmDims &d = w->d;
     mmb_status st;
-    if ((st = launch_set_parameters(p, p->d_x)) != MMB_OK) return st;
     if ((st = launch_variants(p, p->d_x, true)) != MMB_OK) return st;
     if ((st = launch_jacobian(p, nullptr, nullptr, p->d_jac, nullptr, w->dist2)) != MMB_OK) return st;
     if (d.KE) {
@@ -425,6 +433,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     const LmDims &d = w->d;
     cudaStream_t s = p->stream;
+    if (w->profile) cudaEventRecord(w->ev[0], s);
     if (d.KE) {
         const size_t sm = sizeof(double) * ((size_t)d.na * d.na + d.na);
         k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
@@ -443,6 +452,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_schur_syrk<<<dim3(tiles, ksplit), 128, 0, s>>>(d, w->Y, w->S);
         LAUNCH_CHECK();
     }
+    if (w->profile) cudaEventRecord(w->ev[1], s);
     for (int kb = 0; kb < nb; ++kb) {
         k_chol_panel<<<nb - kb, 256, 2 * 64 * kCS * sizeof(double), s>>>(d, kb, w->st, w->S, w->Ld);
         LAUNCH_CHECK();
@@ -450,7 +460,8 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
         LAUNCH_CHECK();
     }
-    k_backward_s<<<1, 1024, 0, s>>>(d, w->S, w->p_int + d.KE);
+    if (w->profile) cudaEventRecord(w->ev[2], s);
+    k_backward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64 + 32 * 64), s>>>(d, w->S, w->p_int + d.KE);
     LAUNCH_CHECK();
     if (d.KE) {
         k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
@@ -458,6 +469,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     k_dxnorm<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->diag, w->i2p);
     LAUNCH_CHECK();
+    if (w->profile) cudaEventRecord(w->ev[3], s);
     // Newton correction: w = L^-1 (D^2 p / dxnorm)
     if (d.KE) {
         k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->st, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
@@ -468,11 +480,17 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     if (d.ns) {
         k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->st, d.KE ? w->gemv_chunks : 0, w->part_gemv, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
         LAUNCH_CHECK();
-        k_forward_s<<<1, 1024, 0, s>>>(d, w->S, w->w_int + d.KE, w->w_int + d.KE);
+        k_forward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64), s>>>(d, w->S, w->w_int + d.KE, w->w_int + d.KE);
         LAUNCH_CHECK();
     }
     k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int);
     LAUNCH_CHECK();
+    if (w->profile) {
+        cudaEventRecord(w->ev[4], s);
+        cudaEventSynchronize(w->ev[4]);
+        for (int i = 0; i < 4; ++i) { float ms = 0; cudaEventElapsedTime(&ms, w->ev[i], w->ev[i + 1]); w->phase_ms[i] += ms; }
+        ++w->phase_n;
+    }
     return MMB_OK;
 }
 
@@ -520,7 +538,6 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
         x0[i] = bound_external_to_internal(v, hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
     }
     MMB_CUDA_CHECK(cudaMemcpyAsync(p->d_x, x0.data(), sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
-    if ((st = launch_reset_store(p)) != MMB_OK) return st;
 
     LmState h{};
     h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
@@ -540,7 +557,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     // scene's own values, before any parameter is set.
     double init_avg = 0.0;
     if (hp.opt.accept_only_better) {
-        if ((st = launch_variants(p, p->d_x, false)) != MMB_OK) return st;
+        if ((st = launch_variants(p, nullptr, false)) != MMB_OK) return st;
         if ((st = launch_residuals(p, p->d_fvec, p->d_dist)) != MMB_OK) return st;
         k_error_stats<<<1, 1024, 0, p->stream>>>(w->st, p->d_dist, hp.nobs);
         LAUNCH_CHECK();
@@ -618,6 +635,11 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     res->timer_jacobian_s = t_jac;
     res->timer_function_s = t_func;
     res->timer_linear_s = t_lin;
+    if (w->profile && w->phase_n) {
+        fprintf(stderr, "[mmb lm profile] %d lmpar steps: schur %.3f ms, cholesky %.3f ms, backsolve %.3f ms, qsolve %.3f ms (per step)\n",
+                w->phase_n, w->phase_ms[0] / w->phase_n, w->phase_ms[1] / w->phase_n, w->phase_ms[2] / w->phase_n, w->phase_ms[3] / w->phase_n);
+        w->phase_n = 0; for (double &v : w->phase_ms) v = 0;
+    }
     (void)d;
     return MMB_OK;
 }

@@ -471,32 +471,44 @@ __global__ void __launch_bounds__(128) k_chol_trailing(LmDims d, int kb, double 
 }
 
 // ---- triangular solves with L_S (single CTA, 1024 threads) ---------------------------
-// forward: solve L w = b for rows [0, ns); left-looking, warp per row.
-// b and w may alias.  Used for the Newton correction of lmpar.
+// Both sweeps stage the 64x64 diagonal block in shared memory (the dependent
+// substitution then never waits on global memory) and read the off-diagonal
+// panel with fully coalesced warp-per-row accesses.
+constexpr int kDS = 65;  // shared stride of the staged diagonal block
+
+// forward: solve L w = b for rows [0, ns).  b and w may alias.
 __global__ void __launch_bounds__(1024) k_forward_s(LmDims d, const double *__restrict__ S, const double *b, double *w) {
-    __shared__ double xs[kNB];
-    __shared__ double acc[kNB];
+    extern __shared__ double sm[];
+    double *D = sm;               // 64 x kDS
+    double *xs = sm + 64 * kDS;   // 64: rhs then solution of the block
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ns = d.ns;
     for (int c0 = 0; c0 < ns; c0 += kNB) {
-        // rows c0 .. c0+63: subtract L[row, 0:c0] w[0:c0]
+        for (int t = threadIdx.x; t < 64 * 64; t += blockDim.x) {
+            const int r = t >> 6, c = t & 63;
+            const bool in = (c <= r) && (c0 + r < ns);  // rows >= ns (rhs row, padding): identity
+            D[r * kDS + c] = in ? S[(size_t)(c0 + r) * d.NSP + c0 + c] : (r == c ? 1.0 : 0.0);
+        }
+        // rows c0 .. c0+63: rhs = b[row] - L[row, 0:c0] . w[0:c0]   (two rows per warp)
         for (int rr = warp; rr < kNB; rr += 32) {
             const int row = c0 + rr;
             double a = 0.0;
-            if (row < ns)
-                for (int c = lane; c < c0; c += 32) a += S[(size_t)row * d.NSP + c] * w[c];
+            if (row < ns) {
+                const double *Lr = S + (size_t)row * d.NSP;
+                for (int c = lane; c < c0; c += 32) a += Lr[c] * w[c];
+            }
             a = warp_sum(a);
-            if (lane == 0) acc[rr] = (row < ns) ? b[row] - a : 0.0;
+            if (lane == 0) xs[rr] = (row < ns) ? b[row] - a : 0.0;
         }
         __syncthreads();
-        // diagonal 64x64 solve by warp 0 (sequential over rows, lanes over cols)
         if (warp == 0) {
-            for (int r = 0; r < kNB && c0 + r < ns; ++r) {
-                const int row = c0 + r;
-                double a = 0.0;
-                for (int c = lane; c < r; c += 32) a += S[(size_t)row * d.NSP + c0 + c] * xs[c];
-                a = warp_sum(a);
-                if (lane == 0) xs[r] = (acc[r] - a) / S[(size_t)row * d.NSP + row];
+            // 64x64 lower-triangular solve out of shared memory; lanes own rows lane, lane+32
+            for (int j = 0; j < kNB; ++j) {
+                const double xj = xs[j] / D[j * kDS + j];
+                __syncwarp();
+                if (lane == 0) xs[j] = xj;
+                for (int r = lane; r < kNB; r += 32)
+                    if (r > j) xs[r] -= D[r * kDS + j] * xj;
                 __syncwarp();
             }
         }
@@ -509,38 +521,45 @@ __global__ void __launch_bounds__(1024) k_forward_s(LmDims d, const double *__re
 
 // backward: solve L^T p = y where y is the augmented row ns of S.
 __global__ void __launch_bounds__(1024) k_backward_s(LmDims d, const double *__restrict__ S, double *__restrict__ p) {
-    __shared__ double part[32][kNB + 1];
-    __shared__ double xs[kNB];
+    extern __shared__ double sm[];
+    double *D = sm;                     // 64 x kDS
+    double *xs = sm + 64 * kDS;         // 64
+    double *part = xs + 64;             // 32 x 64 per-warp partial column sums
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ns = d.ns;
     const int nblk = (ns + kNB - 1) / kNB;
-    for (int b = nblk - 1; b >= 0; --b) {
-        const int c0 = b * kNB;
-        // sum over rows c >= c0+64 of L[c][c0 + j] p[c], j = 0..63 (two halves per lane)
+    for (int bb = nblk - 1; bb >= 0; --bb) {
+        const int c0 = bb * kNB;
+        for (int t = threadIdx.x; t < 64 * 64; t += blockDim.x) {
+            const int r = t >> 6, c = t & 63;
+            const bool in = (c <= r) && (c0 + r < ns);
+            D[r * kDS + c] = in ? S[(size_t)(c0 + r) * d.NSP + c0 + c] : (r == c ? 1.0 : 0.0);
+        }
+        // sum over rows c >= c0+64 of L[c][c0 + j] p[c], j = lane, lane+32
         double a0 = 0.0, a1 = 0.0;
         for (int c = c0 + kNB + warp; c < ns; c += 32) {
             const double pc = p[c];
             a0 += S[(size_t)c * d.NSP + c0 + lane] * pc;
             a1 += S[(size_t)c * d.NSP + c0 + 32 + lane] * pc;
         }
-        part[warp][lane] = a0;
-        part[warp][lane + 32] = a1;
+        part[warp * 64 + lane] = a0;
+        part[warp * 64 + lane + 32] = a1;
         __syncthreads();
         if (threadIdx.x < kNB) {
             double t = 0.0;
-            for (int w2 = 0; w2 < 32; ++w2) t += part[w2][threadIdx.x];
+            for (int w2 = 0; w2 < 32; ++w2) t += part[w2 * 64 + threadIdx.x];
             const int col = c0 + threadIdx.x;
             xs[threadIdx.x] = (col < ns) ? S[(size_t)ns * d.NSP + col] - t : 0.0;
         }
         __syncthreads();
         if (warp == 0) {
-            const int hi = min(kNB, ns - c0);
-            for (int r = hi - 1; r >= 0; --r) {
-                // p[c0+r] = (xs[r] - sum_{c>r in block} L[c0+c][c0+r] p[c0+c]) / L[r][r]
-                double a = 0.0;
-                for (int c = r + 1 + lane; c < hi; c += 32) a += S[(size_t)(c0 + c) * d.NSP + c0 + r] * xs[c];
-                a = warp_sum(a);
-                if (lane == 0) xs[r] = (xs[r] - a) / S[(size_t)(c0 + r) * d.NSP + c0 + r];
+            // solve L_kk^T x = xs: column sweep from the bottom; lanes own rows lane, lane+32
+            for (int j = kNB - 1; j >= 0; --j) {
+                const double xj = xs[j] / D[j * kDS + j];
+                __syncwarp();
+                if (lane == 0) xs[j] = xj;
+                for (int r = lane; r < kNB; r += 32)
+                    if (r < j) xs[r] -= D[j * kDS + r] * xj;
                 __syncwarp();
             }
         }

@@ -210,6 +210,13 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         }
     }
     hp.n = (int)hp.par_attr.size();
+    // later duplicates of an attribute win, as the last setParameters write would
+    hp.stat_attr.assign(std::max(hp.num_static, 1), -1);
+    hp.anim_attr.assign(std::max(hp.num_anim, 1), -1);
+    for (int a = 0; a < hp.A; ++a) {
+        if (hp.attr_ref[a] >= 0) hp.stat_attr[hp.attr_ref[a]] = a;
+        else hp.anim_attr[-hp.attr_ref[a] - 1] = a;
+    }
     hp.par_to_int.assign(hp.n, 0); hp.int_to_par.assign(hp.n, 0);
     for (int p = 0; p < hp.n; ++p) {
         const int a = hp.par_attr[p];
@@ -279,6 +286,15 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
            hp.bnd_job_ent, hp.bnd_job_var, hp.bnd_job_attr, hp.bnd_job_start, hp.bnd_jobs_total);
     layout(hp.lens_deps, hp.lens_varies, 24, hp.lens_off, hp.lens_fs, hp.lens_nvar, hp.lens_tab_size,
            hp.lens_job_ent, hp.lens_job_var, hp.lens_job_attr, hp.lens_job_start, hp.lens_jobs_total);
+
+    auto expand = [](const std::vector<int64_t> &start, std::vector<int32_t> &out) {
+        out.assign((size_t)start.back(), 0);
+        for (size_t j = 0; j + 1 < start.size(); ++j)
+            for (int64_t t = start[j]; t < start[j + 1]; ++t) out[(size_t)t] = (int32_t)j;
+    };
+    expand(hp.cam_job_start, hp.cam_thread_job);
+    expand(hp.bnd_job_start, hp.bnd_thread_job);
+    expand(hp.lens_job_start, hp.lens_thread_job);
 
     // ---- per-marker column plan -------------------------------------------
     hp.mkr_k.assign(hp.M, 0);

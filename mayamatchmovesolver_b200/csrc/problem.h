@@ -52,6 +52,7 @@ struct HostProblem {
     std::vector<int32_t> par_attr, par_frame;     // paramToAttrList
     std::vector<int32_t> attr_param_base;         // first param of attr a
     std::vector<uint8_t> attr_anim;               // attr expands per frame
+    std::vector<int32_t> stat_attr, anim_attr;    // attribute-store slot -> solver attr or -1
     bool dense_grid = false;                      // nobs == M*F, i = m*F+f
 
     // ---- entity dependency lists ---------------------------------------
@@ -71,6 +72,7 @@ struct HostProblem {
     std::vector<int32_t> lens_job_ent, lens_job_var, lens_job_attr;
     int64_t cam_jobs_total = 0, bnd_jobs_total = 0, lens_jobs_total = 0;
     std::vector<int64_t> cam_job_start, bnd_job_start, lens_job_start;  // prefix (threads)
+    std::vector<int32_t> cam_thread_job, bnd_thread_job, lens_thread_job;  // thread -> job
 
     // ---- per-marker column plan ---------------------------------------
     int kmax = 0;

@@ -10,6 +10,7 @@ using namespace mmb;
 
 struct Emu {
     HostProblem hp;
+    std::vector<uint8_t> plain;
     DevScene ds;
     std::vector<double> stat, anim, cam_tab, bnd_tab, lens_tab, da, db;
     std::vector<int32_t> cnd, bnd, lnd;
@@ -27,6 +28,9 @@ int emu_create(const mmb_scene_desc *s, const mmb_options *o, Emu **out) {
     d.central = o->auto_diff_type == 1; d.dense_grid = hp.dense_grid; d.any_lens = hp.any_lens;
     d.lens_literal = o->lens_index_literal; d.delta = o->delta; d.image_width = o->image_width;
     e->stat = hp.stat0; e->anim = hp.anim0; e->stat.resize(e->stat.size() + 1); e->anim.resize(e->anim.size() + 1);
+    d.cam_thread_job = hp.cam_thread_job.data(); d.bnd_thread_job = hp.bnd_thread_job.data(); d.lens_thread_job = hp.lens_thread_job.data();
+    e->plain.assign(std::max(hp.A, 1), 0); d.attr_plain = e->plain.data();  // emu: always the general transform
+    d.stat_attr = hp.stat_attr.data(); d.anim_attr = hp.anim_attr.data();
     d.stat = e->stat.data(); d.anim = e->anim.data();
     d.tfm_parent = hp.tfm_parent.data(); d.tfm_roo = hp.tfm_roo.data(); d.tfm_attrs = hp.tfm_attrs.data();
     d.cam_tfm = hp.cam_tfm.data(); d.cam_attrs = hp.cam_attrs.data(); d.cam_fit = hp.cam_fit.data();
@@ -62,9 +66,6 @@ int emu_create(const mmb_scene_desc *s, const mmb_options *o, Emu **out) {
 void emu_destroy(Emu *e) { delete e; }
 void emu_sizes(Emu *e, int *n, int *nobs, int *kmax) { *n = e->hp.n; *nobs = e->hp.nobs; *kmax = e->ds.kmax; }
 static void prep(Emu *e, const double *x) {
-    std::copy(e->hp.stat0.begin(), e->hp.stat0.end(), e->stat.begin());
-    std::copy(e->hp.anim0.begin(), e->hp.anim0.end(), e->anim.begin());
-    for (int i = 0; i < e->hp.n; ++i) set_parameter_thread(e->ds, x, i);
     for (long long t = 0; t < e->ds.cam_jobs_total; ++t) camera_variant_thread(e->ds, x, t);
     for (long long t = 0; t < e->ds.bnd_jobs_total; ++t) bundle_variant_thread(e->ds, x, t);
     for (long long t = 0; t < e->ds.lens_jobs_total; ++t) lens_variant_thread(e->ds, x, t);
