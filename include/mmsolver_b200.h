@@ -230,6 +230,18 @@ mmb_status mmb_eval_jacobian_blocks(mmb_problem *p, const double *x,
 mmb_status mmb_solve(mmb_problem *p, mmb_result *result, double *x_out,
                      double *attr_values_out, double *error_dist_out);
 
+/* frameSolveMode = 1 (solve_v1's per-frame loop, adjust_base.cpp:1430-1484):
+ * every frame is its own LM problem; the aggregate follows
+ * CommandResult::add / divide (adjust_results.h:89-117).  All frames run in ONE
+ * launch (one CTA per frame) when every solver attribute is animated; a scene
+ * with static solver attributes returns MMB_ERR_UNSUPPORTED (the reference
+ * carries their values from one frame's solve into the next).
+ * per_frame_results: [F] or NULL.  mmb_solve() routes here when
+ * options.frame_solve_mode == 1. */
+mmb_status mmb_solve_per_frame(mmb_problem *p, mmb_result *result,
+                               mmb_result *per_frame_results, double *x_out,
+                               double *attr_values_out, double *error_dist_out);
+
 /* MComputation::isInterruptRequested analogue; callable from another thread */
 void mmb_request_cancel(mmb_problem *p);
 

@@ -81,6 +81,7 @@ SYMBOLS = [
     ("mmb_eval_jacobian_dense", C.c_int32, [C.c_void_p, c_f64p, c_f64p, C.c_int32]),
     ("mmb_eval_jacobian_blocks", C.c_int32, [C.c_void_p, c_f64p, c_f64p, c_i32p, c_i32p]),
     ("mmb_solve", C.c_int32, [C.c_void_p, C.POINTER(Result), c_f64p, c_f64p, c_f64p]),
+    ("mmb_solve_per_frame", C.c_int32, [C.c_void_p, C.POINTER(Result), C.POINTER(Result), c_f64p, c_f64p, c_f64p]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),

@@ -185,11 +185,29 @@ mmb_status mmb_solve(mmb_problem *p, mmb_result *result, double *x_out, double *
                      double *error_dist_out) {
     if (!p || !result) return MMB_ERR_INVALID_ARGUMENT;
     try {
+        if (p->dp->hp.opt.frame_solve_mode == 1)
+            return mmb_solve_per_frame(p, result, nullptr, x_out, attr_values_out, error_dist_out);
         mmb_status st = lm_solve(p->dp, result, x_out, attr_values_out, error_dist_out);
         result->reason_str = mmb_reason_string(result->reason_num);
         return st;
     } catch (...) {
         set_last_error("unexpected exception in mmb_solve");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+mmb_status mmb_solve_per_frame(mmb_problem *p, mmb_result *result, mmb_result *per_frame_results, double *x_out,
+                               double *attr_values_out, double *error_dist_out) {
+    if (!p || !result) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        mmb_status st = lm_solve_per_frame(p->dp, result, x_out, attr_values_out, error_dist_out, per_frame_results);
+        result->reason_str = mmb_reason_string(result->reason_num);
+        if (per_frame_results && st == MMB_OK)
+            for (int f = 0; f < p->dp->hp.F; ++f)
+                per_frame_results[f].reason_str = mmb_reason_string(per_frame_results[f].reason_num);
+        return st;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_solve_per_frame");
         return MMB_ERR_INTERNAL;
     }
 }

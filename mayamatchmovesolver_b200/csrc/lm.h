@@ -4,5 +4,7 @@
 
 namespace mmb {
 mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out);
+mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out,
+                              mmb_result *per_frame_out);
 void lm_workspace_destroy(LmWorkspace *w);
 }  // namespace mmb

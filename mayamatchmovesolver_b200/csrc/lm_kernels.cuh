@@ -18,38 +18,15 @@
 
 #include "eval_bodies.cuh"
 #include "lm_state.h"
+#include "reduce.cuh"
 
 namespace mmb {
 
 constexpr int kNB = 64;        // Cholesky block
-constexpr int kMaxNA = 64;     // largest per-frame eliminated block
 
 struct LmDims {
     int F, na, ns, NS1, NSP, KE, KEP, n, nobs, m, kmax;
 };
-
-// ---- reductions --------------------------------------------------------------
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
-
-// deterministic block reduction (blockDim multiple of 32, <= 1024)
-__device__ __forceinline__ double block_sum(double v, double *sh /*32*/) {
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    v = warp_sum(v);
-    __syncthreads();
-    if (lane == 0) sh[w] = v;
-    __syncthreads();
-    const int nw = (blockDim.x + 31) >> 5;
-    double r = (threadIdx.x < nw) ? sh[threadIdx.x] : 0.0;
-    if (w == 0) r = warp_sum(r);
-    if (threadIdx.x == 0) sh[0] = r;
-    __syncthreads();
-    r = sh[0];
-    return r;
-}
 
 // partial[blockIdx] = sum of squares of v[0..n) (grid-stride); stage 2 sums
 // the partials in a control kernel -> deterministic.

@@ -54,6 +54,7 @@ class Problem:
         self._lib = _capi.load()
         self.options = options if options is not None else default_options(**opt_overrides)
         desc, keep = scene.desc()
+        self.num_frames = int(desc.num_frames)
         self._h = C.c_void_p()
         check(self._lib.mmb_problem_create(C.byref(desc), C.byref(self.options), C.byref(self._h)),
               "mmb_problem_create")
@@ -132,6 +133,19 @@ class Problem:
         check(self._lib.mmb_solve(self._h, C.byref(r), x.ctypes.data_as(c_f64p), av.ctypes.data_as(c_f64p),
                                   dist.ctypes.data_as(c_f64p)), "mmb_solve")
         return SolveResult(r, x, av, dist)
+
+    def solve_per_frame(self):
+        """frameSolveMode=1: -> (aggregate SolveResult, [per-frame SolveResult])"""
+        r = Result()
+        F = self.num_frames
+        per = (Result * F)()
+        x = np.zeros(self.n)
+        av = np.zeros(self.n)
+        dist = np.zeros(self.nobs)
+        check(self._lib.mmb_solve_per_frame(self._h, C.byref(r), per, x.ctypes.data_as(c_f64p),
+                                            av.ctypes.data_as(c_f64p), dist.ctypes.data_as(c_f64p)),
+              "mmb_solve_per_frame")
+        return SolveResult(r, x, av, dist), [SolveResult(per[f], None, None, None) for f in range(F)]
 
     def request_cancel(self):
         self._lib.mmb_request_cancel(self._h)

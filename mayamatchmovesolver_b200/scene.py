@@ -146,6 +146,19 @@ class SceneBuilder:
         self.attr_scl.append(1.0 if scale is None else float(scale))
         return len(self.attr_ref) - 1
 
+    def slice_frames(self, frame_indices):
+        """A copy of the scene restricted to some frames (what solve_v1 hands to
+        solveFrames for one entry of its per-frame loop, adjust_base.cpp:1447)."""
+        import copy
+        idx = np.asarray(frame_indices, dtype=np.int64)
+        o = copy.deepcopy(self)
+        o.frames = self.frames[idx].copy()
+        o.F = len(idx)
+        o._anim = [a[idx].copy() for a in self._anim]
+        for name in ("mkr_x", "mkr_y", "mkr_w", "mkr_en"):
+            setattr(o, name, [a[idx].copy() for a in getattr(self, name)])
+        return o
+
     # ---- flatten -------------------------------------------------------
     def arrays(self):
         F = self.F
