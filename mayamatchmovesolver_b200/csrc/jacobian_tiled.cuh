@@ -35,6 +35,8 @@ struct TiledPlan {
     const int8_t *mkr_cam_col;   // [M*VC] Jacobian column of camera dep v for marker m (-1: none)
     const int8_t *mkr_bnd_col;   // [M*VB] Jacobian column of bundle dep v
     const int32_t *mkr_bnd_attr; // [M*VB] solver attr of bundle dep v (-1: none)
+    int bnd_contig;              // bundle records of markers 0..M-1 are consecutive in bnd_tab
+    long long bnd_rec0;          // ... starting at this offset (doubles)
     int last_attr_cam_var;       // 0-based camera dep index of attr A-1 (the variant the
                                  // reference's errorDistanceList ends on), or -1
 };
@@ -264,6 +266,179 @@ __global__ void __launch_bounds__(kTileFrames, MINB) k_jacobian_tiled_fast(DevSc
             if (DIST_LAST) {
                 if (tp.mkr_bnd_attr[(size_t)(m0 + j) * tp.VB + v] == s.A - 1)
                     dist_last[i0 + (size_t)j * F] = sqrt((dx * dx) + (dy * dy)) * imw;
+            }
+        }
+    }
+}
+
+// ---- shared-memory camera rows: the one-wave instance -----------------------------------
+// A CTA owns 32 consecutive frames and `mt` consecutive markers.  The camera rows of
+// its frames (base + every perturbed variant, (VC+1) x 14 rows x 32 frames) are brought
+// into shared memory once with 1-D TMA bulk copies (cp.async.bulk, one mbarrier per
+// variant, so the first evaluations start while later variants are still in flight)
+// and are then shared by the CTA's W warps, each of which walks its own marker pairs.
+// A thread keeps only the base rows and two markers in registers; the grid is sized by
+// the host to exactly one resident wave (kernels.cu).
+constexpr int kRowFrames = 32;
+constexpr int kRowSlots = 14;  // rows 0..11, then base: film-fit scale x,y / variant: 1/delta
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "MMB_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra MMB_DONE_%=;\n"
+        "bra MMB_WAIT_%=;\n"
+        "MMB_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// same as eval_pair with the three dot products as nested FMAs
+__device__ __forceinline__ void eval_pair_fma(const double *cm, double b0, double b1, double b2, double mkx,
+                                              double mky, double &dx, double &dy) {
+    const double sx = fma(cm[0], b0, fma(cm[1], b1, fma(cm[2], b2, cm[3])));
+    const double sy = fma(cm[4], b0, fma(cm[5], b1, fma(cm[6], b2, cm[7])));
+    const double sw = fma(cm[8], b0, fma(cm[9], b1, fma(cm[10], b2, cm[11])));
+    const double r = rcp_nr(sw);
+    dx = fabs(fma(div_nr(sx, sw, r), -0.5, mkx));  // reprojection.rs:55-62
+    dy = fabs(fma(div_nr(sy, sw, r), -0.5, mky));
+}
+
+template <int W, int MINB, bool DIST_LAST>
+__global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, TiledPlan tp, int mt,
+                                                                double *__restrict__ fvec, double *__restrict__ dist,
+                                                                double *__restrict__ jac, double *__restrict__ dist_last) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int nv = tp.VC + 1;
+    const int nrec = (tp.VB + 1) * kBndRec;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);                        // [nv + 1]
+    double *scam = reinterpret_cast<double *>(smem_raw + 256);                      // [nv][14][32]
+    double *smk = scam + (size_t)nv * kRowSlots * kRowFrames;                       // [mt][3][32] marker x, y, weight
+    double *sbnd = smk + (size_t)mt * 3 * kRowFrames;                               // [mt][VB+1][4]
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int f0 = blockIdx.x * kRowFrames, f = f0 + lane;
+    const int F = s.F;
+    const int nfr = min(kRowFrames, F - f0);
+    const int m0 = blockIdx.y * mt;
+    const int mcount = min(mt, s.M - m0);
+    uint64_t *bar_mk = &bars[nv];
+    if (threadIdx.x == 0) {
+        for (int v = 0; v <= nv; ++v) mbar_init(&bars[v], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    const uint32_t row_bytes = (uint32_t)nfr * 8u;
+    if (threadIdx.x == 0) {
+        mbar_expect_tx(&bars[0], 14u * row_bytes + (tp.bnd_contig ? (uint32_t)(mcount * nrec) * 8u : 0u));
+        for (int v = 1; v < nv; ++v) mbar_expect_tx(&bars[v], 13u * row_bytes);
+        mbar_expect_tx(bar_mk, 3u * (uint32_t)mcount * row_bytes);
+        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)m0 * nrec, (uint32_t)(mcount * nrec) * 8u, &bars[0]);
+    }
+    const double *ctab = s.cam_tab + s.cam_off[tp.cam] + f0;
+    const int ncam = nv * kRowSlots;
+    for (int t = threadIdx.x; t < ncam + 3 * mcount; t += 32 * W) {
+        if (t < ncam) {
+            const int v = t / kRowSlots, j = t - v * kRowSlots;
+            int src_row = j;
+            if (v > 0) { if (j == 13) continue; if (j == 12) src_row = 14; }
+            bulk_g2s(scam + ((size_t)v * kRowSlots + j) * kRowFrames, ctab + ((size_t)v * kCamRec + src_row) * F, row_bytes, &bars[v]);
+        } else {
+            const int u = t - ncam, j = u / 3, a = u - 3 * j;
+            const double *src = (a == 0 ? s.obs_mx : a == 1 ? s.obs_my : s.obs_w) + (size_t)(m0 + j) * F + f0;
+            bulk_g2s(smk + ((size_t)j * 3 + a) * kRowFrames, src, row_bytes, bar_mk);
+        }
+    }
+    if (!tp.bnd_contig) {
+        for (int t = threadIdx.x; t < mcount * nrec; t += 32 * W) {
+            const int j = t / nrec, r = t - j * nrec;
+            sbnd[t] = s.bnd_tab[s.bnd_off[s.mkr_bnd[m0 + j]] + r];
+        }
+        __syncthreads();
+    }
+    if (f >= F) return;
+    const double imw = s.image_width;
+    mbar_wait(&bars[0], 0);
+    double cm[14];
+#pragma unroll
+    for (int j = 0; j < 14; ++j) cm[j] = scam[j * kRowFrames + lane];
+    mbar_wait(bar_mk, 0);
+    bool variants_ready = false;
+    double2 *jac2 = reinterpret_cast<double2 *>(jac);
+    for (int jj = 2 * w; jj < mcount; jj += 2 * W) {
+        const bool two = jj + 1 < mcount;
+        const int j1 = two ? jj + 1 : jj;
+        const size_t i0 = (size_t)(m0 + jj) * F + f;
+        const size_t i1 = (size_t)(m0 + j1) * F + f;
+        const double *b0 = sbnd + (size_t)jj * nrec;
+        const double *b1 = sbnd + (size_t)j1 * nrec;
+        const double *k0 = smk + (size_t)jj * 3 * kRowFrames + lane, *k1 = smk + (size_t)j1 * 3 * kRowFrames + lane;
+        const double mkx0 = k0[0] * cm[12], mky0 = k0[kRowFrames] * cm[13], w0 = sqrt(k0[2 * kRowFrames]);
+        const double mkx1 = k1[0] * cm[12], mky1 = k1[kRowFrames] * cm[13], w1 = sqrt(k1[2 * kRowFrames]);
+        double dx0, dy0, dx1, dy1;
+        eval_pair_fma(cm, b0[0], b0[1], b0[2], mkx0, mky0, dx0, dy0);
+        eval_pair_fma(cm, b1[0], b1[1], b1[2], mkx1, mky1, dx1, dy1);
+        if (fvec) {
+            reinterpret_cast<double2 *>(fvec)[i0] = make_double2(dx0 * imw * w0, dy0 * imw * w0);
+            if (two) reinterpret_cast<double2 *>(fvec)[i1] = make_double2(dx1 * imw * w1, dy1 * imw * w1);
+        }
+        if (dist || DIST_LAST) {
+            const double d0 = sqrt((dx0 * dx0) + (dy0 * dy0)) * imw, d1 = sqrt((dx1 * dx1) + (dy1 * dy1)) * imw;
+            if (dist) { dist[i0] = d0; if (two) dist[i1] = d1; }
+            if (DIST_LAST) { dist_last[i0] = d0; if (two) dist_last[i1] = d1; }
+        }
+        // (|a| - |e|) * imageWidth * sqrt(weight) / delta: the subtraction of the two
+        // unweighted deviations is exact-or-better than subtracting the weighted ones
+        const double c0 = imw * w0, c1 = imw * w1;
+        // bundle columns: base camera rows, perturbed bundle
+        for (int v = 0; v < tp.VB; ++v) {
+            const double *q0 = b0 + (v + 1) * kBndRec, *q1 = b1 + (v + 1) * kBndRec;
+            double ax, ay, bx, by;
+            eval_pair_fma(cm, q0[0], q0[1], q0[2], mkx0, mky0, ax, ay);
+            eval_pair_fma(cm, q1[0], q1[1], q1[2], mkx1, mky1, bx, by);
+            double2 *jp = jac2 + tp.bnd_coloff_u[v];
+            const double g0 = c0 * q0[3], g1 = c1 * q1[3];
+            jp[i0] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            if (two) jp[i1] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            if (DIST_LAST) {
+                if (tp.mkr_bnd_attr[(size_t)(m0 + jj) * tp.VB + v] == s.A - 1) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (two && tp.mkr_bnd_attr[(size_t)(m0 + j1) * tp.VB + v] == s.A - 1)
+                    dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
+            }
+        }
+        // camera columns: perturbed camera rows from shared memory, base bundle
+        if (!variants_ready) {
+            for (int v = 1; v < nv; ++v) mbar_wait(&bars[v], 0);
+            variants_ready = true;
+        }
+        for (int v = 0; v < tp.VC; ++v) {
+            const double *sv = scam + (size_t)(v + 1) * kRowSlots * kRowFrames + lane;
+            double cv[12];
+#pragma unroll
+            for (int j = 0; j < 12; ++j) cv[j] = sv[j * kRowFrames];
+            const double inv_delta = sv[12 * kRowFrames];
+            double ax, ay, bx, by;
+            eval_pair_fma(cv, b0[0], b0[1], b0[2], mkx0, mky0, ax, ay);
+            eval_pair_fma(cv, b1[0], b1[1], b1[2], mkx1, mky1, bx, by);
+            double2 *jp = jac2 + tp.cam_coloff_u[v];
+            const double g0 = c0 * inv_delta, g1 = c1 * inv_delta;
+            jp[i0] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            if (two) jp[i1] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            if (DIST_LAST && tp.last_attr_cam_var == v) {
+                dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (two) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
     }

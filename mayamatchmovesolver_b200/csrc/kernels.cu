@@ -1,5 +1,6 @@
 // CUDA kernels (sm_100a) of the residual / FD-Jacobian path and the handle
 // that owns their HBM buffers.  Per-thread bodies live in eval_bodies.cuh.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 
@@ -62,9 +63,40 @@ mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist) {
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols, double *d_dist_last) {
     if (p->tiled_ok) {
         static int variant = -1;
-        if (variant < 0) { const char *e = getenv("MMB_TILE"); variant = e ? atoi(e) : 0; }
+        if (variant < 0) { const char *e = getenv("MMB_TILE"); variant = e ? atoi(e) : 4; }
         const int fblocks = (p->hp.F + kTileFrames - 1) / kTileFrames;
         int m_done = 0;
+        // animated camera, uniform layout: camera rows in shared memory, one resident wave
+        static int rows_mode = -1, rows_g = 0, sm_count = 0;
+        if (rows_mode < 0) {
+            const char *e = getenv("MMB_JAC_ROWS"); rows_mode = e ? atoi(e) : 1;
+            const char *g = getenv("MMB_ROWS_G"); rows_g = g ? atoi(g) : 0;
+            cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device);
+        }
+        if (rows_mode && p->tiled.uniform && !d_cols && p->hp.cam_fs[p->tiled.cam] == p->hp.F && (p->hp.F % 2) == 0 &&
+            (p->hp.cam_off[p->tiled.cam] % 2) == 0) {
+            constexpr int W = 4, MINB = 4;
+            const int nv = p->tiled.VC + 1, nrec = (p->tiled.VB + 1) * kBndRec;
+            const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
+            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kRowSlots * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
+            auto kern = d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>;
+            int mt = 2, G = 0;
+            {   // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
+                int occ = 1;
+                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(64)));
+                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(32)));
+                const int slots = std::max(1, occ) * sm_count;
+                G = rows_g > 0 ? rows_g : std::max(1, slots / fb);
+                G = std::min(G, (p->hp.M + 1) / 2);
+                mt = (p->hp.M + G - 1) / G;
+                mt = std::min(64, (mt + 1) & ~1);
+                G = (p->hp.M + mt - 1) / mt;
+            }
+            kern<<<dim3(fb, G), 32 * W, smem_for(mt), p->stream>>>(p->ds, p->tiled, mt, d_fvec, d_dist, d_jac, d_dist_last);
+            ++p->launches;
+            MMB_CUDA_CHECK(cudaGetLastError());
+            return MMB_OK;
+        }
         // full tiles of a uniform-layout scene: fast instance
         if (p->tiled.uniform && !d_cols) {
 #define MMB_FAST(MPC, MINB)                                                                                          \
@@ -85,8 +117,8 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
                 case 1: MMB_FAST(1, 6) break;
                 case 2: MMB_FAST(3, 4) break;
                 case 3: MMB_FAST(4, 3) break;
-                case 4: MMB_FAST(4, 4) break;
-                default: MMB_FAST(2, 4) break;
+                case 0: MMB_FAST(2, 4) break;
+                default: MMB_FAST(4, 4) break;
             }
 #undef MMB_FAST
         }
@@ -278,6 +310,14 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             CK(A.upload(&d8, ccol)); t.mkr_cam_col = d8;
             CK(A.upload(&d8, bcol)); t.mkr_bnd_col = d8;
             CK(A.upload(&tmp_i, battr)); t.mkr_bnd_attr = tmp_i;
+            t.bnd_contig = 1;
+            t.bnd_rec0 = hp.bnd_off[hp.mkr_bnd[0]];
+            for (int mk = 0; mk < hp.M && t.bnd_contig; ++mk) {
+                const int b = hp.mkr_bnd[mk];
+                if (hp.bnd_fs[b] != 1 || hp.bnd_nvar[b] != (int)VB + 1 ||
+                    hp.bnd_off[b] != t.bnd_rec0 + (int64_t)mk * (int64_t)(VB + 1) * kBndRec) t.bnd_contig = 0;
+            }
+            if (t.bnd_rec0 % 2) t.bnd_contig = 0;  // 16-byte alignment of the bulk copy
             t.last_attr_cam_var = -1;
             for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
             p->tiled_ok = true;

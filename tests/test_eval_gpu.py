@@ -55,7 +55,9 @@ def test_residuals_and_jacobian_match_oracle(case, adt, path, monkeypatch):
             vals, cols = p.eval_jacobian_blocks(xt)
             assert np.array_equal(blocks_to_dense(vals, cols, p.n), J)
             # values-only call: the kernel instance the LM loop and bench use (no column ids)
-            assert np.array_equal(p.eval_jacobian_blocks(xt, want_cols=False), vals)
+            # (different schedule and FMA contraction: equal to rounding, amplified by 1/delta)
+            fast = p.eval_jacobian_blocks(xt, want_cols=False)
+            assert np.abs(fast - vals).max() <= 1e-9 * np.abs(Jo).max()
 
 
 def test_full_size_properties():
