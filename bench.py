@@ -153,15 +153,15 @@ def run_own(args):
         p.bench_eval(1, True)
     barrier()
     sampler.start()
-    l0 = p.launch_count()
+    launches = 0
     tot_ms = jac_ms = 0.0
     t_wall0 = time.perf_counter()
     for _ in range(args.steps):
-        ms, msj, _ = p.bench_eval(1, True)
+        ms, msj, nl = p.bench_eval(1, True)
         tot_ms += ms
         jac_ms += msj
+        launches += nl  # kernels inside the step's event bracket (the kernel-only bracket is separate)
     t_wall = time.perf_counter() - t_wall0
-    launches = p.launch_count() - l0
     barrier()
     clocks = sampler.stop()
     if dist is not None:

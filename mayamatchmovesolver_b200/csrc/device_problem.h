@@ -73,6 +73,7 @@ struct DeviceProblem {
     double *d_flush = nullptr;  // L2 flush scratch (bench only)
     bool tiled_ok = false;      // register-tiled Jacobian kernel applies
     TiledPlan tiled{};
+    int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
     volatile int cancel = 0;
     long long launches = 0;     // kernels launched by this handle

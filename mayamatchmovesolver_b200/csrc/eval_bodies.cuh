@@ -108,6 +108,19 @@ MMB_HD int find_job(const int64_t *start, int njobs, long long t) {
 }
 
 constexpr int kCamRec = 16;  // doubles per camera variant record
+// Camera table index of (variant v, row j, frame f) for a camera with nvar variants.
+// Animated cameras are stored in blocks of 32 frames, [frame block][variant][row pair][frame][2]:
+// rows 2k and 2k+1 of one frame are adjacent (one 16-byte access), consecutive frames are
+// consecutive (coalesced), and everything a 32-frame tile needs -- all variants -- is ONE
+// contiguous run that a single TMA bulk copy brings into shared memory.
+constexpr int kCamBlock = 32;
+MMB_HD size_t cam_idx(int v, int j, int fs, int f, int nvar) {
+    if (fs == 1) return (size_t)v * kCamRec + (size_t)j;
+    const size_t fb = (size_t)(f / kCamBlock);
+    const int fl = f % kCamBlock;
+    return ((((fb * nvar + v) * (kCamRec / 2) + (size_t)(j >> 1)) * kCamBlock + fl) << 1) + (size_t)(j & 1);
+}
+MMB_HD int cam_nvar_of(int ndep, int central) { return 1 + (central ? 2 : 1) * ndep; }
 constexpr int kBndRec = 4;   // doubles per bundle variant record
 
 // View for variant `var` of an entity with `ndep` dependencies at frame f.
@@ -151,7 +164,7 @@ MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
 // One thread per (camera, variant, frame): kCamRec doubles
 //   [0..11] rows 0,1,3 of P*inv(W);  [12],[13] marker film-fit scale;
 //   [14] 1/deltaA of the perturbed parameter (variants only)
-// table layout: cam_off[c] + ((v*kCamRec + j) * fs + f)
+// table layout: cam_off[c] + cam_idx(v, j, fs, f, nvar)
 MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
     const int job = s.cam_thread_job[t];
     const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
@@ -169,9 +182,10 @@ MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long 
     camera_rows(w, p, out);
     marker_film_fit_scale(s.cam_fit[c], sw / sh, (double)s.cam_rw[c] / (double)s.cam_rh[c], out[12], out[13]);
     double *dst = s.cam_tab + s.cam_off[c];
+    const int nvar = cam_nvar_of(s.cam_ndep[c], s.central);
 #pragma unroll
-    for (int j = 0; j < 14; ++j) dst[((size_t)v * kCamRec + j) * fs + f] = out[j];
-    dst[((size_t)v * kCamRec + 14) * fs + f] = inv_da;
+    for (int j = 0; j < 14; ++j) dst[cam_idx(v, j, fs, f, nvar)] = out[j];
+    dst[cam_idx(v, 14, fs, f, nvar)] = inv_da;
 }
 
 // One thread per (bundle, variant, frame): world position + 1/deltaA (kBndRec doubles)
@@ -217,9 +231,10 @@ struct ObsCtx {
 MMB_HD void load_cam(const DevScene &s, int c, int v, int f, double *cm /*14*/) {
     const int fs = s.cam_fs[c];
     const int ff = fs == 1 ? 0 : f;
-    const double *src = s.cam_tab + s.cam_off[c] + (size_t)v * kCamRec * fs + ff;
+    const double *src = s.cam_tab + s.cam_off[c];
+    const int nvar = cam_nvar_of(s.cam_ndep[c], s.central);
 #pragma unroll
-    for (int j = 0; j < 14; ++j) cm[j] = src[(size_t)j * fs];
+    for (int j = 0; j < 14; ++j) cm[j] = src[cam_idx(v, j, fs, ff, nvar)];
 }
 MMB_HD void load_bnd(const DevScene &s, int b, int v, int f, double *bp /*3*/) {
     const int fs = s.bnd_fs[b];

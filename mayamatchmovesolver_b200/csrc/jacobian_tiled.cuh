@@ -37,6 +37,7 @@ struct TiledPlan {
     const int32_t *mkr_bnd_attr; // [M*VB] solver attr of bundle dep v (-1: none)
     int bnd_contig;              // bundle records of markers 0..M-1 are consecutive in bnd_tab
     long long bnd_rec0;          // ... starting at this offset (doubles)
+    const double *mk_blk;        // marker x, y, weight re-blocked [frame block of 32][marker][3][32]
     int last_attr_cam_var;       // 0-based camera dep index of attr A-1 (the variant the
                                  // reference's errorDistanceList ends on), or -1
 };
@@ -98,10 +99,14 @@ __global__ void __launch_bounds__(kTileFrames, MINB) k_jacobian_tiled(DevScene s
     const size_t mtot = 2 * (size_t)s.nobs;
     const double imw = s.image_width;
     const int cfs = s.cam_fs[tp.cam];
-    const double *ctab = s.cam_tab + s.cam_off[tp.cam] + (cfs == 1 ? 0 : f);
+    // row pairs of (variant 0, this frame); next pair: + cps, next variant: + cvs (cam_idx)
+    const int cps = cfs == 1 ? 1 : kCamBlock;
+    const size_t cvs = (size_t)(kCamRec / 2) * cps;
+    const double2 *ctab = reinterpret_cast<const double2 *>(s.cam_tab + s.cam_off[tp.cam]) +
+                          (cfs == 1 ? (size_t)0 : (size_t)(f / kCamBlock) * (tp.VC + 1) * cvs + (size_t)(f % kCamBlock));
     double cm[14];
 #pragma unroll
-    for (int j = 0; j < 14; ++j) cm[j] = ctab[(size_t)j * cfs];
+    for (int j = 0; j < 7; ++j) { const double2 t = ctab[(size_t)j * cps]; cm[2 * j] = t.x; cm[2 * j + 1] = t.y; }
 
     // ---- base evaluation of the MPC markers of this frame ------------------
     double mkx[MPC], mky[MPC], wim[MPC], ex[MPC], ey[MPC];
@@ -137,10 +142,10 @@ __global__ void __launch_bounds__(kTileFrames, MINB) k_jacobian_tiled(DevScene s
     // ---- camera columns: one variant in registers at a time ------------------
     for (int v = 0; v < tp.VC; ++v) {
         double cv[12];
-        const double *vt = ctab + (size_t)(v + 1) * kCamRec * cfs;
+        const double2 *vt = ctab + (size_t)(v + 1) * cvs;
 #pragma unroll
-        for (int j = 0; j < 12; ++j) cv[j] = vt[(size_t)j * cfs];
-        const double inv_delta = vt[(size_t)14 * cfs];
+        for (int j = 0; j < 6; ++j) { const double2 t = vt[(size_t)j * cps]; cv[2 * j] = t.x; cv[2 * j + 1] = t.y; }
+        const double inv_delta = vt[(size_t)7 * cps].x;
         const bool is_last = dist_last && tp.last_attr_cam_var == v;
         const int ucol = tp.cam_col_u[v];
 #pragma unroll
@@ -210,10 +215,14 @@ __global__ void __launch_bounds__(kTileFrames, MINB) k_jacobian_tiled_fast(DevSc
     const double imw = s.image_width;
     const int F = s.F;
     const int cfs = s.cam_fs[tp.cam];
-    const double *ctab = s.cam_tab + s.cam_off[tp.cam] + (cfs == 1 ? 0 : f);
+    // row pairs of (variant 0, this frame); next pair: + cps, next variant: + cvs (cam_idx)
+    const int cps = cfs == 1 ? 1 : kCamBlock;
+    const size_t cvs = (size_t)(kCamRec / 2) * cps;
+    const double2 *ctab = reinterpret_cast<const double2 *>(s.cam_tab + s.cam_off[tp.cam]) +
+                          (cfs == 1 ? (size_t)0 : (size_t)(f / kCamBlock) * (tp.VC + 1) * cvs + (size_t)(f % kCamBlock));
     double cm[14];
 #pragma unroll
-    for (int j = 0; j < 14; ++j) cm[j] = ctab[(size_t)j * cfs];
+    for (int j = 0; j < 7; ++j) { const double2 t = ctab[(size_t)j * cps]; cm[2 * j] = t.x; cm[2 * j + 1] = t.y; }
     const size_t i0 = (size_t)m0 * F + f;
     const double *pmx = s.obs_mx + i0, *pmy = s.obs_my + i0, *pw = s.obs_w + i0;
     double2 *jac2 = reinterpret_cast<double2 *>(jac) + i0;
@@ -239,10 +248,10 @@ __global__ void __launch_bounds__(kTileFrames, MINB) k_jacobian_tiled_fast(DevSc
     }
     for (int v = 0; v < tp.VC; ++v) {
         double cv[12];
-        const double *vt = ctab + (size_t)(v + 1) * kCamRec * cfs;
+        const double2 *vt = ctab + (size_t)(v + 1) * cvs;
 #pragma unroll
-        for (int j = 0; j < 12; ++j) cv[j] = vt[(size_t)j * cfs];
-        const double inv_delta = vt[(size_t)14 * cfs];
+        for (int j = 0; j < 6; ++j) { const double2 t = vt[(size_t)j * cps]; cv[2 * j] = t.x; cv[2 * j + 1] = t.y; }
+        const double inv_delta = vt[(size_t)7 * cps].x;
         double2 *jp = jac2 + tp.cam_coloff_u[v];
         const bool is_last = DIST_LAST && tp.last_attr_cam_var == v;
 #pragma unroll
@@ -306,16 +315,20 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  : "memory");
 }
 
-// same as eval_pair with the three dot products as nested FMAs
+// eval_pair with the three dot products as nested FMAs and the quotient taken as
+// s * (1/w) without the final residual correction (<= 2 ulp; both sides of every finite
+// difference use the same formula)
 __device__ __forceinline__ void eval_pair_fma(const double *cm, double b0, double b1, double b2, double mkx,
                                               double mky, double &dx, double &dy) {
     const double sx = fma(cm[0], b0, fma(cm[1], b1, fma(cm[2], b2, cm[3])));
     const double sy = fma(cm[4], b0, fma(cm[5], b1, fma(cm[6], b2, cm[7])));
     const double sw = fma(cm[8], b0, fma(cm[9], b1, fma(cm[10], b2, cm[11])));
-    const double r = rcp_nr(sw);
-    dx = fabs(fma(div_nr(sx, sw, r), -0.5, mkx));  // reprojection.rs:55-62
-    dy = fabs(fma(div_nr(sy, sw, r), -0.5, mky));
+    const double r = rcp_nr(sw) * -0.5;  // reprojection.rs:55-62
+    dx = fabs(fma(sx, r, mkx));
+    dy = fabs(fma(sy, r, mky));
 }
+
+constexpr int kRowPairs = kCamRec / 2;  // 16-byte row pairs per camera variant
 
 template <int W, int MINB, bool DIST_LAST>
 __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, TiledPlan tp, int mt,
@@ -325,13 +338,12 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     const int nv = tp.VC + 1;
     const int nrec = (tp.VB + 1) * kBndRec;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);                        // [nv + 1]
-    double *scam = reinterpret_cast<double *>(smem_raw + 256);                      // [nv][14][32]
-    double *smk = scam + (size_t)nv * kRowSlots * kRowFrames;                       // [mt][3][32] marker x, y, weight
+    double2 *scam = reinterpret_cast<double2 *>(smem_raw + 256);                    // [nv][8 row pairs][32 frames]
+    double *smk = reinterpret_cast<double *>(scam + (size_t)nv * kRowPairs * kRowFrames);  // [mt][3][32] marker x, y, weight
     double *sbnd = smk + (size_t)mt * 3 * kRowFrames;                               // [mt][VB+1][4]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int f0 = blockIdx.x * kRowFrames, f = f0 + lane;
     const int F = s.F;
-    const int nfr = min(kRowFrames, F - f0);
     const int m0 = blockIdx.y * mt;
     const int mcount = min(mt, s.M - m0);
     uint64_t *bar_mk = &bars[nv];
@@ -340,28 +352,29 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    const uint32_t row_bytes = (uint32_t)nfr * 8u;
+    // Every input of the tile is one contiguous run (cam_idx block layout, frame-blocked
+    // marker copy, marker-ordered bundle records): nv + 2 TMA bulk copies per CTA.
     if (threadIdx.x == 0) {
-        mbar_expect_tx(&bars[0], 14u * row_bytes + (tp.bnd_contig ? (uint32_t)(mcount * nrec) * 8u : 0u));
-        for (int v = 1; v < nv; ++v) mbar_expect_tx(&bars[v], 13u * row_bytes);
-        mbar_expect_tx(bar_mk, 3u * (uint32_t)mcount * row_bytes);
-        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)m0 * nrec, (uint32_t)(mcount * nrec) * 8u, &bars[0]);
-    }
-    const double *ctab = s.cam_tab + s.cam_off[tp.cam] + f0;
-    const int ncam = nv * kRowSlots;
-    for (int t = threadIdx.x; t < ncam + 3 * mcount; t += 32 * W) {
-        if (t < ncam) {
-            const int v = t / kRowSlots, j = t - v * kRowSlots;
-            int src_row = j;
-            if (v > 0) { if (j == 13) continue; if (j == 12) src_row = 14; }
-            bulk_g2s(scam + ((size_t)v * kRowSlots + j) * kRowFrames, ctab + ((size_t)v * kCamRec + src_row) * F, row_bytes, &bars[v]);
-        } else {
-            const int u = t - ncam, j = u / 3, a = u - 3 * j;
-            const double *src = (a == 0 ? s.obs_mx : a == 1 ? s.obs_my : s.obs_w) + (size_t)(m0 + j) * F + f0;
-            bulk_g2s(smk + ((size_t)j * 3 + a) * kRowFrames, src, row_bytes, bar_mk);
+        const uint32_t var_bytes = (uint32_t)(kRowPairs * kRowFrames * sizeof(double2));
+        const uint32_t mk_bytes = (uint32_t)mcount * 3u * kRowFrames * 8u;
+        const uint32_t bnd_bytes = tp.bnd_contig ? (uint32_t)(mcount * nrec) * 8u : 0u;
+        const double2 *ctab = reinterpret_cast<const double2 *>(s.cam_tab + s.cam_off[tp.cam]) +
+                              (size_t)blockIdx.x * nv * kRowPairs * kRowFrames;
+        // the marker tracks are problem constants: fetch them (HBM latency) before waiting on
+        // the variants kernel this launch may overlap with (programmatic dependent launch)
+        mbar_expect_tx(bar_mk, mk_bytes);
+        bulk_g2s(smk, tp.mk_blk + ((size_t)blockIdx.x * s.M + m0) * 3 * kRowFrames, mk_bytes, bar_mk);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        mbar_expect_tx(&bars[0], var_bytes + bnd_bytes);
+        bulk_g2s(scam, ctab, var_bytes, &bars[0]);
+        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)m0 * nrec, bnd_bytes, &bars[0]);
+        for (int v = 1; v < nv; ++v) {
+            mbar_expect_tx(&bars[v], var_bytes);
+            bulk_g2s(scam + (size_t)v * kRowPairs * kRowFrames, ctab + (size_t)v * kRowPairs * kRowFrames, var_bytes, &bars[v]);
         }
     }
     if (!tp.bnd_contig) {
+        asm volatile("griddepcontrol.wait;" ::: "memory");
         for (int t = threadIdx.x; t < mcount * nrec; t += 32 * W) {
             const int j = t / nrec, r = t - j * nrec;
             sbnd[t] = s.bnd_tab[s.bnd_off[s.mkr_bnd[m0 + j]] + r];
@@ -373,49 +386,52 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     mbar_wait(&bars[0], 0);
     double cm[14];
 #pragma unroll
-    for (int j = 0; j < 14; ++j) cm[j] = scam[j * kRowFrames + lane];
+    for (int j = 0; j < 7; ++j) { const double2 t = scam[j * kRowFrames + lane]; cm[2 * j] = t.x; cm[2 * j + 1] = t.y; }
     mbar_wait(bar_mk, 0);
     bool variants_ready = false;
-    double2 *jac2 = reinterpret_cast<double2 *>(jac);
+    double2 *const jac2 = reinterpret_cast<double2 *>(jac) + f;
+    const int VB = tp.VB, VC = tp.VC;
     for (int jj = 2 * w; jj < mcount; jj += 2 * W) {
-        const bool two = jj + 1 < mcount;
-        const int j1 = two ? jj + 1 : jj;
-        const size_t i0 = (size_t)(m0 + jj) * F + f;
-        const size_t i1 = (size_t)(m0 + j1) * F + f;
+        // an odd marker count evaluates its last marker twice (same values to the same addresses)
+        const int j1 = min(jj + 1, mcount - 1);
+        const size_t i0 = (size_t)(m0 + jj) * F;
+        const size_t i1 = (size_t)(m0 + j1) * F;
         const double *b0 = sbnd + (size_t)jj * nrec;
         const double *b1 = sbnd + (size_t)j1 * nrec;
         const double *k0 = smk + (size_t)jj * 3 * kRowFrames + lane, *k1 = smk + (size_t)j1 * 3 * kRowFrames + lane;
         const double mkx0 = k0[0] * cm[12], mky0 = k0[kRowFrames] * cm[13], w0 = sqrt(k0[2 * kRowFrames]);
         const double mkx1 = k1[0] * cm[12], mky1 = k1[kRowFrames] * cm[13], w1 = sqrt(k1[2 * kRowFrames]);
+        const double p0x = b0[0], p0y = b0[1], p0z = b0[2], p1x = b1[0], p1y = b1[1], p1z = b1[2];
         double dx0, dy0, dx1, dy1;
-        eval_pair_fma(cm, b0[0], b0[1], b0[2], mkx0, mky0, dx0, dy0);
-        eval_pair_fma(cm, b1[0], b1[1], b1[2], mkx1, mky1, dx1, dy1);
+        eval_pair_fma(cm, p0x, p0y, p0z, mkx0, mky0, dx0, dy0);
+        eval_pair_fma(cm, p1x, p1y, p1z, mkx1, mky1, dx1, dy1);
+        // (|a| - |e|) * imageWidth * sqrt(weight) / delta: subtracting the two unweighted
+        // deviations first loses nothing to rounding
+        const double c0 = imw * w0, c1 = imw * w1;
         if (fvec) {
-            reinterpret_cast<double2 *>(fvec)[i0] = make_double2(dx0 * imw * w0, dy0 * imw * w0);
-            if (two) reinterpret_cast<double2 *>(fvec)[i1] = make_double2(dx1 * imw * w1, dy1 * imw * w1);
+            double2 *fv = reinterpret_cast<double2 *>(fvec) + f;
+            fv[i0] = make_double2(dx0 * c0, dy0 * c0);
+            fv[i1] = make_double2(dx1 * c1, dy1 * c1);
         }
         if (dist || DIST_LAST) {
             const double d0 = sqrt((dx0 * dx0) + (dy0 * dy0)) * imw, d1 = sqrt((dx1 * dx1) + (dy1 * dy1)) * imw;
-            if (dist) { dist[i0] = d0; if (two) dist[i1] = d1; }
-            if (DIST_LAST) { dist_last[i0] = d0; if (two) dist_last[i1] = d1; }
+            if (dist) { dist[i0 + f] = d0; dist[i1 + f] = d1; }
+            if (DIST_LAST) { dist_last[i0 + f] = d0; dist_last[i1 + f] = d1; }
         }
-        // (|a| - |e|) * imageWidth * sqrt(weight) / delta: the subtraction of the two
-        // unweighted deviations is exact-or-better than subtracting the weighted ones
-        const double c0 = imw * w0, c1 = imw * w1;
+        double2 *const jp0 = jac2 + i0, *const jp1 = jac2 + i1;
         // bundle columns: base camera rows, perturbed bundle
-        for (int v = 0; v < tp.VB; ++v) {
+        for (int v = 0; v < VB; ++v) {
             const double *q0 = b0 + (v + 1) * kBndRec, *q1 = b1 + (v + 1) * kBndRec;
             double ax, ay, bx, by;
             eval_pair_fma(cm, q0[0], q0[1], q0[2], mkx0, mky0, ax, ay);
             eval_pair_fma(cm, q1[0], q1[1], q1[2], mkx1, mky1, bx, by);
-            double2 *jp = jac2 + tp.bnd_coloff_u[v];
+            const long long co = tp.bnd_coloff_u[v];
             const double g0 = c0 * q0[3], g1 = c1 * q1[3];
-            jp[i0] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            if (two) jp[i1] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
             if (DIST_LAST) {
-                if (tp.mkr_bnd_attr[(size_t)(m0 + jj) * tp.VB + v] == s.A - 1) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
-                if (two && tp.mkr_bnd_attr[(size_t)(m0 + j1) * tp.VB + v] == s.A - 1)
-                    dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
+                if (tp.mkr_bnd_attr[(size_t)(m0 + jj) * VB + v] == s.A - 1) dist_last[i0 + f] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (tp.mkr_bnd_attr[(size_t)(m0 + j1) * VB + v] == s.A - 1) dist_last[i1 + f] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
         // camera columns: perturbed camera rows from shared memory, base bundle
@@ -423,22 +439,22 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             for (int v = 1; v < nv; ++v) mbar_wait(&bars[v], 0);
             variants_ready = true;
         }
-        for (int v = 0; v < tp.VC; ++v) {
-            const double *sv = scam + (size_t)(v + 1) * kRowSlots * kRowFrames + lane;
+        const double2 *sv = scam + (size_t)kRowPairs * kRowFrames + lane;
+        for (int v = 0; v < VC; ++v, sv += kRowPairs * kRowFrames) {
             double cv[12];
 #pragma unroll
-            for (int j = 0; j < 12; ++j) cv[j] = sv[j * kRowFrames];
-            const double inv_delta = sv[12 * kRowFrames];
+            for (int j = 0; j < 6; ++j) { const double2 t = sv[j * kRowFrames]; cv[2 * j] = t.x; cv[2 * j + 1] = t.y; }
+            const double inv_delta = sv[7 * kRowFrames].x;
             double ax, ay, bx, by;
-            eval_pair_fma(cv, b0[0], b0[1], b0[2], mkx0, mky0, ax, ay);
-            eval_pair_fma(cv, b1[0], b1[1], b1[2], mkx1, mky1, bx, by);
-            double2 *jp = jac2 + tp.cam_coloff_u[v];
+            eval_pair_fma(cv, p0x, p0y, p0z, mkx0, mky0, ax, ay);
+            eval_pair_fma(cv, p1x, p1y, p1z, mkx1, mky1, bx, by);
+            const long long co = tp.cam_coloff_u[v];
             const double g0 = c0 * inv_delta, g1 = c1 * inv_delta;
-            jp[i0] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            if (two) jp[i1] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
             if (DIST_LAST && tp.last_attr_cam_var == v) {
-                dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
-                if (two) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
+                dist_last[i0 + f] = sqrt((ax * ax) + (ay * ay)) * imw;
+                dist_last[i1 + f] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
     }

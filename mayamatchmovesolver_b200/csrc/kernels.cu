@@ -15,6 +15,9 @@ const std::string &get_last_error() { return g_last_error; }
 // ---- kernels ---------------------------------------------------------------
 // kind 0 camera, 1 bundle, 2 lens; base_only skips perturbed variants
 __global__ void k_variants(DevScene s, const double *x, int base_only) {
+    // a dependent launch (k_jacobian_rows) may start its prologue now; it waits for this
+    // grid's results with griddepcontrol.wait
+    asm volatile("griddepcontrol.launch_dependents;");
     const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     const long long nc = s.cam_jobs_total, nb = s.bnd_jobs_total, nl = s.lens_jobs_total;
     if (t < nc) {
@@ -67,34 +70,41 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
         const int fblocks = (p->hp.F + kTileFrames - 1) / kTileFrames;
         int m_done = 0;
         // animated camera, uniform layout: camera rows in shared memory, one resident wave
-        static int rows_mode = -1, rows_g = 0, sm_count = 0;
+        static int rows_mode = -1, rows_g = 0;
         if (rows_mode < 0) {
             const char *e = getenv("MMB_JAC_ROWS"); rows_mode = e ? atoi(e) : 1;
             const char *g = getenv("MMB_ROWS_G"); rows_g = g ? atoi(g) : 0;
-            cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device);
         }
-        if (rows_mode && p->tiled.uniform && !d_cols && p->hp.cam_fs[p->tiled.cam] == p->hp.F && (p->hp.F % 2) == 0 &&
-            (p->hp.cam_off[p->tiled.cam] % 2) == 0) {
+        if (rows_mode && p->tiled.uniform && !d_cols && p->tiled.mk_blk && p->hp.cam_fs[p->tiled.cam] == p->hp.F &&
+            p->hp.F > 1 && (p->hp.cam_off[p->tiled.cam] % 2) == 0) {
             constexpr int W = 4, MINB = 4;
             const int nv = p->tiled.VC + 1, nrec = (p->tiled.VB + 1) * kBndRec;
             const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
-            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kRowSlots * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
+            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
             auto kern = d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>;
-            int mt = 2, G = 0;
-            {   // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
-                int occ = 1;
+            int &mt = p->rows_mt[d_dist_last ? 1 : 0];
+            if (mt == 0) {  // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
+                int occ = 1, sm_count = 1;
+                MMB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device));
                 MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(64)));
                 MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(32)));
                 const int slots = std::max(1, occ) * sm_count;
-                G = rows_g > 0 ? rows_g : std::max(1, slots / fb);
+                int G = rows_g > 0 ? rows_g : std::max(1, slots / fb);
                 G = std::min(G, (p->hp.M + 1) / 2);
                 mt = (p->hp.M + G - 1) / G;
                 mt = std::min(64, (mt + 1) & ~1);
-                G = (p->hp.M + mt - 1) / mt;
             }
-            kern<<<dim3(fb, G), 32 * W, smem_for(mt), p->stream>>>(p->ds, p->tiled, mt, d_fvec, d_dist, d_jac, d_dist_last);
+            const int G = (p->hp.M + mt - 1) / mt;
+            // programmatic dependent launch: the prologue (barrier setup, marker-track fetch)
+            // may start while the preceding kernel of the stream (entity variants) drains
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(fb, G); cfg.blockDim = dim3(32 * W); cfg.dynamicSmemBytes = smem_for(mt); cfg.stream = p->stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, p->tiled, mt, d_fvec, d_dist, d_jac, d_dist_last));
             ++p->launches;
-            MMB_CUDA_CHECK(cudaGetLastError());
             return MMB_OK;
         }
         // full tiles of a uniform-layout scene: fast instance
@@ -318,6 +328,19 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
                     hp.bnd_off[b] != t.bnd_rec0 + (int64_t)mk * (int64_t)(VB + 1) * kBndRec) t.bnd_contig = 0;
             }
             if (t.bnd_rec0 % 2) t.bnd_contig = 0;  // 16-byte alignment of the bulk copy
+            t.mk_blk = nullptr;
+            if (hp.dense_grid) {  // frame-blocked copy of the marker tracks: one contiguous run per tile
+                const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
+                std::vector<double> blk((size_t)FB * hp.M * 3 * kRowFrames, 0.0);
+                for (int mk = 0; mk < hp.M; ++mk)
+                    for (int f = 0; f < hp.F; ++f) {
+                        const size_t i = (size_t)mk * hp.F + f;
+                        double *dst = &blk[(((size_t)(f / kRowFrames) * hp.M + mk) * 3) * kRowFrames + (f % kRowFrames)];
+                        dst[0] = hp.obs_mx[i]; dst[kRowFrames] = hp.obs_my[i]; dst[2 * kRowFrames] = hp.obs_w[i];
+                    }
+                double *d_blk = nullptr;
+                CK(A.upload(&d_blk, blk)); t.mk_blk = d_blk;
+            }
             t.last_attr_cam_var = -1;
             for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
             p->tiled_ok = true;

@@ -258,7 +258,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
                       int width, std::vector<int64_t> &off, std::vector<int32_t> &fs,
                       std::vector<int32_t> &nvar, int64_t &total, std::vector<int32_t> &job_ent,
                       std::vector<int32_t> &job_var, std::vector<int32_t> &job_attr,
-                      std::vector<int64_t> &job_start, int64_t &jobs_total) {
+                      std::vector<int64_t> &job_start, int64_t &jobs_total, int frame_block) {
         const int E = (int)deps.size();
         off.assign(E, 0); fs.assign(E, 1); nvar.assign(E, 1);
         job_ent.clear(); job_var.clear(); job_attr.clear(); job_start.clear();
@@ -270,7 +270,9 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
             fs[e] = varies[e] ? (int32_t)F : 1;
             nvar[e] = 1 + vmul * (int)deps[e].size();
             off[e] = total;
-            total += (int64_t)nvar[e] * width * fs[e];
+            // animated records may be stored in whole frame blocks (cam_idx, eval_bodies.cuh)
+            const int64_t fpad = fs[e] == 1 ? 1 : ((int64_t)fs[e] + frame_block - 1) / frame_block * frame_block;
+            total += (int64_t)nvar[e] * width * fpad;
             for (int v = 0; v < nvar[e]; ++v) {
                 job_ent.push_back(e); job_var.push_back(v);
                 job_attr.push_back(v == 0 ? -1 : deps[e][(v - 1) % deps[e].size()]);
@@ -281,11 +283,11 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         job_start.push_back(jobs_total);
     };
     layout(hp.cam_deps, hp.cam_varies, 16, hp.cam_off, hp.cam_fs, hp.cam_nvar, hp.cam_tab_size,
-           hp.cam_job_ent, hp.cam_job_var, hp.cam_job_attr, hp.cam_job_start, hp.cam_jobs_total);
+           hp.cam_job_ent, hp.cam_job_var, hp.cam_job_attr, hp.cam_job_start, hp.cam_jobs_total, 32);
     layout(hp.bnd_deps, hp.bnd_varies, 4, hp.bnd_off, hp.bnd_fs, hp.bnd_nvar, hp.bnd_tab_size,
-           hp.bnd_job_ent, hp.bnd_job_var, hp.bnd_job_attr, hp.bnd_job_start, hp.bnd_jobs_total);
+           hp.bnd_job_ent, hp.bnd_job_var, hp.bnd_job_attr, hp.bnd_job_start, hp.bnd_jobs_total, 1);
     layout(hp.lens_deps, hp.lens_varies, 24, hp.lens_off, hp.lens_fs, hp.lens_nvar, hp.lens_tab_size,
-           hp.lens_job_ent, hp.lens_job_var, hp.lens_job_attr, hp.lens_job_start, hp.lens_jobs_total);
+           hp.lens_job_ent, hp.lens_job_var, hp.lens_job_attr, hp.lens_job_start, hp.lens_jobs_total, 1);
 
     auto expand = [](const std::vector<int64_t> &start, std::vector<int32_t> &out) {
         out.assign((size_t)start.back(), 0);
