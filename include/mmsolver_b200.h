@@ -43,6 +43,7 @@ typedef int32_t mmb_status;
 #define MMB_ERR_MORE_PARAMS_THAN_ERRORS (-5) /* adjust_base.cpp:864-882 */
 #define MMB_ERR_UNSUPPORTED (-6)
 #define MMB_ERR_INTERNAL (-7)
+#define MMB_ERR_COMM (-8) /* NCCL missing / collective failed */
 
 /* ---- attribute references ----------------------------------------------
  * Every scene value that the reference keeps in its AttrDataBlock is named by
@@ -241,6 +242,46 @@ mmb_status mmb_solve(mmb_problem *p, mmb_result *result, double *x_out,
 mmb_status mmb_solve_per_frame(mmb_problem *p, mmb_result *result,
                                mmb_result *per_frame_results, double *x_out,
                                double *attr_values_out, double *error_dist_out);
+
+/* ---- multi-GPU: frame-range shards (one process per GPU) -----------------
+ * The reference is single-threaded; what shards is its own structure: a
+ * frame's observations touch only that frame's animated parameters
+ * (findErrorToParameterRelationship, adjust_relationships.cpp:565-617).
+ *   per-frame mode (solve_v1's loop, adjust_base.cpp:1430-1484): shards are
+ *     independent, no collective; merge with mmb_aggregate_results.
+ *   global mode: every rank runs the same LM control law on its frames; the
+ *     reduced (static-parameter) system and a few scalars are all-reduced
+ *     once per lmpar trial over NCCL (NVLink / NVSwitch).
+ * Every rank passes the FULL scene; the library cuts it to the rank's frames.
+ * Parameters / observations of a shard handle are numbered locally;
+ * mmb_shard_param_map gives their ids in the unsharded problem. */
+#define MMB_COMM_ID_BYTES 128
+/* contiguous balanced ranges: [*frame_begin, *frame_end) of rank */
+mmb_status mmb_shard_frames(int32_t num_frames, int32_t world, int32_t rank,
+                            int32_t *frame_begin, int32_t *frame_end);
+/* host only (no GPU needed): n of the shard and, when global_param != NULL,
+ * the unsharded parameter id of each of its n_local parameters */
+mmb_status mmb_shard_param_map(const mmb_scene_desc *scene, int32_t world,
+                               int32_t rank, int32_t *n_local,
+                               int32_t *global_param);
+mmb_status mmb_problem_create_shard(const mmb_scene_desc *scene,
+                                    const mmb_options *opt, int32_t rank,
+                                    int32_t world, mmb_problem **out);
+/* rank 0 makes the id (an ncclUniqueId; local_backend != 0: an in-process
+ * group of handles on one device, used by single-GPU tests) and hands the
+ * 128 bytes to the other ranks by any channel (torch.distributed, MPI, file) */
+mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES],
+                              int32_t local_backend);
+/* collective: every rank of the id calls it.  Afterwards mmb_solve() on the
+ * handle is the sharded global solve; results that describe the whole problem
+ * (reason, iteration counts, error_final, error_avg/min/max) are identical on
+ * every rank, x_out / attr_values_out / error_dist_out cover the shard. */
+mmb_status mmb_problem_attach_comm(mmb_problem *p,
+                                   const uint8_t id[MMB_COMM_ID_BYTES],
+                                   int32_t rank, int32_t world);
+/* CommandResult::add / divide (adjust_results.h:89-117, 208-243) */
+mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count,
+                                 mmb_result *out);
 
 /* MComputation::isInterruptRequested analogue; callable from another thread */
 void mmb_request_cancel(mmb_problem *p);

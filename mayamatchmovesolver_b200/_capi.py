@@ -14,9 +14,10 @@ LIB_PATH = os.path.join(HERE, "libmmsolver_b200.so")
 MMB_ABI_VERSION = 1
 MMB_ATTR_NONE = -(2 ** 31)
 MMB_LENS_MAX_COEFFS = 14
+MMB_COMM_ID_BYTES = 128
 
 (MMB_OK, MMB_ERR_INVALID_ARGUMENT, MMB_ERR_CUDA, MMB_ERR_NO_DEVICE, MMB_ERR_NOT_ENOUGH_OBJECTS,
- MMB_ERR_MORE_PARAMS_THAN_ERRORS, MMB_ERR_UNSUPPORTED, MMB_ERR_INTERNAL) = (0, -1, -2, -3, -4, -5, -6, -7)
+ MMB_ERR_MORE_PARAMS_THAN_ERRORS, MMB_ERR_UNSUPPORTED, MMB_ERR_INTERNAL, MMB_ERR_COMM) = (0, -1, -2, -3, -4, -5, -6, -7, -8)
 
 c_i32p = C.POINTER(C.c_int32)
 c_f64p = C.POINTER(C.c_double)
@@ -82,6 +83,13 @@ SYMBOLS = [
     ("mmb_eval_jacobian_blocks", C.c_int32, [C.c_void_p, c_f64p, c_f64p, c_i32p, c_i32p]),
     ("mmb_solve", C.c_int32, [C.c_void_p, C.POINTER(Result), c_f64p, c_f64p, c_f64p]),
     ("mmb_solve_per_frame", C.c_int32, [C.c_void_p, C.POINTER(Result), C.POINTER(Result), c_f64p, c_f64p, c_f64p]),
+    ("mmb_shard_frames", C.c_int32, [C.c_int32, C.c_int32, C.c_int32, c_i32p, c_i32p]),
+    ("mmb_shard_param_map", C.c_int32, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, c_i32p, c_i32p]),
+    ("mmb_problem_create_shard", C.c_int32, [C.POINTER(SceneDesc), C.POINTER(Options), C.c_int32, C.c_int32,
+                                             C.POINTER(C.c_void_p)]),
+    ("mmb_comm_unique_id", C.c_int32, [c_u8p, C.c_int32]),
+    ("mmb_problem_attach_comm", C.c_int32, [C.c_void_p, c_u8p, C.c_int32, C.c_int32]),
+    ("mmb_aggregate_results", C.c_int32, [C.POINTER(Result), C.c_int32, C.POINTER(Result)]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),

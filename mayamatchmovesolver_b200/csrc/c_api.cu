@@ -2,8 +2,10 @@
 #include <cstring>
 #include <new>
 
+#include "comm.h"
 #include "device_problem.h"
 #include "lm.h"
+#include "shard.h"
 
 using namespace mmb;
 
@@ -212,6 +214,97 @@ mmb_status mmb_solve_per_frame(mmb_problem *p, mmb_result *result, mmb_result *p
     }
 }
 
+// ---- multi-GPU: frame-range shards ----------------------------------------------------------
+mmb_status mmb_shard_frames(int32_t num_frames, int32_t world, int32_t rank, int32_t *frame_begin, int32_t *frame_end) {
+    if (num_frames < 0 || world < 1 || rank < 0 || rank >= world || !frame_begin || !frame_end) return MMB_ERR_INVALID_ARGUMENT;
+    int f0, f1;
+    shard_frame_range(num_frames, world, rank, &f0, &f1);
+    *frame_begin = f0; *frame_end = f1;
+    return MMB_OK;
+}
+
+mmb_status mmb_shard_param_map(const mmb_scene_desc *scene, int32_t world, int32_t rank, int32_t *n_local,
+                               int32_t *global_param) {
+    if (!scene || world < 1 || rank < 0 || rank >= world) return MMB_ERR_INVALID_ARGUMENT;
+    if (scene->num_attrs > 0 && !scene->attr_ref) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        int f0, f1;
+        shard_frame_range(scene->num_frames, world, rank, &f0, &f1);
+        std::vector<int32_t> map;
+        shard_param_map(scene, f0, f1, &map);
+        if (n_local) *n_local = (int32_t)map.size();
+        if (global_param) std::memcpy(global_param, map.data(), sizeof(int32_t) * map.size());
+        return MMB_OK;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_shard_param_map");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+mmb_status mmb_problem_create_shard(const mmb_scene_desc *scene, const mmb_options *opt, int32_t rank, int32_t world,
+                                    mmb_problem **out) {
+    if (!scene || !opt || !out || world < 1 || rank < 0 || rank >= world) return MMB_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    try {
+        int f0, f1;
+        shard_frame_range(scene->num_frames, world, rank, &f0, &f1);
+        if (f1 <= f0) {
+            set_last_error("more ranks than frames: this rank's shard is empty");
+            return MMB_ERR_NOT_ENOUGH_OBJECTS;
+        }
+        SceneSlice slice;
+        slice_scene_frames(scene, f0, f1, &slice);
+        mmb_status st = mmb_problem_create(&slice.desc, opt, out);
+        if (st != MMB_OK) return st;
+        (*out)->dp->frame_begin = f0;
+        (*out)->dp->frames_global = scene->num_frames;
+        return MMB_OK;
+    } catch (const std::bad_alloc &) {
+        set_last_error("host allocation failed");
+        return MMB_ERR_INTERNAL;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_problem_create_shard");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES], int32_t local_backend) {
+    if (!id) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        return comm_unique_id(id, local_backend);
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_comm_unique_id");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+mmb_status mmb_problem_attach_comm(mmb_problem *p, const uint8_t id[MMB_COMM_ID_BYTES], int32_t rank, int32_t world) {
+    if (!p || !id) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        DeviceProblem *dp = p->dp;
+        if (dp->comm) { set_last_error("handle already has a communicator"); return MMB_ERR_INVALID_ARGUMENT; }
+        if (dp->hp.opt.frame_solve_mode == 1) {
+            set_last_error("per-frame solves of different shards are independent: no communicator is needed");
+            return MMB_ERR_INVALID_ARGUMENT;
+        }
+        Comm *c = nullptr;
+        mmb_status st = comm_create(id, rank, world, dp->device, &c);
+        if (st != MMB_OK) return st;
+        dp->comm = c;
+        return MMB_OK;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_problem_attach_comm");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count, mmb_result *out) {
+    if (!per_frame || !out || count < 0) return MMB_ERR_INVALID_ARGUMENT;
+    aggregate_results(per_frame, count, out);
+    out->reason_str = mmb_reason_string(out->reason_num);
+    return MMB_OK;
+}
+
 void mmb_request_cancel(mmb_problem *p) {
     if (p) p->dp->cancel = 1;
 }
@@ -284,6 +377,7 @@ const char *mmb_status_string(mmb_status s) {
         case MMB_ERR_MORE_PARAMS_THAN_ERRORS: return "more unknown parameters than error measurements";
         case MMB_ERR_UNSUPPORTED: return "unsupported option";
         case MMB_ERR_INTERNAL: return "internal error";
+        case MMB_ERR_COMM: return "communicator error (NCCL)";
         default: return "unknown status";
     }
 }

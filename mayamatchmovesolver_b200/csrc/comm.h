@@ -1,0 +1,34 @@
+// Collective plumbing of a sharded global solve: the only
+// exchange step of the path is a sum (or max) all-reduce of device buffers.
+//
+// Two backends behind one interface:
+//   * NCCL over NVLink / NVSwitch (one process per GPU).  libnccl.so.2 is
+//     opened with dlopen the first time a communicator is asked for, so the
+//     single-GPU product does not depend on NCCL being installed.
+//   * "local": several handles of ONE process on ONE device (one host thread
+//     each).  The reduction is a kernel over the ranks' buffers, ordered by a
+//     host barrier.  It exists so the sharded LM logic can be exercised on a
+//     one-GPU box; it is not a CPU path (every buffer stays in HBM).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+#include "../../include/mmsolver_b200.h"
+
+namespace mmb {
+
+struct Comm {
+    int rank = 0, world = 1;
+    virtual ~Comm() {}
+    // in-place all-reduce of buf[0..count) on `stream`; sum, or max when is_max
+    virtual mmb_status allreduce(double *buf, size_t count, bool is_max, cudaStream_t stream) = 0;
+    virtual const char *backend() const = 0;
+};
+
+mmb_status comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES], int local_backend);
+// collective over all ranks of the id; binds the communicator to `device`
+mmb_status comm_create(const uint8_t id[MMB_COMM_ID_BYTES], int rank, int world, int device, Comm **out);
+
+}  // namespace mmb

@@ -56,6 +56,7 @@ struct DeviceArena {
 };
 
 struct LmWorkspace;  // lm_global.cu
+struct Comm;         // comm.h
 
 struct DeviceProblem {
     HostProblem hp;
@@ -75,6 +76,9 @@ struct DeviceProblem {
     TiledPlan tiled{};
     int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
+    Comm *comm = nullptr;       // set by mmb_problem_attach_comm: mmb_solve is then the sharded global solve
+    int frame_begin = 0;        // first frame of this shard in the unsharded scene
+    int frames_global = 0;      // frame count of the unsharded scene
     volatile int cancel = 0;
     long long launches = 0;     // kernels launched by this handle
 

@@ -4,6 +4,7 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "comm.h"
 #include "device_problem.h"
 
 namespace mmb {
@@ -154,6 +155,7 @@ void lm_workspace_destroy(LmWorkspace *w);
 DeviceProblem::~DeviceProblem() {
     cudaSetDevice(device);
     if (lm) lm_workspace_destroy(lm);
+    if (comm) { if (stream) cudaStreamSynchronize(stream); delete comm; }
     if (stream) cudaStreamDestroy(stream);
     arena.release();
 }

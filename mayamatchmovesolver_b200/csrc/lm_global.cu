@@ -13,12 +13,17 @@
 #include <cstdlib>
 #include <cstring>
 
+#include "comm.h"
 #include "lm.h"
 #include "lm_kernels.cuh"
 
 namespace mmb {
 
 constexpr int kRedBlocks = 592;  // 148 SMs x 4 partial-sum blocks
+// One contiguous reduction scratch, so a sharded solve all-reduces each stage in one call:
+//   [part_f kRedBlocks][part_jp kRedBlocks][scal kRedScal (sums)][mx kRedMax (maxima)]
+constexpr int kRedScal = 8, kRedMax = 4;
+constexpr int kStatBlocks = 148;
 
 struct LmWorkspace {
     LmDims d{};
@@ -33,8 +38,13 @@ struct LmWorkspace {
     double *p_par = nullptr, *x2 = nullptr;           // [n] parameter order
     double *fvec2 = nullptr, *dist2 = nullptr;
     double *part_f = nullptr, *part_jp = nullptr;     // [kRedBlocks]
+    double *scal = nullptr, *mx = nullptr;            // [kRedScal], [kRedMax]
+    double *sdiag = nullptr;                          // [2 ns]: diagonal of V, then J^T f of the static side
+    double *tvec = nullptr;                           // [ns]: Y^T w
+    double *stat_part = nullptr;                      // [3 kStatBlocks]
     double *part_gemv = nullptr;                      // [chunks * NSP]
     int gemv_chunks = 1;
+    long long n_allreduce = 0;
     double init_avg = 0, init_min = 0, init_max = 0;
     // optional phase timing (MMB_LM_PROFILE=1): schur, cholesky, back-substitution, q-solve
     bool profile = false;
@@ -49,6 +59,10 @@ struct LmWorkspace {
 void lm_workspace_destroy(LmWorkspace *w) { delete w; }
 
 // ---- control kernels (one block of 1024 threads) ---------------------------------------
+// Sums over all parameters are split in two: the eliminated side (animated parameters:
+// local to a shard, so its part is all-reduced when the solve is sharded) goes to the
+// reduction scratch `scal` / `mx`; the reduced side (static parameters: replicated and
+// identical on every rank) goes to st->part_s and is added after the all-reduce.
 __device__ double sum_partials(const double *part, int n, double *sh) {
     double a = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) a += part[i];
@@ -73,27 +87,38 @@ __global__ void k_ctrl_init(LmState *st, const double *part_f, int nparts) {
     }
 }
 
-// After assembly: column norms, diag, delta (first iteration), gnorm / gtol test,
-// and the start of lmpar.
+// diagonal and right-hand side of the static block: what the column norms / gradient test
+// need from V.  A sharded solve all-reduces these 2 ns values instead of the whole block.
+__global__ void k_prep_gather(LmDims d, const double *__restrict__ V, double *__restrict__ sdiag) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= d.ns) return;
+    sdiag[j] = V[(size_t)j * d.NSP + j];
+    sdiag[d.ns + j] = V[(size_t)d.ns * d.NSP + j];
+}
+
+// After assembly: column norms and diag; partial sums of xnorm^2, ||g/diag||^2 and the
+// gradient test's maximum.
 __global__ void __launch_bounds__(1024) k_ctrl_prep(LmDims d, LmState *st, const double *U, const double *gE,
-                                                    const double *V, const int32_t *i2p, const double *x,
-                                                    double *diag, double *acnorm) {
+                                                    const double *sdiag, const int32_t *i2p, const double *x,
+                                                    double *diag, double *acnorm, double *scal, double *mx) {
     __shared__ double sh[32];
+    __shared__ double wmax[2][32];
     const int n = d.n;
     const bool first = st->iter == 1;
     const double fnorm = st->fnorm;
-    double xs = 0.0, gmax = 0.0, gs = 0.0;
+    double xsE = 0.0, gsE = 0.0, xsS = 0.0, gsS = 0.0, gmaxE = 0.0, gmaxS = 0.0;
     for (int q = threadIdx.x; q < n; q += blockDim.x) {
         const int pid = i2p[q];
+        const bool elim = q < d.KE;
         double h, g;
-        if (q < d.KE) {
+        if (elim) {
             const int f = q / d.na, a = q - f * d.na;
             h = U[((size_t)f * d.na + a) * d.na + a];
             g = gE[q];
         } else {
             const int s = q - d.KE;
-            h = V[(size_t)s * d.NSP + s];
-            g = V[(size_t)d.ns * d.NSP + s];
+            h = sdiag[s];
+            g = sdiag[d.ns + s];
         }
         const double ac = sqrt(fmax(h, 0.0));
         acnorm[pid] = ac;
@@ -103,60 +128,73 @@ __global__ void __launch_bounds__(1024) k_ctrl_prep(LmDims d, LmState *st, const
         }
         if (first) {
             const double t = dg * x[pid];
-            xs += t * t;
+            if (elim) xsE += t * t; else xsS += t * t;
         }
-        if (fnorm != 0.0 && ac != 0.0) gmax = fmax(gmax, fabs(g / fnorm) / ac);
+        if (fnorm != 0.0 && ac != 0.0) {
+            const double t = fabs(g / fnorm) / ac;
+            if (elim) gmaxE = fmax(gmaxE, t); else gmaxS = fmax(gmaxS, t);
+        }
         if (st->mode != 2) dg = fmax(dg, ac);
         diag[pid] = dg;
         const double t2 = g / dg;
-        gs += t2 * t2;
+        if (elim) gsE += t2 * t2; else gsS += t2 * t2;
     }
-    xs = block_sum(xs, sh);
-    gs = block_sum(gs, sh);
-    // max-reduce
-    __syncthreads();
-    for (int o = 16; o > 0; o >>= 1) gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o));
-    __shared__ double wmax[32];
-    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = gmax;
+    xsE = block_sum(xsE, sh); gsE = block_sum(gsE, sh);
+    xsS = block_sum(xsS, sh); gsS = block_sum(gsS, sh);
+    for (int o = 16; o > 0; o >>= 1) {
+        gmaxE = fmax(gmaxE, __shfl_xor_sync(0xffffffffu, gmaxE, o));
+        gmaxS = fmax(gmaxS, __shfl_xor_sync(0xffffffffu, gmaxS, o));
+    }
+    if ((threadIdx.x & 31) == 0) { wmax[0][threadIdx.x >> 5] = gmaxE; wmax[1][threadIdx.x >> 5] = gmaxS; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        double g = 0.0;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) g = fmax(g, wmax[w]);
-        st->njev += 1;
-        if (first) {
-            st->xnorm = sqrt(xs);
-            st->delta = st->factor * st->xnorm;
-            if (st->delta == 0.0) st->delta = st->factor;
-        }
-        st->gnorm = g;
-        st->gnorm_scaled = sqrt(gs);
-        st->need_jacobian = 0;
-        if (g <= st->gtol) { st->info = 4; st->done = 1; }
-        st->lmpar_iter = 0; st->lmpar_done = 0; st->chol_fail = 0; st->par_cur = 0.0;
+        double ge = 0.0, gs2 = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { ge = fmax(ge, wmax[0][w]); gs2 = fmax(gs2, wmax[1][w]); }
+        scal[0] = xsE; scal[1] = gsE; mx[0] = ge;
+        st->part_s[0] = xsS; st->part_s[1] = gsS; st->part_s[2] = gs2;
     }
 }
 
-// dxnorm = ||D p|| after a solve (needed by the q-solve that follows)
-__global__ void __launch_bounds__(1024) k_dxnorm(LmDims d, LmState *st, const double *p_int, const double *diag,
-                                                 const int32_t *i2p) {
-    __shared__ double sh[32];
-    double a = 0.0;
-    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
-        const double t = diag[i2p[q]] * p_int[q < d.KE ? q : q];
-        a += t * t;
+// xnorm / delta on the first iteration, the gtol test (info 4), start of lmpar
+__global__ void k_ctrl_prep_decide(LmState *st, const double *scal, const double *mx) {
+    const bool first = st->iter == 1;
+    const double g = fmax(mx[0], st->part_s[2]);
+    st->njev += 1;
+    if (first) {
+        st->xnorm = sqrt(scal[0] + st->part_s[0]);
+        st->delta = st->factor * st->xnorm;
+        if (st->delta == 0.0) st->delta = st->factor;
     }
-    a = block_sum(a, sh);
+    st->gnorm = g;
+    st->gnorm_scaled = sqrt(scal[1] + st->part_s[1]);
+    st->need_jacobian = 0;
+    if (g <= st->gtol) { st->info = 4; st->done = 1; }
+    st->lmpar_iter = 0; st->lmpar_done = 0; st->chol_fail = 0; st->par_cur = 0.0;
+}
+
+// After a factorisation + solve: eliminated-side parts of ||D p||^2 and of ||L^-1 D^2 p||^2
+// (the Newton-correction vector, still unscaled by 1/||D p||) and the failure flag.
+__global__ void __launch_bounds__(1024) k_lmpar_partial(LmDims d, LmState *st, const double *p_int, const double *w_int,
+                                                        const double *diag, const int32_t *i2p, double *scal) {
+    __shared__ double sh[32];
+    double dxE = 0.0, dxS = 0.0, wE = 0.0;
+    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
+        const double t = diag[i2p[q]] * p_int[q];
+        if (q < d.KE) { dxE += t * t; const double w = w_int[q]; wE += w * w; }
+        else dxS += t * t;
+    }
+    dxE = block_sum(dxE, sh); dxS = block_sum(dxS, sh); wE = block_sum(wE, sh);
     if (threadIdx.x == 0) {
-        st->dxnorm = st->chol_fail ? INFINITY : sqrt(a);
-        st->n_factor += 1;
+        scal[0] = dxE; scal[1] = st->chol_fail ? 1.0 : 0.0; scal[2] = wE;
+        st->part_s[0] = dxS;
     }
 }
 
 // lmpar step (MINPACK lmpar restated on the normal equations)
-__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int) {
+__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int, const double *scal) {
     __shared__ double sh[32];
     double a = 0.0;
-    for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
+    for (int q = d.KE + threadIdx.x; q < d.n; q += blockDim.x) {
         const double t = w_int[q];
         a += t * t;
     }
@@ -164,10 +202,14 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
     if (threadIdx.x != 0) return;
     const double p1 = 0.1, p001 = 0.001, dwarf = 2.2250738585072014e-308;
     const double delta = st->delta;
-    const bool fail = st->chol_fail != 0;
+    const bool fail = scal[1] > 0.0;  // a pivot <= 0 on any rank
     if (fail) st->chol_fail_total += 1;
     st->chol_fail = 0;
-    const double qn2 = a;
+    st->n_factor += 1;
+    const double dx2 = scal[0] + st->part_s[0];
+    st->dxnorm = fail ? INFINITY : sqrt(dx2);
+    // ||L^-1 (D^2 p / dxnorm)||^2: the solves ran without the 1/dxnorm factor
+    const double qn2 = (fail || !(dx2 > 0.0)) ? 0.0 : (scal[2] + a) / dx2;
     st->qnorm2 = qn2;
     if (st->lmpar_iter == 0) {
         // Gauss-Newton probe at par = 0
@@ -213,41 +255,41 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
     st->lmpar_iter += 1;
 }
 
-// trial point: x2 = x - p, pnorm = ||D p||, delta clamp on the first iteration
+// trial point: x2 = x - p; partial sums of pnorm^2 = ||D p||^2 and of ||D x2||^2
 __global__ void __launch_bounds__(1024) k_ctrl_trial(LmDims d, LmState *st, const double *p_int, const int32_t *i2p,
-                                                     const double *diag, const double *x, double *x2, double *p_par) {
+                                                     const double *diag, const double *x, double *x2, double *p_par,
+                                                     double *scal) {
     __shared__ double sh[32];
-    double a = 0.0;
+    double pE = 0.0, pS = 0.0, xE = 0.0, xS = 0.0;
     for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
         const int pid = i2p[q];
         const double step = -p_int[q];
         p_par[pid] = step;
-        x2[pid] = x[pid] + step;
-        const double t = diag[pid] * step;
-        a += t * t;
+        const double xn = x[pid] + step;
+        x2[pid] = xn;
+        const double t = diag[pid] * step, u = diag[pid] * xn;
+        if (q < d.KE) { pE += t * t; xE += u * u; } else { pS += t * t; xS += u * u; }
     }
-    a = block_sum(a, sh);
+    pE = block_sum(pE, sh); pS = block_sum(pS, sh); xE = block_sum(xE, sh); xS = block_sum(xS, sh);
     if (threadIdx.x == 0) {
-        st->pnorm = sqrt(a);
-        if (st->iter == 1) st->delta = fmin(st->delta, st->pnorm);
+        scal[0] = pE; scal[1] = xE;
+        st->part_s[0] = pS; st->part_s[1] = xS;
     }
 }
 
 // ratio test, delta / par update, accept / reject, convergence tests
 __global__ void __launch_bounds__(1024) k_ctrl_accept(LmDims d, LmState *st, const double *part_f, const double *part_jp,
-                                                      int nparts, const double *diag, const double *x2) {
+                                                      int nparts, const double *scal) {
     __shared__ double sh[32];
     const double ss1 = sum_partials(part_f, nparts, sh);
     const double jp2 = sum_partials(part_jp, nparts, sh);
-    double xs = 0.0;
-    for (int i = threadIdx.x; i < d.n; i += blockDim.x) {
-        const double t = diag[i] * x2[i];
-        xs += t * t;
-    }
-    xs = block_sum(xs, sh);
     if (threadIdx.x != 0) return;
     const double p1 = 0.1, p5 = 0.5, p25 = 0.25, p75 = 0.75, p0001 = 1e-4, epsmch = 2.220446049250313e-16;
-    const double fnorm = st->fnorm, fnorm1 = sqrt(ss1), pnorm = st->pnorm;
+    const double pnorm = sqrt(scal[0] + st->part_s[0]);
+    const double xs = scal[1] + st->part_s[1];
+    st->pnorm = pnorm;
+    if (st->iter == 1) st->delta = fmin(st->delta, pnorm);
+    const double fnorm = st->fnorm, fnorm1 = sqrt(ss1);
     st->fnorm1 = fnorm1;
     st->jp_sumsq = jp2;
     st->nfev += 1;
@@ -292,6 +334,7 @@ __global__ void __launch_bounds__(1024) k_ctrl_accept(LmDims d, LmState *st, con
     // next pass: a new Jacobian after an accepted step, else lmpar again
     st->need_jacobian = st->accepted;
     st->lmpar_iter = 0; st->lmpar_done = 0; st->par_cur = 0.0; st->chol_fail = 0;
+    (void)d;
 }
 
 __global__ void k_accept_copy(const LmState *st, size_t n, size_t m, size_t nobs, const double *x2, double *x,
@@ -304,12 +347,15 @@ __global__ void k_accept_copy(const LmState *st, size_t n, size_t m, size_t nobs
     }
 }
 
-// compute_error_stats (adjust_base.cpp:346-372): avg / min / max of finite distances
-__global__ void __launch_bounds__(1024) k_error_stats(LmState *st, const double *dist, int nobs) {
+// compute_error_stats (adjust_base.cpp:346-372): avg / min / max of finite distances.
+// Stage 1: per-block sum / min / max; stage 2 folds them into scal / mx (sum and count;
+// max and -min, so a sharded solve needs one sum and one max all-reduce); stage 3
+// writes LmState.
+__global__ void __launch_bounds__(256) k_error_stats_partial(const double *__restrict__ dist, int nobs, double *part) {
     __shared__ double sh[32];
-    __shared__ double smin[32], smax[32];
+    __shared__ double smin[8], smax[8];
     double a = 0.0, mn = 1.7976931348623157e308, mx = -0.0;
-    for (int i = threadIdx.x; i < nobs; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nobs; i += gridDim.x * blockDim.x) {
         const double e = dist[i];
         if (!isfinite(e)) continue;
         a += e; mn = fmin(mn, e); mx = fmax(mx, e);
@@ -323,8 +369,18 @@ __global__ void __launch_bounds__(1024) k_error_stats(LmState *st, const double 
     __syncthreads();
     if (threadIdx.x == 0) {
         for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { mn = fmin(mn, smin[w]); mx = fmax(mx, smax[w]); }
-        st->err_avg = a / (double)nobs; st->err_min = mn; st->err_max = mx;
+        part[3 * blockIdx.x] = a; part[3 * blockIdx.x + 1] = mn; part[3 * blockIdx.x + 2] = mx;
     }
+}
+__global__ void k_error_stats_fold(const double *part, int nparts, int nobs, double *scal, double *mxv) {
+    if (threadIdx.x != 0) return;
+    double a = 0.0, mn = 1.7976931348623157e308, mx = -0.0;
+    for (int b = 0; b < nparts; ++b) { a += part[3 * b]; mn = fmin(mn, part[3 * b + 1]); mx = fmax(mx, part[3 * b + 2]); }
+    scal[0] = a; scal[1] = (double)nobs;
+    mxv[0] = mx; mxv[1] = -mn;
+}
+__global__ void k_error_stats_final(LmState *st, const double *scal, const double *mxv) {
+    st->err_avg = scal[0] / scal[1]; st->err_max = mxv[0]; st->err_min = -mxv[1];
 }
 
 // ---- workspace ------------------------------------------------------------------------------
@@ -372,8 +428,13 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.alloc(&w->x2, (size_t)d.n));
     CKW(A.alloc(&w->fvec2, (size_t)d.m));
     CKW(A.alloc(&w->dist2, (size_t)d.nobs));
-    CKW(A.alloc(&w->part_f, (size_t)kRedBlocks));
-    CKW(A.alloc(&w->part_jp, (size_t)kRedBlocks));
+    CKW(A.alloc(&w->part_f, (size_t)2 * kRedBlocks + kRedScal + kRedMax));
+    w->part_jp = w->part_f + kRedBlocks;
+    w->scal = w->part_jp + kRedBlocks;
+    w->mx = w->scal + kRedScal;
+    CKW(A.alloc(&w->sdiag, (size_t)2 * std::max(d.ns, 1)));
+    CKW(A.alloc(&w->tvec, (size_t)std::max(d.ns, 1)));
+    CKW(A.alloc(&w->stat_part, (size_t)3 * kStatBlocks));
     w->gemv_chunks = std::max(1, std::min(64, d.KE / 256));
     CKW(A.alloc(&w->part_gemv, (size_t)w->gemv_chunks * d.NSP));
     CKW(cudaFuncSetAttribute(k_backward_s, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * (64 * kDS + 64 + 32 * 64)));
@@ -399,12 +460,35 @@ static mmb_status read_state(DeviceProblem *p) {
     return MMB_OK;
 }
 
+// the exchange step of a sharded solve: in-place sum (or max) over the ranks; nothing to do
+// for an unsharded handle
+static mmb_status all_reduce(DeviceProblem *p, double *buf, size_t count, bool is_max = false) {
+    if (!p->comm || p->comm->world == 1 || count == 0) return MMB_OK;
+    ++p->lm->n_allreduce;
+    return p->comm->allreduce(buf, count, is_max, p->stream);
+}
+
 static mmb_status enqueue_residual_eval(DeviceProblem *p, const double *d_x, double *d_f, double *d_dist) {
     LmWorkspace *w = p->lm;
     mmb_status st;
     if ((st = launch_variants(p, d_x, false)) != MMB_OK) return st;
     if ((st = launch_residuals(p, d_f, d_dist)) != MMB_OK) return st;
     k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(d_f, (size_t)p->hp.m, w->part_f);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
+// avg / min / max of `dist` over every shard -> LmState err_*
+static mmb_status enqueue_error_stats(DeviceProblem *p, const double *dist) {
+    LmWorkspace *w = p->lm;
+    mmb_status st;
+    k_error_stats_partial<<<kStatBlocks, 256, 0, p->stream>>>(dist, p->hp.nobs, w->stat_part);
+    LAUNCH_CHECK();
+    k_error_stats_fold<<<1, 32, 0, p->stream>>>(w->stat_part, kStatBlocks, p->hp.nobs, w->scal, w->mx);
+    LAUNCH_CHECK();
+    if ((st = all_reduce(p, w->scal, 2)) != MMB_OK) return st;
+    if ((st = all_reduce(p, w->mx, 2, true)) != MMB_OK) return st;
+    k_error_stats_final<<<1, 1, 0, p->stream>>>(w->st, w->scal, w->mx);
     LAUNCH_CHECK();
     return MMB_OK;
 }
@@ -423,7 +507,16 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     MMB_CUDA_CHECK(cudaMemsetAsync(w->V, 0, sizeof(double) * (size_t)d.NSP * d.NSP, p->stream));
     k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->U, w->gE, w->W, w->V);
     LAUNCH_CHECK();
-    k_ctrl_prep<<<1, 1024, 0, p->stream>>>(d, w->st, w->U, w->gE, w->V, w->i2p, p->d_x, w->diag, w->acnorm);
+    if (d.ns) {
+        k_prep_gather<<<(d.ns + 255) / 256, 256, 0, p->stream>>>(d, w->V, w->sdiag);
+        LAUNCH_CHECK();
+        if ((st = all_reduce(p, w->sdiag, (size_t)2 * d.ns)) != MMB_OK) return st;
+    }
+    k_ctrl_prep<<<1, 1024, 0, p->stream>>>(d, w->st, w->U, w->gE, w->sdiag, w->i2p, p->d_x, w->diag, w->acnorm, w->scal, w->mx);
+    LAUNCH_CHECK();
+    if ((st = all_reduce(p, w->scal, 2)) != MMB_OK) return st;
+    if ((st = all_reduce(p, w->mx, 1, true)) != MMB_OK) return st;
+    k_ctrl_prep_decide<<<1, 1, 0, p->stream>>>(w->st, w->scal, w->mx);
     LAUNCH_CHECK();
     return MMB_OK;
 }
@@ -433,6 +526,8 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     const LmDims &d = w->d;
     cudaStream_t s = p->stream;
+    const bool sharded = p->comm && p->comm->world > 1;
+    mmb_status rs;
     if (w->profile) cudaEventRecord(w->ev[0], s);
     if (d.KE) {
         const size_t sm = sizeof(double) * ((size_t)d.na * d.na + d.na);
@@ -441,7 +536,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     {
         const size_t tot = (size_t)d.NSP * d.NSP;
-        k_schur_init<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(d, w->st, w->V, w->diag, w->i2p, w->S);
+        k_schur_init<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(d, w->st, w->V, w->diag, w->i2p, w->S, sharded ? 0 : 1);
         LAUNCH_CHECK();
     }
     const int nb = d.NSP / 64;
@@ -450,6 +545,13 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         int ksplit = 1;
         while (tiles * ksplit < 296 && ksplit < 16 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
         k_schur_syrk<<<dim3(tiles, ksplit), 128, 0, s>>>(d, w->Y, w->S);
+        LAUNCH_CHECK();
+    }
+    if (sharded) {
+        // the one data-path collective of the solve: rows 0..ns of the reduced system
+        // (lower triangle + right-hand side row), summed over the frame shards
+        if ((rs = all_reduce(p, w->S, (size_t)(d.ns + 1) * d.NSP)) != MMB_OK) return rs;
+        k_schur_damp<<<(d.NSP + 255) / 256, 256, 0, s>>>(d, w->st, w->diag, w->i2p, w->S);
         LAUNCH_CHECK();
     }
     if (w->profile) cudaEventRecord(w->ev[1], s);
@@ -467,23 +569,31 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
         LAUNCH_CHECK();
     }
-    k_dxnorm<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->diag, w->i2p);
-    LAUNCH_CHECK();
     if (w->profile) cudaEventRecord(w->ev[3], s);
-    // Newton correction: w = L^-1 (D^2 p / dxnorm)
+    // Newton correction: w = L^-1 D^2 p (scaled by 1/||D p|| in k_ctrl_lmpar)
     if (d.KE) {
-        k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->st, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
+        k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
         LAUNCH_CHECK();
-        k_gemv_t_partial<<<dim3((d.ns + 127) / 128 > 0 ? (d.ns + 127) / 128 : 1, w->gemv_chunks), 128, 0, s>>>(d, w->Y, w->w_int, w->part_gemv);
-        LAUNCH_CHECK();
+        if (d.ns) {
+            k_gemv_t_partial<<<dim3((d.ns + 127) / 128, w->gemv_chunks), 128, 0, s>>>(d, w->Y, w->w_int, w->part_gemv);
+            LAUNCH_CHECK();
+        }
     }
     if (d.ns) {
-        k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->st, d.KE ? w->gemv_chunks : 0, w->part_gemv, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
+        k_gemv_fold<<<(d.ns + 127) / 128, 128, 0, s>>>(d, d.KE ? w->gemv_chunks : 0, w->part_gemv, w->tvec);
+        LAUNCH_CHECK();
+    }
+    k_lmpar_partial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->w_int, w->diag, w->i2p, w->scal);
+    LAUNCH_CHECK();
+    if ((rs = all_reduce(p, w->scal, 3)) != MMB_OK) return rs;
+    if (d.ns) {
+        if ((rs = all_reduce(p, w->tvec, (size_t)d.ns)) != MMB_OK) return rs;
+        k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->tvec, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
         LAUNCH_CHECK();
         k_forward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64), s>>>(d, w->S, w->w_int + d.KE, w->w_int + d.KE);
         LAUNCH_CHECK();
     }
-    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int);
+    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal);
     LAUNCH_CHECK();
     if (w->profile) {
         cudaEventRecord(w->ev[4], s);
@@ -498,13 +608,15 @@ static mmb_status enqueue_trial(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     const LmDims &d = w->d;
     cudaStream_t s = p->stream;
-    k_ctrl_trial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->i2p, w->diag, p->d_x, w->x2, w->p_par);
+    k_ctrl_trial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->i2p, w->diag, p->d_x, w->x2, w->p_par, w->scal);
     LAUNCH_CHECK();
     mmb_status st = enqueue_residual_eval(p, w->x2, w->fvec2, w->dist2);
     if (st != MMB_OK) return st;
     k_jp_partial<<<kRedBlocks, 256, 0, s>>>(p->ds, d, p->d_jac, w->p_par, w->part_jp);
     LAUNCH_CHECK();
-    k_ctrl_accept<<<1, 1024, 0, s>>>(d, w->st, w->part_f, w->part_jp, kRedBlocks, w->diag, w->x2);
+    // squared norms of the trial residual and of J p, ||D p||^2, ||D x2||^2: one all-reduce
+    if ((st = all_reduce(p, w->part_f, (size_t)2 * kRedBlocks + 2)) != MMB_OK) return st;
+    k_ctrl_accept<<<1, 1024, 0, s>>>(d, w->st, w->part_f, w->part_jp, kRedBlocks, w->scal);
     LAUNCH_CHECK();
     k_accept_copy<<<296, 256, 0, s>>>(w->st, (size_t)d.n, (size_t)d.m, (size_t)d.nobs, w->x2, p->d_x, w->fvec2, p->d_fvec, w->dist2, p->d_dist);
     LAUNCH_CHECK();
@@ -559,14 +671,14 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     if (hp.opt.accept_only_better) {
         if ((st = launch_variants(p, nullptr, false)) != MMB_OK) return st;
         if ((st = launch_residuals(p, p->d_fvec, p->d_dist)) != MMB_OK) return st;
-        k_error_stats<<<1, 1024, 0, p->stream>>>(w->st, p->d_dist, hp.nobs);
-        LAUNCH_CHECK();
+        if ((st = enqueue_error_stats(p, p->d_dist)) != MMB_OK) return st;
         if ((st = read_state(p)) != MMB_OK) return st;
         init_avg = w->h_st->err_avg;
     }
     // first function evaluation
     auto t0 = clk::now();
     if ((st = enqueue_residual_eval(p, p->d_x, p->d_fvec, p->d_dist)) != MMB_OK) return st;
+    if ((st = all_reduce(p, w->part_f, kRedBlocks)) != MMB_OK) return st;
     k_ctrl_init<<<1, 1024, 0, p->stream>>>(w->st, w->part_f, kRedBlocks);
     LAUNCH_CHECK();
     if ((st = read_state(p)) != MMB_OK) return st;
@@ -599,12 +711,12 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
         ++func_evals;
     }
     // results (adjust_cminpack_lmder.cpp:185-197, adjust_base.cpp:1201-1282)
-    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)hp.m, w->part_f);
-    LAUNCH_CHECK();
     // errorDistanceList holds whatever the LAST measureErrors call left there (a
     // rejected trial or the last FD perturbation included): dist2 tracks that.
-    k_error_stats<<<1, 1024, 0, p->stream>>>(w->st, w->dist2, hp.nobs);
+    if ((st = enqueue_error_stats(p, w->dist2)) != MMB_OK) return st;
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)hp.m, w->part_f);
     LAUNCH_CHECK();
+    if ((st = all_reduce(p, w->part_f, kRedBlocks)) != MMB_OK) return st;
     std::vector<double> part(kRedBlocks), x(hp.n);
     MMB_CUDA_CHECK(cudaMemcpyAsync(part.data(), w->part_f, sizeof(double) * kRedBlocks, cudaMemcpyDeviceToHost, p->stream));
     MMB_CUDA_CHECK(cudaMemcpyAsync(x.data(), p->d_x, sizeof(double) * hp.n, cudaMemcpyDeviceToHost, p->stream));

@@ -206,10 +206,12 @@ __global__ void __launch_bounds__(128) k_block_factor(LmDims d, LmState *st, con
     }
 }
 
-// S = V (lower, incl. rhs row ns) + par D_S^2 on the diagonal; padding = identity
+// S = V (lower, incl. rhs row ns) + par D_S^2 on the diagonal; padding = identity.
+// damp = 0 (sharded solve): the shard's part of V only; the damping and the padding
+// diagonal are applied by k_schur_damp after the all-reduce of S.
 __global__ void k_schur_init(LmDims d, const LmState *st, const double *__restrict__ V,
                              const double *__restrict__ diag, const int32_t *__restrict__ i2p,
-                             double *__restrict__ S) {
+                             double *__restrict__ S, int damp) {
     const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (t >= (size_t)d.NSP * d.NSP) return;
     const int r = (int)(t / d.NSP), c = (int)(t - (size_t)r * d.NSP);
@@ -218,11 +220,21 @@ __global__ void k_schur_init(LmDims d, const LmState *st, const double *__restri
     if (r == c) {
         if (r < d.ns) {
             const double dd = diag[i2p[d.KE + r]];
-            v += st->par_cur * dd * dd;
+            if (damp) v += st->par_cur * dd * dd;
         } else if (r == d.ns) v = 0.0;  // augmented pivot: unused
-        else v = 1.0;
+        else v = damp ? 1.0 : 0.0;
     }
     S[t] = v;
+}
+__global__ void k_schur_damp(LmDims d, const LmState *st, const double *__restrict__ diag,
+                             const int32_t *__restrict__ i2p, double *__restrict__ S) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= d.NSP) return;
+    double *s = &S[(size_t)r * d.NSP + r];
+    if (r < d.ns) {
+        const double dd = diag[i2p[d.KE + r]];
+        *s += st->par_cur * dd * dd;
+    } else *s = (r == d.ns) ? 0.0 : 1.0;
 }
 
 // ---- DMMA helpers ------------------------------------------------------------------
@@ -574,18 +586,18 @@ __global__ void __launch_bounds__(128) k_backsolve_e(LmDims d, const double *__r
     }
 }
 
-// w_f = L_f^-1 q_f with q = D^2 p / dxnorm (internal order); one thread per frame.
-__global__ void k_qsolve_e(LmDims d, const LmState *st, const double *__restrict__ Lf, const double *__restrict__ p_int,
+// w_f = L_f^-1 q_f with q = D^2 p (internal order; the 1/||D p|| factor of lmpar's Newton
+// correction is applied to the squared norm at the end); one thread per frame.
+__global__ void k_qsolve_e(LmDims d, const double *__restrict__ Lf, const double *__restrict__ p_int,
                            const double *__restrict__ diag, const int32_t *__restrict__ i2p, double *__restrict__ w_int) {
     const int f = blockIdx.x * blockDim.x + threadIdx.x;
     if (f >= d.F) return;
     const int na = d.na;
     const double *L = Lf + (size_t)f * na * na;
     double w[kMaxNA];
-    const double inv = 1.0 / st->dxnorm;
     for (int a = 0; a < na; ++a) {
         const double dd = diag[i2p[f * na + a]];
-        double v = dd * dd * p_int[(size_t)f * na + a] * inv;
+        double v = dd * dd * p_int[(size_t)f * na + a];
         for (int c = 0; c < a; ++c) v -= L[a * na + c] * w[c];
         w[a] = v / L[a * na + a];
     }
@@ -604,16 +616,21 @@ __global__ void __launch_bounds__(128) k_gemv_t_partial(LmDims d, const double *
     partial[(size_t)blockIdx.y * d.NSP + j] = acc;
 }
 
-// b_S[j] = D_j^2 p_j / dxnorm - sum_chunks partial[chunk][j]
-__global__ void k_qrhs_s(LmDims d, const LmState *st, int nchunks, const double *__restrict__ partial,
-                         const double *__restrict__ p_int, const double *__restrict__ diag,
-                         const int32_t *__restrict__ i2p, double *__restrict__ b) {
+// tvec[j] = sum_chunks partial[chunk][j]  (= (Y^T w_E)[j] of this shard)
+__global__ void k_gemv_fold(LmDims d, int nchunks, const double *__restrict__ partial, double *__restrict__ tvec) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= d.ns) return;
+    double v = 0.0;
+    for (int c = 0; c < nchunks; ++c) v += partial[(size_t)c * d.NSP + j];
+    tvec[j] = v;
+}
+// b_S[j] = D_j^2 p_j - (Y^T w_E)[j]
+__global__ void k_qrhs_s(LmDims d, const double *__restrict__ tvec, const double *__restrict__ p_int,
+                         const double *__restrict__ diag, const int32_t *__restrict__ i2p, double *__restrict__ b) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= d.ns) return;
     const double dd = diag[i2p[d.KE + j]];
-    double v = dd * dd * p_int[d.KE + j] / st->dxnorm;
-    for (int c = 0; c < nchunks; ++c) v -= partial[(size_t)c * d.NSP + j];
-    b[j] = v;
+    b[j] = dd * dd * p_int[d.KE + j] - tvec[j];
 }
 
 }  // namespace mmb

@@ -13,6 +13,7 @@
 #include <cstring>
 
 #include "lm.h"
+#include "shard.h"
 #include "reduce.cuh"
 
 namespace mmb {
@@ -440,31 +441,21 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     MMB_CUDA_CHECK(cudaMemcpyAsync(x.data(), p->d_x, sizeof(double) * hp.n, cudaMemcpyDeviceToHost, p->stream));
     if (dist_out) MMB_CUDA_CHECK(cudaMemcpyAsync(dist_out, d_d2, sizeof(double) * hp.nobs, cudaMemcpyDeviceToHost, p->stream));
     MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
-    // CommandResult::add / divide (adjust_results.h:89-117)
-    res->success = 1;
-    res->error_min = 1.7976931348623157e308; res->error_max = -0.0;
-    int better_all = 1;
+    // per-frame results, then CommandResult::add / divide (adjust_results.h:89-117)
+    std::vector<mmb_result> per(hp.F);
     for (int f = 0; f < hp.F; ++f) {
         const PfFrameResult &r = fr[f];
-        const int ok = (r.info != -100 && r.func_evals > 0) ? 1 : 0;
-        res->success = std::min(res->success, ok);
-        res->error_final += r.fnorm; res->error_avg += r.err_avg;
-        res->error_min = std::min(res->error_min, r.err_min); res->error_max = std::max(res->error_max, r.err_max);
-        res->iteration_num += r.nfev; res->iteration_function_num += r.func_evals;
-        res->iteration_jacobian_num += r.njev * hp.na * (hp.opt.auto_diff_type == 1 ? 2 : 1);
-        res->iteration_attempt_num += r.njev;
-        res->reason_num = r.info;
-        better_all = std::min(better_all, r.better);
-        if (per_frame_out) {
-            mmb_result &o = per_frame_out[f];
-            std::memset(&o, 0, sizeof(o));
-            o.success = ok; o.reason_num = r.info; o.error_final = r.fnorm; o.error_avg = r.err_avg;
-            o.error_min = r.err_min; o.error_max = r.err_max; o.iteration_num = r.nfev;
-            o.iteration_function_num = r.func_evals; o.iteration_attempt_num = r.njev; o.error_is_better = r.better;
-        }
+        mmb_result &o = per[f];
+        std::memset(&o, 0, sizeof(o));
+        o.success = (r.info != -100 && r.func_evals > 0) ? 1 : 0;
+        o.reason_num = r.info; o.error_final = r.fnorm; o.error_avg = r.err_avg;
+        o.error_min = r.err_min; o.error_max = r.err_max; o.iteration_num = r.nfev;
+        o.iteration_function_num = r.func_evals;
+        o.iteration_jacobian_num = r.njev * hp.na * (hp.opt.auto_diff_type == 1 ? 2 : 1);
+        o.iteration_attempt_num = r.njev; o.error_is_better = r.better;
     }
-    if (hp.F > 1) { res->error_final /= hp.F; res->error_avg /= hp.F; }
-    res->error_is_better = better_all;
+    aggregate_results(per.data(), hp.F, res);
+    if (per_frame_out) std::memcpy(per_frame_out, per.data(), sizeof(mmb_result) * hp.F);
     for (int i = 0; i < hp.n; ++i) {
         const int at = hp.par_attr[i], f = hp.par_frame[i];
         if (x_out) x_out[i] = x[i];

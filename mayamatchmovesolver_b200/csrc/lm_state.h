@@ -30,6 +30,8 @@ struct LmState {
     int lmpar_done;
     int chol_fail;          // a pivot was <= 0 in the current factorisation
     int chol_fail_total;
+    // reduced-side (replicated) parts of sums whose eliminated-side parts are all-reduced
+    double part_s[4];
     // statistics
     int n_factor;
     double err_avg, err_min, err_max;  // compute_error_stats (adjust_base.cpp:346)

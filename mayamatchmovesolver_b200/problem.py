@@ -20,6 +20,42 @@ def default_options(**overrides):
     return o
 
 
+def shard_frames(num_frames, world, rank):
+    lib = _capi.load()
+    f0, f1 = C.c_int32(), C.c_int32()
+    check(lib.mmb_shard_frames(int(num_frames), int(world), int(rank), C.byref(f0), C.byref(f1)), "mmb_shard_frames")
+    return f0.value, f1.value
+
+
+def shard_param_map(scene, world, rank):
+    """unsharded parameter id of every parameter of rank's shard (host only, no GPU)"""
+    lib = _capi.load()
+    desc, keep = scene.desc()
+    n = C.c_int32()
+    check(lib.mmb_shard_param_map(C.byref(desc), int(world), int(rank), C.byref(n), None), "mmb_shard_param_map")
+    out = np.zeros(n.value, np.int32)
+    check(lib.mmb_shard_param_map(C.byref(desc), int(world), int(rank), C.byref(n), out.ctypes.data_as(c_i32p)),
+          "mmb_shard_param_map")
+    return out
+
+
+def comm_unique_id(local_backend=False):
+    """128 bytes: an ncclUniqueId (or the id of an in-process group for single-GPU tests)"""
+    lib = _capi.load()
+    buf = (C.c_uint8 * _capi.MMB_COMM_ID_BYTES)()
+    check(lib.mmb_comm_unique_id(buf, 1 if local_backend else 0), "mmb_comm_unique_id")
+    return bytes(buf)
+
+
+def aggregate_results(results):
+    """CommandResult::add / divide over per-frame mmb_result records"""
+    lib = _capi.load()
+    arr = (Result * len(results))(*results)
+    out = Result()
+    check(lib.mmb_aggregate_results(arr, len(results), C.byref(out)), "mmb_aggregate_results")
+    return out
+
+
 class SolveResult:
     """Field names follow SolverResult / ErrorMetricsResult (adjust_results.h:119-286)."""
 
@@ -42,6 +78,7 @@ class SolveResult:
         self.x = x
         self.attr_values = attr_values
         self.error_dist = error_dist
+        self.raw = r
 
     def __repr__(self):
         return ("SolveResult(success=%s reason=%d nfev=%d err_final=%.6g avg=%.6g max=%.6g)" %
@@ -49,15 +86,33 @@ class SolveResult:
                  self.error_max))
 
 
+def _copy_result(r):
+    o = Result()
+    C.memmove(C.byref(o), C.byref(r), C.sizeof(Result))
+    return o
+
+
 class Problem:
-    def __init__(self, scene, options=None, **opt_overrides):
+    def __init__(self, scene, options=None, shard=None, **opt_overrides):
+        """shard = (rank, world): the handle covers this rank's frame range of `scene`
+        (mmb_problem_create_shard); parameters and observations are then numbered locally."""
         self._lib = _capi.load()
         self.options = options if options is not None else default_options(**opt_overrides)
         desc, keep = scene.desc()
         self.num_frames = int(desc.num_frames)
+        self.frame_begin, self.shard = 0, None
         self._h = C.c_void_p()
-        check(self._lib.mmb_problem_create(C.byref(desc), C.byref(self.options), C.byref(self._h)),
-              "mmb_problem_create")
+        if shard is None:
+            check(self._lib.mmb_problem_create(C.byref(desc), C.byref(self.options), C.byref(self._h)),
+                  "mmb_problem_create")
+        else:
+            rank, world = int(shard[0]), int(shard[1])
+            f0, f1 = shard_frames(self.num_frames, world, rank)
+            check(self._lib.mmb_problem_create_shard(C.byref(desc), C.byref(self.options), rank, world,
+                                                     C.byref(self._h)), "mmb_problem_create_shard")
+            self.shard = (rank, world)
+            self.frame_begin, self.num_frames = f0, f1 - f0
+            self.param_map = shard_param_map(scene, world, rank)
         n, nobs, m = C.c_int32(), C.c_int32(), C.c_int32()
         check(self._lib.mmb_problem_sizes(self._h, C.byref(n), C.byref(nobs), C.byref(m)), "mmb_problem_sizes")
         self.n, self.nobs, self.m = n.value, nobs.value, m.value
@@ -145,7 +200,13 @@ class Problem:
         check(self._lib.mmb_solve_per_frame(self._h, C.byref(r), per, x.ctypes.data_as(c_f64p),
                                             av.ctypes.data_as(c_f64p), dist.ctypes.data_as(c_f64p)),
               "mmb_solve_per_frame")
-        return SolveResult(r, x, av, dist), [SolveResult(per[f], None, None, None) for f in range(F)]
+        return SolveResult(r, x, av, dist), [SolveResult(_copy_result(per[f]), None, None, None) for f in range(F)]
+
+    def attach_comm(self, comm_id, rank, world):
+        """collective over the ranks of `comm_id` (bytes from comm_unique_id): mmb_solve on this
+        handle becomes the sharded global solve"""
+        buf = (C.c_uint8 * _capi.MMB_COMM_ID_BYTES).from_buffer_copy(bytes(comm_id))
+        check(self._lib.mmb_problem_attach_comm(self._h, buf, int(rank), int(world)), "mmb_problem_attach_comm")
 
     def request_cancel(self):
         self._lib.mmb_request_cancel(self._h)

@@ -1,0 +1,90 @@
+"""Worker of the multi-process tests (one process per rank, torch.distributed).
+
+  cpu : gloo, world 2 -- host logic of the sharded path, no GPU
+  gpu : nccl, one GPU per rank -- sharded global solve (NCCL all-reduce of the reduced
+        system) and sharded per-frame solve against the unsharded solve on rank 0
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from mayamatchmovesolver_b200 import _capi, synth  # noqa: E402
+from mayamatchmovesolver_b200.distributed import (TorchGroup, merge_shard_vectors, solve_global_sharded,  # noqa: E402
+                                                  solve_per_frame_sharded)
+from mayamatchmovesolver_b200.problem import Problem, aggregate_results, shard_frames, shard_param_map  # noqa: E402
+
+
+def cpu_mode():
+    dist.init_process_group("gloo")
+    g = TorchGroup()
+    F, B = 13, 5
+    sb, _ = synth.make_scene(F, B, seed=11)
+    n = 6 * F + 3 * B
+    f0, f1 = shard_frames(F, g.world, g.rank)
+    m = shard_param_map(sb, g.world, g.rank)
+    # every rank "solves" x[global id] = 10 * id on its shard
+    parts = g.allgather(dict(map=m, x=10.0 * m, f0=f0))
+    parts.sort(key=lambda d: d["f0"])
+    x = merge_shard_vectors(n, [d["map"] for d in parts], [d["x"] for d in parts])
+    np.testing.assert_array_equal(x, 10.0 * np.arange(n))
+    # per-frame records: frame f has error_final = f + 1
+    mine = []
+    for f in range(f0, f1):
+        r = _capi.Result()
+        r.success, r.error_final, r.error_avg, r.error_min, r.error_max, r.iteration_num = 1, f + 1.0, 2.0 * f, f, f, 1
+        r.error_is_better = 1
+        mine.append(tuple(getattr(r, k) for k, _ in _capi.Result._fields_ if k != "reason_str"))
+    gathered = [t for part in g.allgather(mine) for t in part]
+    recs = []
+    for t in gathered:
+        r = _capi.Result()
+        for (k, v) in zip([k for k, _ in _capi.Result._fields_ if k != "reason_str"], t):
+            setattr(r, k, v)
+        recs.append(r)
+    a = aggregate_results(recs)
+    assert a.iteration_num == F and abs(a.error_final - (F + 1) / 2.0) < 1e-12 and a.error_max == F - 1
+    # the communicator id travels as bytes
+    cid = g.broadcast_bytes(bytes(range(128)) if g.rank == 0 else None)
+    assert cid == bytes(range(128))
+    print("rank %d ok" % g.rank)
+    dist.destroy_process_group()
+
+
+def gpu_mode():
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    g = TorchGroup()
+    # global solve, gauge-fixed so the solved values are determined
+    sb, _ = synth.make_scene(F=24, B=20, seed=21, fixed_bundles=4, period=24)
+    r = solve_global_sharded(sb, g, device=local)
+    sb2, _ = synth.make_scene(F=30, B=16, seed=22, solve_bundles=False, period=30)
+    rp, per = solve_per_frame_sharded(sb2, g, device=local)
+    if g.rank == 0:
+        with Problem(sb, device=local) as p:
+            r1 = p.solve()
+        assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (r1.reason_num, r1.iteration_num, r1.iteration_attempt_num), (r, r1)
+        scale = np.maximum(np.abs(r1.attr_values), 1.0)
+        assert np.max(np.abs(r.attr_values - r1.attr_values) / scale) <= 1e-6
+        assert np.max(np.abs(r.error_dist - r1.error_dist)) <= 1e-5
+        assert abs(r.error_final - r1.error_final) <= 1e-6 * r1.error_final
+        with Problem(sb2, device=local, frame_solve_mode=1) as p:
+            q1, per1 = p.solve_per_frame()
+        np.testing.assert_array_equal(rp.attr_values, q1.attr_values)  # independent solves: identical
+        np.testing.assert_array_equal(rp.error_dist, q1.error_dist)
+        assert [x.iteration_num for x in per] == [x.iteration_num for x in per1]
+        assert abs(rp.error_final - q1.error_final) <= 1e-12 * q1.error_final and rp.iteration_num == q1.iteration_num
+    print("rank %d ok" % g.rank)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    cpu_mode() if sys.argv[1] == "cpu" else gpu_mode()
