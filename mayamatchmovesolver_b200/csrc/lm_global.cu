@@ -45,6 +45,9 @@ struct LmWorkspace {
     double *part_gemv = nullptr;                      // [chunks * NSP]
     int gemv_chunks = 1;
     long long n_allreduce = 0;
+    int *wave_flags = nullptr;   // [NSP / 64] epoch flags of the wavefront triangular solves
+    int wave_epoch = 0;
+    bool wave_ok = false;        // every block of the wavefront kernels fits on the device at once
     double init_avg = 0, init_min = 0, init_max = 0;
     // optional phase timing (MMB_LM_PROFILE=1): schur, cholesky, back-substitution, q-solve
     bool profile = false;
@@ -437,8 +440,22 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.alloc(&w->stat_part, (size_t)3 * kStatBlocks));
     w->gemv_chunks = std::max(1, std::min(64, d.KE / 256));
     CKW(A.alloc(&w->part_gemv, (size_t)w->gemv_chunks * d.NSP));
+    CKW(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholPanelSmem));
     CKW(cudaFuncSetAttribute(k_backward_s, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * (64 * kDS + 64 + 32 * 64)));
-    CKW(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 64 * kCS * (int)sizeof(double)));
+    {
+        const int nblk = std::max(1, (d.ns + kNB - 1) / kNB);
+        CKW(A.alloc(&w->wave_flags, (size_t)d.NSP / 64 + 1));
+        CKW(cudaMemset(w->wave_flags, 0, sizeof(int) * ((size_t)d.NSP / 64 + 1)));
+        CKW(cudaFuncSetAttribute(k_backward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemBwd));
+        CKW(cudaFuncSetAttribute(k_forward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemFwd));
+        int coop = 0, sms = 0, occ_b = 0, occ_f = 0;
+        CKW(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, p->device));
+        CKW(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device));
+        CKW(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_b, k_backward_wave, 256, kWaveSmemBwd));
+        CKW(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_f, k_forward_wave, 256, kWaveSmemFwd));
+        const char *e = getenv("MMB_WAVE");
+        w->wave_ok = coop && nblk <= sms * std::min(occ_b, occ_f) && !(e && atoi(e) == 0);
+    }
 #undef CKW
     w->profile = getenv("MMB_LM_PROFILE") != nullptr;
     if (w->profile) for (auto &e : w->ev) cudaEventCreate(&e);
@@ -521,6 +538,43 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     return MMB_OK;
 }
 
+// triangular solves with the factor of the reduced system
+static mmb_status enqueue_backward_s(DeviceProblem *p, double *pS) {
+    LmWorkspace *w = p->lm;
+    LmDims d = w->d;
+    if (w->wave_ok && d.ns > 0) {
+        const int nblk = (d.ns + kNB - 1) / kNB;
+        int epoch = ++w->wave_epoch;
+        const double *S = w->S;
+        int *flags = w->wave_flags;
+        void *args[] = {&d, &S, &pS, &flags, &epoch};
+        MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_backward_wave, dim3(nblk), dim3(256), args, kWaveSmemBwd, p->stream));
+        ++p->launches;
+        return MMB_OK;
+    }
+    k_backward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64 + 32 * 64), p->stream>>>(d, w->S, pS);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+static mmb_status enqueue_forward_s(DeviceProblem *p, double *wS) {
+    LmWorkspace *w = p->lm;
+    LmDims d = w->d;
+    if (w->wave_ok && d.ns > 0) {
+        const int nblk = (d.ns + kNB - 1) / kNB;
+        int epoch = ++w->wave_epoch;
+        const double *S = w->S;
+        const double *rhs = wS;
+        int *flags = w->wave_flags;
+        void *args[] = {&d, &S, &rhs, &wS, &flags, &epoch};
+        MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_forward_wave, dim3(nblk), dim3(256), args, kWaveSmemFwd, p->stream));
+        ++p->launches;
+        return MMB_OK;
+    }
+    k_forward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64), p->stream>>>(d, w->S, wS, wS);
+    LAUNCH_CHECK();
+    return MMB_OK;
+}
+
 // one factorisation + solve + Newton-correction solve at st->par_cur, then the lmpar control step
 static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
@@ -556,15 +610,14 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     if (w->profile) cudaEventRecord(w->ev[1], s);
     for (int kb = 0; kb < nb; ++kb) {
-        k_chol_panel<<<nb - kb, 256, 2 * 64 * kCS * sizeof(double), s>>>(d, kb, w->st, w->S, w->Ld);
+        k_chol_panel<<<nb - kb, 256, kCholPanelSmem, s>>>(d, kb, w->st, w->S, w->Ld);
         LAUNCH_CHECK();
         const int nt = nb - kb - 1;
         k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
         LAUNCH_CHECK();
     }
     if (w->profile) cudaEventRecord(w->ev[2], s);
-    k_backward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64 + 32 * 64), s>>>(d, w->S, w->p_int + d.KE);
-    LAUNCH_CHECK();
+    if ((rs = enqueue_backward_s(p, w->p_int + d.KE)) != MMB_OK) return rs;
     if (d.KE) {
         k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
         LAUNCH_CHECK();
@@ -590,8 +643,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         if ((rs = all_reduce(p, w->tvec, (size_t)d.ns)) != MMB_OK) return rs;
         k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->tvec, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
         LAUNCH_CHECK();
-        k_forward_s<<<1, 1024, sizeof(double) * (64 * kDS + 64), s>>>(d, w->S, w->w_int + d.KE, w->w_int + d.KE);
-        LAUNCH_CHECK();
+        if ((rs = enqueue_forward_s(p, w->w_int + d.KE)) != MMB_OK) return rs;
     }
     k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal);
     LAUNCH_CHECK();

@@ -350,72 +350,162 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
 }
 
 // ---- blocked Cholesky of S (lower, row-major, ld = NSP) ----------------------------
-// Step kb, kernel 1: every CTA factors the diagonal block redundantly in shared
-// memory; CTA 0 stores it to `Ld`; CTA r>0 solves its 64-row panel block
-// X = A_ik L_kk^-T in place.  The pivot of the augmented row (global index ns)
-// is skipped: that row is the right-hand side being forward-solved.
-constexpr int kCS = 65;  // shared stride for 64x64 tiles in the panel kernel
+// sqrt(x) and 1/sqrt(x) from the hardware seed (~22 bits) + two Newton steps + one
+// correction each (<= 1-2 ulp): the IEEE sqrt and division sequences would sit on the
+// critical path of every pivot.
+__device__ __forceinline__ void sqrt_rsqrt(double x, double &s, double &inv) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double h = 0.5 * x;
+    double e = fma(-h * y, y, 0.5);
+    y = fma(y, e, y);
+    e = fma(-h * y, y, 0.5);
+    y = fma(y, e, y);
+    s = x * y;
+    s = fma(0.5 * y, fma(-s, s, x), s);
+    inv = fma(y, fma(-s, y, 1.0), y);
+}
+
+// Cholesky of an 8x8 block held in registers (lower part of a[i][j]); g0 = global index of
+// its first row.  The augmented row (global index ns) gets no pivot.
+__device__ __forceinline__ void chol8_regs(double (&a)[8][8], double (&dinv)[8], int g0, int ns, int &fail) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        double sq = 1.0, inv = 1.0;
+        const double pv = a[j][j];
+        if (g0 + j != ns) {
+            if (!(pv > 1e-290)) fail = 1;
+            else sqrt_rsqrt(pv, sq, inv);
+        }
+        a[j][j] = sq;
+        dinv[j] = inv;
+#pragma unroll
+        for (int i = j + 1; i < 8; ++i) a[i][j] *= inv;
+#pragma unroll
+        for (int c = j + 1; c < 8; ++c)
+#pragma unroll
+            for (int i = c; i < 8; ++i) a[i][c] = fma(-a[i][j], a[c][j], a[i][c]);
+    }
+}
+
+// Step kb, kernel 1 (256 threads per CTA), 8x8 sub-blocking inside the 64x64 blocks:
+// every CTA factors the diagonal block in shared memory (redundantly: the factorisation
+// is the sequential part of the step, repeating it costs no time) -- per sub-block column
+// every thread factors the 8x8 pivot block in registers, the rows below are solved one per
+// thread and the trailing part is updated by all threads: two barriers per 8 pivots.
+// CTA 0 stores the factor to `Ld`; CTA r > 0 then solves its 64-row panel block
+// X L_kk^T = A_ik the same way.  The pivot of the augmented row (global index ns) is
+// skipped: that row is the right-hand side being forward-solved.
+constexpr int kCS = 65;   // shared stride of the 64x64 tiles (conflict-free column walks)
+constexpr size_t kCholPanelSmem = sizeof(double) * (2 * 64 * kCS + 64);
 __global__ void __launch_bounds__(256) k_chol_panel(LmDims d, int kb, LmState *st, double *__restrict__ S,
                                                     double *__restrict__ Ld) {
-    extern __shared__ double sm[];
-    double *L = sm;                 // 64 x kCS
-    double *X = sm + 64 * kCS;      // 64 x kCS
-    __shared__ int fail;
+    extern __shared__ __align__(16) double sm[];
+    double *T = sm;                   // diagonal block -> its factor L, row-major
+    double *X = sm + 64 * kCS;        // panel block
+    double *dinv_s = X + 64 * kCS;    // 1 / L[c][c]
     const int tid = threadIdx.x;
-    if (tid == 0) fail = 0;
     const int base = kb * 64;
-    for (int t = tid; t < 64 * 64; t += blockDim.x) {
-        const int r = t >> 6, c = t & 63;
-        L[r * kCS + c] = (c <= r) ? S[(size_t)(base + r) * d.NSP + base + c] : 0.0;
+    const int rb = (kb + blockIdx.x) * 64;
+    for (int t = tid; t < 64 * 64; t += 256) {
+        const int rr = t >> 6, c = t & 63;
+        T[rr * kCS + c] = S[(size_t)(base + rr) * d.NSP + base + c];
+        if (blockIdx.x) X[rr * kCS + c] = S[(size_t)(rb + rr) * d.NSP + base + c];
     }
     __syncthreads();
-    for (int j = 0; j < 64; ++j) {
-        if (tid == 0) {
-            const int gj = base + j;
-            double pv = L[j * kCS + j];
-            if (gj == d.ns) pv = 1.0;  // augmented row: no pivot
-            else if (!(pv > 0.0)) { fail = 1; pv = 1.0; }
-            else pv = sqrt(pv);
-            L[j * kCS + j] = pv;
+    int fail = 0;
+#pragma unroll
+    for (int sblk = 0; sblk < 8; ++sblk) {
+        const int k0 = sblk * 8, nrest = 56 - k0;
+        double a[8][8], dinv[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j <= i; ++j) a[i][j] = T[(k0 + i) * kCS + k0 + j];
+        chol8_regs(a, dinv, base + k0, d.ns, fail);
+        __syncthreads();  // every thread holds the pivot block before anyone overwrites it
+        if (tid < nrest) {
+            // row below the pivot block: x L_ss^T = a
+            const int r = k0 + 8 + tid;
+            double x[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = T[r * kCS + k0 + k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                x[k] *= dinv[k];
+#pragma unroll
+                for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], a[k2][k], x[k2]);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) T[r * kCS + k0 + k] = x[k];
+        } else if (tid < nrest + 8) {
+            const int i = tid - nrest;
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii)
+                if (ii == i) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) T[(k0 + ii) * kCS + k0 + j] = j <= ii ? a[ii][j] : 0.0;
+                    dinv_s[k0 + ii] = dinv[ii];
+                }
         }
         __syncthreads();
-        const double dj = L[j * kCS + j];
-        if (tid > j && tid < 64) L[tid * kCS + j] /= dj;
-        __syncthreads();
-        // trailing update of the lower triangle: rows r > j, cols j < c <= r
-        for (int t = tid; t < 64 * 64; t += blockDim.x) {
-            const int r = t >> 6, c = t & 63;
-            if (c > j && c <= r) L[r * kCS + c] -= L[r * kCS + j] * L[c * kCS + j];
+        if (nrest > 0) {
+            for (int e = tid; e < nrest * nrest; e += 256) {
+                const int rr = e / nrest, cc = e - rr * nrest;
+                if (cc > rr) continue;
+                const double *pr = &T[(k0 + 8 + rr) * kCS + k0], *pc = &T[(k0 + 8 + cc) * kCS + k0];
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc = fma(pr[k], pc[k], acc);
+                T[(k0 + 8 + rr) * kCS + k0 + 8 + cc] -= acc;
+            }
+            __syncthreads();
         }
-        __syncthreads();
     }
     if (blockIdx.x == 0) {
         if (tid == 0 && fail) atomicExch(&st->chol_fail, 1);
-        for (int t = tid; t < 64 * 64; t += blockDim.x) Ld[t] = L[(t >> 6) * kCS + (t & 63)];
+        for (int t = tid; t < 64 * 64; t += 256) {
+            const int rr = t >> 6, c = t & 63;
+            Ld[t] = c <= rr ? T[rr * kCS + c] : 0.0;
+        }
         return;
     }
-    const int rb = (kb + blockIdx.x) * 64;
-    for (int t = tid; t < 64 * 64; t += blockDim.x) {
-        const int r = t >> 6, c = t & 63;
-        X[r * kCS + c] = S[(size_t)(rb + r) * d.NSP + base + c];
-    }
-    __syncthreads();
-    // x L^T = a  ->  x[c] = (a[c] - sum_{j<c} x[j] L[c][j]) / L[c][c]; 4 threads per row
-    {
-        const int r = tid >> 2, part = tid & 3;
-        for (int c = 0; c < 64; ++c) {
-            double sacc = 0.0;
-            for (int j = part; j < c; j += 4) sacc += X[r * kCS + j] * L[c * kCS + j];
-            sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
-            sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
-            if (part == 0) X[r * kCS + c] = (X[r * kCS + c] - sacc) / L[c * kCS + c];
-            __syncwarp();
+    // panel rows: X L^T = A, sub-block column by sub-block column
+    const int r = tid & 63, q = tid >> 6;
+#pragma unroll
+    for (int sblk = 0; sblk < 8; ++sblk) {
+        const int k0 = sblk * 8;
+        if (tid < 64) {
+            double x[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) x[k] = X[r * kCS + k0 + k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                x[k] *= dinv_s[k0 + k];
+#pragma unroll
+                for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], T[(k0 + k2) * kCS + k0 + k], x[k2]);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) X[r * kCS + k0 + k] = x[k];
+        }
+        __syncthreads();
+        if (sblk < 7) {
+            double xr[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) xr[k] = X[r * kCS + k0 + k];
+            for (int c = k0 + 8 + q; c < 64; c += 4) {
+                const double *pc = &T[c * kCS + k0];
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc = fma(xr[k], pc[k], acc);
+                X[r * kCS + c] -= acc;
+            }
+            __syncthreads();
         }
     }
-    __syncthreads();
-    for (int t = tid; t < 64 * 64; t += blockDim.x) {
-        const int r = t >> 6, c = t & 63;
-        S[(size_t)(rb + r) * d.NSP + base + c] = X[r * kCS + c];
+    for (int t = tid; t < 64 * 64; t += 256) {
+        const int rr = t >> 6, c = t & 63;
+        S[(size_t)(rb + rr) * d.NSP + base + c] = X[rr * kCS + c];
     }
 }
 
@@ -558,6 +648,157 @@ __global__ void __launch_bounds__(1024) k_backward_s(LmDims d, const double *__r
         __syncthreads();
     }
 }
+
+// ---- wavefront triangular solves (one CTA per 64-row block, one launch) --------------------
+// The single-CTA kernels above walk the 24 blocks of cfg3 one after another and pull the
+// whole factor (9 MB) through one SM.  Here CTA b owns block b of the solution: it folds
+// the blocks already solved by the other CTAs into its right-hand side as soon as each is
+// published (a 64x64 GEMV, operands prefetched while it waits), then solves its own
+// diagonal block and publishes.  The critical path is nblk x (flag + GEMV + 64-step
+// substitution in one warp); every CTA must be resident (cooperative launch, the host falls
+// back to the single-CTA kernels when the grid does not fit).  Flags carry an epoch so they
+// need no reset between launches.
+__device__ __forceinline__ void wave_publish(int *flag, int epoch) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(flag), "r"(epoch) : "memory");
+    }
+}
+__device__ __forceinline__ void wave_wait(const int *flag, int epoch) {
+    if (threadIdx.x == 0) {
+        int v;
+        do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        } while (v != epoch);
+    }
+    __syncthreads();
+}
+
+// 64x64 substitution in one warp out of the staged diagonal block D (stride kDS); lanes own
+// entries lane and lane + 32 of the vector xs (shared).  lower = true: L x = b, else L^T x = b.
+template <bool LOWER>
+__device__ __forceinline__ void wave_block_solve(const double *D, const double *dinv, double *xs, int lane) {
+    double x0 = xs[lane], x1 = xs[lane + 32];
+    if (LOWER) {
+#pragma unroll 8
+        for (int j = 0; j < 64; ++j) {
+            const double src = j < 32 ? x0 : x1;
+            const double xj = __shfl_sync(0xffffffffu, src, j & 31) * dinv[j];
+            if (lane == (j & 31)) { if (j < 32) x0 = xj; else x1 = xj; }
+            if (lane > j) x0 = fma(-D[lane * kDS + j], xj, x0);
+            if (lane + 32 > j) x1 = fma(-D[(lane + 32) * kDS + j], xj, x1);
+        }
+    } else {
+#pragma unroll 8
+        for (int j = 63; j >= 0; --j) {
+            const double src = j < 32 ? x0 : x1;
+            const double xj = __shfl_sync(0xffffffffu, src, j & 31) * dinv[j];
+            if (lane == (j & 31)) { if (j < 32) x0 = xj; else x1 = xj; }
+            if (lane < j) x0 = fma(-D[j * kDS + lane], xj, x0);
+            if (lane + 32 < j) x1 = fma(-D[j * kDS + lane + 32], xj, x1);
+        }
+    }
+    xs[lane] = x0; xs[lane + 32] = x1;
+}
+
+__device__ __forceinline__ void wave_stage_diag(LmDims d, const double *__restrict__ S, int c0, double *D, double *dinv) {
+    for (int t = threadIdx.x; t < 64 * 64; t += blockDim.x) {
+        const int r = t >> 6, c = t & 63;
+        const bool in = (c <= r) && (c0 + r < d.ns);  // rows >= ns (rhs row, padding): identity
+        D[r * kDS + c] = in ? S[(size_t)(c0 + r) * d.NSP + c0 + c] : (r == c ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    if (threadIdx.x < 64) dinv[threadIdx.x] = 1.0 / D[threadIdx.x * kDS + threadIdx.x];
+}
+
+// backward: L^T p = y, y = augmented row ns of S.  blockIdx 0 owns the LAST block.
+__global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *__restrict__ S, double *p, int *flags,
+                                                       int epoch) {
+    extern __shared__ double sm[];
+    double *D = sm;                // 64 x kDS
+    double *dinv = D + 64 * kDS;   // 64
+    double *acc = dinv + 64;       // 64: right-hand side, then solution
+    double *pi = acc + 64;         // 64
+    double *part = pi + 64;        // 4 x 64
+    const int nblk = (d.ns + kNB - 1) / kNB;
+    const int b = nblk - 1 - blockIdx.x, c0 = b * kNB;
+    const int tid = threadIdx.x, g = tid >> 6, c = tid & 63;
+    wave_stage_diag(d, S, c0, D, dinv);
+    if (tid < 64) acc[tid] = (c0 + tid < d.ns) ? S[(size_t)d.ns * d.NSP + c0 + tid] : 0.0;
+    // block (i, b) of L, rows g, g+4, ... of block row i, column c of block column b
+    double cur[16], nxt[16];
+    auto fetch = [&](int i, double (&v)[16]) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = S[(size_t)(i * kNB + g + 4 * k) * d.NSP + c0 + c];
+    };
+    if (nblk - 1 > b) fetch(nblk - 1, cur);
+    for (int i = nblk - 1; i > b; --i) {
+        if (i - 1 > b) fetch(i - 1, nxt);
+        wave_wait(&flags[i], epoch);
+        if (tid < 64) pi[tid] = __ldcg(&p[i * kNB + tid]);
+        __syncthreads();
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) sacc = fma(cur[k], pi[g + 4 * k], sacc);
+        part[g * 64 + c] = sacc;
+        __syncthreads();
+        if (tid < 64) acc[tid] -= (part[tid] + part[64 + tid]) + (part[128 + tid] + part[192 + tid]);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) cur[k] = nxt[k];
+    }
+    __syncthreads();
+    if (tid < 32) wave_block_solve<false>(D, dinv, acc, tid);
+    __syncthreads();
+    if (tid < 64) p[c0 + tid] = (c0 + tid < d.ns) ? acc[tid] : 0.0;
+    wave_publish(&flags[b], epoch);
+}
+
+// forward: L w = rhs for rows [0, ns).  rhs and w may alias.  blockIdx b owns block b.
+__global__ void __launch_bounds__(256) k_forward_wave(LmDims d, const double *__restrict__ S, const double *rhs, double *w,
+                                                      int *flags, int epoch) {
+    extern __shared__ double sm[];
+    double *D = sm;
+    double *dinv = D + 64 * kDS;
+    double *acc = dinv + 64;
+    double *wi = acc + 64;
+    const int b = blockIdx.x, c0 = b * kNB;
+    const int tid = threadIdx.x, r = tid >> 2, q = tid & 3;
+    wave_stage_diag(d, S, c0, D, dinv);
+    if (tid < 64) acc[tid] = (c0 + tid < d.ns) ? rhs[c0 + tid] : 0.0;
+    __syncthreads();
+    // block (b, i) of L: row r of block row b, columns q*16 .. q*16+15 of block column i
+    const bool live = c0 + r < d.ns;
+    double cur[16], nxt[16];
+    auto fetch = [&](int i, double (&v)[16]) {
+        const double2 *src = reinterpret_cast<const double2 *>(&S[(size_t)(c0 + r) * d.NSP + i * kNB + q * 16]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) { const double2 t = src[k]; v[2 * k] = t.x; v[2 * k + 1] = t.y; }
+    };
+    if (b > 0) fetch(0, cur);
+    for (int i = 0; i < b; ++i) {
+        if (i + 1 < b) fetch(i + 1, nxt);
+        wave_wait(&flags[i], epoch);
+        if (tid < 64) wi[tid] = __ldcg(&w[i * kNB + tid]);
+        __syncthreads();
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) sacc = fma(cur[k], wi[q * 16 + k], sacc);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+        if (q == 0 && live) acc[r] -= sacc;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; ++k) cur[k] = nxt[k];
+    }
+    __syncthreads();
+    if (tid < 32) wave_block_solve<true>(D, dinv, acc, tid);
+    __syncthreads();
+    if (tid < 64 && c0 + tid < d.ns) w[c0 + tid] = acc[tid];
+    wave_publish(&flags[b], epoch);
+}
+constexpr size_t kWaveSmemBwd = sizeof(double) * (64 * kDS + 64 * 3 + 4 * 64);
+constexpr size_t kWaveSmemFwd = sizeof(double) * (64 * kDS + 64 * 3);
 
 // ---- eliminated-side back substitution -------------------------------------------------
 // p_f = L_f^-T (z_f - Y_f p_S); CTA per frame.  p_int = [p_E (KE) | p_S (ns)]
