@@ -298,6 +298,15 @@ mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
                           int32_t *launches);
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 int64_t mmb_launch_count(const mmb_problem *p);
+/* How the last mmb_solve() on this handle was driven.  The reference's loop is
+ * host code calling back into the scene once per function / Jacobian evaluation
+ * (lmder -> solveFunc, adjust_cminpack_lmder.cpp:114, adjust_solveFunc.cpp:529).
+ * Here an unsharded global solve is one CUDA graph launch (conditional WHILE /
+ * IF nodes steered from the device) and one synchronisation to read the result:
+ * host_syncs = 1, graph_launches = 1.  A sharded solve is host-driven
+ * (graph_launches = 0, a few host_syncs per LM iteration). */
+mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs,
+                           int64_t *graph_launches);
 
 const char *mmb_status_string(mmb_status s);
 /* detail of the last failing call on this thread (static storage) */

@@ -306,7 +306,7 @@ mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count, mmb
 }
 
 void mmb_request_cancel(mmb_problem *p) {
-    if (p) p->dp->cancel = 1;
+    if (p) lm_request_cancel(p->dp);
 }
 
 mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2, double *ms_per_eval,
@@ -366,6 +366,13 @@ mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2, double
 }
 
 int64_t mmb_launch_count(const mmb_problem *p) { return p ? (int64_t)p->dp->launches : 0; }
+
+mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs, int64_t *graph_launches) {
+    if (!p) return MMB_ERR_INVALID_ARGUMENT;
+    if (host_syncs) *host_syncs = p->dp->solve_host_syncs;
+    if (graph_launches) *graph_launches = p->dp->solve_graph_launches;
+    return MMB_OK;
+}
 
 const char *mmb_status_string(mmb_status s) {
     switch (s) {

@@ -81,6 +81,8 @@ struct DeviceProblem {
     int frames_global = 0;      // frame count of the unsharded scene
     volatile int cancel = 0;
     long long launches = 0;     // kernels launched by this handle
+    long long solve_host_syncs = 0;      // host<->device synchronisations inside the last mmb_solve
+    long long solve_graph_launches = 0;  // CUDA graph launches of the last mmb_solve (device-resident LM loop)
 
     ~DeviceProblem();
 };

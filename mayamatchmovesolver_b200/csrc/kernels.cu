@@ -1,6 +1,7 @@
 // CUDA kernels (sm_100a) of the residual / FD-Jacobian path and the handle
 // that owns their HBM buffers.  Per-thread bodies live in eval_bodies.cuh.
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -153,11 +154,18 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
 void lm_workspace_destroy(LmWorkspace *w);
 
 DeviceProblem::~DeviceProblem() {
+    const bool timing = getenv("MMB_TIMING") != nullptr;
+    const auto t0 = std::chrono::steady_clock::now();
     cudaSetDevice(device);
     if (lm) lm_workspace_destroy(lm);
+    const auto t1 = std::chrono::steady_clock::now();
     if (comm) { if (stream) cudaStreamSynchronize(stream); delete comm; }
     if (stream) cudaStreamDestroy(stream);
     arena.release();
+    if (timing)
+        fprintf(stderr, "[mmb timing] destroy: LM workspace %.3f ms, scene buffers %.3f ms\n",
+                1e3 * std::chrono::duration<double>(t1 - t0).count(),
+                1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count());
 }
 
 mmb_status ensure_jacobian_buffers(DeviceProblem *p) {
@@ -181,8 +189,11 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
         set_last_error("device ordinal out of range");
         return MMB_ERR_INVALID_ARGUMENT;
     }
+    const bool timing = getenv("MMB_TIMING") != nullptr;
+    const auto tc0 = std::chrono::steady_clock::now();
     DeviceProblem *p = new DeviceProblem();
     mmb_status st = build_host_problem(s, opt, &p->hp);
+    const auto tc1 = std::chrono::steady_clock::now();
     if (st != MMB_OK) {
         set_last_error(p->hp.error);
         delete p;
@@ -355,6 +366,13 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
 #undef UP_I
 #undef UP_D
 #undef UP_L
+    if (timing) {
+        cudaDeviceSynchronize();
+        const auto tc2 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mmb timing] create: host index maps / plans %.3f ms, device alloc + upload %.3f ms (%zu allocations, %.1f MB)\n",
+                1e3 * std::chrono::duration<double>(tc1 - tc0).count(), 1e3 * std::chrono::duration<double>(tc2 - tc1).count(),
+                A.ptrs.size(), A.bytes / 1e6);
+    }
     *out = p;
     return MMB_OK;
 }

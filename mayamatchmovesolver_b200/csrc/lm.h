@@ -7,4 +7,6 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
 mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out,
                               mmb_result *per_frame_out);
 void lm_workspace_destroy(LmWorkspace *w);
+// sets the flag the device-resident loop polls (pinned, mapped) and the host loop's flag
+void lm_request_cancel(DeviceProblem *p);
 }  // namespace mmb

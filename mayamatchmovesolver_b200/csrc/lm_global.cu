@@ -4,8 +4,16 @@
 // tail of solveFrames (adjust_base.cpp:1076-1287).  The control law is
 // MINPACK's lmder/lmpar evaluated by single-block
 // control kernels on the device; the linear algebra is the Schur/Cholesky
-// path of lm_kernels.cuh.  The host enqueues kernels and reads the flag words
-// of LmState to know what to enqueue next.
+// path of lm_kernels.cuh.
+//
+// Unsharded solve: the whole LM loop is ONE CUDA graph.  Its conditional nodes
+//   WHILE(!done) { IF(need_jacobian){J, assembly}  WHILE(!lmpar_done){factor, solve}
+//                  IF(!done){trial, ratio test, accept} }
+// are steered by tiny kernels that copy LmState flags into the conditional
+// handles (cudaGraphSetConditional), so the host launches the graph once and
+// reads the result once: no host round trip per iteration.
+// Sharded solve (NCCL all-reduces between the kernels): the host enqueues the
+// same kernels and reads the flag words of LmState to know what comes next.
 #include <algorithm>
 #include <chrono>
 #include <cmath>
@@ -46,7 +54,17 @@ struct LmWorkspace {
     int gemv_chunks = 1;
     long long n_allreduce = 0;
     int *wave_flags = nullptr;   // [NSP / 64] epoch flags of the wavefront triangular solves
-    int wave_epoch = 0;
+    int *wave_ctr = nullptr;     // device epoch counter (k_ctrl_lmpar adds 2 per lmpar step)
+    double *h_stage = nullptr;   // pinned staging: [max(2 n, kRedBlocks + n)]
+    int *h_cancel = nullptr;     // pinned, mapped: set by mmb_request_cancel, polled by the loop-head kernel
+    int *d_cancel = nullptr;     // device alias of h_cancel
+    // the device-resident loop
+    bool capturing = false;      // enqueue helpers are recording into a graph
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    bool graph_failed = false;
+    int body_launches[4] = {0, 0, 0, 0};  // kernels per execution of: loop head/tail, jacobian body, lmpar body, trial body
+    int fixed_launches = 0;               // prologue + epilogue kernels
     bool wave_ok = false;        // every block of the wavefront kernels fits on the device at once
     double init_avg = 0, init_min = 0, init_max = 0;
     // optional phase timing (MMB_LM_PROFILE=1): schur, cholesky, back-substitution, q-solve
@@ -55,7 +73,11 @@ struct LmWorkspace {
     double phase_ms[4] = {0, 0, 0, 0};
     int phase_n = 0;
     ~LmWorkspace() {
+        if (graph_exec) cudaGraphExecDestroy(graph_exec);
+        if (graph) cudaGraphDestroy(graph);
         if (h_st) cudaFreeHost(h_st);
+        if (h_cancel) cudaFreeHost(h_cancel);
+        if (h_stage) cudaFreeHost(h_stage);
     }
 };
 
@@ -194,7 +216,8 @@ __global__ void __launch_bounds__(1024) k_lmpar_partial(LmDims d, LmState *st, c
 }
 
 // lmpar step (MINPACK lmpar restated on the normal equations)
-__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int, const double *scal) {
+__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int, const double *scal,
+                                                     int *wave_ctr) {
     __shared__ double sh[32];
     double a = 0.0;
     for (int q = d.KE + threadIdx.x; q < d.n; q += blockDim.x) {
@@ -203,6 +226,7 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
     }
     a = block_sum(a, sh);
     if (threadIdx.x != 0) return;
+    *wave_ctr += 2;  // the two wavefront solves of this step are done: retire their epochs
     const double p1 = 0.1, p001 = 0.001, dwarf = 2.2250738585072014e-308;
     const double delta = st->delta;
     const bool fail = scal[1] > 0.0;  // a pivot <= 0 on any rank
@@ -382,8 +406,50 @@ __global__ void k_error_stats_fold(const double *part, int nparts, int nobs, dou
     scal[0] = a; scal[1] = (double)nobs;
     mxv[0] = mx; mxv[1] = -mn;
 }
-__global__ void k_error_stats_final(LmState *st, const double *scal, const double *mxv) {
+__global__ void k_error_stats_final(LmState *st, const double *scal, const double *mxv, int to_init) {
     st->err_avg = scal[0] / scal[1]; st->err_max = mxv[0]; st->err_min = -mxv[1];
+    if (to_init) st->init_avg = st->err_avg;
+}
+
+// ---- phase boundaries of the device-resident loop ---------------------------------------
+// One thread: stamps the phase timers (%globaltimer) and copies LmState flags into the
+// conditional handles of the graph (the device-side half of cudaGraphConditionalHandle).
+enum { kCondStart = 0, kCondLoopHead, kCondAfterJac, kCondInLmpar, kCondAfterLmpar, kCondAfterTrial };
+__global__ void k_cond(LmState *st, const int *cancel, int where, cudaGraphConditionalHandle h0,
+                       cudaGraphConditionalHandle h1) {
+    unsigned long long now;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+    switch (where) {
+        case kCondStart:  // after k_ctrl_init; h0 = outer WHILE
+            cudaGraphSetConditional(h0, st->done ? 0u : 1u);
+            break;
+        case kCondLoopHead:  // h0 = IF(jacobian)
+            if (*(const volatile int *)cancel) { st->cancelled = 1; st->done = 1; }
+            st->n_body_loop += 1;
+            st->t_mark = now;
+            cudaGraphSetConditional(h0, (!st->done && st->need_jacobian) ? 1u : 0u);
+            break;
+        case kCondAfterJac:  // h0 = WHILE(lmpar)
+            st->t_jac_ns += now - st->t_mark;
+            st->t_mark = now;
+            cudaGraphSetConditional(h0, (!st->done && !st->lmpar_done) ? 1u : 0u);
+            break;
+        case kCondInLmpar:  // tail of the lmpar body; h0 = WHILE(lmpar)
+            st->n_body_lmpar += 1;
+            cudaGraphSetConditional(h0, (!st->done && !st->lmpar_done) ? 1u : 0u);
+            break;
+        case kCondAfterLmpar:  // h0 = IF(trial); h1 = outer WHILE (the trial body may be skipped)
+            st->t_lin_ns += now - st->t_mark;
+            st->t_mark = now;
+            cudaGraphSetConditional(h0, st->done ? 0u : 1u);
+            cudaGraphSetConditional(h1, st->done ? 0u : 1u);
+            break;
+        default:  // kCondAfterTrial: tail of the trial body; h0 = outer WHILE
+            st->n_body_trial += 1;
+            st->t_func_ns += now - st->t_mark;
+            cudaGraphSetConditional(h0, st->done ? 0u : 1u);
+            break;
+    }
 }
 
 // ---- workspace ------------------------------------------------------------------------------
@@ -412,6 +478,10 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     } while (0)
     CKW(A.alloc(&w->st, 1));
     CKW(cudaMallocHost((void **)&w->h_st, sizeof(LmState)));
+    CKW(cudaHostAlloc((void **)&w->h_cancel, sizeof(int), cudaHostAllocMapped));
+    *w->h_cancel = 0;
+    CKW(cudaMallocHost((void **)&w->h_stage, sizeof(double) * (size_t)(2 * d.n + kRedBlocks)));
+    CKW(cudaHostGetDevicePointer((void **)&w->d_cancel, w->h_cancel, 0));
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
     CKW(A.alloc(&w->U, (size_t)d.F * d.na * d.na));
@@ -446,6 +516,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         const int nblk = std::max(1, (d.ns + kNB - 1) / kNB);
         CKW(A.alloc(&w->wave_flags, (size_t)d.NSP / 64 + 1));
         CKW(cudaMemset(w->wave_flags, 0, sizeof(int) * ((size_t)d.NSP / 64 + 1)));
+        CKW(A.alloc(&w->wave_ctr, 1));
+        CKW(cudaMemset(w->wave_ctr, 0, sizeof(int)));
         CKW(cudaFuncSetAttribute(k_backward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemBwd));
         CKW(cudaFuncSetAttribute(k_forward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemFwd));
         int coop = 0, sms = 0, occ_b = 0, occ_f = 0;
@@ -457,7 +529,7 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         w->wave_ok = coop && nblk <= sms * std::min(occ_b, occ_f) && !(e && atoi(e) == 0);
     }
 #undef CKW
-    w->profile = getenv("MMB_LM_PROFILE") != nullptr;
+    { const char *e = getenv("MMB_LM_PROFILE"); w->profile = e && atoi(e) != 0; }
     if (w->profile) for (auto &e : w->ev) cudaEventCreate(&e);
     p->lm = w;
     return MMB_OK;
@@ -474,6 +546,7 @@ static mmb_status read_state(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     MMB_CUDA_CHECK(cudaMemcpyAsync(w->h_st, w->st, sizeof(LmState), cudaMemcpyDeviceToHost, p->stream));
     MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
+    ++p->solve_host_syncs;
     return MMB_OK;
 }
 
@@ -496,7 +569,7 @@ static mmb_status enqueue_residual_eval(DeviceProblem *p, const double *d_x, dou
 }
 
 // avg / min / max of `dist` over every shard -> LmState err_*
-static mmb_status enqueue_error_stats(DeviceProblem *p, const double *dist) {
+static mmb_status enqueue_error_stats(DeviceProblem *p, const double *dist, bool to_init = false) {
     LmWorkspace *w = p->lm;
     mmb_status st;
     k_error_stats_partial<<<kStatBlocks, 256, 0, p->stream>>>(dist, p->hp.nobs, w->stat_part);
@@ -505,7 +578,7 @@ static mmb_status enqueue_error_stats(DeviceProblem *p, const double *dist) {
     LAUNCH_CHECK();
     if ((st = all_reduce(p, w->scal, 2)) != MMB_OK) return st;
     if ((st = all_reduce(p, w->mx, 2, true)) != MMB_OK) return st;
-    k_error_stats_final<<<1, 1, 0, p->stream>>>(w->st, w->scal, w->mx);
+    k_error_stats_final<<<1, 1, 0, p->stream>>>(w->st, w->scal, w->mx, to_init ? 1 : 0);
     LAUNCH_CHECK();
     return MMB_OK;
 }
@@ -544,10 +617,16 @@ static mmb_status enqueue_backward_s(DeviceProblem *p, double *pS) {
     LmDims d = w->d;
     if (w->wave_ok && d.ns > 0) {
         const int nblk = (d.ns + kNB - 1) / kNB;
-        int epoch = ++w->wave_epoch;
         const double *S = w->S;
         int *flags = w->wave_flags;
-        void *args[] = {&d, &S, &pS, &flags, &epoch};
+        const int *ctr = w->wave_ctr;
+        int slot = 1;
+        if (w->capturing) {  // graph body: plain launch (see the note above k_backward_wave)
+            k_backward_wave<<<nblk, 256, kWaveSmemBwd, p->stream>>>(d, S, pS, flags, ctr, slot);
+            LAUNCH_CHECK();
+            return MMB_OK;
+        }
+        void *args[] = {&d, &S, &pS, &flags, &ctr, &slot};
         MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_backward_wave, dim3(nblk), dim3(256), args, kWaveSmemBwd, p->stream));
         ++p->launches;
         return MMB_OK;
@@ -561,11 +640,17 @@ static mmb_status enqueue_forward_s(DeviceProblem *p, double *wS) {
     LmDims d = w->d;
     if (w->wave_ok && d.ns > 0) {
         const int nblk = (d.ns + kNB - 1) / kNB;
-        int epoch = ++w->wave_epoch;
         const double *S = w->S;
         const double *rhs = wS;
         int *flags = w->wave_flags;
-        void *args[] = {&d, &S, &rhs, &wS, &flags, &epoch};
+        const int *ctr = w->wave_ctr;
+        int slot = 2;
+        if (w->capturing) {
+            k_forward_wave<<<nblk, 256, kWaveSmemFwd, p->stream>>>(d, S, rhs, wS, flags, ctr, slot);
+            LAUNCH_CHECK();
+            return MMB_OK;
+        }
+        void *args[] = {&d, &S, &rhs, &wS, &flags, &ctr, &slot};
         MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_forward_wave, dim3(nblk), dim3(256), args, kWaveSmemFwd, p->stream));
         ++p->launches;
         return MMB_OK;
@@ -582,7 +667,8 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     cudaStream_t s = p->stream;
     const bool sharded = p->comm && p->comm->world > 1;
     mmb_status rs;
-    if (w->profile) cudaEventRecord(w->ev[0], s);
+    const bool prof = w->profile && !w->capturing;
+    if (prof) cudaEventRecord(w->ev[0], s);
     if (d.KE) {
         const size_t sm = sizeof(double) * ((size_t)d.na * d.na + d.na);
         k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
@@ -608,7 +694,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_schur_damp<<<(d.NSP + 255) / 256, 256, 0, s>>>(d, w->st, w->diag, w->i2p, w->S);
         LAUNCH_CHECK();
     }
-    if (w->profile) cudaEventRecord(w->ev[1], s);
+    if (prof) cudaEventRecord(w->ev[1], s);
     for (int kb = 0; kb < nb; ++kb) {
         k_chol_panel<<<nb - kb, 256, kCholPanelSmem, s>>>(d, kb, w->st, w->S, w->Ld);
         LAUNCH_CHECK();
@@ -616,13 +702,13 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
         LAUNCH_CHECK();
     }
-    if (w->profile) cudaEventRecord(w->ev[2], s);
+    if (prof) cudaEventRecord(w->ev[2], s);
     if ((rs = enqueue_backward_s(p, w->p_int + d.KE)) != MMB_OK) return rs;
     if (d.KE) {
         k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
         LAUNCH_CHECK();
     }
-    if (w->profile) cudaEventRecord(w->ev[3], s);
+    if (prof) cudaEventRecord(w->ev[3], s);
     // Newton correction: w = L^-1 D^2 p (scaled by 1/||D p|| in k_ctrl_lmpar)
     if (d.KE) {
         k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
@@ -645,9 +731,9 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
         if ((rs = enqueue_forward_s(p, w->w_int + d.KE)) != MMB_OK) return rs;
     }
-    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal);
+    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal, w->wave_ctr);
     LAUNCH_CHECK();
-    if (w->profile) {
+    if (prof) {
         cudaEventRecord(w->ev[4], s);
         cudaEventSynchronize(w->ev[4]);
         for (int i = 0; i < 4; ++i) { float ms = 0; cudaEventElapsedTime(&ms, w->ev[i], w->ev[i + 1]); w->phase_ms[i] += ms; }
@@ -678,65 +764,180 @@ static mmb_status enqueue_trial(DeviceProblem *p) {
 using clk = std::chrono::steady_clock;
 static double secs(clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); }
 
-mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out) {
-    std::memset(res, 0, sizeof(*res));
-    const HostProblem &hp = p->hp;
-    // pre-checks of solveFrames (adjust_base.cpp:844-882)
-    if (hp.nobs == 0 || hp.n == 0) { set_last_error("no used markers or attributes"); return MMB_ERR_NOT_ENOUGH_OBJECTS; }
-    if (hp.n > hp.m) { set_last_error("more parameters than errors"); return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
-    MMB_CUDA_CHECK(cudaSetDevice(p->device));
-    mmb_status st;
-    if ((st = ensure_jacobian_buffers(p)) != MMB_OK) return st;
-    if ((st = lm_workspace_create(p)) != MMB_OK) return st;
+void lm_request_cancel(DeviceProblem *p) {
+    p->cancel = 1;
+    if (p->lm && p->lm->h_cancel) *(volatile int *)p->lm->h_cancel = 1;
+}
+
+// prologue of both drivers: the acceptOnlyBetter reference measurement, the first function
+// evaluation and the lmder input checks
+static mmb_status enqueue_prologue(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
-    const LmDims &d = w->d;
-    const auto t_begin = clk::now();
-    p->cancel = 0;
-
-    // initial parameters (get_initial_parameters, adjust_base.cpp:260-295)
-    std::vector<double> x0(hp.n);
-    for (int i = 0; i < hp.n; ++i) {
-        const int a = hp.par_attr[i], f = hp.par_frame[i];
-        const int32_t ref = hp.attr_ref[a];
-        const double v = ref >= 0 ? hp.stat0[ref] : hp.anim0[(size_t)(-ref - 1) * hp.F + f];
-        x0[i] = bound_external_to_internal(v, hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
-    }
-    MMB_CUDA_CHECK(cudaMemcpyAsync(p->d_x, x0.data(), sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
-
-    LmState h{};
-    h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
-    h.ftol = hp.opt.eps1; h.xtol = hp.opt.eps2; h.gtol = hp.opt.eps3; h.factor = hp.opt.tau * 100.0;
-    *w->h_st = h;
-    MMB_CUDA_CHECK(cudaMemcpyAsync(w->st, w->h_st, sizeof(LmState), cudaMemcpyHostToDevice, p->stream));
-    MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
-    {   // diag = paramWeightList = 1.0 (adjust_relationships.cpp:320)
-        std::vector<double> ones(hp.n, 1.0);
-        MMB_CUDA_CHECK(cudaMemcpyAsync(w->diag, ones.data(), sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
-        MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
-    }
-    double t_jac = 0, t_func = 0, t_lin = 0;
-    int func_evals = 0, jac_evals = 0;
-
+    mmb_status st;
     // initial measureErrors when acceptOnlyBetter (adjust_base.cpp:1080-1103): at the
     // scene's own values, before any parameter is set.
-    double init_avg = 0.0;
-    if (hp.opt.accept_only_better) {
+    if (p->hp.opt.accept_only_better) {
         if ((st = launch_variants(p, nullptr, false)) != MMB_OK) return st;
         if ((st = launch_residuals(p, p->d_fvec, p->d_dist)) != MMB_OK) return st;
-        if ((st = enqueue_error_stats(p, p->d_dist)) != MMB_OK) return st;
-        if ((st = read_state(p)) != MMB_OK) return st;
-        init_avg = w->h_st->err_avg;
+        if ((st = enqueue_error_stats(p, p->d_dist, true)) != MMB_OK) return st;
     }
-    // first function evaluation
-    auto t0 = clk::now();
     if ((st = enqueue_residual_eval(p, p->d_x, p->d_fvec, p->d_dist)) != MMB_OK) return st;
     if ((st = all_reduce(p, w->part_f, kRedBlocks)) != MMB_OK) return st;
     k_ctrl_init<<<1, 1024, 0, p->stream>>>(w->st, w->part_f, kRedBlocks);
     LAUNCH_CHECK();
-    if ((st = read_state(p)) != MMB_OK) return st;
-    t_func += secs(t0, clk::now());
-    ++func_evals;
+    return MMB_OK;
+}
 
+// epilogue: error statistics of the last measureErrors call and ||fvec||^2 partials.
+// errorDistanceList holds whatever the LAST measureErrors call left there (a rejected
+// trial or the last FD perturbation included): dist2 tracks that.
+static mmb_status enqueue_epilogue(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    mmb_status st;
+    if ((st = enqueue_error_stats(p, w->dist2)) != MMB_OK) return st;
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)p->hp.m, w->part_f);
+    LAUNCH_CHECK();
+    return all_reduce(p, w->part_f, kRedBlocks);
+}
+
+// ---- the device-resident loop: one CUDA graph with conditional nodes -------------------
+// Adds a conditional node after whatever the capturing stream has recorded so far and
+// makes it the stream's new dependency; returns the (empty) body graph.
+static mmb_status capture_conditional(cudaStream_t s, cudaGraphConditionalHandle h, cudaGraphConditionalNodeType type,
+                                      cudaGraph_t *body) {
+    cudaStreamCaptureStatus status;
+    unsigned long long id = 0;
+    cudaGraph_t g = nullptr;
+    const cudaGraphNode_t *deps = nullptr;
+    size_t ndeps = 0;
+    MMB_CUDA_CHECK(cudaStreamGetCaptureInfo(s, &status, &id, &g, &deps, &ndeps));
+    cudaGraphNodeParams params = {cudaGraphNodeTypeConditional};
+    params.type = cudaGraphNodeTypeConditional;
+    params.conditional.handle = h;
+    params.conditional.type = type;
+    params.conditional.size = 1;
+    cudaGraphNode_t node;
+    MMB_CUDA_CHECK(cudaGraphAddNode(&node, g, deps, ndeps, &params));
+    MMB_CUDA_CHECK(cudaStreamUpdateCaptureDependencies(s, &node, 1, cudaStreamSetCaptureDependencies));
+    *body = params.conditional.phGraph_out[0];
+    return MMB_OK;
+}
+
+// handle_owner: which graph the handles of the nested conditionals are created on
+// (0 = the top-level graph, 1 = the loop body that holds their nodes)
+static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
+    LmWorkspace *w = p->lm;
+    cudaStream_t s = p->stream;
+    mmb_status st = MMB_OK;
+    cudaGraph_t g = nullptr, body_loop = nullptr, body_jac = nullptr, body_lmpar = nullptr, body_trial = nullptr, tmp = nullptr;
+    cudaGraphConditionalHandle h_loop, h_jac, h_lmpar, h_trial;
+    MMB_CUDA_CHECK(cudaGraphCreate(&g, 0));
+    w->graph = g;
+    MMB_CUDA_CHECK(cudaGraphConditionalHandleCreate(&h_loop, g, 0, 0));
+    const long long launches_before = p->launches;
+    w->capturing = true;
+    auto fail = [&](mmb_status e) {
+        cudaGraph_t dead = nullptr;
+        cudaStreamEndCapture(s, &dead);  // leaves capture mode whatever state it is in
+        cudaGetLastError();
+        w->capturing = false;
+        p->launches = launches_before;
+        return e;
+    };
+#define GB(expr)                                                                      \
+    do {                                                                              \
+        cudaError_t _e = (expr);                                                      \
+        if (_e != cudaSuccess) {                                                      \
+            set_last_error(std::string("LM graph: " #expr ": ") + cudaGetErrorString(_e)); \
+            return fail(MMB_ERR_CUDA);                                                \
+        }                                                                             \
+    } while (0)
+#define GS(expr)                                     \
+    do {                                             \
+        if ((st = (expr)) != MMB_OK) return fail(st); \
+    } while (0)
+    // top level: prologue, WHILE(!done), epilogue
+    long long l0 = p->launches;
+    GB(cudaStreamBeginCaptureToGraph(s, g, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    GS(enqueue_prologue(p));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondStart, h_loop, h_loop);
+    ++p->launches;
+    GS(capture_conditional(s, h_loop, cudaGraphCondTypeWhile, &body_loop));
+    GS(enqueue_epilogue(p));
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->fixed_launches = (int)(p->launches - l0);
+    // loop body: IF(need_jacobian) ; WHILE(!lmpar_done) ; IF(!done) trial
+    l0 = p->launches;
+    {
+        cudaGraph_t owner = handle_owner ? body_loop : g;
+        cudaError_t e1 = cudaGraphConditionalHandleCreate(&h_jac, owner, 0, 0);
+        cudaError_t e2 = cudaGraphConditionalHandleCreate(&h_lmpar, owner, 0, 0);
+        cudaError_t e3 = cudaGraphConditionalHandleCreate(&h_trial, owner, 0, 0);
+        if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
+            set_last_error(std::string("LM graph: cudaGraphConditionalHandleCreate: ") +
+                           cudaGetErrorString(e1 != cudaSuccess ? e1 : (e2 != cudaSuccess ? e2 : e3)));
+            cudaGetLastError();
+            w->capturing = false;
+            p->launches = launches_before;
+            return MMB_ERR_CUDA;
+        }
+    }
+    GB(cudaStreamBeginCaptureToGraph(s, body_loop, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondLoopHead, h_jac, h_jac);
+    GS(capture_conditional(s, h_jac, cudaGraphCondTypeIf, &body_jac));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterJac, h_lmpar, h_lmpar);
+    GS(capture_conditional(s, h_lmpar, cudaGraphCondTypeWhile, &body_lmpar));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterLmpar, h_trial, h_loop);
+    p->launches += 3;
+    GS(capture_conditional(s, h_trial, cudaGraphCondTypeIf, &body_trial));
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->body_launches[0] = (int)(p->launches - l0);
+    // Jacobian + assembly
+    l0 = p->launches;
+    GB(cudaStreamBeginCaptureToGraph(s, body_jac, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    GS(enqueue_jacobian_and_assembly(p));
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->body_launches[1] = (int)(p->launches - l0);
+    // one lmpar step
+    l0 = p->launches;
+    GB(cudaStreamBeginCaptureToGraph(s, body_lmpar, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    GS(enqueue_lmpar_step(p));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondInLmpar, h_lmpar, h_lmpar);
+    ++p->launches;
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->body_launches[2] = (int)(p->launches - l0);
+    // trial point, ratio test, accept / reject
+    l0 = p->launches;
+    GB(cudaStreamBeginCaptureToGraph(s, body_trial, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    GS(enqueue_trial(p));
+    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterTrial, h_loop, h_loop);
+    ++p->launches;
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->body_launches[3] = (int)(p->launches - l0);
+#undef GB
+#undef GS
+    w->capturing = false;
+    p->launches = launches_before;  // nothing ran yet
+    const auto ti0 = clk::now();
+    cudaError_t e = cudaGraphInstantiate(&w->graph_exec, g, 0);
+    if (getenv("MMB_LM_GRAPH_VERBOSE")) fprintf(stderr, "[mmb] LM graph: cudaGraphInstantiate %.3f ms\n", 1e3 * secs(ti0, clk::now()));
+    if (e != cudaSuccess) {
+        set_last_error(std::string("LM graph: cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        cudaGetLastError();
+        w->graph_exec = nullptr;
+        return MMB_ERR_CUDA;
+    }
+    return MMB_OK;
+}
+
+// host-driven loop (sharded solves: NCCL collectives sit between the kernels)
+static mmb_status lm_run_host_loop(DeviceProblem *p, mmb_result *res, double *t_jac, double *t_func, double *t_lin) {
+    LmWorkspace *w = p->lm;
+    mmb_status st;
+    auto t0 = clk::now();
+    if ((st = enqueue_prologue(p)) != MMB_OK) return st;
+    if ((st = read_state(p)) != MMB_OK) return st;
+    *t_func += secs(t0, clk::now());
     int guard = 0;
     while (!w->h_st->done) {
         if (p->cancel) { res->user_interrupted = 1; break; }
@@ -745,8 +946,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
             t0 = clk::now();
             if ((st = enqueue_jacobian_and_assembly(p)) != MMB_OK) return st;
             if ((st = read_state(p)) != MMB_OK) return st;
-            t_jac += secs(t0, clk::now());
-            jac_evals += hp.n * (hp.opt.auto_diff_type == 1 ? 2 : 1);
+            *t_jac += secs(t0, clk::now());
             if (w->h_st->done) break;
         }
         t0 = clk::now();
@@ -754,40 +954,121 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
             if ((st = enqueue_lmpar_step(p)) != MMB_OK) return st;
             if ((st = read_state(p)) != MMB_OK) return st;
         }
-        t_lin += secs(t0, clk::now());
+        *t_lin += secs(t0, clk::now());
         if (w->h_st->done) break;
         t0 = clk::now();
         if ((st = enqueue_trial(p)) != MMB_OK) return st;
         if ((st = read_state(p)) != MMB_OK) return st;
-        t_func += secs(t0, clk::now());
-        ++func_evals;
+        *t_func += secs(t0, clk::now());
+    }
+    return enqueue_epilogue(p);
+}
+
+mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out) {
+    std::memset(res, 0, sizeof(*res));
+    const HostProblem &hp = p->hp;
+    // pre-checks of solveFrames (adjust_base.cpp:844-882)
+    if (hp.nobs == 0 || hp.n == 0) { set_last_error("no used markers or attributes"); return MMB_ERR_NOT_ENOUGH_OBJECTS; }
+    if (hp.n > hp.m) { set_last_error("more parameters than errors"); return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
+    MMB_CUDA_CHECK(cudaSetDevice(p->device));
+    mmb_status st;
+    const auto t_begin = clk::now();
+    p->cancel = 0;
+    p->solve_host_syncs = 0;
+    p->solve_graph_launches = 0;
+    if ((st = ensure_jacobian_buffers(p)) != MMB_OK) return st;
+    if ((st = lm_workspace_create(p)) != MMB_OK) return st;
+    if (getenv("MMB_TIMING")) {
+        cudaDeviceSynchronize();
+        fprintf(stderr, "[mmb timing] solve: Jacobian buffers + LM workspace %.3f ms\n", 1e3 * secs(t_begin, clk::now()));
+    }
+    LmWorkspace *w = p->lm;
+    *(volatile int *)w->h_cancel = p->cancel;  // a request that raced the workspace creation
+
+    // initial parameters (get_initial_parameters, adjust_base.cpp:260-295); diag =
+    // paramWeightList = 1.0 (adjust_relationships.cpp:320).  One pinned staging buffer,
+    // asynchronous uploads.
+    double *stage = w->h_stage;  // [2 n]: x0, ones
+    for (int i = 0; i < hp.n; ++i) {
+        const int a = hp.par_attr[i], f = hp.par_frame[i];
+        const int32_t ref = hp.attr_ref[a];
+        const double v = ref >= 0 ? hp.stat0[ref] : hp.anim0[(size_t)(-ref - 1) * hp.F + f];
+        stage[i] = bound_external_to_internal(v, hp.attr_min[a], hp.attr_max[a], hp.attr_off[a], hp.attr_scl[a]);
+        stage[hp.n + i] = 1.0;
+    }
+    std::vector<double> x0(stage, stage + hp.n);
+    MMB_CUDA_CHECK(cudaMemcpyAsync(p->d_x, stage, sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
+    MMB_CUDA_CHECK(cudaMemcpyAsync(w->diag, stage + hp.n, sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
+    LmState h{};
+    h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
+    h.ftol = hp.opt.eps1; h.xtol = hp.opt.eps2; h.gtol = hp.opt.eps3; h.factor = hp.opt.tau * 100.0;
+    *w->h_st = h;
+    MMB_CUDA_CHECK(cudaMemcpyAsync(w->st, w->h_st, sizeof(LmState), cudaMemcpyHostToDevice, p->stream));
+
+    const bool sharded = p->comm && p->comm->world > 1;
+    int graph_mode = 1;
+    { const char *e = getenv("MMB_LM_GRAPH"); if (e) graph_mode = atoi(e); }
+    bool use_graph = graph_mode && !sharded && !w->profile && !w->graph_failed;
+    if (use_graph && !w->graph_exec) {
+        const auto tg0 = clk::now();
+        mmb_status gs = lm_graph_build(p, 0);
+        if (gs != MMB_OK) {
+            if (w->graph) { cudaGraphDestroy(w->graph); w->graph = nullptr; }
+            const std::string first = get_last_error();
+            gs = lm_graph_build(p, 1);
+            if (gs != MMB_OK) set_last_error(first + " | " + get_last_error());
+        }
+        if (gs != MMB_OK) {
+            if (w->graph) { cudaGraphDestroy(w->graph); w->graph = nullptr; }
+            // not fatal: the host-driven loop runs the same kernels
+            if (getenv("MMB_LM_GRAPH_STRICT")) return MMB_ERR_CUDA;
+            if (getenv("MMB_LM_GRAPH_VERBOSE")) fprintf(stderr, "[mmb] %s -> host-driven loop\n", get_last_error().c_str());
+            w->graph_failed = true;
+            use_graph = false;
+        } else if (getenv("MMB_LM_GRAPH_VERBOSE")) {
+            const auto tg1 = clk::now();
+            cudaGraphUpload(w->graph_exec, p->stream);
+            cudaStreamSynchronize(p->stream);
+            fprintf(stderr, "[mmb] LM graph: build+instantiate %.3f ms, upload %.3f ms\n", 1e3 * secs(tg0, tg1), 1e3 * secs(tg1, clk::now()));
+        }
+    }
+    double t_jac = 0, t_func = 0, t_lin = 0;
+    if (use_graph) {
+        MMB_CUDA_CHECK(cudaGraphLaunch(w->graph_exec, p->stream));
+        ++p->solve_graph_launches;
+    } else {
+        MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));  // h_st is reused as the read-back mirror
+        ++p->solve_host_syncs;
+        if ((st = lm_run_host_loop(p, res, &t_jac, &t_func, &t_lin)) != MMB_OK) return st;
     }
     // results (adjust_cminpack_lmder.cpp:185-197, adjust_base.cpp:1201-1282)
-    // errorDistanceList holds whatever the LAST measureErrors call left there (a
-    // rejected trial or the last FD perturbation included): dist2 tracks that.
-    if ((st = enqueue_error_stats(p, w->dist2)) != MMB_OK) return st;
-    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)hp.m, w->part_f);
-    LAUNCH_CHECK();
-    if ((st = all_reduce(p, w->part_f, kRedBlocks)) != MMB_OK) return st;
-    std::vector<double> part(kRedBlocks), x(hp.n);
-    MMB_CUDA_CHECK(cudaMemcpyAsync(part.data(), w->part_f, sizeof(double) * kRedBlocks, cudaMemcpyDeviceToHost, p->stream));
-    MMB_CUDA_CHECK(cudaMemcpyAsync(x.data(), p->d_x, sizeof(double) * hp.n, cudaMemcpyDeviceToHost, p->stream));
+    double *part = stage;            // [kRedBlocks]
+    double *x = stage + kRedBlocks;  // [n]
+    MMB_CUDA_CHECK(cudaMemcpyAsync(part, w->part_f, sizeof(double) * kRedBlocks, cudaMemcpyDeviceToHost, p->stream));
+    MMB_CUDA_CHECK(cudaMemcpyAsync(x, p->d_x, sizeof(double) * hp.n, cudaMemcpyDeviceToHost, p->stream));
     if (dist_out)
         MMB_CUDA_CHECK(cudaMemcpyAsync(dist_out, w->dist2, sizeof(double) * hp.nobs, cudaMemcpyDeviceToHost, p->stream));
     if ((st = read_state(p)) != MMB_OK) return st;
     const LmState &f = *w->h_st;
+    if (use_graph) {
+        if (f.cancelled) res->user_interrupted = 1;
+        t_jac = 1e-9 * (double)f.t_jac_ns; t_lin = 1e-9 * (double)f.t_lin_ns; t_func = 1e-9 * (double)f.t_func_ns;
+        p->launches += w->fixed_launches + (long long)f.n_body_loop * w->body_launches[0] +
+                       (long long)f.njev * w->body_launches[1] + (long long)f.n_body_lmpar * w->body_launches[2] +
+                       (long long)f.n_body_trial * w->body_launches[3];
+    }
     double ss = 0.0;
-    for (double v : part) ss += v;
+    for (int i = 0; i < kRedBlocks; ++i) ss += part[i];
     res->error_final = std::sqrt(ss);
-    res->success = func_evals > 0 ? 1 : 0;  // success = iterNum > 0
+    res->success = 1;  // success = iterNum > 0: the first function evaluation always runs
     res->reason_num = res->user_interrupted ? -1 : f.info;
     res->iteration_num = f.nfev;
-    res->iteration_function_num = func_evals;
-    res->iteration_jacobian_num = jac_evals;
+    res->iteration_function_num = f.nfev;  // iflag = 1 calls: the first evaluation + one per trial
+    res->iteration_jacobian_num = f.njev * hp.n * (hp.opt.auto_diff_type == 1 ? 2 : 1);
     res->iteration_attempt_num = f.njev;
     res->error_avg = f.err_avg; res->error_min = f.err_min; res->error_max = f.err_max;
     bool better = true;
-    if (hp.opt.accept_only_better) better = f.err_avg <= init_avg;
+    if (hp.opt.accept_only_better) better = f.err_avg <= f.init_avg;
     res->error_is_better = better ? 1 : 0;
     for (int i = 0; i < hp.n; ++i) {
         const int a = hp.par_attr[i];
@@ -804,7 +1085,6 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
                 w->phase_n, w->phase_ms[0] / w->phase_n, w->phase_ms[1] / w->phase_n, w->phase_ms[2] / w->phase_n, w->phase_ms[3] / w->phase_n);
         w->phase_n = 0; for (double &v : w->phase_ms) v = 0;
     }
-    (void)d;
     return MMB_OK;
 }
 

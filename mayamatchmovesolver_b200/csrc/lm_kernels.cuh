@@ -657,7 +657,11 @@ __global__ void __launch_bounds__(1024) k_backward_s(LmDims d, const double *__r
 // diagonal block and publishes.  The critical path is nblk x (flag + GEMV + 64-step
 // substitution in one warp); every CTA must be resident (cooperative launch, the host falls
 // back to the single-CTA kernels when the grid does not fit).  Flags carry an epoch so they
-// need no reset between launches.
+// need no reset between launches; the epoch counter lives in device memory (advanced by
+// k_ctrl_lmpar) so that the launch arguments are the same every time -- the launches can
+// be replayed from a CUDA graph.  A CTA only ever waits for CTAs of lower blockIdx, so
+// the plain (non-cooperative) launch used inside graph bodies cannot deadlock under
+// in-order block dispatch either.
 __device__ __forceinline__ void wave_publish(int *flag, int epoch) {
     __threadfence();
     __syncthreads();
@@ -714,8 +718,9 @@ __device__ __forceinline__ void wave_stage_diag(LmDims d, const double *__restri
 
 // backward: L^T p = y, y = augmented row ns of S.  blockIdx 0 owns the LAST block.
 __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *__restrict__ S, double *p, int *flags,
-                                                       int epoch) {
+                                                       const int *epoch_ctr, int slot) {
     extern __shared__ double sm[];
+    const int epoch = __ldcg(epoch_ctr) + slot;
     double *D = sm;                // 64 x kDS
     double *dinv = D + 64 * kDS;   // 64
     double *acc = dinv + 64;       // 64: right-hand side, then solution
@@ -756,8 +761,9 @@ __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *_
 
 // forward: L w = rhs for rows [0, ns).  rhs and w may alias.  blockIdx b owns block b.
 __global__ void __launch_bounds__(256) k_forward_wave(LmDims d, const double *__restrict__ S, const double *rhs, double *w,
-                                                      int *flags, int epoch) {
+                                                      int *flags, const int *epoch_ctr, int slot) {
     extern __shared__ double sm[];
+    const int epoch = __ldcg(epoch_ctr) + slot;
     double *D = sm;
     double *dinv = D + 64 * kDS;
     double *acc = dinv + 64;

@@ -6,7 +6,10 @@
 // structure of J^T J can be used (Schur complement + Cholesky).  Every
 // decision (lmpar iteration, ratio test, delta / par update, accept / reject,
 // convergence tests) is taken by single-thread control kernels on the device;
-// the host only reads the flags below to know what to enqueue next.
+// the host either replays one CUDA graph whose conditional (WHILE / IF) nodes
+// are steered by these flags -- no host round trip inside the solve -- or, for
+// a sharded solve (NCCL collectives between the kernels), reads the flags to
+// know what to enqueue next.
 #pragma once
 #include <stdint.h>
 
@@ -35,6 +38,12 @@ struct LmState {
     // statistics
     int n_factor;
     double err_avg, err_min, err_max;  // compute_error_stats (adjust_base.cpp:346)
+    double init_avg;                   // err_avg of the scene's own values (acceptOnlyBetter)
+    // device-resident loop (CUDA graph with conditional nodes): how often each body ran,
+    // and the device time of each phase (%globaltimer, ns) stamped at the phase boundaries
+    int n_body_jac, n_body_lmpar, n_body_trial, n_body_loop;
+    int cancelled;                     // the host's cancel flag was seen set
+    unsigned long long t_mark, t_jac_ns, t_lin_ns, t_func_ns;
 };
 
 }  // namespace mmb

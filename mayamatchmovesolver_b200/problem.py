@@ -222,3 +222,9 @@ class Problem:
 
     def launch_count(self):
         return int(self._lib.mmb_launch_count(self._h))
+
+    def solve_stats(self):
+        """-> (host synchronisations, CUDA graph launches) of the last solve on this handle"""
+        a, b = C.c_int64(), C.c_int64()
+        check(self._lib.mmb_solve_stats(self._h, C.byref(a), C.byref(b)), "mmb_solve_stats")
+        return a.value, b.value

@@ -1,10 +1,9 @@
-"""One cfg3-shaped global solve with the LM phase timers on (MMB_LM_PROFILE=1)."""
+"""One cfg3-shaped global solve; MMB_LM_PROFILE=1 turns the LM phase timers on (host-driven loop)."""
 import os
 import sys
 import time
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-os.environ.setdefault("MMB_LM_PROFILE", "1")
 from mayamatchmovesolver_b200 import synth  # noqa: E402
 from mayamatchmovesolver_b200.problem import Problem  # noqa: E402
 
@@ -19,5 +18,6 @@ for rep in range(2):
         r = p.solve()
         t2 = time.perf_counter()
         n = p.launch_count()
-    print("create %.4f s, solve %.4f s (jac %.4f, func %.4f, linear %.4f), launches %d: %r, LM iterations %d" %
-          (t1 - t0, t2 - t1, r.timer_jacobian_s, r.timer_function_s, r.timer_linear_s, n, r, r.iteration_attempt_num))
+        stats = p.solve_stats()
+    print("create %.4f s, solve %.4f s (jac %.4f, func %.4f, linear %.4f), launches %d: %r, LM iterations %d, host syncs %d, graph launches %d" %
+          (t1 - t0, t2 - t1, r.timer_jacobian_s, r.timer_function_s, r.timer_linear_s, n, r, r.iteration_attempt_num, stats[0], stats[1]))
