@@ -308,6 +308,12 @@ int64_t mmb_launch_count(const mmb_problem *p);
 mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs,
                            int64_t *graph_launches);
 
+/* Device buffers come from the device's stream-ordered memory pool and stay
+ * cached there when a handle is destroyed, so the next mmb_problem_create of a
+ * session (the reference calls mmSolver once per solver step) does not pay for
+ * allocation again.  This hands the cached memory back to the driver. */
+mmb_status mmb_release_cached_memory(int32_t device);
+
 const char *mmb_status_string(mmb_status s);
 /* detail of the last failing call on this thread (static storage) */
 const char *mmb_last_error(void);

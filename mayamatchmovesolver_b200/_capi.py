@@ -94,6 +94,7 @@ SYMBOLS = [
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),
     ("mmb_solve_stats", C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    ("mmb_release_cached_memory", C.c_int32, [C.c_int32]),
     ("mmb_status_string", C.c_char_p, [C.c_int32]),
     ("mmb_last_error", C.c_char_p, []),
     ("mmb_version", C.c_char_p, []),

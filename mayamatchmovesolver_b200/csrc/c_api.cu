@@ -374,6 +374,16 @@ mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs, int64_t *g
     return MMB_OK;
 }
 
+mmb_status mmb_release_cached_memory(int32_t device) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;
+    if (device < 0 || device >= ndev) return MMB_ERR_INVALID_ARGUMENT;
+    cudaMemPool_t pool = nullptr;
+    MMB_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
+    MMB_CUDA_CHECK(cudaMemPoolTrimTo(pool, 0));
+    return MMB_OK;
+}
+
 const char *mmb_status_string(mmb_status s) {
     switch (s) {
         case MMB_OK: return "ok";

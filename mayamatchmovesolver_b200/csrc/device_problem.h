@@ -24,13 +24,21 @@ namespace mmb {
 void set_last_error(const std::string &msg);
 const std::string &get_last_error();
 
-// Simple arena of device allocations freed together.
+// Arena of device allocations freed together.  Allocations come from the device's
+// stream-ordered memory pool (cudaMallocAsync) on the handle's stream; the pool's release
+// threshold is raised so that the memory of a destroyed handle is kept for the next one
+// (mmSolver is called once per solver step: create / solve / destroy repeats with the same
+// shapes).  mmb_release_cached_memory() trims the pool.  Uploads are asynchronous copies
+// on the same stream (a pageable source is staged before the call returns, so the caller
+// may free it right away).
 struct DeviceArena {
     std::vector<void *> ptrs;
     size_t bytes = 0;
+    cudaStream_t stream = nullptr;
     ~DeviceArena() { release(); }
+    void bind(cudaStream_t s) { stream = s; }
     void release() {
-        for (void *p : ptrs) cudaFree(p);
+        for (void *p : ptrs) cudaFreeAsync(p, stream);
         ptrs.clear();
         bytes = 0;
     }
@@ -39,7 +47,7 @@ struct DeviceArena {
         *out = nullptr;
         if (count == 0) count = 1;
         void *p = nullptr;
-        cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+        cudaError_t e = cudaMallocAsync(&p, count * sizeof(T), stream);
         if (e != cudaSuccess) return e;
         ptrs.push_back(p);
         bytes += count * sizeof(T);
@@ -50,7 +58,7 @@ struct DeviceArena {
     cudaError_t upload(T **out, const std::vector<T> &v) {
         cudaError_t e = alloc(out, v.size());
         if (e != cudaSuccess) return e;
-        if (!v.empty()) e = cudaMemcpy(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+        if (!v.empty()) e = cudaMemcpyAsync(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, stream);
         return e;
     }
 };

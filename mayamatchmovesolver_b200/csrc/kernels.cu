@@ -47,6 +47,19 @@ __global__ void __launch_bounds__(256) k_jacobian(DevScene s, double *fvec, doub
     if (i < s.nobs) jacobian_thread(s, i, fvec, dist, jac, cols, dist_last);
 }
 
+// frame-blocked copy of the marker tracks for k_jacobian_rows: block fb holds, marker by
+// marker, kRowFrames x-values, kRowFrames y-values, kRowFrames weights (one contiguous run
+// per CTA tile).  Built once per handle from the observation arrays already in HBM.
+__global__ void __launch_bounds__(256) k_block_markers(const double *__restrict__ mx, const double *__restrict__ my,
+                                                       const double *__restrict__ w, int M, int F,
+                                                       double *__restrict__ blk) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= (long long)M * F) return;
+    const int mk = (int)(i / F), f = (int)(i - (long long)mk * F);
+    double *dst = &blk[(((size_t)(f / kRowFrames) * M + mk) * 3) * kRowFrames + (f % kRowFrames)];
+    dst[0] = mx[i]; dst[kRowFrames] = my[i]; dst[2 * kRowFrames] = w[i];
+}
+
 // ---- launchers -------------------------------------------------------------
 static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
@@ -160,8 +173,8 @@ DeviceProblem::~DeviceProblem() {
     if (lm) lm_workspace_destroy(lm);
     const auto t1 = std::chrono::steady_clock::now();
     if (comm) { if (stream) cudaStreamSynchronize(stream); delete comm; }
-    if (stream) cudaStreamDestroy(stream);
-    arena.release();
+    arena.release();  // stream-ordered frees: back to the pool once the stream's work is done
+    if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
     if (timing)
         fprintf(stderr, "[mmb timing] destroy: LM workspace %.3f ms, scene buffers %.3f ms\n",
                 1e3 * std::chrono::duration<double>(t1 - t0).count(),
@@ -174,8 +187,8 @@ mmb_status ensure_jacobian_buffers(DeviceProblem *p) {
     MMB_CUDA_CHECK(p->arena.alloc(&p->d_jac, k * (size_t)p->hp.m));
     MMB_CUDA_CHECK(p->arena.alloc(&p->d_cols, k * (size_t)p->hp.nobs));
     // the tiled kernel never touches unused columns: they stay 0 / -1
-    MMB_CUDA_CHECK(cudaMemset(p->d_jac, 0, sizeof(double) * k * (size_t)p->hp.m));
-    MMB_CUDA_CHECK(cudaMemset(p->d_cols, 0xff, sizeof(int32_t) * k * (size_t)p->hp.nobs));
+    MMB_CUDA_CHECK(cudaMemsetAsync(p->d_jac, 0, sizeof(double) * k * (size_t)p->hp.m, p->stream));
+    MMB_CUDA_CHECK(cudaMemsetAsync(p->d_cols, 0xff, sizeof(int32_t) * k * (size_t)p->hp.nobs, p->stream));
     return MMB_OK;
 }
 
@@ -211,6 +224,13 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     } while (0)
     CK(cudaSetDevice(p->device));
     CK(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    {   // keep freed device memory in the pool for the next handle (see DeviceArena)
+        cudaMemPool_t pool = nullptr;
+        CK(cudaDeviceGetDefaultMemPool(&pool, p->device));
+        unsigned long long keep = ~0ull;
+        CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
+    p->arena.bind(p->stream);
     HostProblem &hp = p->hp;
     DevScene &d = p->ds;
     DeviceArena &A = p->arena;
@@ -276,7 +296,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
         PlanEntryD *dp = nullptr;
         CK(A.alloc(&dp, hp.plan.size()));
         if (!hp.plan.empty())
-            CK(cudaMemcpy(dp, hp.plan.data(), hp.plan.size() * sizeof(PlanEntry), cudaMemcpyHostToDevice));
+            CK(cudaMemcpyAsync(dp, hp.plan.data(), hp.plan.size() * sizeof(PlanEntry), cudaMemcpyHostToDevice, p->stream));
         d.plan = dp;
     }
     UP_I(mkr_k, hp.mkr_k);
@@ -344,15 +364,14 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             t.mk_blk = nullptr;
             if (hp.dense_grid) {  // frame-blocked copy of the marker tracks: one contiguous run per tile
                 const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
-                std::vector<double> blk((size_t)FB * hp.M * 3 * kRowFrames, 0.0);
-                for (int mk = 0; mk < hp.M; ++mk)
-                    for (int f = 0; f < hp.F; ++f) {
-                        const size_t i = (size_t)mk * hp.F + f;
-                        double *dst = &blk[(((size_t)(f / kRowFrames) * hp.M + mk) * 3) * kRowFrames + (f % kRowFrames)];
-                        dst[0] = hp.obs_mx[i]; dst[kRowFrames] = hp.obs_my[i]; dst[2 * kRowFrames] = hp.obs_w[i];
-                    }
+                const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
                 double *d_blk = nullptr;
-                CK(A.upload(&d_blk, blk)); t.mk_blk = d_blk;
+                CK(A.alloc(&d_blk, nblk));
+                CK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
+                k_block_markers<<<blocks_for((long long)hp.M * hp.F, 256), 256, 0, p->stream>>>(d.obs_mx, d.obs_my, d.obs_w, hp.M, hp.F, d_blk);
+                ++p->launches;
+                CK(cudaGetLastError());
+                t.mk_blk = d_blk;
             }
             t.last_attr_cam_var = -1;
             for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;

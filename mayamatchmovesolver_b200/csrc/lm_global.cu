@@ -20,6 +20,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "comm.h"
 #include "lm.h"
@@ -33,10 +34,37 @@ constexpr int kRedBlocks = 592;  // 148 SMs x 4 partial-sum blocks
 constexpr int kRedScal = 8, kRedMax = 4;
 constexpr int kStatBlocks = 148;
 
+// One pinned (mapped) host block per workspace: [LmState mirror | cancel flag | staging].
+// Pinning is slow (~1 ms), so the block of a destroyed workspace is kept for the next one.
+struct PinnedBlock { void *ptr = nullptr; size_t bytes = 0; };
+static std::mutex g_pinned_mu;
+static PinnedBlock g_pinned_spare;
+static cudaError_t pinned_acquire(size_t bytes, PinnedBlock *out) {
+    {
+        std::lock_guard<std::mutex> lk(g_pinned_mu);
+        if (g_pinned_spare.ptr && g_pinned_spare.bytes >= bytes) {
+            *out = g_pinned_spare;
+            g_pinned_spare = PinnedBlock{};
+            return cudaSuccess;
+        }
+    }
+    out->bytes = bytes;
+    return cudaHostAlloc(&out->ptr, bytes, cudaHostAllocMapped | cudaHostAllocPortable);
+}
+static void pinned_release(PinnedBlock b) {
+    if (!b.ptr) return;
+    {
+        std::lock_guard<std::mutex> lk(g_pinned_mu);
+        if (!g_pinned_spare.ptr || g_pinned_spare.bytes < b.bytes) std::swap(g_pinned_spare, b);
+    }
+    if (b.ptr) cudaFreeHost(b.ptr);
+}
+
 struct LmWorkspace {
     LmDims d{};
     DeviceArena arena;
     LmState *st = nullptr;     // device
+    PinnedBlock pinned;        // backs h_st, h_cancel, h_stage
     LmState *h_st = nullptr;   // pinned host mirror
     int32_t *attr_slot = nullptr, *i2p = nullptr;
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
@@ -75,9 +103,7 @@ struct LmWorkspace {
     ~LmWorkspace() {
         if (graph_exec) cudaGraphExecDestroy(graph_exec);
         if (graph) cudaGraphDestroy(graph);
-        if (h_st) cudaFreeHost(h_st);
-        if (h_cancel) cudaFreeHost(h_cancel);
-        if (h_stage) cudaFreeHost(h_stage);
+        pinned_release(pinned);
     }
 };
 
@@ -467,6 +493,7 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     d.KE = hp.F * hp.na; d.KEP = ((d.KE + kSyrkKT - 1) / kSyrkKT) * kSyrkKT;
     d.n = hp.n; d.nobs = hp.nobs; d.m = hp.m; d.kmax = p->ds.kmax;
     DeviceArena &A = w->arena;
+    A.bind(p->stream);
 #define CKW(expr)                                                                \
     do {                                                                         \
         cudaError_t _e = (expr);                                                 \
@@ -477,18 +504,23 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         }                                                                        \
     } while (0)
     CKW(A.alloc(&w->st, 1));
-    CKW(cudaMallocHost((void **)&w->h_st, sizeof(LmState)));
-    CKW(cudaHostAlloc((void **)&w->h_cancel, sizeof(int), cudaHostAllocMapped));
-    *w->h_cancel = 0;
-    CKW(cudaMallocHost((void **)&w->h_stage, sizeof(double) * (size_t)(2 * d.n + kRedBlocks)));
-    CKW(cudaHostGetDevicePointer((void **)&w->d_cancel, w->h_cancel, 0));
+    {
+        const size_t st_bytes = (sizeof(LmState) + 255) / 256 * 256;
+        CKW(pinned_acquire(st_bytes + 256 + sizeof(double) * (size_t)(2 * d.n + kRedBlocks), &w->pinned));
+        char *base = (char *)w->pinned.ptr;
+        w->h_st = (LmState *)base;
+        w->h_cancel = (int *)(base + st_bytes);
+        w->h_stage = (double *)(base + st_bytes + 256);
+        *w->h_cancel = 0;
+        CKW(cudaHostGetDevicePointer((void **)&w->d_cancel, w->h_cancel, 0));
+    }
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
     CKW(A.alloc(&w->U, (size_t)d.F * d.na * d.na));
     CKW(A.alloc(&w->gE, (size_t)d.KE));
     CKW(A.alloc(&w->W, (size_t)d.KE * d.NSP));
     CKW(A.alloc(&w->Y, (size_t)d.KEP * d.NSP));
-    CKW(cudaMemset(w->Y, 0, sizeof(double) * std::max<size_t>((size_t)d.KEP * d.NSP, 1)));
+    CKW(cudaMemsetAsync(w->Y, 0, sizeof(double) * std::max<size_t>((size_t)d.KEP * d.NSP, 1), p->stream));
     CKW(A.alloc(&w->V, (size_t)d.NSP * d.NSP));
     CKW(A.alloc(&w->S, (size_t)d.NSP * d.NSP));
     CKW(A.alloc(&w->Lf, (size_t)d.F * d.na * d.na));
@@ -515,9 +547,9 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     {
         const int nblk = std::max(1, (d.ns + kNB - 1) / kNB);
         CKW(A.alloc(&w->wave_flags, (size_t)d.NSP / 64 + 1));
-        CKW(cudaMemset(w->wave_flags, 0, sizeof(int) * ((size_t)d.NSP / 64 + 1)));
+        CKW(cudaMemsetAsync(w->wave_flags, 0, sizeof(int) * ((size_t)d.NSP / 64 + 1), p->stream));
         CKW(A.alloc(&w->wave_ctr, 1));
-        CKW(cudaMemset(w->wave_ctr, 0, sizeof(int)));
+        CKW(cudaMemsetAsync(w->wave_ctr, 0, sizeof(int), p->stream));
         CKW(cudaFuncSetAttribute(k_backward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemBwd));
         CKW(cudaFuncSetAttribute(k_forward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemFwd));
         int coop = 0, sms = 0, occ_b = 0, occ_f = 0;

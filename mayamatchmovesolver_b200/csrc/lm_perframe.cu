@@ -391,6 +391,7 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     if ((st = ensure_jacobian_buffers(p)) != MMB_OK) return st;
     const auto t0 = std::chrono::steady_clock::now();
     DeviceArena A;
+    A.bind(p->stream);
     // observations grouped by frame
     std::vector<int32_t> start(hp.F + 1, 0), ids(hp.nobs);
     for (int i = 0; i < hp.nobs; ++i) start[hp.err_frame[i] + 1]++;

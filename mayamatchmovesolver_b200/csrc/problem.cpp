@@ -72,15 +72,28 @@ static void chain_refs(const HostProblem &hp, int t, std::vector<int32_t> &out) 
     }
 }
 
-static void deps_from_refs(const HostProblem &hp, const std::vector<int32_t> &refs,
+// Solver attributes that write one of `refs` (sorted attr indices).  ref_attrs maps an
+// attribute-store reference to the solver attributes naming it (duplicates allowed), so the
+// cost is O(refs) per entity instead of a scan over all A attributes.
+struct RefAttrs {
+    std::vector<std::vector<int32_t>> stat, anim;
+    const std::vector<int32_t> *find(int32_t r) const {
+        if (r == MMB_ATTR_NONE) return nullptr;
+        if (r >= 0) return (size_t)r < stat.size() ? &stat[r] : nullptr;
+        const size_t i = (size_t)(-(int64_t)r - 1);
+        return i < anim.size() ? &anim[i] : nullptr;
+    }
+};
+static void deps_from_refs(const RefAttrs &ra, const std::vector<int32_t> &refs,
                            std::vector<int32_t> &deps, uint8_t &varies) {
-    std::set<int32_t> rs(refs.begin(), refs.end());
     deps.clear();
     varies = 0;
-    for (int32_t r : rs)
+    for (int32_t r : refs) {
         if (r != MMB_ATTR_NONE && r < 0) varies = 1;
-    for (int a = 0; a < hp.A; ++a)
-        if (rs.count(hp.attr_ref[a])) deps.push_back(a);
+        if (const std::vector<int32_t> *v = ra.find(r)) deps.insert(deps.end(), v->begin(), v->end());
+    }
+    std::sort(deps.begin(), deps.end());
+    deps.erase(std::unique(deps.begin(), deps.end()), deps.end());
 }
 
 mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
@@ -169,23 +182,30 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     // ---- countUpNumberOfErrors (marker-major, frame-minor) ---------------
     std::vector<double> wmax(F, 0.0);
     std::vector<uint8_t> wseen(F, 0);
-    hp.err_marker.clear(); hp.err_frame.clear();
-    hp.obs_mx.clear(); hp.obs_my.clear(); hp.obs_w.clear();
-    for (int i = 0; i < hp.M; ++i) {
-        for (size_t j = 0; j < F; ++j) {
-            const size_t o = (size_t)i * F + j;
-            const bool enable = s->mkr_enable[o] != 0;
-            const double weight = s->mkr_weight[o];
-            if (enable && (weight > 0.0)) {
-                hp.err_marker.push_back(i);
-                hp.err_frame.push_back((int32_t)j);
-                hp.obs_w.push_back(weight);
-                hp.obs_mx.push_back(s->mkr_x[o]);
-                hp.obs_my.push_back(s->mkr_y[o]);
-                if (!wseen[j] || weight > wmax[j]) wmax[j] = weight;
-                wseen[j] = 1;
+    {
+        const size_t cap = (size_t)hp.M * F;
+        hp.err_marker.resize(cap); hp.err_frame.resize(cap);
+        hp.obs_mx.resize(cap); hp.obs_my.resize(cap); hp.obs_w.resize(cap);
+        size_t k = 0;
+        for (int i = 0; i < hp.M; ++i) {
+            const size_t o0 = (size_t)i * F;
+            for (size_t j = 0; j < F; ++j) {
+                const size_t o = o0 + j;
+                const double weight = s->mkr_weight[o];
+                if (s->mkr_enable[o] != 0 && (weight > 0.0)) {
+                    hp.err_marker[k] = i;
+                    hp.err_frame[k] = (int32_t)j;
+                    hp.obs_w[k] = weight;
+                    hp.obs_mx[k] = s->mkr_x[o];
+                    hp.obs_my[k] = s->mkr_y[o];
+                    ++k;
+                    if (!wseen[j] || weight > wmax[j]) wmax[j] = weight;
+                    wseen[j] = 1;
+                }
             }
         }
+        hp.err_marker.resize(k); hp.err_frame.resize(k);
+        hp.obs_mx.resize(k); hp.obs_my.resize(k); hp.obs_w.resize(k);
     }
     hp.nobs = (int)hp.err_marker.size();
     hp.m = 2 * hp.nobs;
@@ -229,11 +249,17 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     hp.cam_deps.assign(hp.C, {}); hp.bnd_deps.assign(hp.B, {}); hp.lens_deps.assign(hp.L, {});
     hp.cam_varies.assign(hp.C, 0); hp.bnd_varies.assign(hp.B, 0); hp.lens_varies.assign(hp.L, 0);
     hp.cam_mscale_varies.assign(hp.C, 0);
+    RefAttrs ra;
+    ra.stat.resize(hp.num_static); ra.anim.resize(hp.num_anim);
+    for (int a = 0; a < hp.A; ++a) {
+        const int32_t r = hp.attr_ref[a];
+        if (r >= 0) ra.stat[r].push_back(a); else ra.anim[(size_t)(-(int64_t)r - 1)].push_back(a);
+    }
     for (int c = 0; c < hp.C; ++c) {
         std::vector<int32_t> refs;
         chain_refs(hp, hp.cam_tfm[c], refs);
         for (int k = 0; k < MMB_CAM_ATTRS; ++k) refs.push_back(hp.cam_attrs[c * MMB_CAM_ATTRS + k]);
-        deps_from_refs(hp, refs, hp.cam_deps[c], hp.cam_varies[c]);
+        deps_from_refs(ra, refs, hp.cam_deps[c], hp.cam_varies[c]);
         for (int a : hp.cam_deps[c])
             if (hp.attr_ref[a] == hp.cam_attrs[c * MMB_CAM_ATTRS + 0] || hp.attr_ref[a] == hp.cam_attrs[c * MMB_CAM_ATTRS + 1])
                 hp.cam_mscale_varies[c] = 1;
@@ -241,13 +267,13 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     for (int b = 0; b < hp.B; ++b) {
         std::vector<int32_t> refs;
         chain_refs(hp, hp.bnd_tfm[b], refs);
-        deps_from_refs(hp, refs, hp.bnd_deps[b], hp.bnd_varies[b]);
+        deps_from_refs(ra, refs, hp.bnd_deps[b], hp.bnd_varies[b]);
     }
     hp.any_lens = false;
     for (int l = 0; l < hp.L; ++l) {
         std::vector<int32_t> refs;
         for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k) refs.push_back(hp.lens_attrs[l * MMB_LENS_MAX_COEFFS + k]);
-        deps_from_refs(hp, refs, hp.lens_deps[l], hp.lens_varies[l]);
+        deps_from_refs(ra, refs, hp.lens_deps[l], hp.lens_varies[l]);
     }
     for (int c = 0; c < hp.C; ++c)
         if (hp.cam_lens[c] >= 0 && hp.lens_model[hp.cam_lens[c]] != MMB_LENS_PASSTHROUGH) hp.any_lens = true;
