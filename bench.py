@@ -30,7 +30,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WORKLOAD = "cfg3: global camera+bundle solve, 1000 frames x 500 bundles (n=7500, 500000 observations per GPU)"
+WORKLOAD = "cfg3: global camera+bundle solve, 1000 frames x 500 bundles per GPU (n=7500, 500000 observations per GPU)"
 CPU_SAMPLE = dict(F=40, B=40, seed=3)   # bounded sample of the same workload for the CPU legs
 
 
@@ -136,17 +136,38 @@ def run_own(args):
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from mayamatchmovesolver_b200 import synth
-    from mayamatchmovesolver_b200.problem import Problem
+    from mayamatchmovesolver_b200.distributed import SingleGroup, TorchGroup
+    from mayamatchmovesolver_b200.problem import Problem, comm_unique_id
 
-    F, B = 1000, 500
-    sb, _ = synth.make_scene(F, B, 3 + rank)
-    p = Problem(sb, device=local)
+    group = TorchGroup() if dist is not None else SingleGroup()
+    # Weak scaling: ONE scene of 1000 x N frames, frame-range shards of 1000 frames per GPU
+    # (SURVEY.md 8e).  Every rank builds the same scene from the same seed.
+    F1, B = 1000, 500
+    F = F1 * world
+    sb, _ = synth.make_scene(F, B, 3)
+    p = Problem(sb, device=local, shard=(rank, world)) if world > 1 else Problem(sb, device=local)
     k = p.jacobian_kmax()
     bytes_per_obs = 48 + 16 * k  # marker 24 B + residuals 16 B + distance 8 B + 2*k*8 B block J
 
     def barrier():
         if dist is not None:
             dist.barrier()
+
+    def allmax(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        import torch
+        t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(v) for v in t.cpu()]
+
+    def allsum(vals):
+        if dist is None:
+            return [float(v) for v in vals]
+        import torch
+        t = torch.tensor(list(vals), device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(v) for v in t.cpu()]
 
     sampler = ClockSampler(local)
     for _ in range(args.warmup):
@@ -164,48 +185,72 @@ def run_own(args):
     t_wall = time.perf_counter() - t_wall0
     barrier()
     clocks = sampler.stop()
-    if dist is not None:
-        import torch
-        t = torch.tensor([tot_ms, jac_ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        tot_ms, jac_ms = float(t[0]), float(t[1])
-        lt = torch.tensor([launches], device="cuda", dtype=torch.int64)
-        dist.all_reduce(lt, op=dist.ReduceOp.SUM)
-        launches = int(lt[0])
-    evals_all = world * p.nobs * args.steps
-    value = evals_all / (tot_ms * 1e-3)
+    tot_ms, jac_ms = allmax([tot_ms, jac_ms])
+    launches, evals_per_step = allsum([launches, p.nobs])
+    value = evals_per_step * args.steps / (tot_ms * 1e-3)
     ms_per_step = tot_ms / args.steps
+    nobs_rank, n_rank = p.nobs, p.n
+    p.close()
 
     # ---- end to end through the public solve call, host buffers ----------
+    # N = 1: mmb_problem_create + mmb_solve + destroy (one CUDA graph launch per solve).
+    # N > 1: the sharded global solve of the N x 1000-frame scene: create_shard + attach_comm
+    # (NCCL) + mmb_solve with one all-reduce of the reduced system per lmpar trial + destroy.
+    E2E_REPS = 3
+
     def e2e_once(seed):
         sb2, _ = synth.make_scene(F, B, seed, noise_px=0.5)
         arrays = sb2.arrays()
         h2d = sum(a.nbytes for a in arrays.values())
+        cid = None
+        if world > 1:
+            cid = group.broadcast_bytes(comm_unique_id() if rank == 0 else None, src=0)
+        barrier()
         t0 = time.perf_counter()
-        with Problem(sb2, device=local, iter_max=20) as q:
+        q = Problem(sb2, device=local, iter_max=20, shard=(rank, world)) if world > 1 else Problem(sb2, device=local, iter_max=20)
+        with q:
+            if world > 1:
+                q.attach_comm(cid, rank, world)
             r = q.solve()
             d2h = 8 * (2 * q.n + q.nobs) + 160
             nobs = q.nobs
+            stats = q.solve_stats()
+            solve_launches = q.launch_count()
         dt = time.perf_counter() - t0
-        return r, dt, h2d, d2h, nobs
-    e2e_once(100 + rank)  # warm-up (module load, allocations)
-    barrier()
-    r, dt, h2d, d2h, nobs = e2e_once(200 + rank)
-    e2e_evals = nobs * r.iteration_attempt_num
-    stats = np.array([dt, r.timer_solve_s], dtype=np.float64)
-    if dist is not None:
-        import torch
-        t = torch.tensor(stats, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        stats = t.cpu().numpy()
-    e2e_value = world * e2e_evals / stats[0]
-    lm_iters_per_s = r.iteration_attempt_num / stats[1]
-    frames_per_s = world * F / stats[0]
+        return r, dt, h2d, d2h, nobs, stats, solve_launches
+    e2e_once(100)  # warm-up (module load, memory pool, NCCL communicator set-up)
+    e2e_dt = e2e_solve = 0.0
+    for rep in range(E2E_REPS):
+        r, dt, h2d, d2h, nobs, stats, solve_launches = e2e_once(200 + rep)
+        dt, ts = allmax([dt, r.timer_solve_s])
+        e2e_dt += dt
+        e2e_solve += ts
+    (nobs_all,) = allsum([nobs])
+    e2e_evals = nobs_all * r.iteration_attempt_num
+    e2e_value = e2e_evals * E2E_REPS / e2e_dt
+    lm_iters_per_s = r.iteration_attempt_num * E2E_REPS / e2e_solve
+    frames_per_s = F * E2E_REPS / e2e_dt
+
+    # ---- per-frame mode (cfg2): 240 x N frames x 50 bundles, frames sharded, no collective
+    def perframe_once(seed):
+        sbp, _ = synth.make_scene(240 * world, 50, seed, solve_bundles=False)
+        barrier()
+        t0 = time.perf_counter()
+        q = (Problem(sbp, device=local, frame_solve_mode=1, shard=(rank, world)) if world > 1
+             else Problem(sbp, device=local, frame_solve_mode=1))
+        with q:
+            agg, per = q.solve_per_frame()
+        return time.perf_counter() - t0, agg
+    perframe_once(2)
+    pf_dt, pf_agg = perframe_once(2)
+    (pf_dt,) = allmax([pf_dt])
 
     if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
         return
     peaks, peaks_src = _peaks()
-    algo_bytes = p.nobs * bytes_per_obs
+    algo_bytes = nobs_rank * bytes_per_obs
     achieved = algo_bytes / (jac_ms / args.steps * 1e-3) / 1e9
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic_k_jacobian.json")
@@ -216,19 +261,26 @@ def run_own(args):
         "metric": "marker-frame residual+FD-Jacobian evals/s", "value": value, "unit": "evals/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames": F, "bundles": B, "params": p.n, "observations_per_gpu": p.nobs,
+        "config": {"workload": WORKLOAD, "frames": F, "frames_per_gpu": F1, "bundles": B, "params_per_gpu": n_rank,
+                   "observations_per_gpu": nobs_rank,
                    "local_params_per_obs_k": k, "l2": "flushed before every step (256 MiB memset outside the event brackets)",
-                   "sharding": "independent frame-range shards per GPU, no data-path collective"},
+                   "sharding": "one scene of 1000 x N frames; frame-range shard of 1000 frames per GPU; no data-path collective in the evaluation step"},
         "clocks": clocks,
-        "gpu_launches": launches,
+        "gpu_launches": int(launches),
         "wall_s_timed_region": t_wall,
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "what": "mmb_problem_create + mmb_solve (iter_max=20) + destroy with host buffers; evals = observations x Jacobian evaluations",
-                "seconds": float(stats[0]), "lm_outer_iterations": r.iteration_attempt_num, "nfev": r.iteration_num,
-                "reason_num": r.reason_num, "error_avg_px": r.error_avg},
+                "what": ("mmb_problem_create + mmb_solve (iter_max=20) + destroy with host buffers, mean of %d solves; "
+                         "evals = observations x Jacobian evaluations" % E2E_REPS) +
+                        ("; sharded global solve, one NCCL all-reduce of the reduced system per lmpar trial" if world > 1 else ""),
+                "seconds": e2e_dt / E2E_REPS, "lm_outer_iterations": r.iteration_attempt_num, "nfev": r.iteration_num,
+                "reason_num": r.reason_num, "error_avg_px": r.error_avg,
+                "host_syncs_per_solve": stats[0], "graph_launches_per_solve": stats[1], "kernel_launches_per_solve": solve_launches},
         "lm_iters_per_s": lm_iters_per_s,
         "solved_frames_per_s": frames_per_s,
-        "roofline": {"bound": "hbm", "kernel": "k_jacobian", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+        "per_frame_mode": {"workload": "cfg2: %d frames x 50 bundles, one LM solve per frame (n=6, m=100 each), one launch" % (240 * world),
+                           "solved_frames_per_s": 240 * world / pf_dt, "seconds": pf_dt,
+                           "error_avg_px": pf_agg.error_avg, "what": "create + mmb_solve_per_frame + destroy, host buffers"},
+        "roofline": {"bound": "hbm", "kernel": "k_jacobian_rows", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                      "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes,
                      "peak_source": peaks_src, "kernel_ms": jac_ms / args.steps},
     }

@@ -83,6 +83,8 @@ struct LmWorkspace {
     long long n_allreduce = 0;
     int *wave_flags = nullptr;   // [NSP / 64] epoch flags of the wavefront triangular solves
     int *wave_ctr = nullptr;     // device epoch counter (k_ctrl_lmpar adds 2 per lmpar step)
+    int *tile_flags = nullptr;   // [(NSP/64)^2] epoch flags of the tile-dataflow Cholesky
+    bool chol_tiles = true;      // one-launch tile-dataflow Cholesky (MMB_CHOL=steps: two launches per block step)
     double *h_stage = nullptr;   // pinned staging: [max(2 n, kRedBlocks + n)]
     int *h_cancel = nullptr;     // pinned, mapped: set by mmb_request_cancel, polled by the loop-head kernel
     int *d_cancel = nullptr;     // device alias of h_cancel
@@ -548,6 +550,14 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         const int nblk = std::max(1, (d.ns + kNB - 1) / kNB);
         CKW(A.alloc(&w->wave_flags, (size_t)d.NSP / 64 + 1));
         CKW(cudaMemsetAsync(w->wave_flags, 0, sizeof(int) * ((size_t)d.NSP / 64 + 1), p->stream));
+        {
+            const size_t nt = ((size_t)d.NSP / 64) * ((size_t)d.NSP / 64);
+            CKW(A.alloc(&w->tile_flags, nt));
+            CKW(cudaMemsetAsync(w->tile_flags, 0, sizeof(int) * nt, p->stream));
+            CKW(cudaFuncSetAttribute(k_chol_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
+            const char *e = getenv("MMB_CHOL");
+            w->chol_tiles = !(e && !strcmp(e, "steps"));
+        }
         CKW(A.alloc(&w->wave_ctr, 1));
         CKW(cudaMemsetAsync(w->wave_ctr, 0, sizeof(int), p->stream));
         CKW(cudaFuncSetAttribute(k_backward_wave, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWaveSmemBwd));
@@ -714,8 +724,13 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     const int nb = d.NSP / 64;
     if (d.KE) {
         const int tiles = nb * (nb + 1) / 2;
+        // 300 tiles on 148 SMs leave some SMs with 3 CTAs and most with 2 (measured 0.72 ms); 16 x
+        // 148 CTAs of an eighth of the K range balance the tensor pipe (0.50 ms).  K splits add
+        // their partial sums with atomics.
         int ksplit = 1;
-        while (tiles * ksplit < 296 && ksplit < 16 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
+        static int ks_target = -1;
+        if (ks_target < 0) { const char *e = getenv("MMB_SYRK_CTAS"); ks_target = e ? atoi(e) : 2368; }
+        while (tiles * ksplit < ks_target && ksplit < 16 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
         k_schur_syrk<<<dim3(tiles, ksplit), 128, 0, s>>>(d, w->Y, w->S);
         LAUNCH_CHECK();
     }
@@ -727,12 +742,17 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
     }
     if (prof) cudaEventRecord(w->ev[1], s);
-    for (int kb = 0; kb < nb; ++kb) {
-        k_chol_panel<<<nb - kb, 256, kCholPanelSmem, s>>>(d, kb, w->st, w->S, w->Ld);
+    if (w->chol_tiles) {
+        k_chol_tiles<<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr);
         LAUNCH_CHECK();
-        const int nt = nb - kb - 1;
-        k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
-        LAUNCH_CHECK();
+    } else {
+        for (int kb = 0; kb < nb; ++kb) {
+            k_chol_panel<<<nb - kb, 256, kCholPanelSmem, s>>>(d, kb, w->st, w->S, w->Ld);
+            LAUNCH_CHECK();
+            const int nt = nb - kb - 1;
+            k_chol_trailing<<<std::max(1, nt * (nt + 1) / 2), 128, 0, s>>>(d, kb, w->S, w->Ld);
+            LAUNCH_CHECK();
+        }
     }
     if (prof) cudaEventRecord(w->ev[2], s);
     if ((rs = enqueue_backward_s(p, w->p_int + d.KE)) != MMB_OK) return rs;

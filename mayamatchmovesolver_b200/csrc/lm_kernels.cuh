@@ -299,8 +299,8 @@ __device__ __forceinline__ void tile_index(int t, int &bi, int &bj) {
 // (partial sums are subtracted with atomics only when grid.y > 1).
 constexpr int kSyrkKT = 16;
 __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S) {
-    __shared__ double sA[2][kSyrkKT * kTS];
-    __shared__ double sB[2][kSyrkKT * kTS];
+    __shared__ __align__(16) double sA[2][kSyrkKT * kTS];
+    __shared__ __align__(16) double sB[2][kSyrkKT * kTS];
     int bi, bj;
     tile_index(blockIdx.x, bi, bj);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -313,25 +313,36 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     const int ksteps = d.KEP / kSyrkKT;
     const int per = (ksteps + gridDim.y - 1) / gridDim.y;
     const int ks0 = blockIdx.y * per, ks1 = min(ksteps, ks0 + per);
-    // each thread loads 8 doubles of each operand tile per step: 16 rows x 64 cols
-    auto load = [&](int buf, int ks) {
+    // each thread moves 8 doubles of each operand tile per step (16 rows x 64 cols).  The
+    // global loads of step ks+1 are issued before the DMMAs of step ks and land in shared
+    // memory after them, so the L2 latency hides behind the tensor pipe.
+    double2 ra[4], rb[4];
+    auto fetch = [&](int ks) {
         const int kbase = ks * kSyrkKT;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
             const int idx = threadIdx.x + t * 128;  // 0..511 double2 slots
             const int row = idx >> 5, c2 = (idx & 31) * 2;
-            const double2 va = *reinterpret_cast<const double2 *>(&Y[(size_t)(kbase + row) * d.NSP + bi * 64 + c2]);
-            const double2 vb = *reinterpret_cast<const double2 *>(&Y[(size_t)(kbase + row) * d.NSP + bj * 64 + c2]);
-            sA[buf][row * kTS + c2] = va.x; sA[buf][row * kTS + c2 + 1] = va.y;
-            sB[buf][row * kTS + c2] = vb.x; sB[buf][row * kTS + c2 + 1] = vb.y;
+            ra[t] = *reinterpret_cast<const double2 *>(&Y[(size_t)(kbase + row) * d.NSP + bi * 64 + c2]);
+            if (bi != bj) rb[t] = *reinterpret_cast<const double2 *>(&Y[(size_t)(kbase + row) * d.NSP + bj * 64 + c2]);
         }
     };
-    if (ks0 < ks1) load(0, ks0);
+    auto commit = [&](int buf) {
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int idx = threadIdx.x + t * 128;
+            const int row = idx >> 5, c2 = (idx & 31) * 2;
+            *reinterpret_cast<double2 *>(&sA[buf][row * kTS + c2]) = ra[t];
+            if (bi != bj) *reinterpret_cast<double2 *>(&sB[buf][row * kTS + c2]) = rb[t];
+        }
+    };
+    if (ks0 < ks1) { fetch(ks0); commit(0); }
     __syncthreads();
     for (int ks = ks0; ks < ks1; ++ks) {
         const int buf = (ks - ks0) & 1;
-        if (ks + 1 < ks1) load(buf ^ 1, ks + 1);
-        tile_mma<kSyrkKT>(sA[buf], sB[buf], wr, wc, lane, acc);
+        if (ks + 1 < ks1) fetch(ks + 1);
+        tile_mma<kSyrkKT>(sA[buf], bi != bj ? sB[buf] : sA[buf], wr, wc, lane, acc);
+        if (ks + 1 < ks1) commit(buf ^ 1);
         __syncthreads();
     }
     if (gridDim.y == 1) {
@@ -547,6 +558,214 @@ __global__ void __launch_bounds__(128) k_chol_trailing(LmDims d, int kb, double 
         __syncthreads();
     }
     tile_store_sub(S, d.NSP, bi, bj, wr, wc, lane, acc);
+}
+
+// ---- tile-dataflow Cholesky: the whole factorisation of S in ONE launch ------------------
+// The step-by-step kernels above cost two launches per 64-column block step and every step
+// waits for the slowest tile of the previous one.  Here every 64x64 tile (i, j), i >= j, of
+// the lower triangle has its own CTA (left-looking, owner computes):
+//   A.  acc = sum_{k<j} L(i,k) L(j,k)^T on the tensor cores, consuming each pair of tiles as
+//       soon as their owners publish them (per-tile epoch flags, acquire / release);
+//   B.  X = S(i,j) - acc in shared memory;
+//   C.  i == j: Cholesky of X (8x8 sub-blocked, register pivot blocks), publish L(j,j);
+//       i >  j: wait for L(j,j), X <- X L(j,j)^-T, publish L(i,j).
+// The critical path per block column is potrf -> trsm of the tile below -> one tile update,
+// everything else overlaps.  CTAs are numbered column by column, so a tile only ever waits
+// for tiles of LOWER blockIdx: under in-order block dispatch no cooperative launch is
+// needed and the kernel can sit in a CUDA-graph body.  Tiles published by other CTAs are
+// read with ld.global.cg (L2): an SM's L1 may still hold the pre-factorisation lines.
+constexpr int kOS = 68;   // operand tile stride: (stride mod 16) == 4 -> conflict-free DMMA fragment loads
+constexpr size_t kCholTilesSmem = sizeof(double) * (2 * 64 * kOS + 64) + 16;
+
+__global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
+                                                    const int *epoch_ctr) {
+    extern __shared__ __align__(16) double sm[];
+    double *sA = sm;                 // L(i,k) during phase A; afterwards T (stride kCS)
+    double *sB = sm + 64 * kOS;      // L(j,k) during phase A; afterwards X (stride kCS)
+    double *dinv_s = sB + 64 * kOS;  // 1 / L(j,j)[c][c]
+    const int nb = d.NSP / 64;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int epoch = __ldcg(epoch_ctr) + 1;
+    // column-major tile numbering: column j holds nb - j tiles
+    int j = 0, t = blockIdx.x;
+    while (t >= nb - j) { t -= nb - j; ++j; }
+    const int i = j + t;
+    const bool diag = i == j;
+    const size_t ld = (size_t)d.NSP;
+    int *flags = tile_flags;
+    // ---- A: left-looking update on the tensor cores ----
+    const int wr = warp >> 1, wc = warp & 1;   // warp tile: rows wr*16.., cols wc*32..
+    const int g = lane >> 2, q = lane & 3;
+    double acc[2][4][2];
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+    for (int k = 0; k < j; ++k) {
+        if (tid == 0) {
+            int v;
+            const int *f1 = &flags[k * nb + i], *f2 = &flags[k * nb + j];
+            do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f1) : "memory"); } while (v != epoch);
+            if (!diag) do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f2) : "memory"); } while (v != epoch);
+        }
+        __syncthreads();  // also: everyone is done with the previous k's operands
+        // 64 x 64 doubles per operand = 2048 double2; 8 per thread
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = tid + u * 256;
+            const int r = idx >> 5, c2 = (idx & 31) * 2;
+            const double2 va = __ldcg(reinterpret_cast<const double2 *>(&S[(size_t)(i * 64 + r) * ld + k * 64 + c2]));
+            *reinterpret_cast<double2 *>(&sA[r * kOS + c2]) = va;
+            if (!diag) {
+                const double2 vb = __ldcg(reinterpret_cast<const double2 *>(&S[(size_t)(j * 64 + r) * ld + k * 64 + c2]));
+                *reinterpret_cast<double2 *>(&sB[r * kOS + c2]) = vb;
+            }
+        }
+        __syncthreads();
+        const double *pB = diag ? sA : sB;
+#pragma unroll 4
+        for (int k0 = 0; k0 < 64; k0 += 4) {
+            double a[2], b[4];
+#pragma unroll
+            for (int u = 0; u < 2; ++u) a[u] = sA[(wr * 16 + u * 8 + g) * kOS + k0 + q];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) b[u] = pB[(wc * 32 + u * 8 + g) * kOS + k0 + q];
+#pragma unroll
+            for (int ti = 0; ti < 2; ++ti)
+#pragma unroll
+                for (int tj = 0; tj < 4; ++tj) dmma884(acc[ti][tj][0], acc[ti][tj][1], a[ti], b[tj]);
+        }
+    }
+    __syncthreads();
+    // ---- B: X = S(i,j) - acc (stride kCS) ----
+    double *T = sA, *X = sB;
+    double *dst = diag ? T : X;
+#pragma unroll
+    for (int ti = 0; ti < 2; ++ti)
+#pragma unroll
+        for (int tj = 0; tj < 4; ++tj) {
+            const int r = wr * 16 + ti * 8 + g, c = wc * 32 + tj * 8 + q * 2;
+            const double2 v = *reinterpret_cast<const double2 *>(&S[(size_t)(i * 64 + r) * ld + j * 64 + c]);
+            dst[r * kCS + c] = v.x - acc[ti][tj][0];
+            dst[r * kCS + c + 1] = v.y - acc[ti][tj][1];
+        }
+    __syncthreads();
+    const int base = j * 64;
+    if (diag) {
+        // ---- C: factor the diagonal tile (as k_chol_panel) ----
+        int fail = 0;
+#pragma unroll
+        for (int sblk = 0; sblk < 8; ++sblk) {
+            const int k0 = sblk * 8, nrest = 56 - k0;
+            double a[8][8], dinv[8];
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii)
+#pragma unroll
+                for (int jj = 0; jj <= ii; ++jj) a[ii][jj] = T[(k0 + ii) * kCS + k0 + jj];
+            chol8_regs(a, dinv, base + k0, d.ns, fail);
+            __syncthreads();
+            if (tid < nrest) {
+                const int r = k0 + 8 + tid;
+                double x[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = T[r * kCS + k0 + k];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    x[k] *= dinv[k];
+#pragma unroll
+                    for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], a[k2][k], x[k2]);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) T[r * kCS + k0 + k] = x[k];
+            } else if (tid < nrest + 8) {
+                const int ii0 = tid - nrest;
+#pragma unroll
+                for (int ii = 0; ii < 8; ++ii)
+                    if (ii == ii0) {
+#pragma unroll
+                        for (int jj = 0; jj < 8; ++jj) T[(k0 + ii) * kCS + k0 + jj] = jj <= ii ? a[ii][jj] : 0.0;
+                        dinv_s[k0 + ii] = dinv[ii];
+                    }
+            }
+            __syncthreads();
+            if (nrest > 0) {
+                for (int e = tid; e < nrest * nrest; e += 256) {
+                    const int rr = e / nrest, cc = e - rr * nrest;
+                    if (cc > rr) continue;
+                    const double *pr = &T[(k0 + 8 + rr) * kCS + k0], *pc = &T[(k0 + 8 + cc) * kCS + k0];
+                    double s2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) s2 = fma(pr[k], pc[k], s2);
+                    T[(k0 + 8 + rr) * kCS + k0 + 8 + cc] -= s2;
+                }
+                __syncthreads();
+            }
+        }
+        if (tid == 0 && fail) atomicExch(&st->chol_fail, 1);
+        for (int e = tid; e < 64 * 64; e += 256) {
+            const int rr = e >> 6, c = e & 63;
+            S[(size_t)(base + rr) * ld + base + c] = c <= rr ? T[rr * kCS + c] : 0.0;
+        }
+    } else {
+        // ---- D: X <- X L(j,j)^-T once the diagonal tile is published ----
+        if (tid == 0) {
+            int v;
+            const int *f = &flags[j * nb + j];
+            do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while (v != epoch);
+        }
+        __syncthreads();
+        for (int e = tid; e < 64 * 64; e += 256) {
+            const int rr = e >> 6, c = e & 63;
+            T[rr * kCS + c] = __ldcg(&S[(size_t)(base + rr) * ld + base + c]);
+        }
+        __syncthreads();
+        if (tid < 64) dinv_s[tid] = 1.0 / T[tid * kCS + tid];
+        __syncthreads();
+        const int r = tid & 63, qq = tid >> 6;
+#pragma unroll
+        for (int sblk = 0; sblk < 8; ++sblk) {
+            const int k0 = sblk * 8;
+            if (tid < 64) {
+                double x[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = X[r * kCS + k0 + k];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    x[k] *= dinv_s[k0 + k];
+#pragma unroll
+                    for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], T[(k0 + k2) * kCS + k0 + k], x[k2]);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) X[r * kCS + k0 + k] = x[k];
+            }
+            __syncthreads();
+            if (sblk < 7) {
+                double xr[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) xr[k] = X[r * kCS + k0 + k];
+                for (int c = k0 + 8 + qq; c < 64; c += 4) {
+                    const double *pc = &T[c * kCS + k0];
+                    double s2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) s2 = fma(xr[k], pc[k], s2);
+                    X[r * kCS + c] -= s2;
+                }
+                __syncthreads();
+            }
+        }
+        const int rb = i * 64;
+        for (int e = tid; e < 64 * 64; e += 256) {
+            const int rr = e >> 6, c = e & 63;
+            S[(size_t)(rb + rr) * ld + base + c] = X[rr * kCS + c];
+        }
+    }
+    // publish
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) {
+        int *f = &flags[j * nb + i];
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(f), "r"(epoch) : "memory");
+    }
 }
 
 // ---- triangular solves with L_S (single CTA, 1024 threads) ---------------------------

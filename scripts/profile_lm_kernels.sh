@@ -1,10 +1,13 @@
 #!/bin/bash
-# full captures of the dominant LM kernels of one cfg3 global solve
-TAG=${1:-r1e}
+# full captures of the dominant LM kernels of one cfg3 global solve (host-driven loop so
+# that ncu sees plain launches; the graph replays the same kernels)
+TAG=${1:-r1h}
+export MMB_LM_GRAPH=0
 CMD="python scripts/solve_profile.py 1000 500 3"
-MMB_LM_PROFILE=0 $CMD > gpurun_out/${TAG}_solve_plain2.log 2>&1 || exit 1
-for K in k_chol_panel k_chol_trailing k_schur_syrk k_assemble; do
+$CMD > gpurun_out/${TAG}_solve_plain2.log 2>&1 || exit 1
+for K in k_schur_syrk k_chol_tiles k_assemble k_block_factor k_backward_wave; do
   ncu --set full --clock-control none --import-source on -k regex:$K -s 1 -c 1 \
       -o gpurun_out/${TAG}_$K -f $CMD > gpurun_out/${TAG}_ncu_$K.log 2>&1
+  ncu -i gpurun_out/${TAG}_$K.ncu-rep --page details > gpurun_out/${TAG}_${K}_ncu_details.txt 2>&1
 done
-ls -la gpurun_out | tail -8
+ls -la gpurun_out | tail -12
