@@ -279,6 +279,17 @@ mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES],
 mmb_status mmb_problem_attach_comm(mmb_problem *p,
                                    const uint8_t id[MMB_COMM_ID_BYTES],
                                    int32_t rank, int32_t world);
+/* A communicator that outlives handles.  Setting up an NCCL communicator and
+ * its first collective costs ~1 s; a session that solves repeatedly (the
+ * reference calls mmSolver once per solver step) creates it once -- collective
+ * over the ranks of the id, connections warmed up -- and lends it to each
+ * handle with mmb_problem_use_comm (the handle does not own it: destroy the
+ * communicator after the handles that use it). */
+typedef struct mmb_comm mmb_comm; /* opaque */
+mmb_status mmb_comm_create(const uint8_t id[MMB_COMM_ID_BYTES], int32_t rank,
+                           int32_t world, int32_t device, mmb_comm **out);
+void mmb_comm_destroy(mmb_comm *c);
+mmb_status mmb_problem_use_comm(mmb_problem *p, mmb_comm *c);
 /* CommandResult::add / divide (adjust_results.h:89-117, 208-243) */
 mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count,
                                  mmb_result *out);

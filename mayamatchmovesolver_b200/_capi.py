@@ -89,6 +89,9 @@ SYMBOLS = [
                                              C.POINTER(C.c_void_p)]),
     ("mmb_comm_unique_id", C.c_int32, [c_u8p, C.c_int32]),
     ("mmb_problem_attach_comm", C.c_int32, [C.c_void_p, c_u8p, C.c_int32, C.c_int32]),
+    ("mmb_comm_create", C.c_int32, [c_u8p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    ("mmb_comm_destroy", None, [C.c_void_p]),
+    ("mmb_problem_use_comm", C.c_int32, [C.c_void_p, C.c_void_p]),
     ("mmb_aggregate_results", C.c_int32, [C.POINTER(Result), C.c_int32, C.POINTER(Result)]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),

@@ -12,6 +12,10 @@ using namespace mmb;
 struct mmb_problem {
     DeviceProblem *dp;
 };
+struct mmb_comm {
+    Comm *c;
+    int device;
+};
 
 static const char *k_reasons[9] = {
     // adjust_cminpack_base.h:51-83
@@ -296,6 +300,58 @@ mmb_status mmb_problem_attach_comm(mmb_problem *p, const uint8_t id[MMB_COMM_ID_
         set_last_error("unexpected exception in mmb_problem_attach_comm");
         return MMB_ERR_INTERNAL;
     }
+}
+
+mmb_status mmb_comm_create(const uint8_t id[MMB_COMM_ID_BYTES], int32_t rank, int32_t world, int32_t device,
+                           mmb_comm **out) {
+    if (!id || !out) return MMB_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    try {
+        Comm *c = nullptr;
+        mmb_status st = comm_create(id, rank, world, device, &c);
+        if (st != MMB_OK) return st;
+        // warm-up: the first collectives of an NCCL communicator set up its connections
+        // (hundreds of ms); pay that here, once, for a latency-sized and a bandwidth-sized call
+        if (world > 1) {
+            cudaStream_t s = nullptr;
+            double *buf = nullptr;
+            const size_t big = (size_t)2 << 20;  // 16 MB of doubles: the size class of the reduced system
+            bool ok = cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess &&
+                      cudaMalloc((void **)&buf, big * sizeof(double)) == cudaSuccess &&
+                      cudaMemsetAsync(buf, 0, big * sizeof(double), s) == cudaSuccess;
+            if (ok) ok = c->allreduce(buf, 4, false, s) == MMB_OK && c->allreduce(buf, 4, true, s) == MMB_OK &&
+                         c->allreduce(buf, 1184 + 2, false, s) == MMB_OK && c->allreduce(buf, big, false, s) == MMB_OK;
+            if (ok) ok = cudaStreamSynchronize(s) == cudaSuccess;
+            if (buf) cudaFree(buf);
+            if (s) cudaStreamDestroy(s);
+            if (!ok) { delete c; if (get_last_error().empty()) set_last_error("communicator warm-up failed"); return MMB_ERR_COMM; }
+        }
+        *out = new mmb_comm{c, device};
+        return MMB_OK;
+    } catch (...) {
+        set_last_error("unexpected exception in mmb_comm_create");
+        return MMB_ERR_INTERNAL;
+    }
+}
+
+void mmb_comm_destroy(mmb_comm *c) {
+    if (!c) return;
+    delete c->c;
+    delete c;
+}
+
+mmb_status mmb_problem_use_comm(mmb_problem *p, mmb_comm *c) {
+    if (!p || !c) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    if (dp->comm) { set_last_error("handle already has a communicator"); return MMB_ERR_INVALID_ARGUMENT; }
+    if (dp->hp.opt.frame_solve_mode == 1) {
+        set_last_error("per-frame solves of different shards are independent: no communicator is needed");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    if (c->device != dp->device) { set_last_error("communicator and handle are bound to different devices"); return MMB_ERR_INVALID_ARGUMENT; }
+    dp->comm = c->c;
+    dp->comm_owned = false;
+    return MMB_OK;
 }
 
 mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count, mmb_result *out) {

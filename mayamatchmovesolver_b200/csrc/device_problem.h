@@ -84,7 +84,8 @@ struct DeviceProblem {
     TiledPlan tiled{};
     int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
-    Comm *comm = nullptr;       // set by mmb_problem_attach_comm: mmb_solve is then the sharded global solve
+    Comm *comm = nullptr;       // set by mmb_problem_attach_comm / use_comm: mmb_solve is then the sharded global solve
+    bool comm_owned = true;     // false: borrowed from an mmb_comm that outlives the handle
     int frame_begin = 0;        // first frame of this shard in the unsharded scene
     int frames_global = 0;      // frame count of the unsharded scene
     volatile int cancel = 0;

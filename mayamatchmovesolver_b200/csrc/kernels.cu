@@ -172,7 +172,7 @@ DeviceProblem::~DeviceProblem() {
     cudaSetDevice(device);
     if (lm) lm_workspace_destroy(lm);
     const auto t1 = std::chrono::steady_clock::now();
-    if (comm) { if (stream) cudaStreamSynchronize(stream); delete comm; }
+    if (comm) { if (stream) cudaStreamSynchronize(stream); if (comm_owned) delete comm; }
     arena.release();  // stream-ordered frees: back to the pool once the stream's work is done
     if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
     if (timing)

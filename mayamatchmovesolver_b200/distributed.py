@@ -19,7 +19,7 @@ there.
 import numpy as np
 
 from . import _capi
-from .problem import Problem, SolveResult, aggregate_results, comm_unique_id, shard_frames, shard_param_map  # noqa: F401
+from .problem import Comm, Problem, SolveResult, aggregate_results, comm_unique_id, shard_frames, shard_param_map  # noqa: F401
 
 
 class TorchGroup:
@@ -101,13 +101,27 @@ def solve_per_frame_sharded(scene, group, device=0, options=None, **opt_override
     return result, [SolveResult(r, None, None, None) for r in raw]
 
 
-def solve_global_sharded(scene, group, device=0, options=None, local_backend=False, **opt_overrides):
-    """frameSolveMode=0 over `group`: the sharded global solve.  -> SolveResult with unsharded
-    x / attr values / per-observation distances, identical on every rank."""
+def make_comm(group, device=0, local_backend=False):
+    """collective: a long-lived communicator over `group` (None for a single rank)"""
+    if group.world == 1:
+        return None
     cid = comm_unique_id(local_backend) if group.rank == 0 else None
     cid = group.broadcast_bytes(cid, src=0)
+    return Comm(cid, group.rank, group.world, device)
+
+
+def solve_global_sharded(scene, group, device=0, options=None, local_backend=False, comm=None, **opt_overrides):
+    """frameSolveMode=0 over `group`: the sharded global solve.  -> SolveResult with unsharded
+    x / attr values / per-observation distances, identical on every rank.  `comm`: a
+    communicator from make_comm() to reuse; else one is made for this solve."""
+    cid = None
+    if comm is None and group.world > 1:
+        cid = comm_unique_id(local_backend) if group.rank == 0 else None
+        cid = group.broadcast_bytes(cid, src=0)
     with Problem(scene, options=options, shard=(group.rank, group.world), device=device, **opt_overrides) as p:
-        if group.world > 1:
+        if comm is not None:
+            p.use_comm(comm)
+        elif group.world > 1:
             p.attach_comm(cid, group.rank, group.world)
         r = p.solve()
         e2m, _ = p.index_maps()

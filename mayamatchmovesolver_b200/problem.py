@@ -47,6 +47,31 @@ def comm_unique_id(local_backend=False):
     return bytes(buf)
 
 
+class Comm:
+    """A communicator that outlives Problem handles (mmb_comm_create: collective over the
+    ranks of `comm_id`; NCCL set-up and warm-up are paid once)."""
+
+    def __init__(self, comm_id, rank, world, device=0):
+        self._lib = _capi.load()
+        self._h = C.c_void_p()
+        buf = (C.c_uint8 * _capi.MMB_COMM_ID_BYTES).from_buffer_copy(bytes(comm_id))
+        check(self._lib.mmb_comm_create(buf, int(rank), int(world), int(device), C.byref(self._h)), "mmb_comm_create")
+        self.rank, self.world, self.device = int(rank), int(world), int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.mmb_comm_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
 def aggregate_results(results):
     """CommandResult::add / divide over per-frame mmb_result records"""
     lib = _capi.load()
@@ -207,6 +232,11 @@ class Problem:
         handle becomes the sharded global solve"""
         buf = (C.c_uint8 * _capi.MMB_COMM_ID_BYTES).from_buffer_copy(bytes(comm_id))
         check(self._lib.mmb_problem_attach_comm(self._h, buf, int(rank), int(world)), "mmb_problem_attach_comm")
+
+    def use_comm(self, comm):
+        """lend a long-lived Comm to this handle (it must outlive the handle's solves)"""
+        check(self._lib.mmb_problem_use_comm(self._h, comm._h), "mmb_problem_use_comm")
+        self._comm_keepalive = comm
 
     def request_cancel(self):
         self._lib.mmb_request_cancel(self._h)

@@ -16,8 +16,8 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 from mayamatchmovesolver_b200 import _capi, synth  # noqa: E402
-from mayamatchmovesolver_b200.distributed import (TorchGroup, merge_shard_vectors, solve_global_sharded,  # noqa: E402
-                                                  solve_per_frame_sharded)
+from mayamatchmovesolver_b200.distributed import (TorchGroup, make_comm, merge_shard_vectors,  # noqa: E402
+                                                  solve_global_sharded, solve_per_frame_sharded)
 from mayamatchmovesolver_b200.problem import Problem, aggregate_results, shard_frames, shard_param_map  # noqa: E402
 
 
@@ -65,6 +65,13 @@ def gpu_mode():
     # global solve, gauge-fixed so the solved values are determined
     sb, _ = synth.make_scene(F=24, B=20, seed=21, fixed_bundles=4, period=24)
     r = solve_global_sharded(sb, g, device=local)
+    # the same solve twice more through one session communicator (mmb_comm_create)
+    comm = make_comm(g, device=local)
+    for _ in range(2):
+        rs = solve_global_sharded(sb, g, device=local, comm=comm)
+        assert (rs.reason_num, rs.iteration_num) == (r.reason_num, r.iteration_num)
+        np.testing.assert_allclose(rs.attr_values, r.attr_values, rtol=1e-7, atol=1e-7)
+    comm.close()
     sb2, _ = synth.make_scene(F=30, B=16, seed=22, solve_bundles=False, period=30)
     rp, per = solve_per_frame_sharded(sb2, g, device=local)
     if g.rank == 0:

@@ -15,7 +15,7 @@ import pytest
 
 from groups import run_ranks
 from mayamatchmovesolver_b200 import synth
-from mayamatchmovesolver_b200.distributed import SingleGroup, solve_global_sharded, solve_per_frame_sharded
+from mayamatchmovesolver_b200.distributed import SingleGroup, make_comm, solve_global_sharded, solve_per_frame_sharded
 from mayamatchmovesolver_b200.problem import Problem
 
 pytestmark = pytest.mark.gpu
@@ -71,6 +71,25 @@ def test_global_sharded_matches_unsharded(name, world):
     assert np.max(np.abs(r.error_dist - r1.error_dist)) <= 1e-5
     assert abs(r.error_final - r1.error_final) <= 1e-6 * r1.error_final
     assert abs(r.error_avg - r1.error_avg) <= 1e-6 and abs(r.error_max - r1.error_max) <= 1e-5
+
+
+def test_session_communicator_is_reused_across_solves():
+    """mmb_comm_create once, mmb_problem_use_comm per handle (the handle does not own it)"""
+    sb, _ = synth.make_scene(**GLOBAL_CASES["camera_bundles_24x20"])
+    with Problem(sb) as p:
+        r1 = p.solve()
+
+    def body(g):
+        comm = make_comm(g, local_backend=True)
+        a = solve_global_sharded(sb, g, comm=comm)
+        b = solve_global_sharded(sb, g, comm=comm)
+        comm.close()
+        return a, b
+    for a, b in run_ranks(2, body):
+        for r in (a, b):
+            assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (r1.reason_num, r1.iteration_num, r1.iteration_attempt_num)
+            scale = np.maximum(np.abs(r1.attr_values), 1.0)
+            assert np.max(np.abs(r.attr_values - r1.attr_values) / scale) <= 1e-6
 
 
 @pytest.mark.parametrize("world", [2, 4])
