@@ -52,19 +52,26 @@ def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
 
 def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, init_noise_t=0.1,
                init_noise_r=0.5, init_noise_b=0.05, fixed_bundles=0, lens=None, solve_focal=False,
-               solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False, period=120.0):
+               solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False, period=120.0,
+               in_frame=False):
     """One animated camera, B static bundles, full (or thinned) visibility.
 
     cfg2: make_scene(240, 50, 2, solve_bundles=False)
     cfg3: make_scene(1000, 500, 3)
-    cfg4: make_scene(1000, 500, 4, lens={...}, solve_focal=True, solve_lens=(...))
+    cfg4: make_scene(1000, 500, 4, lens={...}, solve_focal=True, solve_lens=(...), in_frame=True)
     `fixed_bundles` bundles are left out of the attr list (removes the gauge
     freedom so solved values are comparable between solvers).
+    `in_frame` keeps every bundle inside the image on every frame (a plate only has
+    markers inside the frame; outside it the degree-4 lens polynomial is not
+    invertible and the fixed-point inverse of LDPK diverges) -- used by cfg4.
     Returns (SceneBuilder, info dict).
     """
     rng = np.random.default_rng(seed)
     sensor_w, sensor_h, rw, rh = 36.0, 24.0, 2048, 1556
-    pts = np.stack([rng.uniform(-10, 10, B), rng.uniform(-10, 10, B), rng.uniform(-30, -10, B)], 1)
+    if in_frame:
+        pts = np.stack([rng.uniform(-4, 4, B), rng.uniform(-2.2, 2.2, B), rng.uniform(-30, -14, B)], 1)
+    else:
+        pts = np.stack([rng.uniform(-10, 10, B), rng.uniform(-10, 10, B), rng.uniform(-30, -10, B)], 1)
     cam_t, cam_r = camera_path(F, rng, period=period)
     sb = SceneBuilder(frames=np.arange(1, F + 1))
     lens_node = None
