@@ -247,6 +247,29 @@ def run_own(args):
     pf_dt, pf_agg = perframe_once(2)
     (pf_dt,) = allmax([pf_dt])
 
+    # ---- cfg4 evaluation step: lens distortion (LDPK fixed-point inverse) inside every
+    # residual / FD evaluation -> FP64-bound, reported against the measured DFMA ceiling
+    cfg4 = None
+    if world == 1:
+        from mayamatchmovesolver_b200.problem import fp64_peaks
+        lens = dict(degree2_distortion=0.05, degree2_u=0.002, degree2_v=-0.002, degree4_distortion=0.01,
+                    degree4_u=0.0, degree4_v=0.0)
+        sb4, _ = synth.make_scene(F1, B, 4, lens=lens, solve_focal=True, solve_lens=tuple(lens), focal_init=33.0,
+                                  in_frame=True)
+        with Problem(sb4, device=local) as p4:
+            k4 = p4.jacobian_kmax()
+            for _ in range(3):
+                p4.bench_eval(1, True)
+            t4 = [p4.bench_eval(1, True) for _ in range(20)]
+            step4 = sum(t[0] for t in t4) / len(t4)
+            jac4 = sum(t[1] for t in t4) / len(t4)
+            cfg4 = {"workload": "cfg4: cfg3 + focal + 6 radial-decentered deg-4 lens coefficients (n=%d), lens in the loop" % p4.n,
+                    "evals_per_s": p4.nobs / (step4 * 1e-3), "ms_per_step": step4, "jacobian_kernel_ms": jac4,
+                    "local_params_per_obs_k": k4, "bound": "fp64",
+                    "algorithmic_GBps": p4.nobs * (48 + 16 * k4) / (jac4 * 1e-3) / 1e9}
+        dfma, dmma = fp64_peaks(local)
+        cfg4["fp64_peaks_measured_tflops"] = {"dfma": dfma, "dmma_m8n8k4": dmma}
+
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -287,6 +310,8 @@ def run_own(args):
                      "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes,
                      "peak_source": peaks_src, "kernel_ms": jac_ms / args.steps},
     }
+    if cfg4 is not None:
+        line["cfg4_eval"] = cfg4
     if world == 1 and not args.no_cpu:
         leg = cpu_reference_leg(steps=1)
         line["cpu_baseline"] = {"value": leg["value"], "unit": "evals/s", "cores": 1, "kind": "port",

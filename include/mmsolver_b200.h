@@ -307,6 +307,11 @@ void mmb_request_cancel(mmb_problem *p);
 mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
                           double *ms_per_eval, double *ms_jacobian_kernel,
                           int32_t *launches);
+/* measured FP64 ceilings of the device in TFLOP/s (dependent-free DFMA chains; DMMA
+ * m8n8k4): the roofline denominators of the compute-bound kernels (lens distortion in
+ * the loop, the reduced-system SYRK / Cholesky updates) */
+mmb_status mmb_bench_fp64_peaks(int32_t device, double *dfma_tflops,
+                                double *dmma_tflops);
 /* kernels launched by this handle so far (bench.py's gpu_launches) */
 int64_t mmb_launch_count(const mmb_problem *p);
 /* How the last mmb_solve() on this handle was driven.  The reference's loop is

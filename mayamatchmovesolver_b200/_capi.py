@@ -95,6 +95,7 @@ SYMBOLS = [
     ("mmb_aggregate_results", C.c_int32, [C.POINTER(Result), C.c_int32, C.POINTER(Result)]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
+    ("mmb_bench_fp64_peaks", C.c_int32, [C.c_int32, c_f64p, c_f64p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),
     ("mmb_solve_stats", C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     ("mmb_release_cached_memory", C.c_int32, [C.c_int32]),

@@ -430,6 +430,13 @@ mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs, int64_t *g
     return MMB_OK;
 }
 
+mmb_status mmb_bench_fp64_peaks(int32_t device, double *dfma_tflops, double *dmma_tflops) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;
+    if (device < 0 || device >= ndev) return MMB_ERR_INVALID_ARGUMENT;
+    return measure_fp64_peaks(device, dfma_tflops, dmma_tflops);
+}
+
 mmb_status mmb_release_cached_memory(int32_t device) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;

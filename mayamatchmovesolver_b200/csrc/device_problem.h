@@ -96,6 +96,9 @@ struct DeviceProblem {
     ~DeviceProblem();
 };
 
+// FP64 ceilings of the device (peaks.cu)
+mmb_status measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflops);
+
 mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt, DeviceProblem **out);
 mmb_status ensure_jacobian_buffers(DeviceProblem *p);
 

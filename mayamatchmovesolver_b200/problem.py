@@ -47,6 +47,14 @@ def comm_unique_id(local_backend=False):
     return bytes(buf)
 
 
+def fp64_peaks(device=0):
+    """-> (DFMA TFLOP/s, DMMA TFLOP/s) measured on `device`"""
+    lib = _capi.load()
+    a, b = C.c_double(), C.c_double()
+    check(lib.mmb_bench_fp64_peaks(int(device), C.byref(a), C.byref(b)), "mmb_bench_fp64_peaks")
+    return a.value, b.value
+
+
 class Comm:
     """A communicator that outlives Problem handles (mmb_comm_create: collective over the
     ranks of `comm_id`; NCCL set-up and warm-up are paid once)."""
