@@ -294,6 +294,33 @@ mmb_status mmb_problem_use_comm(mmb_problem *p, mmb_comm *c);
 mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count,
                                  mmb_result *out);
 
+/* fvec of the accepted point of the last mmb_solve(): errorList [m]
+ * (SolveValuesResult, adjust_results.h:298-311) */
+mmb_status mmb_get_last_residuals(mmb_problem *p, double *fvec);
+
+/* The `key=value` strings the mmSolver command returns
+ * (CommandResult::appendToMStringArray, adjust_results.h:871-938; split char
+ * '#', adjust_defines.h:64), in the reference's order, one per line ('\n'),
+ * so python/mmSolver/_api/solveresult.py parses them unchanged.  Host only.
+ * error_to_marker [n_obs*2] / frames [num_frames] / marker_names [num_markers]
+ * (NULL -> "marker<i>") name the per-marker-per-frame deviations;
+ * solve_parameter_list [n_params], solve_error_list [2*n_obs], error_dist
+ * [n_obs] may be NULL when their flag is off.  *needed = bytes incl. NUL;
+ * MMB_ERR_INVALID_ARGUMENT with *needed set when cap is too small. */
+#define MMB_FMT_ERROR_PER_MARKER_PER_FRAME 1
+#define MMB_FMT_ERROR_PER_FRAME 2
+#define MMB_FMT_SOLVE_VALUES 4
+#define MMB_FMT_INPUT_STATS 8 /* printStatistics 'inputs': numberOf* counts */
+mmb_status mmb_format_results(const mmb_result *r, int32_t n_params,
+                              int32_t n_obs, const int32_t *error_to_marker,
+                              const int32_t *frames, int32_t num_frames,
+                              const char *const *marker_names,
+                              int32_t num_markers,
+                              const double *solve_parameter_list,
+                              const double *solve_error_list,
+                              const double *error_dist, int32_t flags,
+                              char *buf, int64_t cap, int64_t *needed);
+
 /* MComputation::isInterruptRequested analogue; callable from another thread */
 void mmb_request_cancel(mmb_problem *p);
 

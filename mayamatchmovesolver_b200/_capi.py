@@ -57,6 +57,12 @@ class Options(C.Structure):
     ]
 
 
+MMB_FMT_ERROR_PER_MARKER_PER_FRAME = 1
+MMB_FMT_ERROR_PER_FRAME = 2
+MMB_FMT_SOLVE_VALUES = 4
+MMB_FMT_INPUT_STATS = 8
+
+
 class Result(C.Structure):
     _fields_ = [
         ("success", C.c_int32), ("reason_num", C.c_int32), ("reason_str", C.c_char_p),
@@ -93,6 +99,10 @@ SYMBOLS = [
     ("mmb_comm_destroy", None, [C.c_void_p]),
     ("mmb_problem_use_comm", C.c_int32, [C.c_void_p, C.c_void_p]),
     ("mmb_aggregate_results", C.c_int32, [C.POINTER(Result), C.c_int32, C.POINTER(Result)]),
+    ("mmb_get_last_residuals", C.c_int32, [C.c_void_p, c_f64p]),
+    ("mmb_format_results", C.c_int32, [C.POINTER(Result), C.c_int32, C.c_int32, c_i32p, c_i32p, C.c_int32,
+                                       C.POINTER(C.c_char_p), C.c_int32, c_f64p, c_f64p, c_f64p, C.c_int32,
+                                       C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
     ("mmb_bench_fp64_peaks", C.c_int32, [C.c_int32, c_f64p, c_f64p]),

@@ -361,6 +361,15 @@ mmb_status mmb_aggregate_results(const mmb_result *per_frame, int32_t count, mmb
     return MMB_OK;
 }
 
+mmb_status mmb_get_last_residuals(mmb_problem *p, double *fvec) {
+    if (!p || !fvec) return MMB_ERR_INVALID_ARGUMENT;
+    DeviceProblem *dp = p->dp;
+    MMB_CUDA_CHECK(cudaSetDevice(dp->device));
+    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
+    MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
+    return MMB_OK;
+}
+
 void mmb_request_cancel(mmb_problem *p) {
     if (p) lm_request_cancel(p->dp);
 }

@@ -34,11 +34,14 @@ LENS_COEFF_NAMES = {
 
 
 class Node(dict):
-    """index + {attr name: attribute-store ref}"""
+    """index + {attr name: attribute-store ref}; `name` is the Maya node name the
+    mmSolver command flags would use (optional)"""
 
-    def __init__(self, index, refs):
+    def __init__(self, index, refs, kind="", name=None):
         super().__init__(refs)
         self.index = index
+        self.kind = kind
+        self.name = name
 
 
 class SceneBuilder:
@@ -53,6 +56,18 @@ class SceneBuilder:
         self.mkr_cam, self.mkr_bnd, self.mkr_x, self.mkr_y, self.mkr_w, self.mkr_en = [], [], [], [], [], []
         self.lens_model, self.lens_attrs, self.lens_cam = [], [], []
         self.attr_ref, self.attr_min, self.attr_max, self.attr_off, self.attr_scl = [], [], [], [], []
+        self.names = {}  # node name -> Node (what the command's -camera / -marker / -attr flags name)
+
+    def _register(self, node):
+        if node.name is not None:
+            self.names[node.name] = node
+        return node
+
+    def plug(self, plug_name):
+        """'node.attr' -> attribute-store ref (the MPlug of an `-attr` flag)"""
+        node_name, _, attr = plug_name.rpartition(".")
+        node = self.names[node_name]
+        return node[attr]
 
     # ---- attribute store (datablock.rs) --------------------------------
     def value(self, v):
@@ -77,16 +92,17 @@ class SceneBuilder:
             self._anim[-ref - 1][frame_index] = v
 
     # ---- nodes ---------------------------------------------------------
-    def add_transform(self, parent=None, rotate_order="xyz", **vals):
+    def add_transform(self, parent=None, rotate_order="xyz", name=None, **vals):
         defaults = dict(tx=0.0, ty=0.0, tz=0.0, rx=0.0, ry=0.0, rz=0.0, sx=1.0, sy=1.0, sz=1.0)
         defaults.update(vals)
         refs = {k: self.value(defaults[k]) for k in TFM_ATTR_NAMES}
         self.tfm_parent.append(-1 if parent is None else int(getattr(parent, "index", parent)))
         self.tfm_roo.append(ROTATE_ORDERS[rotate_order] if isinstance(rotate_order, str) else int(rotate_order))
         self.tfm_attrs.append([refs[k] for k in TFM_ATTR_NAMES])
-        return Node(len(self.tfm_parent) - 1, refs)
+        return self._register(Node(len(self.tfm_parent) - 1, refs, "transform", name))
 
-    def add_camera(self, tfm, film_fit="horizontal", render_width=2048, render_height=1556, lens=None, **vals):
+    def add_camera(self, tfm, film_fit="horizontal", render_width=2048, render_height=1556, lens=None, name=None,
+                   **vals):
         # defaults of a Maya camera in mm (dag.rs:120-172 reads these 8)
         defaults = dict(sensor_width_mm=36.0, sensor_height_mm=24.0, focal_length_mm=35.0,
                         lens_offset_x_mm=0.0, lens_offset_y_mm=0.0, near_clip=0.1, far_clip=10000.0,
@@ -99,13 +115,13 @@ class SceneBuilder:
         self.cam_rw.append(int(render_width))
         self.cam_rh.append(int(render_height))
         self.cam_lens.append(-1 if lens is None else int(getattr(lens, "index", lens)))
-        return Node(len(self.cam_tfm) - 1, refs)
+        return self._register(Node(len(self.cam_tfm) - 1, refs, "camera", name))
 
-    def add_bundle(self, tfm):
+    def add_bundle(self, tfm, name=None):
         self.bnd_tfm.append(int(getattr(tfm, "index", tfm)))
-        return Node(len(self.bnd_tfm) - 1, {})
+        return self._register(Node(len(self.bnd_tfm) - 1, {}, "bundle", name))
 
-    def add_marker(self, cam, bnd, x, y, weight=1.0, enable=True):
+    def add_marker(self, cam, bnd, x, y, weight=1.0, enable=True, name=None):
         F = self.F
         self.mkr_cam.append(int(getattr(cam, "index", cam)))
         self.mkr_bnd.append(int(getattr(bnd, "index", bnd)))
@@ -113,9 +129,9 @@ class SceneBuilder:
         self.mkr_y.append(np.broadcast_to(np.asarray(y, dtype=np.float64), (F,)).copy())
         self.mkr_w.append(np.broadcast_to(np.asarray(weight, dtype=np.float64), (F,)).copy())
         self.mkr_en.append(np.broadcast_to(np.asarray(enable, dtype=np.uint8), (F,)).copy())
-        return Node(len(self.mkr_cam) - 1, {})
+        return self._register(Node(len(self.mkr_cam) - 1, {}, "marker", name))
 
-    def add_lens(self, model, camera_params=(3.0, 3.6, 2.4, 1.0, 0.0, 0.0), **coeffs):
+    def add_lens(self, model, camera_params=(3.0, 3.6, 2.4, 1.0, 0.0, 0.0), name=None, **coeffs):
         mid = LENS_MODELS[model] if isinstance(model, str) else int(model)
         names = LENS_COEFF_NAMES.get(mid, ())
         defaults = {k: 0.0 for k in names}
@@ -134,7 +150,7 @@ class SceneBuilder:
         self.lens_model.append(mid)
         self.lens_attrs.append(row)
         self.lens_cam.append([float(v) for v in camera_params])
-        return Node(len(self.lens_model) - 1, refs)
+        return self._register(Node(len(self.lens_model) - 1, refs, "lens", name))
 
     def add_attr(self, ref, min=None, max=None, offset=None, scale=None):
         """One `-attr node.attr min max offset scale` flag; None keeps the
