@@ -361,9 +361,8 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
 }
 
 // ---- blocked Cholesky of S (lower, row-major, ld = NSP) ----------------------------
-// sqrt(x) and 1/sqrt(x) from the hardware seed (~22 bits) + two Newton steps + one
-// correction each (<= 1-2 ulp): the IEEE sqrt and division sequences would sit on the
-// critical path of every pivot.
+// sqrt(x) and 1/sqrt(x) from the hardware seed (~22 bits) + two Newton steps (<= 2 ulp):
+// the IEEE sqrt and division sequences would sit on the critical path of every pivot.
 __device__ __forceinline__ void sqrt_rsqrt(double x, double &s, double &inv) {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -372,9 +371,11 @@ __device__ __forceinline__ void sqrt_rsqrt(double x, double &s, double &inv) {
     y = fma(y, e, y);
     e = fma(-h * y, y, 0.5);
     y = fma(y, e, y);
+    // 1/sqrt(x) is what the next pivot waits for: two Newton steps from the 22-bit seed
+    // (<= 2 ulp); sqrt(x) gets its correction off the critical path
+    inv = y;
     s = x * y;
     s = fma(0.5 * y, fma(-s, s, x), s);
-    inv = fma(y, fma(-s, y, 1.0), y);
 }
 
 // Cholesky of an 8x8 block held in registers (lower part of a[i][j]); g0 = global index of
@@ -689,14 +690,20 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
             }
             __syncthreads();
             if (nrest > 0) {
-                for (int e = tid; e < nrest * nrest; e += 256) {
-                    const int rr = e / nrest, cc = e - rr * nrest;
-                    if (cc > rr) continue;
-                    const double *pr = &T[(k0 + 8 + rr) * kCS + k0], *pc = &T[(k0 + 8 + cc) * kCS + k0];
-                    double s2 = 0.0;
+                // rank-8 update of the lower triangle below the pivot block: thread = (row, column
+                // phase); the row's 8 panel entries stay in registers
+                const int rr = tid >> 2;
+                if (rr < nrest) {
+                    double pr[8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) s2 = fma(pr[k], pc[k], s2);
-                    T[(k0 + 8 + rr) * kCS + k0 + 8 + cc] -= s2;
+                    for (int k = 0; k < 8; ++k) pr[k] = T[(k0 + 8 + rr) * kCS + k0 + k];
+                    for (int cc = tid & 3; cc <= rr; cc += 4) {
+                        const double *pc = &T[(k0 + 8 + cc) * kCS + k0];
+                        double s2 = 0.0;
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) s2 = fma(pr[k], pc[k], s2);
+                        T[(k0 + 8 + rr) * kCS + k0 + 8 + cc] -= s2;
+                    }
                 }
                 __syncthreads();
             }

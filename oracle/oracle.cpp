@@ -129,6 +129,12 @@ static void error_stats(const orc_problem *p, double &avg, double &mn, double &m
     avg /= p->nobs;
 }
 
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+extern "C" int orc_initial_parameters(orc_problem *p, double *x);
+#include "oracle_sparse.h"
+
 extern "C" {
 
 int orc_create(const mmb_scene_desc *s, const mmb_options *opt, orc_problem **out) {
@@ -270,6 +276,60 @@ int orc_solve(orc_problem *p, mmb_result *res, double *x_out, double *attr_out,
         if (attr_out) attr_out[i] = boundInternalToExternal(fin[i], p->attr_min[ai], p->attr_max[ai], p->attr_off[ai], p->attr_scl[ai]);
     }
     if (dist_out) for (int i = 0; i < p->nobs; ++i) dist_out[i] = p->errorDist[i];
+    return MMB_OK;
+}
+
+// Block-sparse solve (oracle_sparse.h): same evaluation arithmetic and control law, normal
+// equations + Schur complement instead of the dense QR.  threads <= 0: all cores.
+// max_outer > 0 stops after that many Jacobian evaluations (bounded timing samples).
+int orc_solve_sparse(orc_problem *p, mmb_result *res, double *x_out, double *attr_out, double *dist_out,
+                     int32_t threads, int32_t max_outer) {
+    std::memset(res, 0, sizeof(*res));
+    if (p->nobs == 0 || p->n == 0) { res->success = 0; return MMB_ERR_NOT_ENOUGH_OBJECTS; }
+    if (p->n > p->m) { res->success = 0; return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
+    if (p->opt.auto_diff_type != 0) return MMB_ERR_UNSUPPORTED;
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#else
+    (void)threads;
+#endif
+    p->stat = p->stat0; p->anim = p->anim0;
+    p->iterNum = p->jacIterNum = p->funcEvalNum = 0;
+    orcs::Sparse s;
+    orcs::sparse_init(s, p);
+    const int n = p->n, m = p->m;
+    std::vector<double> fvec(m, 0.0), x(n), prev(n), dist(p->nobs, 0.0);
+    double iavg = 0, imin = 0, imax = 0;
+    if (p->opt.accept_only_better) {
+        // measureErrors at the scene's own values (adjust_base.cpp:1080-1103)
+        orcs::Getter G{p, {0, 0, 0.0, false}};
+        for (int i = 0; i < p->nobs; ++i) orcs::obs_eval(G, i, fvec[2 * i], fvec[2 * i + 1], p->errorDist[i]);
+        error_stats(p, iavg, imin, imax);
+    }
+    orc_initial_parameters(p, x.data());
+    prev = x;
+    int nfev = 0, njev = 0;
+    const int info = orcs::sparse_lmder(s, x, fvec, dist, &nfev, &njev, max_outer);
+    p->errorDist = dist;
+    res->error_final = enorm(m, fvec.data());
+    res->success = p->iterNum > 0;
+    res->reason_num = info;
+    res->reason_str = (info >= 0 && info < 9) ? k_reasons[info] : "";
+    res->iteration_num = nfev;
+    res->iteration_function_num = p->iterNum;
+    res->iteration_jacobian_num = p->jacIterNum;
+    res->iteration_attempt_num = njev;
+    error_stats(p, res->error_avg, res->error_min, res->error_max);
+    bool better = true;
+    if (p->opt.accept_only_better) better = res->error_avg <= iavg;
+    res->error_is_better = better;
+    const std::vector<double> &fin = better ? x : prev;
+    for (int i = 0; i < n; ++i) {
+        const int ai = p->paramToAttr[i].first;
+        if (x_out) x_out[i] = x[i];
+        if (attr_out) attr_out[i] = boundInternalToExternal(fin[i], p->attr_min[ai], p->attr_max[ai], p->attr_off[ai], p->attr_scl[ai]);
+    }
+    if (dist_out) for (int i = 0; i < p->nobs; ++i) dist_out[i] = dist[i];
     return MMB_OK;
 }
 

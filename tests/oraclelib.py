@@ -157,6 +157,17 @@ class OracleProblem:
         self.lib.orc_eval_jacobian_dense(self.h, _p(x), _p(f), _p(J), ld, 1 if structural_skip else 0)
         return J[:, :self.m].T.copy()
 
+    def solve_sparse(self, threads=0, max_outer=0):
+        """block-sparse CPU solve (oracle/oracle_sparse.h): feasible at full cfg3 / cfg4 size"""
+        from mayamatchmovesolver_b200.problem import SolveResult
+        r = Result()
+        x = np.zeros(self.n); av = np.zeros(self.n); d = np.zeros(self.nobs)
+        self.lib.orc_solve_sparse.argtypes = [C.c_void_p, C.POINTER(Result), c_f64p, c_f64p, c_f64p, C.c_int32, C.c_int32]
+        st = self.lib.orc_solve_sparse(self.h, C.byref(r), _p(x), _p(av), _p(d), int(threads), int(max_outer))
+        res = SolveResult(r, x, av, d)
+        res.status = st
+        return res
+
     def solve(self, structural_skip=True):
         from mayamatchmovesolver_b200.problem import SolveResult
         r = Result()

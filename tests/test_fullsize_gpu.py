@@ -105,3 +105,37 @@ def test_cfg4_full_size_noise_free_recovers_focal_and_lens():
     # coefficients are well determined
     assert abs(focal - 35.0) < 1.0                     # started at 33
     np.testing.assert_allclose(lens, [LENS[k] for k in LENS], atol=1e-2)  # started at 0; c2 trades against focal
+
+
+GOLDEN_SCENES = {
+    "cfg3": lambda: synth.make_scene(F, B, 3, fixed_bundles=4),
+    "cfg4": lambda: synth.make_scene(F, B, 4, lens=LENS, solve_focal=True, solve_lens=tuple(LENS), focal_init=33.0,
+                                     in_frame=True, fixed_bundles=4),
+}
+
+
+@pytest.mark.parametrize("name", list(GOLDEN_SCENES))
+def test_full_size_solve_matches_cpu_golden(name):
+    """Whole solves at full size against tests/golden/fullsize_<cfg>.npz: the block-sparse CPU
+    oracle (oracle/oracle_sparse.h -- the reference's evaluation arithmetic and MINPACK control
+    law, itself pinned to the dense faithful oracle at small sizes) on the same seeded scene,
+    4 bundles held so that the solved values are determined.  north_star tolerances: solved
+    attribute values 1e-6 relative, per-marker reprojection error 1e-6 px."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "fullsize_%s.npz" % name))
+    sb, _ = GOLDEN_SCENES[name]()
+    with Problem(sb) as p:
+        r = p.solve()
+        assert p.solve_stats() == (1, 1)
+    reason, nfev, njev, nfunc, njac, better = [int(v) for v in g["summary"]]
+    print(name, r, "njev", r.iteration_attempt_num, "golden", reason, nfev, njev, "cpu s", float(g["cpu_seconds"]),
+          "gpu solve s", r.timer_solve_s)
+    assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (reason, nfev, njev)
+    assert (r.iteration_function_num, r.iteration_jacobian_num, int(r.error_is_better)) == (nfunc, njac, better)
+    scale = np.maximum(np.abs(g["attr_values"]), 1.0)
+    assert np.max(np.abs(r.attr_values - g["attr_values"]) / scale) <= 1e-6
+    stride = int(g["sample_stride"])
+    assert np.max(np.abs(r.error_dist[::stride] - g["dist_sample"])) <= 1e-6
+    ef, ea, emin, emax = g["errors"]
+    assert abs(r.error_final - ef) <= 1e-6 * ef and abs(r.error_avg - ea) <= 1e-6
+    assert abs(r.error_min - emin) <= 1e-6 and abs(r.error_max - emax) <= 1e-6

@@ -241,3 +241,35 @@ def test_oracle_structural_skip_is_exact():
     o = OracleProblem(sb)
     x = o.initial_parameters()
     assert np.array_equal(o.eval_jacobian_dense(x, True), o.eval_jacobian_dense(x, False))
+
+
+SPARSE_CASES = {
+    "camera_bundles_12x16": dict(F=12, B=16, seed=9, fixed_bundles=3, period=12),
+    "camera_bundles_40x30": dict(F=40, B=30, seed=5, fixed_bundles=4, period=40),
+    "sparse_weighted": dict(F=20, B=14, seed=6, fixed_bundles=3, drop_fraction=0.15, weights=True, period=20),
+    "bundles_only": dict(F=2, B=20, seed=1, solve_camera=False),
+    "camera_only": dict(F=6, B=12, seed=2, solve_bundles=False),
+    "lens_focal": dict(F=12, B=16, seed=4, fixed_bundles=16, solve_bundles=False,
+                       lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree2_v=-0.002, degree4_distortion=0.01),
+                       solve_focal=True, solve_lens=("degree2_distortion", "degree2_u", "degree2_v", "degree4_distortion"),
+                       focal_init=33.0, period=12),
+}
+
+
+@pytest.mark.parametrize("name", list(SPARSE_CASES))
+def test_block_sparse_oracle_matches_dense_oracle(name):
+    """oracle_sparse.h (normal equations + Schur complement; what makes full-size CPU solves and
+    the tests/golden/fullsize_*.npz vectors possible) against the faithful dense path
+    (one scene evaluation per column, pivoted-QR lmder): same LM decisions, same answers."""
+    from mayamatchmovesolver_b200 import synth
+    sb, _ = synth.make_scene(**SPARSE_CASES[name])
+    rd = OracleProblem(sb).solve()
+    rs = OracleProblem(sb).solve_sparse(threads=2)
+    assert rs.status == 0
+    assert (rs.reason_num, rs.iteration_num, rs.iteration_attempt_num) == (rd.reason_num, rd.iteration_num, rd.iteration_attempt_num)
+    assert (rs.iteration_function_num, rs.iteration_jacobian_num, rs.error_is_better) == \
+           (rd.iteration_function_num, rd.iteration_jacobian_num, rd.error_is_better)
+    scale = np.maximum(np.abs(rd.attr_values), 1.0)
+    assert np.max(np.abs(rs.attr_values - rd.attr_values) / scale) <= 1e-7
+    assert np.max(np.abs(rs.error_dist - rd.error_dist)) <= 1e-6
+    assert abs(rs.error_final - rd.error_final) <= 1e-7 * max(1.0, rd.error_final)
