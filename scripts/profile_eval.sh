@@ -2,7 +2,7 @@
 # One gpurun call: plain bench run, then the ncu launch list and a full capture of the
 # Jacobian kernel of the same command (B200_PROFILING.md recipe).
 set -u
-TAG=${1:-r1d}
+TAG=${1:-r1k}
 CMD="python bench.py --steps 5 --warmup 3 --no-cpu"
 $CMD > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \

@@ -1,7 +1,7 @@
 #!/bin/bash
 # full captures of the dominant LM kernels of one cfg3 global solve (host-driven loop so
 # that ncu sees plain launches; the graph replays the same kernels)
-TAG=${1:-r1h}
+TAG=${1:-r1k}
 export MMB_LM_GRAPH=0
 CMD="python scripts/solve_profile.py 1000 500 3"
 $CMD > gpurun_out/${TAG}_solve_plain2.log 2>&1 || exit 1

@@ -1,6 +1,6 @@
 #!/bin/bash
 # launch list of one cfg3 global solve (shares of the LM kernels)
-TAG=${1:-r1e}
+TAG=${1:-r1k}
 CMD="python scripts/solve_profile.py 1000 500 6"
 MMB_LM_PROFILE=0 $CMD > gpurun_out/${TAG}_solve_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -s 200 -c 700 --csv \
