@@ -334,6 +334,21 @@ void mmb_request_cancel(mmb_problem *p);
 mmb_status mmb_bench_eval(mmb_problem *p, int32_t reps, int32_t flush_l2,
                           double *ms_per_eval, double *ms_jacobian_kernel,
                           int32_t *launches);
+/* Bulk lens (un)distortion of a point buffer: LensModel::applyModelUndistort
+ * (direction 0) / applyModelDistort (direction 1) of
+ * lib/cppbind/mmlens/src/lens_model_3de_*.cpp applied to n_points interleaved
+ * (x, y) pairs in -0.5..0.5 units -- the per-pixel loop of tools/lensdistortion
+ * (ST-maps).  coeffs [MMB_LENS_MAX_COEFFS] in the model's parameter order (NULL
+ * = zeros), camera_params [6] as in mmb_scene_desc.lens_camera_params.  Host
+ * buffers in and out; the arithmetic is the solve path's own lens code. */
+mmb_status mmb_lens_apply(int32_t device, int32_t model, const double *coeffs,
+                          const double *camera_params, int32_t direction,
+                          int64_t n_points, const double *xy_in,
+                          double *xy_out);
+/* the same kernel timed on a device-resident grid of n_points (CUDA events) */
+mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs,
+                          const double *camera_params, int32_t direction,
+                          int64_t n_points, int32_t reps, double *ms_per_pass);
 /* measured FP64 ceilings of the device in TFLOP/s (dependent-free DFMA chains; DMMA
  * m8n8k4): the roofline denominators of the compute-bound kernels (lens distortion in
  * the loop, the reduced-system SYRK / Cholesky updates) */

@@ -105,6 +105,8 @@ SYMBOLS = [
                                        C.c_char_p, C.c_int64, C.POINTER(C.c_int64)]),
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
+    ("mmb_lens_apply", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, c_f64p, c_f64p]),
+    ("mmb_bench_lens", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, C.c_int32, c_f64p]),
     ("mmb_bench_fp64_peaks", C.c_int32, [C.c_int32, c_f64p, c_f64p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),
     ("mmb_solve_stats", C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libmmsolver_b200.so")
-SOURCES = ["problem.cpp", "shard.cpp", "results.cpp", "comm.cu", "kernels.cu", "lm_global.cu", "lm_perframe.cu", "peaks.cu", "c_api.cu"]
+SOURCES = ["problem.cpp", "shard.cpp", "results.cpp", "comm.cu", "kernels.cu", "lm_global.cu", "lm_perframe.cu", "peaks.cu", "lens_bulk.cu", "c_api.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC", "-DMMB_BUILD",

@@ -96,6 +96,7 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
     marker: only the listed markers take part; attr: the listed plugs become the solver
     attributes (in flag order); frame: the listed frame numbers (in flag order)."""
     sb = copy.deepcopy(scene)
+    sb._arrays_cache = None
     if frame is not None:
         numbers = [int(f) for f in frame]
         index = {int(n): i for i, n in enumerate(scene.frames)}
@@ -117,8 +118,10 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
         for i in range(len(sb.mkr_en)):
             if i not in keep:
                 sb.mkr_en[i] = np.zeros_like(sb.mkr_en[i])
+        sb._arrays_cache = None
     if attr is not None:
         sb.attr_ref, sb.attr_min, sb.attr_max, sb.attr_off, sb.attr_scl = [], [], [], [], []
+        sb._arrays_cache = None
         for entry in attr:
             if len(entry) != 5:
                 # the command logs an error and skips the flag (arg_flags_solve_object.cpp:262-273)

@@ -446,6 +446,32 @@ mmb_status mmb_bench_fp64_peaks(int32_t device, double *dfma_tflops, double *dmm
     return measure_fp64_peaks(device, dfma_tflops, dmma_tflops);
 }
 
+static mmb_status lens_args_ok(int32_t device, int32_t model, const double *cam, int32_t direction) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_last_error("no CUDA device: this library has no CPU path");
+        return MMB_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev || model < 0 || model > 4 || !cam || (direction != 0 && direction != 1))
+        return MMB_ERR_INVALID_ARGUMENT;
+    return MMB_OK;
+}
+
+mmb_status mmb_lens_apply(int32_t device, int32_t model, const double *coeffs, const double *camera_params,
+                          int32_t direction, int64_t n_points, const double *xy_in, double *xy_out) {
+    mmb_status st = lens_args_ok(device, model, camera_params, direction);
+    if (st != MMB_OK) return st;
+    if (n_points < 0 || (n_points > 0 && (!xy_in || !xy_out))) return MMB_ERR_INVALID_ARGUMENT;
+    return lens_apply_host(device, model, coeffs, camera_params, direction, n_points, xy_in, xy_out);
+}
+
+mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs, const double *camera_params,
+                          int32_t direction, int64_t n_points, int32_t reps, double *ms_per_pass) {
+    mmb_status st = lens_args_ok(device, model, camera_params, direction);
+    if (st != MMB_OK) return st;
+    return lens_bench(device, model, coeffs, camera_params, direction, n_points, reps, ms_per_pass);
+}
+
 mmb_status mmb_release_cached_memory(int32_t device) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;

@@ -99,6 +99,12 @@ struct DeviceProblem {
 // FP64 ceilings of the device (peaks.cu)
 mmb_status measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflops);
 
+// bulk lens (un)distortion of point buffers (lens_bulk.cu)
+mmb_status lens_apply_host(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
+                           const double *xy_in, double *xy_out);
+mmb_status lens_bench(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
+                      int reps, double *ms_per_pass);
+
 mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt, DeviceProblem **out);
 mmb_status ensure_jacobian_buffers(DeviceProblem *p);
 

@@ -1,0 +1,138 @@
+// Bulk lens (un)distortion of point buffers: the reference's
+// LensModel::applyModelUndistort / applyModelDistort loops
+// (lib/cppbind/mmlens/src/lens_model_3de_*.cpp, distortion_operations.h:33-96 -- what
+// tools/lensdistortion runs per pixel to make ST-maps) as one streaming kernel.
+//   direction 0 (undistort): direct polynomial, 32 B per point -> HBM-bound
+//   direction 1 (distort):   LDPK fixed-point inverse (<= 22 polynomial evaluations) -> FP64-bound
+// Same per-point arithmetic as the solve path (device_math.cuh), so the solver's lens and
+// this kernel cannot drift apart.
+#include <algorithm>
+#include <cstring>
+
+#include "device_problem.h"
+
+namespace mmb {
+
+struct LensBulk {
+    double rec[kLensRec];  // prepared record (lens_prepare)
+    double after[4];       // undistort: 2x2 applied after the polynomial
+    double before[4];      // undistort: 2x2 applied before it
+};
+
+// applyModelUndistort: unit -> diagonal-normalised -> [before] -> polynomial -> [after] -> unit
+__device__ __forceinline__ void lens_undistort_pt(const LensBulk &L, double px, double py, double &ox, double &oy) {
+    const int model = (int)L.rec[0];
+    ox = px; oy = py;
+    if (model == 0) return;
+    const double radius = L.rec[1], w = L.rec[2], h = L.rec[3], lx = L.rec[4], ly = L.rec[5];
+    double qx = (((px + 0.5) - 0.5) * w - lx) / radius;
+    double qy = (((py + 0.5) - 0.5) * h - ly) / radius;
+    {
+        const double tx = L.before[0] * qx + L.before[1] * qy, ty = L.before[2] * qx + L.before[3] * qy;
+        qx = tx; qy = ty;
+    }
+    double fx, fy;
+    lens_core(model, &L.rec[6], qx, qy, fx, fy);
+    const double x = L.after[0] * fx + L.after[1] * fy, y = L.after[2] * fx + L.after[3] * fy;
+    double xc = x * radius, yc = y * radius;
+    xc += (w / 2) + lx; yc += (h / 2) + ly;
+    ox = xc / w - 0.5; oy = yc / h - 0.5;
+}
+
+__global__ void __launch_bounds__(256) k_lens_bulk(LensBulk L, int direction, long long n,
+                                                   const double2 *__restrict__ in, double2 *__restrict__ out) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double2 p = in[i];
+        double2 o;
+        if (direction == 0) lens_undistort_pt(L, p.x, p.y, o.x, o.y);
+        else lens_distort(L.rec, p.x, p.y, o.x, o.y);
+        out[i] = o;
+    }
+}
+
+static void make_bulk(int model, const double *coeffs, const double *cam, LensBulk *L) {
+    double c[MMB_LENS_MAX_COEFFS];
+    for (int i = 0; i < MMB_LENS_MAX_COEFFS; ++i) c[i] = coeffs ? coeffs[i] : 0.0;
+    lens_prepare(model, c, cam, L->rec);
+    const double ident[4] = {1.0, 0.0, 0.0, 1.0};
+    std::memcpy(L->after, ident, sizeof(ident));
+    std::memcpy(L->before, ident, sizeof(ident));
+    if (model == 2) {
+        m2_inv(&L->rec[16], L->after);           // cylindric extender itself (the record holds its inverse)
+    } else if (model == 3 || model == 4) {
+        m2_inv(&L->rec[16], L->after);           // rotation / squeeze / pixel-aspect product
+        m2_inv(&L->rec[20], L->before);          // inverse of the matrix the distort direction applies last
+    }
+}
+
+static unsigned grid_for(long long n, int device) {
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const long long want = (n + 255) / 256;
+    return (unsigned)std::max<long long>(1, std::min<long long>(want, (long long)sms * 8));
+}
+
+mmb_status lens_apply_host(int device, int model, const double *coeffs, const double *cam, int direction,
+                           long long n, const double *xy_in, double *xy_out) {
+    MMB_CUDA_CHECK(cudaSetDevice(device));
+    LensBulk L;
+    make_bulk(model, coeffs, cam, &L);
+    if (n == 0) return MMB_OK;
+    cudaStream_t s = nullptr;
+    MMB_CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    double2 *d_in = nullptr, *d_out = nullptr;
+    cudaError_t e = cudaMallocAsync((void **)&d_in, sizeof(double2) * n, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_out, sizeof(double2) * n, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, xy_in, sizeof(double2) * n, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) {
+        k_lens_bulk<<<grid_for(n, device), 256, 0, s>>>(L, direction, n, d_in, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xy_out, d_out, sizeof(double2) * n, cudaMemcpyDeviceToHost, s);
+    if (d_in) cudaFreeAsync(d_in, s);
+    if (d_out) cudaFreeAsync(d_out, s);
+    const cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaStreamDestroy(s);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) { set_last_error(std::string("lens_apply: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
+    return MMB_OK;
+}
+
+// device-resident timing on a regular grid of points over the image (an ST-map)
+__global__ void k_lens_grid(long long n, int width, double2 *pts) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const long long y = i / width, x = i - y * width;
+        const long long height = (n + width - 1) / width;
+        pts[i] = make_double2(((double)x + 0.5) / width - 0.5, ((double)y + 0.5) / (double)height - 0.5);
+    }
+}
+
+mmb_status lens_bench(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
+                      int reps, double *ms_per_pass) {
+    MMB_CUDA_CHECK(cudaSetDevice(device));
+    if (n <= 0 || reps <= 0) return MMB_ERR_INVALID_ARGUMENT;
+    LensBulk L;
+    make_bulk(model, coeffs, cam, &L);
+    double2 *d_in = nullptr, *d_out = nullptr;
+    MMB_CUDA_CHECK(cudaMalloc((void **)&d_in, sizeof(double2) * n));
+    cudaError_t e = cudaMalloc((void **)&d_out, sizeof(double2) * n);
+    if (e != cudaSuccess) { cudaFree(d_in); set_last_error("lens_bench: out of memory"); return MMB_ERR_CUDA; }
+    const unsigned grid = grid_for(n, device);
+    k_lens_grid<<<grid, 256>>>(n, 4096, d_in);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    k_lens_bulk<<<grid, 256>>>(L, direction, n, d_in, d_out);  // warm-up
+    cudaEventRecord(e0);
+    for (int r = 0; r < reps; ++r) k_lens_bulk<<<grid, 256>>>(L, direction, n, d_in, d_out);
+    cudaEventRecord(e1);
+    e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) { set_last_error(std::string("lens_bench: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
+    if (ms_per_pass) *ms_per_pass = ms / reps;
+    return MMB_OK;
+}
+
+}  // namespace mmb

@@ -57,6 +57,7 @@ class SceneBuilder:
         self.lens_model, self.lens_attrs, self.lens_cam = [], [], []
         self.attr_ref, self.attr_min, self.attr_max, self.attr_off, self.attr_scl = [], [], [], [], []
         self.names = {}  # node name -> Node (what the command's -camera / -marker / -attr flags name)
+        self._arrays_cache = None  # flattened arrays of the current state (dropped by every mutator)
 
     def _register(self, node):
         if node.name is not None:
@@ -72,6 +73,7 @@ class SceneBuilder:
     # ---- attribute store (datablock.rs) --------------------------------
     def value(self, v):
         """scalar -> static slot, length-F sequence -> animated slot; returns the ref"""
+        self._arrays_cache = None
         if np.ndim(v) == 0:
             self._static.append(float(v))
             return len(self._static) - 1
@@ -84,6 +86,7 @@ class SceneBuilder:
         return self._static[ref] if ref >= 0 else float(self._anim[-ref - 1][frame_index])
 
     def set_value(self, ref, v, frame_index=None):
+        self._arrays_cache = None
         if ref >= 0:
             self._static[ref] = float(v)
         elif frame_index is None:
@@ -118,11 +121,13 @@ class SceneBuilder:
         return self._register(Node(len(self.cam_tfm) - 1, refs, "camera", name))
 
     def add_bundle(self, tfm, name=None):
+        self._arrays_cache = None
         self.bnd_tfm.append(int(getattr(tfm, "index", tfm)))
         return self._register(Node(len(self.bnd_tfm) - 1, {}, "bundle", name))
 
     def add_marker(self, cam, bnd, x, y, weight=1.0, enable=True, name=None):
         F = self.F
+        self._arrays_cache = None
         self.mkr_cam.append(int(getattr(cam, "index", cam)))
         self.mkr_bnd.append(int(getattr(bnd, "index", bnd)))
         self.mkr_x.append(np.broadcast_to(np.asarray(x, dtype=np.float64), (F,)).copy())
@@ -155,6 +160,7 @@ class SceneBuilder:
     def add_attr(self, ref, min=None, max=None, offset=None, scale=None):
         """One `-attr node.attr min max offset scale` flag; None keeps the
         reference default (maya_attr.cpp:88-91: -/+FLT_MAX, 0, 1)."""
+        self._arrays_cache = None
         self.attr_ref.append(int(ref))
         self.attr_min.append(-FLT_MAX if min is None else float(min))
         self.attr_max.append(FLT_MAX if max is None else float(max))
@@ -168,6 +174,7 @@ class SceneBuilder:
         import copy
         idx = np.asarray(frame_indices, dtype=np.int64)
         o = copy.deepcopy(self)
+        o._arrays_cache = None
         o.frames = self.frames[idx].copy()
         o.F = len(idx)
         o._anim = [a[idx].copy() for a in self._anim]
@@ -177,6 +184,10 @@ class SceneBuilder:
 
     # ---- flatten -------------------------------------------------------
     def arrays(self):
+        """flat numpy arrays of the scene (cached until the scene is changed through its
+        methods; code that edits the lists directly must set `_arrays_cache = None`)"""
+        if self._arrays_cache is not None:
+            return self._arrays_cache
         F = self.F
         i32 = lambda v, shape=None: np.ascontiguousarray(np.asarray(v, dtype=np.int32).reshape(shape) if shape else np.asarray(v, dtype=np.int32))
         f64 = lambda v: np.ascontiguousarray(np.asarray(v, dtype=np.float64))
@@ -200,6 +211,7 @@ class SceneBuilder:
             attr_ref=i32(self.attr_ref), attr_min=f64(self.attr_min), attr_max=f64(self.attr_max),
             attr_offset=f64(self.attr_off), attr_scale=f64(self.attr_scl),
         )
+        self._arrays_cache = a
         return a
 
     def desc(self):

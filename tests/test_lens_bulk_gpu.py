@@ -1,0 +1,89 @@
+"""Bulk lens (un)distortion kernel (mmb_lens_apply) against the reference's own compiled
+mmlens (oracle/_ref/libmmlens_ref.so) and the oracle restatement, all four 3DE models,
+both directions (lib/cppbind/mmlens/tests/test_once_*.cpp / test_both_*.cpp)."""
+import numpy as np
+import pytest
+
+from mayamatchmovesolver_b200 import lens
+from oraclelib import _p, oracle, ref_lens
+
+pytestmark = pytest.mark.gpu
+
+LENS_PARAMS = {
+    1: [0.1, 1.0, 0.01, 0.02, 0.05],
+    2: [0.1, 0.02, -0.01, 0.05, 0.01, -0.02, 10.0, 0.1],
+    3: [0.02, 0.01, -0.015, 0.005, 0.03, -0.01, 0.002, 0.004, -0.003, 0.001, 5.0, 1.02, 0.98],
+    4: [0.02, 0.01, -0.015, 0.005, 0.03, -0.01, 0.002, 0.004, -0.003, 0.001, 5.0, 1.02, 0.98, 1.1],
+}
+CAM = np.array([3.5, 3.6, 2.4, 1.0, 0.05, -0.03])
+# undistort is a closed-form polynomial: only FMA contraction separates GPU and CPU.
+# distort is the LDPK fixed-point iteration stopped at 1e-6 (diagonal units) and polished by
+# two Newton steps: a borderline stop may differ by one iteration.
+TOL = {0: 1e-13, 1: 1e-9}
+
+
+def _coeffs(model):
+    co = np.zeros(14)
+    co[:len(LENS_PARAMS[model])] = LENS_PARAMS[model]
+    return co
+
+
+@pytest.mark.parametrize("model", [1, 2, 3, 4])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_bulk_matches_reference_mmlens(model, direction):
+    rng = np.random.default_rng(10 * model + direction)
+    pts = rng.uniform(-0.5, 0.5, (100000, 2))
+    co = _coeffs(model)
+    got = lens.apply(model, co, pts, direction, CAM)
+    want = np.zeros_like(pts)
+    ref = ref_lens()
+    if ref is not None:
+        assert ref.ref_lens_apply(model, _p(co), _p(CAM), direction, len(pts), _p(pts), _p(want)) == 0
+        assert np.abs(got - want).max() < TOL[direction], np.abs(got - want).max()
+    orc = np.zeros_like(pts)
+    oracle().orc_lens_apply(model, _p(co), _p(CAM), direction, len(pts), _p(pts), _p(orc))
+    assert np.abs(got - orc).max() < TOL[direction], np.abs(got - orc).max()
+
+
+def test_passthrough_and_empty():
+    pts = np.random.default_rng(0).uniform(-0.5, 0.5, (1000, 2))
+    for direction in (0, 1):
+        assert np.array_equal(lens.apply(0, None, pts, direction, CAM), pts)
+        assert lens.apply(2, _coeffs(2), np.zeros((0, 2)), direction, CAM).shape == (0, 2)
+
+
+def test_coefficients_by_name_and_defaults():
+    pts = np.random.default_rng(1).uniform(-0.4, 0.4, (500, 2))
+    a = lens.apply("3de_classic", {"distortion": 0.1, "quartic_distortion": 0.05}, pts, 0, CAM)
+    b = lens.apply(1, [0.1, 1.0, 0.0, 0.0, 0.05], pts, 0, CAM)
+    assert np.array_equal(a, b)
+    with pytest.raises(KeyError):
+        lens.apply("3de_classic", {"nope": 1.0}, pts, 0, CAM)
+
+
+@pytest.mark.parametrize("model", [1, 2, 3, 4])
+def test_stmap_round_trip_full_size(model):
+    """size-independent property at ST-map size (UHD, 8.3 M points): undistort -> redistort
+    returns the pixel centres (test_both_*.cpp at every pixel)."""
+    w, h = 3840, 2160
+    xs = (np.arange(w) + 0.5) / w - 0.5
+    ys = (np.arange(h) + 0.5) / h - 0.5
+    pts = np.stack(np.meshgrid(xs, ys), axis=-1).reshape(-1, 2)
+    co = _coeffs(model)
+    und = lens.apply(model, co, pts, lens.UNDISTORT, CAM)
+    red = lens.apply(model, co, und, lens.DISTORT, CAM)
+    assert np.isfinite(red).all()
+    assert np.abs(red - pts).max() < 1e-8, np.abs(red - pts).max()
+
+
+def test_bad_arguments():
+    pts = np.zeros((4, 2))
+    with pytest.raises(Exception):
+        lens.apply(7, None, pts, 0, CAM)
+    with pytest.raises(Exception):
+        lens.apply(1, None, pts, 3, CAM)
+
+
+def test_device_resident_bench_runs():
+    ms = lens.bench(2, _coeffs(2), 0, 1 << 20, reps=3, camera_params=CAM)
+    assert 0 < ms < 100
