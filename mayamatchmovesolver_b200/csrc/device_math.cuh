@@ -237,8 +237,10 @@ MMB_HD void lens_prepare(int model, const double *c, const double *cam, double *
     rec[16] = 1.0; rec[19] = 1.0; rec[20] = 1.0; rec[23] = 1.0;
     if (model == 1) {  // ldpk_classic_3de_mixed_distortion.h:29-42
         const double ld = c[0], sq = c[1], cx = c[2], cy = c[3], qu = c[4];
-        rec[6] = ld / sq; rec[7] = (ld + cx) / sq; rec[8] = ld + cy; rec[9] = ld;
-        rec[10] = qu / sq; rec[11] = 2.0 * qu / sq; rec[12] = qu / sq;
+        // lens_core order: x row (x2 y2 x4 x2y2 y4) then y row
+        rec[6] = ld / sq; rec[7] = (ld + cx) / sq;
+        rec[8] = qu / sq; rec[9] = 2.0 * qu / sq; rec[10] = qu / sq;
+        rec[11] = ld + cy; rec[12] = ld;
         rec[13] = qu; rec[14] = 2.0 * qu; rec[15] = qu;
     } else if (model == 2) {  // radial decentered deg 4 + cylindric extender
         for (int i = 0; i < 6; ++i) rec[6 + i] = c[i];

@@ -53,7 +53,7 @@ def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
 def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, init_noise_t=0.1,
                init_noise_r=0.5, init_noise_b=0.05, fixed_bundles=0, lens=None, solve_focal=False,
                solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False, period=120.0,
-               in_frame=False):
+               in_frame=False, lens_model="3de_radial_std_deg4"):
     """One animated camera, B static bundles, full (or thinned) visibility.
 
     cfg2: make_scene(240, 50, 2, solve_bundles=False)
@@ -64,6 +64,8 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
     `in_frame` keeps every bundle inside the image on every frame (a plate only has
     markers inside the frame; outside it the degree-4 lens polynomial is not
     invertible and the fixed-point inverse of LDPK diverges) -- used by cfg4.
+    `lens_model` other than the radial one takes its coefficients from `lens` too, but
+    the markers are left undistorted (residual / Jacobian parity scenes, not fits).
     Returns (SceneBuilder, info dict).
     """
     rng = np.random.default_rng(seed)
@@ -79,7 +81,7 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
         # truth coefficients are only used to make the markers; the scene
         # starts from zero coefficients when they are solved
         init = {k: (0.0 if k in solve_lens else v) for k, v in lens.items()}
-        lens_node = sb.add_lens("3de_radial_std_deg4", camera_params=(focal_truth * 0.1, sensor_w * 0.1, sensor_h * 0.1, 1.0, 0.0, 0.0), **init)
+        lens_node = sb.add_lens(lens_model, camera_params=(focal_truth * 0.1, sensor_w * 0.1, sensor_h * 0.1, 1.0, 0.0, 0.0), **init)
     t0 = cam_t + rng.normal(0, init_noise_t, cam_t.shape) if solve_camera else cam_t
     r0 = cam_r + rng.normal(0, init_noise_r, cam_r.shape) if solve_camera else cam_r
     r0[:, 2] = cam_r[:, 2] + (rng.normal(0, init_noise_r, F) if solve_camera else 0.0)
@@ -97,7 +99,7 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
         x, y = project_truth(cam_t[f], cam_r[f], pts, focal_truth, sensor_w, sensor_h, rw, rh)
         mx[:, f] = x
         my[:, f] = y
-    if lens is not None:
+    if lens is not None and lens_model == "3de_radial_std_deg4" and lens.get("cylindric_bending", 0.0) == 0.0:
         mx, my = _distort_markers(mx, my, lens, (focal_truth * 0.1, sensor_w * 0.1, sensor_h * 0.1, 1.0, 0.0, 0.0), rw / rh, sensor_w / sensor_h)
     mx = mx + rng.normal(0, noise_px / 2048.0, mx.shape)
     my = my + rng.normal(0, noise_px / 2048.0, my.shape)

@@ -7,6 +7,7 @@ import time
 import numpy as np
 
 sys.path.insert(0, "tests")
+sys.path.insert(0, ".")
 from mayamatchmovesolver_b200 import lens  # noqa: E402
 from oraclelib import _p, ref_lens  # noqa: E402
 

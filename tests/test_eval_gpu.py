@@ -20,6 +20,22 @@ CASES = [
     dict(F=30, B=40, seed=3),
     dict(F=12, B=16, seed=4, lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree2_v=-0.002, degree4_distortion=0.01),
          solve_focal=True, solve_lens=("degree2_distortion", "degree2_u", "degree2_v", "degree4_distortion"), focal_init=33.0),
+    # the other lens models in the loop, coefficients and focal length solved (in_frame: the
+    # LDPK inverse only converges inside the image)
+    dict(F=6, B=12, seed=6, in_frame=True, lens_model="3de_classic",
+         lens=dict(distortion=0.06, anamorphic_squeeze=1.02, curvature_x=0.01, curvature_y=-0.005, quartic_distortion=0.01),
+         solve_focal=True, solve_lens=("distortion", "curvature_x", "quartic_distortion")),
+    dict(F=6, B=12, seed=7, in_frame=True, lens_model="3de_radial_std_deg4",
+         lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree4_distortion=0.01, cylindric_direction=20.0, cylindric_bending=0.05),
+         solve_lens=("degree2_distortion", "cylindric_bending")),
+    dict(F=6, B=12, seed=8, in_frame=True, lens_model="3de_anamorphic_std_deg4",
+         lens=dict(degree2_cx02=0.02, degree2_cy02=0.01, degree2_cx22=-0.01, degree4_cx04=0.01, degree4_cy44=0.002,
+                   lens_rotation=3.0, squeeze_x=1.02, squeeze_y=0.99),
+         solve_focal=True, solve_lens=("degree2_cx02", "degree2_cy02", "lens_rotation", "squeeze_x")),
+    dict(F=6, B=12, seed=9, in_frame=True, lens_model="3de_anamorphic_std_deg4_rescaled",
+         lens=dict(degree2_cx02=0.02, degree2_cy02=0.01, degree4_cx24=0.004, lens_rotation=-2.0, squeeze_x=1.01,
+                   squeeze_y=1.0, rescale=1.05),
+         solve_lens=("degree2_cx02", "rescale")),
 ]
 
 
