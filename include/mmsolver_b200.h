@@ -267,6 +267,17 @@ mmb_status mmb_shard_param_map(const mmb_scene_desc *scene, int32_t world,
 mmb_status mmb_problem_create_shard(const mmb_scene_desc *scene,
                                     const mmb_options *opt, int32_t rank,
                                     int32_t world, mmb_problem **out);
+/* The same for a caller that holds only its own frames: `slice` is frames
+ * [frame_begin, frame_begin + slice->num_frames) of a scene of frames_global
+ * frames (static attributes, objects and attr flags identical on every rank).
+ * Nothing is cut; use it when the whole scene does not fit one host (cfg5:
+ * 4e8 observations).  Unsharded id of local parameter: animated attribute a,
+ * local frame f -> its global base + frame_begin + f (as mmb_shard_param_map). */
+mmb_status mmb_problem_create_shard_local(const mmb_scene_desc *slice,
+                                          const mmb_options *opt,
+                                          int32_t frame_begin,
+                                          int32_t frames_global,
+                                          mmb_problem **out);
 /* rank 0 makes the id (an ncclUniqueId; local_backend != 0: an in-process
  * group of handles on one device, used by single-GPU tests) and hands the
  * 128 bytes to the other ranks by any channel (torch.distributed, MPI, file) */

@@ -91,6 +91,8 @@ SYMBOLS = [
     ("mmb_solve_per_frame", C.c_int32, [C.c_void_p, C.POINTER(Result), C.POINTER(Result), c_f64p, c_f64p, c_f64p]),
     ("mmb_shard_frames", C.c_int32, [C.c_int32, C.c_int32, C.c_int32, c_i32p, c_i32p]),
     ("mmb_shard_param_map", C.c_int32, [C.POINTER(SceneDesc), C.c_int32, C.c_int32, c_i32p, c_i32p]),
+    ("mmb_problem_create_shard_local", C.c_int32, [C.POINTER(SceneDesc), C.POINTER(Options), C.c_int32, C.c_int32,
+                                                   C.POINTER(C.c_void_p)]),
     ("mmb_problem_create_shard", C.c_int32, [C.POINTER(SceneDesc), C.POINTER(Options), C.c_int32, C.c_int32,
                                              C.POINTER(C.c_void_p)]),
     ("mmb_comm_unique_id", C.c_int32, [c_u8p, C.c_int32]),

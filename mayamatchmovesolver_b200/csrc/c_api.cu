@@ -272,6 +272,18 @@ mmb_status mmb_problem_create_shard(const mmb_scene_desc *scene, const mmb_optio
     }
 }
 
+mmb_status mmb_problem_create_shard_local(const mmb_scene_desc *slice, const mmb_options *opt, int32_t frame_begin,
+                                          int32_t frames_global, mmb_problem **out) {
+    if (!slice || !opt || !out || frame_begin < 0 || frame_begin + slice->num_frames > frames_global)
+        return MMB_ERR_INVALID_ARGUMENT;
+    *out = nullptr;
+    mmb_status st = mmb_problem_create(slice, opt, out);
+    if (st != MMB_OK) return st;
+    (*out)->dp->frame_begin = frame_begin;
+    (*out)->dp->frames_global = frames_global;
+    return MMB_OK;
+}
+
 mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES], int32_t local_backend) {
     if (!id) return MMB_ERR_INVALID_ARGUMENT;
     try {

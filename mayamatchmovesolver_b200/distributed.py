@@ -110,20 +110,26 @@ def make_comm(group, device=0, local_backend=False):
     return Comm(cid, group.rank, group.world, device)
 
 
-def solve_global_sharded(scene, group, device=0, options=None, local_backend=False, comm=None, **opt_overrides):
+def solve_global_sharded(scene, group, device=0, options=None, local_backend=False, comm=None, local_slice=None,
+                         gather=True, **opt_overrides):
     """frameSolveMode=0 over `group`: the sharded global solve.  -> SolveResult with unsharded
     x / attr values / per-observation distances, identical on every rank.  `comm`: a
-    communicator from make_comm() to reuse; else one is made for this solve."""
+    communicator from make_comm() to reuse; else one is made for this solve.
+    `local_slice=(frame_begin, frames_global)`: `scene` holds only this rank's frames.
+    `gather=False` skips the merge of the per-rank vectors (-> this rank's own SolveResult)."""
     cid = None
     if comm is None and group.world > 1:
         cid = comm_unique_id(local_backend) if group.rank == 0 else None
         cid = group.broadcast_bytes(cid, src=0)
-    with Problem(scene, options=options, shard=(group.rank, group.world), device=device, **opt_overrides) as p:
+    with Problem(scene, options=options, shard=(group.rank, group.world), local_slice=local_slice, device=device,
+                 **opt_overrides) as p:
         if comm is not None:
             p.use_comm(comm)
         elif group.world > 1:
             p.attach_comm(cid, group.rank, group.world)
         r = p.solve()
+        if not gather:
+            return r
         e2m, _ = p.index_maps()
         payload = dict(map=p.param_map, x=r.x, av=r.attr_values, f0=p.frame_begin,
                        obs=(e2m[:, 0].copy(), e2m[:, 1] + p.frame_begin, r.error_dist))

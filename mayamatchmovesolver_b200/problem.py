@@ -39,6 +39,20 @@ def shard_param_map(scene, world, rank):
     return out
 
 
+def local_slice_param_map(scene, frame_begin, frames_global):
+    """the same map for a scene that already is frames [frame_begin, frame_begin + F) of a
+    frames_global-frame scene (mmb_problem_create_shard_local; shard.cpp shard_param_map)"""
+    out, gbase = [], 0
+    for ref in scene.arrays()["attr_ref"]:
+        if ref < 0:   # animated: one parameter per frame, frame-minor
+            out.append(gbase + frame_begin + np.arange(scene.F, dtype=np.int64))
+            gbase += frames_global
+        else:
+            out.append(np.array([gbase], dtype=np.int64))
+            gbase += 1
+    return np.concatenate(out).astype(np.int32) if out else np.zeros(0, np.int32)
+
+
 def comm_unique_id(local_backend=False):
     """128 bytes: an ncclUniqueId (or the id of an in-process group for single-GPU tests)"""
     lib = _capi.load()
@@ -126,16 +140,25 @@ def _copy_result(r):
 
 
 class Problem:
-    def __init__(self, scene, options=None, shard=None, **opt_overrides):
+    def __init__(self, scene, options=None, shard=None, local_slice=None, **opt_overrides):
         """shard = (rank, world): the handle covers this rank's frame range of `scene`
-        (mmb_problem_create_shard); parameters and observations are then numbered locally."""
+        (mmb_problem_create_shard); parameters and observations are then numbered locally.
+        local_slice = (frame_begin, frames_global): `scene` already IS this rank's frame range
+        of a larger scene (mmb_problem_create_shard_local)."""
         self._lib = _capi.load()
         self.options = options if options is not None else default_options(**opt_overrides)
         desc, keep = scene.desc()
         self.num_frames = int(desc.num_frames)
         self.frame_begin, self.shard = 0, None
         self._h = C.c_void_p()
-        if shard is None:
+        if local_slice is not None:
+            f0, fg = int(local_slice[0]), int(local_slice[1])
+            check(self._lib.mmb_problem_create_shard_local(C.byref(desc), C.byref(self.options), f0, fg,
+                                                           C.byref(self._h)), "mmb_problem_create_shard_local")
+            self.shard = shard
+            self.frame_begin = f0
+            self.param_map = local_slice_param_map(scene, f0, fg)
+        elif shard is None:
             check(self._lib.mmb_problem_create(C.byref(desc), C.byref(self.options), C.byref(self._h)),
                   "mmb_problem_create")
         else:

@@ -153,3 +153,92 @@ def _distort_markers(mx, my, lens, cam6, render_aspect, sensor_aspect):
         px = px + qx - fx
         py = py + qy - fy
     return px * radius / w, py * radius / h / scale_y
+
+
+def witness_camera_paths(C, frames, focus=(0.0, 0.0, -22.0), radius=22.0, arc_deg=80.0, period=120.0):
+    """C cameras on an arc around `focus`, each looking at it, with a small deterministic
+    wobble that is a function of the absolute frame number (so that a rank can generate its
+    own frame range of a sharded scene).  -> t [C, F, 3], r [C, F, 3] degrees (rotate order xyz)"""
+    f = np.asarray(frames, dtype=np.float64)
+    t = np.zeros((C, len(f), 3))
+    r = np.zeros((C, len(f), 3))
+    for c in range(C):
+        th = (-0.5 + (c + 0.5) / C) * arc_deg
+        w = 2 * np.pi * f / period + 0.7 * c
+        t[c, :, 0] = focus[0] + radius * np.sin(th * DEG) + 0.5 * np.sin(w)
+        t[c, :, 1] = focus[1] + 0.3 * np.sin(w + 1.0)
+        t[c, :, 2] = focus[2] + radius * np.cos(th * DEG) + 0.5 * np.sin(w + 2.0)
+        r[c, :, 0] = 1.0 * np.sin(w + 3.0)
+        r[c, :, 1] = th + 1.5 * np.sin(w + 4.0)
+        r[c, :, 2] = 0.5 * np.sin(w + 5.0)
+    return t, r
+
+
+def make_multicam_scene(C, F, B, seed, frame_range=None, noise_px=0.5, init_noise_t=0.05, init_noise_r=0.2,
+                        init_noise_b=0.05, fixed_bundles=0, solve_camera=True, solve_bundles=True):
+    """cfg5 shape: C witness cameras (animated, 6 attributes each solved per frame) all seeing
+    the same B static bundles on every frame: M = C*B markers, Nobs = C*B*F.
+
+    `frame_range=(f0, f1)` generates only frames f0..f1-1 of the F-frame scene (this rank's
+    shard, for Problem(..., local_slice=(f0, F))): truth bundles, start values of the static
+    attributes and the camera paths do not depend on the range; marker noise and the start
+    noise of the animated attributes are seeded per absolute frame.
+    Returns (SceneBuilder, info dict).
+    """
+    f0, f1 = (0, F) if frame_range is None else frame_range
+    frames = np.arange(f0, f1)
+    Fl = len(frames)
+    rng = np.random.default_rng(seed)
+    sensor_w, sensor_h, rw, rh, focal = 36.0, 24.0, 2048, 1556, 35.0
+    pts = np.stack([rng.uniform(-4, 4, B), rng.uniform(-2.2, 2.2, B), rng.uniform(-26, -18, B)], 1)
+    b0 = pts + (rng.normal(0, init_noise_b, pts.shape) if solve_bundles else 0.0)
+    if fixed_bundles:
+        b0[:fixed_bundles] = pts[:fixed_bundles]
+    cam_t, cam_r = witness_camera_paths(C, frames)
+    # per-frame random streams: the same numbers whatever range the frame is generated in
+    def per_frame_normal(tag, shape_tail, sigma):
+        out = np.zeros((Fl,) + shape_tail)
+        if sigma == 0.0:
+            return out
+        for i, fr in enumerate(frames):
+            out[i] = np.random.default_rng([seed, tag, int(fr)]).normal(0, sigma, shape_tail)
+        return out
+    nt = per_frame_normal(1, (C, 3), init_noise_t if solve_camera else 0.0)
+    nr = per_frame_normal(2, (C, 3), init_noise_r if solve_camera else 0.0)
+    nm = per_frame_normal(3, (C, B, 2), noise_px / 2048.0)
+    sb = SceneBuilder(frames=frames + 1)
+    cams, cam_tfms = [], []
+    for c in range(C):
+        t0 = cam_t[c] + nt[:, c]
+        r0 = cam_r[c] + nr[:, c]
+        tf = sb.add_transform(tx=t0[:, 0], ty=t0[:, 1], tz=t0[:, 2], rx=r0[:, 0], ry=r0[:, 1], rz=r0[:, 2])
+        cam_tfms.append(tf)
+        cams.append(sb.add_camera(tf, film_fit="horizontal", render_width=rw, render_height=rh,
+                                  sensor_width_mm=sensor_w, sensor_height_mm=sensor_h, focal_length_mm=focal))
+    bnds, bnd_tfms = [], []
+    for b in range(B):
+        tf = sb.add_transform(tx=b0[b, 0], ty=b0[b, 1], tz=b0[b, 2])
+        bnd_tfms.append(tf)
+        bnds.append(sb.add_bundle(tf))
+    ones = np.ones(Fl)
+    en = np.ones(Fl, np.uint8)
+    for c in range(C):
+        mx = np.zeros((B, Fl))
+        my = np.zeros((B, Fl))
+        for i in range(Fl):
+            x, y = project_truth(cam_t[c, i], cam_r[c, i], pts, focal, sensor_w, sensor_h, rw, rh)
+            mx[:, i] = x + nm[i, c, :, 0]
+            my[:, i] = y + nm[i, c, :, 1]
+        for b in range(B):
+            sb.add_marker(cams[c], bnds[b], mx[b], my[b], weight=ones, enable=en)
+    if solve_camera:
+        for tf in cam_tfms:
+            for k in ("tx", "ty", "tz", "rx", "ry", "rz"):
+                sb.add_attr(tf[k])
+    if solve_bundles:
+        for b in range(fixed_bundles, B):
+            for k in ("tx", "ty", "tz"):
+                sb.add_attr(bnd_tfms[b][k])
+    info = dict(C=C, F=F, B=B, seed=seed, frame_range=(f0, f1), truth_points=pts, truth_cam_t=cam_t, truth_cam_r=cam_r,
+                cam_tfms=cam_tfms, cams=cams, bnd_tfms=bnd_tfms)
+    return sb, info
