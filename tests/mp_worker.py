@@ -18,7 +18,8 @@ import torch.distributed as dist  # noqa: E402
 from mayamatchmovesolver_b200 import _capi, synth  # noqa: E402
 from mayamatchmovesolver_b200.distributed import (TorchGroup, make_comm, merge_shard_vectors,  # noqa: E402
                                                   solve_global_sharded, solve_per_frame_sharded)
-from mayamatchmovesolver_b200.problem import Problem, aggregate_results, shard_frames, shard_param_map  # noqa: E402
+from mayamatchmovesolver_b200.problem import (Problem, aggregate_results, local_slice_param_map, shard_frames,  # noqa: E402
+                                              shard_param_map)
 
 
 def cpu_mode():
@@ -34,6 +35,16 @@ def cpu_mode():
     parts.sort(key=lambda d: d["f0"])
     x = merge_shard_vectors(n, [d["map"] for d in parts], [d["x"] for d in parts])
     np.testing.assert_array_equal(x, 10.0 * np.arange(n))
+    # a rank that generated only its own frames of a multi-camera scene numbers its
+    # parameters like the library's cut of the full scene
+    C_, F_, B_ = 3, 11, 4
+    full, _ = synth.make_multicam_scene(C_, F_, B_, 7)
+    g0, g1 = shard_frames(F_, g.world, g.rank)
+    mine, _ = synth.make_multicam_scene(C_, F_, B_, 7, frame_range=(g0, g1))
+    np.testing.assert_array_equal(local_slice_param_map(mine, g0, F_), shard_param_map(full, g.world, g.rank))
+    a_full, a_mine = full.arrays(), mine.arrays()
+    np.testing.assert_array_equal(a_full["mkr_x"].reshape(-1, F_)[:, g0:g1], a_mine["mkr_x"].reshape(-1, g1 - g0))
+    np.testing.assert_array_equal(a_full["anim_values"].reshape(-1, F_)[:, g0:g1], a_mine["anim_values"].reshape(-1, g1 - g0))
     # per-frame records: frame f has error_final = f + 1
     mine = []
     for f in range(f0, f1):
@@ -74,6 +85,18 @@ def gpu_mode():
     comm.close()
     sb2, _ = synth.make_scene(F=30, B=16, seed=22, solve_bundles=False, period=30)
     rp, per = solve_per_frame_sharded(sb2, g, device=local)
+    # cfg5 shape: witness cameras, every rank generates and holds only its own frames
+    C5, F5, B5 = 4, 18, 16
+    h0, h1 = shard_frames(F5, g.world, g.rank)
+    mine, _ = synth.make_multicam_scene(C5, F5, B5, 3, frame_range=(h0, h1), fixed_bundles=4)
+    r5 = solve_global_sharded(mine, g, device=local, local_slice=(h0, F5))
+    if g.rank == 0:
+        full5, _ = synth.make_multicam_scene(C5, F5, B5, 3, fixed_bundles=4)
+        with Problem(full5, device=local) as p:
+            u5 = p.solve()
+        assert (r5.reason_num, r5.iteration_num, r5.iteration_attempt_num) == (u5.reason_num, u5.iteration_num, u5.iteration_attempt_num), (r5, u5)
+        assert np.max(np.abs(r5.attr_values - u5.attr_values) / np.maximum(np.abs(u5.attr_values), 1.0)) <= 1e-6
+        assert np.max(np.abs(r5.error_dist - u5.error_dist)) <= 1e-5
     if g.rank == 0:
         with Problem(sb, device=local) as p:
             r1 = p.solve()
