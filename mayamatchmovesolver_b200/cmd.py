@@ -127,7 +127,7 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
                 # the command logs an error and skips the flag (arg_flags_solve_object.cpp:262-273)
                 continue
             plug, mn, mx, off, scl = entry
-            sb.add_attr(sb.plug(plug), min=float(mn) if _is_double(mn) else None, max=float(mx) if _is_double(mx) else None,
+            sb.add_attr(sb.plug(plug) if isinstance(plug, str) else int(plug), min=float(mn) if _is_double(mn) else None, max=float(mx) if _is_double(mx) else None,
                         offset=float(off) if _is_double(off) else None, scale=float(scl) if _is_double(scl) else None)
     return sb
 
