@@ -61,7 +61,10 @@ mmb_status mmb_problem_create(const mmb_scene_desc *scene, const mmb_options *op
     *out = nullptr;
     try {
         DeviceProblem *dp = nullptr;
-        mmb_status st = device_problem_create(scene, opt, &dp);
+        mmb_options o = *opt;
+        // lmdif only has forward differences (adjust_cminpack_lmdif.cpp:103-105)
+        if (o.solver_type == 1) o.auto_diff_type = 0;
+        mmb_status st = device_problem_create(scene, &o, &dp);
         if (st != MMB_OK) return st;
         mmb_problem *p = new mmb_problem{dp};
         *out = p;

@@ -27,6 +27,8 @@ struct DevScene {
     int any_lens;
     int lens_literal;   // reference's [markerIndex + frameIndex] lens read
     double delta;       // SolverOptions.delta
+    int lmdif;          // solverType == cminpack_lmdif: fdjac2 relative forward step
+    double fd_eps;      // sqrt(max(|delta|, epsmch))
     double image_width;
     // attribute store (AttrDataBlock): live values
     const double *stat; // [num_static]  read-only: solved values come from x
@@ -135,8 +137,15 @@ MMB_HD AttrView make_view(const DevScene &s, const double *x, int f, int attr, i
     inv_delta_a = 0.0;
     if (var > 0) {
         const int p = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
-        const double da = parameter_delta(x[p], s.delta, 1.0, s.attr_min[attr], s.attr_max[attr]);
-        const double db = parameter_delta(x[p], s.delta, -1.0, s.attr_min[attr], s.attr_max[attr]);
+        double da, db;
+        if (s.lmdif) {  // fdjac2: h = eps * |x_j|, eps when x_j == 0; no bound logic
+            da = s.fd_eps * fabs(x[p]);
+            if (da == 0.0) da = s.fd_eps;
+            db = -da;
+        } else {
+            da = parameter_delta(x[p], s.delta, 1.0, s.attr_min[attr], s.attr_max[attr]);
+            db = parameter_delta(x[p], s.delta, -1.0, s.attr_min[attr], s.attr_max[attr]);
+        }
         s.par_delta_a[p] = da;  // same value from every entity that depends on p
         s.par_delta_b[p] = db;
         inv_delta_a = 1.0 / da;

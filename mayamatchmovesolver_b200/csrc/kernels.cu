@@ -241,6 +241,8 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     d.any_lens = hp.any_lens;
     d.lens_literal = opt->lens_index_literal;
     d.delta = opt->delta;
+    d.lmdif = opt->solver_type == 1;
+    d.fd_eps = std::sqrt(std::max(std::fabs(opt->delta), 2.220446049250313e-16));
     d.image_width = opt->image_width;
     CK(A.upload(&p->d_stat0, hp.stat0));
     CK(A.upload(&p->d_anim0, hp.anim0));

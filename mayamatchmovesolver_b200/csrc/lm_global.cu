@@ -213,6 +213,7 @@ __global__ void k_ctrl_prep_decide(LmState *st, const double *scal, const double
     const bool first = st->iter == 1;
     const double g = fmax(mx[0], st->part_s[2]);
     st->njev += 1;
+    st->nfev += st->nfev_per_jac;
     if (first) {
         st->xnorm = sqrt(scal[0] + st->part_s[0]);
         st->delta = st->factor * st->xnorm;
@@ -1054,6 +1055,9 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     LmState h{};
     h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
     h.ftol = hp.opt.eps1; h.xtol = hp.opt.eps2; h.gtol = hp.opt.eps3; h.factor = hp.opt.tau * 100.0;
+    // lmdif: fdjac2 calls fcn once per parameter of the WHOLE problem (all shards)
+    const int n_all = p->frames_global > hp.F ? hp.ns + hp.na * p->frames_global : hp.n;
+    h.nfev_per_jac = hp.opt.solver_type == 1 ? n_all : 0;
     *w->h_st = h;
     MMB_CUDA_CHECK(cudaMemcpyAsync(w->st, w->h_st, sizeof(LmState), cudaMemcpyHostToDevice, p->stream));
 
@@ -1115,7 +1119,8 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     res->success = 1;  // success = iterNum > 0: the first function evaluation always runs
     res->reason_num = res->user_interrupted ? -1 : f.info;
     res->iteration_num = f.nfev;
-    res->iteration_function_num = f.nfev;  // iflag = 1 calls: the first evaluation + one per trial
+    // iflag = 1 calls: the first evaluation + one per trial (lmdif's nfev also counts fdjac2's calls)
+    res->iteration_function_num = f.nfev - f.njev * f.nfev_per_jac;
     res->iteration_jacobian_num = f.njev * hp.n * (hp.opt.auto_diff_type == 1 ? 2 : 1);
     res->iteration_attempt_num = f.njev;
     res->error_avg = f.err_avg; res->error_min = f.err_min; res->error_max = f.err_max;

@@ -28,6 +28,7 @@ struct PfFrameResult {
 
 struct PfArgs {
     int na, F, kmax, maxfev, mode, accept_only_better;
+    int nfev_per_jac;  // lmdif: na function calls per Jacobian count towards maxfev
     double ftol, xtol, gtol, factor;
     const int32_t *frame_obs_start;  // [F+1]
     const int32_t *frame_obs;        // [nobs] observation ids grouped by frame
@@ -245,6 +246,7 @@ __global__ void __launch_bounds__(kPfThreads) k_perframe_lm(DevScene s, PfArgs a
         __syncthreads();
         if (tid == 0) {
             sh.njev += 1;
+            sh.nfev += a.nfev_per_jac;
             const bool first = sh.iter == 1;
             double xs2 = 0.0, gmax = 0.0, gs = 0.0;
             for (int j = 0; j < na; ++j) {
@@ -415,6 +417,7 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     }
     PfArgs a{};
     a.na = hp.na; a.F = hp.F; a.kmax = p->ds.kmax; a.maxfev = hp.opt.iter_max;
+    a.nfev_per_jac = hp.opt.solver_type == 1 ? hp.na : 0;
     a.mode = hp.opt.auto_param_scale == 1 ? 1 : 2; a.accept_only_better = hp.opt.accept_only_better;
     a.ftol = hp.opt.eps1; a.xtol = hp.opt.eps2; a.gtol = hp.opt.eps3; a.factor = hp.opt.tau * 100.0;
     int32_t *d_i = nullptr; int8_t *d_8 = nullptr; double *d_x2 = nullptr, *d_f2 = nullptr, *d_d2 = nullptr;

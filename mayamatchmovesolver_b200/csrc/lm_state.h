@@ -18,6 +18,7 @@ namespace mmb {
 struct LmState {
     // problem constants
     int n, m, maxfev, mode;
+    int nfev_per_jac;  // lmdif: fdjac2 costs n function calls per Jacobian (0 for lmder)
     double ftol, xtol, gtol, factor;
     // lmder scalars
     double fnorm, fnorm1, xnorm, delta, par, gnorm, pnorm, ratio, actred, prered;

@@ -119,8 +119,8 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         hp.error = "only sceneGraphMode=2 (mmscenegraph) is implemented; the Maya DAG mode needs Maya";
         return MMB_ERR_UNSUPPORTED;
     }
-    if (opt->solver_type != 2) {
-        hp.error = "only solverType=2 (cminpack_lmder) is implemented";
+    if (opt->solver_type != 2 && opt->solver_type != 1) {
+        hp.error = "only solverType=2 (cminpack_lmder) and 1 (cminpack_lmdif) are implemented";
         return MMB_ERR_UNSUPPORTED;
     }
     const size_t F = hp.F;

@@ -39,8 +39,11 @@ static void determineMarkersToBeEvaluated(orc_problem *p, const double *x,
 }
 
 // solveFunc iflag=1: adjust_solveFunc.cpp:262-303
-static void func_residuals(orc_problem *p, const double *x, double *fvec) {
-    ++p->funcEvalNum; ++p->iterNum;
+static void func_residuals(orc_problem *p, const double *x, double *fvec, bool jacobian_call = false) {
+    // incrementNormalIteration / incrementJacobianIteration (adjust_solveFunc.cpp:227-259):
+    // an lmdif fdjac2 call (iflag = 2, doCalcJacobian = false) counts as a Jacobian iteration
+    ++p->funcEvalNum;
+    if (jacobian_call) ++p->jacIterNum; else ++p->iterNum;
     std::vector<bool> evalM(p->nobs, true), frameEn(p->F, true);
     setParameters(p, x);
     double a, b, c;
@@ -98,11 +101,12 @@ static void func_jacobian(orc_problem *p, const double *x, const double *fvec,
     }
 }
 
-struct CbData { orc_problem *p; bool skip; };
+struct CbData { orc_problem *p; bool skip; bool dif = false; };
 static int lm_callback(void *ud, int m, int n, const double *x, double *fvec,
                        double *fjac, int ldfjac, int iflag) {
     CbData *d = (CbData *)ud; (void)m; (void)n;
     if (iflag == 1) func_residuals(d->p, x, fvec);
+    else if (iflag == 2 && d->dif) func_residuals(d->p, x, fvec, true);  // solveFunc_cminpack_lmdif
     else if (iflag == 2) func_jacobian(d->p, x, fvec, fjac, ldfjac, d->skip);
     return 0;
 }
@@ -252,11 +256,13 @@ int orc_solve(orc_problem *p, mmb_result *res, double *x_out, double *attr_out,
     const int mode = p->opt.auto_param_scale == 1 ? 1 : 2;
     const double factor = p->opt.tau * 100.0;
     int nfev = 0, njev = 0;
-    CbData cb{p, structural_skip != 0};
+    // solverType 1 = cminpack_lmdif (adjust_cminpack_lmdif.cpp:60-198: epsfcn = |delta|)
+    const bool dif = p->opt.solver_type == 1;
+    CbData cb{p, structural_skip != 0, dif};
     int info = lmder(lm_callback, &cb, m, n, x.data(), errors.data(), fjac.data(), ldfjac,
                      p->opt.eps1, p->opt.eps2, p->opt.eps3, p->opt.iter_max, diag.data(), mode,
                      factor, &nfev, &njev, ipvt.data(), qtf.data(), wa1.data(), wa2.data(),
-                     wa3.data(), wa4.data());
+                     wa3.data(), wa4.data(), nullptr, dif, std::fabs(p->opt.delta));
     res->error_final = enorm(m, errors.data());
     res->success = p->iterNum > 0;
     res->reason_num = info;
@@ -376,6 +382,17 @@ int orc_lmder(lmder_fcn fcn, void *ud, int m, int n, double *x, double *fvec, do
     std::vector<int> ipvt(n);
     return lmder(fcn, ud, m, n, x, fvec, fjac.data(), ld, ftol, xtol, gtol, maxfev, diag.data(), mode,
                  factor, nfev, njev, ipvt.data(), qtf.data(), wa1.data(), wa2.data(), wa3.data(), wa4.data());
+}
+
+// lmdif through the same entry (scipy cross-check): fcn fills fvec for iflag 1 and 2.
+int orc_lmdif(lmder_fcn fcn, void *ud, int m, int n, double *x, double *fvec, double ftol,
+              double xtol, double gtol, int maxfev, double epsfcn, int mode, double factor, int *nfev, int *njev) {
+    const int ld = std::max(m, n);
+    std::vector<double> fjac((size_t)n * ld), qtf(n), wa1(n), wa2(n), wa3(n), wa4(m), diag(n, 1.0);
+    std::vector<int> ipvt(n);
+    return lmder(fcn, ud, m, n, x, fvec, fjac.data(), ld, ftol, xtol, gtol, maxfev, diag.data(), mode,
+                 factor, nfev, njev, ipvt.data(), qtf.data(), wa1.data(), wa2.data(), wa3.data(), wa4.data(),
+                 nullptr, true, epsfcn);
 }
 
 }  // extern "C"

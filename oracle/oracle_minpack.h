@@ -219,7 +219,12 @@ inline int lmder(lmder_fcn fcn, void *ud, int m, int n, double *x, double *fvec,
                  double *fjac, int ldfjac, double ftol, double xtol, double gtol,
                  int maxfev, double *diag, int mode, double factor, int *nfev,
                  int *njev, int *ipvt, double *qtf, double *wa1, double *wa2,
-                 double *wa3, double *wa4, LmderTrace *trace = nullptr) {
+                 double *wa3, double *wa4, LmderTrace *trace = nullptr, bool dif = false,
+                 double epsfcn = 0.0) {
+    // dif = true is MINPACK lmdif (adjust_cminpack_lmdif.cpp:114-184): the same control law,
+    // the Jacobian by fdjac2 -- n calls of fcn with iflag = 2 that only fill fvec, forward
+    // differences with the relative step h = sqrt(max(epsfcn, epsmch)) * |x_j| (h = that
+    // factor when x_j = 0) -- and nfev += n per Jacobian.
     const double epsmch = DBL_EPSILON;
     const double p1 = 0.1, p5 = 0.5, p25 = 0.25, p75 = 0.75, p0001 = 1e-4;
     int info = 0, iflag = 0;
@@ -237,7 +242,22 @@ inline int lmder(lmder_fcn fcn, void *ud, int m, int n, double *x, double *fvec,
     par = 0.0;
     int iter = 1;
     for (;;) {
-        iflag = fcn(ud, m, n, x, fvec, fjac, ldfjac, 2);
+        if (!dif) {
+            iflag = fcn(ud, m, n, x, fvec, fjac, ldfjac, 2);
+        } else {
+            const double eps = std::sqrt(std::max(epsfcn, epsmch));
+            for (int j = 0; j < n; ++j) {
+                const double temp = x[j];
+                double h = eps * std::fabs(temp);
+                if (h == 0.0) h = eps;
+                x[j] = temp + h;
+                iflag = fcn(ud, m, n, x, wa4, nullptr, ldfjac, 2);
+                x[j] = temp;
+                if (iflag < 0) break;
+                for (int i = 0; i < m; ++i) fjac[i + (size_t)j * ldfjac] = (wa4[i] - fvec[i]) / h;
+            }
+            *nfev += n;
+        }
         ++(*njev);
         if (iflag < 0) return iflag;
         qrfac(m, n, fjac, ldfjac, true, ipvt, wa1, wa2, wa3);

@@ -193,6 +193,43 @@ def test_oracle_lmder_matches_scipy_minpack():
         assert np.allclose(x, xs, rtol=1e-10, atol=1e-12)
 
 
+def test_oracle_lmdif_matches_scipy_minpack():
+    """lmdif (fdjac2 forward differences, nfev += n per Jacobian) against MINPACK's own lmdif:
+    scipy.optimize.leastsq without Dfun."""
+    from scipy.optimize import leastsq
+    lib = oracle()
+    rng = np.random.default_rng(1)
+    m, n = 40, 6
+    A = rng.normal(size=(m, n))
+    t = rng.normal(size=m)
+
+    def f(x):
+        return np.tanh(A @ x) - t
+
+    FCN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                      C.POINTER(C.c_double), C.c_int, C.c_int)
+
+    def cb(ud, m_, n_, xp, fp, jp, ld, iflag):
+        np.ctypeslib.as_array(fp, (m_,))[:] = f(np.ctypeslib.as_array(xp, (n_,)).copy())
+        return 0
+    lib.orc_lmdif.argtypes = [FCN, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                              C.c_double, C.c_double, C.c_double, C.c_int, C.c_double, C.c_int, C.c_double,
+                              C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    x0 = rng.normal(size=n) * 0.1
+    x0[2] = 0.0   # h = eps when x_j == 0
+    for tol, maxfev, epsfcn in ((1e-6, 400, 1e-5), (1e-12, 400, 1e-5), (1e-6, 20, 1e-5), (1e-8, 400, 0.0)):
+        x = x0.copy()
+        fvec = np.zeros(m)
+        nfev, njev = C.c_int(), C.c_int()
+        info = lib.orc_lmdif(FCN(cb), None, m, n, _p(x), _p(fvec), tol, tol, tol, maxfev, epsfcn, 1, 100.0,
+                             C.byref(nfev), C.byref(njev))
+        xs, cov, infodict, mesg, ier = leastsq(f, x0, full_output=1, ftol=tol, xtol=tol, gtol=tol, maxfev=maxfev,
+                                               epsfcn=epsfcn if epsfcn else None, factor=100.0)
+        assert info == ier, (info, ier, mesg)
+        assert nfev.value == infodict["nfev"]
+        assert np.allclose(x, xs, rtol=1e-9, atol=1e-11)
+
+
 def test_index_maps_reference_order():
     """adjust_relationships.cpp: errors marker-major/frame-minor over enabled & weight>0 pairs;
     parameters attr-major, animated attrs expand per frame; weights normalised per frame."""

@@ -32,13 +32,20 @@ def oracle_per_frame(sb, **opts):
     return agg, per, np.stack(attrs, 1)  # attrs[a, f]
 
 
-@pytest.mark.parametrize("case", ["camera6_24x20", "camera6_weights_drop", "camera_focal_central"])
+@pytest.mark.parametrize("case", ["camera6_24x20", "camera6_weights_drop", "camera_focal_central", "camera6_lmdif",
+                                  "camera6_lmdif_maxfev"])
 def test_per_frame_parity(case):
     opts = dict(OPTS)
     if case == "camera6_24x20":
         sb, _ = make_scene(24, 20, 5, solve_bundles=False, period=24.0)
     elif case == "camera6_weights_drop":
         sb, _ = make_scene(16, 30, 6, solve_bundles=False, weights=True, drop_fraction=0.2, period=16.0)
+    elif case.startswith("camera6_lmdif"):
+        # solverType 1 = cminpack_lmdif: relative forward steps, 6 function calls per Jacobian
+        # count towards `iterations` (maxfev); the second case stops on it (reason 5)
+        sb, _ = make_scene(10, 20, 8, solve_bundles=False, period=10.0)
+        opts["solver_type"] = 1
+        opts["iter_max"] = 400 if case == "camera6_lmdif" else 20
     else:
         sb, _ = make_scene(8, 24, 7, solve_bundles=False, period=8.0)
         opts["auto_diff_type"] = 1
@@ -51,6 +58,8 @@ def test_per_frame_parity(case):
     for f in range(sb.F):
         assert frames[f].reason_num == per[f].reason_num, (f, frames[f], per[f])
         assert frames[f].iteration_num == per[f].iteration_num, (f, frames[f], per[f])
+        assert frames[f].iteration_function_num == per[f].iteration_function_num
+        assert frames[f].iteration_jacobian_num == per[f].iteration_jacobian_num
         np.testing.assert_allclose(frames[f].error_final, per[f].error_final, rtol=1e-6)
         np.testing.assert_allclose(frames[f].error_avg, per[f].error_avg, rtol=1e-6)
     np.testing.assert_allclose(got, attrs, rtol=1e-6, atol=1e-8)

@@ -63,6 +63,28 @@ def test_solve_matches_oracle(name):
     assert abs(r.error_avg - ro.error_avg) <= px_tol and abs(r.error_max - ro.error_max) <= px_tol
 
 
+@pytest.mark.parametrize("iter_max", [100000, 300])
+def test_lmdif_solve_matches_oracle(iter_max):
+    """solverType 1 (cminpack_lmdif, adjust_cminpack_lmdif.cpp): fdjac2's relative forward step
+    h = sqrt(|delta|) * |x_j| and n function calls per Jacobian counted in nfev / maxfev."""
+    sb, _ = synth.make_scene(**CASES["camera_bundles_12x16"])
+    o = OracleProblem(sb, solver_type=1, iter_max=iter_max)
+    ro = o.solve()
+    with Problem(sb, solver_type=1, iter_max=iter_max) as p:
+        r = p.solve()
+    print("oracle", ro, "gpu", r)
+    assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (ro.reason_num, ro.iteration_num, ro.iteration_attempt_num)
+    assert (r.iteration_function_num, r.iteration_jacobian_num) == (ro.iteration_function_num, ro.iteration_jacobian_num)
+    assert r.iteration_num == r.iteration_function_num + r.iteration_attempt_num * p.n
+    if iter_max == 300:
+        assert r.reason_num == 5   # maxfev reached by the Jacobians' own function calls
+    scale = np.maximum(np.abs(ro.attr_values), 1.0)
+    # sqrt(delta) = 1e-2 relative steps: the FD noise amplification is 100x smaller than lmder's
+    assert np.max(np.abs(r.attr_values - ro.attr_values) / scale) <= 1e-6
+    assert np.max(np.abs(r.error_dist - ro.error_dist)) <= 1e-6
+    assert abs(r.error_final - ro.error_final) <= 1e-6 * max(1.0, ro.error_final)
+
+
 def test_gauge_free_reaches_same_error():
     sb, _ = synth.make_scene(F=8, B=12, seed=3)
     ro = OracleProblem(sb).solve()
