@@ -149,7 +149,7 @@ typedef struct mmb_options {
     int32_t robust_loss_type;  /* accepted, unused (adjust_defines.h:134) */
     double robust_loss_scale;
     int32_t scene_graph_mode;  /* 2 = mmscenegraph (only mode implemented) */
-    int32_t solver_type;       /* 2 = cminpack_lmder (default) */
+    int32_t solver_type;       /* 2 = cminpack_lmder (default), 1 = cminpack_lmdif */
     int32_t time_eval_mode;    /* accepted, unused without Maya */
     int32_t accept_only_better;/* default 1 */
     double image_width;        /* default 2048.0 */
