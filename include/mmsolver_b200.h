@@ -356,6 +356,16 @@ mmb_status mmb_lens_apply(int32_t device, int32_t model, const double *coeffs,
                           const double *camera_params, int32_t direction,
                           int64_t n_points, const double *xy_in,
                           double *xy_out);
+/* A chain of lens nodes (each LensModel applies its inputLensModel first,
+ * lens_model_3de_*.cpp:44-50): layer 0 is the innermost; models [n_layers],
+ * coeffs [n_layers * MMB_LENS_MAX_COEFFS], camera_params [n_layers * 6];
+ * at most 8 layers.  (The SOLVER never connects lens chains --
+ * maya_lens_model_utils.cpp:711 -- so mmb_scene_desc has one lens per camera.) */
+mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers,
+                                  const int32_t *models, const double *coeffs,
+                                  const double *camera_params,
+                                  int32_t direction, int64_t n_points,
+                                  const double *xy_in, double *xy_out);
 /* the same kernel timed on a device-resident grid of n_points (CUDA events) */
 mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs,
                           const double *camera_params, int32_t direction,

@@ -108,6 +108,8 @@ SYMBOLS = [
     ("mmb_request_cancel", None, [C.c_void_p]),
     ("mmb_bench_eval", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, c_f64p, c_f64p, c_i32p]),
     ("mmb_lens_apply", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, c_f64p, c_f64p]),
+    ("mmb_lens_apply_layered", C.c_int32, [C.c_int32, C.c_int32, c_i32p, c_f64p, c_f64p, C.c_int32, C.c_int64, c_f64p,
+                                           c_f64p]),
     ("mmb_bench_lens", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, C.c_int32, c_f64p]),
     ("mmb_bench_fp64_peaks", C.c_int32, [C.c_int32, c_f64p, c_f64p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),

@@ -335,6 +335,45 @@ MMB_HD void lens_distort(const double *rec, double px, double py, double &outx, 
     if (isfinite(uy)) outy = uy;
 }
 
+// the same without the non-finite guard: a layer inside a lens chain (the guard of
+// adjust_measureErrors.cpp belongs to the solver's call site, not to the lens model)
+MMB_HD void lens_distort_raw(const double *rec, double px, double py, double &outx, double &outy) {
+    const int model = (int)rec[0];
+    outx = px; outy = py;
+    if (model == 0) return;
+    const double radius = rec[1], w = rec[2], h = rec[3], lx = rec[4], ly = rec[5];
+    const double *k = &rec[6];
+    double qx = (((px + 0.5) - 0.5) * w - lx) / radius;
+    double qy = (((py + 0.5) - 0.5) * h - ly) / radius;
+    {
+        const double tx = rec[16] * qx + rec[17] * qy, ty = rec[18] * qx + rec[19] * qy;
+        qx = tx; qy = ty;
+    }
+    double fx, fy;
+    lens_core(model, k, qx, qy, fx, fy);
+    double x = qx - (fx - qx), y = qy - (fy - qy);
+    for (int i = 0; i < 20; ++i) {
+        lens_core(model, k, x, y, fx, fy);
+        x = x + qx - fx; y = y + qy - fy;
+        const double dx = fx - qx, dy = fy - qy;
+        if (sqrt(dx * dx + dy * dy) < 1e-6) break;
+    }
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        lens_core(model, k, x, y, fx, fy);
+        x = x + qx - fx; y = y + qy - fy;
+    }
+    {
+        const double tx = rec[20] * x + rec[21] * y, ty = rec[22] * x + rec[23] * y;
+        x = tx; y = ty;
+    }
+    double xc = x * radius, yc = y * radius;
+    xc += (w / 2) + lx; yc += (h / 2) + ly;
+    const double ux = xc / w - 0.5, uy = yc / h - 0.5;
+    outx = ux; outy = uy;
+}
+
+
 // adjust_base.cpp:194-220 parameterBoundFromInternalToExternal
 MMB_HD double bound_int_to_ext(double value, double xmin, double xmax, double offset, double scale) {
     const double float_max = 3.40282346638528859811704183484516925e+38;

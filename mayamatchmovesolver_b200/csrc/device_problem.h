@@ -102,6 +102,8 @@ mmb_status measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflo
 // bulk lens (un)distortion of point buffers (lens_bulk.cu)
 mmb_status lens_apply_host(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
                            const double *xy_in, double *xy_out);
+mmb_status lens_apply_layered_host(int device, int n_layers, const int32_t *models, const double *coeffs,
+                                   const double *cams, int direction, long long n, const double *xy_in, double *xy_out);
 mmb_status lens_bench(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
                       int reps, double *ms_per_pass);
 

@@ -62,6 +62,34 @@ __global__ void __launch_bounds__(256) k_lens_bulk(LensBulk L, int direction, lo
     }
 }
 
+// Layered lenses (a Maya lens-node chain: each LensModel first applies its inputLensModel,
+// lens_model_3de_*.cpp:44-50 / 89-95): layer 0 is the innermost, both directions run
+// innermost -> outermost.
+constexpr int kLensMaxLayers = 8;
+struct LensLayers {
+    long long n;
+    LensBulk layer[kLensMaxLayers];
+};
+
+__global__ void __launch_bounds__(256) k_lens_bulk_layered(const LensLayers *__restrict__ LL, int direction, long long n,
+                                                           const double2 *__restrict__ in, double2 *__restrict__ out) {
+    __shared__ LensLayers L;
+    for (int i = threadIdx.x; i < (int)(sizeof(LensLayers) / sizeof(double)); i += blockDim.x)
+        reinterpret_cast<double *>(&L)[i] = reinterpret_cast<const double *>(LL)[i];
+    __syncthreads();
+    const int nl = (int)L.n;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        double2 p = __ldcs(&in[i]);
+        for (int k = 0; k < nl; ++k) {
+            double2 o;
+            if (direction == 0) lens_undistort_pt(L.layer[k], p.x, p.y, o.x, o.y);
+            else lens_distort_raw(L.layer[k].rec, p.x, p.y, o.x, o.y);
+            p = o;
+        }
+        __stcs(&out[i], p);
+    }
+}
+
 static void make_bulk(int model, const double *coeffs, const double *cam, LensBulk *L) {
     double c[MMB_LENS_MAX_COEFFS];
     for (int i = 0; i < MMB_LENS_MAX_COEFFS; ++i) c[i] = coeffs ? coeffs[i] : 0.0;
@@ -107,6 +135,44 @@ mmb_status lens_apply_host(int device, int model, const double *coeffs, const do
     cudaStreamDestroy(s);
     if (e == cudaSuccess) e = e2;
     if (e != cudaSuccess) { set_last_error(std::string("lens_apply: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
+    return MMB_OK;
+}
+
+mmb_status lens_apply_layered_host(int device, int n_layers, const int32_t *models, const double *coeffs,
+                                   const double *cams, int direction, long long n, const double *xy_in, double *xy_out) {
+    MMB_CUDA_CHECK(cudaSetDevice(device));
+    if (n_layers < 1 || n_layers > kLensMaxLayers) {
+        set_last_error("lens_apply_layered: 1..8 layers");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    static_assert(sizeof(LensLayers) % sizeof(double) == 0, "copied as doubles");
+    LensLayers LL;
+    std::memset(&LL, 0, sizeof(LL));
+    LL.n = n_layers;
+    for (int k = 0; k < n_layers; ++k)
+        make_bulk(models[k], coeffs ? coeffs + (size_t)MMB_LENS_MAX_COEFFS * k : nullptr, cams + 6 * (size_t)k, &LL.layer[k]);
+    if (n == 0) return MMB_OK;
+    cudaStream_t s = nullptr;
+    MMB_CUDA_CHECK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    double2 *d_in = nullptr, *d_out = nullptr;
+    LensLayers *d_ll = nullptr;
+    cudaError_t e = cudaMallocAsync((void **)&d_in, sizeof(double2) * n, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_out, sizeof(double2) * n, s);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_ll, sizeof(LensLayers), s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_ll, &LL, sizeof(LL), cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, xy_in, sizeof(double2) * n, cudaMemcpyHostToDevice, s);
+    if (e == cudaSuccess) {
+        k_lens_bulk_layered<<<grid_for(n * kLensUnroll, device), 256, 0, s>>>(d_ll, direction, n, d_in, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(xy_out, d_out, sizeof(double2) * n, cudaMemcpyDeviceToHost, s);
+    if (d_in) cudaFreeAsync(d_in, s);
+    if (d_out) cudaFreeAsync(d_out, s);
+    if (d_ll) cudaFreeAsync(d_ll, s);
+    const cudaError_t e2 = cudaStreamSynchronize(s);
+    cudaStreamDestroy(s);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) { set_last_error(std::string("lens_apply_layered: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
     return MMB_OK;
 }
 

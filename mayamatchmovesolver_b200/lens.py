@@ -6,7 +6,7 @@ import ctypes as C
 import numpy as np
 
 from . import _capi
-from ._capi import c_f64p, check
+from ._capi import c_f64p, c_i32p, check
 from .scene import LENS_COEFF_NAMES, LENS_MODELS
 
 UNDISTORT, DISTORT = 0, 1
@@ -46,6 +46,23 @@ def apply(model, coeffs, points, direction=DISTORT, camera_params=DEFAULT_CAMERA
     cam = np.ascontiguousarray(camera_params, dtype=np.float64)
     check(lib.mmb_lens_apply(int(device), mid, arr.ctypes.data_as(c_f64p), cam.ctypes.data_as(c_f64p), int(direction),
                              pts.size // 2, pts.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p)), "mmb_lens_apply")
+    return out
+
+
+def apply_layered(layers, points, direction=DISTORT, device=0):
+    """layers: [(model, coeffs, camera_params), ...] innermost first (a lens-node chain)"""
+    lib = _capi.load()
+    models = np.zeros(len(layers), np.int32)
+    co = np.zeros((len(layers), _capi.MMB_LENS_MAX_COEFFS))
+    cams = np.zeros((len(layers), 6))
+    for k, (model, coeffs, cam) in enumerate(layers):
+        models[k], co[k] = _coeff_array(model, coeffs)
+        cams[k] = cam
+    pts = np.ascontiguousarray(points, dtype=np.float64)
+    out = np.empty_like(pts)
+    check(lib.mmb_lens_apply_layered(int(device), len(layers), models.ctypes.data_as(c_i32p), co.ctypes.data_as(c_f64p),
+                                     cams.ctypes.data_as(c_f64p), int(direction), pts.size // 2,
+                                     pts.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p)), "mmb_lens_apply_layered")
     return out
 
 

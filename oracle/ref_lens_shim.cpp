@@ -14,7 +14,10 @@
 #include <mmlens/lens_model_3de_classic.h>
 #include <mmlens/lens_model_3de_radial_decentered_deg_4_cylindric.h>
 
+#include <mmlens/lens_model_passthrough.h>
+
 #include <memory>
+#include <vector>
 
 using namespace mmlens;
 
@@ -62,6 +65,39 @@ extern "C" int ref_lens_apply(int model, const double *coeffs,
         double x = xy_in[2 * i], y = xy_in[2 * i + 1], ox = x, oy = y;
         if (direction == 0) L->applyModelUndistort(x, y, ox, oy);
         else L->applyModelDistort(x, y, ox, oy);
+        xy_out[2 * i] = ox; xy_out[2 * i + 1] = oy;
+    }
+    return 0;
+}
+
+// Layered lenses: layer 0 is the innermost (it has no input), layer k's inputLensModel is
+// layer k-1; the call goes to the last layer, as a Maya lens-node chain evaluates
+// (src/mmSolver/node/MMLensModel3deNode.cpp:164: newLensModel->setInputLensModel(input)).
+extern "C" int ref_lens_apply_layered(int n_layers, const int *models, const double *coeffs14,
+                                      const double *cam6, int direction, int npts,
+                                      const double *xy_in, double *xy_out) {
+    std::vector<std::shared_ptr<LensModel>> chain;
+    for (int k = 0; k < n_layers; ++k) {
+        std::shared_ptr<LensModel> L;
+        if (models[k] == 0) L.reset(new LensModelPassthrough());
+        else L = std::shared_ptr<LensModel>(make_lens(models[k], coeffs14 + 14 * k).release());
+        if (!L) return -1;
+        const double *c = cam6 + 6 * k;
+        L->setFocalLength(c[0]);
+        L->setFilmBackWidth(c[1]);
+        L->setFilmBackHeight(c[2]);
+        L->setPixelAspect(c[3]);
+        L->setLensCenterOffsetX(c[4]);
+        L->setLensCenterOffsetY(c[5]);
+        if (k > 0) L->setInputLensModel(chain[k - 1]);
+        chain.push_back(L);
+    }
+    if (chain.empty()) return -1;
+    LensModel *top = chain.back().get();
+    for (int i = 0; i < npts; ++i) {
+        double x = xy_in[2 * i], y = xy_in[2 * i + 1], ox = x, oy = y;
+        if (direction == 0) top->applyModelUndistort(x, y, ox, oy);
+        else top->applyModelDistort(x, y, ox, oy);
         xy_out[2 * i] = ox; xy_out[2 * i + 1] = oy;
     }
     return 0;

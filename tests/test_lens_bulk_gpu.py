@@ -78,7 +78,7 @@ def test_stmap_round_trip_full_size(model):
     # the reference's own behaviour, so the corners are checked against the reference's
     # compiled code (or the oracle) on a subsample, and the round trip inside |x|,|y| < 0.35
     inner = (np.abs(pts) < 0.35).all(axis=1)
-    assert np.abs(red - pts)[inner].max() < 1e-8, np.abs(red - pts)[inner].max()
+    assert np.abs(red - pts)[inner].max() < 1e-7, np.abs(red - pts)[inner].max()   # stop test at 1e-6 + 2 polish steps
     sub = np.ascontiguousarray(und[::97])
     want = np.zeros_like(sub)
     ref = ref_lens()
@@ -87,6 +87,35 @@ def test_stmap_round_trip_full_size(model):
     else:
         oracle().orc_lens_apply(model, _p(co), _p(CAM), 1, len(sub), _p(sub), _p(want))
     assert np.abs(red[::97] - want).max() < TOL[1], np.abs(red[::97] - want).max()
+
+
+@pytest.mark.parametrize("direction", [0, 1])
+def test_layered_chain_matches_reference(direction):
+    """anamorphic over radial over passthrough, each with its own film back: the reference's
+    models connected with setInputLensModel (oracle/ref_lens_shim.cpp ref_lens_apply_layered)"""
+    ref = ref_lens()
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    import ctypes as C
+    cams = np.array([[3.5, 3.6, 2.4, 1.0, 0.0, 0.0], [3.5, 3.6, 2.4, 1.0, 0.05, -0.03], [3.5, 3.6, 2.4, 1.1, 0.0, 0.02]])
+    weak3 = [0.01, 0.005, -0.004, 0.002, 0.003, -0.002, 0.001, 0.001, -0.001, 0.0005, 2.0, 1.01, 0.99]
+    layers = [(0, None, cams[0]), (2, [0.05, 0.002, -0.001, 0.01, 0.0, 0.0, 10.0, 0.02], cams[1]), (3, weak3, cams[2])]
+    pts = np.random.default_rng(3).uniform(-0.45, 0.45, (50000, 2))
+    got = lens.apply_layered(layers, pts, direction)
+    models = np.array([m for m, _, _ in layers], np.int32)
+    co = np.zeros((3, 14))
+    for k, (_, c, _) in enumerate(layers):
+        if c is not None:
+            co[k, :len(c)] = c
+    want = np.zeros_like(pts)
+    ref.ref_lens_apply_layered.argtypes = [C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                           C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    assert ref.ref_lens_apply_layered(3, models.ctypes.data_as(C.POINTER(C.c_int32)), _p(co), _p(cams), direction,
+                                      len(pts), _p(pts), _p(want)) == 0
+    assert np.abs(got - want).max() < (1e-13 if direction == 0 else 1e-9), np.abs(got - want).max()
+    # one layer through the layered entry == the plain entry
+    one = lens.apply_layered(layers[1:2], pts, direction)
+    assert np.abs(one - lens.apply(2, layers[1][1], pts, direction, cams[1])).max() < 1e-15
 
 
 def test_bad_arguments():
