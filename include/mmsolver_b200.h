@@ -370,6 +370,10 @@ mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers,
 mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs,
                           const double *camera_params, int32_t direction,
                           int64_t n_points, int32_t reps, double *ms_per_pass);
+/* debug: %globaltimer timeline (ns) of the critical path of the last reduced-
+ * system Cholesky: [block column][0 diagonal tile, 1 tile below it][6 marks]
+ * (csrc/lm_kernels.cuh g_chol_trace); count <= 768 */
+mmb_status mmb_debug_chol_trace(uint64_t *out, int32_t count);
 /* measured FP64 ceilings of the device in TFLOP/s (dependent-free DFMA chains; DMMA
  * m8n8k4): the roofline denominators of the compute-bound kernels (lens distortion in
  * the loop, the reduced-system SYRK / Cholesky updates) */

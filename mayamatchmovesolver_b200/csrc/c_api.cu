@@ -499,6 +499,11 @@ mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs, c
     return lens_bench(device, model, coeffs, camera_params, direction, n_points, reps, ms_per_pass);
 }
 
+mmb_status mmb_debug_chol_trace(uint64_t *out, int32_t count) {
+    if (!out || count <= 0) return MMB_ERR_INVALID_ARGUMENT;
+    return lm_chol_trace(reinterpret_cast<unsigned long long *>(out), count);
+}
+
 mmb_status mmb_release_cached_memory(int32_t device) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;

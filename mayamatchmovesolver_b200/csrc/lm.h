@@ -9,4 +9,6 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
 void lm_workspace_destroy(LmWorkspace *w);
 // sets the flag the device-resident loop polls (pinned, mapped) and the host loop's flag
 void lm_request_cancel(DeviceProblem *p);
+// debug: critical-path timeline of the last k_chol_tiles launch (lm_kernels.cuh g_chol_trace)
+mmb_status lm_chol_trace(unsigned long long *out, int count);
 }  // namespace mmb

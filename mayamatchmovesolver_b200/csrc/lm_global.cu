@@ -481,6 +481,13 @@ __global__ void k_cond(LmState *st, const int *cancel, int where, cudaGraphCondi
     }
 }
 
+// debug: the Cholesky critical-path timeline of the last factorisation (see g_chol_trace)
+mmb_status lm_chol_trace(unsigned long long *out, int count) {
+    MMB_CUDA_CHECK(cudaDeviceSynchronize());
+    MMB_CUDA_CHECK(cudaMemcpyFromSymbol(out, g_chol_trace, sizeof(unsigned long long) * std::min(count, 64 * 2 * 6)));
+    return MMB_OK;
+}
+
 // ---- workspace ------------------------------------------------------------------------------
 static mmb_status lm_workspace_create(DeviceProblem *p) {
     if (p->lm) return MMB_OK;

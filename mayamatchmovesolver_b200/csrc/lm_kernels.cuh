@@ -378,8 +378,19 @@ __device__ __forceinline__ void sqrt_rsqrt(double x, double &s, double &inv) {
     s = fma(0.5 * y, fma(-s, s, x), s);
 }
 
+// 1/x from the hardware seed and ONE cubically convergent step (e = 1 - x r; r += r e (1 + e)):
+// three dependent operations after the seed instead of the four of two Newton steps.
+__device__ __forceinline__ double rcp_fast(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    const double e = fma(-x, r, 1.0);
+    return fma(r * e, 1.0 + e, r);
+}
+
 // Cholesky of an 8x8 block held in registers (lower part of a[i][j]); g0 = global index of
 // its first row.  The augmented row (global index ns) gets no pivot.
+// (An LDL^T-style chain -- next pivot from 1/d_j only, square roots off the chain -- was
+// measured slower here: 0.82 vs 0.72 us per block; in-order issue does not overlap the two.)
 __device__ __forceinline__ void chol8_regs(double (&a)[8][8], double (&dinv)[8], int g0, int ns, int &fail) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -575,8 +586,19 @@ __global__ void __launch_bounds__(128) k_chol_trailing(LmDims d, int kb, double 
 // for tiles of LOWER blockIdx: under in-order block dispatch no cooperative launch is
 // needed and the kernel can sit in a CUDA-graph body.  Tiles published by other CTAs are
 // read with ld.global.cg (L2): an SM's L1 may still hold the pre-factorisation lines.
+constexpr int kPS = 12;   // staged 8-column panel stride: (12 g + q) mod 16 distinct -> conflict-free fragments
 constexpr int kOS = 68;   // operand tile stride: (stride mod 16) == 4 -> conflict-free DMMA fragment loads
 constexpr size_t kCholTilesSmem = sizeof(double) * (2 * 64 * kOS + 64) + 16;
+
+// timeline of the critical path (diagonal and first sub-diagonal tile of every block column),
+// %globaltimer ns: [col][diag?0:1][0 last operand flag seen, 1 operands in smem, 2 update done,
+// 3 factor/solve done, 4 (sub-diagonal) diagonal flag seen, 5 published]; mmb_debug_chol_trace
+__device__ unsigned long long g_chol_trace[64 * 2 * 6];
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 
 __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
                                                     const int *epoch_ctr) {
@@ -594,20 +616,28 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
     const bool diag = i == j;
     const size_t ld = (size_t)d.NSP;
     int *flags = tile_flags;
+    const bool traced = tid == 0 && i <= j + 1 && j < 64;
+    unsigned long long *tr = &g_chol_trace[(j * 2 + (diag ? 0 : 1)) * 6];
     // ---- A: left-looking update on the tensor cores ----
     const int wr = warp >> 1, wc = warp & 1;   // warp tile: rows wr*16.., cols wc*32..
     const int g = lane >> 2, q = lane & 3;
     double acc[2][4][2];
+    double2 sij[2][4];   // this tile of S, fetched before the waits: off the critical path
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b][0] = acc[a][b][1] = 0.0;
+        for (int b = 0; b < 4; ++b) {
+            acc[a][b][0] = acc[a][b][1] = 0.0;
+            const int r = wr * 16 + a * 8 + g, c = wc * 32 + b * 8 + q * 2;
+            sij[a][b] = __ldcg(reinterpret_cast<const double2 *>(&S[(size_t)(i * 64 + r) * ld + j * 64 + c]));
+        }
     for (int k = 0; k < j; ++k) {
         if (tid == 0) {
             int v;
             const int *f1 = &flags[k * nb + i], *f2 = &flags[k * nb + j];
             do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f1) : "memory"); } while (v != epoch);
             if (!diag) do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f2) : "memory"); } while (v != epoch);
+            if (traced && k == j - 1) tr[0] = gtimer();
         }
         __syncthreads();  // also: everyone is done with the previous k's operands
         // 64 x 64 doubles per operand = 2048 double2; 8 per thread
@@ -623,6 +653,7 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
             }
         }
         __syncthreads();
+        if (traced && k == j - 1) tr[1] = gtimer();
         const double *pB = diag ? sA : sB;
 #pragma unroll 4
         for (int k0 = 0; k0 < 64; k0 += 4) {
@@ -646,11 +677,12 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
 #pragma unroll
         for (int tj = 0; tj < 4; ++tj) {
             const int r = wr * 16 + ti * 8 + g, c = wc * 32 + tj * 8 + q * 2;
-            const double2 v = *reinterpret_cast<const double2 *>(&S[(size_t)(i * 64 + r) * ld + j * 64 + c]);
+            const double2 v = sij[ti][tj];
             dst[r * kCS + c] = v.x - acc[ti][tj][0];
             dst[r * kCS + c + 1] = v.y - acc[ti][tj][1];
         }
     __syncthreads();
+    if (traced) tr[2] = gtimer();
     const int base = j * 64;
     if (diag) {
         // ---- C: factor the diagonal tile (as k_chol_panel) ----
@@ -658,12 +690,16 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
 #pragma unroll
         for (int sblk = 0; sblk < 8; ++sblk) {
             const int k0 = sblk * 8, nrest = 56 - k0;
+            // the pivot block is factored in registers by the threads that use the result (the
+            // panel rows and the write-back: tid < 64); the other six warps stay off the FP64 pipe
             double a[8][8], dinv[8];
+            if (tid < 64) {
 #pragma unroll
-            for (int ii = 0; ii < 8; ++ii)
+                for (int ii = 0; ii < 8; ++ii)
 #pragma unroll
-                for (int jj = 0; jj <= ii; ++jj) a[ii][jj] = T[(k0 + ii) * kCS + k0 + jj];
-            chol8_regs(a, dinv, base + k0, d.ns, fail);
+                    for (int jj = 0; jj <= ii; ++jj) a[ii][jj] = T[(k0 + ii) * kCS + k0 + jj];
+                chol8_regs(a, dinv, base + k0, d.ns, fail);
+            }
             __syncthreads();
             if (tid < nrest) {
                 const int r = k0 + 8 + tid;
@@ -678,6 +714,11 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
                 }
 #pragma unroll
                 for (int k = 0; k < 8; ++k) T[r * kCS + k0 + k] = x[k];
+                // second copy for the tensor-core update below: stride 12 makes the m8n8k4
+                // operand fragments bank-conflict free (stride 65 is 4-way conflicted there);
+                // the X region is free in the diagonal CTA
+#pragma unroll
+                for (int k = 0; k < 8; ++k) X[tid * kPS + k] = x[k];
             } else if (tid < nrest + 8) {
                 const int ii0 = tid - nrest;
 #pragma unroll
@@ -690,25 +731,46 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
             }
             __syncthreads();
             if (nrest > 0) {
-                // rank-8 update of the lower triangle below the pivot block: thread = (row, column
-                // phase); the row's 8 panel entries stay in registers
-                const int rr = tid >> 2;
-                if (rr < nrest) {
-                    double pr[8];
+                // rank-8 update of the lower triangle below the pivot block on the tensor cores:
+                // 8x8 output tiles (rt >= ct) dealt to the warps (at most 4 each), operands of
+                // all of a warp's tiles fetched (from the staged panel) before the first m8n8k4.
+                // The scalar version was a chain of 8 dependent FMAs (~20 cycles each) per entry.
+                const int nt = nrest >> 3, ntile = nt * (nt + 1) / 2;
+                const double *P = X;   // staged panel, row stride kPS
+                double pa[4][2], pb[4][2], cacc[4][2];
+                int roff[4];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) pr[k] = T[(k0 + 8 + rr) * kCS + k0 + k];
-                    for (int cc = tid & 3; cc <= rr; cc += 4) {
-                        const double *pc = &T[(k0 + 8 + cc) * kCS + k0];
-                        double s2 = 0.0;
+                for (int u = 0; u < 4; ++u) {
+                    const int tI = warp + 8 * u;
+                    int rt = 0, ct = tI;
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) s2 = fma(pr[k], pc[k], s2);
-                        T[(k0 + 8 + rr) * kCS + k0 + 8 + cc] -= s2;
+                    for (int z = 0; z < 6; ++z)
+                        if (ct > rt) { ct -= rt + 1; ++rt; }
+                    roff[u] = (k0 + 8 + rt * 8 + g) * kCS + k0 + 8 + ct * 8 + 2 * q;
+                    if (tI < ntile) {
+#pragma unroll
+                        for (int kk = 0; kk < 2; ++kk) {
+                            pa[u][kk] = P[(rt * 8 + g) * kPS + kk * 4 + q];
+                            pb[u][kk] = P[(ct * 8 + g) * kPS + kk * 4 + q];
+                        }
+                        cacc[u][0] = T[roff[u]];
+                        cacc[u][1] = T[roff[u] + 1];
                     }
                 }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (warp + 8 * u < ntile) {
+                        double c0 = 0.0, c1 = 0.0;
+                        dmma884(c0, c1, pa[u][0], pb[u][0]);
+                        dmma884(c0, c1, pa[u][1], pb[u][1]);
+                        T[roff[u]] = cacc[u][0] - c0;
+                        T[roff[u] + 1] = cacc[u][1] - c1;
+                    }
                 __syncthreads();
             }
         }
         if (tid == 0 && fail) atomicExch(&st->chol_fail, 1);
+        if (traced) tr[3] = gtimer();
         for (int e = tid; e < 64 * 64; e += 256) {
             const int rr = e >> 6, c = e & 63;
             S[(size_t)(base + rr) * ld + base + c] = c <= rr ? T[rr * kCS + c] : 0.0;
@@ -719,16 +781,21 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
             int v;
             const int *f = &flags[j * nb + j];
             do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while (v != epoch);
+            if (traced) tr[4] = gtimer();
         }
         __syncthreads();
-        for (int e = tid; e < 64 * 64; e += 256) {
-            const int rr = e >> 6, c = e & 63;
-            T[rr * kCS + c] = __ldcg(&S[(size_t)(base + rr) * ld + base + c]);
+        // L(j,j) with the fragment-friendly row stride kOS (it is only read by broadcast and as
+        // m8n8k4 operands here); 16-byte loads; 1/diag by the thread that fetched the diagonal
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = tid + u * 256;
+            const int rr = idx >> 5, c2 = (idx & 31) * 2;
+            const double2 v = __ldcg(reinterpret_cast<const double2 *>(&S[(size_t)(base + rr) * ld + base + c2]));
+            *reinterpret_cast<double2 *>(&T[rr * kOS + c2]) = v;
+            if (c2 == (rr & ~1)) dinv_s[rr] = rcp_fast((rr & 1) ? v.y : v.x);
         }
         __syncthreads();
-        if (tid < 64) dinv_s[tid] = 1.0 / T[tid * kCS + tid];
-        __syncthreads();
-        const int r = tid & 63, qq = tid >> 6;
+        const int r = tid & 63;
 #pragma unroll
         for (int sblk = 0; sblk < 8; ++sblk) {
             const int k0 = sblk * 8;
@@ -740,27 +807,40 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
                 for (int k = 0; k < 8; ++k) {
                     x[k] *= dinv_s[k0 + k];
 #pragma unroll
-                    for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], T[(k0 + k2) * kCS + k0 + k], x[k2]);
+                    for (int k2 = k + 1; k2 < 8; ++k2) x[k2] = fma(-x[k], T[(k0 + k2) * kOS + k0 + k], x[k2]);
                 }
 #pragma unroll
                 for (int k = 0; k < 8; ++k) X[r * kCS + k0 + k] = x[k];
             }
             __syncthreads();
             if (sblk < 7) {
-                double xr[8];
+                // X[:, k0+8..] -= X[:, k0..k0+8) L(j,j)[k0+8.., k0..k0+8)^T on the tensor cores:
+                // warp w owns the 8 rows w*8.. (one A fragment) and walks the 7 - sblk column tiles
+                const int nct = 7 - sblk;
+                const double xa0 = X[(warp * 8 + g) * kCS + k0 + q], xa1 = X[(warp * 8 + g) * kCS + k0 + 4 + q];
+                double tb[7][2], xc[7][2];
 #pragma unroll
-                for (int k = 0; k < 8; ++k) xr[k] = X[r * kCS + k0 + k];
-                for (int c = k0 + 8 + qq; c < 64; c += 4) {
-                    const double *pc = &T[c * kCS + k0];
-                    double s2 = 0.0;
+                for (int ct = 0; ct < 7; ++ct)
+                    if (ct < nct) {
+                        tb[ct][0] = T[(k0 + 8 + ct * 8 + g) * kOS + k0 + q];
+                        tb[ct][1] = T[(k0 + 8 + ct * 8 + g) * kOS + k0 + 4 + q];
+                        xc[ct][0] = X[(warp * 8 + g) * kCS + k0 + 8 + ct * 8 + 2 * q];
+                        xc[ct][1] = X[(warp * 8 + g) * kCS + k0 + 8 + ct * 8 + 2 * q + 1];
+                    }
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) s2 = fma(xr[k], pc[k], s2);
-                    X[r * kCS + c] -= s2;
-                }
+                for (int ct = 0; ct < 7; ++ct)
+                    if (ct < nct) {
+                        double c0 = 0.0, c1 = 0.0;
+                        dmma884(c0, c1, xa0, tb[ct][0]);
+                        dmma884(c0, c1, xa1, tb[ct][1]);
+                        X[(warp * 8 + g) * kCS + k0 + 8 + ct * 8 + 2 * q] = xc[ct][0] - c0;
+                        X[(warp * 8 + g) * kCS + k0 + 8 + ct * 8 + 2 * q + 1] = xc[ct][1] - c1;
+                    }
                 __syncthreads();
             }
         }
         const int rb = i * 64;
+        if (traced) tr[3] = gtimer();
         for (int e = tid; e < 64 * 64; e += 256) {
             const int rr = e >> 6, c = e & 63;
             S[(size_t)(rb + rr) * ld + base + c] = X[rr * kCS + c];
@@ -772,6 +852,7 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
     if (tid == 0) {
         int *f = &flags[j * nb + i];
         asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(f), "r"(epoch) : "memory");
+        if (traced) tr[5] = gtimer();
     }
 }
 
