@@ -330,7 +330,10 @@ __device__ __forceinline__ void eval_pair_fma(const double *cm, double b0, doubl
 
 constexpr int kRowPairs = kCamRec / 2;  // 16-byte row pairs per camera variant
 
-template <int W, int MINB, bool DIST_LAST>
+// VCT / VBT: compile-time camera / bundle variant counts (0 = read them from the plan): with
+// them the variant loops unroll completely and the FP64 chains (~20 cycles per dependent
+// operation) of different variants interleave.
+template <int W, int MINB, bool DIST_LAST, int VCT = 0, int VBT = 0>
 __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, TiledPlan tp, int mt,
                                                                 double *__restrict__ fvec, double *__restrict__ dist,
                                                                 double *__restrict__ jac, double *__restrict__ dist_last) {
@@ -390,7 +393,7 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     mbar_wait(bar_mk, 0);
     bool variants_ready = false;
     double2 *const jac2 = reinterpret_cast<double2 *>(jac) + f;
-    const int VB = tp.VB, VC = tp.VC;
+    const int VB = VBT ? VBT : tp.VB, VC = VCT ? VCT : tp.VC;
     for (int jj = 2 * w; jj < mcount; jj += 2 * W) {
         // an odd marker count evaluates its last marker twice (same values to the same addresses)
         const int j1 = min(jj + 1, mcount - 1);
@@ -420,6 +423,7 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         }
         double2 *const jp0 = jac2 + i0, *const jp1 = jac2 + i1;
         // bundle columns: base camera rows, perturbed bundle
+#pragma unroll(VBT ? VBT : 1)
         for (int v = 0; v < VB; ++v) {
             const double *q0 = b0 + (v + 1) * kBndRec, *q1 = b1 + (v + 1) * kBndRec;
             double ax, ay, bx, by;
@@ -440,6 +444,7 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             variants_ready = true;
         }
         const double2 *sv = scam + (size_t)kRowPairs * kRowFrames + lane;
+#pragma unroll(VCT ? VCT : 1)
         for (int v = 0; v < VC; ++v, sv += kRowPairs * kRowFrames) {
             double cv[12];
 #pragma unroll

@@ -96,7 +96,12 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             const int nv = p->tiled.VC + 1, nrec = (p->tiled.VB + 1) * kBndRec;
             const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
             auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
-            auto kern = d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>;
+            // the common shape (6 camera attributes, 3 bundle attributes) has its own instance
+            static int fixed_mode = -1;
+            if (fixed_mode < 0) { const char *e = getenv("MMB_ROWS_FIXED"); fixed_mode = e ? atoi(e) : 1; }
+            const bool fixed = fixed_mode && p->tiled.VC == 6 && p->tiled.VB == 3;
+            auto kern = fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
+                              : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>);
             int &mt = p->rows_mt[d_dist_last ? 1 : 0];
             if (mt == 0) {  // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
                 int occ = 1, sm_count = 1;

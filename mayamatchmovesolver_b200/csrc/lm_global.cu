@@ -67,6 +67,7 @@ struct LmWorkspace {
     PinnedBlock pinned;        // backs h_st, h_cancel, h_stage
     LmState *h_st = nullptr;   // pinned host mirror
     int32_t *attr_slot = nullptr, *i2p = nullptr;
+    AsmShared asm_shared{};    // columns shared by every marker (k_assemble_shared)
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
     double *diag = nullptr, *acnorm = nullptr;        // [n] by parameter id
@@ -524,6 +525,33 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         *w->h_cancel = 0;
         CKW(cudaHostGetDevicePointer((void **)&w->d_cancel, w->h_cancel, 0));
     }
+    {   // columns whose attribute is the same for every marker (dense-grid scenes only)
+        AsmShared &as = w->asm_shared;
+        as.ns = 0; as.mask = 0;
+        const char *e = getenv("MMB_ASM_SHARED");
+        const bool enabled = !(e && atoi(e) == 0);
+        if (enabled && hp.dense_grid && hp.M > 1 && hp.kmax <= 32) {
+            const int k0 = hp.mkr_k[0];
+            bool same_k = true;
+            for (int mk = 1; mk < hp.M && same_k; ++mk) same_k = hp.mkr_k[mk] == k0;
+            if (same_k) {
+                for (int c = 0; c < k0 && as.ns < 16; ++c) {
+                    const int a0 = hp.plan[c].attr;
+                    bool same = a0 >= 0;
+                    for (int mk = 1; mk < hp.M && same; ++mk) same = hp.plan[(size_t)mk * hp.kmax + c].attr == a0;
+                    if (same) {
+                        as.col[as.ns] = c; as.slot[as.ns] = hp.attr_slot[a0]; as.anim[as.ns] = hp.attr_anim[a0] ? 1 : 0;
+                        as.mask |= 1u << c;
+                        ++as.ns;
+                    }
+                }
+            }
+            const int ok[] = {6, 7, 9, 11, 13, 15};
+            bool supported = false;
+            for (int v : ok) supported = supported || v == as.ns;
+            if (!supported) { as.ns = 0; as.mask = 0; }
+        }
+    }
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
     CKW(A.alloc(&w->U, (size_t)d.F * d.na * d.na));
@@ -645,7 +673,28 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
         MMB_CUDA_CHECK(cudaMemsetAsync(w->W, 0, sizeof(double) * (size_t)d.KE * d.NSP, p->stream));
     }
     MMB_CUDA_CHECK(cudaMemsetAsync(w->V, 0, sizeof(double) * (size_t)d.NSP * d.NSP, p->stream));
-    k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->U, w->gE, w->W, w->V);
+    k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->U, w->gE, w->W, w->V,
+                                                            w->asm_shared.mask);
+    if (w->asm_shared.ns) {
+        LAUNCH_CHECK();
+        const HostProblem &hp = p->hp;
+        // marker groups sized for about two CTAs per SM slot
+        const int fb = (hp.F + 31) / 32;
+        int G = std::max(1, std::min(hp.M, (148 * 8 + fb - 1) / fb));
+        const int mt = (hp.M + G - 1) / G;
+        G = (hp.M + mt - 1) / mt;
+        const dim3 grid(fb, G);
+#define MMB_ASM_SHARED(NS_)                                                                                          \
+    case NS_:                                                                                                        \
+        k_assemble_shared<NS_><<<grid, 128, 0, p->stream>>>(w->asm_shared, d, hp.F, hp.M, mt, p->d_jac, p->d_fvec,   \
+                                                            w->U, w->gE, w->W, w->V);                                \
+        break;
+        switch (w->asm_shared.ns) {
+            MMB_ASM_SHARED(6) MMB_ASM_SHARED(7) MMB_ASM_SHARED(9) MMB_ASM_SHARED(11) MMB_ASM_SHARED(13) MMB_ASM_SHARED(15)
+            default: break;
+        }
+#undef MMB_ASM_SHARED
+    }
     LAUNCH_CHECK();
     if (d.ns) {
         k_prep_gather<<<(d.ns + 255) / 256, 256, 0, p->stream>>>(d, w->V, w->sdiag);

@@ -43,10 +43,23 @@ __global__ void k_sumsq_partial(const double *__restrict__ v, size_t n, double *
 
 // ---- assembly of J^T J and J^T f from the block Jacobian ---------------------
 // jac[c*m + 2i + {0,1}], plan gives the attr of column c of marker(i).
+// Columns whose solver attribute is the same for EVERY marker (the camera's animated attributes,
+// focal length, lens coefficients): their mutual products are sums over all markers of a frame
+// (or over all observations), i.e. heavily contended addresses for atomics.  With a shared-column
+// mask they are left to k_assemble_shared (register accumulation, one atomic per CTA and entry)
+// and this kernel only does the pairs that involve a per-marker (bundle) column.
+struct AsmShared {
+    int ns;          // number of shared columns (0: none, k_assemble does everything)
+    unsigned mask;   // bit c set: column c is shared
+    int col[16];     // the shared columns
+    int slot[16];    // their slot in the animated / static class
+    int anim[16];
+};
+
 __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const double *__restrict__ jac,
                                                   const double *__restrict__ fvec,
                                                   const int32_t *__restrict__ attr_slot, double *U, double *gE,
-                                                  double *W, double *V) {
+                                                  double *W, double *V, unsigned shared_mask) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = i < s.nobs;
     int marker = -1, frame = 0;
@@ -69,9 +82,11 @@ __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const do
         const int s1 = attr_slot[a1];
         const double jx1 = live ? jac[(size_t)c1 * m + 2 * (size_t)i] : 0.0;
         const double jy1 = live ? jac[(size_t)c1 * m + 2 * (size_t)i + 1] : 0.0;
+        const bool sh1 = (shared_mask >> c1) & 1u;
         // gradient
         const double gv = jx1 * fx + jy1 * fy;
-        if (an1) {
+        if (sh1) {
+        } else if (an1) {
             if (live) atomicAdd(&gE[(size_t)frame * d.na + s1], gv);
         } else if (uniform) {
             const double r = warp_sum(gv);
@@ -80,6 +95,7 @@ __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const do
             atomicAdd(&V[(size_t)d.ns * d.NSP + s1], gv);
         }
         for (int c2 = 0; c2 <= c1; ++c2) {
+            if (sh1 && ((shared_mask >> c2) & 1u)) continue;
             const int a2 = pl[c2].attr;
             const bool an2 = s.attr_anim[a2];
             const int s2 = attr_slot[a2];
@@ -106,6 +122,92 @@ __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const do
                 }
             }
         }
+    }
+}
+
+// Products among the NS shared columns (and their gradient entries) for dense-grid scenes
+// (observation i = marker * F + frame).  CTA = (32 frames, group of mt markers), lane = frame,
+// 4 warps; the NS (NS + 1) / 2 + NS sums are dealt to the warps, every warp walks all markers of
+// the group with its share of the sums in registers.  Per-frame sums (animated x animated ->
+// U, animated x static -> W, animated gradient -> gE) end as one atomic per CTA, frame and entry;
+// static x static sums are reduced over the frames of the warp first.
+template <int NS, int WID>
+__device__ __forceinline__ void assemble_shared_body(const AsmShared &sh, const LmDims &d, const double2 *__restrict__ jac2,
+                                                     const double2 *__restrict__ f2, int F, int frame, bool live,
+                                                     int m_begin, int m_end, double *U, double *gE, double *W, double *V) {
+    constexpr int P = NS * (NS + 1) / 2 + NS;   // pairs (c1 >= c2) then gradient entries
+    constexpr int PW = (P + 3) / 4;             // sums per warp
+    constexpr int P0 = WID * PW, P1 = (P0 + PW < P) ? P0 + PW : P;
+    double acc[PW];
+#pragma unroll
+    for (int u = 0; u < PW; ++u) acc[u] = 0.0;
+    const size_t mh = (size_t)d.m / 2;          // double2 elements per Jacobian column
+    for (int mk = m_begin; mk < m_end; ++mk) {
+        const size_t i = (size_t)mk * F + frame;
+        double2 jv[NS];
+#pragma unroll
+        for (int c = 0; c < NS; ++c) jv[c] = live ? __ldg(&jac2[(size_t)sh.col[c] * mh + i]) : make_double2(0.0, 0.0);
+        const double2 fv = live ? __ldg(&f2[i]) : make_double2(0.0, 0.0);
+        int pidx = 0;
+#pragma unroll
+        for (int c1 = 0; c1 < NS; ++c1)
+#pragma unroll
+            for (int c2 = 0; c2 <= c1; ++c2, ++pidx)
+                if (pidx >= P0 && pidx < P1) acc[pidx - P0] = fma(jv[c1].x, jv[c2].x, fma(jv[c1].y, jv[c2].y, acc[pidx - P0]));
+#pragma unroll
+        for (int c1 = 0; c1 < NS; ++c1, ++pidx)
+            if (pidx >= P0 && pidx < P1) acc[pidx - P0] = fma(jv[c1].x, fv.x, fma(jv[c1].y, fv.y, acc[pidx - P0]));
+    }
+    const int lane = threadIdx.x & 31;
+    int pidx = 0;
+#pragma unroll
+    for (int c1 = 0; c1 < NS; ++c1)
+#pragma unroll
+        for (int c2 = 0; c2 <= c1; ++c2, ++pidx)
+            if (pidx >= P0 && pidx < P1) {
+                const double v = acc[pidx - P0];
+                const int s1 = sh.slot[c1], s2 = sh.slot[c2];
+                const bool an1 = sh.anim[c1], an2 = sh.anim[c2];
+                if (an1 && an2) {
+                    const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
+                    if (live) atomicAdd(&U[((size_t)frame * d.na + r) * d.na + cc], v);
+                } else if (an1 != an2) {
+                    const int ja = an1 ? s1 : s2, js = an1 ? s2 : s1;
+                    if (live) atomicAdd(&W[((size_t)frame * d.na + ja) * d.NSP + js], v);
+                } else {
+                    const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
+                    const double t = warp_sum(v);
+                    if (lane == 0) atomicAdd(&V[(size_t)r * d.NSP + cc], t);
+                }
+            }
+#pragma unroll
+    for (int c1 = 0; c1 < NS; ++c1, ++pidx)
+        if (pidx >= P0 && pidx < P1) {
+            const double v = acc[pidx - P0];
+            if (sh.anim[c1]) {
+                if (live) atomicAdd(&gE[(size_t)frame * d.na + sh.slot[c1]], v);
+            } else {
+                const double t = warp_sum(v);
+                if (lane == 0) atomicAdd(&V[(size_t)d.ns * d.NSP + sh.slot[c1]], t);
+            }
+        }
+}
+
+template <int NS>
+__global__ void __launch_bounds__(128) k_assemble_shared(AsmShared sh, LmDims d, int F, int M, int mt,
+                                                         const double *__restrict__ jac, const double *__restrict__ fvec,
+                                                         double *U, double *gE, double *W, double *V) {
+    const int frame = blockIdx.x * 32 + (threadIdx.x & 31);
+    const bool live = frame < F;
+    const int m_begin = blockIdx.y * mt, m_end = min(M, m_begin + mt);
+    const double2 *jac2 = reinterpret_cast<const double2 *>(jac);
+    const double2 *f2 = reinterpret_cast<const double2 *>(fvec);
+    const int fr = live ? frame : 0;
+    switch (threadIdx.x >> 5) {
+        case 0: assemble_shared_body<NS, 0>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
+        case 1: assemble_shared_body<NS, 1>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
+        case 2: assemble_shared_body<NS, 2>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
+        default: assemble_shared_body<NS, 3>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
     }
 }
 
