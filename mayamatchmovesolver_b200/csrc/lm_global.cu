@@ -70,6 +70,7 @@ struct LmWorkspace {
     AsmShared asm_shared{};    // columns shared by every marker (k_assemble_shared)
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
+    double *Dinv = nullptr;    // [NSP/64][64*64] inverses of the factor's diagonal blocks (k_chol_tiles phase E)
     double *diag = nullptr, *acnorm = nullptr;        // [n] by parameter id
     double *p_int = nullptr, *w_int = nullptr;        // [KE + NSP] internal order
     double *p_par = nullptr, *x2 = nullptr;           // [n] parameter order
@@ -578,7 +579,7 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.alloc(&w->sdiag, (size_t)2 * std::max(d.ns, 1)));
     CKW(A.alloc(&w->tvec, (size_t)std::max(d.ns, 1)));
     CKW(A.alloc(&w->stat_part, (size_t)3 * kStatBlocks));
-    w->gemv_chunks = std::max(1, std::min(64, d.KE / 256));
+    w->gemv_chunks = std::max(1, std::min(256, d.KE / 48));   // ~1100 CTAs of 128 threads at cfg3
     CKW(A.alloc(&w->part_gemv, (size_t)w->gemv_chunks * d.NSP));
     CKW(cudaFuncSetAttribute(k_chol_panel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholPanelSmem));
     CKW(cudaFuncSetAttribute(k_backward_s, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(double) * (64 * kDS + 64 + 32 * 64)));
@@ -593,6 +594,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
             CKW(cudaFuncSetAttribute(k_chol_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             const char *e = getenv("MMB_CHOL");
             w->chol_tiles = !(e && !strcmp(e, "steps"));
+            const char *ei = getenv("MMB_WAVE_INV");
+            if (w->chol_tiles && !(ei && atoi(ei) == 0)) CKW(A.alloc(&w->Dinv, ((size_t)d.NSP / 64) * 4096));
         }
         CKW(A.alloc(&w->wave_ctr, 1));
         CKW(cudaMemsetAsync(w->wave_ctr, 0, sizeof(int), p->stream));
@@ -719,13 +722,14 @@ static mmb_status enqueue_backward_s(DeviceProblem *p, double *pS) {
         const double *S = w->S;
         int *flags = w->wave_flags;
         const int *ctr = w->wave_ctr;
+        const double *dinv = w->Dinv;
         int slot = 1;
         if (w->capturing) {  // graph body: plain launch (see the note above k_backward_wave)
-            k_backward_wave<<<nblk, 256, kWaveSmemBwd, p->stream>>>(d, S, pS, flags, ctr, slot);
+            k_backward_wave<<<nblk, 256, kWaveSmemBwd, p->stream>>>(d, S, pS, flags, ctr, slot, dinv);
             LAUNCH_CHECK();
             return MMB_OK;
         }
-        void *args[] = {&d, &S, &pS, &flags, &ctr, &slot};
+        void *args[] = {&d, &S, &pS, &flags, &ctr, &slot, &dinv};
         MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_backward_wave, dim3(nblk), dim3(256), args, kWaveSmemBwd, p->stream));
         ++p->launches;
         return MMB_OK;
@@ -743,13 +747,14 @@ static mmb_status enqueue_forward_s(DeviceProblem *p, double *wS) {
         const double *rhs = wS;
         int *flags = w->wave_flags;
         const int *ctr = w->wave_ctr;
+        const double *dinv = w->Dinv;
         int slot = 2;
         if (w->capturing) {
-            k_forward_wave<<<nblk, 256, kWaveSmemFwd, p->stream>>>(d, S, rhs, wS, flags, ctr, slot);
+            k_forward_wave<<<nblk, 256, kWaveSmemFwd, p->stream>>>(d, S, rhs, wS, flags, ctr, slot, dinv);
             LAUNCH_CHECK();
             return MMB_OK;
         }
-        void *args[] = {&d, &S, &rhs, &wS, &flags, &ctr, &slot};
+        void *args[] = {&d, &S, &rhs, &wS, &flags, &ctr, &slot, &dinv};
         MMB_CUDA_CHECK(cudaLaunchCooperativeKernel((void *)k_forward_wave, dim3(nblk), dim3(256), args, kWaveSmemFwd, p->stream));
         ++p->launches;
         return MMB_OK;
@@ -800,7 +805,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     if (prof) cudaEventRecord(w->ev[1], s);
     if (w->chol_tiles) {
-        k_chol_tiles<<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr);
+        k_chol_tiles<<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
         LAUNCH_CHECK();
     } else {
         for (int kb = 0; kb < nb; ++kb) {

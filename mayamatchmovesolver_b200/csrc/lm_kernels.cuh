@@ -703,7 +703,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
 }
 
 __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
-                                                    const int *epoch_ctr) {
+                                                    const int *epoch_ctr, double *__restrict__ Dinv) {
     extern __shared__ __align__(16) double sm[];
     double *sA = sm;                 // L(i,k) during phase A; afterwards T (stride kCS)
     double *sB = sm + 64 * kOS;      // L(j,k) during phase A; afterwards X (stride kCS)
@@ -956,6 +956,60 @@ __global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, doubl
         asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(f), "r"(epoch) : "memory");
         if (traced) tr[5] = gtimer();
     }
+    // ---- E (diagonal tiles, after publishing: nobody waits for this): inverse of L(j,j) ----
+    // The triangular solves that follow (k_forward_wave / k_backward_wave) are chains of 24
+    // dependent 64x64 block solves; with L(j,j)^-1 at hand each block solve is a 64x64
+    // matrix-vector product instead of 64 dependent substitution steps.
+    if (diag && Dinv) {
+        double *T = sA, *X = sB;
+        if (tid < 64) {  // inverses of the eight 8x8 diagonal blocks, one column per thread
+            const int b8 = (tid >> 3) * 8, c = tid & 7;
+            double x[8];
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) {
+                double sacc = (ii == c) ? 1.0 : 0.0;
+#pragma unroll
+                for (int k = 0; k < ii; ++k) sacc = fma(-T[(b8 + ii) * kCS + b8 + k], x[k], sacc);
+                x[ii] = sacc * dinv_s[b8 + ii];
+            }
+#pragma unroll
+            for (int ii = 0; ii < 8; ++ii) X[(b8 + ii) * kCS + b8 + c] = x[ii];
+        }
+        __syncthreads();
+        // off-diagonal 8x8 blocks by distance from the diagonal:
+        //   Inv(i,j) = -Inv(i,i) * sum_{k=j}^{i-1} L(i,k) Inv(k,j); the inner sum is parked in the
+        //   mirrored (upper) block (j,i), which the result never uses
+        for (int dd = 1; dd < 8; ++dd) {
+            const int cnt = (8 - dd) * 64;
+            for (int e = tid; e < cnt; e += 256) {
+                const int jb = e >> 6, r = (e >> 3) & 7, c = e & 7, ib = jb + dd;
+                double s0 = 0.0, s1 = 0.0;
+                for (int kb = jb; kb < ib; ++kb) {
+#pragma unroll
+                    for (int t = 0; t < 8; t += 2) {
+                        s0 = fma(T[(8 * ib + r) * kCS + 8 * kb + t], X[(8 * kb + t) * kCS + 8 * jb + c], s0);
+                        s1 = fma(T[(8 * ib + r) * kCS + 8 * kb + t + 1], X[(8 * kb + t + 1) * kCS + 8 * jb + c], s1);
+                    }
+                }
+                X[(8 * jb + r) * kCS + 8 * ib + c] = s0 + s1;
+            }
+            __syncthreads();
+            for (int e = tid; e < cnt; e += 256) {
+                const int jb = e >> 6, r = (e >> 3) & 7, c = e & 7, ib = jb + dd;
+                double s0 = 0.0;
+#pragma unroll
+                for (int t = 0; t < 8; ++t)
+                    if (t <= r) s0 = fma(X[(8 * ib + r) * kCS + 8 * ib + t], X[(8 * jb + t) * kCS + 8 * ib + c], s0);
+                X[(8 * ib + r) * kCS + 8 * jb + c] = -s0;
+            }
+            __syncthreads();
+        }
+        double *out = Dinv + (size_t)j * 4096;
+        for (int e = tid; e < 64 * 64; e += 256) {
+            const int rr = e >> 6, c = e & 63;
+            out[e] = c <= rr ? X[rr * kCS + c] : 0.0;
+        }
+    }
 }
 
 // ---- triangular solves with L_S (single CTA, 1024 threads) ---------------------------
@@ -1115,19 +1169,24 @@ __device__ __forceinline__ void wave_block_solve(const double *D, const double *
     xs[lane] = x0; xs[lane + 32] = x1;
 }
 
-__device__ __forceinline__ void wave_stage_diag(LmDims d, const double *__restrict__ S, int c0, double *D, double *dinv) {
+// Dinv != nullptr: stage the INVERSE of the diagonal block (k_chol_tiles phase E) instead; the
+// identity rows of the mask are their own inverse
+__device__ __forceinline__ void wave_stage_diag(LmDims d, const double *__restrict__ S, int c0, double *D, double *dinv,
+                                                const double *__restrict__ Dinv = nullptr) {
+    const double *inv = Dinv ? Dinv + (size_t)(c0 / kNB) * 4096 : nullptr;
     for (int t = threadIdx.x; t < 64 * 64; t += blockDim.x) {
         const int r = t >> 6, c = t & 63;
         const bool in = (c <= r) && (c0 + r < d.ns);  // rows >= ns (rhs row, padding): identity
-        D[r * kDS + c] = in ? S[(size_t)(c0 + r) * d.NSP + c0 + c] : (r == c ? 1.0 : 0.0);
+        const double v = inv ? inv[t] : S[(size_t)(c0 + r) * d.NSP + c0 + c];
+        D[r * kDS + c] = in ? v : (r == c ? 1.0 : 0.0);
     }
     __syncthreads();
-    if (threadIdx.x < 64) dinv[threadIdx.x] = 1.0 / D[threadIdx.x * kDS + threadIdx.x];
+    if (!inv && threadIdx.x < 64) dinv[threadIdx.x] = 1.0 / D[threadIdx.x * kDS + threadIdx.x];
 }
 
 // backward: L^T p = y, y = augmented row ns of S.  blockIdx 0 owns the LAST block.
 __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *__restrict__ S, double *p, int *flags,
-                                                       const int *epoch_ctr, int slot) {
+                                                       const int *epoch_ctr, int slot, const double *__restrict__ Dinv) {
     extern __shared__ double sm[];
     const int epoch = __ldcg(epoch_ctr) + slot;
     double *D = sm;                // 64 x kDS
@@ -1138,7 +1197,7 @@ __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *_
     const int nblk = (d.ns + kNB - 1) / kNB;
     const int b = nblk - 1 - blockIdx.x, c0 = b * kNB;
     const int tid = threadIdx.x, g = tid >> 6, c = tid & 63;
-    wave_stage_diag(d, S, c0, D, dinv);
+    wave_stage_diag(d, S, c0, D, dinv, Dinv);
     if (tid < 64) acc[tid] = (c0 + tid < d.ns) ? S[(size_t)d.ns * d.NSP + c0 + tid] : 0.0;
     // block (i, b) of L, rows g, g+4, ... of block row i, column c of block column b
     double cur[16], nxt[16];
@@ -1162,7 +1221,19 @@ __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *_
         for (int k = 0; k < 16; ++k) cur[k] = nxt[k];
     }
     __syncthreads();
-    if (tid < 32) wave_block_solve<false>(D, dinv, acc, tid);
+    if (Dinv) {  // x = L(b,b)^-T acc: x_c = sum_k inv[k][c] acc[k], four partial sums per entry
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; k += 2) {
+            s0 = fma(D[(g + 4 * k) * kDS + c], acc[g + 4 * k], s0);
+            s1 = fma(D[(g + 4 * k + 4) * kDS + c], acc[g + 4 * k + 4], s1);
+        }
+        part[g * 64 + c] = s0 + s1;
+        __syncthreads();
+        if (tid < 64) acc[tid] = (part[tid] + part[64 + tid]) + (part[128 + tid] + part[192 + tid]);
+    } else if (tid < 32) {
+        wave_block_solve<false>(D, dinv, acc, tid);
+    }
     __syncthreads();
     if (tid < 64) p[c0 + tid] = (c0 + tid < d.ns) ? acc[tid] : 0.0;
     wave_publish(&flags[b], epoch);
@@ -1170,7 +1241,8 @@ __global__ void __launch_bounds__(256) k_backward_wave(LmDims d, const double *_
 
 // forward: L w = rhs for rows [0, ns).  rhs and w may alias.  blockIdx b owns block b.
 __global__ void __launch_bounds__(256) k_forward_wave(LmDims d, const double *__restrict__ S, const double *rhs, double *w,
-                                                      int *flags, const int *epoch_ctr, int slot) {
+                                                      int *flags, const int *epoch_ctr, int slot,
+                                                      const double *__restrict__ Dinv) {
     extern __shared__ double sm[];
     const int epoch = __ldcg(epoch_ctr) + slot;
     double *D = sm;
@@ -1179,7 +1251,7 @@ __global__ void __launch_bounds__(256) k_forward_wave(LmDims d, const double *__
     double *wi = acc + 64;
     const int b = blockIdx.x, c0 = b * kNB;
     const int tid = threadIdx.x, r = tid >> 2, q = tid & 3;
-    wave_stage_diag(d, S, c0, D, dinv);
+    wave_stage_diag(d, S, c0, D, dinv, Dinv);
     if (tid < 64) acc[tid] = (c0 + tid < d.ns) ? rhs[c0 + tid] : 0.0;
     __syncthreads();
     // block (b, i) of L: row r of block row b, columns q*16 .. q*16+15 of block column i
@@ -1207,7 +1279,21 @@ __global__ void __launch_bounds__(256) k_forward_wave(LmDims d, const double *__
         for (int k = 0; k < 16; ++k) cur[k] = nxt[k];
     }
     __syncthreads();
-    if (tid < 32) wave_block_solve<true>(D, dinv, acc, tid);
+    if (Dinv) {  // x = L(b,b)^-1 acc: row r by four threads, 16 columns each
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 16; k += 2) {
+            s0 = fma(D[r * kDS + q * 16 + k], acc[q * 16 + k], s0);
+            s1 = fma(D[r * kDS + q * 16 + k + 1], acc[q * 16 + k + 1], s1);
+        }
+        double sacc = s0 + s1;
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+        __syncthreads();
+        if (q == 0) acc[r] = sacc;
+    } else if (tid < 32) {
+        wave_block_solve<true>(D, dinv, acc, tid);
+    }
     __syncthreads();
     if (tid < 64 && c0 + tid < d.ns) w[c0 + tid] = acc[tid];
     wave_publish(&flags[b], epoch);
@@ -1267,9 +1353,19 @@ __global__ void __launch_bounds__(128) k_gemv_t_partial(LmDims d, const double *
     const int per = (d.KE + gridDim.y - 1) / gridDim.y;
     const int r0 = blockIdx.y * per, r1 = min(d.KE, r0 + per);
     if (j >= d.ns) return;
-    double acc = 0.0;
-    for (int r = r0; r < r1; ++r) acc += Y[(size_t)r * d.NSP + j] * w_int[r];
-    partial[(size_t)blockIdx.y * d.NSP + j] = acc;
+    // eight independent accumulators: the loads of eight rows are in flight together and no
+    // FMA waits for the previous one (a single chain ran at HBM latency per row)
+    double acc[8] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    int r = r0;
+    for (; r + 8 <= r1; r += 8) {
+        double y[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) y[u] = Y[(size_t)(r + u) * d.NSP + j];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) acc[u] = fma(y[u], w_int[r + u], acc[u]);
+    }
+    for (; r < r1; ++r) acc[0] = fma(Y[(size_t)r * d.NSP + j], w_int[r], acc[0]);
+    partial[(size_t)blockIdx.y * d.NSP + j] = ((acc[0] + acc[1]) + (acc[2] + acc[3])) + ((acc[4] + acc[5]) + (acc[6] + acc[7]));
 }
 
 // tvec[j] = sum_chunks partial[chunk][j]  (= (Y^T w_E)[j] of this shard)
