@@ -9,6 +9,11 @@
 #include "problem.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <functional>
+#include <thread>
 #include <cmath>
 #include <limits>
 #include <set>
@@ -153,6 +158,15 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         hp.attr_off.assign(s->attr_offset, s->attr_offset + hp.A);
         hp.attr_scl.assign(s->attr_scale, s->attr_scale + hp.A);
     }
+    const bool timing = getenv("MMB_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto mark = [&](const char *what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mmb timing]   host: %s %.3f ms\n", what, 1e3 * std::chrono::duration<double>(now - t_prev).count());
+        t_prev = now;
+    };
+    mark("copy of the scene tables");
     // ---- validation ------------------------------------------------------
     for (int t = 0; t < hp.T; ++t) {
         if (hp.tfm_parent[t] >= t || hp.tfm_parent[t] < -1) { hp.error = "tfm_parent must precede child"; return MMB_ERR_INVALID_ARGUMENT; }
@@ -179,39 +193,70 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     for (int a = 0; a < hp.A; ++a)
         if (!ref_ok(hp.attr_ref[a], hp.num_static, hp.num_anim, false)) { hp.error = "bad solver attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
 
+    mark("validation");
     // ---- countUpNumberOfErrors (marker-major, frame-minor) ---------------
     std::vector<double> wmax(F, 0.0);
     std::vector<uint8_t> wseen(F, 0);
     {
-        const size_t cap = (size_t)hp.M * F;
-        hp.err_marker.resize(cap); hp.err_frame.resize(cap);
-        hp.obs_mx.resize(cap); hp.obs_my.resize(cap); hp.obs_w.resize(cap);
-        size_t k = 0;
-        for (int i = 0; i < hp.M; ++i) {
-            const size_t o0 = (size_t)i * F;
-            for (size_t j = 0; j < F; ++j) {
-                const size_t o = o0 + j;
-                const double weight = s->mkr_weight[o];
-                if (s->mkr_enable[o] != 0 && (weight > 0.0)) {
-                    hp.err_marker[k] = i;
+        // Two passes over marker ranges on a few host threads (the scan is 5e5 .. 5e7 entries):
+        // count the enabled observations per range, then fill at the prefix offsets.  The
+        // order (marker-major, frame-minor) is the reference's.
+        const size_t M = (size_t)hp.M;
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)16, (M * F) / 65536 + 1}));
+        std::vector<size_t> count(T + 1, 0);
+        std::vector<std::vector<double>> twmax(T, std::vector<double>(F, 0.0));
+        std::vector<std::vector<uint8_t>> tseen(T, std::vector<uint8_t>(F, 0));
+        auto range = [&](int t, size_t *m0, size_t *m1) { *m0 = M * t / T; *m1 = M * (t + 1) / T; };
+        auto enabled = [&](size_t o) { return s->mkr_enable[o] != 0 && (s->mkr_weight[o] > 0.0); };
+        auto run = [&](const std::function<void(int)> &fn) {
+            std::vector<std::thread> th;
+            for (int t = 1; t < T; ++t) th.emplace_back(fn, t);
+            fn(0);
+            for (auto &x : th) x.join();
+        };
+        run([&](int t) {
+            size_t m0, m1, k = 0;
+            range(t, &m0, &m1);
+            for (size_t o = m0 * F; o < m1 * F; ++o) k += enabled(o) ? 1 : 0;
+            count[t + 1] = k;
+        });
+        for (int t = 0; t < T; ++t) count[t + 1] += count[t];
+        const size_t total = count[T];
+        hp.err_marker.resize(total); hp.err_frame.resize(total);
+        hp.obs_mx.resize(total); hp.obs_my.resize(total); hp.obs_w.resize(total);
+        run([&](int t) {
+            size_t m0, m1, k = count[t];
+            range(t, &m0, &m1);
+            std::vector<double> &wm = twmax[t];
+            std::vector<uint8_t> &ws = tseen[t];
+            for (size_t i = m0; i < m1; ++i) {
+                const size_t o0 = i * F;
+                for (size_t j = 0; j < F; ++j) {
+                    const size_t o = o0 + j;
+                    if (!enabled(o)) continue;
+                    const double weight = s->mkr_weight[o];
+                    hp.err_marker[k] = (int32_t)i;
                     hp.err_frame[k] = (int32_t)j;
                     hp.obs_w[k] = weight;
                     hp.obs_mx[k] = s->mkr_x[o];
                     hp.obs_my[k] = s->mkr_y[o];
                     ++k;
-                    if (!wseen[j] || weight > wmax[j]) wmax[j] = weight;
-                    wseen[j] = 1;
+                    if (!ws[j] || weight > wm[j]) wm[j] = weight;
+                    ws[j] = 1;
                 }
             }
-        }
-        hp.err_marker.resize(k); hp.err_frame.resize(k);
-        hp.obs_mx.resize(k); hp.obs_my.resize(k); hp.obs_w.resize(k);
+        });
+        for (int t = 0; t < T; ++t)
+            for (size_t j = 0; j < F; ++j)
+                if (tseen[t][j] && (!wseen[j] || twmax[t][j] > wmax[j])) { wmax[j] = twmax[t][j]; wseen[j] = 1; }
     }
     hp.nobs = (int)hp.err_marker.size();
     hp.m = 2 * hp.nobs;
     for (int i = 0; i < hp.nobs; ++i) hp.obs_w[i] = hp.obs_w[i] / wmax[hp.err_frame[i]];
     hp.dense_grid = ((size_t)hp.nobs == (size_t)hp.M * F);
 
+    mark("observation scan");
     // ---- countUpNumberOfUnknownParameters (attr-major, frame-minor) -------
     hp.par_attr.clear(); hp.par_frame.clear();
     hp.attr_param_base.assign(hp.A, 0);
@@ -245,6 +290,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         hp.par_to_int[p] = q; hp.int_to_par[q] = p;
     }
 
+    mark("parameters");
     // ---- entity dependencies ---------------------------------------------
     hp.cam_deps.assign(hp.C, {}); hp.bnd_deps.assign(hp.B, {}); hp.lens_deps.assign(hp.L, {});
     hp.cam_varies.assign(hp.C, 0); hp.bnd_varies.assign(hp.B, 0); hp.lens_varies.assign(hp.L, 0);
@@ -278,6 +324,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     for (int c = 0; c < hp.C; ++c)
         if (hp.cam_lens[c] >= 0 && hp.lens_model[hp.cam_lens[c]] != MMB_LENS_PASSTHROUGH) hp.any_lens = true;
 
+    mark("dependencies");
     // ---- variant tables ---------------------------------------------------
     const int vmul = (opt->auto_diff_type == 1) ? 2 : 1;
     auto layout = [&](const std::vector<std::vector<int32_t>> &deps, const std::vector<uint8_t> &varies,
@@ -324,6 +371,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     expand(hp.bnd_job_start, hp.bnd_thread_job);
     expand(hp.lens_job_start, hp.lens_thread_job);
 
+    mark("variant tables");
     // ---- per-marker column plan -------------------------------------------
     hp.mkr_k.assign(hp.M, 0);
     std::vector<std::vector<PlanEntry>> plans(hp.M);
@@ -352,6 +400,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     hp.plan.assign((size_t)hp.M * std::max(hp.kmax, 1), PlanEntry{-1, 0, 0, 0, 0});
     for (int mk = 0; mk < hp.M; ++mk)
         for (size_t c = 0; c < plans[mk].size(); ++c) hp.plan[(size_t)mk * hp.kmax + c] = plans[mk][c];
+    mark("column plans");
     return MMB_OK;
 }
 
