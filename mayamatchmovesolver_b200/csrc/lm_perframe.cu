@@ -18,7 +18,7 @@
 
 namespace mmb {
 
-constexpr int kPfThreads = 128;
+constexpr int kPfThreads = 64;   // 234 registers per thread: 64 threads keep four frames per SM in flight (128: two)
 
 struct PfFrameResult {
     int info, nfev, njev, func_evals;

@@ -139,6 +139,29 @@ def _copy_result(r):
     return o
 
 
+class PerFrameResults:
+    """The per-frame records of mmb_solve_per_frame as a read-only sequence of SolveResult;
+    entries are built when asked for (a large batch has tens of thousands of frames)."""
+
+    def __init__(self, raw):
+        self._raw = raw
+
+    def __len__(self):
+        return len(self._raw)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        return SolveResult(_copy_result(self._raw[i]), None, None, None)
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+
 class Problem:
     def __init__(self, scene, options=None, shard=None, local_slice=None, **opt_overrides):
         """shard = (rank, world): the handle covers this rank's frame range of `scene`
@@ -256,7 +279,7 @@ class Problem:
         check(self._lib.mmb_solve_per_frame(self._h, C.byref(r), per, x.ctypes.data_as(c_f64p),
                                             av.ctypes.data_as(c_f64p), dist.ctypes.data_as(c_f64p)),
               "mmb_solve_per_frame")
-        return SolveResult(r, x, av, dist), [SolveResult(_copy_result(per[f]), None, None, None) for f in range(F)]
+        return SolveResult(r, x, av, dist), PerFrameResults(per)
 
     def attach_comm(self, comm_id, rank, world):
         """collective over the ranks of `comm_id` (bytes from comm_unique_id): mmb_solve on this
