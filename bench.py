@@ -331,6 +331,16 @@ def run_own(args):
                      "frac": achieved / peaks["hbm_gbs"], "traffic": traffic, "algorithmic_bytes_per_launch": algo_bytes,
                      "peak_source": peaks_src, "kernel_ms": jac_ms / args.steps},
     }
+    # the same bytes through a plain streaming kernel (12 MB read, 84 MB written, L2 flushed):
+    # the share of the 2-GiB copy peak a transfer of THIS size can reach at all
+    if rank == 0:
+        from mayamatchmovesolver_b200.problem import stream_floor
+        read_b = 24 * nobs_rank
+        floor_ms = stream_floor(read_b, algo_bytes - read_b, 30, local)
+        line["roofline"]["same_size_stream"] = {
+            "what": "plain kernel reading %d B and writing %d B, median of 30, same L2 flush" % (read_b, algo_bytes - read_b),
+            "ms": floor_ms, "GBps": algo_bytes / (floor_ms * 1e-3) / 1e9, "frac_of_peak": algo_bytes / (floor_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+            "kernel_vs_stream": floor_ms / (jac_ms / args.steps)}
     if cfg4 is not None:
         line["cfg4_eval"] = cfg4
     if world == 1 and not args.no_cpu:

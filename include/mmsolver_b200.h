@@ -370,6 +370,13 @@ mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers,
 mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs,
                           const double *camera_params, int32_t direction,
                           int64_t n_points, int32_t reps, double *ms_per_pass);
+/* time (median ms over reps, CUDA events, L2 flushed before each) of a plain
+ * streaming kernel that reads read_bytes and writes write_bytes: what the memory
+ * system gives a transfer of the SIZE of one Jacobian launch (the copy figure in
+ * MEASURED_PEAKS.json is taken over 2 GiB) */
+mmb_status mmb_bench_stream_floor(int32_t device, int64_t read_bytes,
+                                  int64_t write_bytes, int32_t reps,
+                                  double *ms_median);
 /* debug: %globaltimer timeline (ns) of the critical path of the last reduced-
  * system Cholesky: [block column][0 diagonal tile, 1 tile below it][6 marks]
  * (csrc/lm_kernels.cuh g_chol_trace); count <= 768 */

@@ -112,6 +112,7 @@ SYMBOLS = [
                                            c_f64p]),
     ("mmb_bench_lens", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, C.c_int32, c_f64p]),
     ("mmb_debug_chol_trace", C.c_int32, [C.POINTER(C.c_uint64), C.c_int32]),
+    ("mmb_bench_stream_floor", C.c_int32, [C.c_int32, C.c_int64, C.c_int64, C.c_int32, c_f64p]),
     ("mmb_bench_fp64_peaks", C.c_int32, [C.c_int32, c_f64p, c_f64p]),
     ("mmb_launch_count", C.c_int64, [C.c_void_p]),
     ("mmb_solve_stats", C.c_int32, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),

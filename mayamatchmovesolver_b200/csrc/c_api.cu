@@ -461,6 +461,13 @@ mmb_status mmb_bench_fp64_peaks(int32_t device, double *dfma_tflops, double *dmm
     return measure_fp64_peaks(device, dfma_tflops, dmma_tflops);
 }
 
+mmb_status mmb_bench_stream_floor(int32_t device, int64_t read_bytes, int64_t write_bytes, int32_t reps, double *ms_median) {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return MMB_ERR_NO_DEVICE;
+    if (device < 0 || device >= ndev) return MMB_ERR_INVALID_ARGUMENT;
+    return measure_stream_floor(device, read_bytes, write_bytes, reps, ms_median);
+}
+
 static mmb_status lens_args_ok(int32_t device, int32_t model, const double *cam, int32_t direction) {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {

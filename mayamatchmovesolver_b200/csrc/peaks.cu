@@ -4,6 +4,10 @@
 //   DMMA: 8 independent mma.sync.m8n8k4.f64 accumulator pairs per warp.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+#include <string>
+#include <vector>
+
 #include "device_problem.h"
 
 namespace mmb {
@@ -67,6 +71,51 @@ mmb_status measure_fp64_peaks(int device, double *dfma_tflops, double *dmma_tflo
     cudaFree(out);
     if (dfma_tflops) *dfma_tflops = best_fma;
     if (dmma_tflops) *dmma_tflops = best_mma;
+    return MMB_OK;
+}
+
+// What a plain streaming kernel reaches at the SIZE of one Jacobian launch: reads `read_bytes`,
+// writes `write_bytes` (16-byte accesses, one wave of CTAs), L2 flushed before every repetition
+// exactly as bench.py does.  MEASURED_PEAKS.json's copy figure is taken over 2 GiB; a 96 MB
+// transfer spends a visible part of its time ramping up and draining.
+__global__ void __launch_bounds__(256) k_stream_rw(const double2 *__restrict__ in, long long nr, double2 *__restrict__ out,
+                                                   long long nw) {
+    const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x, step = (long long)gridDim.x * blockDim.x;
+    double s = 0.0;
+    for (long long i = t; i < nr; i += step) { const double2 v = in[i]; s += v.x + v.y; }
+    const double2 val = make_double2(s, 1.5);
+    for (long long i = t; i < nw; i += step) out[i] = val;
+}
+
+mmb_status measure_stream_floor(int device, long long read_bytes, long long write_bytes, int reps, double *ms_median) {
+    MMB_CUDA_CHECK(cudaSetDevice(device));
+    if (read_bytes < 0 || write_bytes <= 0 || reps < 1) return MMB_ERR_INVALID_ARGUMENT;
+    int sms = 0;
+    MMB_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const size_t flush_bytes = (size_t)256 << 20;
+    double2 *in = nullptr, *out = nullptr;
+    void *flush = nullptr;
+    MMB_CUDA_CHECK(cudaMalloc((void **)&in, (size_t)std::max<long long>(read_bytes, 16)));
+    MMB_CUDA_CHECK(cudaMalloc((void **)&out, (size_t)write_bytes));
+    MMB_CUDA_CHECK(cudaMalloc(&flush, flush_bytes));
+    MMB_CUDA_CHECK(cudaMemset(in, 0, (size_t)std::max<long long>(read_bytes, 16)));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    std::vector<float> ms(reps);
+    cudaError_t e = cudaSuccess;
+    for (int r = 0; r < reps + 2 && e == cudaSuccess; ++r) {
+        cudaMemsetAsync(flush, r, flush_bytes);
+        cudaEventRecord(e0);
+        k_stream_rw<<<sms * 8, 256>>>(in, read_bytes / 16, out, write_bytes / 16);
+        cudaEventRecord(e1);
+        e = cudaEventSynchronize(e1);
+        if (r >= 2) cudaEventElapsedTime(&ms[r - 2], e0, e1);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(in); cudaFree(out); cudaFree(flush);
+    if (e != cudaSuccess) { set_last_error(std::string("stream floor: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
+    std::sort(ms.begin(), ms.end());
+    if (ms_median) *ms_median = ms[reps / 2];
     return MMB_OK;
 }
 

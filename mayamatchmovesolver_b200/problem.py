@@ -69,6 +69,15 @@ def fp64_peaks(device=0):
     return a.value, b.value
 
 
+def stream_floor(read_bytes, write_bytes, reps=30, device=0):
+    """-> median ms of a plain streaming kernel of that size (mmb_bench_stream_floor)"""
+    lib = _capi.load()
+    ms = C.c_double()
+    check(lib.mmb_bench_stream_floor(int(device), int(read_bytes), int(write_bytes), int(reps), C.byref(ms)),
+          "mmb_bench_stream_floor")
+    return ms.value
+
+
 class Comm:
     """A communicator that outlives Problem handles (mmb_comm_create: collective over the
     ranks of `comm_id`; NCCL set-up and warm-up are paid once)."""
