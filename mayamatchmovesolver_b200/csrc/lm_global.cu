@@ -591,7 +591,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
             const size_t nt = ((size_t)d.NSP / 64) * ((size_t)d.NSP / 64);
             CKW(A.alloc(&w->tile_flags, nt));
             CKW(cudaMemsetAsync(w->tile_flags, 0, sizeof(int) * nt, p->stream));
-            CKW(cudaFuncSetAttribute(k_chol_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
+            CKW(cudaFuncSetAttribute(k_chol_tiles<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
+            CKW(cudaFuncSetAttribute(k_chol_tiles<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             const char *e = getenv("MMB_CHOL");
             w->chol_tiles = !(e && !strcmp(e, "steps"));
             const char *ei = getenv("MMB_WAVE_INV");
@@ -805,7 +806,10 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     if (prof) cudaEventRecord(w->ev[1], s);
     if (w->chol_tiles) {
-        k_chol_tiles<<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
+        if (nb > 64)
+            k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
+        else
+            k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
         LAUNCH_CHECK();
     } else {
         for (int kb = 0; kb < nb; ++kb) {

@@ -702,7 +702,11 @@ __device__ __forceinline__ unsigned long long gtimer() {
     return t;
 }
 
-__global__ void __launch_bounds__(256) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
+// MINB = 1: no register cap (176 registers, one CTA per SM) -- fastest block-column chain, for
+// systems whose factorisation is that chain (cfg3: 24 block columns); MINB = 2: 128 registers,
+// two CTAs per SM -- for large systems (cfg5: 235 block columns), which are throughput-bound.
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
                                                     const int *epoch_ctr, double *__restrict__ Dinv) {
     extern __shared__ __align__(16) double sm[];
     double *sA = sm;                 // L(i,k) during phase A; afterwards T (stride kCS)
