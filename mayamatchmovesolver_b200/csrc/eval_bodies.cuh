@@ -59,6 +59,11 @@ struct DevScene {
     const int64_t *cam_job_start;
     const int32_t *cam_thread_job, *bnd_thread_job, *lens_thread_job;  // thread -> job
     int cam_njobs; long long cam_jobs_total;
+    // block path of k_variants: one CTA per (animated, parentless camera, 32 frames)
+    const int32_t *cam_job0;             // [C] job of variant 0
+    const uint8_t *cam_blk;              // [C] camera is evaluated by the block path
+    const int32_t *vblk_cam, *vblk_fb;   // [vblk_count] camera and frame block of CTA i
+    int vblk_count, vblk_all;            // vblk_all: every camera is on the block path
     const int32_t *bnd_job_ent, *bnd_job_var, *bnd_job_attr;
     const int64_t *bnd_job_start;
     int bnd_njobs; long long bnd_jobs_total;
@@ -174,19 +179,13 @@ MMB_HD Aff world_matrix(const DevScene &s, const AttrView &av, int t) {
 //   [0..11] rows 0,1,3 of P*inv(W);  [12],[13] marker film-fit scale;
 //   [14] 1/deltaA of the perturbed parameter (variants only)
 // table layout: cam_off[c] + cam_idx(v, j, fs, f, nvar)
-MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
-    const int job = s.cam_thread_job[t];
-    const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
-    const int f = (int)(t - s.cam_job_start[job]);
+// the record of camera c, variant v, frame f from its world matrix and the camera attribute
+// values cav[0..4] = sensor w, sensor h, focal, offset x, offset y; cav[5] = camera scale
+MMB_HD void camera_variant_store(const DevScene &s, int c, int v, int f, const Aff &w, const double *cav, double inv_da) {
     const int fs = s.cam_fs[c];
-    double inv_da;
-    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
-    const Aff w = world_matrix(s, av, s.cam_tfm[c]);
-    const int32_t *ca = &s.cam_attrs[c * 8];
-    const double sw = av.get(ca[0]), sh = av.get(ca[1]);
-    const Proj p = projection_entries(av.get(ca[2]), sw, sh, av.get(ca[3]), av.get(ca[4]),
-                                      (double)s.cam_rw[c], (double)s.cam_rh[c], s.cam_fit[c],
-                                      0.1 /* dag.rs:152 */, av.get(ca[7]));
+    const double sw = cav[0], sh = cav[1];
+    const Proj p = projection_entries(cav[2], sw, sh, cav[3], cav[4], (double)s.cam_rw[c], (double)s.cam_rh[c],
+                                      s.cam_fit[c], 0.1 /* dag.rs:152 */, cav[5]);
     double out[14];
     camera_rows(w, p, out);
     marker_film_fit_scale(s.cam_fit[c], sw / sh, (double)s.cam_rw[c] / (double)s.cam_rh[c], out[12], out[13]);
@@ -196,6 +195,19 @@ MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long 
     for (int j = 0; j < 14; ++j) dst[cam_idx(v, j, fs, f, nvar)] = out[j];
     dst[cam_idx(v, 14, fs, f, nvar)] = inv_da;
 }
+
+MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
+    const int job = s.cam_thread_job[t];
+    const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];
+    const int f = (int)(t - s.cam_job_start[job]);
+    double inv_da;
+    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
+    const Aff w = world_matrix(s, av, s.cam_tfm[c]);
+    const int32_t *ca = &s.cam_attrs[c * 8];
+    const double cav[6] = {av.get(ca[0]), av.get(ca[1]), av.get(ca[2]), av.get(ca[3]), av.get(ca[4]), av.get(ca[7])};
+    camera_variant_store(s, c, v, f, w, cav, inv_da);
+}
+
 
 // One thread per (bundle, variant, frame): world position + 1/deltaA (kBndRec doubles)
 MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long t) {

@@ -16,14 +16,65 @@ const std::string &get_last_error() { return g_last_error; }
 
 // ---- kernels ---------------------------------------------------------------
 // kind 0 camera, 1 bundle, 2 lens; base_only skips perturbed variants
-__global__ void k_variants(DevScene s, const double *x, int base_only) {
+// Camera variants of 32 frames of one camera by one CTA: the 17 attribute values of the frames
+// (9 transform + 8 camera attributes) go through the attribute view ONCE into shared memory;
+// each (variant, frame) thread then takes them from there and looks up only the attribute its
+// variant perturbs.  The flat one-thread-per-job path did the 17 lookups (100 dependent, cold
+// loads and most of its 1 500 instructions) in every variant thread.
+constexpr int kVarThreads = 256;
+__device__ void camera_block_variants(const DevScene &s, const double *x, int base_only) {
+    __shared__ double vals[17][32];
+    __shared__ int refs[17], attr_of[17];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int c = s.vblk_cam[blockIdx.x], f0 = s.vblk_fb[blockIdx.x] * 32;
+    const int tfm = s.cam_tfm[c];
+    if (tid < 17) {
+        const int32_t ref = tid < 9 ? s.tfm_attrs[tfm * 9 + tid] : s.cam_attrs[c * 8 + tid - 9];
+        refs[tid] = ref;
+        attr_of[tid] = x ? (ref >= 0 ? s.stat_attr[ref] : s.anim_attr[-ref - 1]) : -1;
+    }
+    __syncthreads();
+    for (int e = tid; e < 17 * 32; e += kVarThreads) {
+        const int j = e >> 5, ff = f0 + (e & 31);
+        if (ff < s.F) {
+            AttrView b;
+            b.s = &s; b.x = x; b.f = ff; b.ovr_attr = -1; b.ovr_delta = 0.0;
+            vals[j][e & 31] = b.get(refs[j]);
+        }
+    }
+    __syncthreads();
+    const int f = f0 + lane;
+    if (f >= s.F) return;
+    const int nvar = base_only ? 1 : cam_nvar_of(s.cam_ndep[c], s.central);
+    const int job0 = s.cam_job0[c], roo = s.tfm_roo[tfm];
+    for (int v = tid >> 5; v < nvar; v += kVarThreads / 32) {
+        const int attr = s.cam_job_attr[job0 + v];
+        double inv_da;
+        const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
+        double a[17];
+#pragma unroll
+        for (int j = 0; j < 17; ++j) a[j] = (v > 0 && attr_of[j] == attr) ? av.get(refs[j]) : vals[j][lane];
+        const Aff w = local_matrix(a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], a[8], roo);
+        const double cav[6] = {a[9], a[10], a[11], a[12], a[13], a[16]};
+        camera_variant_store(s, c, v, f, w, cav, inv_da);
+    }
+}
+
+__global__ void __launch_bounds__(kVarThreads) k_variants(DevScene s, const double *x, int base_only) {
     // a dependent launch (k_jacobian_rows) may start its prologue now; it waits for this
     // grid's results with griddepcontrol.wait
     asm volatile("griddepcontrol.launch_dependents;");
-    const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if ((int)blockIdx.x < s.vblk_count) { camera_block_variants(s, x, base_only); return; }
     const long long nc = s.cam_jobs_total, nb = s.bnd_jobs_total, nl = s.lens_jobs_total;
+    // flat one-thread-per-job path (bundles, lenses, cameras the block path does not take): ONE
+    // warp per CTA -- these are long dependent chains with fewer warps than the device has
+    // schedulers; spread over all SMs they do not share a front end
+    if (threadIdx.x >= 32) return;
+    const long long t = (s.vblk_all ? nc : 0) + (blockIdx.x - s.vblk_count) * 32LL + threadIdx.x;
     if (t < nc) {
-        if (base_only && s.cam_job_var[s.cam_thread_job[t]] != 0) return;
+        const int job = s.cam_thread_job[t];
+        if (s.cam_blk[s.cam_job_ent[job]]) return;   // done by the block path
+        if (base_only && s.cam_job_var[job] != 0) return;
         camera_variant_thread(s, x, t);
     } else if (t < nc + nb) {
         const long long u = t - nc;
@@ -64,12 +115,11 @@ __global__ void __launch_bounds__(256) k_block_markers(const double *__restrict_
 static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
 mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_perturbed) {
-    const long long total = p->ds.cam_jobs_total + p->ds.bnd_jobs_total + p->ds.lens_jobs_total;
-    // one warp per CTA: the kernel is a long dependent chain per thread with fewer warps than
-    // schedulers on the device; spread over all SMs the warps do not share a front end (+3 %)
-    static int bs = 0;
-    if (!bs) { const char *e = getenv("MMB_VARIANTS_BS"); bs = e ? atoi(e) : 32; }
-    k_variants<<<blocks_for(total, bs), bs, 0, p->stream>>>(p->ds, d_x, with_perturbed ? 0 : 1);
+    const long long flat = (p->ds.vblk_all ? 0 : p->ds.cam_jobs_total) + p->ds.bnd_jobs_total + p->ds.lens_jobs_total;
+    const unsigned grid = (unsigned)p->ds.vblk_count + (flat ? blocks_for(flat, 32) : 0u);
+    if (grid == 0) return MMB_OK;
+    const unsigned bs = p->ds.vblk_count ? kVarThreads : 32;   // only the block path needs full CTAs
+    k_variants<<<grid, bs, 0, p->stream>>>(p->ds, d_x, with_perturbed ? 0 : 1);
     ++p->launches;
     MMB_CUDA_CHECK(cudaGetLastError());
     return MMB_OK;
@@ -296,6 +346,25 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     UP_L(cam_job_start, hp.cam_job_start);
     UP_I(cam_thread_job, hp.cam_thread_job); UP_I(bnd_thread_job, hp.bnd_thread_job); UP_I(lens_thread_job, hp.lens_thread_job);
     d.cam_njobs = (int)hp.cam_job_ent.size(); d.cam_jobs_total = hp.cam_jobs_total;
+    {   // block path: animated cameras whose transform has no parent
+        std::vector<int32_t> job0(hp.C, 0), vcam, vfb;
+        std::vector<uint8_t> blk(hp.C, 0);
+        for (size_t j = 0; j < hp.cam_job_ent.size(); ++j)
+            if (hp.cam_job_var[j] == 0) job0[hp.cam_job_ent[j]] = (int32_t)j;
+        const char *e = getenv("MMB_VARIANTS_BLOCK");
+        const bool enabled = !(e && atoi(e) == 0);
+        int nblk = 0;
+        for (int c = 0; c < hp.C; ++c) {
+            if (!enabled || hp.cam_fs[c] != hp.F || hp.F < 2 || hp.tfm_parent[hp.cam_tfm[c]] >= 0) continue;
+            blk[c] = 1; ++nblk;
+            for (int fb = 0; fb < (hp.F + 31) / 32; ++fb) { vcam.push_back(c); vfb.push_back(fb); }
+        }
+        d.vblk_count = (int)vcam.size();
+        d.vblk_all = nblk == hp.C;
+        if (vcam.empty()) { vcam.push_back(0); vfb.push_back(0); }
+        UP_I(cam_job0, job0); UP_I(vblk_cam, vcam); UP_I(vblk_fb, vfb);
+        CK(A.upload(&tmp_b, blk)); d.cam_blk = tmp_b;
+    }
     UP_I(bnd_job_ent, hp.bnd_job_ent); UP_I(bnd_job_var, hp.bnd_job_var); UP_I(bnd_job_attr, hp.bnd_job_attr);
     UP_L(bnd_job_start, hp.bnd_job_start);
     d.bnd_njobs = (int)hp.bnd_job_ent.size(); d.bnd_jobs_total = hp.bnd_jobs_total;
