@@ -217,11 +217,21 @@ MMB_HD void bundle_variant_thread(const DevScene &s, const double *x, long long 
     const int fs = s.bnd_fs[b];
     double inv_da;
     const AttrView av = make_view(s, x, f, attr, v, s.bnd_ndep[b], inv_da);
-    const Aff w = world_matrix(s, av, s.bnd_tfm[b]);
+    const int tfm = s.bnd_tfm[b];
+    double px, py, pz;
+    if (s.tfm_parent[tfm] < 0) {
+        // the world position of a parentless transform is its translation (T * R * S puts
+        // tx, ty, tz in the last column untouched): no rotation, no scale, three lookups
+        const int32_t *a = &s.tfm_attrs[tfm * 9];
+        px = av.get(a[0]); py = av.get(a[1]); pz = av.get(a[2]);
+    } else {
+        const Aff w = world_matrix(s, av, tfm);
+        px = w.m[3]; py = w.m[7]; pz = w.m[11];
+    }
     double *dst = s.bnd_tab + s.bnd_off[b];
-    dst[((size_t)v * kBndRec + 0) * fs + f] = w.m[3];
-    dst[((size_t)v * kBndRec + 1) * fs + f] = w.m[7];
-    dst[((size_t)v * kBndRec + 2) * fs + f] = w.m[11];
+    dst[((size_t)v * kBndRec + 0) * fs + f] = px;
+    dst[((size_t)v * kBndRec + 1) * fs + f] = py;
+    dst[((size_t)v * kBndRec + 2) * fs + f] = pz;
     dst[((size_t)v * kBndRec + 3) * fs + f] = inv_da;
 }
 
