@@ -196,6 +196,23 @@ MMB_HD void camera_variant_store(const DevScene &s, int c, int v, int f, const A
     dst[cam_idx(v, 14, fs, f, nvar)] = inv_da;
 }
 
+// Variant v of camera c at frame f when the frame's 17 attribute values (9 transform, 8 camera;
+// vals[j * stride]) have already been read through the attribute view: only the attribute the
+// variant perturbs is looked up again.  refs / attr_of: attribute-store ref and solver attribute
+// of the 17 slots.  Cameras whose transform has no parent only.
+MMB_HD void camera_variant_gathered(const DevScene &s, const double *x, int c, int v, int f, const double *vals,
+                                    int stride, const int *refs, const int *attr_of) {
+    const int attr = s.cam_job_attr[s.cam_job0[c] + v];
+    double inv_da;
+    const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
+    double a[17];
+#pragma unroll
+    for (int j = 0; j < 17; ++j) a[j] = (v > 0 && attr_of[j] == attr) ? av.get(refs[j]) : vals[j * stride];
+    const Aff w = local_matrix(a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], a[8], s.tfm_roo[s.cam_tfm[c]]);
+    const double cav[6] = {a[9], a[10], a[11], a[12], a[13], a[16]};
+    camera_variant_store(s, c, v, f, w, cav, inv_da);
+}
+
 MMB_HD void camera_variant_thread(const DevScene &s, const double *x, long long t) {
     const int job = s.cam_thread_job[t];
     const int c = s.cam_job_ent[job], v = s.cam_job_var[job], attr = s.cam_job_attr[job];

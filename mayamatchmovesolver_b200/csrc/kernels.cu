@@ -46,18 +46,8 @@ __device__ void camera_block_variants(const DevScene &s, const double *x, int ba
     const int f = f0 + lane;
     if (f >= s.F) return;
     const int nvar = base_only ? 1 : cam_nvar_of(s.cam_ndep[c], s.central);
-    const int job0 = s.cam_job0[c], roo = s.tfm_roo[tfm];
-    for (int v = tid >> 5; v < nvar; v += kVarThreads / 32) {
-        const int attr = s.cam_job_attr[job0 + v];
-        double inv_da;
-        const AttrView av = make_view(s, x, f, attr, v, s.cam_ndep[c], inv_da);
-        double a[17];
-#pragma unroll
-        for (int j = 0; j < 17; ++j) a[j] = (v > 0 && attr_of[j] == attr) ? av.get(refs[j]) : vals[j][lane];
-        const Aff w = local_matrix(a[0], a[1], a[2], a[3], a[4], a[5], a[6], a[7], a[8], roo);
-        const double cav[6] = {a[9], a[10], a[11], a[12], a[13], a[16]};
-        camera_variant_store(s, c, v, f, w, cav, inv_da);
-    }
+    for (int v = tid >> 5; v < nvar; v += kVarThreads / 32)
+        camera_variant_gathered(s, x, c, v, f, &vals[0][lane], 32, refs, attr_of);
 }
 
 __global__ void __launch_bounds__(kVarThreads) k_variants(DevScene s, const double *x, int base_only) {
