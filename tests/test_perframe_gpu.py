@@ -33,13 +33,22 @@ def oracle_per_frame(sb, **opts):
 
 
 @pytest.mark.parametrize("case", ["camera6_24x20", "camera6_weights_drop", "camera_focal_central", "camera6_lmdif",
-                                  "camera6_lmdif_maxfev"])
+                                  "camera6_lmdif_maxfev", "camera3_translate"])
 def test_per_frame_parity(case):
     opts = dict(OPTS)
     if case == "camera6_24x20":
         sb, _ = make_scene(24, 20, 5, solve_bundles=False, period=24.0)
     elif case == "camera6_weights_drop":
         sb, _ = make_scene(16, 30, 6, solve_bundles=False, weights=True, drop_fraction=0.2, period=16.0)
+    elif case == "camera3_translate":
+        # three animated attributes per frame (the other register-resident block size)
+        sb, info = make_scene(12, 20, 9, solve_camera=False, solve_bundles=False, period=12.0)
+        rng = np.random.default_rng(3)
+        for k in ("tx", "ty", "tz"):
+            ref = info["cam_tfm"][k]
+            for i in range(sb.F):
+                sb.set_value(ref, sb.get_value(ref, i) + rng.normal(0, 0.05), i)
+            sb.add_attr(ref)
     elif case.startswith("camera6_lmdif"):
         # solverType 1 = cminpack_lmdif: relative forward steps, 6 function calls per Jacobian
         # count towards `iterations` (maxfev); the second case stops on it (reason 5)
