@@ -54,8 +54,8 @@ struct DeviceArena {
         *out = (T *)p;
         return cudaSuccess;
     }
-    template <typename T>
-    cudaError_t upload(T **out, const std::vector<T> &v) {
+    template <typename T, typename Al>
+    cudaError_t upload(T **out, const std::vector<T, Al> &v) {
         cudaError_t e = alloc(out, v.size());
         if (e != cudaSuccess) return e;
         if (!v.empty()) e = cudaMemcpyAsync(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, stream);

@@ -9,6 +9,7 @@
 #include "problem.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -203,31 +204,32 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         // order (marker-major, frame-minor) is the reference's.
         const size_t M = (size_t)hp.M;
         const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-        const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)16, (M * F) / 65536 + 1}));
+        const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)8, (M * F) / 65536 + 1}));
         std::vector<size_t> count(T + 1, 0);
         std::vector<std::vector<double>> twmax(T, std::vector<double>(F, 0.0));
         std::vector<std::vector<uint8_t>> tseen(T, std::vector<uint8_t>(F, 0));
         auto range = [&](int t, size_t *m0, size_t *m1) { *m0 = M * t / T; *m1 = M * (t + 1) / T; };
         auto enabled = [&](size_t o) { return s->mkr_enable[o] != 0 && (s->mkr_weight[o] > 0.0); };
-        auto run = [&](const std::function<void(int)> &fn) {
-            std::vector<std::thread> th;
-            for (int t = 1; t < T; ++t) th.emplace_back(fn, t);
-            fn(0);
-            for (auto &x : th) x.join();
-        };
-        run([&](int t) {
+        // one set of threads for both passes: count, meet, (thread 0: prefix sums and the
+        // uninitialised resize), meet, fill
+        std::atomic<int> arrived{0}, released{0};
+        auto body = [&](int t) {
             size_t m0, m1, k = 0;
             range(t, &m0, &m1);
             for (size_t o = m0 * F; o < m1 * F; ++o) k += enabled(o) ? 1 : 0;
             count[t + 1] = k;
-        });
-        for (int t = 0; t < T; ++t) count[t + 1] += count[t];
-        const size_t total = count[T];
-        hp.err_marker.resize(total); hp.err_frame.resize(total);
-        hp.obs_mx.resize(total); hp.obs_my.resize(total); hp.obs_w.resize(total);
-        run([&](int t) {
-            size_t m0, m1, k = count[t];
-            range(t, &m0, &m1);
+            arrived.fetch_add(1, std::memory_order_acq_rel);
+            if (t == 0) {
+                while (arrived.load(std::memory_order_acquire) < T) std::this_thread::yield();
+                for (int u = 0; u < T; ++u) count[u + 1] += count[u];
+                const size_t total = count[T];
+                hp.err_marker.resize(total); hp.err_frame.resize(total);
+                hp.obs_mx.resize(total); hp.obs_my.resize(total); hp.obs_w.resize(total);
+                released.store(1, std::memory_order_release);
+            } else {
+                while (!released.load(std::memory_order_acquire)) std::this_thread::yield();
+            }
+            k = count[t];
             std::vector<double> &wm = twmax[t];
             std::vector<uint8_t> &ws = tseen[t];
             for (size_t i = m0; i < m1; ++i) {
@@ -246,7 +248,13 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
                     ws[j] = 1;
                 }
             }
-        });
+        };
+        {
+            std::vector<std::thread> th;
+            for (int t = 1; t < T; ++t) th.emplace_back(body, t);
+            body(0);
+            for (auto &x : th) x.join();
+        }
         for (int t = 0; t < T; ++t)
             for (size_t j = 0; j < F; ++j)
                 if (tseen[t][j] && (!wseen[j] || twmax[t][j] > wmax[j])) { wmax[j] = twmax[t][j]; wseen[j] = 1; }

@@ -15,6 +15,8 @@
 #pragma once
 #include <cstdint>
 #include <string>
+#include <memory>
+#include <utility>
 #include <vector>
 
 #include "../../include/mmsolver_b200.h"
@@ -22,6 +24,21 @@
 namespace mmb {
 
 // per-marker plan entry: column c of marker m
+// std::vector whose resize() leaves new elements uninitialised: the per-observation arrays
+// (5e5 .. 5e7 entries) are filled right after the resize by several threads, a zero fill by
+// one thread first would only take the page faults serially.
+template <class T>
+struct NoInitAlloc : std::allocator<T> {
+    template <class U> struct rebind { using other = NoInitAlloc<U>; };
+    NoInitAlloc() = default;
+    template <class U> NoInitAlloc(const NoInitAlloc<U> &) {}
+    template <class U, class... Args> void construct(U *ptr, Args &&...args) {
+        if constexpr (sizeof...(Args) == 0) ::new ((void *)ptr) U;
+        else ::new ((void *)ptr) U(std::forward<Args>(args)...);
+    }
+};
+template <class T> using RawVec = std::vector<T, NoInitAlloc<T>>;
+
 struct PlanEntry {
     int32_t attr;      // solver attribute index (or -1 unused)
     int16_t cam_var;   // 0 = base, else 1-based index into camera dep list
@@ -47,8 +64,8 @@ struct HostProblem {
 
     // ---- index maps (adjust_relationships.cpp) --------------------------
     int n = 0, nobs = 0, m = 0;
-    std::vector<int32_t> err_marker, err_frame;   // errorToMarkerList
-    std::vector<double> obs_mx, obs_my, obs_w;    // markerPosList / weights
+    RawVec<int32_t> err_marker, err_frame;   // errorToMarkerList
+    RawVec<double> obs_mx, obs_my, obs_w;    // markerPosList / weights
     std::vector<int32_t> par_attr, par_frame;     // paramToAttrList
     std::vector<int32_t> attr_param_base;         // first param of attr a
     std::vector<uint8_t> attr_anim;               // attr expands per frame
