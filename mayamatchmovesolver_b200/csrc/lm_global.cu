@@ -776,7 +776,10 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     if (prof) cudaEventRecord(w->ev[0], s);
     if (d.KE) {
         const size_t sm = sizeof(double) * ((size_t)d.na * d.na + d.na);
-        k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
+        if (d.na == 6)
+            k_block_factor_fixed<6><<<d.F, 128, 0, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
+        else
+            k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
         LAUNCH_CHECK();
     }
     {
@@ -823,7 +826,8 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     if (prof) cudaEventRecord(w->ev[2], s);
     if ((rs = enqueue_backward_s(p, w->p_int + d.KE)) != MMB_OK) return rs;
     if (d.KE) {
-        k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
+        if (d.na == 6) k_backsolve_e_fixed<6><<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
+        else k_backsolve_e<<<d.F, 128, 0, s>>>(d, w->Lf, w->Y, w->p_int);
         LAUNCH_CHECK();
     }
     if (prof) cudaEventRecord(w->ev[3], s);

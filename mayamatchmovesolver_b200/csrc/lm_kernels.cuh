@@ -241,6 +241,75 @@ __global__ void __launch_bounds__(256) k_jp_partial(DevScene s, LmDims d, const 
 // ---- per-frame block factorisation ---------------------------------------------
 // One CTA per frame:  L_f = chol(U_f + par D_f^2);  Y_f = L_f^-1 W_f ;
 // z_f = L_f^-1 g_f stored in the augmented column ns of Y.
+// The same for a compile-time block size (a camera: NA = 6): every thread factors the block in
+// registers (no barriers, reciprocal pivots), then streams its columns of W through the forward
+// substitution -- the kernel is then the HBM stream W -> Y it should be.
+template <int NA>
+__global__ void __launch_bounds__(128) k_block_factor_fixed(LmDims d, LmState *st, const double *__restrict__ U,
+                                                            const double *__restrict__ gE, const double *__restrict__ W,
+                                                            const double *__restrict__ diag, const int32_t *__restrict__ i2p,
+                                                            double *__restrict__ Lf, double *__restrict__ Y) {
+    const int f = blockIdx.x;
+    const double par = st->par_cur;
+    double L[NA][NA], inv[NA], z[NA];
+#pragma unroll
+    for (int r = 0; r < NA; ++r) {
+#pragma unroll
+        for (int c = 0; c <= r; ++c) L[r][c] = U[((size_t)f * NA + r) * NA + c];
+        const double dd = diag[i2p[f * NA + r]];
+        L[r][r] += par * dd * dd;
+        z[r] = gE[(size_t)f * NA + r];
+    }
+    int fail = 0;
+#pragma unroll
+    for (int j = 0; j < NA; ++j) {
+        double pv = L[j][j];
+        if (!(pv > 0.0)) { fail = 1; pv = 1.0; }
+        else pv = sqrt(pv);
+        L[j][j] = pv;
+        inv[j] = 1.0 / pv;
+#pragma unroll
+        for (int r = j + 1; r < NA; ++r) L[r][j] *= inv[j];
+#pragma unroll
+        for (int c = j + 1; c < NA; ++c)
+#pragma unroll
+            for (int r = c; r < NA; ++r) L[r][c] -= L[r][j] * L[c][j];
+    }
+#pragma unroll
+    for (int r = 0; r < NA; ++r) {
+        double v = z[r];
+#pragma unroll
+        for (int c = 0; c < r; ++c) v -= L[r][c] * z[c];
+        z[r] = v * inv[r];
+    }
+    if (threadIdx.x == 0) {
+        if (fail) atomicExch(&st->chol_fail, 1);
+#pragma unroll
+        for (int r = 0; r < NA; ++r)
+#pragma unroll
+            for (int c = 0; c < NA; ++c) Lf[(size_t)f * NA * NA + r * NA + c] = c <= r ? L[r][c] : 0.0;
+    }
+    for (int j = threadIdx.x; j < d.NSP; j += blockDim.x) {
+        double y[NA];
+        if (j < d.ns) {
+#pragma unroll
+            for (int r = 0; r < NA; ++r) y[r] = W[((size_t)f * NA + r) * d.NSP + j];
+#pragma unroll
+            for (int r = 0; r < NA; ++r) {
+                double v = y[r];
+#pragma unroll
+                for (int c = 0; c < r; ++c) v -= L[r][c] * y[c];
+                y[r] = v * inv[r];
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < NA; ++r) y[r] = (j == d.ns) ? z[r] : 0.0;
+        }
+#pragma unroll
+        for (int r = 0; r < NA; ++r) Y[((size_t)f * NA + r) * d.NSP + j] = y[r];
+    }
+}
+
 __global__ void __launch_bounds__(128) k_block_factor(LmDims d, LmState *st, const double *__restrict__ U,
                                                       const double *__restrict__ gE, const double *__restrict__ W,
                                                       const double *__restrict__ diag, const int32_t *__restrict__ i2p,
@@ -1307,6 +1376,47 @@ constexpr size_t kWaveSmemFwd = sizeof(double) * (64 * kDS + 64 * 3);
 
 // ---- eliminated-side back substitution -------------------------------------------------
 // p_f = L_f^-T (z_f - Y_f p_S); CTA per frame.  p_int = [p_E (KE) | p_S (ns)]
+// compile-time block size: the NA dot products of a frame in ONE pass over its rows of Y
+// (all loads in flight together, one reduction stage) instead of NA passes with a block
+// reduction each
+template <int NA>
+__global__ void __launch_bounds__(128) k_backsolve_e_fixed(LmDims d, const double *__restrict__ Lf,
+                                                           const double *__restrict__ Y, double *__restrict__ p_int) {
+    __shared__ double part[4][NA];
+    const int f = blockIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const double *pS = p_int + d.KE;
+    const double *yr = Y + (size_t)f * NA * d.NSP;
+    double acc[NA];
+#pragma unroll
+    for (int a = 0; a < NA; ++a) acc[a] = 0.0;
+    for (int j = threadIdx.x; j < d.ns; j += blockDim.x) {
+        const double pj = pS[j];
+#pragma unroll
+        for (int a = 0; a < NA; ++a) acc[a] = fma(yr[(size_t)a * d.NSP + j], pj, acc[a]);
+    }
+#pragma unroll
+    for (int a = 0; a < NA; ++a) {
+        const double v = warp_sum(acc[a]);
+        if (lane == 0) part[w][a] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double r[NA];
+#pragma unroll
+        for (int a = 0; a < NA; ++a) r[a] = yr[(size_t)a * d.NSP + d.ns] - ((part[0][a] + part[1][a]) + (part[2][a] + part[3][a]));
+        const double *L = Lf + (size_t)f * NA * NA;
+#pragma unroll
+        for (int a = NA - 1; a >= 0; --a) {
+            double v = r[a];
+#pragma unroll
+            for (int c = a + 1; c < NA; ++c) v -= L[c * NA + a] * r[c];
+            r[a] = v / L[a * NA + a];
+        }
+#pragma unroll
+        for (int a = 0; a < NA; ++a) p_int[(size_t)f * NA + a] = r[a];
+    }
+}
+
 __global__ void __launch_bounds__(128) k_backsolve_e(LmDims d, const double *__restrict__ Lf,
                                                      const double *__restrict__ Y, double *__restrict__ p_int) {
     __shared__ double sh[32];
