@@ -366,6 +366,26 @@ mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers,
                                   const double *camera_params,
                                   int32_t direction, int64_t n_points,
                                   const double *xy_in, double *xy_out);
+/* mmb_lens_apply_layered for callers that must not allocate device memory
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernel, same results; the layer table
+ * and the staging of the points live in one static __device__ array of
+ * 4096 + 2 * MMB_LENS_NO_ALLOC_MAX_POINTS * 16 bytes (8 MiB) that every GPU
+ * which loads the library holds until exit.  n_points above
+ * MMB_LENS_NO_ALLOC_MAX_POINTS is refused (MMB_ERR_INVALID_ARGUMENT, message in
+ * mmb_last_error).  Calls no cudaMalloc / cudaFree / allocating routine: blocking
+ * copies and one launch on the legacy default stream.  All calls share the
+ * array, which keeps the previous call's contents (nothing in it needs to start
+ * at zero); calls that overlap on one GPU -- from several host threads or
+ * processes sharing a context -- race on it: serialise them. */
+#define MMB_LENS_NO_ALLOC_MAX_POINTS 262144
+mmb_status mmb_lens_apply_layered_no_alloc(int32_t device, int32_t n_layers,
+                                           const int32_t *models,
+                                           const double *coeffs,
+                                           const double *camera_params,
+                                           int32_t direction, int64_t n_points,
+                                           const double *xy_in, double *xy_out);
 /* the same kernel timed on a device-resident grid of n_points (CUDA events) */
 mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs,
                           const double *camera_params, int32_t direction,

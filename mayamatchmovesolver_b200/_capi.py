@@ -110,6 +110,8 @@ SYMBOLS = [
     ("mmb_lens_apply", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, c_f64p, c_f64p]),
     ("mmb_lens_apply_layered", C.c_int32, [C.c_int32, C.c_int32, c_i32p, c_f64p, c_f64p, C.c_int32, C.c_int64, c_f64p,
                                            c_f64p]),
+    ("mmb_lens_apply_layered_no_alloc", C.c_int32, [C.c_int32, C.c_int32, c_i32p, c_f64p, c_f64p, C.c_int32, C.c_int64,
+                                                    c_f64p, c_f64p]),
     ("mmb_bench_lens", C.c_int32, [C.c_int32, C.c_int32, c_f64p, c_f64p, C.c_int32, C.c_int64, C.c_int32, c_f64p]),
     ("mmb_debug_chol_trace", C.c_int32, [C.POINTER(C.c_uint64), C.c_int32]),
     ("mmb_bench_stream_floor", C.c_int32, [C.c_int32, C.c_int64, C.c_int64, C.c_int32, c_f64p]),

@@ -499,6 +499,19 @@ mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers, const int32_
     return lens_apply_layered_host(device, n_layers, models, coeffs, camera_params, direction, n_points, xy_in, xy_out);
 }
 
+mmb_status mmb_lens_apply_layered_no_alloc(int32_t device, int32_t n_layers, const int32_t *models, const double *coeffs,
+                                           const double *camera_params, int32_t direction, int64_t n_points,
+                                           const double *xy_in, double *xy_out) {
+    if (!models || n_layers < 1) return MMB_ERR_INVALID_ARGUMENT;
+    for (int k = 0; k < n_layers; ++k) {
+        mmb_status st = lens_args_ok(device, models[k], camera_params, direction);
+        if (st != MMB_OK) return st;
+    }
+    if (n_points < 0 || (n_points > 0 && (!xy_in || !xy_out))) return MMB_ERR_INVALID_ARGUMENT;
+    return lens_apply_layered_no_alloc_host(device, n_layers, models, coeffs, camera_params, direction, n_points, xy_in,
+                                            xy_out);
+}
+
 mmb_status mmb_bench_lens(int32_t device, int32_t model, const double *coeffs, const double *camera_params,
                           int32_t direction, int64_t n_points, int32_t reps, double *ms_per_pass) {
     mmb_status st = lens_args_ok(device, model, camera_params, direction);

@@ -105,6 +105,9 @@ mmb_status lens_apply_host(int device, int model, const double *coeffs, const do
 mmb_status lens_apply_layered_host(int device, int n_layers, const int32_t *models, const double *coeffs,
                                    const double *cams, int direction, long long n, const double *xy_in, double *xy_out);
 mmb_status measure_stream_floor(int device, long long read_bytes, long long write_bytes, int reps, double *ms_median);
+mmb_status lens_apply_layered_no_alloc_host(int device, int n_layers, const int32_t *models, const double *coeffs,
+                                            const double *cams, int direction, long long n, const double *xy_in,
+                                            double *xy_out);
 mmb_status lens_bench(int device, int model, const double *coeffs, const double *cam, int direction, long long n,
                       int reps, double *ms_per_pass);
 

@@ -8,6 +8,8 @@
 // this kernel cannot drift apart.
 #include <algorithm>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include "device_problem.h"
 
@@ -173,6 +175,78 @@ mmb_status lens_apply_layered_host(int device, int n_layers, const int32_t *mode
     cudaStreamDestroy(s);
     if (e == cudaSuccess) e = e2;
     if (e != cudaSuccess) { set_last_error(std::string("lens_apply_layered: ") + cudaGetErrorString(e)); return MMB_ERR_CUDA; }
+    return MMB_OK;
+}
+
+// ---- the layered kernel for callers that cannot allocate -------------------------------------
+// mmb_lens_apply_layered_no_alloc: same kernel, same host buffers in and out, but every byte of
+// device memory it needs -- the layer table the kernel reads and the staging of the points --
+// lives in ONE file-scope array instead of cudaMallocAsync'd buffers.  Every GPU that loads the
+// library holds these 8 MiB until exit.  All calls share the array and it keeps the last call's
+// contents: nothing in it has to start at zero (the layer table is rewritten whole, only the
+// first n points of either staging area are read), but two calls that overlap on one GPU race.
+constexpr long long kNoAllocMaxPoints = MMB_LENS_NO_ALLOC_MAX_POINTS;
+constexpr size_t kNoAllocHeader = 4096;   // LensLayers
+constexpr size_t kNoAllocBytes = kNoAllocHeader + 2 * (size_t)kNoAllocMaxPoints * sizeof(double2);
+static_assert(sizeof(LensLayers) <= kNoAllocHeader, "layer table must fit the scratch header");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocBytes];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address is
+// asked for once per device, with that device current, and cached.
+static mmb_status noalloc_scratch_ptr(int device, unsigned char **out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static unsigned char *ptrs[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) {
+        set_last_error("lens_apply_layered_no_alloc: device ordinal out of range");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            set_last_error(std::string("lens_apply_layered_no_alloc: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            return MMB_ERR_CUDA;
+        }
+        ptrs[device] = static_cast<unsigned char *>(p);
+    }
+    *out = ptrs[device];
+    return MMB_OK;
+}
+
+mmb_status lens_apply_layered_no_alloc_host(int device, int n_layers, const int32_t *models, const double *coeffs,
+                                            const double *cams, int direction, long long n, const double *xy_in,
+                                            double *xy_out) {
+    if (n_layers < 1 || n_layers > kLensMaxLayers) {
+        set_last_error("lens_apply_layered_no_alloc: 1..8 layers");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    if (n > kNoAllocMaxPoints) {
+        set_last_error("lens_apply_layered_no_alloc: n_points = " + std::to_string(n) + " exceeds the fixed scratch of " +
+                       std::to_string(kNoAllocMaxPoints) + " points (MMB_LENS_NO_ALLOC_MAX_POINTS); split the buffer or "
+                       "use mmb_lens_apply_layered");
+        return MMB_ERR_INVALID_ARGUMENT;
+    }
+    MMB_CUDA_CHECK(cudaSetDevice(device));
+    unsigned char *base = nullptr;
+    const mmb_status st = noalloc_scratch_ptr(device, &base);
+    if (st != MMB_OK) return st;
+    if (n == 0) return MMB_OK;
+    LensLayers LL;
+    std::memset(&LL, 0, sizeof(LL));
+    LL.n = n_layers;
+    for (int k = 0; k < n_layers; ++k)
+        make_bulk(models[k], coeffs ? coeffs + (size_t)MMB_LENS_MAX_COEFFS * k : nullptr, cams + 6 * (size_t)k, &LL.layer[k]);
+    LensLayers *d_ll = reinterpret_cast<LensLayers *>(base);
+    double2 *d_in = reinterpret_cast<double2 *>(base + kNoAllocHeader);
+    double2 *d_out = d_in + kNoAllocMaxPoints;
+    // legacy default stream, blocking copies: no stream, event or buffer is created here
+    MMB_CUDA_CHECK(cudaMemcpy(d_ll, &LL, sizeof(LL), cudaMemcpyHostToDevice));
+    MMB_CUDA_CHECK(cudaMemcpy(d_in, xy_in, sizeof(double2) * (size_t)n, cudaMemcpyHostToDevice));
+    k_lens_bulk_layered<<<grid_for(n * kLensUnroll, device), 256>>>(d_ll, direction, n, d_in, d_out);
+    MMB_CUDA_CHECK(cudaGetLastError());
+    MMB_CUDA_CHECK(cudaMemcpy(xy_out, d_out, sizeof(double2) * (size_t)n, cudaMemcpyDeviceToHost));
     return MMB_OK;
 }
 

@@ -49,7 +49,10 @@ def apply(model, coeffs, points, direction=DISTORT, camera_params=DEFAULT_CAMERA
     return out
 
 
-def apply_layered(layers, points, direction=DISTORT, device=0):
+NO_ALLOC_MAX_POINTS = 262144   # MMB_LENS_NO_ALLOC_MAX_POINTS
+
+
+def apply_layered(layers, points, direction=DISTORT, device=0, no_alloc=False):
     """layers: [(model, coeffs, camera_params), ...] innermost first (a lens-node chain)"""
     lib = _capi.load()
     models = np.zeros(len(layers), np.int32)
@@ -60,9 +63,13 @@ def apply_layered(layers, points, direction=DISTORT, device=0):
         cams[k] = cam
     pts = np.ascontiguousarray(points, dtype=np.float64)
     out = np.empty_like(pts)
-    check(lib.mmb_lens_apply_layered(int(device), len(layers), models.ctypes.data_as(c_i32p), co.ctypes.data_as(c_f64p),
-                                     cams.ctypes.data_as(c_f64p), int(direction), pts.size // 2,
-                                     pts.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p)), "mmb_lens_apply_layered")
+    # no_alloc: the entry point that uses the library's static device scratch (at most
+    # NO_ALLOC_MAX_POINTS points, calls must not overlap on one GPU)
+    fn = lib.mmb_lens_apply_layered_no_alloc if no_alloc else lib.mmb_lens_apply_layered
+    check(fn(int(device), len(layers), models.ctypes.data_as(c_i32p), co.ctypes.data_as(c_f64p),
+             cams.ctypes.data_as(c_f64p), int(direction), pts.size // 2,
+             pts.ctypes.data_as(c_f64p), out.ctypes.data_as(c_f64p)),
+          "mmb_lens_apply_layered_no_alloc" if no_alloc else "mmb_lens_apply_layered")
     return out
 
 
