@@ -81,6 +81,7 @@ struct DeviceProblem {
     double *d_stat0 = nullptr, *d_anim0 = nullptr;  // pristine attribute store
     double *d_flush = nullptr;  // L2 flush scratch (bench only)
     bool tiled_ok = false;      // register-tiled Jacobian kernel applies
+    bool lens_tile_ok = false;  // lens-in-the-loop tiled kernel applies (k_jacobian_lens)
     TiledPlan tiled{};
     int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
