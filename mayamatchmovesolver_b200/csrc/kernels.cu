@@ -101,79 +101,106 @@ __global__ void __launch_bounds__(256) k_jacobian(DevScene s, double *fvec, doub
 // Needs: dense grid, one animated camera (block layout), static lens and bundles, forward
 // differences.
 constexpr int kLensTileMaxEval = 24;
-template <int MAXE, int MINB>
+constexpr int kLensTileMB = 4;   // markers per barrier round
+// GENERAL = false: one camera (index 0) with a lens, staged once; true: the camera (and lens, if
+// any) of the current marker, restaged when it changes (markers of one camera are normally
+// consecutive).
+template <int MAXE, int MINB, bool GENERAL>
 __global__ void __launch_bounds__(32 * MAXE, MINB) k_jacobian_lens(DevScene s, int mt, double *fvec, double *dist,
-                                                                   double *jac, int32_t *cols, double *dist_last) {
+                                                                   double *jac, int32_t *cols, double *dist_last,
+                                                                   int nv_max, int nvl_max) {
     extern __shared__ __align__(16) double lsm[];
-    const int cam = 0, lens = s.cam_lens[0];
-    const int nv = cam_nvar_of(s.cam_ndep[cam], 0), nvl = 1 + s.lens_ndep[lens];
     const int NE = blockDim.x >> 5, tid = threadIdx.x, lane = tid & 31, e = tid >> 5;
     double *scam = lsm;                                            // [nv][8 row pairs][32 frames][2]
-    double *slens = scam + (size_t)nv * 512;                       // [nvl][24]
-    double2 *sres = reinterpret_cast<double2 *>(slens + ((nvl * kLensRec + 1) & ~1));   // [NE][32]
-    double *sd = reinterpret_cast<double *>(sres + NE * 32);       // [NE][32]
-    {
-        const double *src = s.cam_tab + s.cam_off[cam] + (size_t)blockIdx.x * nv * 512;
-        for (int t = tid; t < nv * 512; t += blockDim.x) scam[t] = src[t];
-        const double *ls = s.lens_tab + s.lens_off[lens];
-        for (int t = tid; t < nvl * kLensRec; t += blockDim.x) slens[t] = ls[t];
-    }
-    __syncthreads();
+    double *slens = scam + (size_t)nv_max * 512;                   // [nvl][24]
+    double2 *sres = reinterpret_cast<double2 *>(slens + ((nvl_max * kLensRec + 1) & ~1));   // [MB][NE][32]
+    double *sd = reinterpret_cast<double *>(sres + kLensTileMB * NE * 32);                  // [MB][NE][32]
+    int cam = -1, lens = -1;
     const int f = blockIdx.x * 32 + lane;
     const bool live = f < s.F;
     const int m0 = blockIdx.y * mt, m1 = min(s.M, m0 + mt);
     const size_t m = 2 * (size_t)s.nobs;
     const double2 *scam2 = reinterpret_cast<const double2 *>(scam);
-    for (int mk = m0; mk < m1; ++mk) {
-        const int k = s.mkr_k[mk];
-        const PlanEntryD *pl = s.plan + (size_t)mk * s.kmax;
-        const size_t i = (size_t)mk * s.F + (live ? f : 0);
-        double ex = 0.0, ey = 0.0, d = 0.0;
-        if (live && e <= k) {
-            int cv = 0, bv = 0, lv = 0;
-            if (e > 0) { const PlanEntryD en = pl[e - 1]; cv = en.cam_var; bv = en.bnd_var; lv = en.lens_var; }
-            double cm[14], bp[3];
+    for (int mk0 = m0; mk0 < m1;) {
+        const int want = GENERAL ? s.mkr_cam[mk0] : 0;
+        if (want != cam) {
+            __syncthreads();
+            cam = want;
+            const int l = s.cam_lens[cam];
+            lens = (l >= 0 && s.lens_model[l] != 0) ? l : -1;
+            const int nv = cam_nvar_of(s.cam_ndep[cam], 0);
+            const double *src = s.cam_tab + s.cam_off[cam] + (size_t)blockIdx.x * nv * 512;
+            for (int t = tid; t < nv * 512; t += blockDim.x) scam[t] = src[t];
+            if (lens >= 0) {
+                const int nvl = 1 + s.lens_ndep[lens];
+                const double *ls = s.lens_tab + s.lens_off[lens];
+                for (int t = tid; t < nvl * kLensRec; t += blockDim.x) slens[t] = ls[t];
+            }
+            __syncthreads();
+        }
+        int nb = min(kLensTileMB, m1 - mk0);
+        if (GENERAL)
+            for (int u = 1; u < nb; ++u)
+                if (s.mkr_cam[mk0 + u] != cam) { nb = u; break; }
+        // ---- evaluations of nb markers ----
+        for (int u = 0; u < nb; ++u) {
+            const int mk = mk0 + u, k = s.mkr_k[mk];
+            double ex = 0.0, ey = 0.0, d = 0.0;
+            if (live && e <= k) {
+                int cv = 0, bv = 0, lv = 0;
+                if (e > 0) { const PlanEntryD en = s.plan[(size_t)mk * s.kmax + e - 1]; cv = en.cam_var; bv = en.bnd_var; lv = en.lens_var; }
+                double cm[14], bp[3];
 #pragma unroll
-            for (int jp = 0; jp < 7; ++jp) { const double2 t = scam2[(cv * 8 + jp) * 32 + lane]; cm[2 * jp] = t.x; cm[2 * jp + 1] = t.y; }
-            const double *bsrc = s.bnd_tab + s.bnd_off[s.mkr_bnd[mk]] + (size_t)bv * kBndRec;
-            bp[0] = bsrc[0]; bp[1] = bsrc[1]; bp[2] = bsrc[2];
-            ObsCtx o;
-            o.marker = mk; o.frame = f; o.cam = cam; o.bnd = s.mkr_bnd[mk]; o.lens = lens; o.lens_frame = f;
-            o.mx = s.obs_mx[i]; o.my = s.obs_my[i]; o.w = sqrt(s.obs_w[i]);
-            residual_from(s, o, cm, bp, slens + lv * kLensRec, ex, ey, d);
+                for (int jp = 0; jp < 7; ++jp) { const double2 t = scam2[(cv * 8 + jp) * 32 + lane]; cm[2 * jp] = t.x; cm[2 * jp + 1] = t.y; }
+                const int b = s.mkr_bnd[mk];
+                const double *bsrc = s.bnd_tab + s.bnd_off[b] + (size_t)bv * kBndRec;
+                bp[0] = bsrc[0]; bp[1] = bsrc[1]; bp[2] = bsrc[2];
+                const size_t i = (size_t)mk * s.F + f;
+                ObsCtx o;
+                o.marker = mk; o.frame = f; o.cam = cam; o.bnd = b; o.lens = lens; o.lens_frame = f;
+                o.mx = s.obs_mx[i]; o.my = s.obs_my[i]; o.w = sqrt(s.obs_w[i]);
+                const double *rec = GENERAL ? (lens >= 0 ? slens + lv * kLensRec : nullptr) : slens + lv * kLensRec;
+                residual_from(s, o, cm, bp, rec, ex, ey, d);
+            }
+            sres[(u * NE + e) * 32 + lane] = make_double2(ex, ey);
+            sd[(u * NE + e) * 32 + lane] = d;
         }
-        sres[e * 32 + lane] = make_double2(ex, ey);
-        sd[e * 32 + lane] = d;
         __syncthreads();
+        // ---- quotients and stores: warp 0 the base outputs, warp e > 0 column e - 1 ----
         if (live) {
-            if (e == 0) {
-                if (fvec) { fvec[2 * i] = ex; fvec[2 * i + 1] = ey; }
-                if (dist) dist[i] = d;
-                if (dist_last) {
-                    double dl = d;
-                    for (int c = 0; c < k; ++c) if (pl[c].attr == s.A - 1) dl = sd[(c + 1) * 32 + lane];
-                    dist_last[i] = dl;
+            for (int u = 0; u < nb; ++u) {
+                const int mk = mk0 + u, k = s.mkr_k[mk];
+                const PlanEntryD *pl = s.plan + (size_t)mk * s.kmax;
+                const size_t i = (size_t)mk * s.F + f;
+                const double2 base = sres[(u * NE) * 32 + lane];
+                if (e == 0) {
+                    const double d = sd[(u * NE) * 32 + lane];
+                    if (fvec) { fvec[2 * i] = base.x; fvec[2 * i + 1] = base.y; }
+                    if (dist) dist[i] = d;
+                    if (dist_last) {
+                        double dl = d;
+                        for (int c = 0; c < k; ++c) if (pl[c].attr == s.A - 1) dl = sd[(u * NE + c + 1) * 32 + lane];
+                        dist_last[i] = dl;
+                    }
+                } else if (e - 1 < s.kmax) {
+                    const int c = e - 1;
+                    double jx = 0.0, jy = 0.0;
+                    int32_t pid = -1;
+                    if (c < k) {
+                        const int attr = pl[c].attr;
+                        pid = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
+                        const double inv_delta = 1.0 / s.par_delta_a[pid];
+                        const double2 a = sres[(u * NE + e) * 32 + lane];
+                        jx = (a.x - base.x) * inv_delta;
+                        jy = (a.y - base.y) * inv_delta;
+                    }
+                    *reinterpret_cast<double2 *>(&jac[(size_t)c * m + 2 * i]) = make_double2(jx, jy);
+                    if (cols) cols[i * s.kmax + c] = pid;
                 }
-            }
-            // columns: warp e > 0 owns column e - 1; columns beyond the warps (kmax > NE - 1
-            // cannot happen: NE = kmax + 1)
-            if (e > 0 && e - 1 < s.kmax) {
-                const int c = e - 1;
-                double jx = 0.0, jy = 0.0;
-                int32_t pid = -1;
-                if (c < k) {
-                    const int attr = pl[c].attr;
-                    pid = s.attr_param_base[attr] + (s.attr_anim[attr] ? f : 0);
-                    const double inv_delta = 1.0 / s.par_delta_a[pid];
-                    const double2 b = sres[lane];
-                    jx = (ex - b.x) * inv_delta;
-                    jy = (ey - b.y) * inv_delta;
-                }
-                *reinterpret_cast<double2 *>(&jac[(size_t)c * m + 2 * i]) = make_double2(jx, jy);
-                if (cols) cols[i * s.kmax + c] = pid;
             }
         }
         __syncthreads();
+        mk0 += nb;
     }
 }
 
@@ -302,17 +329,25 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
     }
     if (p->lens_tile_ok && lens_tile_mode) {
         const HostProblem &hp = p->hp;
-        const int l = hp.cam_lens[0];
-        const int nv = 1 + (int)hp.cam_deps[0].size(), nvl = 1 + (int)hp.lens_deps[l].size(), NE = hp.kmax + 1;
-        const size_t smem = sizeof(double) * ((size_t)nv * 512 + ((nvl * kLensRec + 1) & ~1) + (size_t)NE * 32 * 3);
+        int nv = 1, nvl = 1;
+        for (int c = 0; c < hp.C; ++c) {
+            nv = std::max(nv, 1 + (int)hp.cam_deps[c].size());
+            const int l = hp.cam_lens[c];
+            if (l >= 0) nvl = std::max(nvl, 1 + (int)hp.lens_deps[l].size());
+        }
+        const int NE = hp.kmax + 1;
+        const size_t smem = sizeof(double) * ((size_t)nv * 512 + ((nvl * kLensRec + 1) & ~1) + (size_t)kLensTileMB * NE * 32 * 3);
         // up to 18 evaluations: 56 registers, two CTAs per SM; more: one CTA of up to 24 warps
         static int small_mode = -1;
         if (small_mode < 0) { const char *e = getenv("MMB_LENS_TILE_SMALL"); small_mode = e ? atoi(e) : 1; }
-        auto kern = (NE <= 18 && small_mode) ? k_jacobian_lens<18, 2> : k_jacobian_lens<kLensTileMaxEval, 1>;
+        const bool general = !(hp.C == 1 && hp.cam_lens[0] >= 0 && hp.lens_model[hp.cam_lens[0]] != 0);
+        auto kern = (NE <= 18 && small_mode)
+                        ? (general ? k_jacobian_lens<18, 2, true> : k_jacobian_lens<18, 2, false>)
+                        : (general ? k_jacobian_lens<kLensTileMaxEval, 1, true> : k_jacobian_lens<kLensTileMaxEval, 1, false>);
         MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         const int mt = std::max(1, lens_tile_mt);
         const dim3 grid((hp.F + 31) / 32, (hp.M + mt - 1) / mt);
-        kern<<<grid, 32 * NE, smem, p->stream>>>(p->ds, mt, d_fvec, d_dist, d_jac, d_cols, d_dist_last);
+        kern<<<grid, 32 * NE, smem, p->stream>>>(p->ds, mt, d_fvec, d_dist, d_jac, d_cols, d_dist_last, nv, nvl);
         ++p->launches;
         MMB_CUDA_CHECK(cudaGetLastError());
         return MMB_OK;
@@ -559,16 +594,20 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             p->tiled_ok = true;
         }
     }
-    {   // lens-in-the-loop tiled kernel (k_jacobian_lens)
-        bool ok = hp.dense_grid && opt->auto_diff_type == 0 && !opt->lens_index_literal && hp.C == 1 && hp.F >= 2 &&
-                  hp.cam_fs[0] == hp.F && hp.cam_lens[0] >= 0 && hp.kmax + 1 <= kLensTileMaxEval && hp.kmax >= 1;
-        if (ok) {
-            const int l = hp.cam_lens[0];
-            ok = hp.lens_model[l] != 0 && hp.lens_fs[l] == 1;
-            const size_t smem = sizeof(double) * ((size_t)(1 + hp.cam_deps[0].size()) * 512 + 26 * (1 + hp.lens_deps[l].size()) +
-                                                  (size_t)(hp.kmax + 1) * 96);
-            if (smem > 200 * 1024) ok = false;
+    {   // evaluation-per-thread tiled kernel (k_jacobian_lens): lens in the loop and / or several cameras
+        bool ok = hp.dense_grid && opt->auto_diff_type == 0 && !opt->lens_index_literal && hp.F >= 2 &&
+                  hp.kmax + 1 <= kLensTileMaxEval && hp.kmax >= 1;
+        size_t nv = 1, nvl = 1;
+        for (int c = 0; ok && c < hp.C; ++c) {
+            if (hp.cam_fs[c] != hp.F) ok = false;
+            nv = std::max(nv, 1 + hp.cam_deps[c].size());
+            const int l = hp.cam_lens[c];
+            if (l >= 0 && hp.lens_model[l] != 0) {
+                if (hp.lens_fs[l] != 1) ok = false;
+                nvl = std::max(nvl, 1 + hp.lens_deps[l].size());
+            }
         }
+        if (sizeof(double) * (nv * 512 + 26 * nvl + (size_t)kLensTileMB * (hp.kmax + 1) * 96) > 200 * 1024) ok = false;
         for (int b = 0; ok && b < hp.B; ++b) if (hp.bnd_fs[b] != 1) ok = false;
         p->lens_tile_ok = ok;
     }
