@@ -61,3 +61,50 @@ def test_multicam_local_slices_match_unsharded(world):
     scale = np.maximum(np.abs(r1.attr_values), 1.0)
     assert np.max(np.abs(r.attr_values - r1.attr_values) / scale) <= 1e-6
     assert np.max(np.abs(r.error_dist - r1.error_dist)) <= 1e-5
+
+
+def test_two_cameras_one_lens_interleaved_markers_match_oracle():
+    """two animated cameras, only the first behind a lens, markers alternating between the
+    cameras: the evaluation-per-thread kernel restages its camera / lens records at every
+    marker and mixes lens and lens-free evaluations"""
+    from mayamatchmovesolver_b200.scene import SceneBuilder
+    rng = np.random.default_rng(17)
+    F, B = 40, 9
+    f = np.arange(F, dtype=np.float64)
+    sb = SceneBuilder(frames=np.arange(1, F + 1))
+    lens = sb.add_lens("3de_radial_std_deg4", camera_params=(3.5, 3.6, 2.4, 1.0, 0.0, 0.0),
+                       degree2_distortion=0.04, degree2_u=0.001, degree4_distortion=0.005)
+    cams, tfms = [], []
+    for c in range(2):
+        t = sb.add_transform(tx=(-1.0 + 2.0 * c) + 0.2 * np.sin(f / 7 + c), ty=0.1 * np.cos(f / 5), tz=0.05 * f / F,
+                             rx=0.3 * np.sin(f / 9), ry=(3.0 - 6.0 * c) + 0.0 * f, rz=0.1 * np.cos(f / 4))
+        tfms.append(t)
+        cams.append(sb.add_camera(t, focal_length_mm=35.0, lens=lens if c == 0 else None))
+    pts = np.stack([rng.uniform(-3, 3, B), rng.uniform(-2, 2, B), rng.uniform(-24, -14, B)], 1)
+    btf = []
+    for b in range(B):
+        t = sb.add_transform(tx=pts[b, 0], ty=pts[b, 1], tz=pts[b, 2])
+        btf.append(t)
+        bn = sb.add_bundle(t)
+        for c in range(2):
+            sb.add_marker(cams[c], bn, rng.uniform(-0.3, 0.3, F), rng.uniform(-0.2, 0.2, F))
+    for t in tfms:
+        for k in ("tx", "ty", "rx", "ry"):
+            sb.add_attr(t[k])
+    sb.add_attr(cams[0]["focal_length_mm"])
+    sb.add_attr(lens["degree2_distortion"])
+    for t in btf:
+        for k in ("tx", "ty", "tz"):
+            sb.add_attr(t[k])
+    o = OracleProblem(sb)
+    with Problem(sb) as p:
+        assert (p.n, p.nobs) == (o.n, o.nobs)
+        x = p.initial_parameters() + rng.normal(0, 1e-2, p.n)
+        fv, d = p.eval_residuals(x)
+        fo, do = o.eval_residuals(x)
+        assert np.abs(fv - fo).max() <= 1e-9 * np.abs(fo).max()
+        J, Jo = p.eval_jacobian_dense(x), o.eval_jacobian_dense(x)
+        assert np.abs(J - Jo).max() <= 1e-9 * np.abs(Jo).max()
+        vals, cols = p.eval_jacobian_blocks(x)
+        fast = p.eval_jacobian_blocks(x, want_cols=False)
+        assert np.abs(fast - vals).max() <= 1e-9 * np.abs(Jo).max()
