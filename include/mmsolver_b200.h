@@ -156,8 +156,9 @@ typedef struct mmb_options {
     int32_t frame_solve_mode;  /* 0 all frames at once, 1 per frame */
     int32_t remove_unused_markers;
     int32_t remove_unused_attributes;
-    /* extensions (0 = reference behaviour) */
-    int32_t lens_index_literal;/* 1: reproduce the reference's
+    /* extensions */
+    int32_t lens_index_literal;/* 0 = intended indexing, 1 = the reference's
+                                  literal read: reproduce the
                                   [markerIndex+frameIndex] lens table read
                                   (adjust_measureErrors.cpp:463); 0: intended
                                   [marker*F+frame] */
@@ -367,8 +368,9 @@ mmb_status mmb_lens_apply_layered(int32_t device, int32_t n_layers,
                                   int32_t direction, int64_t n_points,
                                   const double *xy_in, double *xy_out);
 /* mmb_lens_apply_layered for callers that must not allocate device memory
- * (code under CUDA graph capture, tight serving loops, harnesses that forbid
- * cudaMalloc).  No counterpart in the reference: added at the request of the
+ * (tight serving loops, harnesses that forbid cudaMalloc; NOT usable under
+ * CUDA graph capture: it takes host pointers and issues blocking copies on the
+ * legacy default stream, which a capture cannot record).  No counterpart in the reference.
  * Same arguments, same kernel, same results; the layer table
  * and the staging of the points live in one static __device__ array of
  * 4096 + 2 * MMB_LENS_NO_ALLOC_MAX_POINTS * 16 bytes (8 MiB) that every GPU

@@ -221,3 +221,24 @@ def blocks_to_dense(vals, cols, n):
         J[2 * idx, pid[ok]] = vals[c, 2 * idx]
         J[2 * idx + 1, pid[ok]] = vals[c, 2 * idx + 1]
     return J
+
+
+def oracle_mmsolver(scene, scene_graph_mode=2, **flags):
+    """The command surface (cmd.mmSolver's flag handling) driving the CPU oracle instead of the
+    CUDA library: -> (SolveResult, {plug: solved value}).  Used to pin the oracle to the
+    reference's own Maya-hosted tests (tests/kat_scenes.py)."""
+    from mayamatchmovesolver_b200 import cmd
+    opts, rest = cmd._options_from_kwargs(flags)
+    objects = {k: v for k, v in rest.items() if k in cmd._OBJECT_FLAGS}
+    opts["scene_graph_mode"] = scene_graph_mode
+    sb = cmd.select_scene(scene, **objects) if objects else scene
+    o = OracleProblem(sb, **opts)
+    r = o.solve()
+    _, p2a = o.index_maps()
+    values = {}
+    plugs = [e[0] for e in objects.get("attr", [])]
+    for i in range(o.n):
+        a, f = int(p2a[i, 0]), int(p2a[i, 1])
+        if a < len(plugs) and f <= 0:
+            values[plugs[a]] = float(r.attr_values[i])
+    return r, values

@@ -86,3 +86,26 @@ def test_cfg1_three_attributes_per_bundle_is_refused(tmp_path):
         assert (p.n, p.m) == (60, 40)
         with pytest.raises(MmbError):
             p.solve()
+
+
+def test_cfg1_on_the_reference_marker_file():
+    """cfg1 as BASELINE.json / SURVEY.md 8d specify it: the markers of
+    tests/data/match_mover/loadmarker.rz2 (frame 41: the 20 points tracked there; fixture
+    tests/golden/cfg1_loadmarker_frame41.rz2, read with the product's .rz2 reader), the camera and
+    the bundle start positions of test_solve_operahouse.py; tx, ty per bundle solved through the
+    command surface on the GPU and by the CPU oracle on the same scene."""
+    from kat_scenes import cfg1_operahouse
+    from oraclelib import oracle_mmsolver
+    sb, flags, nodes = cfg1_operahouse()
+    ro, oracle_values = oracle_mmsolver(sb, **flags)
+    strings = mmSolver(sb, sceneGraphMode=2, **flags)
+    res = solveresult.SolveResultStrings(strings)
+    assert strings[0] == "success=1" and res.get_success()
+    assert res.solver_stats["stop_id"] == ro.reason_num
+    assert res.solver_stats["iteration_total_calls"] == ro.iteration_num
+    got = np.array([[sb.get_value(n["tx"]), sb.get_value(n["ty"])] for n in nodes]).reshape(-1)
+    want = np.array([oracle_values[a[0]] for a in flags["attr"]])
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-9)
+    assert abs(res.error_stats["final_average"] - ro.error_avg) <= 1e-6
+    assert res.error_stats["final_average"] < 0.05      # px: every bundle moved onto its marker's ray
+    assert len(res.get_marker_error_list()) == 20

@@ -93,3 +93,91 @@ def test_full_size_properties():
         assert np.array_equal(cols[:, :6], (np.arange(6)[None, :] * 1000 + fr[:, None]))
         assert np.array_equal(cols[:, 6:], 6000 + 3 * e2m[:, :1] + np.arange(3)[None, :])
         assert np.isfinite(vals).all() and np.abs(vals).max() > 1.0
+
+
+BOUNDED_CASES = [
+    dict(F=7, B=9, seed=11, drop_fraction=0.2, weights=True),                  # generic kernel, sparse visibility
+    dict(F=40, B=30, seed=3),                                                  # F >= 32: the rows kernel
+    dict(F=36, B=18, seed=4, in_frame=True,                                    # lens in the loop: the lens-tile kernel
+         lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree2_v=-0.002, degree4_distortion=0.01),
+         solve_focal=True, solve_lens=("degree2_distortion", "degree4_distortion"), focal_init=33.0),
+]
+
+
+@pytest.mark.parametrize("case", BOUNDED_CASES)
+@pytest.mark.parametrize("adt", [0, 1])
+@pytest.mark.parametrize("path", ["generic", "tiled"])
+def test_bounded_offset_scaled_attrs_match_oracle(case, adt, path, monkeypatch):
+    """`-attr node.attr min max offset scale` (arg_flags_solve_object.cpp:288-318): every branch of
+    parameterBoundFromInternalToExternal (adjust_base.cpp:194-258) on the device -- both bounds,
+    upper only, lower only, offset / scale -- and FD steps whose sign calculateParameterDelta flips
+    (adjust_solveFunc.cpp:148-180), in every Jacobian kernel."""
+    from kat_scenes import apply_bounds
+    monkeypatch.setenv("MMB_JACOBIAN_PATH", path)
+    sb, info = synth.make_scene(**case)
+    apply_bounds(sb, info)
+    o = OracleProblem(sb, auto_diff_type=adt)
+    with Problem(sb, auto_diff_type=adt) as p:
+        x = p.initial_parameters()
+        assert np.array_equal(x, o.initial_parameters())
+        _, p2a = o.index_maps()
+        flips = ((x + 1e-4) > np.array(sb.attr_max)[p2a[:, 0]]).sum()
+        assert flips > 0  # the scene does exercise the sign flip
+        rng = np.random.default_rng(7)
+        for trial in range(2):
+            xt = x + (rng.normal(0, 1e-2, x.shape) if trial else 0.0)
+            f, d = p.eval_residuals(xt)
+            fo, do = o.eval_residuals(xt)
+            assert np.abs(f - fo).max() <= 1e-9 * np.abs(fo).max()
+            assert np.abs(d - do).max() <= 1e-9 * np.abs(do).max()
+            J = p.eval_jacobian_dense(xt)
+            Jo = o.eval_jacobian_dense(xt)
+            assert np.abs(J - Jo).max() <= 1e-9 * np.abs(Jo).max()
+            fast = p.eval_jacobian_blocks(xt, want_cols=False)
+            vals, cols = p.eval_jacobian_blocks(xt)
+            assert np.abs(fast - vals).max() <= 1e-9 * np.abs(Jo).max()
+
+
+def test_lens_index_literal_matches_oracle():
+    """options.lens_index_literal = 1: the reference's literal `markerIndex + frameIndex` read of
+    the marker-frame lens table (adjust_measureErrors.cpp:463) -- with two cameras of which only
+    one has a lens, the literal index picks another marker's lens for most observations."""
+    sb = _two_camera_lens_scene()
+    for literal in (0, 1):
+        o = OracleProblem(sb, lens_index_literal=literal)
+        with Problem(sb, lens_index_literal=literal) as p:
+            x = p.initial_parameters()
+            f, d = p.eval_residuals(x)
+            fo, do = o.eval_residuals(x)
+            assert np.abs(f - fo).max() <= 1e-9 * np.abs(fo).max()
+            J = p.eval_jacobian_dense(x)
+            Jo = o.eval_jacobian_dense(x)
+            assert np.abs(J - Jo).max() <= 1e-9 * np.abs(Jo).max()
+            if literal == 0:
+                f0 = f
+    assert np.abs(f - f0).max() > 1e-3  # the two indexings do differ on this scene
+
+
+def _two_camera_lens_scene():
+    from mayamatchmovesolver_b200.scene import SceneBuilder
+    rng = np.random.default_rng(21)
+    F, B = 6, 5
+    sb = SceneBuilder(frames=np.arange(1, F + 1))
+    lens = sb.add_lens("3de_radial_std_deg4", camera_params=(3.5, 3.6, 2.4, 1.0, 0.0, 0.0), degree2_distortion=0.08,
+                       degree4_distortion=0.02)
+    cams = []
+    for c in range(2):
+        t = sb.add_transform(tx=np.linspace(-1, 1, F) + c, ty=0.3 * c, tz=np.linspace(5, 6, F), ry=np.linspace(-3, 3, F))
+        cams.append((t, sb.add_camera(t, lens=lens if c == 0 else None)))
+    pts = np.stack([rng.uniform(-3, 3, B), rng.uniform(-2, 2, B), rng.uniform(-20, -12, B)], 1)
+    bt = [sb.add_transform(tx=p[0], ty=p[1], tz=p[2]) for p in pts]
+    bn = [sb.add_bundle(t) for t in bt]
+    for c in range(2):
+        for b in range(B):
+            sb.add_marker(cams[c][1], bn[b], rng.uniform(-0.3, 0.3, F), rng.uniform(-0.2, 0.2, F))
+    for t, _ in cams:
+        sb.add_attr(t["tx"]); sb.add_attr(t["ry"])
+    sb.add_attr(lens["degree2_distortion"])
+    for t in bt:
+        sb.add_attr(t["tx"]); sb.add_attr(t["tz"])
+    return sb

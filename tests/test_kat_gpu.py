@@ -1,0 +1,69 @@
+"""GPU: the reference's own Maya-hosted solver tests (tests/kat_scenes.py: test1.py, test3.py,
+test_min_max_values.py, test_marker_weight.py, test_marker_enabled.py) run through the command
+surface `mmSolver(**flags)` -> C-ABI -> CUDA, with the reference's own assertions, and compared
+with the CPU oracle driven by the same flags."""
+import numpy as np
+import pytest
+
+from kat_scenes import KATS, apply_bounds
+from mayamatchmovesolver_b200 import mmSolver, solveresult, synth
+from mayamatchmovesolver_b200.problem import Problem
+from oraclelib import OracleProblem, oracle_mmsolver
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", list(KATS))
+def test_reference_kat_through_the_command(name):
+    sb, flags, expected = KATS[name]()
+    ro, oracle_values = oracle_mmsolver(sb, **flags)
+    strings = mmSolver(sb, sceneGraphMode=2, **flags)
+    assert strings[0] == "success=1"
+    for plug, (want, eps) in expected.items():
+        got = sb.get_value(sb.plug(plug))        # the command wrote the solved value back
+        assert abs(got - want) < eps, (name, plug, got, want)
+        assert abs(got - oracle_values[plug]) <= 1e-6 * max(1.0, abs(want)), (name, plug, got, oracle_values[plug])
+    r = solveresult.SolveResultStrings(strings)
+    assert r.solver_stats["stop_id"] == ro.reason_num
+    assert r.solver_stats["iteration_total_calls"] == ro.iteration_num
+
+
+BOUNDED_SOLVES = {
+    "camera_bundles_12x16": dict(F=12, B=16, seed=9, fixed_bundles=3, period=12),
+    "camera_bundles_40x30": dict(F=40, B=30, seed=5, fixed_bundles=4, period=40),
+    "sparse_weighted": dict(F=20, B=14, seed=6, fixed_bundles=3, drop_fraction=0.15, weights=True, period=20),
+}
+
+
+@pytest.mark.parametrize("name", list(BOUNDED_SOLVES))
+def test_bounded_solve_matches_oracle(name):
+    """whole LM solves with box constraints / offset / scale on the solver attributes
+    (adjust_base.cpp:194-258): same LM decisions, solved values 1e-6 relative, errors 1e-6 px"""
+    sb, info = synth.make_scene(**BOUNDED_SOLVES[name])
+    apply_bounds(sb, info, lower_only=False)
+    ro = OracleProblem(sb).solve()
+    with Problem(sb) as p:
+        r = p.solve()
+    print(name, "oracle", ro, "gpu", r)
+    assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (ro.reason_num, ro.iteration_num, ro.iteration_attempt_num)
+    scale = np.maximum(np.abs(ro.attr_values), 1.0)
+    assert np.max(np.abs(r.attr_values - ro.attr_values) / scale) <= 1e-6
+    assert np.max(np.abs(r.error_dist - ro.error_dist)) <= 1e-6
+    # solved values respect their boxes
+    _, p2a = p.index_maps() if False else OracleProblem(sb).index_maps()
+    mn = np.array(sb.attr_min)[p2a[:, 0]]; mx = np.array(sb.attr_max)[p2a[:, 0]]
+    assert (r.attr_values >= mn).all() and (r.attr_values <= mx).all()
+
+
+def test_bounded_per_frame_solve_matches_oracle():
+    """frameSolveMode = 1 with bounded / scaled camera attributes: the per-frame kernel's own
+    copy of the bound transform and step logic against one oracle solve per frame"""
+    sb, info = synth.make_scene(F=10, B=14, seed=2, solve_bundles=False, period=10)
+    apply_bounds(sb, info, lower_only=False)
+    with Problem(sb, frame_solve_mode=1) as p:
+        agg, per = p.solve_per_frame()
+    av = agg.attr_values.reshape(6, 10)
+    for f in range(10):
+        ro = OracleProblem(sb.slice_frames([f])).solve()
+        assert per[f].reason_num == ro.reason_num and per[f].iteration_num == ro.iteration_num
+        assert np.max(np.abs(av[:, f] - ro.attr_values) / np.maximum(np.abs(ro.attr_values), 1.0)) <= 1e-6

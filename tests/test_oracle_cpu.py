@@ -256,11 +256,16 @@ def test_index_maps_reference_order():
     dict(F=5, B=6, seed=4, lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree4_distortion=0.01),
          solve_focal=True, solve_lens=("degree2_distortion", "degree4_distortion"), focal_init=33.0),
 ])
-def test_host_plan_logic_via_emulation(case, adt):
+@pytest.mark.parametrize("bounded", [False, True])
+def test_host_plan_logic_via_emulation(case, adt, bounded):
     """The product's host code (index maps, dependency analysis, variant plan) drives the same
     per-thread bodies the CUDA kernels run; executed on the host here they must reproduce the
-    oracle's residuals and dense Jacobian."""
-    sb, _ = synth.make_scene(**case)
+    oracle's residuals and dense Jacobian.  `bounded`: box constraints, offset and scale on the
+    solver attributes (every branch of the bound transform, sign-flipped FD steps)."""
+    sb, info = synth.make_scene(**case)
+    if bounded:
+        from kat_scenes import apply_bounds
+        apply_bounds(sb, info)
     o = OracleProblem(sb, auto_diff_type=adt)
     e = EmuProblem(sb, auto_diff_type=adt)
     x = o.initial_parameters() + np.random.default_rng(1).normal(0, 1e-2, o.n)
