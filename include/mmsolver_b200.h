@@ -202,6 +202,26 @@ mmb_status mmb_problem_sizes(const mmb_problem *p, int32_t *n_params,
  * (attr, frame | -1).  Either pointer may be NULL. */
 mmb_status mmb_get_index_maps(const mmb_problem *p, int32_t *error_to_marker,
                               int32_t *param_to_attr);
+/* The marker <-> attribute relationship of the mmSolverAffects command
+ * (src/mmSolver/cmd/MMSolverAffectsCmd.cpp; findMarkerToAttributeRelationship,
+ * adjust_relationships.cpp:369-466): marker i is affected by solver attribute j
+ * when j drives the marker's camera (transform chain, camera shape, lens) or its
+ * bundle's transform chain.  marker_affects_attr [M*A] row-major, and the used
+ * flags of splitUsedMarkersAndAttributes (adjust_base.cpp:574-610): marker_used
+ * [M], attr_used [A].  Any output may be NULL.  Host only: needs no GPU. */
+mmb_status mmb_affects(const mmb_scene_desc *scene, uint8_t *marker_affects_attr,
+                       uint8_t *marker_used, uint8_t *attr_used);
+/* solve_v1 drops markers affected by no attribute / attributes affecting no
+ * marker before solveFrames when options.remove_unused_markers /
+ * remove_unused_attributes are set (adjust_base.cpp:1322-1395); the index maps,
+ * parameters and results of the handle then number the USED lists.  This gives
+ * the position of each used marker / attribute in the caller's lists
+ * (used_marker_index [num_markers_used], used_attr_index [num_attrs_used];
+ * call with NULL arrays to get the counts). */
+mmb_status mmb_problem_used_objects(const mmb_problem *p, int32_t *num_markers_used,
+                                    int32_t *used_marker_index,
+                                    int32_t *num_attrs_used,
+                                    int32_t *used_attr_index);
 /* normalised marker weights [Nobs] (adjust_relationships.cpp:166-182) */
 mmb_status mmb_get_marker_weights(const mmb_problem *p, double *weights);
 
@@ -209,7 +229,9 @@ mmb_status mmb_get_marker_weights(const mmb_problem *p, double *weights);
 mmb_status mmb_get_initial_parameters(const mmb_problem *p, double *x);
 
 /* solveFunc iflag=1 (adjust_solveFunc.cpp:262): fvec[m]; optional
- * error_dist[Nobs] (errorDistanceList, px) */
+ * error_dist[Nobs] (errorDistanceList, px).  x == NULL measures the scene at its
+ * own attribute values, no parameter applied: the initial measureErrors of
+ * solveFrames (adjust_base.cpp:1080-1103), which is all a printStatistics call does */
 mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec,
                               double *error_dist);
 

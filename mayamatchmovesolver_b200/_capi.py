@@ -82,6 +82,8 @@ SYMBOLS = [
     ("mmb_problem_destroy", None, [C.c_void_p]),
     ("mmb_problem_sizes", C.c_int32, [C.c_void_p, c_i32p, c_i32p, c_i32p]),
     ("mmb_get_index_maps", C.c_int32, [C.c_void_p, c_i32p, c_i32p]),
+    ("mmb_affects", C.c_int32, [C.POINTER(SceneDesc), c_u8p, c_u8p, c_u8p]),
+    ("mmb_problem_used_objects", C.c_int32, [C.c_void_p, c_i32p, c_i32p, c_i32p, c_i32p]),
     ("mmb_get_marker_weights", C.c_int32, [C.c_void_p, c_f64p]),
     ("mmb_get_initial_parameters", C.c_int32, [C.c_void_p, c_f64p]),
     ("mmb_eval_residuals", C.c_int32, [C.c_void_p, c_f64p, c_f64p, c_f64p]),

@@ -52,7 +52,7 @@ _FLAGS = {
 _SHORT = {v[0]: k for k, v in _FLAGS.items()}
 _OBJECT_FLAGS = {"camera": "c", "marker": "m", "attr": "a", "frame": "f"}
 _IGNORED = {"verbose": "v", "logLevel": "lgl", "resultsNode": "rsn", "setMarkerDeviationAttrs": "smd",
-            "attrStiffness": "asf", "attrSmoothness": "asm"}
+            "attrStiffness": "asf", "attrSmoothness": "asm"}  # stiffness / smoothness: see mmSolver()
 _PRINT_STATS = ("inputs", "affects", "usedSolveObjects", "deviation")
 
 # sceneGraphMode / solverType / frameSolveMode values (adjust_defines.h:92-152, _api/constant.py)
@@ -109,16 +109,13 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
             if tfm_name not in sb.names or shp_name not in sb.names:
                 raise ValueError("unknown camera %r / %r" % (tfm_name, shp_name))
     if marker is not None:
-        keep = set()
+        keep = []
         for mkr_name, cam_name, bnd_name in marker:
             node = sb.names[mkr_name]
             if sb.mkr_cam[node.index] != sb.names[cam_name].index or sb.mkr_bnd[node.index] != sb.names[bnd_name].index:
                 raise ValueError("marker %r is not linked to camera %r / bundle %r" % (mkr_name, cam_name, bnd_name))
-            keep.add(node.index)
-        for i in range(len(sb.mkr_en)):
-            if i not in keep:
-                sb.mkr_en[i] = np.zeros_like(sb.mkr_en[i])
-        sb._arrays_cache = None
+            keep.append(node.index)
+        sb.keep_markers(keep)
     if attr is not None:
         sb.attr_ref, sb.attr_min, sb.attr_max, sb.attr_off, sb.attr_scl = [], [], [], [], []
         sb._arrays_cache = None
@@ -132,16 +129,20 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
     return sb
 
 
-def format_results(problem, result, scene, flags):
-    """CommandResult::appendToMStringArray through the C-ABI -> list of str"""
+def format_results(problem, result, scene, flags, solved=True):
+    """CommandResult::appendToMStringArray through the C-ABI -> list of str.
+    `scene`: frames + the names of the markers the handle numbers (its used list)."""
     lib = _capi.load()
     e2m, _ = problem.index_maps()
     fvec = np.zeros(problem.m)
-    check(lib.mmb_get_last_residuals(problem._h, fvec.ctypes.data_as(c_f64p)), "mmb_get_last_residuals")
+    if solved:
+        check(lib.mmb_get_last_residuals(problem._h, fvec.ctypes.data_as(c_f64p)), "mmb_get_last_residuals")
     frames = np.ascontiguousarray(scene.frames, dtype=np.int32)
-    by_index = {n.index: n.name for n in scene.names.values() if n.kind == "marker"}
-    M = len(scene.mkr_cam)
-    names = (C.c_char_p * M)(*[(by_index.get(i) or ("marker%d" % i)).encode() for i in range(M)])
+    marker_names = getattr(scene, "marker_names", None)
+    if marker_names is None:
+        marker_names = _names(scene, "marker", len(scene.mkr_cam))
+    M = len(marker_names)
+    names = (C.c_char_p * M)(*[n.encode() for n in marker_names])
     e2m = np.ascontiguousarray(e2m, dtype=np.int32)
     x = np.ascontiguousarray(result.x)
     dist = np.ascontiguousarray(result.error_dist)
@@ -158,6 +159,63 @@ def format_results(problem, result, scene, flags):
     return [s for s in buf.value.decode().split("\n") if s]
 
 
+def _names(scene, kind, count):
+    by_index = {n.index: n.name for n in scene.names.values() if n.kind == kind}
+    return [by_index.get(i) or ("%s%d" % (kind, i)) for i in range(count)]
+
+
+def _attr_names(scene):
+    """'node.attr' of every solver attribute of the scene (its plug name when the node is named)"""
+    by_ref = {}
+    for node in scene.names.values():
+        for attr, ref in node.items():
+            by_ref.setdefault(ref, "%s.%s" % (node.name, attr))
+    return [by_ref.get(ref, "attr%d" % i) for i, ref in enumerate(scene.attr_ref)]
+
+
+def affects_strings(scene, used_only=None):
+    """AffectsResult::appendToMStringArray (adjust_results.h:664-680):
+    `marker_affects_attribute=<marker>#<node.attr>#<0|1>` for every (marker, attribute) pair"""
+    from .problem import affects
+    table, mu, au = affects(scene)
+    mk_names = _names(scene, "marker", len(scene.mkr_cam))
+    at_names = _attr_names(scene)
+    out = []
+    for i in range(table.shape[0]):
+        if used_only is not None and not used_only[0][i]:
+            continue
+        for j in range(table.shape[1]):
+            if used_only is not None and not used_only[1][j]:
+                continue
+            out.append("marker_affects_attribute=%s#%s#%d" % (mk_names[i], at_names[j], int(table[i, j])))
+    return out
+
+
+def mmSolverAffects(scene, mode="returnString", **kwargs):
+    """The `mmSolverAffects` command (src/mmSolver/cmd/MMSolverAffectsCmd.cpp): which solver
+    attribute can affect which marker.  mode 'returnString' -> the `marker_affects_attribute=`
+    strings; mode 'addAttrsToMarkers' stores the table on the scene (`scene.affects`, the
+    stand-in for the per-marker Maya attributes the command creates) and returns None."""
+    _, rest = _options_from_kwargs(kwargs)
+    objects = {}
+    for key, value in rest.items():
+        long_name = {v: k for k, v in _OBJECT_FLAGS.items()}.get(key, key)
+        if long_name in _OBJECT_FLAGS:
+            objects[long_name] = value
+    objects.pop("frame", None)
+    sb = select_scene(scene, **objects) if objects else scene
+    if mode == "returnString":
+        return affects_strings(sb)
+    if mode == "addAttrsToMarkers":
+        from .problem import affects
+        table, _, _ = affects(sb)
+        mk_names = _names(sb, "marker", len(sb.mkr_cam))
+        at_names = _attr_names(sb)
+        scene.affects = {(mk_names[i], at_names[j]): bool(table[i, j]) for i in range(table.shape[0]) for j in range(table.shape[1])}
+        return None
+    raise ValueError("mmSolverAffects: mode value is invalid: mode=%r" % mode)
+
+
 def mmSolver(scene, write_back=True, device=0, **kwargs):
     """-> list of `key=value` strings, as `maya.cmds.mmSolver` returns them."""
     opts, rest = _options_from_kwargs(kwargs)
@@ -170,7 +228,7 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
         elif key in ("printStatistics", "pst"):
             print_stats_flags = [value] if isinstance(value, str) else list(value)
         elif key in _IGNORED or key in _IGNORED.values():
-            continue  # accepted for compatibility; Maya-side features (log level, result nodes, v1 stiffness)
+            continue  # accepted for compatibility; Maya-side features (log level, result nodes)
         else:
             raise TypeError("mmSolver: unknown flag %r" % key)
     for name in print_stats_flags:
@@ -184,21 +242,84 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
         assert sgm == SCENE_GRAPH_MODE_MM_SCENE_GRAPH, "per-frame solving needs sceneGraphMode = mmscenegraph"
     sb = select_scene(scene, **objects) if objects else scene
     options = default_options(device=device, **opts)
+    do_not_solve = bool(print_stats_flags)  # constructPrintStats, adjust_base.cpp:618-646
     flags = _capi.MMB_FMT_ERROR_PER_MARKER_PER_FRAME | _capi.MMB_FMT_ERROR_PER_FRAME | _capi.MMB_FMT_SOLVE_VALUES
     if "inputs" in print_stats_flags:
         flags |= _capi.MMB_FMT_INPUT_STATS
+    # used / unused solve objects (solve_v1, adjust_base.cpp:1322-1395)
+    from .problem import affects
+    _, marker_used, attr_used = affects(sb)
+    if not (options.remove_unused_markers or options.remove_unused_attributes):
+        marker_used[:] = True
+        attr_used[:] = True
+    mk_names = _names(sb, "marker", len(sb.mkr_cam))
+    at_names = _attr_names(sb)
+    extra = []
+    if "usedSolveObjects" in print_stats_flags:
+        # SolverObjectUsageResult::appendToMStringArray (adjust_results.h:755-790)
+        groups = (("markers_used=", [n for n, u in zip(mk_names, marker_used) if u]),
+                  ("markers_unused=", [n for n, u in zip(mk_names, marker_used) if not u]),
+                  ("attributes_used=", [n for n, u in zip(at_names, attr_used) if u]),
+                  ("attributes_unused=", [n for n, u in zip(at_names, attr_used) if not u]))
+        extra += [key + "".join(n + "#" for n in names) for key, names in groups if names]
+    if "affects" in print_stats_flags:
+        use_m = marker_used if options.remove_unused_markers else np.ones_like(marker_used)
+        use_a = attr_used if options.remove_unused_attributes else np.ones_like(attr_used)
+        extra += affects_strings(sb, used_only=(use_m, use_a))
+    n_used_m = int(marker_used.sum()) if options.remove_unused_markers else len(mk_names)
+    n_used_a = int(attr_used.sum()) if options.remove_unused_attributes else len(at_names)
+    if n_used_m == 0 or n_used_a == 0:
+        # adjust_base.cpp:844-862: not enough used markers / attributes
+        return extra + (["success=1"] if do_not_solve else ["success=0"])
+
+    def splice(strings):
+        k = 5 if "inputs" in print_stats_flags else 0   # the numberOf* block comes first
+        return strings[:k] + extra + strings[k:]
+
     with Problem(sb, options=options) as p:
+        used_m, used_a = p.used_objects()
+        names_scene = _UsedView(sb, [mk_names[i] for i in used_m])
+        if do_not_solve:
+            # adjust_base.cpp:1105-1135: the initial measurement only
+            r = _initial_measure_result(p, options)
+            return splice(format_results(p, r, names_scene, flags, solved=False))
+        if p.n > p.m:
+            # adjust_base.cpp:864-882: more parameters than errors -> success=0, nothing solved
+            r = _initial_measure_result(p, options)
+            r.raw.success = 0
+            return format_results(p, r, names_scene, flags, solved=False)
         r = p.solve_per_frame()[0] if options.frame_solve_mode == FRAME_SOLVE_MODE_PER_FRAME else p.solve()
-        strings = format_results(p, r, sb, flags)
+        strings = format_results(p, r, names_scene, flags)
         _, p2a = p.index_maps()
     if write_back and r.success:
         # attr_values already holds the initial values when acceptOnlyBetter rejected the solve
         frame_index = {int(n): i for i, n in enumerate(scene.frames)}
         for i in range(len(r.attr_values)):
-            a, f = int(p2a[i, 0]), int(p2a[i, 1])
+            a, f = int(used_a[p2a[i, 0]]), int(p2a[i, 1])
             ref = sb.attr_ref[a]
             if f < 0:
                 scene.set_value(ref, r.attr_values[i])
             else:
                 scene.set_value(ref, r.attr_values[i], frame_index[int(sb.frames[f])])
     return strings
+
+
+class _UsedView:
+    """what format_results needs of a scene: the frames and the names of the USED markers"""
+
+    def __init__(self, scene, marker_names):
+        self.frames = scene.frames
+        self.marker_names = marker_names
+
+
+def _initial_measure_result(p, options):
+    from .problem import SolveResult
+    raw = _capi.Result()
+    raw.success = 1
+    dist = np.zeros(p.nobs)
+    if options.accept_only_better:
+        _, dist = p.eval_residuals(None)
+        finite = dist[np.isfinite(dist)]
+        if len(finite):
+            raw.error_avg, raw.error_min, raw.error_max = float(finite.mean()), float(finite.min()), float(finite.max())
+    return SolveResult(raw, np.zeros(p.n), np.zeros(p.n), dist)

@@ -100,6 +100,38 @@ mmb_status mmb_get_index_maps(const mmb_problem *p, int32_t *e2m, int32_t *p2a) 
     return MMB_OK;
 }
 
+mmb_status mmb_problem_used_objects(const mmb_problem *p, int32_t *num_markers_used, int32_t *used_marker_index,
+                                    int32_t *num_attrs_used, int32_t *used_attr_index) {
+    if (!p) return MMB_ERR_INVALID_ARGUMENT;
+    const HostProblem &hp = p->dp->hp;
+    if (num_markers_used) *num_markers_used = hp.M;
+    if (num_attrs_used) *num_attrs_used = hp.A;
+    if (used_marker_index) for (int i = 0; i < hp.M; ++i) used_marker_index[i] = hp.mkr_src[i];
+    if (used_attr_index) for (int a = 0; a < hp.A; ++a) used_attr_index[a] = hp.attr_src[a];
+    return MMB_OK;
+}
+
+mmb_status mmb_affects(const mmb_scene_desc *scene, uint8_t *marker_affects_attr, uint8_t *marker_used,
+                       uint8_t *attr_used) {
+    if (!scene) return MMB_ERR_INVALID_ARGUMENT;
+    try {
+        HostProblem hp;
+        mmb_options opt;
+        mmb_options_default(&opt);
+        const mmb_status st = copy_scene_tables(scene, &opt, &hp);
+        if (st != MMB_OK) { set_last_error(hp.error); return st; }
+        std::vector<uint8_t> table, mu, au;
+        marker_attr_usage(hp, marker_affects_attr ? &table : nullptr, &mu, &au);
+        if (marker_affects_attr) std::copy(table.begin(), table.end(), marker_affects_attr);
+        if (marker_used) std::copy(mu.begin(), mu.end(), marker_used);
+        if (attr_used) std::copy(au.begin(), au.end(), attr_used);
+    } catch (const std::exception &e) {
+        set_last_error(e.what());
+        return MMB_ERR_INTERNAL;
+    }
+    return MMB_OK;
+}
+
 mmb_status mmb_get_marker_weights(const mmb_problem *p, double *w) {
     if (!p || !w) return MMB_ERR_INVALID_ARGUMENT;
     const HostProblem &hp = p->dp->hp;
@@ -127,11 +159,13 @@ static mmb_status upload_x(DeviceProblem *dp, const double *x) {
 }
 
 mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec, double *error_dist) {
-    if (!p || !x || !fvec) return MMB_ERR_INVALID_ARGUMENT;
+    if (!p || !fvec) return MMB_ERR_INVALID_ARGUMENT;
     DeviceProblem *dp = p->dp;
     mmb_status st;
-    if ((st = upload_x(dp, x)) != MMB_OK) return st;
-    if ((st = launch_variants(dp, dp->d_x, false)) != MMB_OK) return st;
+    if (x && (st = upload_x(dp, x)) != MMB_OK) return st;
+    // x == NULL: the scene at its own attribute values, no parameter applied (the initial
+    // measureErrors of solveFrames, adjust_base.cpp:1080-1103)
+    if ((st = launch_variants(dp, x ? dp->d_x : nullptr, false)) != MMB_OK) return st;
     if ((st = launch_residuals(dp, dp->d_fvec, dp->d_dist)) != MMB_OK) return st;
     MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
     if (error_dist)

@@ -102,8 +102,48 @@ static void deps_from_refs(const RefAttrs &ra, const std::vector<int32_t> &refs,
     deps.erase(std::unique(deps.begin(), deps.end()), deps.end());
 }
 
-mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
-                              HostProblem *hpp) {
+// marker x attribute "affects" table of the scene held in hp (tables already copied, before any
+// removal): table[i * A + j] (may be NULL), plus which markers / attributes are used at all.
+void marker_attr_usage(const HostProblem &hp, std::vector<uint8_t> *table, std::vector<uint8_t> *marker_used,
+                       std::vector<uint8_t> *attr_used) {
+    const int M = hp.M, A = hp.A;
+    RefAttrs ra;
+    ra.stat.resize(hp.num_static); ra.anim.resize(hp.num_anim);
+    for (int a = 0; a < A; ++a) {
+        const int32_t r = hp.attr_ref[a];
+        if (r >= 0) ra.stat[r].push_back(a); else ra.anim[(size_t)(-(int64_t)r - 1)].push_back(a);
+    }
+    // attributes per camera (incl. its lens) and per bundle, once per entity
+    std::vector<std::vector<int32_t>> cam_a(hp.C), bnd_a(hp.B);
+    uint8_t varies;
+    for (int c = 0; c < hp.C; ++c) {
+        std::vector<int32_t> refs;
+        chain_refs(hp, hp.cam_tfm[c], refs);
+        for (int k = 0; k < MMB_CAM_ATTRS; ++k) refs.push_back(hp.cam_attrs[c * MMB_CAM_ATTRS + k]);
+        const int l = hp.cam_lens[c];
+        if (l >= 0) for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k) refs.push_back(hp.lens_attrs[l * MMB_LENS_MAX_COEFFS + k]);
+        deps_from_refs(ra, refs, cam_a[c], varies);
+    }
+    for (int b = 0; b < hp.B; ++b) {
+        std::vector<int32_t> refs;
+        chain_refs(hp, hp.bnd_tfm[b], refs);
+        deps_from_refs(ra, refs, bnd_a[b], varies);
+    }
+    if (table) table->assign((size_t)M * A, 0);
+    if (marker_used) marker_used->assign(M, 0);
+    if (attr_used) attr_used->assign(A, 0);
+    for (int i = 0; i < M; ++i) {
+        const std::vector<int32_t> *lists[2] = {&cam_a[hp.mkr_cam[i]], &bnd_a[hp.mkr_bnd[i]]};
+        for (const std::vector<int32_t> *v : lists)
+            for (int32_t a : *v) {
+                if (table) (*table)[(size_t)i * A + a] = 1;
+                if (marker_used) (*marker_used)[i] = 1;
+                if (attr_used) (*attr_used)[a] = 1;
+            }
+    }
+}
+
+mmb_status copy_scene_tables(const mmb_scene_desc *s, const mmb_options *opt, HostProblem *hpp) {
     HostProblem &hp = *hpp;
     if (!s || !opt) return MMB_ERR_INVALID_ARGUMENT;
     if (s->abi_version != MMB_ABI_VERSION) {
@@ -159,15 +199,6 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         hp.attr_off.assign(s->attr_offset, s->attr_offset + hp.A);
         hp.attr_scl.assign(s->attr_scale, s->attr_scale + hp.A);
     }
-    const bool timing = getenv("MMB_TIMING") != nullptr;
-    auto t_prev = std::chrono::steady_clock::now();
-    auto mark = [&](const char *what) {
-        if (!timing) return;
-        const auto now = std::chrono::steady_clock::now();
-        fprintf(stderr, "[mmb timing]   host: %s %.3f ms\n", what, 1e3 * std::chrono::duration<double>(now - t_prev).count());
-        t_prev = now;
-    };
-    mark("copy of the scene tables");
     // ---- validation ------------------------------------------------------
     for (int t = 0; t < hp.T; ++t) {
         if (hp.tfm_parent[t] >= t || hp.tfm_parent[t] < -1) { hp.error = "tfm_parent must precede child"; return MMB_ERR_INVALID_ARGUMENT; }
@@ -194,7 +225,67 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     for (int a = 0; a < hp.A; ++a)
         if (!ref_ok(hp.attr_ref[a], hp.num_static, hp.num_anim, false)) { hp.error = "bad solver attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
 
+    return MMB_OK;
+}
+
+mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
+                              HostProblem *hpp) {
+    HostProblem &hp = *hpp;
+    const bool timing = getenv("MMB_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto mark = [&](const char *what) {
+        if (!timing) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[mmb timing]   host: %s %.3f ms\n", what, 1e3 * std::chrono::duration<double>(now - t_prev).count());
+        t_prev = now;
+    };
+    {
+        const mmb_status cs = copy_scene_tables(s, opt, hpp);
+        if (cs != MMB_OK) return cs;
+    }
+    const size_t F = hp.F;
     mark("validation");
+    // ---- used / unused solve objects (solve_v1, adjust_base.cpp:1322-1395) ------------------
+    // markerToAttrList: marker i is affected by attribute j when j drives the marker's camera
+    // (transform chain, camera shape, lens) or its bundle's transform chain -- what
+    // findMarkerToAttributeRelationship (adjust_relationships.cpp:369-466) asks Maya's DG.
+    // splitUsedMarkersAndAttributes (adjust_base.cpp:574-610): a marker affected by no attribute
+    // and an attribute affecting no marker are dropped from the solve when the
+    // removeUnused* options say so; the index maps then number the USED lists.
+    hp.M_in = hp.M; hp.A_in = hp.A;
+    hp.marker_used.assign(hp.M, 1); hp.attr_used.assign(hp.A, 1);
+    hp.mkr_src.resize(hp.M);
+    for (int i = 0; i < hp.M; ++i) hp.mkr_src[i] = i;
+    hp.attr_src.resize(hp.A);
+    for (int a = 0; a < hp.A; ++a) hp.attr_src[a] = a;
+    if (opt->remove_unused_markers || opt->remove_unused_attributes) {
+        std::vector<uint8_t> m_used, a_used;
+        marker_attr_usage(hp, nullptr, &m_used, &a_used);
+        hp.marker_used = m_used; hp.attr_used = a_used;
+        if (opt->remove_unused_markers) {
+            int k = 0;
+            for (int i = 0; i < hp.M; ++i)
+                if (m_used[i]) { hp.mkr_cam[k] = hp.mkr_cam[i]; hp.mkr_bnd[k] = hp.mkr_bnd[i]; hp.mkr_src[k] = i; ++k; }
+            hp.M = k;
+            hp.mkr_cam.resize(k); hp.mkr_bnd.resize(k); hp.mkr_src.resize(k);
+        } else {
+            hp.marker_used.assign(hp.M, 1);
+        }
+        if (opt->remove_unused_attributes) {
+            int k = 0;
+            for (int a = 0; a < hp.A; ++a)
+                if (a_used[a]) {
+                    hp.attr_ref[k] = hp.attr_ref[a]; hp.attr_min[k] = hp.attr_min[a]; hp.attr_max[k] = hp.attr_max[a];
+                    hp.attr_off[k] = hp.attr_off[a]; hp.attr_scl[k] = hp.attr_scl[a]; hp.attr_src[k] = a; ++k;
+                }
+            hp.A = k;
+            hp.attr_ref.resize(k); hp.attr_min.resize(k); hp.attr_max.resize(k); hp.attr_off.resize(k); hp.attr_scl.resize(k);
+            hp.attr_src.resize(k);
+        } else {
+            hp.attr_used.assign(hp.A, 1);
+        }
+    }
+    mark("used / unused objects");
     // ---- countUpNumberOfErrors (marker-major, frame-minor) ---------------
     std::vector<double> wmax(F, 0.0);
     std::vector<uint8_t> wseen(F, 0);
@@ -210,13 +301,15 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         std::vector<std::vector<uint8_t>> tseen(T, std::vector<uint8_t>(F, 0));
         auto range = [&](int t, size_t *m0, size_t *m1) { *m0 = M * t / T; *m1 = M * (t + 1) / T; };
         auto enabled = [&](size_t o) { return s->mkr_enable[o] != 0 && (s->mkr_weight[o] > 0.0); };
+        const std::vector<int32_t> &src = hp.mkr_src;  // row of marker i in the caller's tables
         // one set of threads for both passes: count, meet, (thread 0: prefix sums and the
         // uninitialised resize), meet, fill
         std::atomic<int> arrived{0}, released{0};
         auto body = [&](int t) {
             size_t m0, m1, k = 0;
             range(t, &m0, &m1);
-            for (size_t o = m0 * F; o < m1 * F; ++o) k += enabled(o) ? 1 : 0;
+            for (size_t i = m0; i < m1; ++i)
+                for (size_t o = (size_t)src[i] * F, e = o + F; o < e; ++o) k += enabled(o) ? 1 : 0;
             count[t + 1] = k;
             arrived.fetch_add(1, std::memory_order_acq_rel);
             if (t == 0) {
@@ -233,7 +326,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
             std::vector<double> &wm = twmax[t];
             std::vector<uint8_t> &ws = tseen[t];
             for (size_t i = m0; i < m1; ++i) {
-                const size_t o0 = i * F;
+                const size_t o0 = (size_t)src[i] * F;
                 for (size_t j = 0; j < F; ++j) {
                     const size_t o = o0 + j;
                     if (!enabled(o)) continue;

@@ -62,6 +62,10 @@ struct HostProblem {
     std::vector<int32_t> attr_ref;
     std::vector<double> attr_min, attr_max, attr_off, attr_scl;
 
+    // ---- used / unused split (adjust_base.cpp:574-610) -------------------
+    int M_in = 0, A_in = 0;                       // markers / attributes the caller passed
+    std::vector<uint8_t> marker_used, attr_used;  // [M_in], [A_in]
+    std::vector<int32_t> mkr_src, attr_src;       // used marker / attr -> index in the caller's lists
     // ---- index maps (adjust_relationships.cpp) --------------------------
     int n = 0, nobs = 0, m = 0;
     RawVec<int32_t> err_marker, err_frame;   // errorToMarkerList
@@ -112,6 +116,13 @@ struct HostProblem {
 // Build everything above from a scene description. Returns MMB_OK or error.
 mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
                               HostProblem *hp);
+
+// findMarkerToAttributeRelationship (adjust_relationships.cpp:369-466) on the copied scene
+// tables of hp, before any removal: table [M*A] (may be NULL), used flags
+void marker_attr_usage(const HostProblem &hp, std::vector<uint8_t> *table, std::vector<uint8_t> *marker_used,
+                       std::vector<uint8_t> *attr_used);
+// copy + validate the scene tables only (what marker_attr_usage needs)
+mmb_status copy_scene_tables(const mmb_scene_desc *s, const mmb_options *opt, HostProblem *hp);
 
 // adjust_base.cpp:194-258 on the host (used for initial parameters / output)
 double bound_internal_to_external(double v, double mn, double mx, double off, double scl);

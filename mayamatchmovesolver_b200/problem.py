@@ -225,6 +225,18 @@ class Problem:
               "mmb_get_index_maps")
         return e2m, p2a
 
+    def used_objects(self):
+        """-> (used_marker_index, used_attr_index): position in the scene's marker / attr lists of
+        every marker / attribute that takes part (removeUnusedMarkers / removeUnusedAttributes,
+        adjust_base.cpp:1322-1395); index_maps() numbers these used lists"""
+        nm, na = C.c_int32(), C.c_int32()
+        check(self._lib.mmb_problem_used_objects(self._h, C.byref(nm), None, C.byref(na), None), "mmb_problem_used_objects")
+        mi = np.zeros(nm.value, np.int32)
+        ai = np.zeros(na.value, np.int32)
+        check(self._lib.mmb_problem_used_objects(self._h, C.byref(nm), mi.ctypes.data_as(c_i32p), C.byref(na),
+                                                 ai.ctypes.data_as(c_i32p)), "mmb_problem_used_objects")
+        return mi, ai
+
     def marker_weights(self):
         w = np.zeros(self.nobs)
         check(self._lib.mmb_get_marker_weights(self._h, w.ctypes.data_as(c_f64p)), "mmb_get_marker_weights")
@@ -235,11 +247,12 @@ class Problem:
         check(self._lib.mmb_get_initial_parameters(self._h, x.ctypes.data_as(c_f64p)), "mmb_get_initial_parameters")
         return x
 
-    def eval_residuals(self, x):
-        x = np.ascontiguousarray(x, dtype=np.float64)
+    def eval_residuals(self, x=None):
+        """x = None: the scene at its own attribute values (no parameter applied)"""
+        x = None if x is None else np.ascontiguousarray(x, dtype=np.float64)
         fvec = np.zeros(self.m)
         dist = np.zeros(self.nobs)
-        check(self._lib.mmb_eval_residuals(self._h, x.ctypes.data_as(c_f64p), fvec.ctypes.data_as(c_f64p),
+        check(self._lib.mmb_eval_residuals(self._h, None if x is None else x.ctypes.data_as(c_f64p), fvec.ctypes.data_as(c_f64p),
                                            dist.ctypes.data_as(c_f64p)), "mmb_eval_residuals")
         return fvec, dist
 
@@ -321,3 +334,18 @@ class Problem:
         a, b = C.c_int64(), C.c_int64()
         check(self._lib.mmb_solve_stats(self._h, C.byref(a), C.byref(b)), "mmb_solve_stats")
         return a.value, b.value
+
+
+def affects(scene):
+    """findMarkerToAttributeRelationship (adjust_relationships.cpp:369-466) of a scene:
+    -> (marker_affects_attr [M, A] bool, marker_used [M] bool, attr_used [A] bool).  Host only."""
+    lib = _capi.load()
+    desc, keep = scene.desc()
+    M, A = desc.num_markers, desc.num_attrs
+    table = np.zeros((M, max(A, 1)), np.uint8)
+    mu = np.zeros(M, np.uint8)
+    au = np.zeros(max(A, 1), np.uint8)
+    u8 = C.POINTER(C.c_uint8)
+    check(lib.mmb_affects(C.byref(desc), table.ctypes.data_as(u8) if A else None, mu.ctypes.data_as(u8),
+                          au.ctypes.data_as(u8)), "mmb_affects")
+    return table[:, :A].astype(bool), mu.astype(bool), au[:A].astype(bool)

@@ -168,6 +168,22 @@ class SceneBuilder:
         self.attr_scl.append(1.0 if scale is None else float(scale))
         return len(self.attr_ref) - 1
 
+    def keep_markers(self, indices):
+        """Drop every marker that is not listed (the command's `-marker` flags name the markers
+        of the solve; the others are not part of markerList at all)."""
+        self._arrays_cache = None
+        keep = list(dict.fromkeys(int(i) for i in indices))   # the flag order, as markerList has it
+        new_index = {old: new for new, old in enumerate(keep)}
+        for name in ("mkr_cam", "mkr_bnd", "mkr_x", "mkr_y", "mkr_w", "mkr_en"):
+            lst = getattr(self, name)
+            setattr(self, name, [lst[i] for i in keep])
+        for key in [k for k, n in self.names.items() if n.kind == "marker"]:
+            node = self.names[key]
+            if node.index in new_index:
+                node.index = new_index[node.index]
+            else:
+                del self.names[key]
+
     def slice_frames(self, frame_indices):
         """A copy of the scene restricted to some frames (what solve_v1 hands to
         solveFrames for one entry of its per-frame loop, adjust_base.cpp:1447)."""

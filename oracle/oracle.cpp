@@ -179,8 +179,16 @@ int orc_create(const mmb_scene_desc *s, const mmb_options *opt, orc_problem **ou
     p->attr_max.assign(s->attr_max, s->attr_max + p->A);
     p->attr_off.assign(s->attr_offset, s->attr_offset + p->A);
     p->attr_scl.assign(s->attr_scale, s->attr_scale + p->A);
+    split_used_objects(p);
     build_index_maps(p);
     *out = p;
+    return MMB_OK;
+}
+
+// which of the caller's markers / attributes take part (solve_v1's used / unused split)
+int orc_used_objects(const orc_problem *p, uint8_t *marker_used, uint8_t *attr_used) {
+    if (marker_used) for (size_t i = 0; i < p->marker_used_in.size(); ++i) marker_used[i] = p->marker_used_in[i];
+    if (attr_used) for (size_t i = 0; i < p->attr_used_in.size(); ++i) attr_used[i] = p->attr_used_in[i];
     return MMB_OK;
 }
 

@@ -62,6 +62,7 @@ struct orc_problem {
     std::vector<double> out_points, out_markers;  // flat.rs out_*_list [M*F*2]
     std::vector<M4> world;                       // [T*F]
     int iterNum = 0, jacIterNum = 0, funcEvalNum = 0;
+    std::vector<uint8_t> marker_used_in, attr_used_in;  // per marker / attribute of the caller's lists
     bool faithful_eval = true;  // evaluate whole scene on every call
     bool central_literal = false;  // see func_jacobian
 };
@@ -139,6 +140,51 @@ static bool marker_uses_ref(const orc_problem *p, int mk, int32_t ref) {
         for (int k = 0; k < MMB_LENS_MAX_COEFFS; ++k)
             if (p->lens_attrs[l * MMB_LENS_MAX_COEFFS + k] == ref) return true;
     return false;
+}
+
+// solve_v1 (adjust_base.cpp:1322-1395): markerToAttrList, then
+// splitUsedMarkersAndAttributes (adjust_base.cpp:574-610, count maps as there) and the
+// removal of the unused objects when removeUnusedMarkers / removeUnusedAttributes are set.
+static void split_used_objects(orc_problem *p) {
+    const int M = p->M, A = p->A, F = p->F;
+    p->marker_used_in.assign(M, 1); p->attr_used_in.assign(A, 1);
+    if (!p->opt.remove_unused_markers && !p->opt.remove_unused_attributes) return;
+    std::map<size_t, int> markerIndexUsedCount, attrIndexUsedCount;
+    for (int markerIndex = 0; markerIndex < M; ++markerIndex)
+        for (int attrIndex = 0; attrIndex < A; ++attrIndex)
+            if (marker_uses_ref(p, markerIndex, p->attr_ref[attrIndex])) {
+                markerIndexUsedCount[markerIndex] += 1;
+                attrIndexUsedCount[attrIndex] += 1;
+            }
+    if (p->opt.remove_unused_markers) {
+        int k = 0;
+        for (int i = 0; i < M; ++i) {
+            const bool used = markerIndexUsedCount.count(i) && markerIndexUsedCount[i] > 0;
+            p->marker_used_in[i] = used;
+            if (!used) continue;
+            p->mkr_cam[k] = p->mkr_cam[i]; p->mkr_bnd[k] = p->mkr_bnd[i];
+            for (int f = 0; f < F; ++f) {
+                p->mkr_x[(size_t)k * F + f] = p->mkr_x[(size_t)i * F + f];
+                p->mkr_y[(size_t)k * F + f] = p->mkr_y[(size_t)i * F + f];
+                p->mkr_w[(size_t)k * F + f] = p->mkr_w[(size_t)i * F + f];
+                p->mkr_en[(size_t)k * F + f] = p->mkr_en[(size_t)i * F + f];
+            }
+            ++k;
+        }
+        p->M = k;
+    }
+    if (p->opt.remove_unused_attributes) {
+        int k = 0;
+        for (int a = 0; a < A; ++a) {
+            const bool used = attrIndexUsedCount.count(a) && attrIndexUsedCount[a] > 0;
+            p->attr_used_in[a] = used;
+            if (!used) continue;
+            p->attr_ref[k] = p->attr_ref[a]; p->attr_min[k] = p->attr_min[a]; p->attr_max[k] = p->attr_max[a];
+            p->attr_off[k] = p->attr_off[a]; p->attr_scl[k] = p->attr_scl[a];
+            ++k;
+        }
+        p->A = k;
+    }
 }
 
 static void build_index_maps(orc_problem *p) {

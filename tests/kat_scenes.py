@@ -123,7 +123,7 @@ KATS = {
 }
 
 
-def apply_bounds(sb, info, near=True, lower_only=True):
+def apply_bounds(sb, info, near=True, lower_only=True, scale_with_bounds=True):
     """Box constraints / offset / scale on the solver attributes of a synth.make_scene scene
     (`-attr node.attr min max offset scale`, arg_flags_solve_object.cpp:288-318): every
     branch of parameterBoundFromInternalToExternal (adjust_base.cpp:194-258) and, with
@@ -151,16 +151,19 @@ def apply_bounds(sb, info, near=True, lower_only=True):
     if lower_only:  # the external value is pinned at min (formula as written): a zero Jacobian column
         v = vals(cam["tz"]); setb(cam["tz"], mn=v.min() - 2.0)
     setb(cam["rx"], off=0.5, scl=2.0)                                                        # offset / scale, no bounds
-    v = vals(cam["ry"]); setb(cam["ry"], mn=v.min() - 10.0, mx=v.max() + 10.0, off=-1.0, scl=0.5)
+    # bounds AND offset / scale: the reference's two transforms are not inverses of each other
+    # then (external e comes back as e / scale - offset), so solves keep them apart
+    sws = scale_with_bounds
+    v = vals(cam["ry"]); setb(cam["ry"], mn=v.min() - 10.0, mx=v.max() + 10.0, off=-1.0 if sws else None, scl=0.5 if sws else None)
     for b, t in enumerate(info["bnd_tfms"]):
         if b % 3 == 0:
             v = vals(t["tx"]); setb(t["tx"], mn=v[0] - 1.0, mx=v[0] + 1.0)
         elif b % 3 == 1 and near:
-            # the INTERNAL value asin(..) = 1.37 is compared with the EXTERNAL bounds (as the
+            # the INTERNAL value asin(..) = 0.96 is compared with the EXTERNAL bounds (as the
             # reference does): wherever it exceeds max - delta the forward step flips to -delta
-            v = vals(t["ty"]); setb(t["ty"], mn=v[0] - 5.0, mx=v[0] + 0.05)
+            v = vals(t["ty"]); setb(t["ty"], mn=v[0] - 5.0, mx=v[0] + 0.5)
         else:
-            v = vals(t["tz"]); setb(t["tz"], mn=v[0] - 4.0, mx=v[0] + 4.0, scl=1.5)
+            v = vals(t["tz"]); setb(t["tz"], mn=v[0] - 4.0, mx=v[0] + 4.0, scl=1.5 if sws else None)
     return sb
 
 

@@ -37,6 +37,7 @@ def oracle():
         lib.orc_sizes.argtypes = [C.c_void_p, c_i32p, c_i32p, c_i32p]
         lib.orc_index_maps.argtypes = [C.c_void_p, c_i32p, c_i32p]
         lib.orc_weights.argtypes = [C.c_void_p, c_f64p]
+        lib.orc_used_objects.argtypes = [C.c_void_p, C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
         lib.orc_set_faithful.argtypes = [C.c_void_p, C.c_int]
         lib.orc_set_central_literal.argtypes = [C.c_void_p, C.c_int]
         lib.orc_initial_parameters.argtypes = [C.c_void_p, c_f64p]

@@ -104,7 +104,9 @@ def test_object_flags_select_markers_attrs_frames():
                                  ("bad", "flag")],
                            frame=[12, 10])
     assert list(out.frames) == [12, 10] and out.F == 2
-    assert [int(e.any()) for e in out.mkr_en] == [1, 0, 1]
+    # only the listed markers are part of the solve (markerList), in flag order
+    assert len(out.mkr_cam) == 2 and out.names["mkr0"].index == 0 and out.names["mkr2"].index == 1
+    assert "mkr1" not in out.names and out.mkr_bnd == [sb.names["bundle0"].index, sb.names["bundle2"].index]
     assert out.attr_ref == [sb.names["bnd0"]["tx"], sb.names["cam_tfm"]["tx"]]
     # non-numeric strings keep the defaults of maya_attr.cpp:88-91
     assert out.attr_min == [-FLT_MAX, -1.5] and out.attr_max == [FLT_MAX, 2.0]

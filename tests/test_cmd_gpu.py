@@ -43,8 +43,15 @@ def test_command_matches_problem_api_and_print_statistics():
     sb, _ = synth.make_scene(F=12, B=16, seed=9, fixed_bundles=3, period=12)
     with Problem(sb) as p:
         r0 = p.solve()
-    strings = mmSolver(sb, write_back=False, printStatistics=["inputs"], iterations=100, tauFactor=1.0, delta=1e-4)
-    assert strings[0] == "numberOfParameters=%d" % len(r0.x) and strings[1] == "numberOfErrors=%d" % (2 * len(r0.error_dist))
+    # printStatistics: the command reports and does NOT solve (constructPrintStats, adjust_base.cpp:618-646)
+    stats = mmSolver(sb, write_back=False, printStatistics=["inputs"])
+    assert stats[0] == "numberOfParameters=%d" % len(r0.x) and stats[1] == "numberOfErrors=%d" % (2 * len(r0.error_dist))
+    rs = solveresult.SolveResultStrings(stats)
+    assert rs.get_success() and rs.solver_stats["iteration_total_calls"] == 0
+    with Problem(sb) as p:
+        _, d0 = p.eval_residuals(None)
+    assert abs(rs.error_stats["final_average"] - d0.mean()) <= 1e-5 * d0.mean()   # the initial deviation
+    strings = mmSolver(sb, write_back=False, iterations=100, tauFactor=1.0, delta=1e-4)
     r = solveresult.SolveResultStrings(strings)
     assert r.solver_stats["stop_id"] == r0.reason_num and r.solver_stats["iteration_total_calls"] == r0.iteration_num
     assert abs(r.error_stats["final"] - r0.error_final) <= 1e-5 * r0.error_final     # 6 significant digits

@@ -40,7 +40,7 @@ def test_bounded_solve_matches_oracle(name):
     """whole LM solves with box constraints / offset / scale on the solver attributes
     (adjust_base.cpp:194-258): same LM decisions, solved values 1e-6 relative, errors 1e-6 px"""
     sb, info = synth.make_scene(**BOUNDED_SOLVES[name])
-    apply_bounds(sb, info, lower_only=False)
+    apply_bounds(sb, info, lower_only=False, scale_with_bounds=False)
     ro = OracleProblem(sb).solve()
     with Problem(sb) as p:
         r = p.solve()
@@ -59,7 +59,7 @@ def test_bounded_per_frame_solve_matches_oracle():
     """frameSolveMode = 1 with bounded / scaled camera attributes: the per-frame kernel's own
     copy of the bound transform and step logic against one oracle solve per frame"""
     sb, info = synth.make_scene(F=10, B=14, seed=2, solve_bundles=False, period=10)
-    apply_bounds(sb, info, lower_only=False)
+    apply_bounds(sb, info, lower_only=False, scale_with_bounds=False)
     with Problem(sb, frame_solve_mode=1) as p:
         agg, per = p.solve_per_frame()
     av = agg.attr_values.reshape(6, 10)
@@ -67,3 +67,45 @@ def test_bounded_per_frame_solve_matches_oracle():
         ro = OracleProblem(sb.slice_frames([f])).solve()
         assert per[f].reason_num == ro.reason_num and per[f].iteration_num == ro.iteration_num
         assert np.max(np.abs(av[:, f] - ro.attr_values) / np.maximum(np.abs(ro.attr_values), 1.0)) <= 1e-6
+
+
+@pytest.mark.parametrize("rum,rua", [(1, 1), (0, 0)])
+def test_unused_markers_and_attributes_on_the_device(rum, rua):
+    """removeUnusedMarkers / removeUnusedAttributes (solve_v1, adjust_base.cpp:1322-1395): a marker
+    affected by no attribute and an attribute affecting no marker leave the problem -- sizes, index
+    maps, residuals, Jacobian and the solve against the oracle's restatement."""
+    from test_affects_cpu import _scene
+    sb = _scene()
+    o = OracleProblem(sb, remove_unused_markers=rum, remove_unused_attributes=rua)
+    with Problem(sb, remove_unused_markers=rum, remove_unused_attributes=rua) as p:
+        assert (p.n, p.nobs) == (o.n, o.nobs)
+        e2m, p2a = p.index_maps()
+        oe2m, op2a = o.index_maps()
+        assert np.array_equal(e2m, oe2m) and np.array_equal(p2a, op2a)
+        used_m, used_a = p.used_objects()
+        assert used_m.tolist() == ([0, 1, 2] if rum else [0, 1, 2, 3]) and used_a.tolist() == ([0, 1, 3] if rua else [0, 1, 2, 3])
+        x = p.initial_parameters()
+        assert np.array_equal(x, o.initial_parameters())
+        f, d = p.eval_residuals(x)
+        fo, do = o.eval_residuals(x)
+        assert np.abs(f - fo).max() <= 1e-9 * np.abs(fo).max()
+        J = p.eval_jacobian_dense(x)
+        Jo = o.eval_jacobian_dense(x)
+        assert np.abs(J - Jo).max() <= 1e-9 * np.abs(Jo).max()
+        if rua:   # with the all-zero column of the unused attribute kept, J is rank deficient
+            r = p.solve()
+            ro = OracleProblem(sb, remove_unused_markers=rum, remove_unused_attributes=rua).solve()
+            assert (r.reason_num, r.iteration_num) == (ro.reason_num, ro.iteration_num)
+            assert np.max(np.abs(r.attr_values - ro.attr_values) / np.maximum(1.0, np.abs(ro.attr_values))) <= 1e-6
+            assert np.max(np.abs(r.error_dist - ro.error_dist)) <= 1e-6
+
+
+def test_print_statistics_used_objects_and_affects():
+    from test_affects_cpu import _scene
+    sb = _scene()
+    out = mmSolver(sb, printStatistics=["usedSolveObjects", "affects", "inputs"], write_back=False)
+    assert out[0] == "numberOfParameters=5" and out[1] == "numberOfErrors=18"
+    assert "markers_used=mA0#mA1#mB1#" in out and "markers_unused=mB2#" in out
+    assert "attributes_used=camA_tfm.tx#bnd0_tfm.tx#bnd1_tfm.ty#" in out and "attributes_unused=lonely.tx#" in out
+    assert "marker_affects_attribute=mB1#bnd1_tfm.ty#1" in out and "success=1" in out
+    assert not any(s.startswith("marker_affects_attribute=mB2") for s in out)   # only the used objects are listed

@@ -45,7 +45,7 @@ def test_rust_two_bundles_under_group_kat():
     for t in (ba, bb):
         sb.add_marker(cam, sb.add_bundle(t), 0.0, 0.0)
     sb.add_attr(ba["tx"])
-    o = OracleProblem(sb)
+    o = OracleProblem(sb, remove_unused_markers=0)   # the second marker is affected by no attribute
     f, d = o.eval_residuals(o.initial_parameters())
     # markers sit at (0,0): residuals are |point| * 2048
     pts = f.reshape(-1, 2) / 2048.0
