@@ -355,7 +355,9 @@ mmb_status mmb_format_results(const mmb_result *r, int32_t n_params,
                               const double *error_dist, int32_t flags,
                               char *buf, int64_t cap, int64_t *needed);
 
-/* MComputation::isInterruptRequested analogue; callable from another thread */
+/* MComputation::isInterruptRequested analogue; callable from another thread.
+ * Sharded solve: a request on ANY rank travels through the iteration's all-reduce
+ * and stops every rank at the end of the same LM iteration. */
 void mmb_request_cancel(mmb_problem *p);
 
 /* device-side benchmarking hooks (inputs already resident in HBM):

@@ -314,9 +314,11 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
 }
 
 // trial point: x2 = x - p; partial sums of pnorm^2 = ||D p||^2 and of ||D x2||^2
+// scal[2] carries this rank's cancel request through the trial's all-reduce, so that every rank
+// of a sharded solve leaves the loop at the same point (k_ctrl_accept)
 __global__ void __launch_bounds__(1024) k_ctrl_trial(LmDims d, LmState *st, const double *p_int, const int32_t *i2p,
                                                      const double *diag, const double *x, double *x2, double *p_par,
-                                                     double *scal) {
+                                                     double *scal, const int *cancel) {
     __shared__ double sh[32];
     double pE = 0.0, pS = 0.0, xE = 0.0, xS = 0.0;
     for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
@@ -331,6 +333,7 @@ __global__ void __launch_bounds__(1024) k_ctrl_trial(LmDims d, LmState *st, cons
     pE = block_sum(pE, sh); pS = block_sum(pS, sh); xE = block_sum(xE, sh); xS = block_sum(xS, sh);
     if (threadIdx.x == 0) {
         scal[0] = pE; scal[1] = xE;
+        scal[2] = *(const volatile int *)cancel ? 1.0 : 0.0;
         st->part_s[0] = pS; st->part_s[1] = xS;
     }
 }
@@ -389,6 +392,7 @@ __global__ void __launch_bounds__(1024) k_ctrl_accept(LmDims d, LmState *st, con
         if (st->gnorm <= epsmch) info = 8;
     }
     if (info != 0) { st->info = info; st->done = 1; }
+    if (scal[2] > 0.0) { st->cancelled = 1; st->done = 1; }   // some rank was asked to stop
     // next pass: a new Jacobian after an accepted step, else lmpar again
     st->need_jacobian = st->accepted;
     st->lmpar_iter = 0; st->lmpar_done = 0; st->par_cur = 0.0; st->chol_fail = 0;
@@ -868,14 +872,14 @@ static mmb_status enqueue_trial(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     const LmDims &d = w->d;
     cudaStream_t s = p->stream;
-    k_ctrl_trial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->i2p, w->diag, p->d_x, w->x2, w->p_par, w->scal);
+    k_ctrl_trial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->i2p, w->diag, p->d_x, w->x2, w->p_par, w->scal, w->d_cancel);
     LAUNCH_CHECK();
     mmb_status st = enqueue_residual_eval(p, w->x2, w->fvec2, w->dist2);
     if (st != MMB_OK) return st;
     k_jp_partial<<<kRedBlocks, 256, 0, s>>>(p->ds, d, p->d_jac, w->p_par, w->part_jp);
     LAUNCH_CHECK();
     // squared norms of the trial residual and of J p, ||D p||^2, ||D x2||^2: one all-reduce
-    if ((st = all_reduce(p, w->part_f, (size_t)2 * kRedBlocks + 2)) != MMB_OK) return st;
+    if ((st = all_reduce(p, w->part_f, (size_t)2 * kRedBlocks + 3)) != MMB_OK) return st;
     k_ctrl_accept<<<1, 1024, 0, s>>>(d, w->st, w->part_f, w->part_jp, kRedBlocks, w->scal);
     LAUNCH_CHECK();
     k_accept_copy<<<296, 256, 0, s>>>(w->st, (size_t)d.n, (size_t)d.m, (size_t)d.nobs, w->x2, p->d_x, w->fvec2, p->d_fvec, w->dist2, p->d_dist);
@@ -904,6 +908,9 @@ static mmb_status enqueue_prologue(DeviceProblem *p) {
         if ((st = enqueue_error_stats(p, p->d_dist, true)) != MMB_OK) return st;
     }
     if ((st = enqueue_residual_eval(p, p->d_x, p->d_fvec, p->d_dist)) != MMB_OK) return st;
+    // errorDistanceList of the last measureErrors call so far (the epilogue reads dist2: a solve
+    // that stops before its first Jacobian or trial must not report stale pool memory)
+    MMB_CUDA_CHECK(cudaMemcpyAsync(w->dist2, p->d_dist, sizeof(double) * (size_t)p->hp.nobs, cudaMemcpyDeviceToDevice, p->stream));
     if ((st = all_reduce(p, w->part_f, kRedBlocks)) != MMB_OK) return st;
     k_ctrl_init<<<1, 1024, 0, p->stream>>>(w->st, w->part_f, kRedBlocks);
     LAUNCH_CHECK();
@@ -1062,7 +1069,8 @@ static mmb_status lm_run_host_loop(DeviceProblem *p, mmb_result *res, double *t_
     *t_func += secs(t0, clk::now());
     int guard = 0;
     while (!w->h_st->done) {
-        if (p->cancel) { res->user_interrupted = 1; break; }
+        // a cancel request is seen by k_ctrl_trial and travels through the trial's all-reduce:
+        // every rank gets `done` in the same iteration (no rank-local exit between collectives)
         if (++guard > 100000) break;
         if (w->h_st->need_jacobian) {
             t0 = clk::now();
@@ -1175,8 +1183,8 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
         MMB_CUDA_CHECK(cudaMemcpyAsync(dist_out, w->dist2, sizeof(double) * hp.nobs, cudaMemcpyDeviceToHost, p->stream));
     if ((st = read_state(p)) != MMB_OK) return st;
     const LmState &f = *w->h_st;
+    if (f.cancelled) res->user_interrupted = 1;
     if (use_graph) {
-        if (f.cancelled) res->user_interrupted = 1;
         t_jac = 1e-9 * (double)f.t_jac_ns; t_lin = 1e-9 * (double)f.t_lin_ns; t_func = 1e-9 * (double)f.t_func_ns;
         p->launches += w->fixed_launches + (long long)f.n_body_loop * w->body_launches[0] +
                        (long long)f.njev * w->body_launches[1] + (long long)f.n_body_lmpar * w->body_launches[2] +

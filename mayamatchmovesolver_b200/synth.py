@@ -175,9 +175,12 @@ def witness_camera_paths(C, frames, focus=(0.0, 0.0, -22.0), radius=22.0, arc_de
 
 
 def make_multicam_scene(C, F, B, seed, frame_range=None, noise_px=0.5, init_noise_t=0.05, init_noise_r=0.2,
-                        init_noise_b=0.05, fixed_bundles=0, solve_camera=True, solve_bundles=True):
+                        init_noise_b=0.05, fixed_bundles=0, solve_camera=True, solve_bundles=True, visibility=1.0):
     """cfg5 shape: C witness cameras (animated, 6 attributes each solved per frame) all seeing
     the same B static bundles on every frame: M = C*B markers, Nobs = C*B*F.
+
+    `visibility` < 1: a Bernoulli(visibility) mask per (camera, bundle, frame) decides which
+    markers are enabled (cfg5 as SURVEY.md 8d words it: p = 0.25), seeded per absolute frame.
 
     `frame_range=(f0, f1)` generates only frames f0..f1-1 of the F-frame scene (this rank's
     shard, for Problem(..., local_slice=(f0, F))): truth bundles, start values of the static
@@ -222,6 +225,11 @@ def make_multicam_scene(C, F, B, seed, frame_range=None, noise_px=0.5, init_nois
         bnds.append(sb.add_bundle(tf))
     ones = np.ones(Fl)
     en = np.ones(Fl, np.uint8)
+    vis = None
+    if visibility < 1.0:
+        vis = np.zeros((Fl, C, B), np.uint8)
+        for i, fr in enumerate(frames):
+            vis[i] = np.random.default_rng([seed, 4, int(fr)]).uniform(size=(C, B)) < visibility
     for c in range(C):
         mx = np.zeros((B, Fl))
         my = np.zeros((B, Fl))
@@ -230,7 +238,7 @@ def make_multicam_scene(C, F, B, seed, frame_range=None, noise_px=0.5, init_nois
             mx[:, i] = x + nm[i, c, :, 0]
             my[:, i] = y + nm[i, c, :, 1]
         for b in range(B):
-            sb.add_marker(cams[c], bnds[b], mx[b], my[b], weight=ones, enable=en)
+            sb.add_marker(cams[c], bnds[b], mx[b], my[b], weight=ones, enable=en if vis is None else vis[:, c, b])
     if solve_camera:
         for tf in cam_tfms:
             for k in ("tx", "ty", "tz", "rx", "ry", "rz"):

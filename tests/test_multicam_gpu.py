@@ -108,3 +108,57 @@ def test_two_cameras_one_lens_interleaved_markers_match_oracle():
         vals, cols = p.eval_jacobian_blocks(x)
         fast = p.eval_jacobian_blocks(x, want_cols=False)
         assert np.abs(fast - vals).max() <= 1e-9 * np.abs(Jo).max()
+
+
+def _cfg5_sub():
+    # BASELINE.json configs[4] subsampled: 8 witness cameras, Bernoulli(0.25) visibility per
+    # (camera, bundle, frame) -> the sparse-visibility paths (explicit marker / frame indices)
+    return synth.make_multicam_scene(8, 64, 200, 5, visibility=0.25, fixed_bundles=6)
+
+
+def test_cfg5_subsample_residuals_and_jacobian_match_oracle():
+    sb, _ = _cfg5_sub()
+    o = OracleProblem(sb)
+    delta = 1e-4
+    with Problem(sb) as p:
+        assert (p.n, p.nobs) == (o.n, o.nobs) and 0.2 < p.nobs / (8 * 64 * 200) < 0.3
+        e2m, p2a = p.index_maps()
+        oe2m, op2a = o.index_maps()
+        assert np.array_equal(e2m, oe2m) and np.array_equal(p2a, op2a)
+        x = p.initial_parameters()
+        f, d = p.eval_residuals(x)
+        fo, do = o.eval_residuals(x)
+        assert np.abs(f - fo).max() <= 1e-9 * np.abs(fo).max()
+        assert np.abs(d - do).max() <= 1e-9 * np.abs(do).max()
+        vals, cols = p.eval_jacobian_blocks(x)
+        fast = p.eval_jacobian_blocks(x, want_cols=False)
+        n = p.n
+    scale = np.abs(vals).max()
+    assert np.abs(fast - vals).max() <= 1e-9 * scale
+    # Jacobian columns against forward differences of the ORACLE's residuals (built as
+    # adjust_solveFunc.cpp:305-479 builds them): camera attributes of several cameras / frames, bundles
+    F = 64
+    picks = [0, 63, 5 * F + 17, 6 * F + 3, (6 * 3 + 4) * F + 40, (6 * 7 + 5) * F + 63, 48 * F, 48 * F + 301, n - 1]
+    for pid in picks:
+        xa = x.copy(); xa[pid] += delta
+        fa, _ = o.eval_residuals(xa)
+        col_ref = (fa - fo) / delta
+        col = np.zeros(2 * len(cols))
+        for c in range(cols.shape[1]):
+            rows = np.nonzero(cols[:, c] == pid)[0]
+            col[2 * rows] = vals[c, 2 * rows]; col[2 * rows + 1] = vals[c, 2 * rows + 1]
+        assert np.abs(col - col_ref).max() <= 1e-9 * scale, (pid, np.abs(col - col_ref).max(), scale)
+
+
+def test_cfg5_subsample_solve_matches_block_sparse_oracle():
+    sb, _ = _cfg5_sub()
+    ro = OracleProblem(sb).solve_sparse(threads=8)
+    with Problem(sb) as p:
+        r = p.solve()
+    print("cfg5 subsample: oracle", ro, "gpu", r)
+    assert ro.status == 0
+    assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (ro.reason_num, ro.iteration_num, ro.iteration_attempt_num)
+    scale = np.maximum(np.abs(ro.attr_values), 1.0)
+    assert np.max(np.abs(r.attr_values - ro.attr_values) / scale) <= 1e-6
+    assert np.max(np.abs(r.error_dist - ro.error_dist)) <= 1e-6
+    assert abs(r.error_avg - ro.error_avg) <= 1e-6
