@@ -68,6 +68,14 @@ struct LmWorkspace {
     LmState *h_st = nullptr;   // pinned host mirror
     int32_t *attr_slot = nullptr, *i2p = nullptr;
     AsmShared asm_shared{};    // columns shared by every marker (k_assemble_shared)
+    // order-independent assembly (lm_kernels.cuh "order-independent accumulation")
+    unsigned long long *cmax = nullptr;   // [n + 1]
+    long long *det_limbs = nullptr;       // Ui | gEi | Vi | Wci, zeroed with one memset per Jacobian
+    size_t det_limb_count = 0;
+    int32_t *cs_of_slot = nullptr, *slot_of_cs = nullptr;
+    int ncs = 0;
+    int *poison = nullptr;
+    DetBufs det{};
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
     double *Dinv = nullptr;    // [NSP/64][64*64] inverses of the factor's diagonal blocks (k_chol_tiles phase E)
@@ -546,6 +554,7 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
                     for (int mk = 1; mk < hp.M && same; ++mk) same = hp.plan[(size_t)mk * hp.kmax + c].attr == a0;
                     if (same) {
                         as.col[as.ns] = c; as.slot[as.ns] = hp.attr_slot[a0]; as.anim[as.ns] = hp.attr_anim[a0] ? 1 : 0;
+                        as.pbase[as.ns] = hp.attr_param_base[a0];
                         as.mask |= 1u << c;
                         ++as.ns;
                     }
@@ -559,6 +568,45 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     }
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
+    {
+        // Which static columns of W collect three or more contributions per entry?  Entry
+        // (frame, animated slot a, static slot s) gets one per marker whose plan holds both.
+        std::vector<int32_t> cs_of_slot(std::max(d.ns, 1), -1), slot_of_cs;
+        if (d.ns && d.na) {
+            std::vector<int32_t> cnt((size_t)d.na * d.ns, 0);
+            std::vector<uint8_t> hot(d.ns, 0);
+            std::vector<int> as_, ss_;
+            for (int mk = 0; mk < hp.M; ++mk) {
+                as_.clear(); ss_.clear();
+                for (int c = 0; c < hp.mkr_k[mk]; ++c) {
+                    const int a = hp.plan[(size_t)mk * hp.kmax + c].attr;
+                    (hp.attr_anim[a] ? as_ : ss_).push_back(hp.attr_slot[a]);
+                }
+                for (int sl : ss_)
+                    for (int al : as_)
+                        if (++cnt[(size_t)al * d.ns + sl] >= 3) hot[sl] = 1;
+            }
+            for (int sl = 0; sl < d.ns; ++sl)
+                if (hot[sl]) { cs_of_slot[sl] = (int32_t)slot_of_cs.size(); slot_of_cs.push_back(sl); }
+        }
+        w->ncs = (int)slot_of_cs.size();
+        if (slot_of_cs.empty()) slot_of_cs.push_back(0);
+        CKW(A.upload(&w->cs_of_slot, cs_of_slot));
+        CKW(A.upload(&w->slot_of_cs, slot_of_cs));
+        const size_t nU = (size_t)d.F * d.na * d.na, nG = (size_t)d.KE, nV = (size_t)d.NSP * d.NSP, nW = (size_t)d.KE * w->ncs;
+        w->det_limb_count = 2 * (nU + nG + nV + nW);
+        CKW(A.alloc(&w->det_limbs, w->det_limb_count));
+        CKW(A.alloc(&w->cmax, (size_t)d.n + 1));
+        CKW(A.alloc(&w->poison, 1));
+        w->det.cmax = w->cmax;
+        w->det.Ui = w->det_limbs;
+        w->det.gEi = w->det.Ui + 2 * nU;
+        w->det.Vi = w->det.gEi + 2 * nG;
+        w->det.Wci = w->det.Vi + 2 * nV;
+        w->det.cs_of_slot = w->cs_of_slot;
+        w->det.ncs = w->ncs;
+        w->det.poison = w->poison;
+    }
     CKW(A.alloc(&w->U, (size_t)d.F * d.na * d.na));
     CKW(A.alloc(&w->gE, (size_t)d.KE));
     CKW(A.alloc(&w->W, (size_t)d.KE * d.NSP));
@@ -675,13 +723,14 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     mmb_status st;
     if ((st = launch_variants(p, p->d_x, true)) != MMB_OK) return st;
     if ((st = launch_jacobian(p, nullptr, nullptr, p->d_jac, nullptr, w->dist2)) != MMB_OK) return st;
-    if (d.KE) {
-        MMB_CUDA_CHECK(cudaMemsetAsync(w->U, 0, sizeof(double) * (size_t)d.F * d.na * d.na, p->stream));
-        MMB_CUDA_CHECK(cudaMemsetAsync(w->gE, 0, sizeof(double) * (size_t)d.KE, p->stream));
-        MMB_CUDA_CHECK(cudaMemsetAsync(w->W, 0, sizeof(double) * (size_t)d.KE * d.NSP, p->stream));
-    }
-    MMB_CUDA_CHECK(cudaMemsetAsync(w->V, 0, sizeof(double) * (size_t)d.NSP * d.NSP, p->stream));
-    k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->U, w->gE, w->W, w->V,
+    // column maxima -> the fixed-point grids; limbs and the plain-FP part of W start at zero
+    MMB_CUDA_CHECK(cudaMemsetAsync(w->cmax, 0, sizeof(unsigned long long) * ((size_t)d.n + 1), p->stream));
+    MMB_CUDA_CHECK(cudaMemsetAsync(w->poison, 0, sizeof(int), p->stream));
+    MMB_CUDA_CHECK(cudaMemsetAsync(w->det_limbs, 0, sizeof(long long) * w->det_limb_count, p->stream));
+    if (d.KE && d.ns) MMB_CUDA_CHECK(cudaMemsetAsync(w->W, 0, sizeof(double) * (size_t)d.KE * d.NSP, p->stream));
+    k_colmax<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->cmax);
+    LAUNCH_CHECK();
+    k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->det, w->W,
                                                             w->asm_shared.mask);
     if (w->asm_shared.ns) {
         LAUNCH_CHECK();
@@ -695,7 +744,7 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
 #define MMB_ASM_SHARED(NS_)                                                                                          \
     case NS_:                                                                                                        \
         k_assemble_shared<NS_><<<grid, 128, 0, p->stream>>>(w->asm_shared, d, hp.F, hp.M, mt, p->d_jac, p->d_fvec,   \
-                                                            w->U, w->gE, w->W, w->V);                                \
+                                                            w->det, w->W);                                           \
         break;
         switch (w->asm_shared.ns) {
             MMB_ASM_SHARED(6) MMB_ASM_SHARED(7) MMB_ASM_SHARED(9) MMB_ASM_SHARED(11) MMB_ASM_SHARED(13) MMB_ASM_SHARED(15)
@@ -704,6 +753,12 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
 #undef MMB_ASM_SHARED
     }
     LAUNCH_CHECK();
+    {
+        const size_t total = w->det_limb_count / 2;
+        k_assemble_finalize<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(d, w->det, w->slot_of_cs, w->i2p, w->U, w->gE,
+                                                                                    w->V, w->W);
+        LAUNCH_CHECK();
+    }
     if (d.ns) {
         k_prep_gather<<<(d.ns + 255) / 256, 256, 0, p->stream>>>(d, w->V, w->sdiag);
         LAUNCH_CHECK();
@@ -800,8 +855,19 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         int ksplit = 1;
         static int ks_target = -1;
         if (ks_target < 0) { const char *e = getenv("MMB_SYRK_CTAS"); ks_target = e ? atoi(e) : 2368; }
-        while (tiles * ksplit < ks_target && ksplit < 16 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
-        k_schur_syrk<<<dim3(tiles, ksplit), 128, 0, s>>>(d, w->Y, w->S);
+        // the K splits of a tile are one thread-block cluster (portable size <= 8)
+        while (tiles * ksplit < ks_target && ksplit < 8 && (d.KEP / kSyrkKT) / (ksplit * 2) >= 8) ksplit *= 2;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(tiles, ksplit);
+        cfg.blockDim = dim3(128);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = ksplit; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = ksplit > 1 ? 1 : 0;
+        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S));
         LAUNCH_CHECK();
     }
     if (sharded) {

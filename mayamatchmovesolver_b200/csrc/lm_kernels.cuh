@@ -54,12 +54,98 @@ struct AsmShared {
     int col[16];     // the shared columns
     int slot[16];    // their slot in the animated / static class
     int anim[16];
+    int pbase[16];   // first parameter of the column's solver attribute (+ frame when animated)
 };
+
+// ---- order-independent accumulation of the normal equations -------------------------------
+// J^T J and J^T f entries are sums of up to Nobs products whose order on the GPU depends on
+// the schedule.  Floating-point atomics made two runs of the same solve differ (1e-11
+// relative), and the LM iteration amplifies that.  Here every contribution is split into two
+// 64-bit fixed-point limbs on a per-entry grid and accumulated with INTEGER atomics, which
+// are associative: the sums, hence the whole solve, are bit-identical from run to run.
+//   grid of entry (p, q): bound 2^E >= |jx_p jx_q + jy_p jy_q| of one observation, from the
+//   column maxima cmax[] (k_colmax; cmax[n] = max |f| for the gradient entries);
+//   hi = rint(v / 2^(E-35)),  lo = rint((v - hi 2^(E-35)) / 2^(E-71)):  71 bits below the bound.
+//   Sums of partials over G observations stay below G 2^35 (hi) and 2^35 per add (lo):
+//   no overflow for Nobs < 2^27 per GPU.
+// Entries with at most two contributions (W of a camera attribute x a bundle attribute: one
+// marker) keep plain FP atomics onto zero: a + b = b + a.
+constexpr int kDetHi = 35, kDetLo = 36;
+constexpr int kDetEmax = 900;
+__device__ __forceinline__ double pow2i(int k) { return __longlong_as_double((long long)(k + 1023) << 52); }
+// exponent e with |x| < 2^e from the bit pattern of |x| (0 / denormal -> -1022, inf / nan -> 1025)
+__device__ __forceinline__ int det_exp_of(unsigned long long bits) { return (int)((bits >> 52) & 0x7ffull) - 1022; }
+__device__ __forceinline__ int det_exp(int ea, int eb) { return max(-kDetEmax, min(kDetEmax, ea + eb + 1)); }
+__device__ __forceinline__ void det_add(long long *acc, double v, int E, int *poison) {
+    if (v == 0.0) return;
+    const double h = rint(v * pow2i(kDetHi - E));
+    if (!(fabs(h) < 4.0e18)) { *poison = 1; return; }   // non-finite Jacobian entry (or beyond the bound)
+    const double r = fma(-h, pow2i(E - kDetHi), v);      // exact
+    const long long hi = (long long)h;
+    const long long lo = __double2ll_rn(r * pow2i(kDetHi + kDetLo - E));
+    if (hi) atomicAdd(reinterpret_cast<unsigned long long *>(acc), (unsigned long long)hi);
+    if (lo) atomicAdd(reinterpret_cast<unsigned long long *>(acc) + 1, (unsigned long long)lo);
+}
+__device__ __forceinline__ double det_value(const long long *acc, int E) {
+    return fma((double)acc[0], pow2i(E - kDetHi), (double)acc[1] * pow2i(E - kDetHi - kDetLo));
+}
+
+struct DetBufs {
+    const unsigned long long *cmax;  // [n + 1] bit patterns of the column maxima, [n] = max |f|
+    long long *Ui, *gEi, *Vi, *Wci;  // two limbs per entry; Wci [KE][ncs] (contended static columns of W)
+    const int32_t *cs_of_slot;       // [ns] static slot -> contended column index or -1
+    int ncs;
+    int *poison;
+};
+
+// column maxima: cmax[pid] = max over the observations of max(|jx|, |jy|); cmax[n] = max |f|
+__global__ void __launch_bounds__(256) k_colmax(DevScene s, LmDims d, const double *__restrict__ jac,
+                                                const double *__restrict__ fvec, unsigned long long *cmax) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i < s.nobs;
+    int marker = -1, frame = 0;
+    if (live) {
+        if (s.dense_grid) { marker = i / s.F; frame = i - marker * s.F; }
+        else { marker = s.err_marker[i]; frame = s.err_frame[i]; }
+    }
+    const int m0 = __shfl_sync(0xffffffffu, marker, 0);
+    const bool uniform = __all_sync(0xffffffffu, marker == m0 || !live) && m0 >= 0;
+    const int lane = threadIdx.x & 31;
+    const int pm = live ? marker : (uniform ? m0 : 0);
+    const int k = (live || uniform) ? s.mkr_k[pm] : 0;
+    const PlanEntryD *pl = s.plan + (size_t)pm * s.kmax;
+    const size_t m = (size_t)d.m;
+    double fa = live ? fmax(fabs(fvec[2 * (size_t)i]), fabs(fvec[2 * (size_t)i + 1])) : 0.0;
+    if (live && (fvec[2 * (size_t)i] != fvec[2 * (size_t)i] || fvec[2 * (size_t)i + 1] != fvec[2 * (size_t)i + 1]))
+        fa = __longlong_as_double(0x7ff8000000000000ll);
+    for (int c = 0; c < k; ++c) {
+        const int a = pl[c].attr;
+        const bool an = s.attr_anim[a];
+        double v = 0.0;
+        if (live) {
+            const double jx = jac[(size_t)c * m + 2 * (size_t)i], jy = jac[(size_t)c * m + 2 * (size_t)i + 1];
+            v = (jx != jx || jy != jy) ? __longlong_as_double(0x7ff8000000000000ll) : fmax(fabs(jx), fabs(jy));
+        }
+        if (!an && uniform) {
+            // one static parameter for the whole warp
+            unsigned long long b = (unsigned long long)__double_as_longlong(v);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, b, o); b = t > b ? t : b; }
+            if (lane == 0 && b) atomicMax(&cmax[s.attr_param_base[a]], b);
+        } else if (live && v != 0.0) {
+            atomicMax(&cmax[s.attr_param_base[a] + (an ? frame : 0)], (unsigned long long)__double_as_longlong(v));
+        }
+    }
+    unsigned long long fb = (unsigned long long)__double_as_longlong(fa);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, fb, o); fb = t > fb ? t : fb; }
+    if (lane == 0 && fb) atomicMax(&cmax[d.n], fb);
+}
 
 __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const double *__restrict__ jac,
                                                   const double *__restrict__ fvec,
-                                                  const int32_t *__restrict__ attr_slot, double *U, double *gE,
-                                                  double *W, double *V, unsigned shared_mask) {
+                                                  const int32_t *__restrict__ attr_slot, DetBufs db, double *W,
+                                                  unsigned shared_mask) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = i < s.nobs;
     int marker = -1, frame = 0;
@@ -76,49 +162,55 @@ __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const do
     const PlanEntryD *pl = s.plan + (size_t)pm * s.kmax;
     const size_t m = (size_t)d.m;
     const double fx = live ? fvec[2 * (size_t)i] : 0.0, fy = live ? fvec[2 * (size_t)i + 1] : 0.0;
+    const int ef = det_exp_of(db.cmax[d.n]);
     for (int c1 = 0; c1 < k; ++c1) {
         const int a1 = pl[c1].attr;
         const bool an1 = s.attr_anim[a1];
         const int s1 = attr_slot[a1];
+        const int e1 = det_exp_of(db.cmax[s.attr_param_base[a1] + (an1 ? frame : 0)]);
         const double jx1 = live ? jac[(size_t)c1 * m + 2 * (size_t)i] : 0.0;
         const double jy1 = live ? jac[(size_t)c1 * m + 2 * (size_t)i + 1] : 0.0;
         const bool sh1 = (shared_mask >> c1) & 1u;
         // gradient
         const double gv = jx1 * fx + jy1 * fy;
+        const int eg = det_exp(e1, ef);
         if (sh1) {
         } else if (an1) {
-            if (live) atomicAdd(&gE[(size_t)frame * d.na + s1], gv);
+            if (live) det_add(&db.gEi[2 * ((size_t)frame * d.na + s1)], gv, eg, db.poison);
         } else if (uniform) {
             const double r = warp_sum(gv);
-            if (lane == 0) atomicAdd(&V[(size_t)d.ns * d.NSP + s1], r);
+            if (lane == 0) det_add(&db.Vi[2 * ((size_t)d.ns * d.NSP + s1)], r, eg, db.poison);
         } else if (live) {
-            atomicAdd(&V[(size_t)d.ns * d.NSP + s1], gv);
+            det_add(&db.Vi[2 * ((size_t)d.ns * d.NSP + s1)], gv, eg, db.poison);
         }
         for (int c2 = 0; c2 <= c1; ++c2) {
             if (sh1 && ((shared_mask >> c2) & 1u)) continue;
             const int a2 = pl[c2].attr;
             const bool an2 = s.attr_anim[a2];
             const int s2 = attr_slot[a2];
+            const int E = det_exp(e1, det_exp_of(db.cmax[s.attr_param_base[a2] + (an2 ? frame : 0)]));
             const double jx2 = live ? jac[(size_t)c2 * m + 2 * (size_t)i] : 0.0;
             const double jy2 = live ? jac[(size_t)c2 * m + 2 * (size_t)i + 1] : 0.0;
             const double v = jx1 * jx2 + jy1 * jy2;
             if (an1 && an2) {
                 if (live) {
                     const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
-                    atomicAdd(&U[((size_t)frame * d.na + r) * d.na + cc], v);
+                    det_add(&db.Ui[2 * (((size_t)frame * d.na + r) * d.na + cc)], v, E, db.poison);
                 }
             } else if (an1 != an2) {
                 if (live) {
                     const int ja = an1 ? s1 : s2, js = an1 ? s2 : s1;
-                    atomicAdd(&W[((size_t)frame * d.na + ja) * d.NSP + js], v);
+                    const int cs = db.cs_of_slot[js];
+                    if (cs >= 0) det_add(&db.Wci[2 * (((size_t)frame * d.na + ja) * db.ncs + cs)], v, E, db.poison);
+                    else atomicAdd(&W[((size_t)frame * d.na + ja) * d.NSP + js], v);   // <= 2 contributions
                 }
             } else {
                 const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
                 if (uniform) {
                     const double t = warp_sum(v);
-                    if (lane == 0) atomicAdd(&V[(size_t)r * d.NSP + cc], t);
+                    if (lane == 0) det_add(&db.Vi[2 * ((size_t)r * d.NSP + cc)], t, E, db.poison);
                 } else if (live) {
-                    atomicAdd(&V[(size_t)r * d.NSP + cc], v);
+                    det_add(&db.Vi[2 * ((size_t)r * d.NSP + cc)], v, E, db.poison);
                 }
             }
         }
@@ -134,7 +226,7 @@ __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const do
 template <int NS, int WID>
 __device__ __forceinline__ void assemble_shared_body(const AsmShared &sh, const LmDims &d, const double2 *__restrict__ jac2,
                                                      const double2 *__restrict__ f2, int F, int frame, bool live,
-                                                     int m_begin, int m_end, double *U, double *gE, double *W, double *V) {
+                                                     int m_begin, int m_end, const DetBufs &db, double *W) {
     constexpr int P = NS * (NS + 1) / 2 + NS;   // pairs (c1 >= c2) then gradient entries
     constexpr int PW = (P + 3) / 4;             // sums per warp
     constexpr int P0 = WID * PW, P1 = (P0 + PW < P) ? P0 + PW : P;
@@ -159,6 +251,10 @@ __device__ __forceinline__ void assemble_shared_body(const AsmShared &sh, const 
             if (pidx >= P0 && pidx < P1) acc[pidx - P0] = fma(jv[c1].x, fv.x, fma(jv[c1].y, fv.y, acc[pidx - P0]));
     }
     const int lane = threadIdx.x & 31;
+    const int ef = det_exp_of(db.cmax[d.n]);
+    int ex[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) ex[c] = det_exp_of(db.cmax[sh.pbase[c] + (sh.anim[c] ? frame : 0)]);
     int pidx = 0;
 #pragma unroll
     for (int c1 = 0; c1 < NS; ++c1)
@@ -168,27 +264,33 @@ __device__ __forceinline__ void assemble_shared_body(const AsmShared &sh, const 
                 const double v = acc[pidx - P0];
                 const int s1 = sh.slot[c1], s2 = sh.slot[c2];
                 const bool an1 = sh.anim[c1], an2 = sh.anim[c2];
+                const int E = det_exp(ex[c1], ex[c2]);
                 if (an1 && an2) {
                     const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
-                    if (live) atomicAdd(&U[((size_t)frame * d.na + r) * d.na + cc], v);
+                    if (live) det_add(&db.Ui[2 * (((size_t)frame * d.na + r) * d.na + cc)], v, E, db.poison);
                 } else if (an1 != an2) {
                     const int ja = an1 ? s1 : s2, js = an1 ? s2 : s1;
-                    if (live) atomicAdd(&W[((size_t)frame * d.na + ja) * d.NSP + js], v);
+                    if (live) {
+                        const int cs = db.cs_of_slot[js];
+                        if (cs >= 0) det_add(&db.Wci[2 * (((size_t)frame * d.na + ja) * db.ncs + cs)], v, E, db.poison);
+                        else atomicAdd(&W[((size_t)frame * d.na + ja) * d.NSP + js], v);
+                    }
                 } else {
                     const int r = s1 > s2 ? s1 : s2, cc = s1 > s2 ? s2 : s1;
                     const double t = warp_sum(v);
-                    if (lane == 0) atomicAdd(&V[(size_t)r * d.NSP + cc], t);
+                    if (lane == 0) det_add(&db.Vi[2 * ((size_t)r * d.NSP + cc)], t, E, db.poison);
                 }
             }
 #pragma unroll
     for (int c1 = 0; c1 < NS; ++c1, ++pidx)
         if (pidx >= P0 && pidx < P1) {
             const double v = acc[pidx - P0];
+            const int E = det_exp(ex[c1], ef);
             if (sh.anim[c1]) {
-                if (live) atomicAdd(&gE[(size_t)frame * d.na + sh.slot[c1]], v);
+                if (live) det_add(&db.gEi[2 * ((size_t)frame * d.na + sh.slot[c1])], v, E, db.poison);
             } else {
                 const double t = warp_sum(v);
-                if (lane == 0) atomicAdd(&V[(size_t)d.ns * d.NSP + sh.slot[c1]], t);
+                if (lane == 0) det_add(&db.Vi[2 * ((size_t)d.ns * d.NSP + sh.slot[c1])], t, E, db.poison);
             }
         }
 }
@@ -196,7 +298,7 @@ __device__ __forceinline__ void assemble_shared_body(const AsmShared &sh, const 
 template <int NS>
 __global__ void __launch_bounds__(128) k_assemble_shared(AsmShared sh, LmDims d, int F, int M, int mt,
                                                          const double *__restrict__ jac, const double *__restrict__ fvec,
-                                                         double *U, double *gE, double *W, double *V) {
+                                                         DetBufs db, double *W) {
     const int frame = blockIdx.x * 32 + (threadIdx.x & 31);
     const bool live = frame < F;
     const int m_begin = blockIdx.y * mt, m_end = min(M, m_begin + mt);
@@ -204,10 +306,63 @@ __global__ void __launch_bounds__(128) k_assemble_shared(AsmShared sh, LmDims d,
     const double2 *f2 = reinterpret_cast<const double2 *>(fvec);
     const int fr = live ? frame : 0;
     switch (threadIdx.x >> 5) {
-        case 0: assemble_shared_body<NS, 0>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
-        case 1: assemble_shared_body<NS, 1>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
-        case 2: assemble_shared_body<NS, 2>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
-        default: assemble_shared_body<NS, 3>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, U, gE, W, V); break;
+        case 0: assemble_shared_body<NS, 0>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, db, W); break;
+        case 1: assemble_shared_body<NS, 1>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, db, W); break;
+        case 2: assemble_shared_body<NS, 2>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, db, W); break;
+        default: assemble_shared_body<NS, 3>(sh, d, jac2, f2, F, fr, live, m_begin, m_end, db, W); break;
+    }
+}
+
+// Limbs -> FP64: U (lower triangles), gE, V (lower triangle + right-hand side row ns, the rest
+// zero) and the contended static columns of W.  One thread per entry of the four regions.
+__global__ void __launch_bounds__(256) k_assemble_finalize(LmDims d, DetBufs db, const int32_t *__restrict__ slot_of_cs,
+                                                           const int32_t *__restrict__ i2p, double *__restrict__ U,
+                                                           double *__restrict__ gE, double *__restrict__ V,
+                                                           double *__restrict__ W) {
+    const size_t nU = (size_t)d.F * d.na * d.na, nG = (size_t)d.KE, nV = (size_t)d.NSP * d.NSP, nW = (size_t)d.KE * db.ncs;
+    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const bool bad = *db.poison != 0;
+    const double nan = __longlong_as_double(0x7ff8000000000000ll);
+    const int ef = det_exp_of(db.cmax[d.n]);
+    auto ex = [&](int q_int) { return det_exp_of(db.cmax[i2p[q_int]]); };
+    if (t < nU) {
+        const int f = (int)(t / ((size_t)d.na * d.na)), rc = (int)(t - (size_t)f * d.na * d.na);
+        const int r = rc / d.na, c = rc - r * d.na;
+        double v = 0.0;
+        if (c <= r) {
+            const long long *a = &db.Ui[2 * t];
+            if (a[0] | a[1]) v = det_value(a, det_exp(ex(f * d.na + r), ex(f * d.na + c)));
+            if (bad) v = nan;
+        }
+        U[t] = v;
+        return;
+    }
+    t -= nU;
+    if (t < nG) {
+        const long long *a = &db.gEi[2 * t];
+        double v = (a[0] | a[1]) ? det_value(a, det_exp(ex((int)t), ef)) : 0.0;
+        gE[t] = bad ? nan : v;
+        return;
+    }
+    t -= nG;
+    if (t < nV) {
+        const int r = (int)(t / d.NSP), c = (int)(t - (size_t)r * d.NSP);
+        double v = 0.0;
+        if (c <= r && r <= d.ns && c < d.ns) {
+            const long long *a = &db.Vi[2 * t];
+            if (a[0] | a[1]) v = det_value(a, det_exp(ex(d.KE + c), r < d.ns ? ex(d.KE + r) : ef));
+            if (bad) v = nan;
+        }
+        V[t] = v;
+        return;
+    }
+    t -= nV;
+    if (t < nW) {
+        const size_t row = t / db.ncs;
+        const int cs = (int)(t - row * db.ncs), js = slot_of_cs[cs];
+        const long long *a = &db.Wci[2 * t];
+        double v = (a[0] | a[1]) ? det_value(a, det_exp(ex((int)row), ex(d.KE + js))) : 0.0;
+        W[row * d.NSP + js] = bad ? nan : v;
     }
 }
 
@@ -466,12 +621,16 @@ __device__ __forceinline__ void tile_index(int t, int &bi, int &bj) {
 }
 
 // S(lower tiles) -= Y^T Y, Y is [KEP][NSP] row-major (k-major operands).
-// grid.x = lower-triangle tiles of the NSP/64 block grid; grid.y = K splits
-// (partial sums are subtracted with atomics only when grid.y > 1).
+// grid.x = lower-triangle tiles of the NSP/64 block grid; grid.y = K splits.  The CTAs of one
+// tile (its K splits) form a thread-block CLUSTER: every CTA leaves its partial tile in its own
+// shared memory and the cluster folds them through distributed shared memory in rank order,
+// each CTA owning a slice of the tile -- a fixed summation order (two runs give the same bits,
+// where the FP atomics of the earlier version did not) and no extra trip through L2.
 constexpr int kSyrkKT = 16;
 __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S) {
-    __shared__ __align__(16) double sA[2][kSyrkKT * kTS];
-    __shared__ __align__(16) double sB[2][kSyrkKT * kTS];
+    __shared__ __align__(16) double smem[4 * kSyrkKT * kTS];   // sA[2], sB[2]; reused as the 64x64 partial tile
+    double *sA[2] = {smem, smem + kSyrkKT * kTS};
+    double *sB[2] = {smem + 2 * kSyrkKT * kTS, smem + 3 * kSyrkKT * kTS};
     int bi, bj;
     tile_index(blockIdx.x, bi, bj);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -518,17 +677,40 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     }
     if (gridDim.y == 1) {
         tile_store_sub(S, d.NSP, bi, bj, wr, wc, lane, acc);
-    } else {
-        const int g = lane >> 2, q = lane & 3;
-#pragma unroll
-        for (int ti = 0; ti < 4; ++ti)
-#pragma unroll
-            for (int tj = 0; tj < 4; ++tj) {
-                const int r = bi * 64 + wr * 32 + ti * 8 + g, c = bj * 64 + wc * 32 + tj * 8 + q * 2;
-                atomicAdd(&S[(size_t)r * d.NSP + c], -acc[ti][tj][0]);
-                atomicAdd(&S[(size_t)r * d.NSP + c + 1], -acc[ti][tj][1]);
-            }
+        return;
     }
+    // partial tile -> own shared memory, value v of thread t at [v][t] (conflict-free)
+#pragma unroll
+    for (int ti = 0; ti < 4; ++ti)
+#pragma unroll
+        for (int tj = 0; tj < 4; ++tj) {
+            smem[((ti * 4 + tj) * 2 + 0) * 128 + threadIdx.x] = acc[ti][tj][0];
+            smem[((ti * 4 + tj) * 2 + 1) * 128 + threadIdx.x] = acc[ti][tj][1];
+        }
+    unsigned rank, nrank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(nrank));
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    // this CTA folds values [v0, v1) of every thread position over the ranks, in rank order
+    const int per_rank = 32 / (int)nrank;   // nrank in {2, 4, 8}
+    const int v0 = (int)rank * per_rank;
+    const unsigned base = (unsigned)__cvta_generic_to_shared(smem);
+    const int g = lane >> 2, q = lane & 3;
+    for (int v = v0; v < v0 + per_rank; ++v) {
+        double sum = 0.0;
+        for (unsigned r = 0; r < nrank; ++r) {
+            unsigned remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + (unsigned)((v * 128 + threadIdx.x) * 8)), "r"(r));
+            double x;
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(x) : "r"(remote));
+            sum += x;
+        }
+        const int ti = v >> 3, tj = (v >> 1) & 3, h = v & 1;
+        const int row = bi * 64 + wr * 32 + ti * 8 + g, col = bj * 64 + wc * 32 + tj * 8 + q * 2 + h;
+        S[(size_t)row * d.NSP + col] -= sum;
+    }
+    // nobody leaves while a peer may still read its shared memory
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
 // ---- blocked Cholesky of S (lower, row-major, ld = NSP) ----------------------------

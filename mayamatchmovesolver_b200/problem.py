@@ -290,6 +290,12 @@ class Problem:
                                   dist.ctypes.data_as(c_f64p)), "mmb_solve")
         return SolveResult(r, x, av, dist)
 
+    def last_residuals(self):
+        """fvec of the accepted point of the last solve (errorList, adjust_results.h:298-311)"""
+        fvec = np.zeros(self.m)
+        check(self._lib.mmb_get_last_residuals(self._h, fvec.ctypes.data_as(c_f64p)), "mmb_get_last_residuals")
+        return fvec
+
     def solve_per_frame(self):
         """frameSolveMode=1: -> (aggregate SolveResult, [per-frame SolveResult])"""
         r = Result()

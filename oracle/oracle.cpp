@@ -52,7 +52,9 @@ static void func_residuals(orc_problem *p, const double *x, double *fvec, bool j
 
 // solveFunc iflag=2: adjust_solveFunc.cpp:305-525.  `structural_skip` only
 // skips observations that cannot depend on the parameter (their FD quotient
-// is exactly 0 in the reference too); it changes cost, not values.
+// is exactly 0 in the reference too); it changes cost, not values: the
+// reference's measureErrors would leave the UNPERTURBED distance of such an
+// observation in errorDistanceList, which is written here without evaluating.
 static void func_jacobian(orc_problem *p, const double *x, const double *fvec,
                           double *fjac, int ldfjac, bool structural_skip) {
     const int n = p->n, m = p->m;
@@ -60,6 +62,8 @@ static void func_jacobian(orc_problem *p, const double *x, const double *fvec,
     determineMarkersToBeEvaluated(p, x, evalMeasurements);
     std::vector<double> paramA(n), errA(m), paramB, errB;
     const double delta = p->opt.delta;
+    // lmder calls iflag=2 right after an accepted iflag=1 at the same x: errorDist = dist(x)
+    const std::vector<double> baseDist = p->errorDist;
     for (int i = 0; i < n; ++i) {
         for (int j = 0; j < n; ++j) paramA[j] = x[j];
         for (int j = 0; j < m; ++j) errA[j] = fvec[j];
@@ -75,6 +79,9 @@ static void func_jacobian(orc_problem *p, const double *x, const double *fvec,
         setParameters(p, paramA.data());
         double a, b, c;
         measureErrors(p, p->paramFrame[i], evalM, errA.data(), a, b, c);
+        if (structural_skip)
+            for (int j = 0; j < p->nobs; ++j)
+                if (evalMeasurements[j] && !evalM[j] && p->paramFrame[i][p->errorToMarker[j].second]) p->errorDist[j] = baseDist[j];
         bool forward = p->opt.auto_diff_type == 0;
         double deltaB = 0.0;
         if (!forward) {

@@ -114,3 +114,26 @@ def test_full_size_global_solve_converges():
         r = p.solve()
     print(r, "initial avg", d0.mean(), "timers", r.timer_solve_s, r.timer_jacobian_s, r.timer_linear_s, r.timer_function_s)
     assert r.success and r.error_avg < 1e-3 * d0.mean()
+
+
+DETERMINISM_CASES = {
+    "rows_shared_columns": dict(F=96, B=60, seed=12, fixed_bundles=4, period=96),     # k_assemble_shared, K-split SYRK
+    "sparse_generic": dict(F=40, B=30, seed=13, fixed_bundles=4, drop_fraction=0.2, weights=True, period=40),
+    "lens_focal": CASES["lens_focal"],
+}
+
+
+@pytest.mark.parametrize("name", list(DETERMINISM_CASES))
+def test_two_solves_are_bit_identical(name):
+    """The normal equations are accumulated with integer (fixed-point) atomics and the K splits of
+    the Schur SYRK fold in cluster-rank order (lm_kernels.cuh): nothing in a solve depends on the
+    order in which the GPU happened to schedule it -- two solves of one scene agree bit for bit."""
+    sb, _ = synth.make_scene(**DETERMINISM_CASES[name])
+    out = []
+    for _ in range(2):
+        with Problem(sb) as p:
+            r = p.solve()
+            out.append((r.x.copy(), r.error_dist.copy(), r.error_final, r.iteration_num, p.last_residuals()))
+    a, b = out
+    assert a[3] == b[3] and a[2] == b[2]
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[4], b[4])
