@@ -113,7 +113,11 @@ def test_two_cameras_one_lens_interleaved_markers_match_oracle():
 def _cfg5_sub():
     # BASELINE.json configs[4] subsampled: 8 witness cameras, Bernoulli(0.25) visibility per
     # (camera, bundle, frame) -> the sparse-visibility paths (explicit marker / frame indices)
-    return synth.make_multicam_scene(8, 64, 200, 5, visibility=0.25, fixed_bundles=6)
+    # 20 of the 200 bundles held: with 25 % visibility a camera-frame sees ~5 of them, enough to pin
+    # every pose.  (With 6 held the problem is still determined but converges along a flat valley:
+    # 86 evaluations, and GPU and oracle stop -- ftol -- 2e-4 px apart at identical nfev / njev;
+    # measured with scripts/diag_cfg5_sub.py.)
+    return synth.make_multicam_scene(8, 64, 200, 5, visibility=0.25, fixed_bundles=20)
 
 
 def test_cfg5_subsample_residuals_and_jacobian_match_oracle():
