@@ -38,8 +38,8 @@ def project_truth(cam_t, cam_r_deg, pts, focal_mm, sensor_w_mm, sensor_h_mm, ren
     return x, y
 
 
-def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
-    f = np.arange(F)
+def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0, frame_offset=0):
+    f = np.arange(F) + frame_offset
     ph = rng.uniform(0, 2 * np.pi, 5)
     t = np.stack([amp_t * np.sin(2 * np.pi * f / period + ph[0]),
                   amp_t * np.sin(2 * np.pi * f / period + ph[1]),
@@ -53,7 +53,7 @@ def camera_path(F, rng, amp_t=2.0, amp_r=5.0, period=120.0):
 def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, init_noise_t=0.1,
                init_noise_r=0.5, init_noise_b=0.05, fixed_bundles=0, lens=None, solve_focal=False,
                solve_lens=(), focal_truth=35.0, focal_init=None, drop_fraction=0.0, weights=False, period=120.0,
-               in_frame=False, lens_model="3de_radial_std_deg4"):
+               in_frame=False, lens_model="3de_radial_std_deg4", frame_offset=0):
     """One animated camera, B static bundles, full (or thinned) visibility.
 
     cfg2: make_scene(240, 50, 2, solve_bundles=False)
@@ -66,6 +66,8 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
     invertible and the fixed-point inverse of LDPK diverges) -- used by cfg4.
     `lens_model` other than the radial one takes its coefficients from `lens` too, but
     the markers are left undistorted (residual / Jacobian parity scenes, not fits).
+    `frame_offset`: generate frames offset .. offset+F-1 of a longer shot (same bundles, the camera
+    path continues): a rank's own slice of a sharded per-frame workload.
     Returns (SceneBuilder, info dict).
     """
     rng = np.random.default_rng(seed)
@@ -74,8 +76,8 @@ def make_scene(F, B, seed, solve_camera=True, solve_bundles=True, noise_px=0.5, 
         pts = np.stack([rng.uniform(-4, 4, B), rng.uniform(-2.2, 2.2, B), rng.uniform(-30, -14, B)], 1)
     else:
         pts = np.stack([rng.uniform(-10, 10, B), rng.uniform(-10, 10, B), rng.uniform(-30, -10, B)], 1)
-    cam_t, cam_r = camera_path(F, rng, period=period)
-    sb = SceneBuilder(frames=np.arange(1, F + 1))
+    cam_t, cam_r = camera_path(F, rng, period=period, frame_offset=frame_offset)
+    sb = SceneBuilder(frames=np.arange(1, F + 1) + frame_offset)
     lens_node = None
     if lens is not None:
         # truth coefficients are only used to make the markers; the scene
