@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define MMB_ABI_VERSION 1
+#define MMB_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 typedef int32_t mmb_status;
@@ -134,6 +134,29 @@ typedef struct mmb_scene_desc {
     const double *attr_max;       /* [A] +FLT_MAX = none */
     const double *attr_offset;    /* [A] default 0 */
     const double *attr_scale;     /* [A] default 1 */
+
+    /* `-attrStiffness / -attrSmoothness node.attr weightAttr varianceAttr valueAttr`
+     * (v1 command; arg_flags_attr_details.cpp:60-200, StiffAttrs / SmoothAttrs
+     * adjust_data.h): one extra residual per entry whose weight is > 0
+     * (countUpNumberOfErrors, adjust_relationships.cpp:183-219), appended after the
+     * marker errors: (1 / gaussian(attr value, value, variance) - 1) * weight
+     * (adjust_measureErrors.cpp:311-387).  *_attr indexes the USED solver
+     * attribute list, as the reference's attrIndex does; weight / variance /
+     * value are attribute-store refs read -- like the attribute itself -- at
+     * Maya's current time, here frame index `current_frame`.  Only
+     * sceneGraphMode = 1 evaluates them; in mode 2 the rows exist and stay zero
+     * (adjust_measureErrors.cpp:516 "TODO: Support stiffness and smoothness"). */
+    int32_t num_stiffness;
+    const int32_t *stiff_attr;            /* [num_stiffness] */
+    const mmb_attr_ref *stiff_weight;     /* [num_stiffness] */
+    const mmb_attr_ref *stiff_variance;   /* [num_stiffness] */
+    const mmb_attr_ref *stiff_value;      /* [num_stiffness] */
+    int32_t num_smoothness;
+    const int32_t *smooth_attr;
+    const mmb_attr_ref *smooth_weight;
+    const mmb_attr_ref *smooth_variance;
+    const mmb_attr_ref *smooth_value;
+    int32_t current_frame;                /* index into frames (MAnimControl::currentTime) */
 } mmb_scene_desc;
 
 /* ---- solver options: SolverOptions, adjust_data.h:133-185 -------------- */
@@ -148,7 +171,15 @@ typedef struct mmb_options {
     int32_t auto_param_scale;  /* 1 -> lmder mode 1, else mode 2 */
     int32_t robust_loss_type;  /* accepted, unused (adjust_defines.h:134) */
     double robust_loss_scale;
-    int32_t scene_graph_mode;  /* 2 = mmscenegraph (only mode implemented) */
+    int32_t scene_graph_mode;  /* 2 = mmscenegraph (the reference command's default is 1;
+                                  mmb_options_default gives 2, the mode without Maya).
+                                  1 = the Maya-DAG-convention arithmetic of the residual
+                                  (maya_camera.cpp:75-414,863-894: row-vector matrices,
+                                  film offsets in the projection, the C++ film-fit
+                                  variant; behind-camera x1e6 and stiffness / smoothness
+                                  rows, adjust_measureErrors.cpp:262-387) over the same
+                                  flat scene: transforms are still T*R*S, not Maya's DG.
+                                  Global solves on one GPU only. */
     int32_t solver_type;       /* 2 = cminpack_lmder (default), 1 = cminpack_lmdif */
     int32_t time_eval_mode;    /* accepted, unused without Maya */
     int32_t accept_only_better;/* default 1 */
@@ -194,7 +225,8 @@ mmb_status mmb_problem_create(const mmb_scene_desc *scene,
                               const mmb_options *opt, mmb_problem **out);
 void mmb_problem_destroy(mmb_problem *p);
 
-/* sizes: numberOfParameters n, numberOfMarkerErrors/2 (= Nobs), m = 2*Nobs */
+/* sizes: numberOfParameters n, numberOfMarkerErrors/2 (= Nobs), numberOfErrors m =
+ * 2*Nobs + stiffness + smoothness rows */
 mmb_status mmb_problem_sizes(const mmb_problem *p, int32_t *n_params,
                              int32_t *n_obs, int32_t *n_errors);
 
@@ -345,6 +377,10 @@ mmb_status mmb_get_last_residuals(mmb_problem *p, double *fvec);
 #define MMB_FMT_ERROR_PER_FRAME 2
 #define MMB_FMT_SOLVE_VALUES 4
 #define MMB_FMT_INPUT_STATS 8 /* printStatistics 'inputs': numberOf* counts */
+/* stiffness / smoothness rows of the problem (0..2047 each), OR-ed into `flags`:
+ * numberOfErrors and solve_error_list [2*n_obs + rows] then include them */
+#define MMB_FMT_STIFFNESS(n) (((int32_t)(n) & 0x7ff) << 8)
+#define MMB_FMT_SMOOTHNESS(n) (((int32_t)(n) & 0x7ff) << 19)
 mmb_status mmb_format_results(const mmb_result *r, int32_t n_params,
                               int32_t n_obs, const int32_t *error_to_marker,
                               const int32_t *frames, int32_t num_frames,

@@ -11,7 +11,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libmmsolver_b200.so")
 
-MMB_ABI_VERSION = 1
+MMB_ABI_VERSION = 2
 MMB_ATTR_NONE = -(2 ** 31)
 MMB_LENS_MAX_COEFFS = 14
 MMB_COMM_ID_BYTES = 128
@@ -42,6 +42,11 @@ class SceneDesc(C.Structure):
         ("lens_camera_params", c_f64p),
         ("num_attrs", C.c_int32), ("attr_ref", c_i32p), ("attr_min", c_f64p), ("attr_max", c_f64p),
         ("attr_offset", c_f64p), ("attr_scale", c_f64p),
+        ("num_stiffness", C.c_int32), ("stiff_attr", c_i32p), ("stiff_weight", c_i32p), ("stiff_variance", c_i32p),
+        ("stiff_value", c_i32p),
+        ("num_smoothness", C.c_int32), ("smooth_attr", c_i32p), ("smooth_weight", c_i32p), ("smooth_variance", c_i32p),
+        ("smooth_value", c_i32p),
+        ("current_frame", C.c_int32),
     ]
 
 

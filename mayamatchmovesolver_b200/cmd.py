@@ -51,8 +51,8 @@ _FLAGS = {
 }
 _SHORT = {v[0]: k for k, v in _FLAGS.items()}
 _OBJECT_FLAGS = {"camera": "c", "marker": "m", "attr": "a", "frame": "f"}
-_IGNORED = {"verbose": "v", "logLevel": "lgl", "resultsNode": "rsn", "setMarkerDeviationAttrs": "smd",
-            "attrStiffness": "asf", "attrSmoothness": "asm"}  # stiffness / smoothness: see mmSolver()
+_IGNORED = {"verbose": "v", "logLevel": "lgl", "resultsNode": "rsn", "setMarkerDeviationAttrs": "smd"}
+_STIFF_FLAGS = {"attrStiffness": "asf", "attrSmoothness": "asm"}
 _PRINT_STATS = ("inputs", "affects", "usedSolveObjects", "deviation")
 
 # sceneGraphMode / solverType / frameSolveMode values (adjust_defines.h:92-152, _api/constant.py)
@@ -91,7 +91,7 @@ def _options_from_kwargs(kwargs):
     return opts, rest
 
 
-def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
+def select_scene(scene, camera=None, marker=None, attr=None, frame=None, attrStiffness=None, attrSmoothness=None):
     """Apply the command's object flags to a copy of `scene`.
     marker: only the listed markers take part; attr: the listed plugs become the solver
     attributes (in flag order); frame: the listed frame numbers (in flag order)."""
@@ -126,6 +126,24 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None):
             plug, mn, mx, off, scl = entry
             sb.add_attr(sb.plug(plug) if isinstance(plug, str) else int(plug), min=float(mn) if _is_double(mn) else None, max=float(mx) if _is_double(mx) else None,
                         offset=float(off) if _is_double(off) else None, scale=float(scl) if _is_double(scl) else None)
+    # -attrStiffness / -attrSmoothness "node.attr" "weightPlug" "variancePlug" "valuePlug"
+    # (arg_flags_attr_details.cpp:60-200): the attribute is looked up among the -attr flags
+    for flags, smooth in ((attrStiffness, False), (attrSmoothness, True)):
+        if flags is None:
+            continue
+        if smooth:
+            sb.smoothness = []
+        else:
+            sb.stiffness = []
+        for entry in flags:
+            if len(entry) != 4:
+                continue   # the command logs an error and skips the flag
+            plug, wplug, vplug, valplug = entry
+            ref = sb.plug(plug)
+            if ref not in sb.attr_ref:
+                continue   # "is not a declared attribute"
+            sb.add_stiffness(sb.attr_ref.index(ref), int(sb.plug(wplug)), int(sb.plug(vplug)), int(sb.plug(valplug)),
+                             smoothness=smooth)
     return sb
 
 
@@ -225,6 +243,8 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
         long_name = {v: k for k, v in _OBJECT_FLAGS.items()}.get(key, key)
         if long_name in _OBJECT_FLAGS:
             objects[long_name] = value
+        elif key in _STIFF_FLAGS or key in _STIFF_FLAGS.values():
+            objects[{v: k for k, v in _STIFF_FLAGS.items()}.get(key, key)] = value
         elif key in ("printStatistics", "pst"):
             print_stats_flags = [value] if isinstance(value, str) else list(value)
         elif key in _IGNORED or key in _IGNORED.values():
@@ -237,7 +257,10 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
     # solverstep.py:647-657: per-frame needs mmscenegraph, the Maya DAG mode solves all frames at once
     sgm = opts.get("scene_graph_mode", SCENE_GRAPH_MODE_MM_SCENE_GRAPH)
     if "scene_graph_mode" not in opts:
-        opts["scene_graph_mode"] = SCENE_GRAPH_MODE_MM_SCENE_GRAPH  # the only mode without Maya
+        # the reference command defaults to maya_dag (1); without Maya the default here is the
+        # mmscenegraph arithmetic.  sceneGraphMode=1 selects the Maya-DAG-convention arithmetic of
+        # the residual (row-vector projection, behind-camera factor, stiffness / smoothness rows).
+        opts["scene_graph_mode"] = SCENE_GRAPH_MODE_MM_SCENE_GRAPH
     if opts.get("frame_solve_mode", 0) == FRAME_SOLVE_MODE_PER_FRAME:
         assert sgm == SCENE_GRAPH_MODE_MM_SCENE_GRAPH, "per-frame solving needs sceneGraphMode = mmscenegraph"
     sb = select_scene(scene, **objects) if objects else scene
@@ -277,6 +300,9 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
         return strings[:k] + extra + strings[k:]
 
     with Problem(sb, options=options) as p:
+        n_rows = p.m - 2 * p.nobs       # stiffness + smoothness rows (MMB_FMT_STIFFNESS / _SMOOTHNESS)
+        n_smooth = _count_rows(sb, sb.smoothness)
+        flags |= ((n_rows - n_smooth) & 0x7ff) << 8 | (n_smooth & 0x7ff) << 19
         used_m, used_a = p.used_objects()
         names_scene = _UsedView(sb, [mk_names[i] for i in used_m])
         if do_not_solve:
@@ -302,6 +328,11 @@ def mmSolver(scene, write_back=True, device=0, **kwargs):
             else:
                 scene.set_value(ref, r.attr_values[i], frame_index[int(sb.frames[f])])
     return strings
+
+
+def _count_rows(scene, entries):
+    """entries whose weight, at the current frame, is > 0 (adjust_relationships.cpp:183-219)"""
+    return sum(1 for e in entries if scene.get_value(e[1], scene.current_frame) > 0.0)
 
 
 class _UsedView:

@@ -88,7 +88,7 @@ mmb_status mmb_problem_sizes(const mmb_problem *p, int32_t *n, int32_t *nobs, in
     if (!p) return MMB_ERR_INVALID_ARGUMENT;
     if (n) *n = p->dp->hp.n;
     if (nobs) *nobs = p->dp->hp.nobs;
-    if (m) *m = p->dp->hp.m;
+    if (m) *m = p->dp->hp.m_total;
     return MMB_OK;
 }
 
@@ -167,7 +167,8 @@ mmb_status mmb_eval_residuals(mmb_problem *p, const double *x, double *fvec, dou
     // measureErrors of solveFrames, adjust_base.cpp:1080-1103)
     if ((st = launch_variants(dp, x ? dp->d_x : nullptr, false)) != MMB_OK) return st;
     if ((st = launch_residuals(dp, dp->d_fvec, dp->d_dist)) != MMB_OK) return st;
-    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
+    if ((st = launch_extra_rows(dp, x ? dp->d_x : nullptr, dp->d_fvec + dp->hp.m, nullptr, nullptr)) != MMB_OK) return st;
+    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m_total, cudaMemcpyDeviceToHost, dp->stream));
     if (error_dist)
         MMB_CUDA_CHECK(cudaMemcpyAsync(error_dist, dp->d_dist, sizeof(double) * dp->hp.nobs, cudaMemcpyDeviceToHost, dp->stream));
     MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
@@ -205,7 +206,7 @@ mmb_status mmb_eval_jacobian_dense(mmb_problem *p, const double *x, double *fjac
     if (!p || !x || !fjac) return MMB_ERR_INVALID_ARGUMENT;
     DeviceProblem *dp = p->dp;
     const HostProblem &hp = dp->hp;
-    if (ldfjac < hp.m) return MMB_ERR_INVALID_ARGUMENT;
+    if (ldfjac < hp.m_total) return MMB_ERR_INVALID_ARGUMENT;
     const size_t k = dp->ds.kmax;
     std::vector<double> vals(k * (size_t)hp.m);
     std::vector<int32_t> cols(k * (size_t)hp.nobs);
@@ -213,7 +214,7 @@ mmb_status mmb_eval_jacobian_dense(mmb_problem *p, const double *x, double *fjac
     mmb_status st = mmb_eval_jacobian_blocks(p, x, vals.data(), cols.data(), &kk);
     if (st != MMB_OK) return st;
     // layout conversion only: block columns -> cminpack's dense column-major
-    for (size_t j = 0; j < (size_t)hp.n; ++j) std::memset(&fjac[j * ldfjac], 0, sizeof(double) * hp.m);
+    for (size_t j = 0; j < (size_t)hp.n; ++j) std::memset(&fjac[j * ldfjac], 0, sizeof(double) * hp.m_total);
     for (size_t i = 0; i < (size_t)hp.nobs; ++i)
         for (size_t c = 0; c < k; ++c) {
             const int32_t pid = cols[i * k + c];
@@ -221,6 +222,24 @@ mmb_status mmb_eval_jacobian_dense(mmb_problem *p, const double *x, double *fjac
             fjac[(size_t)pid * ldfjac + 2 * i] = vals[c * hp.m + 2 * i];
             fjac[(size_t)pid * ldfjac + 2 * i + 1] = vals[c * hp.m + 2 * i + 1];
         }
+    if (hp.n_extra) {
+        // stiffness / smoothness rows: one entry each (the variants of this x are still in place)
+        double *d_j = nullptr; int32_t *d_p = nullptr;
+        MMB_CUDA_CHECK(cudaMallocAsync((void **)&d_j, sizeof(double) * hp.n_extra, dp->stream));
+        MMB_CUDA_CHECK(cudaMallocAsync((void **)&d_p, sizeof(int32_t) * hp.n_extra, dp->stream));
+        st = launch_extra_rows(dp, dp->d_x, nullptr, d_j, d_p);
+        std::vector<double> jv(hp.n_extra);
+        std::vector<int32_t> pv(hp.n_extra);
+        if (st == MMB_OK) {
+            cudaMemcpyAsync(jv.data(), d_j, sizeof(double) * hp.n_extra, cudaMemcpyDeviceToHost, dp->stream);
+            cudaMemcpyAsync(pv.data(), d_p, sizeof(int32_t) * hp.n_extra, cudaMemcpyDeviceToHost, dp->stream);
+        }
+        cudaFreeAsync(d_j, dp->stream);
+        cudaFreeAsync(d_p, dp->stream);
+        MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
+        if (st != MMB_OK) return st;
+        for (int e = 0; e < hp.n_extra; ++e) fjac[(size_t)pv[e] * ldfjac + hp.m + e] = jv[e];
+    }
     return MMB_OK;
 }
 
@@ -414,7 +433,7 @@ mmb_status mmb_get_last_residuals(mmb_problem *p, double *fvec) {
     if (!p || !fvec) return MMB_ERR_INVALID_ARGUMENT;
     DeviceProblem *dp = p->dp;
     MMB_CUDA_CHECK(cudaSetDevice(dp->device));
-    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m, cudaMemcpyDeviceToHost, dp->stream));
+    MMB_CUDA_CHECK(cudaMemcpyAsync(fvec, dp->d_fvec, sizeof(double) * dp->hp.m_total, cudaMemcpyDeviceToHost, dp->stream));
     MMB_CUDA_CHECK(cudaStreamSynchronize(dp->stream));
     return MMB_OK;
 }

@@ -133,7 +133,7 @@ struct Proj {
 // camera.rs:153-242 with the inputs dag.rs:120-172 passes (mm -> inch -> mm).
 MMB_HD Proj projection_entries(double focal_mm, double sensor_w_mm, double sensor_h_mm,
                                double offx_mm, double offy_mm, double img_w, double img_h,
-                               int film_fit, double near_cm, double camera_scale) {
+                               int film_fit, double near_cm, double camera_scale, int maya = 0) {
     const double fbw_inch = sensor_w_mm * kMmToInch, fbh_inch = sensor_h_mm * kMmToInch;
     const double offx_inch = offx_mm * kMmToInch, offy_inch = offy_mm * kMmToInch;
     const double film_aspect = fbw_inch / fbh_inch;
@@ -144,8 +144,8 @@ MMB_HD Proj projection_entries(double focal_mm, double sensor_w_mm, double senso
     double right = f2n * (0.5 * fw + ox), left = f2n * (-0.5 * fw + ox);
     double top = f2n * (0.5 * fh + oy), bottom = f2n * (-0.5 * fh + oy);
     double fsx = 1.0, fsy = 1.0, size_x = 0.0, size_y = 0.0;
-    if (film_fit == 1) {  // horizontal (camera.rs:200-201 writes scale.x)
-        fsx = image_aspect / film_aspect;
+    if (film_fit == 1) {  // horizontal: camera.rs:200-201 writes scale.x, maya_camera.cpp:160-165 scale.y
+        if (maya) fsy = image_aspect / film_aspect; else fsx = image_aspect / film_aspect;
         size_x = right - left; size_y = size_x / image_aspect;
     } else if (film_fit == 2) {  // vertical
         fsx = 1.0 / (image_aspect / film_aspect);
@@ -197,12 +197,16 @@ MMB_HD void marker_film_fit_scale(int film_fit, double sensor_aspect, double ren
 // -row2 of inv(W) because P's last row is [0 0 -1 0]).  Note P's row 0/1
 // only have their diagonal entry, and S[0,3]/S[3,3] never reads row 2.
 // out[0..3] = row0, out[4..7] = row1, out[8..11] = row3.
-MMB_HD void camera_rows(const Aff &cam_world, const Proj &p, double *out) {
+// maya: Maya's row-vector layout (maya_camera.cpp:339-361, point * inverse(world) * proj) puts the
+// film-offset entries p20, p21 on the camera-space z: x_clip = p00 x + p20 z, y_clip = p11 y + p21 z
+// (in the mmscenegraph layout they only reach z_clip, which nothing reads).
+MMB_HD void camera_rows(const Aff &cam_world, const Proj &p, double *out, int maya = 0) {
     const Aff inv = aff_inverse(cam_world);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         out[j] = p.p00 * inv.m[j];
         out[4 + j] = p.p11 * inv.m[4 + j];
+        if (maya) { out[j] += p.p20 * inv.m[8 + j]; out[4 + j] += p.p21 * inv.m[8 + j]; }
         out[8 + j] = -inv.m[8 + j];
     }
 }

@@ -121,5 +121,8 @@ mmb_status launch_variants(DeviceProblem *p, const double *d_x, bool with_pertur
 mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist);
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols,
                            double *d_dist_last = nullptr);
+// stiffness / smoothness rows at d_x: values into d_row[n_extra] and / or the one Jacobian entry of
+// each row into d_jext[n_extra] with its parameter id in d_pid[n_extra] (either may be nullptr)
+mmb_status launch_extra_rows(DeviceProblem *p, const double *d_x, double *d_row, double *d_jext, int32_t *d_pid);
 
 }  // namespace mmb

@@ -75,6 +75,12 @@ struct DevScene {
     const int32_t *mkr_k;    // [M]
     // per-parameter FD step actually used (deltaA, deltaB) for x
     double *par_delta_a, *par_delta_b;  // [n]
+    // sceneGraphMode = 1 (Maya-DAG-convention arithmetic) and the stiffness / smoothness rows
+    int maya_dag;
+    int cur_frame;                       // "Maya's current time" as a frame index
+    int n_extra;                         // stiffness rows first, then smoothness rows
+    const int32_t *ex_attr, *ex_w, *ex_var, *ex_val;   // [n_extra] solver attr, weight / variance / value refs
+    double *cam_fwd;                     // [camera][variant][4][frames]: forward axis xyz, forward . position
 };
 
 // ---- attribute values --------------------------------------------------------
@@ -185,9 +191,19 @@ MMB_HD void camera_variant_store(const DevScene &s, int c, int v, int f, const A
     const int fs = s.cam_fs[c];
     const double sw = cav[0], sh = cav[1];
     const Proj p = projection_entries(cav[2], sw, sh, cav[3], cav[4], (double)s.cam_rw[c], (double)s.cam_rh[c],
-                                      s.cam_fit[c], 0.1 /* dag.rs:152 */, cav[5]);
+                                      s.cam_fit[c], 0.1 /* dag.rs:152 */, cav[5], s.maya_dag);
     double out[14];
-    camera_rows(w, p, out);
+    camera_rows(w, p, out, s.maya_dag);
+    if (s.maya_dag) {
+        // Camera::getForwardDirection / getWorldPosition (maya_camera.cpp:814-856): (0, 0, -1) * worldMat
+        // is minus the third column of the column-convention world matrix; only the sign of
+        // forward . (bundle - position) is used (adjust_measureErrors.cpp:262-270)
+        const double fx = -w.m[2], fy = -w.m[6], fz = -w.m[10];
+        const long long fpad = fs == 1 ? 1 : ((long long)fs + kCamBlock - 1) / kCamBlock * kCamBlock;
+        double *fw = s.cam_fwd + s.cam_off[c] / 4 + (size_t)v * 4 * fpad + (fs == 1 ? 0 : f);
+        fw[0] = fx; fw[fpad] = fy; fw[2 * fpad] = fz;
+        fw[3 * fpad] = fx * w.m[3] + fy * w.m[7] + fz * w.m[11];
+    }
     marker_film_fit_scale(s.cam_fit[c], sw / sh, (double)s.cam_rw[c] / (double)s.cam_rh[c], out[12], out[13]);
     double *dst = s.cam_tab + s.cam_off[c];
     const int nvar = cam_nvar_of(s.cam_ndep[c], s.central);
@@ -276,13 +292,19 @@ struct ObsCtx {
     double mx, my, w;       // raw marker, sqrt(weight)
 };
 
-MMB_HD void load_cam(const DevScene &s, int c, int v, int f, double *cm /*14*/) {
+constexpr int kCamVals = 18;  // 14 + the forward record of sceneGraphMode 1
+MMB_HD void load_cam(const DevScene &s, int c, int v, int f, double *cm /*kCamVals*/) {
     const int fs = s.cam_fs[c];
     const int ff = fs == 1 ? 0 : f;
     const double *src = s.cam_tab + s.cam_off[c];
     const int nvar = cam_nvar_of(s.cam_ndep[c], s.central);
 #pragma unroll
     for (int j = 0; j < 14; ++j) cm[j] = src[cam_idx(v, j, fs, ff, nvar)];
+    if (s.maya_dag) {
+        const long long fpad = fs == 1 ? 1 : ((long long)fs + kCamBlock - 1) / kCamBlock * kCamBlock;
+        const double *fw = s.cam_fwd + s.cam_off[c] / 4 + (size_t)v * 4 * fpad + ff;
+        cm[14] = fw[0]; cm[15] = fw[fpad]; cm[16] = fw[2 * fpad]; cm[17] = fw[3 * fpad];
+    }
 }
 MMB_HD void load_bnd(const DevScene &s, int b, int v, int f, double *bp /*3*/) {
     const int fs = s.bnd_fs[b];
@@ -329,8 +351,9 @@ MMB_HD ObsCtx make_obs(const DevScene &s, int i) {
     return o;
 }
 
+// fwd: the camera's forward record (sceneGraphMode 1, generic kernels only) or nullptr
 MMB_HD void residual_from(const DevScene &s, const ObsCtx &o, const double *cm, const double *bp,
-                          const double *lens_rec, double &ex, double &ey, double &dist) {
+                          const double *lens_rec, double &ex, double &ey, double &dist, const double *fwd = nullptr) {
     double px, py;
     project_point(cm, bp, px, py);
     if (lens_rec) {
@@ -343,18 +366,63 @@ MMB_HD void residual_from(const DevScene &s, const ObsCtx &o, const double *cm, 
     const double dxp = dx * s.image_width, dyp = dy * s.image_width;
     ex = dxp * o.w;
     ey = dyp * o.w;
+    if (fwd) {
+        // behind the camera: the residual pair (not the reported distance) x 1e6
+        // (adjust_measureErrors.cpp:262-282)
+        const double dot = fwd[0] * bp[0] + fwd[1] * bp[1] + fwd[2] * bp[2] - fwd[3];
+        if (dot < 0.0) { ex *= 1e+6; ey *= 1e+6; }
+    }
     dist = sqrt((dx * dx) + (dy * dy)) * s.image_width;
+}
+
+// ---- stiffness / smoothness rows (adjust_measureErrors.cpp:311-387) ---------------------------
+// error = (1 / gaussian(attr value, value, variance) - 1) * weight, every value read at the
+// current time.  `av` decides which parameter is perturbed (the FD quotient of the row).
+MMB_HD double extra_row_value(const DevScene &s, const AttrView &av, int e) {
+    if (!s.maya_dag) return 0.0;   // measureErrors_mmSceneGraph leaves the rows untouched: zero
+    const double weight = av.get(s.ex_w[e]), variance = av.get(s.ex_var[e]), value = av.get(s.ex_val[e]);
+    const double attr_value = av.get(s.attr_ref[s.ex_attr[e]]);
+    const double g = exp(-(pow((attr_value - value), 2.0) / (2.0 * (pow(variance, 2.0)))));
+    return ((1.0 / g) - 1.0) * weight;
+}
+// row value at x (fvec entry) and its one non-zero Jacobian entry: the parameter of the row's
+// attribute at the current frame, forward or central quotient exactly as the marker rows
+MMB_HD void extra_row_thread(const DevScene &s, const double *x, int e, double *row, double *jext, int32_t *pid_out) {
+    double inv;
+    const AttrView base = make_view(s, x, s.cur_frame, -1, 0, 0, inv);
+    const double r0 = extra_row_value(s, base, e);
+    if (row) row[e] = r0;
+    if (!jext) return;
+    const int a = s.ex_attr[e];
+    const int pid = s.attr_param_base[a] + (s.attr_anim[a] ? s.cur_frame : 0);
+    double j = 0.0;
+    if (s.maya_dag) {
+        const AttrView va = make_view(s, x, s.cur_frame, a, 1, 1, inv);
+        const double ra = extra_row_value(s, va, e);
+        const double da = s.par_delta_a[pid];
+        bool forward = !s.central;
+        double db = 0.0;
+        if (!forward) { db = s.par_delta_b[pid]; if (da == db) forward = true; }
+        if (forward) j = (ra - r0) * (1.0 / da);
+        else {
+            const AttrView vb = make_view(s, x, s.cur_frame, a, 2, 1, inv);
+            const double rb = extra_row_value(s, vb, e);
+            j = (ra - rb) * (0.5 / (fabs(da) + fabs(db)));
+        }
+    }
+    jext[e] = j;
+    pid_out[e] = pid;
 }
 
 // Residuals only (solveFunc iflag=1).  fvec[2i], fvec[2i+1], dist[i].
 MMB_HD void residual_thread(const DevScene &s, int i, double *fvec, double *dist) {
     const ObsCtx o = make_obs(s, i);
-    double cm[14], bp[3], rec[kLensRec];
+    double cm[kCamVals], bp[3], rec[kLensRec];
     load_cam(s, o.cam, 0, o.frame, cm);
     load_bnd(s, o.bnd, 0, o.frame, bp);
     if (o.lens >= 0) load_lens(s, o.lens, 0, o.lens_frame, rec);
     double ex, ey, d;
-    residual_from(s, o, cm, bp, o.lens >= 0 ? rec : nullptr, ex, ey, d);
+    residual_from(s, o, cm, bp, o.lens >= 0 ? rec : nullptr, ex, ey, d, s.maya_dag ? cm + 14 : nullptr);
     fvec[2 * (size_t)i] = ex;
     fvec[2 * (size_t)i + 1] = ey;
     if (dist) dist[i] = d;
@@ -369,13 +437,13 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
                             int32_t *col_ids, double *dist_last = nullptr) {
     const ObsCtx o = make_obs(s, i);
     const size_t m = 2 * (size_t)s.nobs;
-    double cm[14], bp[3], rec[kLensRec];
+    double cm[kCamVals], bp[3], rec[kLensRec];
     load_cam(s, o.cam, 0, o.frame, cm);
     load_bnd(s, o.bnd, 0, o.frame, bp);
     const bool has_lens = o.lens >= 0;
     if (has_lens) load_lens(s, o.lens, 0, o.lens_frame, rec);
     double ex, ey, d;
-    residual_from(s, o, cm, bp, has_lens ? rec : nullptr, ex, ey, d);
+    residual_from(s, o, cm, bp, has_lens ? rec : nullptr, ex, ey, d, s.maya_dag ? cm + 14 : nullptr);
     if (fvec) { fvec[2 * (size_t)i] = ex; fvec[2 * (size_t)i + 1] = ey; }
     if (dist) dist[i] = d;
     double dlast = d;
@@ -389,13 +457,13 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
         if (c < k) {
             const PlanEntryD e = pl[c];
             pid = s.attr_param_base[e.attr] + (s.attr_anim[e.attr] ? o.frame : 0);
-            double cmv[14], bpv[3], recv[kLensRec];
+            double cmv[kCamVals], bpv[3], recv[kLensRec];
             const double *pcm = cm, *pbp = bp, *prec = has_lens ? rec : nullptr;
             if (e.cam_var) { load_cam(s, o.cam, e.cam_var, o.frame, cmv); pcm = cmv; }
             if (e.bnd_var) { load_bnd(s, o.bnd, e.bnd_var, o.frame, bpv); pbp = bpv; }
             if (e.lens_var && has_lens) { load_lens(s, o.lens, e.lens_var, o.lens_frame, recv); prec = recv; }
             double ax, ay, ad;
-            residual_from(s, o, pcm, pbp, prec, ax, ay, ad);
+            residual_from(s, o, pcm, pbp, prec, ax, ay, ad, s.maya_dag ? pcm + 14 : nullptr);
             const double da = s.par_delta_a[pid];
             bool forward = !s.central;
             double db = 0.0;
@@ -411,7 +479,7 @@ MMB_HD void jacobian_thread(const DevScene &s, int i, double *fvec, double *dist
                 if (e.bnd_var) { load_bnd(s, o.bnd, e.bnd_var + bnd_nd, o.frame, bpv); pbp = bpv; }
                 if (e.lens_var && has_lens) { load_lens(s, o.lens, e.lens_var + lnd, o.lens_frame, recv); prec = recv; }
                 double bx, by, bd;
-                residual_from(s, o, pcm, pbp, prec, bx, by, bd);
+                residual_from(s, o, pcm, pbp, prec, bx, by, bd, s.maya_dag ? pcm + 14 : nullptr);
                 // adjust_solveFunc.cpp:468 (0.5/(|dA|+|dB|), as written)
                 const double inv_delta = 0.5 / (fabs(da) + fabs(db));
                 jx = (ax - bx) * inv_delta;

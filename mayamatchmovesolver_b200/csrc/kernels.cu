@@ -238,6 +238,19 @@ mmb_status launch_residuals(DeviceProblem *p, double *d_fvec, double *d_dist) {
     return MMB_OK;
 }
 
+// stiffness / smoothness rows: values (row != nullptr) and / or their Jacobian entries
+__global__ void k_extra_rows(DevScene s, const double *x, double *row, double *jext, int32_t *pid) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < s.n_extra) extra_row_thread(s, x, e, row, jext, pid);
+}
+mmb_status launch_extra_rows(DeviceProblem *p, const double *d_x, double *d_row, double *d_jext, int32_t *d_pid) {
+    if (p->hp.n_extra == 0) return MMB_OK;
+    k_extra_rows<<<(p->hp.n_extra + 63) / 64, 64, 0, p->stream>>>(p->ds, d_x, d_row, d_jext, d_pid);
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    return MMB_OK;
+}
+
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols, double *d_dist_last) {
     if (p->tiled_ok) {
         static int variant = -1;
@@ -439,6 +452,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     d.lmdif = opt->solver_type == 1;
     d.fd_eps = std::sqrt(std::max(std::fabs(opt->delta), 2.220446049250313e-16));
     d.image_width = opt->image_width;
+    d.maya_dag = hp.maya_dag; d.cur_frame = hp.cur_frame; d.n_extra = hp.n_extra;
     CK(A.upload(&p->d_stat0, hp.stat0));
     CK(A.upload(&p->d_anim0, hp.anim0));
     d.stat = p->d_stat0;  // the attribute store is read-only: solved values come from x
@@ -469,6 +483,15 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     else { UP_I(err_marker, hp.err_marker); UP_I(err_frame, hp.err_frame); }
     UP_D(obs_mx, hp.obs_mx); UP_D(obs_my, hp.obs_my); UP_D(obs_w, hp.obs_w);
     CK(A.alloc(&d.cam_tab, (size_t)hp.cam_tab_size));
+    d.cam_fwd = nullptr;
+    if (hp.maya_dag) CK(A.alloc(&d.cam_fwd, (size_t)hp.cam_tab_size / 4 + 4));
+    {
+        std::vector<int32_t> e0(1, 0);
+        CK(A.upload(&tmp_i, hp.n_extra ? hp.ex_attr : e0)); d.ex_attr = tmp_i;
+        CK(A.upload(&tmp_i, hp.n_extra ? hp.ex_w : e0)); d.ex_w = tmp_i;
+        CK(A.upload(&tmp_i, hp.n_extra ? hp.ex_var : e0)); d.ex_var = tmp_i;
+        CK(A.upload(&tmp_i, hp.n_extra ? hp.ex_val : e0)); d.ex_val = tmp_i;
+    }
     CK(A.alloc(&d.bnd_tab, (size_t)hp.bnd_tab_size));
     CK(A.alloc(&d.lens_tab, (size_t)hp.lens_tab_size));
     UP_L(cam_off, hp.cam_off); UP_L(bnd_off, hp.bnd_off); UP_L(lens_off, hp.lens_off);
@@ -527,7 +550,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             if (hp.bnd_fs[b] != 1) bundles_static = false;
         }
         const size_t VC = hp.cam_deps[0].size();
-        bool eligible = hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && hp.C == 1 &&
+        bool eligible = hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && hp.C == 1 && !hp.maya_dag &&
                         !hp.cam_mscale_varies[0] && bundles_static && VC <= (size_t)kTileMaxVC &&
                         VB <= (size_t)kTileMaxVB && hp.kmax <= 127;
         for (int mk = 0; eligible && mk < hp.M; ++mk)
@@ -595,7 +618,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
         }
     }
     {   // evaluation-per-thread tiled kernel (k_jacobian_lens): lens in the loop and / or several cameras
-        bool ok = hp.dense_grid && opt->auto_diff_type == 0 && !opt->lens_index_literal && hp.F >= 2 &&
+        bool ok = hp.dense_grid && opt->auto_diff_type == 0 && !opt->lens_index_literal && hp.F >= 2 && !hp.maya_dag &&
                   hp.kmax + 1 <= kLensTileMaxEval && hp.kmax >= 1;
         size_t nv = 1, nvl = 1;
         for (int c = 0; ok && c < hp.C; ++c) {
@@ -612,7 +635,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
         p->lens_tile_ok = ok;
     }
     CK(A.alloc(&p->d_x, (size_t)hp.n));
-    CK(A.alloc(&p->d_fvec, (size_t)hp.m));
+    CK(A.alloc(&p->d_fvec, (size_t)hp.m_total));
     CK(A.alloc(&p->d_dist, (size_t)hp.nobs));
 #undef CK
 #undef UP_I

@@ -76,6 +76,9 @@ struct LmWorkspace {
     int ncs = 0;
     int *poison = nullptr;
     DetBufs det{};
+    // stiffness / smoothness rows: their one Jacobian entry each and its parameter
+    double *jext = nullptr;
+    int32_t *ext_pid = nullptr, *p2i = nullptr;
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
     double *Dinv = nullptr;    // [NSP/64][64*64] inverses of the factor's diagonal blocks (k_chol_tiles phase E)
@@ -568,6 +571,9 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     }
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
+    CKW(A.upload(&w->p2i, hp.par_to_int));
+    CKW(A.alloc(&w->jext, (size_t)std::max(hp.n_extra, 1)));
+    CKW(A.alloc(&w->ext_pid, (size_t)std::max(hp.n_extra, 1)));
     {
         // Which static columns of W collect three or more contributions per entry?  Entry
         // (frame, animated slot a, static slot s) gets one per marker whose plan holds both.
@@ -622,7 +628,7 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.alloc(&w->w_int, (size_t)d.KE + d.NSP));
     CKW(A.alloc(&w->p_par, (size_t)d.n));
     CKW(A.alloc(&w->x2, (size_t)d.n));
-    CKW(A.alloc(&w->fvec2, (size_t)d.m));
+    CKW(A.alloc(&w->fvec2, (size_t)hp.m_total));
     CKW(A.alloc(&w->dist2, (size_t)d.nobs));
     CKW(A.alloc(&w->part_f, (size_t)2 * kRedBlocks + kRedScal + kRedMax));
     w->part_jp = w->part_f + kRedBlocks;
@@ -697,7 +703,8 @@ static mmb_status enqueue_residual_eval(DeviceProblem *p, const double *d_x, dou
     mmb_status st;
     if ((st = launch_variants(p, d_x, false)) != MMB_OK) return st;
     if ((st = launch_residuals(p, d_f, d_dist)) != MMB_OK) return st;
-    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(d_f, (size_t)p->hp.m, w->part_f);
+    if ((st = launch_extra_rows(p, d_x, d_f + p->hp.m, nullptr, nullptr)) != MMB_OK) return st;
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(d_f, (size_t)p->hp.m_total, w->part_f);
     LAUNCH_CHECK();
     return MMB_OK;
 }
@@ -723,6 +730,8 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     mmb_status st;
     if ((st = launch_variants(p, p->d_x, true)) != MMB_OK) return st;
     if ((st = launch_jacobian(p, nullptr, nullptr, p->d_jac, nullptr, w->dist2)) != MMB_OK) return st;
+    const int nx = p->hp.n_extra;
+    if ((st = launch_extra_rows(p, p->d_x, nullptr, w->jext, w->ext_pid)) != MMB_OK) return st;
     // column maxima -> the fixed-point grids; limbs and the plain-FP part of W start at zero
     MMB_CUDA_CHECK(cudaMemsetAsync(w->cmax, 0, sizeof(unsigned long long) * ((size_t)d.n + 1), p->stream));
     MMB_CUDA_CHECK(cudaMemsetAsync(w->poison, 0, sizeof(int), p->stream));
@@ -730,6 +739,10 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
     if (d.KE && d.ns) MMB_CUDA_CHECK(cudaMemsetAsync(w->W, 0, sizeof(double) * (size_t)d.KE * d.NSP, p->stream));
     k_colmax<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->cmax);
     LAUNCH_CHECK();
+    if (nx) {
+        k_extra_colmax<<<(nx + 63) / 64, 64, 0, p->stream>>>(nx, d.n, w->jext, w->ext_pid, p->d_fvec + d.m, w->cmax);
+        LAUNCH_CHECK();
+    }
     k_assemble<<<(d.nobs + 255) / 256, 256, 0, p->stream>>>(p->ds, d, p->d_jac, p->d_fvec, w->attr_slot, w->det, w->W,
                                                             w->asm_shared.mask);
     if (w->asm_shared.ns) {
@@ -753,6 +766,10 @@ static mmb_status enqueue_jacobian_and_assembly(DeviceProblem *p) {
 #undef MMB_ASM_SHARED
     }
     LAUNCH_CHECK();
+    if (nx) {
+        k_extra_assemble<<<(nx + 63) / 64, 64, 0, p->stream>>>(d, nx, w->jext, w->ext_pid, p->d_fvec + d.m, w->p2i, w->det);
+        LAUNCH_CHECK();
+    }
     {
         const size_t total = w->det_limb_count / 2;
         k_assemble_finalize<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(d, w->det, w->slot_of_cs, w->i2p, w->U, w->gE,
@@ -944,11 +961,15 @@ static mmb_status enqueue_trial(DeviceProblem *p) {
     if (st != MMB_OK) return st;
     k_jp_partial<<<kRedBlocks, 256, 0, s>>>(p->ds, d, p->d_jac, w->p_par, w->part_jp);
     LAUNCH_CHECK();
+    if (p->hp.n_extra) {
+        k_extra_jp<<<1, 32, 0, s>>>(p->hp.n_extra, w->jext, w->ext_pid, w->p_par, w->part_jp);
+        LAUNCH_CHECK();
+    }
     // squared norms of the trial residual and of J p, ||D p||^2, ||D x2||^2: one all-reduce
     if ((st = all_reduce(p, w->part_f, (size_t)2 * kRedBlocks + 3)) != MMB_OK) return st;
     k_ctrl_accept<<<1, 1024, 0, s>>>(d, w->st, w->part_f, w->part_jp, kRedBlocks, w->scal);
     LAUNCH_CHECK();
-    k_accept_copy<<<296, 256, 0, s>>>(w->st, (size_t)d.n, (size_t)d.m, (size_t)d.nobs, w->x2, p->d_x, w->fvec2, p->d_fvec, w->dist2, p->d_dist);
+    k_accept_copy<<<296, 256, 0, s>>>(w->st, (size_t)d.n, (size_t)p->hp.m_total, (size_t)d.nobs, w->x2, p->d_x, w->fvec2, p->d_fvec, w->dist2, p->d_dist);
     LAUNCH_CHECK();
     return MMB_OK;
 }
@@ -990,7 +1011,7 @@ static mmb_status enqueue_epilogue(DeviceProblem *p) {
     LmWorkspace *w = p->lm;
     mmb_status st;
     if ((st = enqueue_error_stats(p, w->dist2)) != MMB_OK) return st;
-    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)p->hp.m, w->part_f);
+    k_sumsq_partial<<<kRedBlocks, 256, 0, p->stream>>>(p->d_fvec, (size_t)p->hp.m_total, w->part_f);
     LAUNCH_CHECK();
     return all_reduce(p, w->part_f, kRedBlocks);
 }
@@ -1165,7 +1186,11 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     const HostProblem &hp = p->hp;
     // pre-checks of solveFrames (adjust_base.cpp:844-882)
     if (hp.nobs == 0 || hp.n == 0) { set_last_error("no used markers or attributes"); return MMB_ERR_NOT_ENOUGH_OBJECTS; }
-    if (hp.n > hp.m) { set_last_error("more parameters than errors"); return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
+    if (hp.n > hp.m_total) { set_last_error("more parameters than errors"); return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
+    if ((hp.maya_dag || hp.n_extra) && p->comm && p->comm->world > 1) {
+        set_last_error("sceneGraphMode=1 / stiffness rows: global solves on one GPU only");
+        return MMB_ERR_UNSUPPORTED;
+    }
     MMB_CUDA_CHECK(cudaSetDevice(p->device));
     mmb_status st;
     const auto t_begin = clk::now();
@@ -1196,7 +1221,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     MMB_CUDA_CHECK(cudaMemcpyAsync(p->d_x, stage, sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
     MMB_CUDA_CHECK(cudaMemcpyAsync(w->diag, stage + hp.n, sizeof(double) * hp.n, cudaMemcpyHostToDevice, p->stream));
     LmState h{};
-    h.n = hp.n; h.m = hp.m; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
+    h.n = hp.n; h.m = hp.m_total; h.maxfev = hp.opt.iter_max; h.mode = hp.opt.auto_param_scale == 1 ? 1 : 2;
     h.ftol = hp.opt.eps1; h.xtol = hp.opt.eps2; h.gtol = hp.opt.eps3; h.factor = hp.opt.tau * 100.0;
     // lmdif: fdjac2 calls fcn once per parameter of the WHOLE problem (all shards)
     const int n_all = p->frames_global > hp.F ? hp.ns + hp.na * p->frames_global : hp.n;

@@ -366,6 +366,42 @@ __global__ void __launch_bounds__(256) k_assemble_finalize(LmDims d, DetBufs db,
     }
 }
 
+// ---- stiffness / smoothness rows in the normal equations --------------------------------------
+// Each of the few extra rows has ONE non-zero Jacobian entry jext[e] in column pid[e]: it adds
+// jext^2 to that parameter's diagonal entry, jext * row to its gradient entry, (jext p)^2 to ||J p||^2.
+__global__ void k_extra_colmax(int n_extra, int n, const double *jext, const int32_t *pid, const double *frow,
+                               unsigned long long *cmax) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_extra) return;
+    const double j = jext[e], r = frow[e];
+    const unsigned long long nanb = 0x7ff8000000000000ull;
+    atomicMax(&cmax[pid[e]], j != j ? nanb : (unsigned long long)__double_as_longlong(fabs(j)));
+    atomicMax(&cmax[n], r != r ? nanb : (unsigned long long)__double_as_longlong(fabs(r)));
+}
+__global__ void k_extra_assemble(LmDims d, int n_extra, const double *jext, const int32_t *pid, const double *frow,
+                                 const int32_t *p2i, DetBufs db) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_extra) return;
+    const double j = jext[e], r = frow[e];
+    const int ej = det_exp_of(db.cmax[pid[e]]), ef = det_exp_of(db.cmax[d.n]);
+    const int q = p2i[pid[e]];
+    if (q < d.KE) {
+        const int f = q / d.na, a = q - f * d.na;
+        det_add(&db.Ui[2 * (((size_t)f * d.na + a) * d.na + a)], j * j, det_exp(ej, ej), db.poison);
+        det_add(&db.gEi[2 * (size_t)q], j * r, det_exp(ej, ef), db.poison);
+    } else {
+        const int sl = q - d.KE;
+        det_add(&db.Vi[2 * ((size_t)sl * d.NSP + sl)], j * j, det_exp(ej, ej), db.poison);
+        det_add(&db.Vi[2 * ((size_t)d.ns * d.NSP + sl)], j * r, det_exp(ej, ef), db.poison);
+    }
+}
+__global__ void k_extra_jp(int n_extra, const double *jext, const int32_t *pid, const double *p_par, double *part_jp) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    double a = 0.0;
+    for (int e = 0; e < n_extra; ++e) { const double t = jext[e] * p_par[pid[e]]; a += t * t; }
+    part_jp[0] += a;
+}
+
 // ||J p||^2 partials straight from the block Jacobian (MINPACK uses R P^T p).
 // p is indexed by parameter id (reference order).
 __global__ void __launch_bounds__(256) k_jp_partial(DevScene s, LmDims d, const double *__restrict__ jac,

@@ -161,8 +161,14 @@ mmb_status copy_scene_tables(const mmb_scene_desc *s, const mmb_options *opt, Ho
         hp.error = "scene needs >=1 frame, transform, camera, bundle and marker";
         return MMB_ERR_NOT_ENOUGH_OBJECTS;
     }
-    if (opt->scene_graph_mode != 2) {
-        hp.error = "only sceneGraphMode=2 (mmscenegraph) is implemented; the Maya DAG mode needs Maya";
+    if (opt->scene_graph_mode != 2 && opt->scene_graph_mode != 1) {
+        hp.error = "sceneGraphMode must be 1 (Maya DAG conventions) or 2 (mmscenegraph)";
+        return MMB_ERR_UNSUPPORTED;
+    }
+    hp.maya_dag = opt->scene_graph_mode == 1;
+    if (hp.maya_dag && opt->frame_solve_mode == 1) {
+        // solverstep.py:647-657: per-frame solving needs mmscenegraph
+        hp.error = "frameSolveMode=1 (per frame) needs sceneGraphMode=2";
         return MMB_ERR_UNSUPPORTED;
     }
     if (opt->solver_type != 2 && opt->solver_type != 1) {
@@ -244,6 +250,28 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         if (cs != MMB_OK) return cs;
     }
     const size_t F = hp.F;
+    hp.cur_frame = s->current_frame;
+    if (hp.cur_frame < 0 || hp.cur_frame >= hp.F) { hp.error = "current_frame outside the frame list"; return MMB_ERR_INVALID_ARGUMENT; }
+    hp.stiff_in.clear(); hp.smooth_in.clear();
+    for (int pass = 0; pass < 2; ++pass) {
+        const int cnt = pass ? s->num_smoothness : s->num_stiffness;
+        const int32_t *a = pass ? s->smooth_attr : s->stiff_attr, *w = pass ? s->smooth_weight : s->stiff_weight;
+        const int32_t *vr = pass ? s->smooth_variance : s->stiff_variance, *vl = pass ? s->smooth_value : s->stiff_value;
+        if (cnt < 0 || (cnt > 0 && (!a || !w || !vr || !vl))) { hp.error = "bad stiffness / smoothness table"; return MMB_ERR_INVALID_ARGUMENT; }
+        std::vector<int32_t> &dst = pass ? hp.smooth_in : hp.stiff_in;
+        for (int i = 0; i < cnt; ++i) {
+            if (!ref_ok(w[i], hp.num_static, hp.num_anim, false) || !ref_ok(vr[i], hp.num_static, hp.num_anim, false) ||
+                !ref_ok(vl[i], hp.num_static, hp.num_anim, false)) { hp.error = "bad stiffness / smoothness attr ref"; return MMB_ERR_INVALID_ARGUMENT; }
+            dst.insert(dst.end(), {a[i], w[i], vr[i], vl[i]});
+        }
+    }
+    if (hp.maya_dag)
+        for (int c = 0; c < hp.C; ++c)
+            if (hp.cam_attrs[c * MMB_CAM_ATTRS + 7] < 0) {
+                // Camera::getProjMatrix reads cameraScale without a time (maya_camera.cpp:790)
+                hp.error = "sceneGraphMode=1: an animated cameraScale is not supported";
+                return MMB_ERR_UNSUPPORTED;
+            }
     mark("validation");
     // ---- used / unused solve objects (solve_v1, adjust_base.cpp:1322-1395) ------------------
     // markerToAttrList: marker i is affected by attribute j when j drives the marker's camera
@@ -354,6 +382,28 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
     }
     hp.nobs = (int)hp.err_marker.size();
     hp.m = 2 * hp.nobs;
+    // stiffness / smoothness rows (adjust_relationships.cpp:183-219): one per entry whose weight,
+    // read at the current time, is > 0; measureErrors then uses the FIRST that many entries of
+    // each list (adjust_measureErrors.cpp:318-323), which is kept
+    {
+        auto value_of = [&](int32_t r) { return r >= 0 ? hp.stat0[r] : hp.anim0[(size_t)(-(int64_t)r - 1) * F + hp.cur_frame]; };
+        hp.n_stiff = hp.n_smooth = 0;
+        for (size_t i = 0; i + 3 < hp.stiff_in.size(); i += 4) if (value_of(hp.stiff_in[i + 1]) > 0.0) ++hp.n_stiff;
+        for (size_t i = 0; i + 3 < hp.smooth_in.size(); i += 4) if (value_of(hp.smooth_in[i + 1]) > 0.0) ++hp.n_smooth;
+        hp.ex_attr.clear(); hp.ex_w.clear(); hp.ex_var.clear(); hp.ex_val.clear();
+        for (int pass = 0; pass < 2; ++pass) {
+            const std::vector<int32_t> &src = pass ? hp.smooth_in : hp.stiff_in;
+            const int cnt = pass ? hp.n_smooth : hp.n_stiff;
+            for (int i = 0; i < cnt; ++i) {
+                const int32_t a = src[4 * i];
+                if (a < 0 || a >= hp.A) { hp.error = "stiffness / smoothness attribute index outside the used attribute list"; return MMB_ERR_INVALID_ARGUMENT; }
+                hp.ex_attr.push_back(a); hp.ex_w.push_back(src[4 * i + 1]);
+                hp.ex_var.push_back(src[4 * i + 2]); hp.ex_val.push_back(src[4 * i + 3]);
+            }
+        }
+        hp.n_extra = hp.n_stiff + hp.n_smooth;
+        hp.m_total = hp.m + hp.n_extra;
+    }
     for (int i = 0; i < hp.nobs; ++i) hp.obs_w[i] = hp.obs_w[i] / wmax[hp.err_frame[i]];
     hp.dense_grid = ((size_t)hp.nobs == (size_t)hp.M * F);
 

@@ -66,8 +66,15 @@ struct HostProblem {
     int M_in = 0, A_in = 0;                       // markers / attributes the caller passed
     std::vector<uint8_t> marker_used, attr_used;  // [M_in], [A_in]
     std::vector<int32_t> mkr_src, attr_src;       // used marker / attr -> index in the caller's lists
+    // ---- sceneGraphMode = 1 and the stiffness / smoothness rows ------------
+    int maya_dag = 0;          // Maya-DAG-convention arithmetic of the residual
+    int cur_frame = 0;         // index of "Maya's current time" in the frame list
+    std::vector<int32_t> stiff_in, smooth_in;           // [count * 4] attr, weight, variance, value (as passed)
+    std::vector<int32_t> ex_attr, ex_w, ex_var, ex_val;  // the counted rows: stiffness first, then smoothness
+    int n_stiff = 0, n_smooth = 0, n_extra = 0;
+    int m_total = 0;           // numberOfErrors = m + n_extra
     // ---- index maps (adjust_relationships.cpp) --------------------------
-    int n = 0, nobs = 0, m = 0;
+    int n = 0, nobs = 0, m = 0;   // m = numberOfMarkerErrors = 2 * nobs
     RawVec<int32_t> err_marker, err_frame;   // errorToMarkerList
     RawVec<double> obs_mx, obs_my, obs_w;    // markerPosList / weights
     std::vector<int32_t> par_attr, par_frame;     // paramToAttrList

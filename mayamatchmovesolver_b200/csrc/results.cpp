@@ -40,16 +40,17 @@ extern "C" mmb_status mmb_format_results(const mmb_result *r, int32_t n_params, 
                                          int64_t *needed) {
     if (!r || n_params < 0 || n_obs < 0 || num_frames < 0 || num_markers < 0) return MMB_ERR_INVALID_ARGUMENT;
     const bool want_metrics = (flags & (MMB_FMT_ERROR_PER_MARKER_PER_FRAME | MMB_FMT_ERROR_PER_FRAME)) != 0;
+    const int n_stiff = (flags >> 8) & 0x7ff, n_smooth = (flags >> 19) & 0x7ff;
     if (want_metrics && (!error_to_marker || !error_dist)) return MMB_ERR_INVALID_ARGUMENT;
     try {
         std::string out;
         auto line = [&](const std::string &s) { out += s; out += '\n'; };
         if (flags & MMB_FMT_INPUT_STATS) {
             line("numberOfParameters=" + num<int>(n_params));
-            line("numberOfErrors=" + num<int>(2 * n_obs));
+            line("numberOfErrors=" + num<int>(2 * n_obs + n_stiff + n_smooth));
             line("numberOfMarkerErrors=" + num<int>(2 * n_obs));
-            line("numberOfAttrStiffnessErrors=" + num<int>(0));
-            line("numberOfAttrSmoothnessErrors=" + num<int>(0));
+            line("numberOfAttrStiffnessErrors=" + num<int>(n_stiff));
+            line("numberOfAttrSmoothnessErrors=" + num<int>(n_smooth));
         }
         line("success=" + num<int>(r->success != 0));
         line("reason_num=" + num<int>(r->reason_num));
@@ -105,7 +106,7 @@ extern "C" mmb_status mmb_format_results(const mmb_result *r, int32_t n_params, 
             line(s);
             s = "solve_error_list=";
             if (solve_error_list)
-                for (int i = 0; i < 2 * n_obs; ++i) { s += num<double>(solve_error_list[i]); s += kSplit; }
+                for (int i = 0; i < 2 * n_obs + n_stiff + n_smooth; ++i) { s += num<double>(solve_error_list[i]); s += kSplit; }
             line(s);
         }
         if (needed) *needed = (int64_t)out.size() + 1;

@@ -273,7 +273,7 @@ class Problem:
     def eval_jacobian_blocks(self, x, want_cols=True):
         x = np.ascontiguousarray(x, dtype=np.float64)
         k = self.jacobian_kmax()
-        vals = np.zeros((k, self.m))
+        vals = np.zeros((k, 2 * self.nobs))   # the marker rows; stiffness / smoothness rows: eval_jacobian_dense
         cols = np.zeros((self.nobs, k), np.int32) if want_cols else None
         kk = C.c_int32()
         check(self._lib.mmb_eval_jacobian_blocks(self._h, x.ctypes.data_as(c_f64p), vals.ctypes.data_as(c_f64p),

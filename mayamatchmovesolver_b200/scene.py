@@ -56,6 +56,9 @@ class SceneBuilder:
         self.mkr_cam, self.mkr_bnd, self.mkr_x, self.mkr_y, self.mkr_w, self.mkr_en = [], [], [], [], [], []
         self.lens_model, self.lens_attrs, self.lens_cam = [], [], []
         self.attr_ref, self.attr_min, self.attr_max, self.attr_off, self.attr_scl = [], [], [], [], []
+        # -attrStiffness / -attrSmoothness entries: [attr index, weight ref, variance ref, value ref]
+        self.stiffness, self.smoothness = [], []
+        self.current_frame = 0   # index into frames of "Maya's current time"
         self.names = {}  # node name -> Node (what the command's -camera / -marker / -attr flags name)
         self._arrays_cache = None  # flattened arrays of the current state (dropped by every mutator)
 
@@ -168,6 +171,20 @@ class SceneBuilder:
         self.attr_scl.append(1.0 if scale is None else float(scale))
         return len(self.attr_ref) - 1
 
+    def add_custom_attrs(self, node, **vals):
+        """dynamic attributes on a named node (`maya.cmds.addAttr`): values for `plug('node.attr')`"""
+        for k, v in vals.items():
+            node[k] = self.value(v)
+        return node
+
+    def add_stiffness(self, attr_index, weight, variance, value, smoothness=False):
+        """One `-attrStiffness` (or `-attrSmoothness`) flag: solver attribute index + the three
+        attribute-store refs (scalars are stored as new static values)."""
+        self._arrays_cache = None
+        refs = [v if isinstance(v, (int, np.integer)) and not isinstance(v, bool) else self.value(v)
+                for v in (weight, variance, value)]
+        (self.smoothness if smoothness else self.stiffness).append([int(attr_index)] + [int(r) for r in refs])
+
     def keep_markers(self, indices):
         """Drop every marker that is not listed (the command's `-marker` flags name the markers
         of the solve; the others are not part of markerList at all)."""
@@ -227,6 +244,10 @@ class SceneBuilder:
             attr_ref=i32(self.attr_ref), attr_min=f64(self.attr_min), attr_max=f64(self.attr_max),
             attr_offset=f64(self.attr_off), attr_scale=f64(self.attr_scl),
         )
+        for key, rows in (("stiff", self.stiffness), ("smooth", self.smoothness)):
+            tab = np.asarray(rows, dtype=np.int32).reshape(-1, 4)
+            for j, name in enumerate(("attr", "weight", "variance", "value")):
+                a["%s_%s" % (key, name)] = np.ascontiguousarray(tab[:, j])
         self._arrays_cache = a
         return a
 
@@ -244,6 +265,9 @@ class SceneBuilder:
         d.num_markers = len(self.mkr_cam)
         d.num_lenses = len(self.lens_model)
         d.num_attrs = len(self.attr_ref)
+        d.num_stiffness = len(self.stiffness)
+        d.num_smoothness = len(self.smoothness)
+        d.current_frame = int(self.current_frame)
         for name, ctype in _capi.SceneDesc._fields_:
             if name in a:
                 setattr(d, name, a[name].ctypes.data_as(ctype))

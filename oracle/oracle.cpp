@@ -186,6 +186,11 @@ int orc_create(const mmb_scene_desc *s, const mmb_options *opt, orc_problem **ou
     p->attr_max.assign(s->attr_max, s->attr_max + p->A);
     p->attr_off.assign(s->attr_offset, s->attr_offset + p->A);
     p->attr_scl.assign(s->attr_scale, s->attr_scale + p->A);
+    for (int i = 0; i < s->num_stiffness; ++i)
+        p->stiffAttrs.push_back({s->stiff_attr[i], s->stiff_weight[i], s->stiff_variance[i], s->stiff_value[i]});
+    for (int i = 0; i < s->num_smoothness; ++i)
+        p->smoothAttrs.push_back({s->smooth_attr[i], s->smooth_weight[i], s->smooth_variance[i], s->smooth_value[i]});
+    p->currentFrame = s->current_frame;
     split_used_objects(p);
     build_index_maps(p);
     *out = p;
@@ -309,6 +314,7 @@ int orc_solve_sparse(orc_problem *p, mmb_result *res, double *x_out, double *att
     if (p->nobs == 0 || p->n == 0) { res->success = 0; return MMB_ERR_NOT_ENOUGH_OBJECTS; }
     if (p->n > p->m) { res->success = 0; return MMB_ERR_MORE_PARAMS_THAN_ERRORS; }
     if (p->opt.auto_diff_type != 0) return MMB_ERR_UNSUPPORTED;
+    if (p->opt.scene_graph_mode == 1 || p->m != 2 * p->nobs) return MMB_ERR_UNSUPPORTED;  // marker rows, mode 2 only
 #ifdef _OPENMP
     if (threads > 0) omp_set_num_threads(threads);
 #else

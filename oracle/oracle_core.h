@@ -50,6 +50,11 @@ struct orc_problem {
     std::vector<double> lens_cam;
     std::vector<int32_t> attr_ref;
     std::vector<double> attr_min, attr_max, attr_off, attr_scl;
+    // StiffAttrs / SmoothAttrs (adjust_data.h): attrIndex + weight / variance / value refs
+    struct ExtraAttr { int attrIndex; int32_t weight, variance, value; };
+    std::vector<ExtraAttr> stiffAttrs, smoothAttrs;
+    int numStiff = 0, numSmooth = 0;  // counted rows (weight > 0, adjust_relationships.cpp:183-219)
+    int currentFrame = 0;
     mmb_options opt;
     // index maps
     std::vector<std::pair<int, int>> errorToMarker, paramToAttr;
@@ -209,7 +214,12 @@ static void build_index_maps(orc_problem *p) {
     for (size_t i = 0; i < p->errorToMarker.size(); ++i)
         p->markerWeight[i] = p->markerWeight[i] / weightMaxPerFrame[p->errorToMarker[i].second];
     p->nobs = (int)p->errorToMarker.size();
-    p->m = 2 * p->nobs;
+    // stiffness / smoothness rows: one per entry whose weight is > 0 (adjust_relationships.cpp:183-219;
+    // getValue without a time = Maya's current time)
+    p->numStiff = p->numSmooth = 0;
+    for (const auto &e : p->stiffAttrs) if (attr_get(p, e.weight, p->currentFrame) > 0.0) p->numStiff++;
+    for (const auto &e : p->smoothAttrs) if (attr_get(p, e.weight, p->currentFrame) > 0.0) p->numSmooth++;
+    p->m = 2 * p->nobs + p->numStiff + p->numSmooth;
     // countUpNumberOfUnknownParameters, adjust_relationships.cpp:223-337
     p->paramToAttr.clear(); p->paramFrame.clear();
     for (int i = 0; i < p->A; ++i) {
@@ -282,6 +292,198 @@ static void evaluate_scene(orc_problem *p, const std::vector<bool> *frameEnable)
     }
 }
 
+// ---- Maya-DAG-convention arithmetic (sceneGraphMode = 1) -----------------------------------
+// maya_camera.cpp:75-414 in Maya's ROW-vector convention: MMatrix m[row][col], point * matrix.
+// getProjectionMatrix :363-414 = computeFrustumCoordinates :75-98 + applyFilmFitLogic :100-205
+// (Horizontal fit scales Y here, X in camera.rs:200) + computeProjectionMatrix :327-361.
+static M4 maya_projection_matrix(double focal_mm, double fbw_inch, double fbh_inch, double offx_inch,
+                                 double offy_inch, double img_w, double img_h, int film_fit, double near_cm,
+                                 double far_cm, double camera_scale) {
+    const double filmAspectRatio = fbw_inch / fbh_inch;
+    const double imageAspectRatio = img_w / img_h;
+    const double filmWidth_mm = fbw_inch * INCH_TO_MM, filmHeight_mm = fbh_inch * INCH_TO_MM;
+    const double offsetX_mm = offx_inch * INCH_TO_MM, offsetY_mm = offy_inch * INCH_TO_MM;
+    const double focal_to_near = (near_cm / focal_mm) * camera_scale;
+    const double right = focal_to_near * (0.5 * filmWidth_mm + offsetX_mm);
+    const double left = focal_to_near * (-0.5 * filmWidth_mm + offsetX_mm);
+    const double top = focal_to_near * (0.5 * filmHeight_mm + offsetY_mm);
+    const double bottom = focal_to_near * (-0.5 * filmHeight_mm + offsetY_mm);
+    double filmFitScaleX = 1.0, filmFitScaleY = 1.0, screenSizeX = 0.0, screenSizeY = 0.0;
+    double screenLeft = left, screenRight = right, screenTop = top, screenBottom = bottom;
+    switch (film_fit) {
+        default:
+        case 1:
+            filmFitScaleY = imageAspectRatio / filmAspectRatio;
+            screenSizeX = right - left;
+            screenSizeY = screenSizeX / imageAspectRatio;
+            break;
+        case 2:
+            filmFitScaleX = 1.0 / (imageAspectRatio / filmAspectRatio);
+            screenSizeY = top - bottom;
+            screenSizeX = screenSizeY * imageAspectRatio;
+            break;
+        case 0:
+            if (filmAspectRatio > imageAspectRatio) {
+                filmFitScaleX = filmAspectRatio / imageAspectRatio;
+                screenSizeY = top - bottom;
+                screenSizeX = screenSizeY * imageAspectRatio;
+            } else {
+                filmFitScaleY = imageAspectRatio / filmAspectRatio;
+                screenSizeX = right - left;
+                screenSizeY = (screenSizeX * (filmAspectRatio / imageAspectRatio)) / filmAspectRatio;
+            }
+            break;
+        case 3:
+            if (filmAspectRatio > imageAspectRatio) {
+                filmFitScaleY = imageAspectRatio / filmAspectRatio;
+                screenSizeX = right - left;
+                screenSizeY = (right - left) / imageAspectRatio;
+            } else {
+                filmFitScaleX = filmAspectRatio / imageAspectRatio;
+                screenSizeX = (right - left) * (imageAspectRatio / filmAspectRatio);
+                screenSizeY = top - bottom;
+            }
+            break;
+    }
+    screenRight *= filmFitScaleX; screenLeft *= filmFitScaleX;
+    screenTop *= filmFitScaleY; screenBottom *= filmFitScaleY;
+    M4 pm; std::memset(pm.m, 0, sizeof(pm.m));   // pm.m[r * 4 + c] = projectionMatrix[r][c]
+    pm.m[0 * 4 + 0] = 1.0 / (screenSizeX * 0.5) * MM_TO_CM;
+    pm.m[1 * 4 + 1] = 1.0 / (screenSizeY * 0.5) * MM_TO_CM;
+    pm.m[2 * 4 + 0] = (screenRight + screenLeft) / (screenRight - screenLeft) * filmFitScaleX;
+    pm.m[2 * 4 + 1] = (screenTop + screenBottom) / (screenTop - screenBottom) * filmFitScaleY;
+    pm.m[2 * 4 + 2] = (far_cm + near_cm) / (far_cm - near_cm);
+    pm.m[2 * 4 + 3] = -1;
+    pm.m[3 * 4 + 2] = 2.0 * far_cm * near_cm / (far_cm - near_cm);
+    return pm;
+}
+static M4 m4_transpose(const M4 &a) {
+    M4 r;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) r.m[i * 4 + j] = a.m[j * 4 + i];
+    return r;
+}
+inline double gaussian(double x, double mean, double sigma) {  // adjust_measureErrors.cpp:106-109
+    return std::exp(-(std::pow((x - mean), 2.0) / (2.0 * (std::pow(sigma, 2.0)))));
+}
+
+static LensEval lens_at(const orc_problem *p, int l, int f);
+
+// adjust_measureErrors.cpp:116-387 measureErrors_mayaDag.  Maya's DG is replaced by the flat
+// scene (world = T * R * S chains); everything after the world matrices is as written there.
+static void measureErrors_mayaDag(orc_problem *p, const std::vector<bool> &frameIndexEnable,
+                                  const std::vector<bool> &errorMeasurements, double *errors,
+                                  double &error_avg, double &error_max, double &error_min) {
+    const int F = p->F;
+    const double imageWidth = p->opt.image_width;
+    // world matrices of every transform (column convention), all frames
+    p->world.resize((size_t)p->T * F);
+    for (int i = 0; i < p->T; ++i) {
+        const int32_t *a = &p->tfm_attrs[i * 9];
+        for (int f = 0; f < F; ++f) {
+            M4 local = local_matrix(attr_get(p, a[0], f), attr_get(p, a[1], f), attr_get(p, a[2], f),
+                                    attr_get(p, a[3], f), attr_get(p, a[4], f), attr_get(p, a[5], f),
+                                    attr_get(p, a[6], f), attr_get(p, a[7], f), attr_get(p, a[8], f), p->tfm_roo[i]);
+            const int par = p->tfm_parent[i];
+            p->world[(size_t)i * F + f] = par >= 0 ? m4_mul(p->world[(size_t)par * F + f], local) : local;
+        }
+    }
+    int numberOfErrorsMeasured = 0;
+    for (int i = 0; i < p->nobs; ++i) {
+        const int markerIndex = p->errorToMarker[i].first, frameIndex = p->errorToMarker[i].second;
+        if (!frameIndexEnable[frameIndex]) continue;
+        if (!errorMeasurements[i]) continue;
+        const int c = p->mkr_cam[markerIndex], b = p->mkr_bnd[markerIndex];
+        const int32_t *ca = &p->cam_attrs[c * 8];
+        // Camera::getWorldProjMatrix maya_camera.cpp:863-894: inverse(world) * proj (row vectors)
+        const M4 worldMat = m4_transpose(p->world[(size_t)p->cam_tfm[c] * F + frameIndex]);  // Maya layout
+        M4 worldInv;
+        if (!m4_inverse(worldMat, worldInv)) worldInv = m4_identity();
+        // Camera::getProjMatrix :741-812: film back / offsets / focal at the frame, camera scale and far
+        // clip plane without a time (the current time), near clip hard-coded 0.1
+        const double filmWidth = attr_get(p, ca[0], frameIndex) * MM_TO_INCH, filmHeight = attr_get(p, ca[1], frameIndex) * MM_TO_INCH;
+        const double filmOffsetX = attr_get(p, ca[3], frameIndex) * MM_TO_INCH, filmOffsetY = attr_get(p, ca[4], frameIndex) * MM_TO_INCH;
+        const double focal = attr_get(p, ca[2], frameIndex);
+        const double cameraScale = attr_get(p, ca[7], p->currentFrame), farClip = attr_get(p, ca[6], p->currentFrame);
+        const M4 projMat = maya_projection_matrix(focal, filmWidth, filmHeight, filmOffsetX, filmOffsetY, (double)p->cam_rw[c],
+                                                  (double)p->cam_rh[c], p->cam_fit[c], 0.1, farClip, cameraScale);
+        const M4 cameraWorldProjectionMatrix = m4_mul(worldInv, projMat);
+        // getWorldPosition :814-833, getForwardDirection :840-856
+        const double cam_pos[3] = {worldMat.m[3 * 4 + 0] / worldMat.m[3 * 4 + 3], worldMat.m[3 * 4 + 1] / worldMat.m[3 * 4 + 3],
+                                   worldMat.m[3 * 4 + 2] / worldMat.m[3 * 4 + 3]};
+        double cam_dir[3] = {-worldMat.m[2 * 4 + 0], -worldMat.m[2 * 4 + 1], -worldMat.m[2 * 4 + 2]};  // (0, 0, -1) * worldMat
+        { const double l = std::sqrt(cam_dir[0] * cam_dir[0] + cam_dir[1] * cam_dir[1] + cam_dir[2] * cam_dir[2]);
+          for (double &v : cam_dir) v /= l; }
+        double mkr_x = p->mkr_x[(size_t)markerIndex * F + frameIndex], mkr_y = p->mkr_y[(size_t)markerIndex * F + frameIndex];
+        const double filmBackAspect = filmWidth / filmHeight;
+        const double renderAspect = (double)p->cam_rw[c] / (double)p->cam_rh[c];
+        // applyFilmFitCorrectionScaleBackward maya_camera.cpp:207-325 (same cases as flat.rs:73-97)
+        scale_marker_film_fit(p->cam_fit[c], filmBackAspect, renderAspect, mkr_x, mkr_y);
+        const double mkr_weight = std::sqrt(p->markerWeight[i]);
+        const M4 &bw = p->world[(size_t)p->bnd_tfm[b] * F + frameIndex];
+        const double bnd[3] = {bw.m[3], bw.m[7], bw.m[11]};
+        double bnd_dir[3] = {bnd[0] - cam_pos[0], bnd[1] - cam_pos[1], bnd[2] - cam_pos[2]};
+        { const double l = std::sqrt(bnd_dir[0] * bnd_dir[0] + bnd_dir[1] * bnd_dir[1] + bnd_dir[2] * bnd_dir[2]);
+          for (double &v : bnd_dir) v /= l; }
+        // bnd_mpos * cameraWorldProjectionMatrix; cartesianize
+        double q[4];
+        for (int col = 0; col < 4; ++col)
+            q[col] = bnd[0] * cameraWorldProjectionMatrix.m[0 * 4 + col] + bnd[1] * cameraWorldProjectionMatrix.m[1 * 4 + col] +
+                     bnd[2] * cameraWorldProjectionMatrix.m[2 * 4 + col] + 1.0 * cameraWorldProjectionMatrix.m[3 * 4 + col];
+        double point_x = (q[0] / q[3]) * 0.5, point_y = (q[1] / q[3]) * 0.5;
+        int lm = markerIndex, lf = frameIndex;
+        if (p->opt.lens_index_literal) {
+            const int idx = markerIndex + frameIndex;
+            lm = idx / F; lf = idx % F;
+            if (lm >= p->M) lm = -1;
+        }
+        const int l = lm >= 0 ? p->cam_lens[p->mkr_cam[lm]] : -1;
+        if (l >= 0 && p->lens_model[l] != 0) {
+            LensEval L = lens_at(p, l, lf);
+            double out_x = point_x, out_y = point_y;
+            lens_distort(L, point_x, point_y, out_x, out_y);
+            if (std::isfinite(out_x)) point_x = out_x;
+            if (std::isfinite(out_y)) point_y = out_y;
+        }
+        // behind the camera?  adjust_measureErrors.cpp:262-270
+        double behind_camera_error_factor = 1.0;
+        const double cam_dot_bnd = cam_dir[0] * bnd_dir[0] + cam_dir[1] * bnd_dir[1] + cam_dir[2] * bnd_dir[2];
+        if (cam_dot_bnd < 0.0) behind_camera_error_factor = 1e+6;
+        const double dx = std::fabs(mkr_x - point_x) * imageWidth;
+        const double dy = std::fabs(mkr_y - point_y) * imageWidth;
+        errors[2 * i] = dx * mkr_weight * behind_camera_error_factor;
+        errors[2 * i + 1] = dy * mkr_weight * behind_camera_error_factor;
+        p->errorList[2 * i] = dx * behind_camera_error_factor;
+        p->errorList[2 * i + 1] = dy * behind_camera_error_factor;
+        const double ddx = mkr_x - point_x, ddy = mkr_y - point_y;
+        const double d = std::sqrt((ddx * ddx) + (ddy * ddy)) * imageWidth;
+        p->errorDist[i] = d;
+        error_avg += d;
+        if (d > error_max) error_max = d;
+        if (d < error_min) error_min = d;
+        ++numberOfErrorsMeasured;
+    }
+    if (numberOfErrorsMeasured == 0) { error_max = 0.0; error_min = 0.0; error_avg = 0.0; }
+    else error_avg *= 1.0 / numberOfErrorsMeasured;
+    // stiffness, then smoothness rows (:311-387): the first numStiff / numSmooth entries of the lists
+    const int numberOfMarkerErrors = 2 * p->nobs;
+    for (int pass = 0; pass < 2; ++pass) {
+        const auto &list = pass == 0 ? p->stiffAttrs : p->smoothAttrs;
+        const int count = pass == 0 ? p->numStiff : p->numSmooth;
+        const int offset = pass == 0 ? 0 : p->numStiff;
+        for (int i = 0; i < count; ++i) {
+            const int indexIntoErrorArray = numberOfMarkerErrors + offset + i;
+            const auto &e = list[i];
+            const double weight = attr_get(p, e.weight, p->currentFrame);
+            const double variance = attr_get(p, e.variance, p->currentFrame);
+            const double value = attr_get(p, e.value, p->currentFrame);
+            const double attrValue = attr_get(p, p->attr_ref[e.attrIndex], p->currentFrame);
+            const double error = ((1.0 / gaussian(attrValue, value, variance)) - 1.0);
+            p->errorList[indexIntoErrorArray] = error * weight;
+            errors[indexIntoErrorArray] = error * weight;
+        }
+    }
+}
+
 static LensEval lens_at(const orc_problem *p, int l, int f) {
     LensEval L; L.model = p->lens_model[l];
     for (int k = 0; k < 6; ++k) L.cam[k] = p->lens_cam[l * 6 + k];
@@ -311,6 +513,10 @@ static void measureErrors(orc_problem *p, const std::vector<bool> &frameEnable,
                           const std::vector<bool> &errorMeasurements, double *errors,
                           double &eavg, double &emax, double &emin) {
     eavg = 0.0; emax = -0.0; emin = std::numeric_limits<double>::max();
+    if (p->opt.scene_graph_mode == 1) {   // measureErrors :539-544
+        measureErrors_mayaDag(p, frameEnable, errorMeasurements, errors, eavg, emax, emin);
+        return;
+    }
     evaluate_scene(p, &frameEnable);
     const double imageWidth = p->opt.image_width;
     const int F = p->F;

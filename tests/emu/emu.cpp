@@ -12,7 +12,8 @@ struct Emu {
     HostProblem hp;
     std::vector<uint8_t> plain;
     DevScene ds;
-    std::vector<double> stat, anim, cam_tab, bnd_tab, lens_tab, da, db;
+    std::vector<double> stat, anim, cam_tab, bnd_tab, lens_tab, da, db, cam_fwd;
+    std::vector<int32_t> exa, exw, exv, exl;
     std::vector<int32_t> cnd, bnd, lnd;
 };
 
@@ -60,11 +61,19 @@ int emu_create(const mmb_scene_desc *s, const mmb_options *o, Emu **out) {
     d.plan = (const PlanEntryD *)hp.plan.data(); d.mkr_k = hp.mkr_k.data();
     e->da.assign(hp.n + 1, 0); e->db.assign(hp.n + 1, 0);
     d.par_delta_a = e->da.data(); d.par_delta_b = e->db.data();
+    d.maya_dag = hp.maya_dag; d.cur_frame = hp.cur_frame; d.n_extra = hp.n_extra;
+    e->cam_fwd.assign(hp.cam_tab_size / 4 + 8, 0); d.cam_fwd = e->cam_fwd.data();
+    e->exa = hp.ex_attr; e->exw = hp.ex_w; e->exv = hp.ex_var; e->exl = hp.ex_val;
+    for (auto *v : {&e->exa, &e->exw, &e->exv, &e->exl}) v->push_back(0);
+    d.ex_attr = e->exa.data(); d.ex_w = e->exw.data(); d.ex_var = e->exv.data(); d.ex_val = e->exl.data();
+    d.lmdif = o->solver_type == 1;
+    d.fd_eps = std::sqrt(std::max(std::fabs(o->delta), 2.220446049250313e-16));
     *out = e;
     return 0;
 }
 void emu_destroy(Emu *e) { delete e; }
 void emu_sizes(Emu *e, int *n, int *nobs, int *kmax) { *n = e->hp.n; *nobs = e->hp.nobs; *kmax = e->ds.kmax; }
+int emu_extra(Emu *e) { return e->hp.n_extra; }
 static void prep(Emu *e, const double *x) {
     for (long long t = 0; t < e->ds.cam_jobs_total; ++t) camera_variant_thread(e->ds, x, t);
     for (long long t = 0; t < e->ds.bnd_jobs_total; ++t) bundle_variant_thread(e->ds, x, t);
@@ -73,6 +82,11 @@ static void prep(Emu *e, const double *x) {
 void emu_residuals(Emu *e, const double *x, double *fvec, double *dist) {
     prep(e, x);
     for (int i = 0; i < e->hp.nobs; ++i) residual_thread(e->ds, i, fvec, dist);
+    for (int k = 0; k < e->hp.n_extra; ++k) extra_row_thread(e->ds, x, k, fvec + e->hp.m, nullptr, nullptr);
+}
+// the one Jacobian entry of every stiffness / smoothness row (after emu_jacobian at the same x)
+void emu_extra_jacobian(Emu *e, const double *x, double *jext, int32_t *pid) {
+    for (int k = 0; k < e->hp.n_extra; ++k) extra_row_thread(e->ds, x, k, nullptr, jext, pid);
 }
 void emu_jacobian(Emu *e, const double *x, double *fvec, double *dist, double *jac, int32_t *cols) {
     prep(e, x);

@@ -202,3 +202,28 @@ def cfg1_operahouse(noise_seed=1):
     flags = dict(camera=[("cam_tfm", "cam_shp")], marker=[(t.name + "_MKR", "cam_shp", t.name + "_BND") for t in tracks],
                  attr=attrs, frame=[frame], iterations=100, solverType=2)
     return sb, flags, [n[2] for n in nodes]
+
+
+def smoothness():
+    """tests/test/test_solver/test_smoothness.py:43-140: animated nodal camera over 10 frames, one
+    marker, rx / ry solved, `-attrSmoothness cam.rx cam.weightValue cam.varianceValue cam.smoothValue`
+    with weight 1, variance 0.5, value 10; iterations = 10.  Runs in the command's default
+    sceneGraphMode (maya_dag).  The reference only asserts `success=1`."""
+    import numpy as np
+    frames = np.arange(1, 11)
+    t = (frames - 1) / 9.0
+    sb = SceneBuilder(frames=frames)
+    cam_t = sb.add_transform(name="cam_tfm", tx=-1.0, ty=1.0, tz=-5.0, rx=-2.0 + 4.0 * t, ry=-2.5 + 5.0 * t)
+    sb.add_camera(cam_t, name="cam_shp", film_fit="fill", render_width=960, render_height=540)
+    sb.add_custom_attrs(cam_t, weightValue=1.0, varianceValue=0.5, smoothValue=10.0)
+    bt = sb.add_transform(name="bundle_tfm", tx=-2.5, ty=2.4, tz=-15.0)
+    # marker keyed in Maya units under the camera at tz = -10: tx -2.5 -> 3.0, ty 1.5 -> 1.3; as a
+    # fraction of the film back (35 mm, 36 x 24 mm): x / (10 * 36 / 35), y / (10 * 24 / 35)
+    mx = (-2.5 + 5.5 * t) / (10.0 * 36.0 / 35.0)
+    my = (1.5 - 0.2 * t) / (10.0 * 24.0 / 35.0)
+    sb.add_marker(sb.names["cam_shp"], sb.add_bundle(bt, name="bundle"), mx, my, name="marker_tfm")
+    flags = dict(camera=[("cam_tfm", "cam_shp")], marker=[("marker_tfm", "cam_shp", "bundle")],
+                 attr=[("cam_tfm.rx",) + NONE4, ("cam_tfm.ry",) + NONE4], frame=[int(f) for f in frames],
+                 attrSmoothness=[("cam_tfm.rx", "cam_tfm.weightValue", "cam_tfm.varianceValue", "cam_tfm.smoothValue")],
+                 iterations=10, verbose=True)
+    return sb, flags

@@ -88,6 +88,8 @@ def emu():
         lib.emu_sizes.argtypes = [C.c_void_p, c_i32p, c_i32p, c_i32p]
         lib.emu_residuals.argtypes = [C.c_void_p, c_f64p, c_f64p, c_f64p]
         lib.emu_jacobian.argtypes = [C.c_void_p, c_f64p, c_f64p, c_f64p, c_f64p, c_i32p]
+        lib.emu_extra.argtypes = [C.c_void_p]
+        lib.emu_extra_jacobian.argtypes = [C.c_void_p, c_f64p, c_f64p, c_i32p]
         _emu = lib
     return _emu
 
@@ -190,7 +192,8 @@ class EmuProblem:
         n, nobs, k = C.c_int32(), C.c_int32(), C.c_int32()
         self.lib.emu_sizes(self.h, C.byref(n), C.byref(nobs), C.byref(k))
         self.n, self.nobs, self.kmax = n.value, nobs.value, k.value
-        self.m = 2 * self.nobs
+        self.n_extra = self.lib.emu_extra(self.h)
+        self.m = 2 * self.nobs + self.n_extra
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -206,9 +209,16 @@ class EmuProblem:
     def eval_jacobian_dense(self, x):
         x = np.ascontiguousarray(x, np.float64)
         f = np.zeros(self.m); d = np.zeros(self.nobs)
-        vals = np.zeros((self.kmax, self.m)); cols = np.zeros((self.nobs, self.kmax), np.int32)
+        vals = np.zeros((self.kmax, 2 * self.nobs)); cols = np.zeros((self.nobs, self.kmax), np.int32)
         self.lib.emu_jacobian(self.h, _p(x), _p(f), _p(d), _p(vals), _p(cols, c_i32p))
-        return blocks_to_dense(vals, cols, self.n), f
+        J = blocks_to_dense(vals, cols, self.n)
+        if self.n_extra:
+            jext = np.zeros(self.n_extra); pid = np.zeros(self.n_extra, np.int32)
+            self.lib.emu_extra_jacobian(self.h, _p(x), _p(jext), _p(pid, c_i32p))
+            rows = np.zeros((self.n_extra, self.n))
+            rows[np.arange(self.n_extra), pid] = jext
+            J = np.vstack([J, rows])
+        return J, f
 
 
 def blocks_to_dense(vals, cols, n):
@@ -230,7 +240,7 @@ def oracle_mmsolver(scene, scene_graph_mode=2, **flags):
     reference's own Maya-hosted tests (tests/kat_scenes.py)."""
     from mayamatchmovesolver_b200 import cmd
     opts, rest = cmd._options_from_kwargs(flags)
-    objects = {k: v for k, v in rest.items() if k in cmd._OBJECT_FLAGS}
+    objects = {k: v for k, v in rest.items() if k in cmd._OBJECT_FLAGS or k in cmd._STIFF_FLAGS}
     opts["scene_graph_mode"] = scene_graph_mode
     sb = cmd.select_scene(scene, **objects) if objects else scene
     o = OracleProblem(sb, **opts)
