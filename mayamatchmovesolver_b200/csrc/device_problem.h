@@ -83,6 +83,8 @@ struct DeviceProblem {
     bool tiled_ok = false;      // register-tiled Jacobian kernel applies
     bool lens_tile_ok = false;  // lens-in-the-loop tiled kernel applies (k_jacobian_lens)
     TiledPlan tiled{};
+    // several cameras (cfg5 shape): the rows kernel once per camera over that camera's markers
+    std::vector<TiledPlan> cam_plans;
     int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
     Comm *comm = nullptr;       // set by mmb_problem_attach_comm / use_comm: mmb_solve is then the sharded global solve

@@ -25,6 +25,7 @@ constexpr int kTileMaxVB = 7;     // bundle deps supported
 
 struct TiledPlan {
     int cam;                     // the camera
+    int m_base, m_count;         // its markers: m_base .. m_base + m_count - 1 (camera-major marker order)
     int VC, VB;                  // camera deps / max bundle deps
     int uniform;                 // every marker has the same column layout
     int8_t cam_col_u[kTileMaxVC];  // uniform layout: column of camera dep v
@@ -347,8 +348,8 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int f0 = blockIdx.x * kRowFrames, f = f0 + lane;
     const int F = s.F;
-    const int m0 = blockIdx.y * mt;
-    const int mcount = min(mt, s.M - m0);
+    const int m0 = tp.m_base + blockIdx.y * mt;
+    const int mcount = min(mt, tp.m_base + tp.m_count - m0);
     uint64_t *bar_mk = &bars[nv];
     if (threadIdx.x == 0) {
         for (int v = 0; v <= nv; ++v) mbar_init(&bars[v], 1);
@@ -370,7 +371,7 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         asm volatile("griddepcontrol.wait;" ::: "memory");
         mbar_expect_tx(&bars[0], var_bytes + bnd_bytes);
         bulk_g2s(scam, ctab, var_bytes, &bars[0]);
-        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)m0 * nrec, bnd_bytes, &bars[0]);
+        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)(m0 - tp.m_base) * nrec, bnd_bytes, &bars[0]);
         for (int v = 1; v < nv; ++v) {
             mbar_expect_tx(&bars[v], var_bytes);
             bulk_g2s(scam + (size_t)v * kRowPairs * kRowFrames, ctab + (size_t)v * kRowPairs * kRowFrames, var_bytes, &bars[v]);

@@ -252,6 +252,44 @@ mmb_status launch_extra_rows(DeviceProblem *p, const double *d_x, double *d_row,
 }
 
 mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, double *d_jac, int32_t *d_cols, double *d_dist_last) {
+    if (!p->cam_plans.empty() && !d_cols) {
+        static int rows_mc = -1;
+        if (rows_mc < 0) { const char *e = getenv("MMB_JAC_ROWS_MC"); rows_mc = e ? atoi(e) : 1; }
+        if (rows_mc) {
+            constexpr int W = 4, MINB = 4;
+            const TiledPlan &t0 = p->cam_plans[0];
+            const int nv = t0.VC + 1, nrec = (t0.VB + 1) * kBndRec;
+            const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
+            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
+            const bool fixed = t0.VC == 6 && t0.VB == 3;
+            auto kern = fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
+                              : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>);
+            int &mt = p->rows_mt[d_dist_last ? 1 : 0];
+            if (mt == 0) {
+                int occ = 1, sm_count = 1;
+                MMB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device));
+                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(64)));
+                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(32)));
+                const int slots = std::max(1, occ) * sm_count;
+                int G = std::max(1, slots / fb);
+                G = std::min(G, (t0.m_count + 1) / 2);
+                mt = (t0.m_count + G - 1) / G;
+                mt = std::min(64, (mt + 1) & ~1);
+            }
+            for (const TiledPlan &t : p->cam_plans) {
+                const int G = (t.m_count + mt - 1) / mt;
+                cudaLaunchConfig_t cfg{};
+                cfg.gridDim = dim3(fb, G); cfg.blockDim = dim3(32 * W); cfg.dynamicSmemBytes = smem_for(mt); cfg.stream = p->stream;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+                at[0].val.programmaticStreamSerializationAllowed = 1;
+                cfg.attrs = at; cfg.numAttrs = 1;
+                MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, t, mt, d_fvec, d_dist, d_jac, d_dist_last));
+                ++p->launches;
+            }
+            return MMB_OK;
+        }
+    }
     if (p->tiled_ok) {
         static int variant = -1;
         if (variant < 0) { const char *e = getenv("MMB_TILE"); variant = e ? atoi(e) : 4; }
@@ -573,6 +611,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
                 }
             TiledPlan &t = p->tiled;
             t.cam = 0; t.VC = (int)VC; t.VB = (int)VB;
+            t.m_base = 0; t.m_count = hp.M;
             t.uniform = 1;
             for (int mk = 1; mk < hp.M && t.uniform; ++mk) {
                 for (size_t v = 0; v < VC; ++v) if (ccol[(size_t)mk * VC + v] != ccol[v]) t.uniform = 0;
@@ -615,6 +654,77 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             t.last_attr_cam_var = -1;
             for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
             p->tiled_ok = true;
+        }
+    }
+    // ---- the rows kernel for several cameras (cfg5 shape): one launch per camera ---------------
+    // Markers in camera-major order, every camera animated with the same number of solved
+    // attributes, every marker the same column layout (its camera's attributes, then its bundle's).
+    if (hp.C > 1 && hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && !hp.maya_dag && hp.F >= 32 && hp.kmax <= 127) {
+        const size_t VC = hp.cam_deps[0].size();
+        size_t VB = 0;
+        bool ok = VC >= 1 && VC <= (size_t)kTileMaxVC;
+        for (int b = 0; b < hp.B; ++b) { VB = std::max(VB, hp.bnd_deps[b].size()); if (hp.bnd_fs[b] != 1) ok = false; }
+        ok = ok && VB <= (size_t)kTileMaxVB;
+        for (int c = 0; ok && c < hp.C; ++c)
+            if (hp.cam_deps[c].size() != VC || hp.cam_fs[c] != hp.F || hp.cam_mscale_varies[c] || (hp.cam_off[c] % 2) != 0) ok = false;
+        for (int mk = 1; ok && mk < hp.M; ++mk) if (hp.mkr_cam[mk] < hp.mkr_cam[mk - 1]) ok = false;
+        std::vector<int8_t> ccol((size_t)hp.M * std::max<size_t>(VC, 1), -1), bcol((size_t)hp.M * std::max<size_t>(VB, 1), -1);
+        std::vector<int32_t> battr((size_t)hp.M * std::max<size_t>(VB, 1), -1);
+        for (int mk = 0; ok && mk < hp.M; ++mk)
+            for (int c = 0; c < hp.mkr_k[mk]; ++c) {
+                const PlanEntry &e = hp.plan[(size_t)mk * hp.kmax + c];
+                if ((e.cam_var != 0) == (e.bnd_var != 0) || e.lens_var != 0) { ok = false; break; }
+                if (e.cam_var) ccol[(size_t)mk * VC + (e.cam_var - 1)] = (int8_t)c;
+                else { bcol[(size_t)mk * VB + (e.bnd_var - 1)] = (int8_t)c; battr[(size_t)mk * VB + (e.bnd_var - 1)] = e.attr; }
+            }
+        for (int mk = 0; ok && mk < hp.M; ++mk) {   // uniform layout, every column present
+            for (size_t v = 0; v < VC; ++v) if (ccol[(size_t)mk * VC + v] != ccol[v] || ccol[v] < 0) ok = false;
+            for (size_t v = 0; v < VB; ++v) if (bcol[(size_t)mk * VB + v] != bcol[v] || bcol[v] < 0) ok = false;
+        }
+        const char *force = getenv("MMB_JACOBIAN_PATH");
+        if (force && !strcmp(force, "generic")) ok = false;
+        if (ok) {
+            int8_t *d8 = nullptr;
+            TiledPlan base{};
+            base.VC = (int)VC; base.VB = (int)VB; base.uniform = 1;
+            for (int v = 0; v < kTileMaxVC; ++v) base.cam_col_u[v] = (size_t)v < VC ? ccol[v] : (int8_t)-1;
+            for (int v = 0; v <= kTileMaxVB; ++v) base.bnd_col_u[v] = (size_t)v < VB ? bcol[v] : (int8_t)-1;
+            for (int v = 0; v < kTileMaxVC; ++v) base.cam_coloff_u[v] = (long long)std::max<int>(base.cam_col_u[v], 0) * hp.nobs;
+            for (int v = 0; v <= kTileMaxVB; ++v) base.bnd_coloff_u[v] = (long long)std::max<int>(base.bnd_col_u[v], 0) * hp.nobs;
+            CK(A.upload(&d8, ccol)); base.mkr_cam_col = d8;
+            CK(A.upload(&d8, bcol)); base.mkr_bnd_col = d8;
+            CK(A.upload(&tmp_i, battr)); base.mkr_bnd_attr = tmp_i;
+            base.cam_dep_attr = nullptr;
+            {   // frame-blocked copy of the marker tracks (as for one camera)
+                const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
+                const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
+                double *d_blk = nullptr;
+                CK(A.alloc(&d_blk, nblk));
+                CK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
+                k_block_markers<<<blocks_for((long long)hp.M * hp.F, 256), 256, 0, p->stream>>>(d.obs_mx, d.obs_my, d.obs_w, hp.M, hp.F, d_blk);
+                ++p->launches;
+                CK(cudaGetLastError());
+                base.mk_blk = d_blk;
+            }
+            int mk = 0;
+            while (mk < hp.M) {
+                const int c = hp.mkr_cam[mk];
+                int end = mk;
+                while (end < hp.M && hp.mkr_cam[end] == c) ++end;
+                TiledPlan t = base;
+                t.cam = c; t.m_base = mk; t.m_count = end - mk;
+                t.bnd_contig = 1;
+                t.bnd_rec0 = hp.bnd_off[hp.mkr_bnd[mk]];
+                for (int q = mk; q < end && t.bnd_contig; ++q) {
+                    const int b = hp.mkr_bnd[q];
+                    if (hp.bnd_nvar[b] != (int)VB + 1 || hp.bnd_off[b] != t.bnd_rec0 + (int64_t)(q - mk) * (int64_t)(VB + 1) * kBndRec) t.bnd_contig = 0;
+                }
+                if (t.bnd_rec0 % 2) t.bnd_contig = 0;
+                t.last_attr_cam_var = -1;
+                for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[c][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
+                p->cam_plans.push_back(t);
+                mk = end;
+            }
         }
     }
     {   // evaluation-per-thread tiled kernel (k_jacobian_lens): lens in the loop and / or several cameras

@@ -166,3 +166,27 @@ def test_cfg5_subsample_solve_matches_block_sparse_oracle():
     assert np.max(np.abs(r.attr_values - ro.attr_values) / scale) <= 1e-6
     assert np.max(np.abs(r.error_dist - ro.error_dist)) <= 1e-6
     assert abs(r.error_avg - ro.error_avg) <= 1e-6
+
+
+@pytest.mark.parametrize("C,F,B", [(3, 40, 11), (2, 70, 6)])
+def test_multicam_rows_kernel_matches_oracle(C, F, B, monkeypatch):
+    """several cameras, full visibility, F >= 32: the register-tiled rows kernel, launched once per
+    camera over that camera's markers (the cfg5 evaluation path), against the oracle and against the
+    generic kernel; and a solve that uses it against the host-selected generic path."""
+    sb, _ = synth.make_multicam_scene(C, F, B, 4, fixed_bundles=3)
+    o = OracleProblem(sb)
+    with Problem(sb) as p:
+        x = p.initial_parameters() + np.random.default_rng(3).normal(0, 1e-2, p.n)
+        fast = p.eval_jacobian_blocks(x, want_cols=False)        # rows kernel (no column ids)
+        vals, cols = p.eval_jacobian_blocks(x)                   # generic kernel
+        Jo = o.eval_jacobian_dense(x)
+        from oraclelib import blocks_to_dense
+        assert np.abs(blocks_to_dense(vals, cols, p.n) - Jo).max() <= 1e-9 * np.abs(Jo).max()
+        assert np.abs(fast - vals).max() <= 1e-9 * np.abs(Jo).max()
+        r = p.solve()
+    monkeypatch.setenv("MMB_JACOBIAN_PATH", "generic")
+    with Problem(sb) as p:
+        r2 = p.solve()
+    assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (r2.reason_num, r2.iteration_num, r2.iteration_attempt_num)
+    assert np.max(np.abs(r.attr_values - r2.attr_values) / np.maximum(np.abs(r2.attr_values), 1.0)) <= 1e-6
+    assert np.max(np.abs(r.error_dist - r2.error_dist)) <= 1e-6
