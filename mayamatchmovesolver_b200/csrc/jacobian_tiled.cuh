@@ -41,6 +41,11 @@ struct TiledPlan {
     const double *mk_blk;        // marker x, y, weight re-blocked [frame block of 32][marker][3][32]
     int last_attr_cam_var;       // 0-based camera dep index of attr A-1 (the variant the
                                  // reference's errorDistanceList ends on), or -1
+    // sparse visibility (disabled / zero-weight marker frames leave no observation): for every
+    // (32-frame block, marker) the index of its first observation and which frames have one;
+    // the observation of frame lane is obs_base + popc(obs_mask & lanes below).  nullptr: dense grid.
+    const int32_t *obs_base;     // [frame blocks][M]
+    const uint32_t *obs_mask;    // [frame blocks][M]
 };
 
 #ifdef __CUDACC__
@@ -334,7 +339,7 @@ constexpr int kRowPairs = kCamRec / 2;  // 16-byte row pairs per camera variant
 // VCT / VBT: compile-time camera / bundle variant counts (0 = read them from the plan): with
 // them the variant loops unroll completely and the FP64 chains (~20 cycles per dependent
 // operation) of different variants interleave.
-template <int W, int MINB, bool DIST_LAST, int VCT = 0, int VBT = 0>
+template <int W, int MINB, bool DIST_LAST, int VCT = 0, int VBT = 0, bool SPARSE = false>
 __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, TiledPlan tp, int mt,
                                                                 double *__restrict__ fvec, double *__restrict__ dist,
                                                                 double *__restrict__ jac, double *__restrict__ dist_last) {
@@ -393,13 +398,26 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     for (int j = 0; j < 7; ++j) { const double2 t = scam[j * kRowFrames + lane]; cm[2 * j] = t.x; cm[2 * j + 1] = t.y; }
     mbar_wait(bar_mk, 0);
     bool variants_ready = false;
-    double2 *const jac2 = reinterpret_cast<double2 *>(jac) + f;
+    double2 *const jac2 = reinterpret_cast<double2 *>(jac);
     const int VB = VBT ? VBT : tp.VB, VC = VCT ? VCT : tp.VC;
+    const int32_t *const obase = SPARSE ? tp.obs_base + (size_t)blockIdx.x * s.M : nullptr;
+    const uint32_t *const omask = SPARSE ? tp.obs_mask + (size_t)blockIdx.x * s.M : nullptr;
+    const uint32_t below = (1u << lane) - 1u;
     for (int jj = 2 * w; jj < mcount; jj += 2 * W) {
         // an odd marker count evaluates its last marker twice (same values to the same addresses)
         const int j1 = min(jj + 1, mcount - 1);
-        const size_t i0 = (size_t)(m0 + jj) * F;
-        const size_t i1 = (size_t)(m0 + j1) * F;
+        // i0, i1: the two observations of this lane's frame; on0 / on1: they exist
+        size_t i0, i1;
+        bool on0 = true, on1 = true;
+        if (SPARSE) {
+            const uint32_t k0m = omask[m0 + jj], k1m = omask[m0 + j1];
+            on0 = (k0m >> lane) & 1u; on1 = (k1m >> lane) & 1u;
+            i0 = (size_t)obase[m0 + jj] + __popc(k0m & below);
+            i1 = (size_t)obase[m0 + j1] + __popc(k1m & below);
+        } else {
+            i0 = (size_t)(m0 + jj) * F + f;
+            i1 = (size_t)(m0 + j1) * F + f;
+        }
         const double *b0 = sbnd + (size_t)jj * nrec;
         const double *b1 = sbnd + (size_t)j1 * nrec;
         const double *k0 = smk + (size_t)jj * 3 * kRowFrames + lane, *k1 = smk + (size_t)j1 * 3 * kRowFrames + lane;
@@ -413,14 +431,14 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         // deviations first loses nothing to rounding
         const double c0 = imw * w0, c1 = imw * w1;
         if (fvec) {
-            double2 *fv = reinterpret_cast<double2 *>(fvec) + f;
-            fv[i0] = make_double2(dx0 * c0, dy0 * c0);
-            fv[i1] = make_double2(dx1 * c1, dy1 * c1);
+            double2 *fv = reinterpret_cast<double2 *>(fvec);
+            if (on0) fv[i0] = make_double2(dx0 * c0, dy0 * c0);
+            if (on1) fv[i1] = make_double2(dx1 * c1, dy1 * c1);
         }
         if (dist || DIST_LAST) {
             const double d0 = sqrt((dx0 * dx0) + (dy0 * dy0)) * imw, d1 = sqrt((dx1 * dx1) + (dy1 * dy1)) * imw;
-            if (dist) { dist[i0 + f] = d0; dist[i1 + f] = d1; }
-            if (DIST_LAST) { dist_last[i0 + f] = d0; dist_last[i1 + f] = d1; }
+            if (dist) { if (on0) dist[i0] = d0; if (on1) dist[i1] = d1; }
+            if (DIST_LAST) { if (on0) dist_last[i0] = d0; if (on1) dist_last[i1] = d1; }
         }
         double2 *const jp0 = jac2 + i0, *const jp1 = jac2 + i1;
         // bundle columns: base camera rows, perturbed bundle
@@ -432,11 +450,11 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             eval_pair_fma(cm, q1[0], q1[1], q1[2], mkx1, mky1, bx, by);
             const long long co = tp.bnd_coloff_u[v];
             const double g0 = c0 * q0[3], g1 = c1 * q1[3];
-            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            if (on0) jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            if (on1) jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
             if (DIST_LAST) {
-                if (tp.mkr_bnd_attr[(size_t)(m0 + jj) * VB + v] == s.A - 1) dist_last[i0 + f] = sqrt((ax * ax) + (ay * ay)) * imw;
-                if (tp.mkr_bnd_attr[(size_t)(m0 + j1) * VB + v] == s.A - 1) dist_last[i1 + f] = sqrt((bx * bx) + (by * by)) * imw;
+                if (on0 && tp.mkr_bnd_attr[(size_t)(m0 + jj) * VB + v] == s.A - 1) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (on1 && tp.mkr_bnd_attr[(size_t)(m0 + j1) * VB + v] == s.A - 1) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
         // camera columns: perturbed camera rows from shared memory, base bundle
@@ -456,11 +474,11 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             eval_pair_fma(cv, p1x, p1y, p1z, mkx1, mky1, bx, by);
             const long long co = tp.cam_coloff_u[v];
             const double g0 = c0 * inv_delta, g1 = c1 * inv_delta;
-            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            if (on0) jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            if (on1) jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
             if (DIST_LAST && tp.last_attr_cam_var == v) {
-                dist_last[i0 + f] = sqrt((ax * ax) + (ay * ay)) * imw;
-                dist_last[i1 + f] = sqrt((bx * bx) + (by * by)) * imw;
+                if (on0) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (on1) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
     }

@@ -217,6 +217,18 @@ __global__ void __launch_bounds__(256) k_block_markers(const double *__restrict_
     dst[0] = mx[i]; dst[kRowFrames] = my[i]; dst[2 * kRowFrames] = w[i];
 }
 
+// the same for sparse visibility: observation i belongs to (err_marker[i], err_frame[i])
+__global__ void __launch_bounds__(256) k_block_markers_sparse(const double *__restrict__ mx, const double *__restrict__ my,
+                                                              const double *__restrict__ w, const int32_t *__restrict__ em,
+                                                              const int32_t *__restrict__ ef, int nobs, int M,
+                                                              double *__restrict__ blk) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nobs) return;
+    const int mk = em[i], f = ef[i];
+    double *dst = &blk[(((size_t)(f / kRowFrames) * M + mk) * 3) * kRowFrames + (f % kRowFrames)];
+    dst[0] = mx[i]; dst[kRowFrames] = my[i]; dst[2 * kRowFrames] = w[i];
+}
+
 // ---- launchers -------------------------------------------------------------
 static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
@@ -262,8 +274,11 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
             auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
             const bool fixed = t0.VC == 6 && t0.VB == 3;
-            auto kern = fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
-                              : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>);
+            const bool sparse = t0.obs_base != nullptr;
+            auto kern = sparse ? (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3, true> : k_jacobian_rows<W, MINB, false, 6, 3, true>)
+                                        : (d_dist_last ? k_jacobian_rows<W, MINB, true, 0, 0, true> : k_jacobian_rows<W, MINB, false, 0, 0, true>))
+                               : (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
+                                        : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>));
             int &mt = p->rows_mt[d_dist_last ? 1 : 0];
             if (mt == 0) {
                 int occ = 1, sm_count = 1;
@@ -290,7 +305,12 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             return MMB_OK;
         }
     }
-    if (p->tiled_ok) {
+    // a sparse-visibility scene can only take the rows kernel (the other tiled kernels index a dense grid)
+    const bool tiled_sparse = p->tiled_ok && p->tiled.obs_base != nullptr;
+    const bool tiled_sparse_rows = tiled_sparse && !d_cols && p->tiled.uniform && p->tiled.mk_blk &&
+                                   p->hp.cam_fs[p->tiled.cam] == p->hp.F && p->hp.F > 1 && (p->hp.cam_off[p->tiled.cam] % 2) == 0 &&
+                                   !(getenv("MMB_JAC_ROWS") && atoi(getenv("MMB_JAC_ROWS")) == 0);
+    if (p->tiled_ok && (!tiled_sparse || tiled_sparse_rows)) {
         static int variant = -1;
         if (variant < 0) { const char *e = getenv("MMB_TILE"); variant = e ? atoi(e) : 4; }
         const int fblocks = (p->hp.F + kTileFrames - 1) / kTileFrames;
@@ -311,8 +331,11 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             static int fixed_mode = -1;
             if (fixed_mode < 0) { const char *e = getenv("MMB_ROWS_FIXED"); fixed_mode = e ? atoi(e) : 1; }
             const bool fixed = fixed_mode && p->tiled.VC == 6 && p->tiled.VB == 3;
-            auto kern = fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
-                              : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>);
+            const bool sparse = p->tiled.obs_base != nullptr;
+            auto kern = sparse ? (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3, true> : k_jacobian_rows<W, MINB, false, 6, 3, true>)
+                                        : (d_dist_last ? k_jacobian_rows<W, MINB, true, 0, 0, true> : k_jacobian_rows<W, MINB, false, 0, 0, true>))
+                               : (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
+                                        : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>));
             int &mt = p->rows_mt[d_dist_last ? 1 : 0];
             if (mt == 0) {  // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
                 int occ = 1, sm_count = 1;
@@ -435,6 +458,41 @@ mmb_status ensure_jacobian_buffers(DeviceProblem *p) {
     // the tiled kernel never touches unused columns: they stay 0 / -1
     MMB_CUDA_CHECK(cudaMemsetAsync(p->d_jac, 0, sizeof(double) * k * (size_t)p->hp.m, p->stream));
     MMB_CUDA_CHECK(cudaMemsetAsync(p->d_cols, 0xff, sizeof(int32_t) * k * (size_t)p->hp.nobs, p->stream));
+    return MMB_OK;
+}
+
+// frame-blocked copy of the marker tracks (one contiguous run per tile of k_jacobian_rows) and,
+// for sparse visibility, the (frame block, marker) -> first observation / frame mask index
+static mmb_status build_marker_blocks(DeviceProblem *p, TiledPlan *t) {
+    const HostProblem &hp = p->hp;
+    DeviceArena &A = p->arena;
+    const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
+    const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
+    double *d_blk = nullptr;
+    MMB_CUDA_CHECK(A.alloc(&d_blk, nblk));
+    MMB_CUDA_CHECK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
+    t->obs_base = nullptr; t->obs_mask = nullptr;
+    if (hp.dense_grid) {
+        k_block_markers<<<(unsigned)(((long long)hp.M * hp.F + 255) / 256), 256, 0, p->stream>>>(p->ds.obs_mx, p->ds.obs_my, p->ds.obs_w, hp.M, hp.F, d_blk);
+    } else {
+        k_block_markers_sparse<<<(unsigned)((hp.nobs + 255) / 256), 256, 0, p->stream>>>(p->ds.obs_mx, p->ds.obs_my, p->ds.obs_w, p->ds.err_marker,
+                                                                                     p->ds.err_frame, hp.nobs, hp.M, d_blk);
+        std::vector<int32_t> base((size_t)FB * hp.M, 0);
+        std::vector<uint32_t> mask((size_t)FB * hp.M, 0u);
+        for (int i = hp.nobs - 1; i >= 0; --i) {   // descending: the first observation of a block is written last
+            const size_t key = (size_t)(hp.err_frame[i] / kRowFrames) * hp.M + hp.err_marker[i];
+            mask[key] |= 1u << (hp.err_frame[i] % kRowFrames);
+            base[key] = i;
+        }
+        int32_t *d_b = nullptr; uint32_t *d_m = nullptr;
+        MMB_CUDA_CHECK(A.upload(&d_b, base));
+        MMB_CUDA_CHECK(A.upload(&d_m, mask));
+        MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));   // the host vectors go out of scope
+        t->obs_base = d_b; t->obs_mask = d_m;
+    }
+    ++p->launches;
+    MMB_CUDA_CHECK(cudaGetLastError());
+    t->mk_blk = d_blk;
     return MMB_OK;
 }
 
@@ -588,7 +646,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             if (hp.bnd_fs[b] != 1) bundles_static = false;
         }
         const size_t VC = hp.cam_deps[0].size();
-        bool eligible = hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && hp.C == 1 && !hp.maya_dag &&
+        bool eligible = opt->auto_diff_type == 0 && !hp.any_lens && hp.C == 1 && !hp.maya_dag &&
                         !hp.cam_mscale_varies[0] && bundles_static && VC <= (size_t)kTileMaxVC &&
                         VB <= (size_t)kTileMaxVB && hp.kmax <= 127;
         for (int mk = 0; eligible && mk < hp.M; ++mk)
@@ -639,27 +697,21 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
                     hp.bnd_off[b] != t.bnd_rec0 + (int64_t)mk * (int64_t)(VB + 1) * kBndRec) t.bnd_contig = 0;
             }
             if (t.bnd_rec0 % 2) t.bnd_contig = 0;  // 16-byte alignment of the bulk copy
-            t.mk_blk = nullptr;
-            if (hp.dense_grid) {  // frame-blocked copy of the marker tracks: one contiguous run per tile
-                const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
-                const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
-                double *d_blk = nullptr;
-                CK(A.alloc(&d_blk, nblk));
-                CK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
-                k_block_markers<<<blocks_for((long long)hp.M * hp.F, 256), 256, 0, p->stream>>>(d.obs_mx, d.obs_my, d.obs_w, hp.M, hp.F, d_blk);
-                ++p->launches;
-                CK(cudaGetLastError());
-                t.mk_blk = d_blk;
+            t.mk_blk = nullptr; t.obs_base = nullptr; t.obs_mask = nullptr;
+            // sparse visibility: only the rows kernel (uniform column layout) knows the index
+            if (hp.dense_grid || t.uniform) {
+                const mmb_status bs = build_marker_blocks(p, &t);
+                if (bs != MMB_OK) { delete p; return bs; }
             }
             t.last_attr_cam_var = -1;
             for (size_t v = 0; v < VC; ++v) if (hp.cam_deps[0][v] == hp.A - 1) t.last_attr_cam_var = (int)v;
-            p->tiled_ok = true;
+            p->tiled_ok = hp.dense_grid || (t.uniform && t.mk_blk);
         }
     }
     // ---- the rows kernel for several cameras (cfg5 shape): one launch per camera ---------------
     // Markers in camera-major order, every camera animated with the same number of solved
     // attributes, every marker the same column layout (its camera's attributes, then its bundle's).
-    if (hp.C > 1 && hp.dense_grid && opt->auto_diff_type == 0 && !hp.any_lens && !hp.maya_dag && hp.F >= 32 && hp.kmax <= 127) {
+    if (hp.C > 1 && opt->auto_diff_type == 0 && !hp.any_lens && !hp.maya_dag && hp.F >= 32 && hp.kmax <= 127) {
         const size_t VC = hp.cam_deps[0].size();
         size_t VB = 0;
         bool ok = VC >= 1 && VC <= (size_t)kTileMaxVC;
@@ -695,16 +747,9 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
             CK(A.upload(&d8, bcol)); base.mkr_bnd_col = d8;
             CK(A.upload(&tmp_i, battr)); base.mkr_bnd_attr = tmp_i;
             base.cam_dep_attr = nullptr;
-            {   // frame-blocked copy of the marker tracks (as for one camera)
-                const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
-                const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
-                double *d_blk = nullptr;
-                CK(A.alloc(&d_blk, nblk));
-                CK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
-                k_block_markers<<<blocks_for((long long)hp.M * hp.F, 256), 256, 0, p->stream>>>(d.obs_mx, d.obs_my, d.obs_w, hp.M, hp.F, d_blk);
-                ++p->launches;
-                CK(cudaGetLastError());
-                base.mk_blk = d_blk;
+            {
+                const mmb_status bs = build_marker_blocks(p, &base);
+                if (bs != MMB_OK) { delete p; return bs; }
             }
             int mk = 0;
             while (mk < hp.M) {

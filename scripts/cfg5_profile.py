@@ -1,6 +1,6 @@
 """cfg5-shaped solve on ONE GPU at a reduced size: per-phase times of the global LM
 (MMB_LM_PROFILE host loop) to see how the kernels behave with 48-wide frame blocks and a
-large static system.  usage: cfg5_profile.py C F B [iters]"""
+large static system.  usage: cfg5_profile.py C F B [iters [visibility]]"""
 import os
 import sys
 import time
@@ -13,8 +13,9 @@ from mayamatchmovesolver_b200.problem import Problem  # noqa: E402
 
 C, F, B = [int(v) for v in sys.argv[1:4]]
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 8
+vis = float(sys.argv[5]) if len(sys.argv) > 5 else 1.0
 t = time.perf_counter()
-sb, _ = synth.make_multicam_scene(C, F, B, 5)
+sb, _ = synth.make_multicam_scene(C, F, B, 5, visibility=vis)
 sb.arrays()
 print("scene s", time.perf_counter() - t, flush=True)
 t = time.perf_counter()

@@ -18,6 +18,7 @@ CASES = [
     dict(F=1, B=20, seed=1, solve_camera=False),
     dict(F=24, B=10, seed=2, solve_bundles=False),
     dict(F=30, B=40, seed=3),
+    dict(F=70, B=9, seed=12, drop_fraction=0.3, weights=True),   # sparse visibility in the rows kernel (F >= 32)
     dict(F=12, B=16, seed=4, lens=dict(degree2_distortion=0.05, degree2_u=0.002, degree2_v=-0.002, degree4_distortion=0.01),
          solve_focal=True, solve_lens=("degree2_distortion", "degree2_u", "degree2_v", "degree4_distortion"), focal_init=33.0),
     # the other lens models in the loop, coefficients and focal length solved (in_frame: the
