@@ -206,8 +206,19 @@ def run_own(args):
     # (SURVEY.md 8e).  Every rank builds the same scene from the same seed.
     F1, B = 1000, 500
     F = F1 * world
-    sb, _ = synth.make_scene(F, B, 3)
-    p = Problem(sb, device=local, shard=(rank, world)) if world > 1 else Problem(sb, device=local)
+
+    def rank_scene(seed, **kw):
+        """this rank's 1000 frames of the 1000 x N-frame scene (same bundles on every rank, the
+        camera path continues across ranks): no rank generates or ingests another rank's frames"""
+        return synth.make_scene(F1, B, seed, frame_offset=rank * F1, **kw)[0]
+
+    def rank_problem(scene, **kw):
+        if world > 1:
+            return Problem(scene, device=local, local_slice=(rank * F1, F), **kw)   # mmb_problem_create_shard_local
+        return Problem(scene, device=local, **kw)
+
+    sb = rank_scene(3)
+    p = rank_problem(sb)
     k = p.jacobian_kmax()
     bytes_per_obs = 48 + 16 * k  # SURVEY.md 8d: marker 24 B + residuals 16 B + distance 8 B + 2*k*8 B block J
 
@@ -256,18 +267,19 @@ def run_own(args):
 
     # ---- end to end through the public solve call, host buffers ----------
     # N = 1: mmb_problem_create + mmb_solve + destroy (one CUDA graph launch per solve).
-    # N > 1: the sharded global solve of the N x 1000-frame scene: create_shard + attach_comm
-    # (NCCL) + mmb_solve with one all-reduce of the reduced system per lmpar trial + destroy.
+    # N > 1: the sharded global solve of the N x 1000-frame scene: create_shard_local (every rank
+    # holds only its 1000 frames) + use_comm (NCCL) + mmb_solve with one all-reduce of the packed
+    # lower triangle of the reduced system per lmpar trial + destroy.
     E2E_REPS = 3
     comm = make_comm(group, device=local)  # NCCL communicator of the session, made once
 
     def e2e_once(seed):
-        sb2, _ = synth.make_scene(F, B, seed, noise_px=0.5)
+        sb2 = rank_scene(seed, noise_px=0.5)
         arrays = sb2.arrays()
         h2d = sum(a.nbytes for a in arrays.values())
         barrier()
         t0 = time.perf_counter()
-        q = Problem(sb2, device=local, iter_max=20, shard=(rank, world)) if world > 1 else Problem(sb2, device=local, iter_max=20)
+        q = rank_problem(sb2, iter_max=20)
         with q:
             if world > 1:
                 q.use_comm(comm)
@@ -294,12 +306,38 @@ def run_own(args):
     if comm is not None:
         comm.close()
 
+    # ---- strong scaling: the FIXED cfg3 problem (1000 frames x 500 bundles) over the N ranks,
+    # 1000 / N frames each; the replicated Cholesky of the 1500-dim reduced system and the
+    # all-reduce are the serial (Amdahl) part
+    strong = None
+    if world > 1 and F1 % world == 0:
+        Fs = F1 // world
+        def strong_once(seed):
+            sbs, _ = synth.make_scene(Fs, B, seed, noise_px=0.5, frame_offset=rank * Fs)
+            barrier()
+            t0 = time.perf_counter()
+            with Problem(sbs, device=local, iter_max=20, local_slice=(rank * Fs, F1)) as q:
+                q.use_comm(comm_strong)
+                r = q.solve()
+            return time.perf_counter() - t0, r
+        comm_strong = make_comm(group, device=local)
+        strong_once(100)
+        ts = []
+        for rep in range(3):
+            dt, rs = strong_once(200 + rep)
+            (dt,) = allmax([dt])
+            ts.append(dt)
+        comm_strong.close()
+        strong = {"workload": "fixed cfg3: 1000 frames x 500 bundles split over %d GPUs (%d frames each)" % (world, Fs),
+                  "seconds": sum(ts) / len(ts), "lm_outer_iterations": rs.iteration_attempt_num, "reason_num": rs.reason_num,
+                  "device_linear_s": rs.timer_linear_s, "device_jacobian_s": rs.timer_jacobian_s}
+
     # ---- per-frame mode (cfg2): 240 x N frames x 50 bundles, frames sharded, no collective
     def perframe_once(seed):
-        sbp, _ = synth.make_scene(240 * world, 50, seed, solve_bundles=False)
+        sbp, _ = synth.make_scene(240, 50, seed, solve_bundles=False, frame_offset=240 * rank)
         barrier()
         t0 = time.perf_counter()
-        q = (Problem(sbp, device=local, frame_solve_mode=1, shard=(rank, world)) if world > 1
+        q = (Problem(sbp, device=local, frame_solve_mode=1, local_slice=(240 * rank, 240 * world)) if world > 1
              else Problem(sbp, device=local, frame_solve_mode=1))
         with q:
             agg, per = q.solve_per_frame()
@@ -399,14 +437,15 @@ def run_own(args):
         "config": {"workload": WORKLOAD, "frames": F, "frames_per_gpu": F1, "bundles": B, "params_per_gpu": n_rank,
                    "observations_per_gpu": nobs_rank,
                    "local_params_per_obs_k": k, "l2": "flushed before every step (256 MiB memset outside the event brackets)",
-                   "sharding": "one scene of 1000 x N frames; frame-range shard of 1000 frames per GPU; no data-path collective in the evaluation step"},
+                   "sharding": "one scene of 1000 x N frames; each rank generates and holds only its own 1000 frames (mmb_problem_create_shard_local); no data-path collective in the evaluation step"},
         "clocks": clocks,
         "gpu_launches": int(launches),
         "wall_s_timed_region": t_wall,
         "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "what": ("mmb_problem_create + mmb_solve (iter_max=20) + destroy with host buffers, mean of %d solves; "
                          "evals = observations x Jacobian evaluations" % E2E_REPS) +
-                        ("; sharded global solve, one NCCL all-reduce of the reduced system per lmpar trial, "
+                        ("; sharded global solve (mmb_problem_create_shard_local: each rank holds only its 1000 frames), "
+                         "one NCCL all-reduce of the packed lower triangle of the reduced system per lmpar trial, "
                          "session communicator (mmb_comm_create) made once outside the timed region" if world > 1 else ""),
                 "seconds": e2e_dt / E2E_REPS, "lm_outer_iterations": e2e_iters / E2E_REPS, "nfev": r.iteration_num,
                 "reason_num": r.reason_num, "error_avg_px": r.error_avg,
@@ -450,6 +489,8 @@ def run_own(args):
             "kernel_vs_stream": floor_ms / (jac_ms / args.steps)}
     if cfg4 is not None:
         line["cfg4_eval"] = cfg4
+    if strong is not None:
+        line["strong_scaling_cfg3"] = strong
     if world == 1 and not args.no_cpu:
         leg = cpu_reference_leg(steps=1)
         line["cpu_baseline"] = {"value": leg["value"], "unit": "evals/s", "cores": 1, "kind": "port",

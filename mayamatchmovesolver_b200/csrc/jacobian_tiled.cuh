@@ -412,6 +412,7 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         if (SPARSE) {
             const uint32_t k0m = omask[m0 + jj], k1m = omask[m0 + j1];
             on0 = (k0m >> lane) & 1u; on1 = (k1m >> lane) & 1u;
+            if ((k0m | k1m) == 0u) continue;   // neither track lives in this frame block
             i0 = (size_t)obase[m0 + jj] + __popc(k0m & below);
             i1 = (size_t)obase[m0 + j1] + __popc(k1m & below);
         } else {

@@ -599,6 +599,32 @@ __global__ void k_schur_damp(LmDims d, const LmState *st, const double *__restri
     } else *s = (r == d.ns) ? 0.0 : 1.0;
 }
 
+// Sharded solve: only the lower triangle of S (by 64-wide block rows: row r keeps columns
+// 0 .. 64 (r / 64 + 1) - 1) and its right-hand side row ns travel over NVLink.  Packed length:
+__host__ __device__ inline size_t tri_pack_offset(int r) {   // first packed element of row r
+    const size_t b = (size_t)(r >> 6), within = (size_t)(r & 63);
+    return 64 * 64 * (b * (b + 1) / 2) + within * 64 * (b + 1);
+}
+__host__ __device__ inline size_t tri_pack_count(int rows) { return tri_pack_offset(rows); }
+// pack = 1: S -> buf; pack = 0: buf -> S, and the damping / padding diagonal of k_schur_damp
+__global__ void __launch_bounds__(256) k_tri_pack(LmDims d, const LmState *st, const double *__restrict__ diag,
+                                                  const int32_t *__restrict__ i2p, double *__restrict__ S,
+                                                  double *__restrict__ buf, int rows, int pack) {
+    const int r = blockIdx.x;
+    if (r < rows) {
+        const int width = 64 * ((r >> 6) + 1);
+        double *row = S + (size_t)r * d.NSP;
+        double *dst = buf + tri_pack_offset(r);
+        if (pack) { for (int c = threadIdx.x; c < width; c += blockDim.x) dst[c] = row[c]; }
+        else { for (int c = threadIdx.x; c < width; c += blockDim.x) row[c] = dst[c]; }
+    }
+    if (!pack && threadIdx.x == 0 && r < d.NSP) {
+        double *sd = &S[(size_t)r * d.NSP + r];
+        if (r < d.ns) { const double dd = diag[i2p[d.KE + r]]; *sd += st->par_cur * dd * dd; }
+        else *sd = (r == d.ns) ? 0.0 : 1.0;
+    }
+}
+
 // ---- DMMA helpers ------------------------------------------------------------------
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"

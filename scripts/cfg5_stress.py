@@ -92,7 +92,7 @@ if g.rank == 0:
                parameters_per_rank=n_local, static_parameters=n_static,
                eval_ms=ms_eval, evals_per_s=nobs / ms_eval * 1e3, scene_gen_s=t_scene, create_s=t_create,
                iter_max=a.iters, solves=solves, host_syncs_graph_launches=stats,
-               reduced_system_allreduce_bytes=8 * (((n_static + 1 + 63) // 64) * 64) ** 2)
+               reduced_system_allreduce_bytes=8 * sum(64 * 64 * (b + 1) for b in range((n_static + 1 + 63) // 64)))  # packed lower triangle
     print(json.dumps(out))
     os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
     json.dump(out, open(a.out, "w"), indent=1)
