@@ -618,6 +618,7 @@ __global__ void __launch_bounds__(256) k_tri_pack(LmDims d, const LmState *st, c
         if (pack) { for (int c = threadIdx.x; c < width; c += blockDim.x) dst[c] = row[c]; }
         else { for (int c = threadIdx.x; c < width; c += blockDim.x) row[c] = dst[c]; }
     }
+    __syncthreads();   // the diagonal entry of this row is in place before it is damped
     if (!pack && threadIdx.x == 0 && r < d.NSP) {
         double *sd = &S[(size_t)r * d.NSP + r];
         if (r < d.ns) { const double dd = diag[i2p[d.KE + r]]; *sd += st->par_cur * dd * dd; }
