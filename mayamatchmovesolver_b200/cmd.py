@@ -138,12 +138,11 @@ def select_scene(scene, camera=None, marker=None, attr=None, frame=None, attrSti
         for entry in flags:
             if len(entry) != 4:
                 continue   # the command logs an error and skips the flag
-            plug, wplug, vplug, valplug = entry
-            ref = sb.plug(plug)
+            as_ref = lambda v: int(sb.plug(v)) if isinstance(v, str) else int(v)   # plug name or attribute-store ref
+            ref, wref, vref, valref = (as_ref(v) for v in entry)
             if ref not in sb.attr_ref:
                 continue   # "is not a declared attribute"
-            sb.add_stiffness(sb.attr_ref.index(ref), int(sb.plug(wplug)), int(sb.plug(vplug)), int(sb.plug(valplug)),
-                             smoothness=smooth)
+            sb.add_stiffness(sb.attr_ref.index(ref), wref, vref, valref, smoothness=smooth)
     return sb
 
 

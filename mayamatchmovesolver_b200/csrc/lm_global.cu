@@ -79,6 +79,7 @@ struct LmWorkspace {
     // stiffness / smoothness rows: their one Jacobian entry each and its parameter
     double *jext = nullptr;
     int32_t *ext_pid = nullptr, *p2i = nullptr;
+    int *d_zero = nullptr;       // an int that stays 0: the cancel word k_cond polls in a sharded graph (see lm_graph_build)
     double *tri_buf = nullptr;   // sharded solve: packed lower triangle of S for the all-reduce (allocated on first use)
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
@@ -573,6 +574,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     CKW(A.upload(&w->attr_slot, hp.attr_slot));
     CKW(A.upload(&w->i2p, hp.int_to_par));
     CKW(A.upload(&w->p2i, hp.par_to_int));
+    CKW(A.alloc(&w->d_zero, 1));
+    CKW(cudaMemsetAsync(w->d_zero, 0, sizeof(int), p->stream));
     CKW(A.alloc(&w->jext, (size_t)std::max(hp.n_extra, 1)));
     CKW(A.alloc(&w->ext_pid, (size_t)std::max(hp.n_extra, 1)));
     {
@@ -1050,6 +1053,10 @@ static mmb_status capture_conditional(cudaStream_t s, cudaGraphConditionalHandle
 static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     LmWorkspace *w = p->lm;
     cudaStream_t s = p->stream;
+    // A sharded solve must not act on a rank-local cancel word at the loop head (the ranks would
+    // leave the collective sequence at different points): there the request only travels through
+    // the trial's all-reduce (k_ctrl_trial / k_ctrl_accept) and k_cond polls a word that stays 0.
+    const int *cond_cancel = (p->comm && p->comm->world > 1) ? w->d_zero : w->d_cancel;
     mmb_status st = MMB_OK;
     cudaGraph_t g = nullptr, body_loop = nullptr, body_jac = nullptr, body_lmpar = nullptr, body_trial = nullptr, tmp = nullptr;
     cudaGraphConditionalHandle h_loop, h_jac, h_lmpar, h_trial;
@@ -1082,7 +1089,7 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     long long l0 = p->launches;
     GB(cudaStreamBeginCaptureToGraph(s, g, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
     GS(enqueue_prologue(p));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondStart, h_loop, h_loop);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondStart, h_loop, h_loop);
     ++p->launches;
     GS(capture_conditional(s, h_loop, cudaGraphCondTypeWhile, &body_loop));
     GS(enqueue_epilogue(p));
@@ -1105,11 +1112,11 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
         }
     }
     GB(cudaStreamBeginCaptureToGraph(s, body_loop, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondLoopHead, h_jac, h_jac);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondLoopHead, h_jac, h_jac);
     GS(capture_conditional(s, h_jac, cudaGraphCondTypeIf, &body_jac));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterJac, h_lmpar, h_lmpar);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondAfterJac, h_lmpar, h_lmpar);
     GS(capture_conditional(s, h_lmpar, cudaGraphCondTypeWhile, &body_lmpar));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterLmpar, h_trial, h_loop);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondAfterLmpar, h_trial, h_loop);
     p->launches += 3;
     GS(capture_conditional(s, h_trial, cudaGraphCondTypeIf, &body_trial));
     GB(cudaStreamEndCapture(s, &tmp));
@@ -1124,7 +1131,7 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     l0 = p->launches;
     GB(cudaStreamBeginCaptureToGraph(s, body_lmpar, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
     GS(enqueue_lmpar_step(p));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondInLmpar, h_lmpar, h_lmpar);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondInLmpar, h_lmpar, h_lmpar);
     ++p->launches;
     GB(cudaStreamEndCapture(s, &tmp));
     w->body_launches[2] = (int)(p->launches - l0);
@@ -1132,7 +1139,7 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     l0 = p->launches;
     GB(cudaStreamBeginCaptureToGraph(s, body_trial, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
     GS(enqueue_trial(p));
-    k_cond<<<1, 1, 0, s>>>(w->st, w->d_cancel, kCondAfterTrial, h_loop, h_loop);
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondAfterTrial, h_loop, h_loop);
     ++p->launches;
     GB(cudaStreamEndCapture(s, &tmp));
     w->body_launches[3] = (int)(p->launches - l0);
@@ -1241,7 +1248,13 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     }
     int graph_mode = 1;
     { const char *e = getenv("MMB_LM_GRAPH"); if (e) graph_mode = atoi(e); }
-    bool use_graph = graph_mode && !sharded && !w->profile && !w->graph_failed;
+    // sharded: the NCCL all-reduces are captured into the graph bodies like the kernels around them
+    // (every rank builds and launches the same graph); the in-process "local" backend orders its
+    // reduction with host barriers and cannot be captured
+    static int sharded_graph = -1;
+    if (sharded_graph < 0) { const char *e = getenv("MMB_LM_GRAPH_SHARDED"); sharded_graph = e ? atoi(e) : 0; }
+    const bool graph_capable = !sharded || (sharded_graph && !strcmp(p->comm->backend(), "nccl"));
+    bool use_graph = graph_mode && graph_capable && !w->profile && !w->graph_failed;
     if (use_graph && !w->graph_exec) {
         const auto tg0 = clk::now();
         mmb_status gs = lm_graph_build(p, 0);

@@ -197,8 +197,16 @@ class SolverStep:
     def set_attributes_use_static(self, v):
         self._use_static = bool(v)
 
-    def set_use_stiffness(self, v):      # v1 Maya-DAG residuals: accepted, no effect
+    def set_use_stiffness(self, v):
+        """pass the scene's `-attrStiffness` entries to the command (solverstep.py:596-606); the rows are
+        evaluated in sceneGraphMode 1 and stay zero in mode 2, as in the reference"""
         self._use_stiffness = bool(v)
+
+    def get_use_stiffness(self):
+        return self._use_stiffness
+
+    def get_use_smoothness(self):
+        return self._use_smoothness
 
     def set_use_smoothness(self, v):
         self._use_smoothness = bool(v)
@@ -225,6 +233,13 @@ class SolverStep:
             if self._data[key] is not None:
                 v = self._data[key]
                 kwargs[flag] = int(v) if isinstance(v, bool) else v
+        # stiffness / smoothness flags of the attributes that take part (solverstep.py:596-636)
+        refs = {int(a[0]) if not isinstance(a[0], str) else scene.plug(a[0]) for a in attrs}
+        for use, entries, flag in ((self._use_stiffness, scene.stiffness, "attrStiffness"),
+                                   (self._use_smoothness, scene.smoothness, "attrSmoothness")):
+            rows = [(scene.attr_ref[e[0]], e[1], e[2], e[3]) for e in entries if scene.attr_ref[e[0]] in refs] if use else []
+            if rows:
+                kwargs[flag] = rows
         action = Action("mmSolver", kwargs=kwargs)
         vaction = None
         if withtest:
