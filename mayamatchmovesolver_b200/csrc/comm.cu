@@ -4,6 +4,7 @@
 #include <dlfcn.h>
 #include <nccl.h>  // types and prototypes only: the library itself is opened with dlopen
 
+#include <algorithm>
 #include <atomic>
 #include <condition_variable>
 #include <cstring>
@@ -25,6 +26,7 @@ struct NcclApi {
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
     std::string error;
 };
@@ -46,16 +48,194 @@ NcclApi *nccl_api() {
         MMB_SYM(CommInitRank, "ncclCommInitRank")
         MMB_SYM(CommDestroy, "ncclCommDestroy")
         MMB_SYM(AllReduce, "ncclAllReduce")
+        MMB_SYM(AllGather, "ncclAllGather")
         MMB_SYM(GetErrorString, "ncclGetErrorString")
 #undef MMB_SYM
     });
     return &api;
 }
 
+// ---- peer-memory all-reduce ---------------------------------------------------------------------
+// Arena of one rank (cudaMalloc, exported with CUDA IPC, mapped by every peer):
+//   [0, 4096)          header: arrive[q] (64-byte stride) written by rank q; own epoch / sequence
+//                      counters (advanced by the kernels themselves, so a replayed graph works);
+//                      error word
+//   small slots        [parity 2][rank 8][kPeerSmall doubles]: contributions to small all-reduces
+//   big buffer         the in-place operand of the big all-reduce (packed triangle of S)
+constexpr int kPeerMax = 8;
+constexpr size_t kPeerSmall = 64 * 1024;   // doubles per slot
+constexpr size_t kPeerHeader = 4096;
+struct PeerView {
+    char *base[kPeerMax];
+    int rank, world;
+    size_t small_off, big_off;
+};
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// one thread: tell every peer this rank has arrived at barrier `epoch`, wait for all of them
+__device__ void peer_barrier(const PeerView &v) {
+    unsigned *hdr = reinterpret_cast<unsigned *>(v.base[v.rank]);
+    const unsigned e = hdr[256] + 1u;   // own epoch counter (offset 1024)
+    hdr[256] = e;
+    __threadfence_system();
+    for (int q = 0; q < v.world; ++q) st_release_sys(reinterpret_cast<unsigned *>(v.base[q]) + 16 * v.rank, e);
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int q = 0; q < v.world; ++q) {
+        const unsigned *flag = hdr + 16 * q;
+        while ((int)(ld_acquire_sys(flag) - e) < 0) {
+            unsigned long long t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t - t0 > 20000000000ull) { hdr[272] = 1u; return; }   // 20 s: ranks out of step (error word, offset 1088)
+            __nanosleep(40);
+        }
+    }
+}
+__global__ void k_peer_barrier(PeerView v) {
+    if (threadIdx.x == 0) peer_barrier(v);
+}
+// small all-reduce: every rank stores its values into its slot of every arena, barrier, every rank
+// folds the slots of its own arena in rank order (identical sums on every rank)
+__global__ void __launch_bounds__(1024) k_peer_small(PeerView v, double *buf, int count, int is_max) {
+    unsigned *hdr = reinterpret_cast<unsigned *>(v.base[v.rank]);
+    __shared__ unsigned parity;
+    if (threadIdx.x == 0) { parity = hdr[257] & 1u; hdr[257] += 1u; }   // own sequence counter (offset 1028)
+    __syncthreads();
+    const size_t slot = ((size_t)parity * kPeerMax + v.rank) * kPeerSmall;
+    for (int q = 0; q < v.world; ++q) {
+        double *dst = reinterpret_cast<double *>(v.base[q] + v.small_off) + slot;
+        for (int i = threadIdx.x; i < count; i += blockDim.x) dst[i] = buf[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) peer_barrier(v);
+    __syncthreads();
+    const double *mine = reinterpret_cast<const double *>(v.base[v.rank] + v.small_off) + (size_t)parity * kPeerMax * kPeerSmall;
+    for (int i = threadIdx.x; i < count; i += blockDim.x) {
+        double a = __ldcg(&mine[i]);
+        for (int q = 1; q < v.world; ++q) {
+            const double t = __ldcg(&mine[(size_t)q * kPeerSmall + i]);
+            a = is_max ? fmax(a, t) : a + t;
+        }
+        buf[i] = a;
+    }
+}
+// big all-reduce in place on the arenas' big buffers: rank r owns chunk r -- it loads that chunk from
+// every arena (rank order), and stores the sum into every arena.  Between two barrier kernels.
+__global__ void __launch_bounds__(256) k_peer_big(PeerView v, size_t count) {
+    const size_t chunk = ((count + v.world - 1) / v.world + 1) & ~(size_t)1;
+    const size_t lo = chunk * v.rank, hi = lo + chunk < count ? lo + chunk : count;
+    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+        double a = __ldcg(reinterpret_cast<const double *>(v.base[0] + v.big_off) + i);
+        for (int q = 1; q < v.world; ++q) a += __ldcg(reinterpret_cast<const double *>(v.base[q] + v.big_off) + i);
+        for (int q = 0; q < v.world; ++q) reinterpret_cast<double *>(v.base[q] + v.big_off)[i] = a;
+    }
+    __threadfence_system();
+}
+
 struct NcclComm : Comm {
     ncclComm_t comm = nullptr;
-    ~NcclComm() override { if (comm) nccl_api()->CommDestroy(comm); }
+    // peer-memory path
+    bool peer_ok = false;
+    PeerView view{};
+    size_t big_doubles = 0;
+    void *arena = nullptr;
+    ~NcclComm() override {
+        if (peer_ok || arena) {
+            cudaDeviceSynchronize();
+            if (comm && peer_ok) {   // nobody unmaps while a peer may still touch the arenas
+                double *d = nullptr;
+                if (cudaMalloc((void **)&d, 8) == cudaSuccess) {
+                    cudaMemset(d, 0, 8);
+                    nccl_api()->AllReduce(d, d, 1, ncclDouble, ncclSum, comm, nullptr);
+                    cudaDeviceSynchronize();
+                    cudaFree(d);
+                }
+            }
+            for (int q = 0; q < world; ++q)
+                if (q != rank && view.base[q]) cudaIpcCloseMemHandle(view.base[q]);
+            if (arena) cudaFree(arena);
+        }
+        if (comm) nccl_api()->CommDestroy(comm);
+    }
+    // collective: map every rank's arena; all ranks agree on the outcome
+    void peer_setup() {
+        const char *e = getenv("MMB_PEER");
+        if ((e && atoi(e) == 0) || world > kPeerMax || world < 2) return;
+        size_t big_mb = 64;
+        if (const char *m = getenv("MMB_PEER_ARENA_MB")) big_mb = (size_t)std::max(1, atoi(m));
+        big_doubles = big_mb * 1024 * 1024 / 8;
+        const size_t small_bytes = 2 * kPeerMax * kPeerSmall * 8;
+        const size_t bytes = kPeerHeader + small_bytes + big_doubles * 8;
+        NcclApi *api = nccl_api();
+        double ok = 1.0;
+        cudaIpcMemHandle_t mine{}, all[kPeerMax];
+        char *d_send = nullptr, *d_recv = nullptr;
+        double *d_ok = nullptr;
+        if (cudaMalloc(&arena, bytes) != cudaSuccess) { arena = nullptr; ok = 0.0; }
+        if (ok > 0 && (cudaMemset(arena, 0, bytes) != cudaSuccess || cudaIpcGetMemHandle(&mine, arena) != cudaSuccess)) ok = 0.0;
+        cudaGetLastError();
+        if (cudaMalloc((void **)&d_send, sizeof(mine)) != cudaSuccess || cudaMalloc((void **)&d_recv, sizeof(mine) * world) != cudaSuccess ||
+            cudaMalloc((void **)&d_ok, 8) != cudaSuccess) { cudaGetLastError(); return; }   // not even the agreement can run: NCCL only
+        cudaMemcpy(d_send, &mine, sizeof(mine), cudaMemcpyHostToDevice);
+        bool gathered = api->AllGather(d_send, d_recv, sizeof(mine), ncclChar, comm, nullptr) == ncclSuccess &&
+                        cudaDeviceSynchronize() == cudaSuccess &&
+                        cudaMemcpy(all, d_recv, sizeof(mine) * world, cudaMemcpyDeviceToHost) == cudaSuccess;
+        if (!gathered) ok = 0.0;
+        for (int q = 0; q < world; ++q) view.base[q] = nullptr;
+        if (ok > 0) {
+            view.base[rank] = static_cast<char *>(arena);
+            for (int q = 0; q < world && ok > 0; ++q) {
+                if (q == rank) continue;
+                void *ptr = nullptr;
+                if (cudaIpcOpenMemHandle(&ptr, all[q], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = 0.0; }
+                view.base[q] = static_cast<char *>(ptr);
+            }
+        }
+        // agreement: the path is on only if it is on everywhere
+        cudaMemcpy(d_ok, &ok, 8, cudaMemcpyHostToDevice);
+        if (api->AllReduce(d_ok, d_ok, 1, ncclDouble, ncclMin, comm, nullptr) != ncclSuccess || cudaDeviceSynchronize() != cudaSuccess) ok = 0.0;
+        else cudaMemcpy(&ok, d_ok, 8, cudaMemcpyDeviceToHost);
+        cudaFree(d_send); cudaFree(d_recv); cudaFree(d_ok);
+        view.rank = rank; view.world = world;
+        view.small_off = kPeerHeader; view.big_off = kPeerHeader + small_bytes;
+        peer_ok = ok > 0;
+        if (!peer_ok) {
+            for (int q = 0; q < world; ++q) if (q != rank && view.base[q]) { cudaIpcCloseMemHandle(view.base[q]); view.base[q] = nullptr; }
+            if (arena) { cudaFree(arena); arena = nullptr; }
+        }
+        if (getenv("MMB_LM_GRAPH_VERBOSE")) fprintf(stderr, "[mmb] rank %d: peer-memory all-reduce %s (arena %zu MB)\n", rank, peer_ok ? "on" : "off", bytes >> 20);
+    }
+    double *peer_buffer(size_t count) override {
+        return (peer_ok && count <= big_doubles) ? reinterpret_cast<double *>(view.base[rank] + view.big_off) : nullptr;
+    }
+    bool capturable(size_t max_small) const override { return peer_ok && max_small <= kPeerSmall; }
+    bool peer_error() override {
+        if (!peer_ok) return false;
+        unsigned err = 0;
+        cudaMemcpy(&err, view.base[rank] + 1088, 4, cudaMemcpyDeviceToHost);
+        return err != 0;
+    }
     mmb_status allreduce(double *buf, size_t count, bool is_max, cudaStream_t stream) override {
+        if (peer_ok && !is_max && buf == reinterpret_cast<double *>(view.base[rank] + view.big_off) && count <= big_doubles) {
+            k_peer_barrier<<<1, 32, 0, stream>>>(view);          // every rank's operand is in its arena
+            const unsigned blocks = (unsigned)std::min<size_t>((count / world + 255) / 256 + 1, 592);
+            k_peer_big<<<blocks, 256, 0, stream>>>(view, count);
+            k_peer_barrier<<<1, 32, 0, stream>>>(view);          // every chunk is back in every arena
+            if (cudaGetLastError() != cudaSuccess) { set_last_error("peer all-reduce launch failed"); return MMB_ERR_CUDA; }
+            return MMB_OK;
+        }
+        if (peer_ok && count <= kPeerSmall) {
+            k_peer_small<<<1, 1024, 0, stream>>>(view, buf, (int)count, is_max ? 1 : 0);
+            if (cudaGetLastError() != cudaSuccess) { set_last_error("peer all-reduce launch failed"); return MMB_ERR_CUDA; }
+            return MMB_OK;
+        }
         NcclApi *api = nccl_api();
         const ncclResult_t r = api->AllReduce(buf, buf, count, ncclDouble, is_max ? ncclMax : ncclSum, comm, stream);
         if (r != ncclSuccess) { set_last_error(std::string("ncclAllReduce: ") + api->GetErrorString(r)); return MMB_ERR_COMM; }
@@ -173,6 +353,7 @@ mmb_status comm_create(const uint8_t id[MMB_COMM_ID_BYTES], int rank, int world,
         delete c;
         return MMB_ERR_COMM;
     }
+    c->peer_setup();   // collective: CUDA IPC mapping of the ranks' arenas (falls back to NCCL alone)
     *out = c;
     return MMB_OK;
 }

@@ -25,6 +25,18 @@ struct Comm {
     // in-place all-reduce of buf[0..count) on `stream`; sum, or max when is_max
     virtual mmb_status allreduce(double *buf, size_t count, bool is_max, cudaStream_t stream) = 0;
     virtual const char *backend() const = 0;
+    // Peer-memory path (NVLink / NVSwitch, one process per GPU): the ranks map each other's arena
+    // (CUDA IPC) and the all-reduce is a plain kernel that loads the peers' buffers and stores the
+    // sum back to them, ordered by flag barriers in the same memory -- no library call, so the
+    // collective can sit inside the conditional CUDA graph of the LM loop.
+    // peer_buffer: a buffer of >= count doubles inside this rank's arena (the big all-reduce runs
+    // in place on it), or nullptr when the path is unavailable / too small.
+    virtual double *peer_buffer(size_t count) { (void)count; return nullptr; }
+    // can every all-reduce of a solve (big: the peer buffer; small: up to max_small doubles) be
+    // captured into a CUDA graph?
+    virtual bool capturable(size_t max_small) const { (void)max_small; return false; }
+    // a barrier of the last solve timed out (ranks out of step): results are not to be trusted
+    virtual bool peer_error() { return false; }
 };
 
 mmb_status comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES], int local_backend);

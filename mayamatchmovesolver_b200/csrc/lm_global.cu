@@ -80,6 +80,7 @@ struct LmWorkspace {
     double *jext = nullptr;
     int32_t *ext_pid = nullptr, *p2i = nullptr;
     int *d_zero = nullptr;       // an int that stays 0: the cancel word k_cond polls in a sharded graph (see lm_graph_build)
+    bool tri_is_peer = false;
     double *tri_buf = nullptr;   // sharded solve: packed lower triangle of S for the all-reduce (allocated on first use)
     double *U = nullptr, *gE = nullptr, *W = nullptr, *Y = nullptr, *V = nullptr, *S = nullptr;
     double *Lf = nullptr, *Ld = nullptr;
@@ -1243,17 +1244,27 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     MMB_CUDA_CHECK(cudaMemcpyAsync(w->st, w->h_st, sizeof(LmState), cudaMemcpyHostToDevice, p->stream));
 
     const bool sharded = p->comm && p->comm->world > 1;
-    if (sharded && !w->tri_buf) {
-        MMB_CUDA_CHECK(w->arena.alloc(&w->tri_buf, tri_pack_count(w->d.ns + 1)));
+    bool peer_graph = false;
+    if (sharded) {
+        // the packed triangle lives in the communicator's peer-mapped arena when there is one (the
+        // all-reduce then runs in place over NVLink peer loads / stores, and is graph-capturable)
+        const size_t tri_n = tri_pack_count(w->d.ns + 1);
+        double *pb = p->comm->peer_buffer(tri_n);
+        if (pb) w->tri_buf = pb;
+        else if (!w->tri_buf || w->tri_is_peer) MMB_CUDA_CHECK(w->arena.alloc(&w->tri_buf, tri_n));
+        w->tri_is_peer = pb != nullptr;
+        peer_graph = pb && p->comm->capturable(std::max<size_t>((size_t)2 * w->d.ns, (size_t)2 * kRedBlocks + 3));
     }
     int graph_mode = 1;
     { const char *e = getenv("MMB_LM_GRAPH"); if (e) graph_mode = atoi(e); }
-    // sharded: the NCCL all-reduces are captured into the graph bodies like the kernels around them
-    // (every rank builds and launches the same graph); the in-process "local" backend orders its
-    // reduction with host barriers and cannot be captured
+    // sharded: with the peer-memory all-reduce (plain kernels + flag barriers over NVLink) the
+    // collectives are captured into the graph bodies like the kernels around them and the sharded
+    // solve is ONE graph launch too -- every rank builds and launches the same graph.  NCCL's own
+    // kernels cannot sit in a conditional body (cudaGraphInstantiate: invalid argument, measured),
+    // and the in-process "local" backend orders its reduction with host barriers.
     static int sharded_graph = -1;
-    if (sharded_graph < 0) { const char *e = getenv("MMB_LM_GRAPH_SHARDED"); sharded_graph = e ? atoi(e) : 0; }
-    const bool graph_capable = !sharded || (sharded_graph && !strcmp(p->comm->backend(), "nccl"));
+    if (sharded_graph < 0) { const char *e = getenv("MMB_LM_GRAPH_SHARDED"); sharded_graph = e ? atoi(e) : 1; }
+    const bool graph_capable = !sharded || (sharded_graph && peer_graph);
     bool use_graph = graph_mode && graph_capable && !w->profile && !w->graph_failed;
     if (use_graph && !w->graph_exec) {
         const auto tg0 = clk::now();
@@ -1296,6 +1307,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
         MMB_CUDA_CHECK(cudaMemcpyAsync(dist_out, w->dist2, sizeof(double) * hp.nobs, cudaMemcpyDeviceToHost, p->stream));
     if ((st = read_state(p)) != MMB_OK) return st;
     const LmState &f = *w->h_st;
+    if (sharded && p->comm->peer_error()) { set_last_error("peer all-reduce: a barrier timed out (ranks out of step)"); return MMB_ERR_COMM; }
     if (f.cancelled) res->user_interrupted = 1;
     if (use_graph) {
         t_jac = 1e-9 * (double)f.t_jac_ns; t_lin = 1e-9 * (double)f.t_lin_ns; t_func = 1e-9 * (double)f.t_func_ns;
