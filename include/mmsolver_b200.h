@@ -338,7 +338,9 @@ mmb_status mmb_problem_create_shard_local(const mmb_scene_desc *slice,
  * 128 bytes to the other ranks by any channel (torch.distributed, MPI, file) */
 mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES],
                               int32_t local_backend);
-/* collective: every rank of the id calls it.  Afterwards mmb_solve() on the
+/* collective: every rank of the id calls it (NCCL communicator + CUDA IPC mapping
+ * of the ranks' all-reduce arenas, 72 MB of device memory each; MMB_PEER=0 keeps
+ * NCCL alone, MMB_PEER_ARENA_MB sizes the arena).  Afterwards mmb_solve() on the
  * handle is the sharded global solve; results that describe the whole problem
  * (reason, iteration counts, error_final, error_avg/min/max) are identical on
  * every rank, x_out / attr_values_out / error_dist_out cover the shard. */
@@ -475,7 +477,10 @@ int64_t mmb_launch_count(const mmb_problem *p);
  * (lmder -> solveFunc, adjust_cminpack_lmder.cpp:114, adjust_solveFunc.cpp:529).
  * Here an unsharded global solve is one CUDA graph launch (conditional WHILE /
  * IF nodes steered from the device) and one synchronisation to read the result:
- * host_syncs = 1, graph_launches = 1.  A sharded solve is host-driven
+ * host_syncs = 1, graph_launches = 1.  A sharded solve is the same single graph
+ * launch when the communicator's peer-memory all-reduce is on (CUDA IPC arenas over
+ * NVLink: plain kernels, capturable); with NCCL collectives between the kernels
+ * (fallback, or a reduced system beyond the arena) it is host-driven
  * (graph_launches = 0, a few host_syncs per LM iteration). */
 mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs,
                            int64_t *graph_launches);

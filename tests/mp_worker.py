@@ -82,6 +82,23 @@ def gpu_mode():
         rs = solve_global_sharded(sb, g, device=local, comm=comm)
         assert (rs.reason_num, rs.iteration_num) == (r.reason_num, r.iteration_num)
         np.testing.assert_allclose(rs.attr_values, r.attr_values, rtol=1e-7, atol=1e-7)
+    # peer-memory all-reduce (CUDA IPC arenas over NVLink): the sharded solve is ONE graph launch and
+    # one synchronisation, like the unsharded one -- and gives the host-driven loop's answer bit for bit
+    f0, f1 = shard_frames(24, g.world, g.rank)
+    with Problem(sb, device=local, shard=(g.rank, g.world)) as p:
+        p.use_comm(comm)
+        rg = p.solve()
+        stats = p.solve_stats()
+    os.environ["MMB_LM_GRAPH"] = "0"
+    with Problem(sb, device=local, shard=(g.rank, g.world)) as p:
+        p.use_comm(comm)
+        rh = p.solve()
+        stats_h = p.solve_stats()
+    del os.environ["MMB_LM_GRAPH"]
+    if os.environ.get("MMB_PEER", "1") != "0":
+        assert stats == (1, 1), stats
+    assert stats_h[1] == 0 and stats_h[0] > 2
+    assert rg.iteration_num == rh.iteration_num and np.array_equal(rg.x, rh.x) and np.array_equal(rg.error_dist, rh.error_dist)
     comm.close()
     sb2, _ = synth.make_scene(F=30, B=16, seed=22, solve_bundles=False, period=30)
     rp, per = solve_per_frame_sharded(sb2, g, device=local)
