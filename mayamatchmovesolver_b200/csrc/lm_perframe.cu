@@ -322,7 +322,10 @@ __device__ void pf_jtj(const DevScene &s, const PfArgs &a, PfShared &sh, int q0,
     }
 }
 
-__global__ void __launch_bounds__(kPfThreads) k_perframe_lm(DevScene s, PfArgs a, int frame0) {
+// MINB = 1: no register cap (255 registers, four frames per SM in flight); MINB = 8: 128 registers,
+// eight frames per SM -- a frame's solve is a latency chain, so frames in flight are throughput
+template <int MINB>
+__global__ void __launch_bounds__(kPfThreads, MINB) k_perframe_lm(DevScene s, PfArgs a, int frame0) {
     __shared__ PfShared sh;
     extern __shared__ double pf_dyn[];
     const int f = frame0 + blockIdx.x;
@@ -577,8 +580,17 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     // static entities never depend on solved attributes here: evaluate their base once
     if ((st = launch_variants(p, nullptr, false)) != MMB_OK) return st;
     const size_t dyn = 2 * sizeof(double) * (size_t)hp.na * hp.na;
-    MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-    k_perframe_lm<<<hp.F, kPfThreads, dyn, p->stream>>>(p->ds, a, 0);
+    static int pf_minb = -1;
+    if (pf_minb < 0) { const char *e = getenv("MMB_PF_MINB"); pf_minb = e ? atoi(e) : 1; }
+    // few frames (less than one wave of the capped instance): the uncapped instance is faster per frame
+    const bool dense = pf_minb >= 8 && hp.F > 148 * 4;
+    if (dense) {
+        MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        k_perframe_lm<8><<<hp.F, kPfThreads, dyn, p->stream>>>(p->ds, a, 0);
+    } else {
+        MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+        k_perframe_lm<1><<<hp.F, kPfThreads, dyn, p->stream>>>(p->ds, a, 0);
+    }
     ++p->launches;
     MMB_CUDA_CHECK(cudaGetLastError());
     std::vector<PfFrameResult> fr(hp.F);
