@@ -882,7 +882,9 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(tiles, ksplit);
         cfg.blockDim = dim3(128);
-        cfg.dynamicSmemBytes = 0;
+        static int syrk_pad = -1;   // experiment: cap the SYRK's residency with unused dynamic shared memory
+        if (syrk_pad < 0) { const char *e = getenv("MMB_SYRK_PAD_KB"); syrk_pad = e ? atoi(e) : 0; if (syrk_pad) cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_pad * 1024); }
+        cfg.dynamicSmemBytes = (size_t)syrk_pad * 1024;
         cfg.stream = s;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -906,7 +908,9 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
     }
     if (prof) cudaEventRecord(w->ev[1], s);
     if (w->chol_tiles) {
-        if (nb > 64)
+        static int chol_minb = -1;
+        if (chol_minb < 0) { const char *e = getenv("MMB_CHOL_MINB"); chol_minb = e ? atoi(e) : 0; }
+        if (nb > 64 || chol_minb == 2)
             k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
         else
             k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);

@@ -581,7 +581,7 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     if ((st = launch_variants(p, nullptr, false)) != MMB_OK) return st;
     const size_t dyn = 2 * sizeof(double) * (size_t)hp.na * hp.na;
     static int pf_minb = -1;
-    if (pf_minb < 0) { const char *e = getenv("MMB_PF_MINB"); pf_minb = e ? atoi(e) : 1; }
+    if (pf_minb < 0) { const char *e = getenv("MMB_PF_MINB"); pf_minb = e ? atoi(e) : 8; }
     // few frames (less than one wave of the capped instance): the uncapped instance is faster per frame
     const bool dense = pf_minb >= 8 && hp.F > 148 * 4;
     if (dense) {
