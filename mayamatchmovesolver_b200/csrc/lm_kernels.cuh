@@ -131,15 +131,20 @@ __global__ void __launch_bounds__(256) k_colmax(DevScene s, LmDims d, const doub
             unsigned long long b = (unsigned long long)__double_as_longlong(v);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, b, o); b = t > b ? t : b; }
-            if (lane == 0 && b) atomicMax(&cmax[s.attr_param_base[a]], b);
+            // most warps find a larger maximum already there: read first (a stale read only costs an
+            // atomic that changes nothing), so the few shared addresses are not hammered by every warp
+            unsigned long long *dst = &cmax[s.attr_param_base[a]];
+            if (lane == 0 && b > *reinterpret_cast<volatile unsigned long long *>(dst)) atomicMax(dst, b);
         } else if (live && v != 0.0) {
-            atomicMax(&cmax[s.attr_param_base[a] + (an ? frame : 0)], (unsigned long long)__double_as_longlong(v));
+            unsigned long long *dst = &cmax[s.attr_param_base[a] + (an ? frame : 0)];
+            const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+            if (b > *reinterpret_cast<volatile unsigned long long *>(dst)) atomicMax(dst, b);
         }
     }
     unsigned long long fb = (unsigned long long)__double_as_longlong(fa);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { const unsigned long long t = __shfl_xor_sync(0xffffffffu, fb, o); fb = t > fb ? t : fb; }
-    if (lane == 0 && fb) atomicMax(&cmax[d.n], fb);
+    if (lane == 0 && fb > *reinterpret_cast<volatile unsigned long long *>(&cmax[d.n])) atomicMax(&cmax[d.n], fb);
 }
 
 __global__ void __launch_bounds__(256) k_assemble(DevScene s, LmDims d, const double *__restrict__ jac,
