@@ -516,6 +516,11 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
         set_last_error("more than 64 animated solver attributes per frame are not supported");
         return MMB_ERR_UNSUPPORTED;
     }
+    if ((long long)hp.nobs >= (1ll << 27)) {
+        // the fixed-point limbs of the normal equations hold sums of up to 2^27 contributions
+        set_last_error("more than 2^27 observations per GPU: shard the frames over more ranks");
+        return MMB_ERR_UNSUPPORTED;
+    }
     LmWorkspace *w = new LmWorkspace();
     LmDims &d = w->d;
     d.F = hp.F; d.na = hp.na; d.ns = hp.ns; d.NS1 = hp.ns + 1;
