@@ -584,9 +584,12 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     if (pf_minb < 0) { const char *e = getenv("MMB_PF_MINB"); pf_minb = e ? atoi(e) : 8; }
     // few frames (less than one wave of the capped instance): the uncapped instance is faster per frame
     const bool dense = pf_minb >= 8 && hp.F > 148 * 4;
+    static int pf_threads = -1;   // threads per frame (a multiple of 32, <= kPfThreads)
+    if (pf_threads < 0) { const char *e = getenv("MMB_PF_THREADS"); pf_threads = e ? atoi(e) : 0; }
+    const int threads = (dense && (pf_threads == 32 || pf_threads == 64)) ? pf_threads : kPfThreads;
     if (dense) {
         MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-        k_perframe_lm<8><<<hp.F, kPfThreads, dyn, p->stream>>>(p->ds, a, 0);
+        k_perframe_lm<8><<<hp.F, threads, dyn, p->stream>>>(p->ds, a, 0);
     } else {
         MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
         k_perframe_lm<1><<<hp.F, kPfThreads, dyn, p->stream>>>(p->ds, a, 0);
