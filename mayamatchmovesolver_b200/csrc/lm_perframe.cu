@@ -322,8 +322,10 @@ __device__ void pf_jtj(const DevScene &s, const PfArgs &a, PfShared &sh, int q0,
     }
 }
 
-// MINB = 1: no register cap (255 registers, four frames per SM in flight); MINB = 8: 128 registers,
-// eight frames per SM -- a frame's solve is a latency chain, so frames in flight are throughput
+// MINB = 1: no register cap (255 registers, 64 threads: four frames per SM in flight), for batches
+// below one wave; MINB = 8: 128 registers, launched with 32 threads per frame: sixteen frames per
+// SM -- a frame's solve is a latency chain, so frames in flight are throughput (24 000 frames:
+// 33.1 ms uncapped, 30.0 ms capped at 64 threads, 26.9 ms capped at 32 threads)
 template <int MINB>
 __global__ void __launch_bounds__(kPfThreads, MINB) k_perframe_lm(DevScene s, PfArgs a, int frame0) {
     __shared__ PfShared sh;
@@ -585,7 +587,7 @@ mmb_status lm_solve_per_frame(DeviceProblem *p, mmb_result *res, double *x_out, 
     // few frames (less than one wave of the capped instance): the uncapped instance is faster per frame
     const bool dense = pf_minb >= 8 && hp.F > 148 * 4;
     static int pf_threads = -1;   // threads per frame (a multiple of 32, <= kPfThreads)
-    if (pf_threads < 0) { const char *e = getenv("MMB_PF_THREADS"); pf_threads = e ? atoi(e) : 0; }
+    if (pf_threads < 0) { const char *e = getenv("MMB_PF_THREADS"); pf_threads = e ? atoi(e) : 32; }
     const int threads = (dense && (pf_threads == 32 || pf_threads == 64)) ? pf_threads : kPfThreads;
     if (dense) {
         MMB_CUDA_CHECK(cudaFuncSetAttribute(k_perframe_lm<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
