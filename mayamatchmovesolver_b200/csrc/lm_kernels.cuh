@@ -764,22 +764,15 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     const int v0 = (int)rank * per_rank;
     const unsigned base = (unsigned)__cvta_generic_to_shared(smem);
     const int g = lane >> 2, q = lane & 3;
-    // all 32 remote loads of this thread are issued before the first sum (a DSMEM load comes back
-    // after ~200 cycles: a dependent chain of 32 would cost as much as a quarter of the main loop)
-    double part[32];
-#pragma unroll
-    for (int u = 0; u < 32; ++u) {
-        const int v = v0 + u / (int)8 * 0 + (u % per_rank), r = u / per_rank;   // u = r * per_rank + (v - v0)
-        unsigned remote;
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + (unsigned)((v * 128 + threadIdx.x) * 8)), "r"((unsigned)r));
-        asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(part[u]) : "r"(remote));
-    }
-#pragma unroll
-    for (int w = 0; w < 16; ++w) {
-        if (w >= per_rank) break;
+    for (int v = v0; v < v0 + per_rank; ++v) {
         double sum = 0.0;
-        for (int r = 0; r < (int)nrank; ++r) sum += part[r * per_rank + w];   // rank order
-        const int v = v0 + w;
+        for (unsigned r = 0; r < nrank; ++r) {
+            unsigned remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + (unsigned)((v * 128 + threadIdx.x) * 8)), "r"(r));
+            double x;
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(x) : "r"(remote));
+            sum += x;
+        }
         const int ti = v >> 3, tj = (v >> 1) & 3, h = v & 1;
         const int row = bi * 64 + wr * 32 + ti * 8 + g, col = bj * 64 + wc * 32 + tj * 8 + q * 2 + h;
         S[(size_t)row * d.NSP + col] -= sum;
