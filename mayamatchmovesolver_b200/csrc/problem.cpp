@@ -322,7 +322,11 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         // count the enabled observations per range, then fill at the prefix offsets.  The
         // order (marker-major, frame-minor) is the reference's.
         const size_t M = (size_t)hp.M;
-        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        // host threads of the scan: the cores of the box divided among the ranks that share it (one
+        // process per GPU: LOCAL_WORLD_SIZE as torchrun / mpirun export it), MMB_HOST_THREADS overrides
+        unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        if (const char *e = getenv("MMB_HOST_THREADS")) hw = (unsigned)std::max(1, atoi(e));
+        else if (const char *lw = getenv("LOCAL_WORLD_SIZE")) hw = std::max(1u, hw / (unsigned)std::max(1, atoi(lw)));
         const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)8, (M * F) / 65536 + 1}));
         std::vector<size_t> count(T + 1, 0);
         std::vector<std::vector<double>> twmax(T, std::vector<double>(F, 0.0));
