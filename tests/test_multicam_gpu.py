@@ -190,3 +190,47 @@ def test_multicam_rows_kernel_matches_oracle(C, F, B, monkeypatch):
     assert (r.reason_num, r.iteration_num, r.iteration_attempt_num) == (r2.reason_num, r2.iteration_num, r2.iteration_attempt_num)
     assert np.max(np.abs(r.attr_values - r2.attr_values) / np.maximum(np.abs(r2.attr_values), 1.0)) <= 1e-6
     assert np.max(np.abs(r.error_dist - r2.error_dist)) <= 1e-6
+
+
+def test_cfg5_shard_scale_matches_oracle_on_sampled_frames():
+    """A cfg5-shaped shard at a size where the per-camera rows launches have many CTAs per frame block
+    (8 cameras x 320 frames x 2000 bundles = 5.1e6 observations): residuals, distances and Jacobian
+    columns of sampled frames against the oracle evaluating just those frames (same static values;
+    a frame's rows only depend on that frame's camera attributes and the bundles)."""
+    C, F, B = 8, 320, 2000
+    sb, _ = synth.make_multicam_scene(C, F, B, 6)
+    sample = [0, 31, 32, 159, 288, 319]
+    sub = sb.slice_frames(sample)
+    o = OracleProblem(sub)
+    Fs = len(sample)
+    with Problem(sb) as p:
+        assert p.nobs == C * F * B
+        x = p.initial_parameters()
+        f, d = p.eval_residuals(x)
+        vals = p.eval_jacobian_blocks(x, want_cols=False)      # the rows kernel, once per camera
+    xo = o.initial_parameters()
+    fo, do = o.eval_residuals(xo)
+    M = C * B
+    big = (np.arange(M)[:, None] * F + np.asarray(sample)[None, :]).reshape(-1)     # observation ids in the shard
+    small = (np.arange(M)[:, None] * Fs + np.arange(Fs)[None, :]).reshape(-1)
+    fb = f.reshape(-1, 2)[big]
+    fs = fo.reshape(-1, 2)[small]
+    assert np.abs(fb - fs).max() <= 1e-9 * np.abs(fs).max()
+    assert np.abs(d[big] - do[small]).max() <= 1e-9 * np.abs(do).max()
+    # Jacobian columns by forward differences of the oracle's residuals: camera 5's ry at the third
+    # sampled frame (block column 4 of that camera's markers), bundle 1234's tz (block column 8)
+    delta = 1e-4
+    scale = np.abs(vals).max()
+    n_cam = 6 * C * Fs
+    for pid, col, rows_sel in (
+            ((6 * 5 + 4) * Fs + 2, 4, [(5 * B + b) for b in range(B)]),
+            (n_cam + 3 * 1234 + 2, 8, [(c * B + 1234) for c in range(C)])):
+        xa = xo.copy(); xa[pid] += delta
+        fa, _ = o.eval_residuals(xa)
+        ref = ((fa - fo) / delta).reshape(-1, 2)
+        for mk in rows_sel:
+            ks = [2] if col == 4 else range(Fs)
+            for k in ks:
+                i_big, i_small = mk * F + sample[k], mk * Fs + k
+                got = vals[col].reshape(-1, 2)[i_big]
+                assert np.abs(got - ref[i_small]).max() <= 1e-9 * scale, (pid, mk, k, got, ref[i_small])
