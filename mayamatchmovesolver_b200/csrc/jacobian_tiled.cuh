@@ -390,6 +390,86 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         }
         __syncthreads();
     }
+    if (SPARSE) {
+        // ---- sparse visibility: compacted lanes ------------------------------------------------
+        // With lane = frame a marker seen on one frame in four leaves three lanes in four idle.
+        // Here a warp takes KB markers at a time and deals their live (marker, frame) pairs to its
+        // lanes: pair t of the batch is the r-th set bit of marker u's frame mask (__fns).  The
+        // camera rows of the lane's frame come from the staged block by frame index, the bundle
+        // record by marker; the observation index is obs_base + r, so the lanes of one marker
+        // still store to consecutive addresses.
+        constexpr int KB = 4;
+        const double imw_s = s.image_width;
+        const int VBs = VBT ? VBT : tp.VB, VCs = VCT ? VCT : tp.VC;
+        const int32_t *const ob_ = tp.obs_base + (size_t)blockIdx.x * s.M;
+        const uint32_t *const om_ = tp.obs_mask + (size_t)blockIdx.x * s.M;
+        double2 *const jac2s = reinterpret_cast<double2 *>(jac);
+        mbar_wait(&bars[0], 0);
+        mbar_wait(bar_mk, 0);
+        for (int v = 1; v < nv; ++v) mbar_wait(&bars[v], 0);
+        for (int j0 = w * KB; j0 < mcount; j0 += W * KB) {
+            uint32_t km[KB];
+            int cnt[KB], total = 0;
+#pragma unroll
+            for (int u = 0; u < KB; ++u) {
+                km[u] = (j0 + u < mcount) ? om_[m0 + j0 + u] : 0u;
+                cnt[u] = __popc(km[u]);
+                total += cnt[u];
+            }
+            for (int t = lane; t < total; t += 32) {
+                int u = 0, r = t;
+#pragma unroll
+                for (int z = 0; z < KB - 1; ++z)
+                    if (u == z && r >= cnt[z]) { r -= cnt[z]; u = z + 1; }
+                uint32_t kmu = km[0];
+#pragma unroll
+                for (int z = 1; z < KB; ++z) if (u == z) kmu = km[z];
+                const int fl = __fns(kmu, 0, r + 1);          // the frame (lane of the block) of this pair
+                const int j = j0 + u;
+                const size_t i = (size_t)ob_[m0 + j] + r;
+                double cmb[14];
+#pragma unroll
+                for (int jp = 0; jp < 7; ++jp) { const double2 q2 = scam[jp * kRowFrames + fl]; cmb[2 * jp] = q2.x; cmb[2 * jp + 1] = q2.y; }
+                const double *bq = sbnd + (size_t)j * nrec;
+                const double *kq = smk + (size_t)j * 3 * kRowFrames + fl;
+                const double mkx = kq[0] * cmb[12], mky = kq[kRowFrames] * cmb[13], wq = sqrt(kq[2 * kRowFrames]);
+                const double px = bq[0], py = bq[1], pz = bq[2];
+                double dx, dy;
+                eval_pair_fma(cmb, px, py, pz, mkx, mky, dx, dy);
+                const double c0 = imw_s * wq;
+                if (fvec) reinterpret_cast<double2 *>(fvec)[i] = make_double2(dx * c0, dy * c0);
+                if (dist || DIST_LAST) {
+                    const double d0 = sqrt((dx * dx) + (dy * dy)) * imw_s;
+                    if (dist) dist[i] = d0;
+                    if (DIST_LAST) dist_last[i] = d0;
+                }
+                double2 *const jp = jac2s + i;
+#pragma unroll(VBT ? VBT : 1)
+                for (int v = 0; v < VBs; ++v) {
+                    const double *qv = bq + (v + 1) * kBndRec;
+                    double ax, ay;
+                    eval_pair_fma(cmb, qv[0], qv[1], qv[2], mkx, mky, ax, ay);
+                    const double g0 = c0 * qv[3];
+                    jp[tp.bnd_coloff_u[v]] = make_double2((ax - dx) * g0, (ay - dy) * g0);
+                    if (DIST_LAST && tp.mkr_bnd_attr[(size_t)(m0 + j) * VBs + v] == s.A - 1) dist_last[i] = sqrt((ax * ax) + (ay * ay)) * imw_s;
+                }
+                const double2 *sv = scam + (size_t)kRowPairs * kRowFrames + fl;
+#pragma unroll(VCT ? VCT : 1)
+                for (int v = 0; v < VCs; ++v, sv += kRowPairs * kRowFrames) {
+                    double cv[12];
+#pragma unroll
+                    for (int jq = 0; jq < 6; ++jq) { const double2 q2 = sv[jq * kRowFrames]; cv[2 * jq] = q2.x; cv[2 * jq + 1] = q2.y; }
+                    const double inv_delta = sv[7 * kRowFrames].x;
+                    double ax, ay;
+                    eval_pair_fma(cv, px, py, pz, mkx, mky, ax, ay);
+                    const double g0 = c0 * inv_delta;
+                    jp[tp.cam_coloff_u[v]] = make_double2((ax - dx) * g0, (ay - dy) * g0);
+                    if (DIST_LAST && tp.last_attr_cam_var == v) dist_last[i] = sqrt((ax * ax) + (ay * ay)) * imw_s;
+                }
+            }
+        }
+        return;
+    }
     if (f >= F) return;
     const double imw = s.image_width;
     mbar_wait(&bars[0], 0);
