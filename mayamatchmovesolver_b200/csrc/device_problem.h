@@ -85,6 +85,7 @@ struct DeviceProblem {
     TiledPlan tiled{};
     // several cameras (cfg5 shape): the rows kernel once per camera over that camera's markers
     std::vector<TiledPlan> cam_plans;
+    const CamSlice *d_cam_slices = nullptr;   // the per-camera part of cam_plans, on the device (blockIdx.z of the one launch)
     int rows_mt[2] = {0, 0};    // markers per CTA of k_jacobian_rows (0 = not configured yet)
     LmWorkspace *lm = nullptr;
     Comm *comm = nullptr;       // set by mmb_problem_attach_comm / use_comm: mmb_solve is then the sharded global solve

@@ -48,6 +48,13 @@ struct TiledPlan {
     const uint32_t *obs_mask;    // [frame blocks][M]
 };
 
+// Several cameras in one launch of k_jacobian_rows: blockIdx.z picks the camera, whose part of
+// the plan (the fields that differ between cameras) comes from this record.
+struct CamSlice {
+    int cam, m_base, m_count, bnd_contig, last_attr_cam_var;
+    long long bnd_rec0;
+};
+
 #ifdef __CUDACC__
 // 1/x to (nearly) full precision without the slow-path branch of the IEEE
 // division: hardware seed (20 bits) + two Newton steps.
@@ -342,19 +349,28 @@ constexpr int kRowPairs = kCamRec / 2;  // 16-byte row pairs per camera variant
 template <int W, int MINB, bool DIST_LAST, int VCT = 0, int VBT = 0, bool SPARSE = false>
 __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, TiledPlan tp, int mt,
                                                                 double *__restrict__ fvec, double *__restrict__ dist,
-                                                                double *__restrict__ jac, double *__restrict__ dist_last) {
+                                                                double *__restrict__ jac, double *__restrict__ dist_last,
+                                                                const CamSlice *__restrict__ slices) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int nv = tp.VC + 1;
     const int nrec = (tp.VB + 1) * kBndRec;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem_raw);                        // [nv + 1]
     double2 *scam = reinterpret_cast<double2 *>(smem_raw + 256);                    // [nv][8 row pairs][32 frames]
     double *smk = reinterpret_cast<double *>(scam + (size_t)nv * kRowPairs * kRowFrames);  // [mt][3][32] marker x, y, weight
-    double *sbnd = smk + (size_t)mt * 3 * kRowFrames;                               // [mt][VB+1][4]
+    double *sbnd = SPARSE ? smk : smk + (size_t)mt * 3 * kRowFrames;                // [mt][VB+1][4]  (sparse: no marker block)
+    int cam_ = tp.cam, m_base_ = tp.m_base, m_count_ = tp.m_count, bnd_contig_ = tp.bnd_contig, last_cam_var_ = tp.last_attr_cam_var;
+    long long bnd_rec0_ = tp.bnd_rec0;
+    if (slices) {
+        const CamSlice cs = slices[blockIdx.z];
+        cam_ = cs.cam; m_base_ = cs.m_base; m_count_ = cs.m_count; bnd_contig_ = cs.bnd_contig; last_cam_var_ = cs.last_attr_cam_var;
+        bnd_rec0_ = cs.bnd_rec0;
+        if ((int)blockIdx.y * mt >= m_count_) return;   // the grid is sized for the camera with the most markers
+    }
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int f0 = blockIdx.x * kRowFrames, f = f0 + lane;
     const int F = s.F;
-    const int m0 = tp.m_base + blockIdx.y * mt;
-    const int mcount = min(mt, tp.m_base + tp.m_count - m0);
+    const int m0 = m_base_ + blockIdx.y * mt;
+    const int mcount = min(mt, m_base_ + m_count_ - m0);
     uint64_t *bar_mk = &bars[nv];
     if (threadIdx.x == 0) {
         for (int v = 0; v <= nv; ++v) mbar_init(&bars[v], 1);
@@ -366,23 +382,25 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     if (threadIdx.x == 0) {
         const uint32_t var_bytes = (uint32_t)(kRowPairs * kRowFrames * sizeof(double2));
         const uint32_t mk_bytes = (uint32_t)mcount * 3u * kRowFrames * 8u;
-        const uint32_t bnd_bytes = tp.bnd_contig ? (uint32_t)(mcount * nrec) * 8u : 0u;
-        const double2 *ctab = reinterpret_cast<const double2 *>(s.cam_tab + s.cam_off[tp.cam]) +
+        const uint32_t bnd_bytes = bnd_contig_ ? (uint32_t)(mcount * nrec) * 8u : 0u;
+        const double2 *ctab = reinterpret_cast<const double2 *>(s.cam_tab + s.cam_off[cam_]) +
                               (size_t)blockIdx.x * nv * kRowPairs * kRowFrames;
         // the marker tracks are problem constants: fetch them (HBM latency) before waiting on
         // the variants kernel this launch may overlap with (programmatic dependent launch)
-        mbar_expect_tx(bar_mk, mk_bytes);
-        bulk_g2s(smk, tp.mk_blk + ((size_t)blockIdx.x * s.M + m0) * 3 * kRowFrames, mk_bytes, bar_mk);
+        if (!SPARSE) {
+            mbar_expect_tx(bar_mk, mk_bytes);
+            bulk_g2s(smk, tp.mk_blk + ((size_t)blockIdx.x * s.M + m0) * 3 * kRowFrames, mk_bytes, bar_mk);
+        }
         asm volatile("griddepcontrol.wait;" ::: "memory");
         mbar_expect_tx(&bars[0], var_bytes + bnd_bytes);
         bulk_g2s(scam, ctab, var_bytes, &bars[0]);
-        if (tp.bnd_contig) bulk_g2s(sbnd, s.bnd_tab + tp.bnd_rec0 + (size_t)(m0 - tp.m_base) * nrec, bnd_bytes, &bars[0]);
+        if (bnd_contig_) bulk_g2s(sbnd, s.bnd_tab + bnd_rec0_ + (size_t)(m0 - m_base_) * nrec, bnd_bytes, &bars[0]);
         for (int v = 1; v < nv; ++v) {
             mbar_expect_tx(&bars[v], var_bytes);
             bulk_g2s(scam + (size_t)v * kRowPairs * kRowFrames, ctab + (size_t)v * kRowPairs * kRowFrames, var_bytes, &bars[v]);
         }
     }
-    if (!tp.bnd_contig) {
+    if (!bnd_contig_) {
         asm volatile("griddepcontrol.wait;" ::: "memory");
         for (int t = threadIdx.x; t < mcount * nrec; t += 32 * W) {
             const int j = t / nrec, r = t - j * nrec;
@@ -398,42 +416,61 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         // camera rows of the lane's frame come from the staged block by frame index, the bundle
         // record by marker; the observation index is obs_base + r, so the lanes of one marker
         // still store to consecutive addresses.
-        constexpr int KB = 4;
+        constexpr int KB = 16;
         const double imw_s = s.image_width;
         const int VBs = VBT ? VBT : tp.VB, VCs = VCT ? VCT : tp.VC;
         const int32_t *const ob_ = tp.obs_base + (size_t)blockIdx.x * s.M;
         const uint32_t *const om_ = tp.obs_mask + (size_t)blockIdx.x * s.M;
         double2 *const jac2s = reinterpret_cast<double2 *>(jac);
         mbar_wait(&bars[0], 0);
-        mbar_wait(bar_mk, 0);
         for (int v = 1; v < nv; ++v) mbar_wait(&bars[v], 0);
+        // The lanes of a pass want different frames: 16-byte reads of [row pair][frame] collide
+        // (frames 8 apart share their banks).  Re-lay every row pair in place as four rows of
+        // 32-bit words, [word][frame]: bank = frame, so any set of frames reads without conflict
+        // and equal frames broadcast.
+        uint32_t *const swd = reinterpret_cast<uint32_t *>(scam);
+        for (int rp = w; rp < nv * kRowPairs; rp += W) {
+            const double2 q2 = scam[rp * kRowFrames + lane];
+            __syncwarp();
+            uint32_t *o = swd + (size_t)rp * 4 * kRowFrames + lane;
+            o[0] = (uint32_t)__double2loint(q2.x); o[kRowFrames] = (uint32_t)__double2hiint(q2.x);
+            o[2 * kRowFrames] = (uint32_t)__double2loint(q2.y); o[3 * kRowFrames] = (uint32_t)__double2hiint(q2.y);
+        }
+        __syncthreads();
+        auto ldw = [&](const uint32_t *q) { return __hiloint2double((int)q[kRowFrames], (int)q[0]); };
         for (int j0 = w * KB; j0 < mcount; j0 += W * KB) {
-            uint32_t km[KB];
-            int cnt[KB], total = 0;
+            // lane u (and u + 16) holds marker j0 + u: its frame mask, first observation, and the
+            // number of live pairs of the markers before it in the batch
+            const int ju = j0 + (lane & (KB - 1));
+            const uint32_t km_l = ju < mcount ? om_[m0 + ju] : 0u;
+            const int ob_l = ju < mcount ? ob_[m0 + ju] : 0;
+            int incl = __popc(km_l);
 #pragma unroll
-            for (int u = 0; u < KB; ++u) {
-                km[u] = (j0 + u < mcount) ? om_[m0 + j0 + u] : 0u;
-                cnt[u] = __popc(km[u]);
-                total += cnt[u];
-            }
-            for (int t = lane; t < total; t += 32) {
-                int u = 0, r = t;
+            for (int d = 1; d < KB; d <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, d, KB); if ((lane & (KB - 1)) >= d) incl += y; }
+            const int total = __shfl_sync(0xffffffffu, incl, KB - 1);
+            const int excl = incl - __popc(km_l);
+            for (int tb = 0; tb < total; tb += 32) {
+                const int t = tb + lane;
+                int u = 0;    // the last marker whose pairs start at or before t (it has pairs: the next one starts after t)
 #pragma unroll
-                for (int z = 0; z < KB - 1; ++z)
-                    if (u == z && r >= cnt[z]) { r -= cnt[z]; u = z + 1; }
-                uint32_t kmu = km[0];
-#pragma unroll
-                for (int z = 1; z < KB; ++z) if (u == z) kmu = km[z];
+                for (int st = KB / 2; st > 0; st >>= 1) { const int e = __shfl_sync(0xffffffffu, excl, u + st); if (e <= t) u += st; }
+                const uint32_t kmu = __shfl_sync(0xffffffffu, km_l, u);
+                const int r = t - __shfl_sync(0xffffffffu, excl, u);
+                const int obu = __shfl_sync(0xffffffffu, ob_l, u);
+                if (t >= total) continue;
                 const int fl = __fns(kmu, 0, r + 1);          // the frame (lane of the block) of this pair
                 const int j = j0 + u;
-                const size_t i = (size_t)ob_[m0 + j] + r;
+                const size_t i = (size_t)obu + r;
+                const uint32_t *cw = swd + fl;
                 double cmb[14];
 #pragma unroll
-                for (int jp = 0; jp < 7; ++jp) { const double2 q2 = scam[jp * kRowFrames + fl]; cmb[2 * jp] = q2.x; cmb[2 * jp + 1] = q2.y; }
-                const double *bq = sbnd + (size_t)j * nrec;
-                const double *kq = smk + (size_t)j * 3 * kRowFrames + fl;
-                const double mkx = kq[0] * cmb[12], mky = kq[kRowFrames] * cmb[13], wq = sqrt(kq[2 * kRowFrames]);
-                const double px = bq[0], py = bq[1], pz = bq[2];
+                for (int q = 0; q < 14; ++q) cmb[q] = ldw(cw + 2 * q * kRowFrames);
+                const double2 *bq = reinterpret_cast<const double2 *>(sbnd + (size_t)j * nrec);
+                // the marker track straight from the observation arrays (consecutive lanes, consecutive
+                // observations): a frame-blocked copy would be read for every slot, live or not
+                const double mkx = __ldg(s.obs_mx + i) * cmb[12], mky = __ldg(s.obs_my + i) * cmb[13], wq = sqrt(__ldg(s.obs_w + i));
+                const double2 b01 = bq[0], b23 = bq[1];
+                const double px = b01.x, py = b01.y, pz = b23.x;
                 double dx, dy;
                 eval_pair_fma(cmb, px, py, pz, mkx, mky, dx, dy);
                 const double c0 = imw_s * wq;
@@ -446,25 +483,25 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
                 double2 *const jp = jac2s + i;
 #pragma unroll(VBT ? VBT : 1)
                 for (int v = 0; v < VBs; ++v) {
-                    const double *qv = bq + (v + 1) * kBndRec;
+                    const double2 q01 = bq[2 * (v + 1)], q23 = bq[2 * (v + 1) + 1];
                     double ax, ay;
-                    eval_pair_fma(cmb, qv[0], qv[1], qv[2], mkx, mky, ax, ay);
-                    const double g0 = c0 * qv[3];
+                    eval_pair_fma(cmb, q01.x, q01.y, q23.x, mkx, mky, ax, ay);
+                    const double g0 = c0 * q23.y;
                     jp[tp.bnd_coloff_u[v]] = make_double2((ax - dx) * g0, (ay - dy) * g0);
                     if (DIST_LAST && tp.mkr_bnd_attr[(size_t)(m0 + j) * VBs + v] == s.A - 1) dist_last[i] = sqrt((ax * ax) + (ay * ay)) * imw_s;
                 }
-                const double2 *sv = scam + (size_t)kRowPairs * kRowFrames + fl;
+                const uint32_t *sv = cw + (size_t)kRowPairs * 4 * kRowFrames;
 #pragma unroll(VCT ? VCT : 1)
-                for (int v = 0; v < VCs; ++v, sv += kRowPairs * kRowFrames) {
+                for (int v = 0; v < VCs; ++v, sv += kRowPairs * 4 * kRowFrames) {
                     double cv[12];
 #pragma unroll
-                    for (int jq = 0; jq < 6; ++jq) { const double2 q2 = sv[jq * kRowFrames]; cv[2 * jq] = q2.x; cv[2 * jq + 1] = q2.y; }
-                    const double inv_delta = sv[7 * kRowFrames].x;
+                    for (int q = 0; q < 12; ++q) cv[q] = ldw(sv + 2 * q * kRowFrames);
+                    const double inv_delta = ldw(sv + 2 * 14 * kRowFrames);
                     double ax, ay;
                     eval_pair_fma(cv, px, py, pz, mkx, mky, ax, ay);
                     const double g0 = c0 * inv_delta;
                     jp[tp.cam_coloff_u[v]] = make_double2((ax - dx) * g0, (ay - dy) * g0);
-                    if (DIST_LAST && tp.last_attr_cam_var == v) dist_last[i] = sqrt((ax * ax) + (ay * ay)) * imw_s;
+                    if (DIST_LAST && last_cam_var_ == v) dist_last[i] = sqrt((ax * ax) + (ay * ay)) * imw_s;
                 }
             }
         }
@@ -480,25 +517,11 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
     bool variants_ready = false;
     double2 *const jac2 = reinterpret_cast<double2 *>(jac);
     const int VB = VBT ? VBT : tp.VB, VC = VCT ? VCT : tp.VC;
-    const int32_t *const obase = SPARSE ? tp.obs_base + (size_t)blockIdx.x * s.M : nullptr;
-    const uint32_t *const omask = SPARSE ? tp.obs_mask + (size_t)blockIdx.x * s.M : nullptr;
-    const uint32_t below = (1u << lane) - 1u;
     for (int jj = 2 * w; jj < mcount; jj += 2 * W) {
         // an odd marker count evaluates its last marker twice (same values to the same addresses)
         const int j1 = min(jj + 1, mcount - 1);
-        // i0, i1: the two observations of this lane's frame; on0 / on1: they exist
-        size_t i0, i1;
-        bool on0 = true, on1 = true;
-        if (SPARSE) {
-            const uint32_t k0m = omask[m0 + jj], k1m = omask[m0 + j1];
-            on0 = (k0m >> lane) & 1u; on1 = (k1m >> lane) & 1u;
-            if ((k0m | k1m) == 0u) continue;   // neither track lives in this frame block
-            i0 = (size_t)obase[m0 + jj] + __popc(k0m & below);
-            i1 = (size_t)obase[m0 + j1] + __popc(k1m & below);
-        } else {
-            i0 = (size_t)(m0 + jj) * F + f;
-            i1 = (size_t)(m0 + j1) * F + f;
-        }
+        // i0, i1: the two observations of this lane's frame (dense grid)
+        const size_t i0 = (size_t)(m0 + jj) * F + f, i1 = (size_t)(m0 + j1) * F + f;
         const double *b0 = sbnd + (size_t)jj * nrec;
         const double *b1 = sbnd + (size_t)j1 * nrec;
         const double *k0 = smk + (size_t)jj * 3 * kRowFrames + lane, *k1 = smk + (size_t)j1 * 3 * kRowFrames + lane;
@@ -513,13 +536,13 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
         const double c0 = imw * w0, c1 = imw * w1;
         if (fvec) {
             double2 *fv = reinterpret_cast<double2 *>(fvec);
-            if (on0) fv[i0] = make_double2(dx0 * c0, dy0 * c0);
-            if (on1) fv[i1] = make_double2(dx1 * c1, dy1 * c1);
+            fv[i0] = make_double2(dx0 * c0, dy0 * c0);
+            fv[i1] = make_double2(dx1 * c1, dy1 * c1);
         }
         if (dist || DIST_LAST) {
             const double d0 = sqrt((dx0 * dx0) + (dy0 * dy0)) * imw, d1 = sqrt((dx1 * dx1) + (dy1 * dy1)) * imw;
-            if (dist) { if (on0) dist[i0] = d0; if (on1) dist[i1] = d1; }
-            if (DIST_LAST) { if (on0) dist_last[i0] = d0; if (on1) dist_last[i1] = d1; }
+            if (dist) { dist[i0] = d0; dist[i1] = d1; }
+            if (DIST_LAST) { dist_last[i0] = d0; dist_last[i1] = d1; }
         }
         double2 *const jp0 = jac2 + i0, *const jp1 = jac2 + i1;
         // bundle columns: base camera rows, perturbed bundle
@@ -531,11 +554,11 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             eval_pair_fma(cm, q1[0], q1[1], q1[2], mkx1, mky1, bx, by);
             const long long co = tp.bnd_coloff_u[v];
             const double g0 = c0 * q0[3], g1 = c1 * q1[3];
-            if (on0) jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            if (on1) jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
             if (DIST_LAST) {
-                if (on0 && tp.mkr_bnd_attr[(size_t)(m0 + jj) * VB + v] == s.A - 1) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
-                if (on1 && tp.mkr_bnd_attr[(size_t)(m0 + j1) * VB + v] == s.A - 1) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
+                if (tp.mkr_bnd_attr[(size_t)(m0 + jj) * VB + v] == s.A - 1) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                if (tp.mkr_bnd_attr[(size_t)(m0 + j1) * VB + v] == s.A - 1) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
         // camera columns: perturbed camera rows from shared memory, base bundle
@@ -555,11 +578,11 @@ __global__ void __launch_bounds__(32 * W, MINB) k_jacobian_rows(DevScene s, Tile
             eval_pair_fma(cv, p1x, p1y, p1z, mkx1, mky1, bx, by);
             const long long co = tp.cam_coloff_u[v];
             const double g0 = c0 * inv_delta, g1 = c1 * inv_delta;
-            if (on0) jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
-            if (on1) jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
-            if (DIST_LAST && tp.last_attr_cam_var == v) {
-                if (on0) dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
-                if (on1) dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
+            jp0[co] = make_double2((ax - dx0) * g0, (ay - dy0) * g0);
+            jp1[co] = make_double2((bx - dx1) * g1, (by - dy1) * g1);
+            if (DIST_LAST && last_cam_var_ == v) {
+                dist_last[i0] = sqrt((ax * ax) + (ay * ay)) * imw;
+                dist_last[i1] = sqrt((bx * bx) + (by * by)) * imw;
             }
         }
     }

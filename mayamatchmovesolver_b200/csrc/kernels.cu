@@ -217,18 +217,6 @@ __global__ void __launch_bounds__(256) k_block_markers(const double *__restrict_
     dst[0] = mx[i]; dst[kRowFrames] = my[i]; dst[2 * kRowFrames] = w[i];
 }
 
-// the same for sparse visibility: observation i belongs to (err_marker[i], err_frame[i])
-__global__ void __launch_bounds__(256) k_block_markers_sparse(const double *__restrict__ mx, const double *__restrict__ my,
-                                                              const double *__restrict__ w, const int32_t *__restrict__ em,
-                                                              const int32_t *__restrict__ ef, int nobs, int M,
-                                                              double *__restrict__ blk) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nobs) return;
-    const int mk = em[i], f = ef[i];
-    double *dst = &blk[(((size_t)(f / kRowFrames) * M + mk) * 3) * kRowFrames + (f % kRowFrames)];
-    dst[0] = mx[i]; dst[kRowFrames] = my[i]; dst[2 * kRowFrames] = w[i];
-}
-
 // ---- launchers -------------------------------------------------------------
 static inline unsigned blocks_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
 
@@ -272,36 +260,45 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             const TiledPlan &t0 = p->cam_plans[0];
             const int nv = t0.VC + 1, nrec = (t0.VB + 1) * kBndRec;
             const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
-            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
             const bool fixed = t0.VC == 6 && t0.VB == 3;
             const bool sparse = t0.obs_base != nullptr;
+            // (sparse visibility keeps no marker block in shared memory; larger marker tiles were no faster:
+            // 10^7 observations at 0.25 visibility, 0.588 ms with 64 markers per CTA, 0.594 with 128, 0.633 with 192)
+            const int mt_cap = 64;
+            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + (sparse ? 0 : 3 * kRowFrames))); };
             auto kern = sparse ? (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3, true> : k_jacobian_rows<W, MINB, false, 6, 3, true>)
                                         : (d_dist_last ? k_jacobian_rows<W, MINB, true, 0, 0, true> : k_jacobian_rows<W, MINB, false, 0, 0, true>))
                                : (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
                                         : (d_dist_last ? k_jacobian_rows<W, MINB, true> : k_jacobian_rows<W, MINB, false>));
+            int m_most = 0;
+            for (const TiledPlan &t : p->cam_plans) m_most = std::max(m_most, t.m_count);
             int &mt = p->rows_mt[d_dist_last ? 1 : 0];
             if (mt == 0) {
                 int occ = 1, sm_count = 1;
                 MMB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device));
-                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(64)));
-                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(32)));
+                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(mt_cap)));
+                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(sparse ? mt_cap : 32)));
                 const int slots = std::max(1, occ) * sm_count;
                 int G = std::max(1, slots / fb);
-                G = std::min(G, (t0.m_count + 1) / 2);
-                mt = (t0.m_count + G - 1) / G;
-                mt = std::min(64, (mt + 1) & ~1);
+                G = std::min(G, (m_most + 1) / 2);
+                mt = (m_most + G - 1) / G;
+                mt = std::min(mt_cap, (mt + 1) & ~1);
+                static int mt_force = -1;
+                if (mt_force < 0) { const char *e = getenv("MMB_ROWS_MT"); mt_force = e ? atoi(e) : 0; }
+                if (mt_force > 0) mt = std::min(mt_cap, (mt_force + 1) & ~1);
             }
-            for (const TiledPlan &t : p->cam_plans) {
-                const int G = (t.m_count + mt - 1) / mt;
-                cudaLaunchConfig_t cfg{};
-                cfg.gridDim = dim3(fb, G); cfg.blockDim = dim3(32 * W); cfg.dynamicSmemBytes = smem_for(mt); cfg.stream = p->stream;
-                cudaLaunchAttribute at[1];
-                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-                at[0].val.programmaticStreamSerializationAllowed = 1;
-                cfg.attrs = at; cfg.numAttrs = 1;
-                MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, t, mt, d_fvec, d_dist, d_jac, d_dist_last));
-                ++p->launches;
-            }
+            // one launch for all the cameras (blockIdx.z): the tail of one camera's tiles overlaps
+            // the next camera's instead of draining the device between launches
+            const int G = (m_most + mt - 1) / mt;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(fb, G, (unsigned)p->cam_plans.size()); cfg.blockDim = dim3(32 * W); cfg.dynamicSmemBytes = smem_for(mt); cfg.stream = p->stream;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            const CamSlice *slices = p->d_cam_slices;
+            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, t0, mt, d_fvec, d_dist, d_jac, d_dist_last, slices));
+            ++p->launches;
             return MMB_OK;
         }
     }
@@ -326,12 +323,13 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             constexpr int W = 4, MINB = 4;
             const int nv = p->tiled.VC + 1, nrec = (p->tiled.VB + 1) * kBndRec;
             const int fb = (p->hp.F + kRowFrames - 1) / kRowFrames;
-            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + 3 * kRowFrames)); };
+            const bool sparse = p->tiled.obs_base != nullptr;
+            const int mt_cap = 64;
+            auto smem_for = [&](int mt) { return (size_t)256 + sizeof(double) * ((size_t)nv * kCamRec * kRowFrames + (size_t)mt * (nrec + (sparse ? 0 : 3 * kRowFrames))); };
             // the common shape (6 camera attributes, 3 bundle attributes) has its own instance
             static int fixed_mode = -1;
             if (fixed_mode < 0) { const char *e = getenv("MMB_ROWS_FIXED"); fixed_mode = e ? atoi(e) : 1; }
             const bool fixed = fixed_mode && p->tiled.VC == 6 && p->tiled.VB == 3;
-            const bool sparse = p->tiled.obs_base != nullptr;
             auto kern = sparse ? (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3, true> : k_jacobian_rows<W, MINB, false, 6, 3, true>)
                                         : (d_dist_last ? k_jacobian_rows<W, MINB, true, 0, 0, true> : k_jacobian_rows<W, MINB, false, 0, 0, true>))
                                : (fixed ? (d_dist_last ? k_jacobian_rows<W, MINB, true, 6, 3> : k_jacobian_rows<W, MINB, false, 6, 3>)
@@ -340,13 +338,13 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             if (mt == 0) {  // one wave: CTAs = resident slots of the device (or as close as the marker count allows)
                 int occ = 1, sm_count = 1;
                 MMB_CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, p->device));
-                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(64)));
-                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(32)));
+                MMB_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_for(mt_cap)));
+                MMB_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * W, smem_for(sparse ? mt_cap : 32)));
                 const int slots = std::max(1, occ) * sm_count;
                 int G = rows_g > 0 ? rows_g : std::max(1, slots / fb);
                 G = std::min(G, (p->hp.M + 1) / 2);
                 mt = (p->hp.M + G - 1) / G;
-                mt = std::min(64, (mt + 1) & ~1);
+                mt = std::min(mt_cap, (mt + 1) & ~1);
             }
             const int G = (p->hp.M + mt - 1) / mt;
             // programmatic dependent launch: the prologue (barrier setup, marker-track fetch)
@@ -357,7 +355,7 @@ mmb_status launch_jacobian(DeviceProblem *p, double *d_fvec, double *d_dist, dou
             at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
             at[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = at; cfg.numAttrs = 1;
-            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, p->tiled, mt, d_fvec, d_dist, d_jac, d_dist_last));
+            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p->ds, p->tiled, mt, d_fvec, d_dist, d_jac, d_dist_last, (const CamSlice *)nullptr));
             ++p->launches;
             return MMB_OK;
         }
@@ -467,7 +465,9 @@ static mmb_status build_marker_blocks(DeviceProblem *p, TiledPlan *t) {
     const HostProblem &hp = p->hp;
     DeviceArena &A = p->arena;
     const int FB = (hp.F + kRowFrames - 1) / kRowFrames;
-    const size_t nblk = (size_t)FB * hp.M * 3 * kRowFrames;
+    // (a sparse scene reads the observation arrays themselves: the blocked copy would hold, and
+    // the kernel would fetch, every (marker, frame) slot whether or not it has an observation)
+    const size_t nblk = hp.dense_grid ? (size_t)FB * hp.M * 3 * kRowFrames : 2;
     double *d_blk = nullptr;
     MMB_CUDA_CHECK(A.alloc(&d_blk, nblk));
     MMB_CUDA_CHECK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
@@ -475,8 +475,6 @@ static mmb_status build_marker_blocks(DeviceProblem *p, TiledPlan *t) {
     if (hp.dense_grid) {
         k_block_markers<<<(unsigned)(((long long)hp.M * hp.F + 255) / 256), 256, 0, p->stream>>>(p->ds.obs_mx, p->ds.obs_my, p->ds.obs_w, hp.M, hp.F, d_blk);
     } else {
-        k_block_markers_sparse<<<(unsigned)((hp.nobs + 255) / 256), 256, 0, p->stream>>>(p->ds.obs_mx, p->ds.obs_my, p->ds.obs_w, p->ds.err_marker,
-                                                                                     p->ds.err_frame, hp.nobs, hp.M, d_blk);
         std::vector<int32_t> base((size_t)FB * hp.M, 0);
         std::vector<uint32_t> mask((size_t)FB * hp.M, 0u);
         for (int i = hp.nobs - 1; i >= 0; --i) {   // descending: the first observation of a block is written last
@@ -770,6 +768,11 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
                 p->cam_plans.push_back(t);
                 mk = end;
             }
+            std::vector<CamSlice> sl;
+            for (const TiledPlan &t : p->cam_plans) sl.push_back(CamSlice{t.cam, t.m_base, t.m_count, t.bnd_contig, t.last_attr_cam_var, t.bnd_rec0});
+            CamSlice *d_sl = nullptr;
+            CK(A.upload(&d_sl, sl));
+            p->d_cam_slices = d_sl;
         }
     }
     {   // evaluation-per-thread tiled kernel (k_jacobian_lens): lens in the loop and / or several cameras
