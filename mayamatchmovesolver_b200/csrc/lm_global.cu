@@ -100,6 +100,10 @@ struct LmWorkspace {
     int *wave_flags = nullptr;   // [NSP / 64] epoch flags of the wavefront triangular solves
     int *wave_ctr = nullptr;     // device epoch counter (k_ctrl_lmpar adds 2 per lmpar step)
     int *tile_flags = nullptr;   // [(NSP/64)^2] epoch flags of the tile-dataflow Cholesky
+    int *syrk_ready = nullptr;   // [(NSP/64)^2] epoch flags of the SYRK's tiles (Cholesky running beside the SYRK)
+    cudaStream_t side = nullptr; // the stream of that Cholesky
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int chol_beside = 0;         // CTAs of the Cholesky launched beside the SYRK (0: one after the other)
     bool chol_tiles = true;      // one-launch tile-dataflow Cholesky (MMB_CHOL=steps: two launches per block step)
     double *h_stage = nullptr;   // pinned staging: [max(2 n, kRedBlocks + n)]
     int *h_cancel = nullptr;     // pinned, mapped: set by mmb_request_cancel, polled by the loop-head kernel
@@ -119,6 +123,9 @@ struct LmWorkspace {
     double phase_ms[4] = {0, 0, 0, 0};
     int phase_n = 0;
     ~LmWorkspace() {
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (ev_join) cudaEventDestroy(ev_join);
+        if (side) cudaStreamDestroy(side);
         if (graph_exec) cudaGraphExecDestroy(graph_exec);
         if (graph) cudaGraphDestroy(graph);
         pinned_release(pinned);
@@ -147,7 +154,7 @@ __global__ void k_ctrl_init(LmState *st, const double *part_f, int nparts) {
         st->iter = 1; st->nfev = 1; st->njev = 0; st->info = 0;
         st->need_jacobian = 1; st->done = 0; st->accepted = 0;
         st->delta = 0.0; st->xnorm = 0.0; st->gnorm = 0.0;
-        st->chol_fail_total = 0; st->n_factor = 0;
+        st->chol_fail_total = 0; st->n_factor = 0; st->dataflow_timeout = 0;
         // lmder input checks (info = 0: improper input parameters)
         if (st->n <= 0 || st->m < st->n || st->ftol < 0.0 || st->xtol < 0.0 || st->gtol < 0.0 ||
             st->maxfev <= 0 || st->factor <= 0.0) {
@@ -659,10 +666,26 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
             const size_t nt = ((size_t)d.NSP / 64) * ((size_t)d.NSP / 64);
             CKW(A.alloc(&w->tile_flags, nt));
             CKW(cudaMemsetAsync(w->tile_flags, 0, sizeof(int) * nt, p->stream));
+            CKW(A.alloc(&w->syrk_ready, nt));
+            CKW(cudaMemsetAsync(w->syrk_ready, 0, sizeof(int) * nt, p->stream));
             CKW(cudaFuncSetAttribute(k_chol_tiles<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             CKW(cudaFuncSetAttribute(k_chol_tiles<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             const char *e = getenv("MMB_CHOL");
             w->chol_tiles = !(e && !strcmp(e, "steps"));
+            // Cholesky beside the SYRK (chain-bound sizes only): that many resident CTAs, one per SM.
+            // cfg3, linear algebra of a 15-iteration solve: 25.5 ms one after the other; beside, with
+            // 16 / 20 / 24 / 28 / 32 / 40 / 48 CTAs: 23.5 / 21.5 / 21.3 / 21.3 / 21.7 / 22.3 / 23.2 ms.
+            const char *eb = getenv("MMB_CHOL_BESIDE");
+            w->chol_beside = eb ? atoi(eb) : 24;
+            if (!w->chol_tiles || d.KE == 0 || d.NSP / 64 > 64) w->chol_beside = 0;
+            if (w->chol_beside > 0) {
+                int sms = 0;
+                CKW(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device));
+                w->chol_beside = std::min(w->chol_beside, sms);
+                CKW(cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking));
+                CKW(cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming));
+                CKW(cudaEventCreateWithFlags(&w->ev_join, cudaEventDisableTiming));
+            }
             const char *ei = getenv("MMB_WAVE_INV");
             if (w->chol_tiles && !(ei && atoi(ei) == 0)) CKW(A.alloc(&w->Dinv, ((size_t)d.NSP / 64) * 4096));
         }
@@ -874,6 +897,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
     }
     const int nb = d.NSP / 64;
+    const bool beside = w->chol_beside > 0 && !sharded && d.KE;
     if (d.KE) {
         const int tiles = nb * (nb + 1) / 2;
         // 300 tiles on 148 SMs leave some SMs with 3 CTAs and most with 2 (measured 0.72 ms); 16 x
@@ -896,8 +920,26 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = ksplit; attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = ksplit > 1 ? 1 : 0;
-        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S));
+        if (beside) {
+            // The factorisation is a latency chain over the block columns that needs few SMs; the
+            // SYRK needs them all.  Launch the Cholesky (a few resident CTAs walking the tiles column
+            // by column) on a second stream and let it take each tile when the SYRK publishes it.
+            // The uncapped instance (254 registers x 256 threads) fills the register file of its SM:
+            // those SMs run the chain undisturbed, the SYRK has the others, and it never waits, so
+            // the pair cannot dead-lock.  (Sharing SMs -- the 128-register instance plus two SYRK
+            // CTAs -- was measured slower: the chain's FP64 operations queue behind the SYRK's DMMAs.)
+            MMB_CUDA_CHECK(cudaEventRecord(w->ev_fork, s));
+            MMB_CUDA_CHECK(cudaStreamWaitEvent(w->side, w->ev_fork, 0));
+            k_chol_tiles<1><<<std::min(w->chol_beside, tiles), 256, kCholTilesSmem, w->side>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv,
+                                                                                          (const int *)w->syrk_ready);
+            LAUNCH_CHECK();
+            MMB_CUDA_CHECK(cudaEventRecord(w->ev_join, w->side));
+        }
+        int *ready = beside ? w->syrk_ready : nullptr;
+        const int *ectr = w->wave_ctr;
+        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S, ready, ectr));
         LAUNCH_CHECK();
+        if (beside) MMB_CUDA_CHECK(cudaStreamWaitEvent(s, w->ev_join, 0));
     }
     if (sharded) {
         // the one data-path collective of the solve: rows 0..ns of the reduced system
@@ -912,13 +954,15 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
     }
     if (prof) cudaEventRecord(w->ev[1], s);
-    if (w->chol_tiles) {
+    if (beside) {
+        // factorised beside the SYRK above
+    } else if (w->chol_tiles) {
         static int chol_minb = -1;
         if (chol_minb < 0) { const char *e = getenv("MMB_CHOL_MINB"); chol_minb = e ? atoi(e) : 0; }
         if (nb > 64 || chol_minb == 2)
-            k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
+            k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr);
         else
-            k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv);
+            k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr);
         LAUNCH_CHECK();
     } else {
         for (int kb = 0; kb < nb; ++kb) {
@@ -1317,6 +1361,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     if ((st = read_state(p)) != MMB_OK) return st;
     const LmState &f = *w->h_st;
     if (sharded && p->comm->peer_error()) { set_last_error("peer all-reduce: a barrier timed out (ranks out of step)"); return MMB_ERR_COMM; }
+    if (f.dataflow_timeout) { set_last_error("Cholesky beside the SYRK: a tile of the reduced system never arrived"); return MMB_ERR_CUDA; }
     if (f.cancelled) res->user_interrupted = 1;
     if (use_graph) {
         t_jac = 1e-9 * (double)f.t_jac_ns; t_lin = 1e-9 * (double)f.t_lin_ns; t_func = 1e-9 * (double)f.t_func_ns;

@@ -694,13 +694,23 @@ __device__ __forceinline__ void tile_index(int t, int &bi, int &bj) {
 // shared memory and the cluster folds them through distributed shared memory in rank order,
 // each CTA owning a slice of the tile -- a fixed summation order (two runs give the same bits,
 // where the FP atomics of the earlier version did not) and no extra trip through L2.
+// Tiles are numbered column by column, as k_chol_tiles numbers them, and (ready != nullptr) each
+// finished tile is published with the epoch the factorisation of this step waits for
+// (ready[bj * nb + bi] = *epoch_ctr + 1): the tile-dataflow Cholesky runs BESIDE this kernel and
+// picks every tile up as soon as it is complete, instead of starting when the last one is.
 constexpr int kSyrkKT = 16;
-__global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S) {
+__global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S,
+                                                    int *ready, const int *epoch_ctr) {
     __shared__ __align__(16) double smem[4 * kSyrkKT * kTS];   // sA[2], sB[2]; reused as the 64x64 partial tile
     double *sA[2] = {smem, smem + kSyrkKT * kTS};
     double *sB[2] = {smem + 2 * kSyrkKT * kTS, smem + 3 * kSyrkKT * kTS};
-    int bi, bj;
-    tile_index(blockIdx.x, bi, bj);
+    const int nb = d.NSP / 64;
+    int bi, bj = 0;
+    {   // column-major tile numbering: column j holds nb - j tiles
+        int t = blockIdx.x;
+        while (t >= nb - bj) { t -= nb - bj; ++bj; }
+        bi = bj + t;
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wr = warp >> 1, wc = warp & 1;
     double acc[4][4][2];
@@ -745,6 +755,14 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     }
     if (gridDim.y == 1) {
         tile_store_sub(S, d.NSP, bi, bj, wr, wc, lane, acc);
+        if (ready) {
+            __threadfence();
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const int epoch = __ldcg(epoch_ctr) + 1;
+                asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(&ready[bj * nb + bi]), "r"(epoch) : "memory");
+            }
+        }
         return;
     }
     // partial tile -> own shared memory, value v of thread t at [v][t] (conflict-free)
@@ -777,8 +795,15 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
         const int row = bi * 64 + wr * 32 + ti * 8 + g, col = bj * 64 + wc * 32 + tj * 8 + q * 2 + h;
         S[(size_t)row * d.NSP + col] -= sum;
     }
-    // nobody leaves while a peer may still read its shared memory
+    // nobody leaves while a peer may still read its shared memory; after the barrier every rank's
+    // slice of the tile is written (fenced to the device before the arrival), so rank 0 publishes
+    if (ready) __threadfence();
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (ready && rank == 0 && threadIdx.x == 0) {
+        const int epoch = __ldcg(epoch_ctr) + 1;
+        __threadfence();
+        asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(&ready[bj * nb + bi]), "r"(epoch) : "memory");
+    }
 }
 
 // ---- blocked Cholesky of S (lower, row-major, ld = NSP) ----------------------------
@@ -1021,12 +1046,14 @@ __device__ __forceinline__ unsigned long long gtimer() {
     return t;
 }
 
-// MINB = 1: no register cap (176 registers, one CTA per SM) -- fastest block-column chain, for
+// MINB = 1: no register cap (254 registers, one CTA per SM) -- fastest block-column chain, for
 // systems whose factorisation is that chain (cfg3: 24 block columns); MINB = 2: 128 registers,
 // two CTAs per SM -- for large systems (cfg5: 235 block columns), which are throughput-bound.
+// syrk_ready != nullptr: launched BESIDE k_schur_syrk with a small grid of resident CTAs; a tile of
+// S is read once the SYRK has published it (see k_schur_syrk).
 template <int MINB>
 __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
-                                                    const int *epoch_ctr, double *__restrict__ Dinv) {
+                                                    const int *epoch_ctr, double *__restrict__ Dinv, const int *syrk_ready) {
     extern __shared__ __align__(16) double sm[];
     double *sA = sm;                 // L(i,k) during phase A; afterwards T (stride kCS)
     double *sB = sm + 64 * kOS;      // L(j,k) during phase A; afterwards X (stride kCS)
@@ -1034,18 +1061,40 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     const int nb = d.NSP / 64;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int epoch = __ldcg(epoch_ctr) + 1;
+    const size_t ld = (size_t)d.NSP;
+    int *flags = tile_flags;
+    const int wr = warp >> 1, wc = warp & 1;   // warp tile: rows wr*16.., cols wc*32..
+    const int g = lane >> 2, q = lane & 3;
+    // gridDim.x = number of tiles: one tile per CTA.  A smaller grid (every CTA resident at once:
+    // the launch beside the SYRK) walks the tiles round-robin; a CTA takes its tiles in increasing
+    // order and a tile only waits for tiles of lower number (and for the SYRK, which waits for
+    // nothing), so the lowest unfinished tile can always proceed.
+    for (int tile = blockIdx.x; tile < nb * (nb + 1) / 2; tile += gridDim.x) {
+    if (tile != (int)blockIdx.x) __syncthreads();   // phase E of the previous tile is done with the shared tiles
     // column-major tile numbering: column j holds nb - j tiles
-    int j = 0, t = blockIdx.x;
+    int j = 0, t = tile;
     while (t >= nb - j) { t -= nb - j; ++j; }
     const int i = j + t;
     const bool diag = i == j;
-    const size_t ld = (size_t)d.NSP;
-    int *flags = tile_flags;
     const bool traced = tid == 0 && i <= j + 1 && j < 64;
     unsigned long long *tr = &g_chol_trace[(j * 2 + (diag ? 0 : 1)) * 6];
+    if (syrk_ready) {
+        // this tile of S is complete when the SYRK has published it (bounded wait: a flag that never
+        // comes is reported, not spun on for ever)
+        if (tid == 0) {
+            const int *f = &syrk_ready[j * nb + i];
+            int v;
+            const unsigned long long t0 = gtimer();
+            unsigned spins = 0;
+            for (;;) {
+                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                if (v == epoch) break;
+                if ((++spins & 1023u) == 0u && (gtimer() - t0 > 2000000000ull || *(volatile int *)&st->dataflow_timeout)) { atomicExch(&st->dataflow_timeout, 1); break; }
+            }
+        }
+        __syncthreads();
+    }
     // ---- A: left-looking update on the tensor cores ----
-    const int wr = warp >> 1, wc = warp & 1;   // warp tile: rows wr*16.., cols wc*32..
-    const int g = lane >> 2, q = lane & 3;
     double acc[2][4][2];
     double2 sij[2][4];   // this tile of S, fetched before the waits: off the critical path
 #pragma unroll
@@ -1333,6 +1382,7 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
             out[e] = c <= rr ? X[rr * kCS + c] : 0.0;
         }
     }
+    }   // tiles of this CTA
 }
 
 // ---- triangular solves with L_S (single CTA, 1024 threads) ---------------------------

@@ -44,6 +44,7 @@ struct LmState {
     // and the device time of each phase (%globaltimer, ns) stamped at the phase boundaries
     int n_body_jac, n_body_lmpar, n_body_trial, n_body_loop;
     int cancelled;                     // the host's cancel flag was seen set
+    int dataflow_timeout;              // a tile of the SYRK never arrived at the Cholesky running beside it
     unsigned long long t_mark, t_jac_ns, t_lin_ns, t_func_ns;
 };
 
