@@ -98,7 +98,7 @@ struct LmWorkspace {
     int gemv_chunks = 1;
     long long n_allreduce = 0;
     int *wave_flags = nullptr;   // [NSP / 64] epoch flags of the wavefront triangular solves
-    int *wave_ctr = nullptr;     // device epoch counter (k_ctrl_lmpar adds 2 per lmpar step)
+    int *wave_ctr = nullptr;     // device epoch counter (k_ctrl_lmpar_decide / _update add 2 per lmpar step)
     int *tile_flags = nullptr;   // [(NSP/64)^2] epoch flags of the tile-dataflow Cholesky
     int *syrk_ready = nullptr;   // [(NSP/64)^2] epoch flags of the SYRK's tiles (Cholesky running beside the SYRK)
     cudaStream_t side = nullptr; // the stream of that Cholesky
@@ -113,7 +113,7 @@ struct LmWorkspace {
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t graph_exec = nullptr;
     bool graph_failed = false;
-    int body_launches[4] = {0, 0, 0, 0};  // kernels per execution of: loop head/tail, jacobian body, lmpar body, trial body
+    int body_launches[5] = {0, 0, 0, 0, 0};  // kernels per execution of: loop head/tail, jacobian body, lmpar body, trial body, Newton-correction body
     int fixed_launches = 0;               // prologue + epilogue kernels
     bool wave_ok = false;        // every block of the wavefront kernels fits on the device at once
     double init_avg = 0, init_min = 0, init_max = 0;
@@ -249,36 +249,38 @@ __global__ void k_ctrl_prep_decide(LmState *st, const double *scal, const double
     st->lmpar_iter = 0; st->lmpar_done = 0; st->chol_fail = 0; st->par_cur = 0.0;
 }
 
-// After a factorisation + solve: eliminated-side parts of ||D p||^2 and of ||L^-1 D^2 p||^2
-// (the Newton-correction vector, still unscaled by 1/||D p||) and the failure flag.
-__global__ void __launch_bounds__(1024) k_lmpar_partial(LmDims d, LmState *st, const double *p_int, const double *w_int,
+// After a factorisation + solve: eliminated-side part of ||D p||^2 and the failure flag.
+__global__ void __launch_bounds__(1024) k_lmpar_partial(LmDims d, LmState *st, const double *p_int,
                                                         const double *diag, const int32_t *i2p, double *scal) {
     __shared__ double sh[32];
-    double dxE = 0.0, dxS = 0.0, wE = 0.0;
+    double dxE = 0.0, dxS = 0.0;
     for (int q = threadIdx.x; q < d.n; q += blockDim.x) {
         const double t = diag[i2p[q]] * p_int[q];
-        if (q < d.KE) { dxE += t * t; const double w = w_int[q]; wE += w * w; }
+        if (q < d.KE) dxE += t * t;
         else dxS += t * t;
     }
-    dxE = block_sum(dxE, sh); dxS = block_sum(dxS, sh); wE = block_sum(wE, sh);
+    dxE = block_sum(dxE, sh); dxS = block_sum(dxS, sh);
     if (threadIdx.x == 0) {
-        scal[0] = dxE; scal[1] = st->chol_fail ? 1.0 : 0.0; scal[2] = wE;
+        scal[0] = dxE; scal[1] = st->chol_fail ? 1.0 : 0.0;
         st->part_s[0] = dxS;
     }
 }
 
-// lmpar step (MINPACK lmpar restated on the normal equations)
-__global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, const double *w_int, const double *scal,
-                                                     int *wave_ctr) {
+// eliminated-side part of ||L^-1 D^2 p||^2 (the Newton-correction vector, still unscaled by 1/||D p||)
+__global__ void __launch_bounds__(1024) k_lmpar_partial_w(LmDims d, const double *w_int, double *scal) {
     __shared__ double sh[32];
-    double a = 0.0;
-    for (int q = d.KE + threadIdx.x; q < d.n; q += blockDim.x) {
-        const double t = w_int[q];
-        a += t * t;
-    }
-    a = block_sum(a, sh);
-    if (threadIdx.x != 0) return;
-    *wave_ctr += 2;  // the two wavefront solves of this step are done: retire their epochs
+    double wE = 0.0;
+    for (int q = threadIdx.x; q < d.KE; q += blockDim.x) { const double w = w_int[q]; wE += w * w; }
+    wE = block_sum(wE, sh);
+    if (threadIdx.x == 0) scal[0] = wE;
+}
+
+// lmpar step (MINPACK lmpar restated on the normal equations), first half: everything ||D p||
+// decides.  lmpar ends here at most steps (Gauss-Newton step inside the trust region, or
+// | ||D p|| - delta | <= 0.1 delta); only a step that goes on needs the Newton correction
+// ||L^-1 D^2 p||, i.e. another pass over the eliminated side and a triangular solve with the
+// reduced factor: lmpar_corr asks for it and k_ctrl_lmpar_update finishes the step.
+__global__ void k_ctrl_lmpar_decide(LmState *st, const double *scal, int *wave_ctr) {
     const double p1 = 0.1, p001 = 0.001, dwarf = 2.2250738585072014e-308;
     const double delta = st->delta;
     const bool fail = scal[1] > 0.0;  // a pivot <= 0 on any rank
@@ -286,27 +288,27 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
     st->chol_fail = 0;
     st->n_factor += 1;
     const double dx2 = scal[0] + st->part_s[0];
+    st->dx2 = dx2;
     st->dxnorm = fail ? INFINITY : sqrt(dx2);
-    // ||L^-1 (D^2 p / dxnorm)||^2: the solves ran without the 1/dxnorm factor
-    const double qn2 = (fail || !(dx2 > 0.0)) ? 0.0 : (scal[2] + a) / dx2;
-    st->qnorm2 = qn2;
+    st->lmpar_corr = 0;
+    st->qnorm2 = 0.0;
     if (st->lmpar_iter == 0) {
         // Gauss-Newton probe at par = 0
         const double dxnorm = st->dxnorm;
         const double fp = dxnorm - delta;
         st->fp = fp;
-        if (!fail && fp <= p1 * delta) { st->par = 0.0; st->lmpar_done = 1; return; }
-        double parl = 0.0;
-        if (!fail && qn2 > 0.0) parl = ((fp / delta) / qn2);
+        if (!fail && fp <= p1 * delta) { st->par = 0.0; st->lmpar_done = 1; *wave_ctr += 2; return; }
+        if (!fail && dx2 > 0.0) { st->lmpar_corr = 1; return; }   // parl needs the correction
         double paru = st->gnorm_scaled / delta;
         if (paru == 0.0) paru = dwarf / fmin(delta, p1);
         double par = st->par;
-        par = fmax(par, parl);
+        par = fmax(par, 0.0);
         par = fmin(par, paru);
         if (par == 0.0) par = fail ? 0.0 : st->gnorm_scaled / dxnorm;
         if (par == 0.0) par = fmax(dwarf, p001 * paru);
-        st->parl = parl; st->paru = paru; st->par = par; st->par_cur = par;
+        st->parl = 0.0; st->paru = paru; st->par = par; st->par_cur = par;
         st->lmpar_iter = 1;
+        *wave_ctr += 2;
         return;
     }
     if (fail) {
@@ -316,6 +318,7 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
         st->par_cur = st->par;
         st->lmpar_iter += 1;
         if (st->lmpar_iter > 30) { st->lmpar_done = 1; st->info = -2; st->done = 1; }
+        *wave_ctr += 2;
         return;
     }
     const double temp = st->fp;
@@ -323,6 +326,46 @@ __global__ void __launch_bounds__(1024) k_ctrl_lmpar(LmDims d, LmState *st, cons
     st->fp = fp;
     if (fabs(fp) <= p1 * delta || (st->parl == 0.0 && fp <= temp && temp < 0.0) || st->lmpar_iter >= 10) {
         st->lmpar_done = 1;
+        *wave_ctr += 2;
+        return;
+    }
+    st->lmpar_corr = 1;
+}
+
+// second half, for a step that goes on: the next par from the Newton correction
+__global__ void __launch_bounds__(1024) k_ctrl_lmpar_update(LmDims d, LmState *st, const double *w_int, const double *scal,
+                                                            int *wave_ctr) {
+    __shared__ double sh[32];
+    if (!st->lmpar_corr) return;   // (the host-driven loop enqueues both halves unconditionally)
+    double a = 0.0;
+    for (int q = d.KE + threadIdx.x; q < d.n; q += blockDim.x) {
+        const double t = w_int[q];
+        a += t * t;
+    }
+    a = block_sum(a, sh);
+    if (threadIdx.x != 0) return;
+    *wave_ctr += 2;  // the two wavefront solves of this step are done: retire their epochs
+    st->lmpar_corr = 0;
+    const double p1 = 0.1, p001 = 0.001, dwarf = 2.2250738585072014e-308;
+    const double delta = st->delta;
+    const double dx2 = st->dx2;
+    // ||L^-1 (D^2 p / dxnorm)||^2: the solves ran without the 1/dxnorm factor
+    const double qn2 = !(dx2 > 0.0) ? 0.0 : (scal[0] + a) / dx2;
+    st->qnorm2 = qn2;
+    const double fp = st->fp;
+    if (st->lmpar_iter == 0) {
+        const double dxnorm = st->dxnorm;
+        double parl = 0.0;
+        if (qn2 > 0.0) parl = ((fp / delta) / qn2);
+        double paru = st->gnorm_scaled / delta;
+        if (paru == 0.0) paru = dwarf / fmin(delta, p1);
+        double par = st->par;
+        par = fmax(par, parl);
+        par = fmin(par, paru);
+        if (par == 0.0) par = st->gnorm_scaled / dxnorm;
+        if (par == 0.0) par = fmax(dwarf, p001 * paru);
+        st->parl = parl; st->paru = paru; st->par = par; st->par_cur = par;
+        st->lmpar_iter = 1;
         return;
     }
     const double parc = ((fp / delta) / qn2);
@@ -470,7 +513,7 @@ __global__ void k_error_stats_final(LmState *st, const double *scal, const doubl
 // ---- phase boundaries of the device-resident loop ---------------------------------------
 // One thread: stamps the phase timers (%globaltimer) and copies LmState flags into the
 // conditional handles of the graph (the device-side half of cudaGraphConditionalHandle).
-enum { kCondStart = 0, kCondLoopHead, kCondAfterJac, kCondInLmpar, kCondAfterLmpar, kCondAfterTrial };
+enum { kCondStart = 0, kCondLoopHead, kCondAfterJac, kCondInLmpar, kCondAfterLmpar, kCondCorr, kCondAfterTrial };
 __global__ void k_cond(LmState *st, const int *cancel, int where, cudaGraphConditionalHandle h0,
                        cudaGraphConditionalHandle h1) {
     unsigned long long now;
@@ -493,6 +536,10 @@ __global__ void k_cond(LmState *st, const int *cancel, int where, cudaGraphCondi
         case kCondInLmpar:  // tail of the lmpar body; h0 = WHILE(lmpar)
             st->n_body_lmpar += 1;
             cudaGraphSetConditional(h0, (!st->done && !st->lmpar_done) ? 1u : 0u);
+            break;
+        case kCondCorr:  // inside the lmpar body, after the decision; h0 = IF(Newton correction)
+            if (st->lmpar_corr) st->n_body_corr += 1;
+            cudaGraphSetConditional(h0, st->lmpar_corr ? 1u : 0u);
             break;
         case kCondAfterLmpar:  // h0 = IF(trial); h1 = outer WHILE (the trial body may be skipped)
             st->t_lin_ns += now - st->t_mark;
@@ -897,7 +944,10 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
     }
     const int nb = d.NSP / 64;
-    const bool beside = w->chol_beside > 0 && !sharded && d.KE;
+    // (graph bodies only: the two launches are independent branches there.  Launched from the host,
+    // two streams may share one hardware queue, and the queue entry that signals the end of the
+    // Cholesky would hold back the SYRK launch behind it -- the SYRK the Cholesky is waiting for.)
+    const bool beside = w->chol_beside > 0 && !sharded && d.KE && w->capturing;
     if (d.KE) {
         const int tiles = nb * (nb + 1) / 2;
         // 300 tiles on 148 SMs leave some SMs with 3 CTAs and most with 2 (measured 0.72 ms); 16 x
@@ -935,7 +985,8 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
             LAUNCH_CHECK();
             MMB_CUDA_CHECK(cudaEventRecord(w->ev_join, w->side));
         }
-        int *ready = beside ? w->syrk_ready : nullptr;
+        // (test hook: flags that never come, to exercise the bounded wait and the fall-back)
+        int *ready = (beside && !getenv("MMB_TEST_DROP_SYRK_FLAGS")) ? w->syrk_ready : nullptr;
         const int *ectr = w->wave_ctr;
         MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S, ready, ectr));
         LAUNCH_CHECK();
@@ -981,7 +1032,29 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         LAUNCH_CHECK();
     }
     if (prof) cudaEventRecord(w->ev[3], s);
-    // Newton correction: w = L^-1 D^2 p (scaled by 1/||D p|| in k_ctrl_lmpar)
+    k_lmpar_partial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->diag, w->i2p, w->scal);
+    LAUNCH_CHECK();
+    if ((rs = all_reduce(p, w->scal, 2)) != MMB_OK) return rs;
+    k_ctrl_lmpar_decide<<<1, 1, 0, s>>>(w->st, w->scal, w->wave_ctr);
+    LAUNCH_CHECK();
+    if (prof) {
+        cudaEventRecord(w->ev[4], s);
+        cudaEventSynchronize(w->ev[4]);
+        for (int i = 0; i < 4; ++i) { float ms = 0; cudaEventElapsedTime(&ms, w->ev[i], w->ev[i + 1]); w->phase_ms[i] += ms; }
+        ++w->phase_n;
+    }
+    return MMB_OK;
+}
+
+// second half of an lmpar step that goes on (st->lmpar_corr): Newton correction
+// w = L^-1 D^2 p (scaled by 1/||D p|| in k_ctrl_lmpar_update), then the next par
+static mmb_status enqueue_lmpar_correction(DeviceProblem *p) {
+    LmWorkspace *w = p->lm;
+    const LmDims &d = w->d;
+    cudaStream_t s = p->stream;
+    mmb_status rs;
+    const bool prof = w->profile && !w->capturing;
+    if (prof) cudaEventRecord(w->ev[3], s);
     if (d.KE) {
         k_qsolve_e<<<(d.F + 127) / 128, 128, 0, s>>>(d, w->Lf, w->p_int, w->diag, w->i2p, w->w_int);
         LAUNCH_CHECK();
@@ -994,22 +1067,21 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         k_gemv_fold<<<(d.ns + 127) / 128, 128, 0, s>>>(d, d.KE ? w->gemv_chunks : 0, w->part_gemv, w->tvec);
         LAUNCH_CHECK();
     }
-    k_lmpar_partial<<<1, 1024, 0, s>>>(d, w->st, w->p_int, w->w_int, w->diag, w->i2p, w->scal);
+    k_lmpar_partial_w<<<1, 1024, 0, s>>>(d, w->w_int, w->scal);
     LAUNCH_CHECK();
-    if ((rs = all_reduce(p, w->scal, 3)) != MMB_OK) return rs;
+    if ((rs = all_reduce(p, w->scal, 1)) != MMB_OK) return rs;
     if (d.ns) {
         if ((rs = all_reduce(p, w->tvec, (size_t)d.ns)) != MMB_OK) return rs;
         k_qrhs_s<<<(d.ns + 127) / 128, 128, 0, s>>>(d, w->tvec, w->p_int, w->diag, w->i2p, w->w_int + d.KE);
         LAUNCH_CHECK();
         if ((rs = enqueue_forward_s(p, w->w_int + d.KE)) != MMB_OK) return rs;
     }
-    k_ctrl_lmpar<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal, w->wave_ctr);
+    k_ctrl_lmpar_update<<<1, 1024, 0, s>>>(d, w->st, w->w_int, w->scal, w->wave_ctr);
     LAUNCH_CHECK();
     if (prof) {
         cudaEventRecord(w->ev[4], s);
         cudaEventSynchronize(w->ev[4]);
-        for (int i = 0; i < 4; ++i) { float ms = 0; cudaEventElapsedTime(&ms, w->ev[i], w->ev[i + 1]); w->phase_ms[i] += ms; }
-        ++w->phase_n;
+        float ms = 0; cudaEventElapsedTime(&ms, w->ev[3], w->ev[4]); w->phase_ms[3] += ms;
     }
     return MMB_OK;
 }
@@ -1112,8 +1184,8 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     // the trial's all-reduce (k_ctrl_trial / k_ctrl_accept) and k_cond polls a word that stays 0.
     const int *cond_cancel = (p->comm && p->comm->world > 1) ? w->d_zero : w->d_cancel;
     mmb_status st = MMB_OK;
-    cudaGraph_t g = nullptr, body_loop = nullptr, body_jac = nullptr, body_lmpar = nullptr, body_trial = nullptr, tmp = nullptr;
-    cudaGraphConditionalHandle h_loop, h_jac, h_lmpar, h_trial;
+    cudaGraph_t g = nullptr, body_loop = nullptr, body_jac = nullptr, body_lmpar = nullptr, body_trial = nullptr, body_corr = nullptr, tmp = nullptr;
+    cudaGraphConditionalHandle h_loop, h_jac, h_lmpar, h_trial, h_corr;
     MMB_CUDA_CHECK(cudaGraphCreate(&g, 0));
     w->graph = g;
     MMB_CUDA_CHECK(cudaGraphConditionalHandleCreate(&h_loop, g, 0, 0));
@@ -1183,12 +1255,31 @@ static mmb_status lm_graph_build(DeviceProblem *p, int handle_owner) {
     w->body_launches[1] = (int)(p->launches - l0);
     // one lmpar step
     l0 = p->launches;
+    {
+        cudaError_t e1 = cudaGraphConditionalHandleCreate(&h_corr, handle_owner ? body_lmpar : g, 0, 0);
+        if (e1 != cudaSuccess) {
+            set_last_error(std::string("LM graph: cudaGraphConditionalHandleCreate: ") + cudaGetErrorString(e1));
+            cudaGetLastError();
+            w->capturing = false;
+            p->launches = launches_before;
+            return MMB_ERR_CUDA;
+        }
+    }
     GB(cudaStreamBeginCaptureToGraph(s, body_lmpar, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
     GS(enqueue_lmpar_step(p));
+    k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondCorr, h_corr, h_corr);
+    ++p->launches;
+    GS(capture_conditional(s, h_corr, cudaGraphCondTypeIf, &body_corr));
     k_cond<<<1, 1, 0, s>>>(w->st, cond_cancel, kCondInLmpar, h_lmpar, h_lmpar);
     ++p->launches;
     GB(cudaStreamEndCapture(s, &tmp));
     w->body_launches[2] = (int)(p->launches - l0);
+    // the Newton correction of an lmpar step that goes on
+    l0 = p->launches;
+    GB(cudaStreamBeginCaptureToGraph(s, body_corr, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
+    GS(enqueue_lmpar_correction(p));
+    GB(cudaStreamEndCapture(s, &tmp));
+    w->body_launches[4] = (int)(p->launches - l0);
     // trial point, ratio test, accept / reject
     l0 = p->launches;
     GB(cudaStreamBeginCaptureToGraph(s, body_trial, nullptr, nullptr, 0, cudaStreamCaptureModeRelaxed));
@@ -1237,6 +1328,10 @@ static mmb_status lm_run_host_loop(DeviceProblem *p, mmb_result *res, double *t_
         while (!w->h_st->lmpar_done && !w->h_st->done) {
             if ((st = enqueue_lmpar_step(p)) != MMB_OK) return st;
             if ((st = read_state(p)) != MMB_OK) return st;
+            if (w->h_st->lmpar_corr) {
+                if ((st = enqueue_lmpar_correction(p)) != MMB_OK) return st;
+                if ((st = read_state(p)) != MMB_OK) return st;
+            }
         }
         *t_lin += secs(t0, clk::now());
         if (w->h_st->done) break;
@@ -1361,13 +1456,24 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     if ((st = read_state(p)) != MMB_OK) return st;
     const LmState &f = *w->h_st;
     if (sharded && p->comm->peer_error()) { set_last_error("peer all-reduce: a barrier timed out (ranks out of step)"); return MMB_ERR_COMM; }
-    if (f.dataflow_timeout) { set_last_error("Cholesky beside the SYRK: a tile of the reduced system never arrived"); return MMB_ERR_CUDA; }
+    if (f.dataflow_timeout) {
+        // never seen; if the two branches of the graph were ever not run side by side, go back to
+        // one after the other for the rest of this handle's life and solve again
+        if (w->chol_beside > 0 && use_graph) {
+            w->chol_beside = 0;
+            cudaGraphExecDestroy(w->graph_exec); w->graph_exec = nullptr;
+            cudaGraphDestroy(w->graph); w->graph = nullptr;
+            return lm_solve(p, res, x_out, attr_out, dist_out);
+        }
+        set_last_error("Cholesky beside the SYRK: a tile of the reduced system never arrived");
+        return MMB_ERR_CUDA;
+    }
     if (f.cancelled) res->user_interrupted = 1;
     if (use_graph) {
         t_jac = 1e-9 * (double)f.t_jac_ns; t_lin = 1e-9 * (double)f.t_lin_ns; t_func = 1e-9 * (double)f.t_func_ns;
         p->launches += w->fixed_launches + (long long)f.n_body_loop * w->body_launches[0] +
                        (long long)f.njev * w->body_launches[1] + (long long)f.n_body_lmpar * w->body_launches[2] +
-                       (long long)f.n_body_trial * w->body_launches[3];
+                       (long long)f.n_body_trial * w->body_launches[3] + (long long)f.n_body_corr * w->body_launches[4];
     }
     double ss = 0.0;
     for (int i = 0; i < kRedBlocks; ++i) ss += part[i];

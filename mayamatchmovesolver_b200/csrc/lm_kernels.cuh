@@ -1494,7 +1494,7 @@ __global__ void __launch_bounds__(1024) k_backward_s(LmDims d, const double *__r
 // substitution in one warp); every CTA must be resident (cooperative launch, the host falls
 // back to the single-CTA kernels when the grid does not fit).  Flags carry an epoch so they
 // need no reset between launches; the epoch counter lives in device memory (advanced by
-// k_ctrl_lmpar) so that the launch arguments are the same every time -- the launches can
+// k_ctrl_lmpar_decide / k_ctrl_lmpar_update) so that the launch arguments are the same every time -- the launches can
 // be replayed from a CUDA graph.  A CTA only ever waits for CTAs of lower blockIdx, so
 // the plain (non-cooperative) launch used inside graph bodies cannot deadlock under
 // in-order block dispatch either.

@@ -32,6 +32,8 @@ struct LmState {
     double parl, paru, fp, dxnorm, gnorm_scaled, qnorm2;
     int lmpar_iter;         // 0 = Gauss-Newton probe pending
     int lmpar_done;
+    int lmpar_corr;         // the lmpar step goes on: the Newton-correction solve is wanted
+    double dx2;             // ||D p||^2 of the current lmpar step
     int chol_fail;          // a pivot was <= 0 in the current factorisation
     int chol_fail_total;
     // reduced-side (replicated) parts of sums whose eliminated-side parts are all-reduced
@@ -42,7 +44,7 @@ struct LmState {
     double init_avg;                   // err_avg of the scene's own values (acceptOnlyBetter)
     // device-resident loop (CUDA graph with conditional nodes): how often each body ran,
     // and the device time of each phase (%globaltimer, ns) stamped at the phase boundaries
-    int n_body_jac, n_body_lmpar, n_body_trial, n_body_loop;
+    int n_body_jac, n_body_lmpar, n_body_trial, n_body_loop, n_body_corr;
     int cancelled;                     // the host's cancel flag was seen set
     int dataflow_timeout;              // a tile of the SYRK never arrived at the Cholesky running beside it
     unsigned long long t_mark, t_jac_ns, t_lin_ns, t_func_ns;
