@@ -61,10 +61,13 @@ NcclApi *nccl_api() {
 //                      counters (advanced by the kernels themselves, so a replayed graph works);
 //                      error word
 //   small slots        [parity 2][rank 8][kPeerSmall doubles]: contributions to small all-reduces
-//   big buffer         the in-place operand of the big all-reduce (packed triangle of S)
+//   big buffer         the in-place operand of the big all-reduce (packed triangle of S), or the ranks'
+//                      partial tiles of the reduced system (PeerBig)
+//   tile flags         [parity 2][source rank 8][kPeerFlagTiles] words (PeerBig::flags)
 constexpr int kPeerMax = 8;
 constexpr size_t kPeerSmall = 64 * 1024;   // doubles per slot
 constexpr size_t kPeerHeader = 4096;
+constexpr size_t kPeerFlagBytes = (size_t)2 * 8 * kPeerFlagTiles * 4;   // tile flags of a sharded factorisation (PeerBig::flags)
 struct PeerView {
     char *base[kPeerMax];
     int rank, world;
@@ -172,7 +175,7 @@ struct NcclComm : Comm {
         if (const char *m = getenv("MMB_PEER_ARENA_MB")) big_mb = (size_t)std::max(1, atoi(m));
         big_doubles = big_mb * 1024 * 1024 / 8;
         const size_t small_bytes = 2 * kPeerMax * kPeerSmall * 8;
-        const size_t bytes = kPeerHeader + small_bytes + big_doubles * 8;
+        const size_t bytes = kPeerHeader + small_bytes + big_doubles * 8 + kPeerFlagBytes;   // flag region after the big buffer
         NcclApi *api = nccl_api();
         double ok = 1.0;
         cudaIpcMemHandle_t mine{}, all[kPeerMax];
@@ -216,6 +219,16 @@ struct NcclComm : Comm {
         return (peer_ok && count <= big_doubles) ? reinterpret_cast<double *>(view.base[rank] + view.big_off) : nullptr;
     }
     bool capturable(size_t max_small) const override { return peer_ok && max_small <= kPeerSmall; }
+    bool peer_big(PeerBig *out) override {
+        if (!peer_ok) return false;
+        for (int q = 0; q < 8; ++q) {
+            out->base[q] = q < world ? reinterpret_cast<double *>(view.base[q] + view.big_off) : nullptr;
+            out->flags[q] = q < world ? reinterpret_cast<unsigned *>(view.base[q] + view.big_off + big_doubles * 8) : nullptr;
+        }
+        out->rank = rank; out->world = world; out->doubles = big_doubles;
+        out->seq = reinterpret_cast<unsigned *>(view.base[rank]) + 258;   // header word at offset 1032
+        return true;
+    }
     bool peer_error() override {
         if (!peer_ok) return false;
         unsigned err = 0;

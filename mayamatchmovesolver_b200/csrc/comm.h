@@ -19,6 +19,17 @@
 
 namespace mmb {
 
+// every rank's peer-mapped big buffer as one rank sees them (base[rank] is its own), and a sequence
+// word in this rank's arena that device code may advance (all ranks advance theirs alike)
+struct PeerBig {
+    double *base[8];
+    unsigned *flags[8];     // a reserved flag region at the end of every arena: [2][8][kPeerFlagTiles] words
+    int rank, world;
+    size_t doubles;         // usable doubles of a big buffer (the flag region is not part of them)
+    unsigned *seq;
+};
+constexpr int kPeerFlagTiles = 2080;   // lower-triangle tiles of a 64 x 64 block grid
+
 struct Comm {
     int rank = 0, world = 1;
     virtual ~Comm() {}
@@ -35,6 +46,8 @@ struct Comm {
     // can every all-reduce of a solve (big: the peer buffer; small: up to max_small doubles) be
     // captured into a CUDA graph?
     virtual bool capturable(size_t max_small) const { (void)max_small; return false; }
+    // the big buffers of all ranks, for kernels that exchange through them directly (false: no peer path)
+    virtual bool peer_big(PeerBig *out) { (void)out; return false; }
     // a barrier of the last solve timed out (ranks out of step): results are not to be trusted
     virtual bool peer_error() { return false; }
 };

@@ -104,6 +104,9 @@ struct LmWorkspace {
     cudaStream_t side = nullptr; // the stream of that Cholesky
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int chol_beside = 0;         // CTAs of the Cholesky launched beside the SYRK (0: one after the other)
+    PeerTiles ptiles{};          // sharded solve: partial tiles through the peer arenas (world == 0: packed all-reduce instead)
+    unsigned *peer_seq = nullptr; // this rank's factorisation sequence number (in its arena)
+    bool ptiles_decided = false;
     bool chol_tiles = true;      // one-launch tile-dataflow Cholesky (MMB_CHOL=steps: two launches per block step)
     double *h_stage = nullptr;   // pinned staging: [max(2 n, kRedBlocks + n)]
     int *h_cancel = nullptr;     // pinned, mapped: set by mmb_request_cancel, polled by the loop-head kernel
@@ -755,6 +758,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
     return MMB_OK;
 }
 
+__global__ void k_peer_seq_next(unsigned *seq) { *seq += 1u; }
+
 // ---- enqueue helpers ------------------------------------------------------------------------
 #define LAUNCH_CHECK()                                  \
     do {                                                \
@@ -938,16 +943,21 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
             k_block_factor<<<d.F, 128, sm, s>>>(d, w->st, w->U, w->gE, w->W, w->diag, w->i2p, w->Lf, w->Y);
         LAUNCH_CHECK();
     }
+    // (graph bodies only: the two launches are independent branches there.  Launched from the host,
+    // two streams may share one hardware queue, and the queue entry that signals the end of the
+    // Cholesky would hold back the SYRK launch behind it -- the SYRK the Cholesky is waiting for.)
+    const bool peer_tiles = sharded && w->ptiles.world > 0;
+    const bool beside = w->chol_beside > 0 && (!sharded || peer_tiles) && d.KE && w->capturing;
     {
         const size_t tot = (size_t)d.NSP * d.NSP;
         k_schur_init<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(d, w->st, w->V, w->diag, w->i2p, w->S, sharded ? 0 : 1);
         LAUNCH_CHECK();
+        if (beside && peer_tiles) {   // a new epoch for the tile flags (every rank counts alike)
+            k_peer_seq_next<<<1, 1, 0, s>>>(w->peer_seq);
+            LAUNCH_CHECK();
+        }
     }
     const int nb = d.NSP / 64;
-    // (graph bodies only: the two launches are independent branches there.  Launched from the host,
-    // two streams may share one hardware queue, and the queue entry that signals the end of the
-    // Cholesky would hold back the SYRK launch behind it -- the SYRK the Cholesky is waiting for.)
-    const bool beside = w->chol_beside > 0 && !sharded && d.KE && w->capturing;
     if (d.KE) {
         const int tiles = nb * (nb + 1) / 2;
         // 300 tiles on 148 SMs leave some SMs with 3 CTAs and most with 2 (measured 0.72 ms); 16 x
@@ -980,19 +990,23 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
             // CTAs -- was measured slower: the chain's FP64 operations queue behind the SYRK's DMMAs.)
             MMB_CUDA_CHECK(cudaEventRecord(w->ev_fork, s));
             MMB_CUDA_CHECK(cudaStreamWaitEvent(w->side, w->ev_fork, 0));
+            PeerTiles ptc{};
+            if (peer_tiles) ptc = w->ptiles;
             k_chol_tiles<1><<<std::min(w->chol_beside, tiles), 256, kCholTilesSmem, w->side>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv,
-                                                                                          (const int *)w->syrk_ready);
+                                                                                          peer_tiles ? (const int *)nullptr : (const int *)w->syrk_ready, ptc);
             LAUNCH_CHECK();
             MMB_CUDA_CHECK(cudaEventRecord(w->ev_join, w->side));
         }
         // (test hook: flags that never come, to exercise the bounded wait and the fall-back)
-        int *ready = (beside && !getenv("MMB_TEST_DROP_SYRK_FLAGS")) ? w->syrk_ready : nullptr;
+        int *ready = (beside && !peer_tiles && !getenv("MMB_TEST_DROP_SYRK_FLAGS")) ? w->syrk_ready : nullptr;
         const int *ectr = w->wave_ctr;
-        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S, ready, ectr));
+        PeerTiles pts{};
+        if (beside && peer_tiles) pts = w->ptiles;
+        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S, ready, ectr, pts));
         LAUNCH_CHECK();
         if (beside) MMB_CUDA_CHECK(cudaStreamWaitEvent(s, w->ev_join, 0));
     }
-    if (sharded) {
+    if (sharded && !beside) {
         // the one data-path collective of the solve: rows 0..ns of the reduced system
         // (lower triangle + right-hand side row), summed over the frame shards
         // (lower triangle by 64-wide block rows + right-hand side row), packed into one buffer:
@@ -1011,9 +1025,9 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         static int chol_minb = -1;
         if (chol_minb < 0) { const char *e = getenv("MMB_CHOL_MINB"); chol_minb = e ? atoi(e) : 0; }
         if (nb > 64 || chol_minb == 2)
-            k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr);
+            k_chol_tiles<2><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr, PeerTiles{});
         else
-            k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr);
+            k_chol_tiles<1><<<nb * (nb + 1) / 2, 256, kCholTilesSmem, s>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr, PeerTiles{});
         LAUNCH_CHECK();
     } else {
         for (int kb = 0; kb < nb; ++kb) {
@@ -1414,6 +1428,29 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     if (sharded_graph < 0) { const char *e = getenv("MMB_LM_GRAPH_SHARDED"); sharded_graph = e ? atoi(e) : 1; }
     const bool graph_capable = !sharded || (sharded_graph && peer_graph);
     bool use_graph = graph_mode && graph_capable && !w->profile && !w->graph_failed;
+    if (sharded && !w->ptiles_decided) {
+        // Reduced system exchanged tile by tile inside the factorisation (PeerTiles) instead of packed
+        // and all-reduced: only if every rank can (first solve of a handle; one small collective).
+        w->ptiles_decided = true;
+        static int tiles_mode = -1;
+        if (tiles_mode < 0) { const char *e = getenv("MMB_PEER_TILES"); tiles_mode = e ? atoi(e) : 1; }
+        const int nbt = w->d.NSP / 64, T = nbt * (nbt + 1) / 2;
+        PeerBig pbg{};
+        const bool can = tiles_mode && use_graph && w->chol_beside > 0 && w->d.KE > 0 && T <= kPeerFlagTiles &&
+                         p->comm->peer_big(&pbg) && (size_t)2 * T * 4096 <= pbg.doubles;
+        double cannot = can ? 0.0 : 1.0;
+        MMB_CUDA_CHECK(cudaMemcpyAsync(w->scal, &cannot, sizeof(double), cudaMemcpyHostToDevice, p->stream));
+        if ((st = all_reduce(p, w->scal, 1, true)) != MMB_OK) return st;
+        MMB_CUDA_CHECK(cudaMemcpyAsync(&cannot, w->scal, sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+        MMB_CUDA_CHECK(cudaStreamSynchronize(p->stream));
+        if (cannot == 0.0) {
+            PeerTiles &t = w->ptiles;
+            t.world = pbg.world; t.rank = pbg.rank; t.ntiles = T; t.maxtiles = kPeerFlagTiles;
+            for (int q = 0; q < 8; ++q) { t.tiles[q] = pbg.base[q]; t.flags[q] = pbg.flags[q]; }
+            t.seq = pbg.seq; t.diag = w->diag; t.i2p = w->i2p;
+            w->peer_seq = pbg.seq;
+        }
+    }
     if (use_graph && !w->graph_exec) {
         const auto tg0 = clk::now();
         mmb_status gs = lm_graph_build(p, 0);
@@ -1459,14 +1496,14 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
     if (f.dataflow_timeout) {
         // never seen; if the two branches of the graph were ever not run side by side, go back to
         // one after the other for the rest of this handle's life and solve again
-        if (w->chol_beside > 0 && use_graph) {
+        if (w->chol_beside > 0 && use_graph && !sharded) {
             w->chol_beside = 0;
             cudaGraphExecDestroy(w->graph_exec); w->graph_exec = nullptr;
             cudaGraphDestroy(w->graph); w->graph = nullptr;
             return lm_solve(p, res, x_out, attr_out, dist_out);
         }
         set_last_error("Cholesky beside the SYRK: a tile of the reduced system never arrived");
-        return MMB_ERR_CUDA;
+        return sharded ? MMB_ERR_COMM : MMB_ERR_CUDA;
     }
     if (f.cancelled) res->user_interrupted = 1;
     if (use_graph) {

@@ -694,13 +694,29 @@ __device__ __forceinline__ void tile_index(int t, int &bi, int &bj) {
 // shared memory and the cluster folds them through distributed shared memory in rank order,
 // each CTA owning a slice of the tile -- a fixed summation order (two runs give the same bits,
 // where the FP atomics of the earlier version did not) and no extra trip through L2.
+// Sharded solve with the Cholesky beside the SYRK: the reduced system is the sum over the ranks of
+// their partial tiles.  Every rank's SYRK leaves its partial tile in its own peer-mapped arena
+// (two buffers, alternating with the factorisation sequence number) and pushes the tile's flag
+// into every rank's arena; every rank's Cholesky, when it comes to a tile, waits for the flags of
+// all ranks in its own arena and adds the ranks' partial tiles in rank order (peer loads over
+// NVLink) -- the all-reduce of the reduced system, tile by tile, inside the factorisation.
+struct PeerTiles {
+    int world, rank;           // world == 0: not in use
+    int ntiles, maxtiles;      // tiles of this system; tiles a flag array has room for
+    double *tiles[8];          // every rank's [2][ntiles][64 x 64]
+    unsigned *flags[8];        // every rank's [2][8 source ranks][maxtiles]
+    const unsigned *seq;       // this rank's factorisation sequence number: the epoch of its flags
+    const double *diag;        // damping of the diagonal (added once, after the sum)
+    const int32_t *i2p;
+};
+
 // Tiles are numbered column by column, as k_chol_tiles numbers them, and (ready != nullptr) each
 // finished tile is published with the epoch the factorisation of this step waits for
 // (ready[bj * nb + bi] = *epoch_ctr + 1): the tile-dataflow Cholesky runs BESIDE this kernel and
 // picks every tile up as soon as it is complete, instead of starting when the last one is.
 constexpr int kSyrkKT = 16;
 __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S,
-                                                    int *ready, const int *epoch_ctr) {
+                                                    int *ready, const int *epoch_ctr, PeerTiles pt) {
     __shared__ __align__(16) double smem[4 * kSyrkKT * kTS];   // sA[2], sB[2]; reused as the 64x64 partial tile
     double *sA[2] = {smem, smem + kSyrkKT * kTS};
     double *sB[2] = {smem + 2 * kSyrkKT * kTS, smem + 3 * kSyrkKT * kTS};
@@ -753,7 +769,36 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
         if (ks + 1 < ks1) commit(buf ^ 1);
         __syncthreads();
     }
+    // peer mode: the result tile (S - Y^T Y of this rank) goes to this rank's arena, S stays as it is
+    unsigned pepoch = 0;
+    double *ptile = nullptr;
+    if (pt.world) {
+        pepoch = __ldcg(pt.seq);
+        ptile = pt.tiles[pt.rank] + ((size_t)(pepoch & 1u) * pt.ntiles + blockIdx.x) * 4096;
+    }
+    auto peer_publish = [&]() {   // one thread, after every writer of the tile has fenced and arrived
+        __threadfence_system();
+        for (int q = 0; q < pt.world; ++q) {
+            unsigned *f = pt.flags[q] + ((size_t)(pepoch & 1u) * 8 + pt.rank) * pt.maxtiles + blockIdx.x;
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(pepoch) : "memory");
+        }
+    };
     if (gridDim.y == 1) {
+        if (pt.world) {
+            const int g = lane >> 2, q = lane & 3;
+#pragma unroll
+            for (int ti = 0; ti < 4; ++ti)
+#pragma unroll
+                for (int tj = 0; tj < 4; ++tj) {
+                    const int r = wr * 32 + ti * 8 + g, c = wc * 32 + tj * 8 + q * 2;
+                    const double2 v = *reinterpret_cast<const double2 *>(&S[(size_t)(bi * 64 + r) * d.NSP + bj * 64 + c]);
+                    *reinterpret_cast<double2 *>(&ptile[r * 64 + c]) = make_double2(v.x - acc[ti][tj][0], v.y - acc[ti][tj][1]);
+                }
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x == 0) peer_publish();
+            return;
+        }
         tile_store_sub(S, d.NSP, bi, bj, wr, wc, lane, acc);
         if (ready) {
             __threadfence();
@@ -792,13 +837,17 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
             sum += x;
         }
         const int ti = v >> 3, tj = (v >> 1) & 3, h = v & 1;
-        const int row = bi * 64 + wr * 32 + ti * 8 + g, col = bj * 64 + wc * 32 + tj * 8 + q * 2 + h;
-        S[(size_t)row * d.NSP + col] -= sum;
+        const int rt = wr * 32 + ti * 8 + g, ct = wc * 32 + tj * 8 + q * 2 + h;
+        const size_t at = (size_t)(bi * 64 + rt) * d.NSP + bj * 64 + ct;
+        if (pt.world) ptile[rt * 64 + ct] = S[at] - sum;
+        else S[at] -= sum;
     }
     // nobody leaves while a peer may still read its shared memory; after the barrier every rank's
     // slice of the tile is written (fenced to the device before the arrival), so rank 0 publishes
     if (ready) __threadfence();
+    if (pt.world) __threadfence_system();
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (pt.world && rank == 0 && threadIdx.x == 0) peer_publish();
     if (ready && rank == 0 && threadIdx.x == 0) {
         const int epoch = __ldcg(epoch_ctr) + 1;
         __threadfence();
@@ -1053,7 +1102,8 @@ __device__ __forceinline__ unsigned long long gtimer() {
 // S is read once the SYRK has published it (see k_schur_syrk).
 template <int MINB>
 __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
-                                                    const int *epoch_ctr, double *__restrict__ Dinv, const int *syrk_ready) {
+                                                    const int *epoch_ctr, double *__restrict__ Dinv, const int *syrk_ready,
+                                                    PeerTiles pt) {
     extern __shared__ __align__(16) double sm[];
     double *sA = sm;                 // L(i,k) during phase A; afterwards T (stride kCS)
     double *sB = sm + 64 * kOS;      // L(j,k) during phase A; afterwards X (stride kCS)
@@ -1097,6 +1147,44 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     // ---- A: left-looking update on the tensor cores ----
     double acc[2][4][2];
     double2 sij[2][4];   // this tile of S, fetched before the waits: off the critical path
+    if (pt.world) {
+        // sharded: the tile is the sum of the ranks' partial tiles, each there once its flag is
+        const unsigned pep = __ldcg(pt.seq);
+        const unsigned pb = pep & 1u;
+        if (tid < pt.world) {
+            const unsigned *f = pt.flags[pt.rank] + ((size_t)pb * 8 + tid) * pt.maxtiles + tile;
+            unsigned v;
+            const unsigned long long t0 = gtimer();
+            unsigned spins = 0;
+            for (;;) {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                if ((int)(v - pep) >= 0) break;
+                if ((++spins & 1023u) == 0u && (gtimer() - t0 > 4000000000ull || *(volatile int *)&st->dataflow_timeout)) { atomicExch(&st->dataflow_timeout, 1); break; }
+            }
+        }
+        __syncthreads();
+        const double par = st->par_cur;
+#pragma unroll
+        for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                acc[a][b][0] = acc[a][b][1] = 0.0;
+                const int r = wr * 16 + a * 8 + g, c = wc * 32 + b * 8 + q * 2;
+                const size_t at = ((size_t)pb * pt.ntiles + tile) * 4096 + r * 64 + c;
+                double2 v = __ldcg(reinterpret_cast<const double2 *>(pt.tiles[0] + at));
+                for (int rk = 1; rk < pt.world; ++rk) {
+                    const double2 u = __ldcg(reinterpret_cast<const double2 *>(pt.tiles[rk] + at));
+                    v.x += u.x; v.y += u.y;
+                }
+                if (diag && (r == c || r == c + 1)) {   // damping / padding of the diagonal, after the sum
+                    const int R = i * 64 + r;
+                    double &x = (r == c) ? v.x : v.y;
+                    if (R < d.ns) { const double dd = pt.diag[pt.i2p[d.KE + R]]; x += par * dd * dd; }
+                    else x = (R == d.ns) ? 0.0 : 1.0;
+                }
+                sij[a][b] = v;
+            }
+    } else {
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
@@ -1105,6 +1193,7 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
             const int r = wr * 16 + a * 8 + g, c = wc * 32 + b * 8 + q * 2;
             sij[a][b] = __ldcg(reinterpret_cast<const double2 *>(&S[(size_t)(i * 64 + r) * ld + j * 64 + c]));
         }
+    }
     for (int k = 0; k < j; ++k) {
         if (tid == 0) {
             int v;
