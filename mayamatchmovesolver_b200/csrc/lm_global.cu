@@ -719,6 +719,8 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
             CKW(A.alloc(&w->syrk_ready, nt));
             CKW(cudaMemsetAsync(w->syrk_ready, 0, sizeof(int) * nt, p->stream));
             CKW(cudaFuncSetAttribute(k_chol_tiles<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
+            CKW(cudaFuncSetAttribute(k_chol_tiles<1, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
+            CKW(cudaFuncSetAttribute(k_chol_tiles<1, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             CKW(cudaFuncSetAttribute(k_chol_tiles<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCholTilesSmem));
             const char *e = getenv("MMB_CHOL");
             w->chol_tiles = !(e && !strcmp(e, "steps"));
@@ -972,7 +974,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         cfg.gridDim = dim3(tiles, ksplit);
         cfg.blockDim = dim3(128);
         static int syrk_pad = -1;   // experiment: cap the SYRK's residency with unused dynamic shared memory
-        if (syrk_pad < 0) { const char *e = getenv("MMB_SYRK_PAD_KB"); syrk_pad = e ? atoi(e) : 0; if (syrk_pad) cudaFuncSetAttribute(k_schur_syrk, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_pad * 1024); }
+        if (syrk_pad < 0) { const char *e = getenv("MMB_SYRK_PAD_KB"); syrk_pad = e ? atoi(e) : 0; if (syrk_pad) cudaFuncSetAttribute(k_schur_syrk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_pad * 1024); }
         cfg.dynamicSmemBytes = (size_t)syrk_pad * 1024;
         cfg.stream = s;
         cudaLaunchAttribute attr[1];
@@ -990,19 +992,22 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
             // CTAs -- was measured slower: the chain's FP64 operations queue behind the SYRK's DMMAs.)
             MMB_CUDA_CHECK(cudaEventRecord(w->ev_fork, s));
             MMB_CUDA_CHECK(cudaStreamWaitEvent(w->side, w->ev_fork, 0));
-            PeerTiles ptc{};
-            if (peer_tiles) ptc = w->ptiles;
-            k_chol_tiles<1><<<std::min(w->chol_beside, tiles), 256, kCholTilesSmem, w->side>>>(d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv,
-                                                                                          peer_tiles ? (const int *)nullptr : (const int *)w->syrk_ready, ptc);
+            if (peer_tiles)
+                k_chol_tiles<1, true, true><<<std::min(w->chol_beside, tiles), 256, kCholTilesSmem, w->side>>>(
+                    d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)nullptr, w->ptiles);
+            else
+                k_chol_tiles<1, true, false><<<std::min(w->chol_beside, tiles), 256, kCholTilesSmem, w->side>>>(
+                    d, w->st, w->S, w->tile_flags, w->wave_ctr, w->Dinv, (const int *)w->syrk_ready, PeerTiles{});
             LAUNCH_CHECK();
             MMB_CUDA_CHECK(cudaEventRecord(w->ev_join, w->side));
         }
         // (test hook: flags that never come, to exercise the bounded wait and the fall-back)
         int *ready = (beside && !peer_tiles && !getenv("MMB_TEST_DROP_SYRK_FLAGS")) ? w->syrk_ready : nullptr;
         const int *ectr = w->wave_ctr;
-        PeerTiles pts{};
-        if (beside && peer_tiles) pts = w->ptiles;
-        MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk, d, (const double *)w->Y, w->S, ready, ectr, pts));
+        if (beside && peer_tiles)
+            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk<true>, d, (const double *)w->Y, w->S, ready, ectr, w->ptiles));
+        else
+            MMB_CUDA_CHECK(cudaLaunchKernelEx(&cfg, k_schur_syrk<false>, d, (const double *)w->Y, w->S, ready, ectr, PeerTiles{}));
         LAUNCH_CHECK();
         if (beside) MMB_CUDA_CHECK(cudaStreamWaitEvent(s, w->ev_join, 0));
     }
@@ -1436,8 +1441,13 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
         if (tiles_mode < 0) { const char *e = getenv("MMB_PEER_TILES"); tiles_mode = e ? atoi(e) : 1; }
         const int nbt = w->d.NSP / 64, T = nbt * (nbt + 1) / 2;
         PeerBig pbg{};
+        // every rank stores its partial tiles into every arena: the traffic grows with the number of
+        // ranks.  Linear algebra of a 15-iteration cfg3-per-GPU solve, tiles vs packed all-reduce:
+        // 23.9 vs 27.5 ms at 2 GPUs, 25.3 vs 26.2 ms at 8 -- where the rest of the step lost more than
+        // that to the 77 MB per trial and rank on the wire; so up to 4 ranks (MMB_PEER_TILES=2: any).
         const bool can = tiles_mode && use_graph && w->chol_beside > 0 && w->d.KE > 0 && T <= kPeerFlagTiles &&
-                         p->comm->peer_big(&pbg) && (size_t)2 * T * 4096 <= pbg.doubles;
+                         p->comm->peer_big(&pbg) && (pbg.world <= 4 || tiles_mode >= 2) &&
+                         (size_t)2 * pbg.world * T * 4096 <= pbg.doubles;
         double cannot = can ? 0.0 : 1.0;
         MMB_CUDA_CHECK(cudaMemcpyAsync(w->scal, &cannot, sizeof(double), cudaMemcpyHostToDevice, p->stream));
         if ((st = all_reduce(p, w->scal, 1, true)) != MMB_OK) return st;
@@ -1447,6 +1457,7 @@ mmb_status lm_solve(DeviceProblem *p, mmb_result *res, double *x_out, double *at
             PeerTiles &t = w->ptiles;
             t.world = pbg.world; t.rank = pbg.rank; t.ntiles = T; t.maxtiles = kPeerFlagTiles;
             for (int q = 0; q < 8; ++q) { t.tiles[q] = pbg.base[q]; t.flags[q] = pbg.flags[q]; }
+            t.my_tiles = pbg.base[pbg.rank]; t.my_flags = pbg.flags[pbg.rank];
             t.seq = pbg.seq; t.diag = w->diag; t.i2p = w->i2p;
             w->peer_seq = pbg.seq;
         }

@@ -695,16 +695,20 @@ __device__ __forceinline__ void tile_index(int t, int &bi, int &bj) {
 // each CTA owning a slice of the tile -- a fixed summation order (two runs give the same bits,
 // where the FP atomics of the earlier version did not) and no extra trip through L2.
 // Sharded solve with the Cholesky beside the SYRK: the reduced system is the sum over the ranks of
-// their partial tiles.  Every rank's SYRK leaves its partial tile in its own peer-mapped arena
-// (two buffers, alternating with the factorisation sequence number) and pushes the tile's flag
-// into every rank's arena; every rank's Cholesky, when it comes to a tile, waits for the flags of
-// all ranks in its own arena and adds the ranks' partial tiles in rank order (peer loads over
-// NVLink) -- the all-reduce of the reduced system, tile by tile, inside the factorisation.
+// their partial tiles.  Every rank's SYRK stores its partial tile into EVERY rank's peer-mapped
+// arena (posted stores over NVLink; two buffers, alternating with the factorisation sequence
+// number) and then the tile's flag; every rank's Cholesky, when it comes to a tile, waits for the
+// flags of all ranks and adds the ranks' partial tiles in rank order, all from its own memory -- the
+// all-reduce of the reduced system, tile by tile, inside the factorisation, with no remote load on
+// the factorisation's chain.  (Pulling the partial tiles from the peers' arenas instead was
+// measured: at 8 GPUs the serial remote loads cost more than the packed all-reduce they replaced.)
 struct PeerTiles {
     int world, rank;           // world == 0: not in use
     int ntiles, maxtiles;      // tiles of this system; tiles a flag array has room for
-    double *tiles[8];          // every rank's [2][ntiles][64 x 64]
+    double *tiles[8];          // every rank's [2][world source ranks][ntiles][64 x 64]
     unsigned *flags[8];        // every rank's [2][8 source ranks][maxtiles]
+    double *my_tiles;          // = tiles[rank], flags[rank] (no dynamic indexing of the parameter arrays)
+    unsigned *my_flags;
     const unsigned *seq;       // this rank's factorisation sequence number: the epoch of its flags
     const double *diag;        // damping of the diagonal (added once, after the sum)
     const int32_t *i2p;
@@ -715,8 +719,9 @@ struct PeerTiles {
 // (ready[bj * nb + bi] = *epoch_ctr + 1): the tile-dataflow Cholesky runs BESIDE this kernel and
 // picks every tile up as soon as it is complete, instead of starting when the last one is.
 constexpr int kSyrkKT = 16;
-__global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S,
-                                                    int *ready, const int *epoch_ctr, PeerTiles pt) {
+template <bool PEER>
+__global__ void __launch_bounds__(128, 4) k_schur_syrk(LmDims d, const double *__restrict__ Y, double *__restrict__ S,
+                                                       int *ready, const int *epoch_ctr, PeerTiles pt) {
     __shared__ __align__(16) double smem[4 * kSyrkKT * kTS];   // sA[2], sB[2]; reused as the 64x64 partial tile
     double *sA[2] = {smem, smem + kSyrkKT * kTS};
     double *sB[2] = {smem + 2 * kSyrkKT * kTS, smem + 3 * kSyrkKT * kTS};
@@ -771,20 +776,22 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     }
     // peer mode: the result tile (S - Y^T Y of this rank) goes to this rank's arena, S stays as it is
     unsigned pepoch = 0;
-    double *ptile = nullptr;
-    if (pt.world) {
+    size_t pslot = 0;   // this rank's slot of the tile in every arena
+    if (PEER) {
         pepoch = __ldcg(pt.seq);
-        ptile = pt.tiles[pt.rank] + ((size_t)(pepoch & 1u) * pt.ntiles + blockIdx.x) * 4096;
+        pslot = (((size_t)(pepoch & 1u) * pt.world + pt.rank) * pt.ntiles + blockIdx.x) * 4096;
     }
     auto peer_publish = [&]() {   // one thread, after every writer of the tile has fenced and arrived
         __threadfence_system();
-        for (int q = 0; q < pt.world; ++q) {
-            unsigned *f = pt.flags[q] + ((size_t)(pepoch & 1u) * 8 + pt.rank) * pt.maxtiles + blockIdx.x;
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(pepoch) : "memory");
-        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            if (q < pt.world) {
+                unsigned *f = pt.flags[q] + ((size_t)(pepoch & 1u) * 8 + pt.rank) * pt.maxtiles + blockIdx.x;
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(pepoch) : "memory");
+            }
     };
     if (gridDim.y == 1) {
-        if (pt.world) {
+        if (PEER) {
             const int g = lane >> 2, q = lane & 3;
 #pragma unroll
             for (int ti = 0; ti < 4; ++ti)
@@ -792,7 +799,10 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
                 for (int tj = 0; tj < 4; ++tj) {
                     const int r = wr * 32 + ti * 8 + g, c = wc * 32 + tj * 8 + q * 2;
                     const double2 v = *reinterpret_cast<const double2 *>(&S[(size_t)(bi * 64 + r) * d.NSP + bj * 64 + c]);
-                    *reinterpret_cast<double2 *>(&ptile[r * 64 + c]) = make_double2(v.x - acc[ti][tj][0], v.y - acc[ti][tj][1]);
+                    const double2 o = make_double2(v.x - acc[ti][tj][0], v.y - acc[ti][tj][1]);
+#pragma unroll
+                    for (int z = 0; z < 8; ++z)
+                        if (z < pt.world) *reinterpret_cast<double2 *>(pt.tiles[z] + pslot + r * 64 + c) = o;
                 }
             __threadfence_system();
             __syncthreads();
@@ -800,7 +810,7 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
             return;
         }
         tile_store_sub(S, d.NSP, bi, bj, wr, wc, lane, acc);
-        if (ready) {
+        if (!PEER && ready) {
             __threadfence();
             __syncthreads();
             if (threadIdx.x == 0) {
@@ -827,28 +837,35 @@ __global__ void __launch_bounds__(128) k_schur_syrk(LmDims d, const double *__re
     const int v0 = (int)rank * per_rank;
     const unsigned base = (unsigned)__cvta_generic_to_shared(smem);
     const int g = lane >> 2, q = lane & 3;
-    for (int v = v0; v < v0 + per_rank; ++v) {
-        double sum = 0.0;
+    for (int v = v0; v < v0 + per_rank; v += 2) {   // (v, v + 1): the two adjacent columns of one accumulator pair
+        double sum0 = 0.0, sum1 = 0.0;
         for (unsigned r = 0; r < nrank; ++r) {
             unsigned remote;
             asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + (unsigned)((v * 128 + threadIdx.x) * 8)), "r"(r));
-            double x;
-            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(x) : "r"(remote));
-            sum += x;
+            double x0, x1;
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(x0) : "r"(remote));
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(x1) : "r"(remote + 128u * 8u));
+            sum0 += x0; sum1 += x1;
         }
-        const int ti = v >> 3, tj = (v >> 1) & 3, h = v & 1;
-        const int rt = wr * 32 + ti * 8 + g, ct = wc * 32 + tj * 8 + q * 2 + h;
-        const size_t at = (size_t)(bi * 64 + rt) * d.NSP + bj * 64 + ct;
-        if (pt.world) ptile[rt * 64 + ct] = S[at] - sum;
-        else S[at] -= sum;
+        const int ti = v >> 3, tj = (v >> 1) & 3;
+        const int rt = wr * 32 + ti * 8 + g, ct = wc * 32 + tj * 8 + q * 2;
+        double2 *sp = reinterpret_cast<double2 *>(&S[(size_t)(bi * 64 + rt) * d.NSP + bj * 64 + ct]);
+        const double2 sv = *sp;
+        const double2 o = make_double2(sv.x - sum0, sv.y - sum1);
+        if (PEER) {
+#pragma unroll
+            for (int z = 0; z < 8; ++z)
+                if (z < pt.world) *reinterpret_cast<double2 *>(pt.tiles[z] + pslot + rt * 64 + ct) = o;
+        }
+        else *sp = o;
     }
     // nobody leaves while a peer may still read its shared memory; after the barrier every rank's
     // slice of the tile is written (fenced to the device before the arrival), so rank 0 publishes
-    if (ready) __threadfence();
-    if (pt.world) __threadfence_system();
+    if (!PEER && ready) __threadfence();
+    if (PEER) __threadfence_system();
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-    if (pt.world && rank == 0 && threadIdx.x == 0) peer_publish();
-    if (ready && rank == 0 && threadIdx.x == 0) {
+    if (PEER && rank == 0 && threadIdx.x == 0) peer_publish();
+    if (!PEER && ready && rank == 0 && threadIdx.x == 0) {
         const int epoch = __ldcg(epoch_ctr) + 1;
         __threadfence();
         asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(&ready[bj * nb + bi]), "r"(epoch) : "memory");
@@ -1100,7 +1117,9 @@ __device__ __forceinline__ unsigned long long gtimer() {
 // two CTAs per SM -- for large systems (cfg5: 235 block columns), which are throughput-bound.
 // syrk_ready != nullptr: launched BESIDE k_schur_syrk with a small grid of resident CTAs; a tile of
 // S is read once the SYRK has published it (see k_schur_syrk).
-template <int MINB>
+// PERSIST: a grid smaller than the number of tiles walks them (the launch beside the SYRK);
+// PEER: sharded, the tile of S is the sum of the ranks' partial tiles (PeerTiles).
+template <int MINB, bool PERSIST = false, bool PEER = false>
 __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st, double *__restrict__ S, int *tile_flags,
                                                     const int *epoch_ctr, double *__restrict__ Dinv, const int *syrk_ready,
                                                     PeerTiles pt) {
@@ -1119,8 +1138,9 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     // the launch beside the SYRK) walks the tiles round-robin; a CTA takes its tiles in increasing
     // order and a tile only waits for tiles of lower number (and for the SYRK, which waits for
     // nothing), so the lowest unfinished tile can always proceed.
-    for (int tile = blockIdx.x; tile < nb * (nb + 1) / 2; tile += gridDim.x) {
-    if (tile != (int)blockIdx.x) __syncthreads();   // phase E of the previous tile is done with the shared tiles
+    int tile = blockIdx.x;
+    do {
+    if (PERSIST && tile != (int)blockIdx.x) __syncthreads();   // phase E of the previous tile is done with the shared tiles
     // column-major tile numbering: column j holds nb - j tiles
     int j = 0, t = tile;
     while (t >= nb - j) { t -= nb - j; ++j; }
@@ -1128,7 +1148,7 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     const bool diag = i == j;
     const bool traced = tid == 0 && i <= j + 1 && j < 64;
     unsigned long long *tr = &g_chol_trace[(j * 2 + (diag ? 0 : 1)) * 6];
-    if (syrk_ready) {
+    if (PERSIST && !PEER && syrk_ready) {
         // this tile of S is complete when the SYRK has published it (bounded wait: a flag that never
         // comes is reported, not spun on for ever)
         if (tid == 0) {
@@ -1147,12 +1167,12 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     // ---- A: left-looking update on the tensor cores ----
     double acc[2][4][2];
     double2 sij[2][4];   // this tile of S, fetched before the waits: off the critical path
-    if (pt.world) {
+    if (PEER) {
         // sharded: the tile is the sum of the ranks' partial tiles, each there once its flag is
         const unsigned pep = __ldcg(pt.seq);
         const unsigned pb = pep & 1u;
         if (tid < pt.world) {
-            const unsigned *f = pt.flags[pt.rank] + ((size_t)pb * 8 + tid) * pt.maxtiles + tile;
+            const unsigned *f = pt.my_flags + ((size_t)pb * 8 + tid) * pt.maxtiles + tile;
             unsigned v;
             const unsigned long long t0 = gtimer();
             unsigned spins = 0;
@@ -1164,23 +1184,30 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
         }
         __syncthreads();
         const double par = st->par_cur;
+        const double *mine = pt.my_tiles + ((size_t)pb * pt.world * pt.ntiles + tile) * 4096;
+        const size_t rstride = (size_t)pt.ntiles * 4096;   // from one source rank's slot to the next
+#pragma unroll
 #pragma unroll
         for (int a = 0; a < 2; ++a)
 #pragma unroll
             for (int b = 0; b < 4; ++b) {
+                // the fragment from every rank first (independent loads), then the sum in rank order
                 acc[a][b][0] = acc[a][b][1] = 0.0;
                 const int r = wr * 16 + a * 8 + g, c = wc * 32 + b * 8 + q * 2;
-                const size_t at = ((size_t)pb * pt.ntiles + tile) * 4096 + r * 64 + c;
-                double2 v = __ldcg(reinterpret_cast<const double2 *>(pt.tiles[0] + at));
-                for (int rk = 1; rk < pt.world; ++rk) {
-                    const double2 u = __ldcg(reinterpret_cast<const double2 *>(pt.tiles[rk] + at));
-                    v.x += u.x; v.y += u.y;
-                }
+                double2 u[8];
+#pragma unroll
+                for (int rk = 0; rk < 8; ++rk)
+                    if (rk < pt.world) u[rk] = __ldcg(reinterpret_cast<const double2 *>(mine + rk * rstride + r * 64 + c));
+                double2 v = u[0];
+#pragma unroll
+                for (int rk = 1; rk < 8; ++rk)
+                    if (rk < pt.world) { v.x += u[rk].x; v.y += u[rk].y; }
                 if (diag && (r == c || r == c + 1)) {   // damping / padding of the diagonal, after the sum
                     const int R = i * 64 + r;
-                    double &x = (r == c) ? v.x : v.y;
+                    double x = (r == c) ? v.x : v.y;
                     if (R < d.ns) { const double dd = pt.diag[pt.i2p[d.KE + R]]; x += par * dd * dd; }
                     else x = (R == d.ns) ? 0.0 : 1.0;
+                    if (r == c) v.x = x; else v.y = x;
                 }
                 sij[a][b] = v;
             }
@@ -1471,7 +1498,7 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
             out[e] = c <= rr ? X[rr * kCS + c] : 0.0;
         }
     }
-    }   // tiles of this CTA
+    } while (PERSIST && (tile += gridDim.x) < nb * (nb + 1) / 2);   // tiles of this CTA
 }
 
 // ---- triangular solves with L_S (single CTA, 1024 threads) ---------------------------
