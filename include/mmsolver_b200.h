@@ -339,7 +339,7 @@ mmb_status mmb_problem_create_shard_local(const mmb_scene_desc *slice,
 mmb_status mmb_comm_unique_id(uint8_t id[MMB_COMM_ID_BYTES],
                               int32_t local_backend);
 /* collective: every rank of the id calls it (NCCL communicator + CUDA IPC mapping
- * of the ranks' all-reduce arenas, 72 MB of device memory each; MMB_PEER=0 keeps
+ * of the ranks' exchange arenas, 104 MB of device memory each; MMB_PEER=0 keeps
  * NCCL alone, MMB_PEER_ARENA_MB sizes the arena).  Afterwards mmb_solve() on the
  * handle is the sharded global solve; results that describe the whole problem
  * (reason, iteration counts, error_final, error_avg/min/max) are identical on

@@ -172,8 +172,8 @@ struct NcclComm : Comm {
         const char *e = getenv("MMB_PEER");
         if ((e && atoi(e) == 0) || world > kPeerMax || world < 2) return;
         // room for the packed triangle of a mid-size reduced system, or for the partial tiles of a
-        // cfg3-size one from 8 ranks (2 buffers x 8 ranks x 300 tiles x 32 KB = 157 MB)
-        size_t big_mb = 176;
+        // cfg3-size one from 4 ranks (2 buffers x 4 ranks x 300 tiles x 32 KB = 79 MB)
+        size_t big_mb = 96;
         if (const char *m = getenv("MMB_PEER_ARENA_MB")) big_mb = (size_t)std::max(1, atoi(m));
         big_doubles = big_mb * 1024 * 1024 / 8;
         const size_t small_bytes = 2 * kPeerMax * kPeerSmall * 8;
