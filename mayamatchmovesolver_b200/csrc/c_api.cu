@@ -584,6 +584,7 @@ mmb_status mmb_release_cached_memory(int32_t device) {
     cudaMemPool_t pool = nullptr;
     MMB_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, device));
     MMB_CUDA_CHECK(cudaMemPoolTrimTo(pool, 0));
+    host_block_trim();   // the page-locked host blocks of the per-observation arrays
     return MMB_OK;
 }
 

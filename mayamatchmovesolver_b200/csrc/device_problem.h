@@ -29,8 +29,10 @@ const std::string &get_last_error();
 // threshold is raised so that the memory of a destroyed handle is kept for the next one
 // (mmSolver is called once per solver step: create / solve / destroy repeats with the same
 // shapes).  mmb_release_cached_memory() trims the pool.  Uploads are asynchronous copies
-// on the same stream (a pageable source is staged before the call returns, so the caller
-// may free it right away).
+// on the same stream: a pageable source is staged before the call returns (the caller may free
+// it right away); the per-observation arrays of the HostProblem live in page-locked blocks
+// (NoInitAlloc) and go out as plain DMA -- they stay alive until the handle's destructor has
+// synchronised the stream.
 struct DeviceArena {
     std::vector<void *> ptrs;
     size_t bytes = 0;

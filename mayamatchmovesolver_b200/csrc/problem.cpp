@@ -18,8 +18,88 @@
 #include <cmath>
 #include <limits>
 #include <set>
+#include <map>
+#include <mutex>
+
+#ifdef MMB_BUILD   // the library; the test-only host emulation includes this file without CUDA
+#include <cuda_runtime.h>
+#endif
 
 namespace mmb {
+
+// ---- page-locked host blocks for the per-observation arrays (see NoInitAlloc) -------------------
+#ifdef MMB_BUILD
+namespace {
+struct HostBlock { size_t bytes; bool pinned; bool in_use; };
+std::mutex g_hb_mu;
+std::map<void *, HostBlock> g_hb;           // every block handed out or cached
+constexpr size_t kHbMin = 256 * 1024;       // smaller requests: plain malloc, not cached
+constexpr size_t kHbCacheMax = (size_t)1 << 30;   // cached (idle) bytes kept at most
+}  // namespace
+
+void *host_block_acquire(size_t bytes) {
+    if (bytes == 0) bytes = 1;
+    if (bytes < kHbMin) {
+        void *p = std::malloc(bytes);
+        if (!p) throw std::bad_alloc();
+        return p;
+    }
+    {
+        std::lock_guard<std::mutex> lk(g_hb_mu);
+        void *best = nullptr;
+        size_t best_bytes = 0;
+        for (auto &kv : g_hb)
+            if (!kv.second.in_use && kv.second.bytes >= bytes && kv.second.bytes <= 2 * bytes && (!best || kv.second.bytes < best_bytes)) {
+                best = kv.first; best_bytes = kv.second.bytes;
+            }
+        if (best) { g_hb[best].in_use = true; return best; }
+    }
+    void *p = nullptr;
+    bool pinned = true;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        pinned = false;
+        p = std::malloc(bytes);
+        if (!p) throw std::bad_alloc();
+    }
+    std::lock_guard<std::mutex> lk(g_hb_mu);
+    g_hb[p] = HostBlock{bytes, pinned, true};
+    return p;
+}
+
+void host_block_release(void *p) {
+    if (!p) return;
+    bool pinned = false, drop = false;
+    {
+        std::lock_guard<std::mutex> lk(g_hb_mu);
+        auto it = g_hb.find(p);
+        if (it == g_hb.end()) { drop = true; }   // a small (plain malloc) request
+        else {
+            size_t idle = 0;
+            for (auto &kv : g_hb) if (!kv.second.in_use) idle += kv.second.bytes;
+            if (!it->second.pinned || idle + it->second.bytes > kHbCacheMax) { pinned = it->second.pinned; g_hb.erase(it); drop = true; }
+            else it->second.in_use = false;
+        }
+    }
+    if (drop) { if (pinned) cudaFreeHost(p); else std::free(p); }
+}
+
+void host_block_trim() {
+    std::vector<void *> dead;
+    {
+        std::lock_guard<std::mutex> lk(g_hb_mu);
+        for (auto it = g_hb.begin(); it != g_hb.end();)
+            if (!it->second.in_use && it->second.pinned) { dead.push_back(it->first); it = g_hb.erase(it); }
+            else ++it;
+    }
+    for (void *p : dead) cudaFreeHost(p);
+}
+#else
+void *host_block_acquire(size_t bytes) { void *p = std::malloc(bytes ? bytes : 1); if (!p) throw std::bad_alloc(); return p; }
+void host_block_release(void *p) { std::free(p); }
+void host_block_trim() {}
+#endif
 
 double bound_internal_to_external(double value, double xmin, double xmax,
                                   double offset, double scale) {

@@ -27,11 +27,20 @@ namespace mmb {
 // std::vector whose resize() leaves new elements uninitialised: the per-observation arrays
 // (5e5 .. 5e7 entries) are filled right after the resize by several threads, a zero fill by
 // one thread first would only take the page faults serially.
+// Their memory comes from a process-wide cache of page-locked host blocks (host_block_acquire):
+// the upload of a pageable vector is staged by the driver on the calling thread (16 MB at cfg3:
+// 1.3 ms, and more when eight processes do it at once); from a page-locked block it is one
+// asynchronous DMA.  Without a device (host-only entry points) the blocks are plain malloc.
+void *host_block_acquire(size_t bytes);
+void host_block_release(void *p);
+void host_block_trim();   // free the cached blocks (mmb_release_cached_memory)
 template <class T>
 struct NoInitAlloc : std::allocator<T> {
     template <class U> struct rebind { using other = NoInitAlloc<U>; };
     NoInitAlloc() = default;
     template <class U> NoInitAlloc(const NoInitAlloc<U> &) {}
+    T *allocate(size_t n) { return static_cast<T *>(host_block_acquire(n * sizeof(T))); }
+    void deallocate(T *p, size_t) { host_block_release(p); }
     template <class U, class... Args> void construct(U *ptr, Args &&...args) {
         if constexpr (sizeof...(Args) == 0) ::new ((void *)ptr) U;
         else ::new ((void *)ptr) U(std::forward<Args>(args)...);
