@@ -729,7 +729,10 @@ static mmb_status lm_workspace_create(DeviceProblem *p) {
             // 16 / 20 / 24 / 28 / 32 / 40 / 48 CTAs: 23.5 / 21.5 / 21.3 / 21.3 / 21.7 / 22.3 / 23.2 ms.
             const char *eb = getenv("MMB_CHOL_BESIDE");
             w->chol_beside = eb ? atoi(eb) : 24;
-            if (!w->chol_tiles || d.KE == 0 || d.NSP / 64 > 64) w->chol_beside = 0;
+            // chain-bound sizes only: at 47 block columns (8 cameras x 200 frames x 1000 bundles) the
+            // factorisation is throughput-bound, 24 CTAs are too few for it and the sequence is faster
+            // (13.75 vs 14.55 ms of linear algebra for three trials)
+            if (!w->chol_tiles || d.KE == 0 || d.NSP / 64 > 32) w->chol_beside = 0;
             if (w->chol_beside > 0) {
                 int sms = 0;
                 CKW(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, p->device));
