@@ -1117,6 +1117,25 @@ __device__ __forceinline__ unsigned long long gtimer() {
 // two CTAs per SM -- for large systems (cfg5: 235 block columns), which are throughput-bound.
 // syrk_ready != nullptr: launched BESIDE k_schur_syrk with a small grid of resident CTAs; a tile of
 // S is read once the SYRK has published it (see k_schur_syrk).
+// Wait until *f == epoch.  BOUNDED (the walking grid beside the SYRK: its CTAs must all be resident
+// for a tile to find its operands; should the device ever not hold them together, the wait ends
+// after 2 s, LmState.dataflow_timeout is set and the host goes back to one kernel after the other).
+template <bool BOUNDED>
+__device__ __forceinline__ void chol_wait_flag(const int *f, int epoch, LmState *st) {
+    int v;
+    if (!BOUNDED) {
+        do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while (v != epoch);
+        return;
+    }
+    const unsigned long long t0 = gtimer();
+    unsigned spins = 0;
+    for (;;) {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if (v == epoch) return;
+        if ((++spins & 1023u) == 0u && (gtimer() - t0 > 2000000000ull || *(volatile int *)&st->dataflow_timeout)) { atomicExch(&st->dataflow_timeout, 1); return; }
+    }
+}
+
 // PERSIST: a grid smaller than the number of tiles walks them (the launch beside the SYRK);
 // PEER: sharded, the tile of S is the sum of the ranks' partial tiles (PeerTiles).
 template <int MINB, bool PERSIST = false, bool PEER = false>
@@ -1223,10 +1242,9 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     }
     for (int k = 0; k < j; ++k) {
         if (tid == 0) {
-            int v;
             const int *f1 = &flags[k * nb + i], *f2 = &flags[k * nb + j];
-            do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f1) : "memory"); } while (v != epoch);
-            if (!diag) do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f2) : "memory"); } while (v != epoch);
+            chol_wait_flag<PERSIST>(f1, epoch, st);
+            if (!diag) chol_wait_flag<PERSIST>(f2, epoch, st);
             if (traced && k == j - 1) tr[0] = gtimer();
         }
         __syncthreads();  // also: everyone is done with the previous k's operands
@@ -1368,9 +1386,8 @@ __global__ void __launch_bounds__(256, MINB) k_chol_tiles(LmDims d, LmState *st,
     } else {
         // ---- D: X <- X L(j,j)^-T once the diagonal tile is published ----
         if (tid == 0) {
-            int v;
             const int *f = &flags[j * nb + j];
-            do { asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(f) : "memory"); } while (v != epoch);
+            chol_wait_flag<PERSIST>(f, epoch, st);
             if (traced) tr[4] = gtimer();
         }
         __syncthreads();
