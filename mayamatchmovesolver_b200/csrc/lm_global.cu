@@ -976,9 +976,7 @@ static mmb_status enqueue_lmpar_step(DeviceProblem *p) {
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(tiles, ksplit);
         cfg.blockDim = dim3(128);
-        static int syrk_pad = -1;   // experiment: cap the SYRK's residency with unused dynamic shared memory
-        if (syrk_pad < 0) { const char *e = getenv("MMB_SYRK_PAD_KB"); syrk_pad = e ? atoi(e) : 0; if (syrk_pad) cudaFuncSetAttribute(k_schur_syrk<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, syrk_pad * 1024); }
-        cfg.dynamicSmemBytes = (size_t)syrk_pad * 1024;
+        cfg.dynamicSmemBytes = 0;
         cfg.stream = s;
         cudaLaunchAttribute attr[1];
         attr[0].id = cudaLaunchAttributeClusterDimension;
