@@ -407,7 +407,9 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         unsigned hw = std::max(1u, std::thread::hardware_concurrency());
         if (const char *e = getenv("MMB_HOST_THREADS")) hw = (unsigned)std::max(1, atoi(e));
         else if (const char *lw = getenv("LOCAL_WORLD_SIZE")) hw = std::max(1u, hw / (unsigned)std::max(1, atoi(lw)));
-        const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)8, (M * F) / 65536 + 1}));
+        static int tcap = -1;
+        if (tcap < 0) { const char *e = getenv("MMB_SCAN_THREADS_MAX"); tcap = e ? std::max(1, atoi(e)) : 8; }
+        const int T = (int)std::max<size_t>(1, std::min<size_t>({(size_t)hw, (size_t)tcap, (M * F) / 65536 + 1}));
         std::vector<size_t> count(T + 1, 0);
         std::vector<std::vector<double>> twmax(T, std::vector<double>(F, 0.0));
         std::vector<std::vector<uint8_t>> tseen(T, std::vector<uint8_t>(F, 0));
@@ -416,7 +418,7 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         const std::vector<int32_t> &src = hp.mkr_src;  // row of marker i in the caller's tables
         // one set of threads for both passes: count, meet, (thread 0: prefix sums and the
         // uninitialised resize), meet, fill
-        std::atomic<int> arrived{0}, released{0};
+        std::atomic<int> arrived{0}, released{0}, filled{0}, merged{0};
         auto body = [&](int t) {
             size_t m0, m1, k = 0;
             range(t, &m0, &m1);
@@ -453,6 +455,19 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
                     ws[j] = 1;
                 }
             }
+            // meet again; thread 0 merges the per-frame weight maxima; then every thread normalises
+            // the weights of its own observations (adjust_relationships.cpp: weight / max of the frame)
+            filled.fetch_add(1, std::memory_order_acq_rel);
+            if (t == 0) {
+                while (filled.load(std::memory_order_acquire) < T) std::this_thread::yield();
+                for (int u = 0; u < T; ++u)
+                    for (size_t j = 0; j < F; ++j)
+                        if (tseen[u][j] && (!wseen[j] || twmax[u][j] > wmax[j])) { wmax[j] = twmax[u][j]; wseen[j] = 1; }
+                merged.store(1, std::memory_order_release);
+            } else {
+                while (!merged.load(std::memory_order_acquire)) std::this_thread::yield();
+            }
+            for (size_t q = count[t]; q < count[t + 1]; ++q) hp.obs_w[q] = hp.obs_w[q] / wmax[hp.err_frame[q]];
         };
         {
             std::vector<std::thread> th;
@@ -460,9 +475,6 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
             body(0);
             for (auto &x : th) x.join();
         }
-        for (int t = 0; t < T; ++t)
-            for (size_t j = 0; j < F; ++j)
-                if (tseen[t][j] && (!wseen[j] || twmax[t][j] > wmax[j])) { wmax[j] = twmax[t][j]; wseen[j] = 1; }
     }
     hp.nobs = (int)hp.err_marker.size();
     hp.m = 2 * hp.nobs;
@@ -488,7 +500,6 @@ mmb_status build_host_problem(const mmb_scene_desc *s, const mmb_options *opt,
         hp.n_extra = hp.n_stiff + hp.n_smooth;
         hp.m_total = hp.m + hp.n_extra;
     }
-    for (int i = 0; i < hp.nobs; ++i) hp.obs_w[i] = hp.obs_w[i] / wmax[hp.err_frame[i]];
     hp.dense_grid = ((size_t)hp.nobs == (size_t)hp.M * F);
 
     mark("observation scan");
