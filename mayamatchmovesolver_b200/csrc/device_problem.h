@@ -4,6 +4,7 @@
 
 #include <cstdio>
 #include <string>
+#include <cstring>
 #include <vector>
 
 #include "eval_bodies.cuh"
@@ -37,12 +38,22 @@ struct DeviceArena {
     std::vector<void *> ptrs;
     size_t bytes = 0;
     cudaStream_t stream = nullptr;
+    // Batch window (mmb_problem_create): the many small index tables (a few dozen uploads of a few
+    // hundred bytes to a few KB) share ONE device slab and ONE page-locked staging block; an upload
+    // is a host memcpy into the staging block, and flush() sends what has gathered since the last
+    // one in a single copy -- instead of one cudaMallocAsync + one staged pageable copy per table.
+    static constexpr size_t kSlabBytes = (size_t)2 << 20, kSlabSmall = (size_t)64 << 10;
+    char *slab = nullptr, *stage = nullptr;
+    size_t slab_used = 0, slab_flushed = 0;
+    bool batching = false;
     ~DeviceArena() { release(); }
     void bind(cudaStream_t s) { stream = s; }
     void release() {
         for (void *p : ptrs) cudaFreeAsync(p, stream);
         ptrs.clear();
         bytes = 0;
+        slab = nullptr; slab_used = slab_flushed = 0; batching = false;
+        if (stage) { host_block_release(stage); stage = nullptr; }   // (the owner has synchronised the stream)
     }
     template <typename T>
     cudaError_t alloc(T **out, size_t count) {
@@ -56,8 +67,32 @@ struct DeviceArena {
         *out = (T *)p;
         return cudaSuccess;
     }
+    cudaError_t begin_batch() {
+        if (!slab) {
+            cudaError_t e = alloc(&slab, kSlabBytes);
+            if (e != cudaSuccess) return e;
+            stage = static_cast<char *>(host_block_acquire(kSlabBytes));
+        }
+        batching = true;
+        return cudaSuccess;
+    }
+    // everything uploaded so far is on its way (call before a kernel that reads it is launched)
+    cudaError_t flush() {
+        if (slab_used == slab_flushed) return cudaSuccess;
+        const cudaError_t e = cudaMemcpyAsync(slab + slab_flushed, stage + slab_flushed, slab_used - slab_flushed, cudaMemcpyHostToDevice, stream);
+        slab_flushed = slab_used;
+        return e;
+    }
+    cudaError_t end_batch() { batching = false; return flush(); }
     template <typename T, typename Al>
     cudaError_t upload(T **out, const std::vector<T, Al> &v) {
+        const size_t nb = (std::max<size_t>(v.size(), 1) * sizeof(T) + 255) & ~(size_t)255;
+        if (batching && nb <= kSlabSmall && slab_used + nb <= kSlabBytes) {
+            *out = reinterpret_cast<T *>(slab + slab_used);
+            if (!v.empty()) std::memcpy(stage + slab_used, v.data(), v.size() * sizeof(T));
+            slab_used += nb;
+            return cudaSuccess;
+        }
         cudaError_t e = alloc(out, v.size());
         if (e != cudaSuccess) return e;
         if (!v.empty()) e = cudaMemcpyAsync(*out, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, stream);

@@ -469,6 +469,7 @@ static mmb_status build_marker_blocks(DeviceProblem *p, TiledPlan *t) {
     // the kernel would fetch, every (marker, frame) slot whether or not it has an observation)
     const size_t nblk = hp.dense_grid ? (size_t)FB * hp.M * 3 * kRowFrames : 2;
     double *d_blk = nullptr;
+    MMB_CUDA_CHECK(A.flush());   // the kernels below read tables uploaded so far
     MMB_CUDA_CHECK(A.alloc(&d_blk, nblk));
     MMB_CUDA_CHECK(cudaMemsetAsync(d_blk, 0, sizeof(double) * nblk, p->stream));
     t->obs_base = nullptr; t->obs_mask = nullptr;
@@ -533,6 +534,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
         CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
     }
     p->arena.bind(p->stream);
+    CK(p->arena.begin_batch());   // small tables: one slab, one staging block, one copy (DeviceArena)
     HostProblem &hp = p->hp;
     DevScene &d = p->ds;
     DeviceArena &A = p->arena;
@@ -795,6 +797,7 @@ mmb_status device_problem_create(const mmb_scene_desc *s, const mmb_options *opt
     CK(A.alloc(&p->d_x, (size_t)hp.n));
     CK(A.alloc(&p->d_fvec, (size_t)hp.m_total));
     CK(A.alloc(&p->d_dist, (size_t)hp.nobs));
+    CK(A.end_batch());
 #undef CK
 #undef UP_I
 #undef UP_D
