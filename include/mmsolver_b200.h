@@ -488,7 +488,8 @@ mmb_status mmb_solve_stats(const mmb_problem *p, int64_t *host_syncs,
 /* Device buffers come from the device's stream-ordered memory pool and stay
  * cached there when a handle is destroyed, so the next mmb_problem_create of a
  * session (the reference calls mmSolver once per solver step) does not pay for
- * allocation again.  This hands the cached memory back to the driver. */
+ * allocation again; the page-locked host blocks the library stages its uploads
+ * in are cached the same way (up to 1 GB idle).  This hands both back. */
 mmb_status mmb_release_cached_memory(int32_t device);
 
 const char *mmb_status_string(mmb_status s);
