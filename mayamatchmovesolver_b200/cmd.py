@@ -208,6 +208,56 @@ def affects_strings(scene, used_only=None):
     return out
 
 
+def solver_types():
+    """getSolverTypes (adjust_base.cpp:80-93): the (index, name) pairs, in the reference's order"""
+    return [(SOLVER_TYPE_CMINPACK_LMDIF, "cminpack_lmdif"), (SOLVER_TYPE_CMINPACK_LMDER, "cminpack_lmder")]
+
+
+def solver_type_default():
+    """getSolverTypeDefault (adjust_base.cpp:96-130): index cminpack_lmder unless the environment
+    variable MMSOLVER_DEFAULT_SOLVER names another type; as in the reference the NAME is only
+    filled in from that variable (it is empty without it), and an unknown value keeps the default"""
+    import os
+    index, name = SOLVER_TYPE_CMINPACK_LMDER, ""
+    wanted = os.environ.get("MMSOLVER_DEFAULT_SOLVER")
+    if wanted is not None:
+        for i, n in solver_types():
+            if wanted == n:
+                index, name = i, n
+    return index, name
+
+
+def mmSolverType(query=False, list=False, default=False, name=None, index=None, **short):
+    """The `mmSolverType` command (src/mmSolver/cmd/MMSolverTypeCmd.cpp:96-258): the solver types
+    this build has, or the default one, as 'index=name' strings, names or indices.  The short flag
+    names of MMSolverTypeCmd.h:63-76 (q, ls, def, n, idx) are accepted too (`def` only through
+    `**{"def": True}`: it is a Python keyword)."""
+    query = short.pop("q", query)
+    list = short.pop("ls", list)
+    default = short.pop("def", default)
+    name = short.pop("n", name)
+    index = short.pop("idx", index)
+    if short:
+        raise TypeError("mmSolverType: unknown flag(s) %s" % sorted(short))
+    if not query:
+        raise RuntimeError("mmSolverType must query using the 'query' flag")
+    if bool(list) == bool(default):
+        raise RuntimeError("mmSolverType; must give 'list' or 'default' flag, not both flags at once")
+    want_name = True if name is None else bool(name)
+    want_index = True if index is None else bool(index)
+    if not want_name and not want_index:
+        raise RuntimeError("mmSolverType must have 'name' or 'index' flags")
+
+    def item(i, n):
+        if want_name:
+            return ("%d=" % i if want_index else "") + n
+        return i
+
+    if list:
+        return [item(i, n) for i, n in solver_types()]
+    return item(*solver_type_default())
+
+
 def mmSolverAffects(scene, mode="returnString", **kwargs):
     """The `mmSolverAffects` command (src/mmSolver/cmd/MMSolverAffectsCmd.cpp): which solver
     attribute can affect which marker.  mode 'returnString' -> the `marker_affects_attribute=`

@@ -126,3 +126,39 @@ def test_flag_names_long_and_short():
     assert rest == dict(verbose=True)
     with pytest.raises(TypeError):
         cmd.mmSolver(_named_scene(), notAFlag=1)
+
+
+def test_mmSolverType_mirrors_the_reference_test(monkeypatch):
+    """tests/test/test_solver/test_solver_type.py:49-121 (src/mmSolver/cmd/MMSolverTypeCmd.cpp,
+    getSolverTypes / getSolverTypeDefault adjust_base.cpp:80-130), with the reference's assertions"""
+    monkeypatch.delenv("MMSOLVER_DEFAULT_SOLVER", raising=False)
+    a_list = cmd.mmSolverType(query=True, list=True)
+    assert len(a_list) > 0
+    for solver_type in a_list:
+        assert "=" in solver_type and isinstance(solver_type, str)
+    assert a_list == ["1=cminpack_lmdif", "2=cminpack_lmder"]
+    b_list = cmd.mmSolverType(query=True, list=True, name=True, index=False)
+    assert len(b_list) == len(a_list) and all("=" not in n for n in b_list)
+    c_list = cmd.mmSolverType(query=True, list=True, name=False, index=True)
+    assert len(c_list) == len(a_list) and all(isinstance(i, int) for i in c_list)
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverType(query=True, list=True, name=False, index=False)
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverType(list=True)                       # not a query
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverType(query=True, list=True, default=True)
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverType(query=True)
+    solver_type = cmd.mmSolverType(query=True, default=True)
+    solver_name = cmd.mmSolverType(query=True, default=True, name=True, index=False)
+    solver_index = cmd.mmSolverType(query=True, default=True, name=False, index=True)
+    assert "=" in solver_type and "=" not in solver_name and len(solver_name) < len(solver_type)
+    assert solver_index == cmd.SOLVER_TYPE_CMINPACK_LMDER == 2
+    # the index the command reports is the one the C-ABI option takes
+    from mayamatchmovesolver_b200.problem import default_options
+    assert default_options().solver_type == solver_index
+    # MMSOLVER_DEFAULT_SOLVER picks the default (and is where the default's name comes from)
+    monkeypatch.setenv("MMSOLVER_DEFAULT_SOLVER", "cminpack_lmdif")
+    assert cmd.mmSolverType(query=True, default=True) == "1=cminpack_lmdif"
+    monkeypatch.setenv("MMSOLVER_DEFAULT_SOLVER", "ceres")   # not in this build: the default stays
+    assert cmd.mmSolverType(q=True, idx=True, n=False, **{"def": True}) == 2
