@@ -227,12 +227,21 @@ class SolverStep:
             if len(mkr_list) == 0:
                 return   # 'No Markers found!'
             kwargs["marker"] = list(mkr_list)
-        if self._data["frame_solve_mode"] == cmd.FRAME_SOLVE_MODE_PER_FRAME:
-            assert self._data["scene_graph_mode"] == cmd.SCENE_GRAPH_MODE_MM_SCENE_GRAPH
+        # solverstep.py:642-657: the command has no 'auto' scene graph (0 is passed as maya_dag);
+        # maya_dag solves all frames at once, per-frame solves need the mm scene graph
+        sgm, fsm = self._data["scene_graph_mode"], self._data["frame_solve_mode"]
+        if sgm is not None:
+            sgm = max(cmd.SCENE_GRAPH_MODE_MAYA_DAG, int(sgm))
+            if sgm == cmd.SCENE_GRAPH_MODE_MAYA_DAG:
+                assert fsm in (None, cmd.FRAME_SOLVE_MODE_ALL_FRAMES_AT_ONCE)
+        if fsm == cmd.FRAME_SOLVE_MODE_PER_FRAME:
+            assert sgm == cmd.SCENE_GRAPH_MODE_MM_SCENE_GRAPH
         for key, flag in self._FIELDS.items():
             if self._data[key] is not None:
                 v = self._data[key]
                 kwargs[flag] = int(v) if isinstance(v, bool) else v
+        if sgm is not None:
+            kwargs["sceneGraphMode"] = sgm
         # stiffness / smoothness flags of the attributes that take part (solverstep.py:596-636)
         refs = {int(a[0]) if not isinstance(a[0], str) else scene.plug(a[0]) for a in attrs}
         for use, entries, flag in ((self._use_stiffness, scene.stiffness, "attrStiffness"),

@@ -3,6 +3,7 @@ logic: frame batching (doc examples of rootframe.py:62-77 and solverstandardutil
 attribute blocks (solverutils.py:43-127), and the Action sequence of compile_multi_frame
 (solverstandardutils.py:433-735).  Host logic only: nothing is solved here."""
 import numpy as np
+import pytest
 
 from mayamatchmovesolver_b200 import solver, synth
 from mayamatchmovesolver_b200.solver import SolverBasic, SolverStandard, SolverStep
@@ -66,6 +67,16 @@ def test_solver_step_flags():
     assert list(s.compile(sb)) == []                                   # 'No Attributes found!'
     s2 = SolverStep()
     assert list(s2.compile(sb)) == []                                  # 'No Frames found!'
+    # solverstep.py:642-657: 'auto' (0) reaches the command as maya_dag (1), which solves all frames
+    # at once; a per-frame solve needs the mm scene graph
+    s3 = SolverStep()
+    s3.set_frame_list([1, 2])
+    s3.set_scene_graph_mode(0)
+    (a3, _), = list(s3.compile(sb))
+    assert a3.kwargs["sceneGraphMode"] == 1
+    s3.set_frame_solve_mode(1)
+    with pytest.raises(AssertionError):
+        list(s3.compile(sb))
 
 
 def test_standard_action_sequence():
