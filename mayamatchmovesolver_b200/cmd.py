@@ -283,6 +283,37 @@ def mmSolverAffects(scene, mode="returnString", **kwargs):
     raise ValueError("mmSolverAffects: mode value is invalid: mode=%r" % mode)
 
 
+def mmSolverSceneGraph(scene, mode="debugConstruct", **kwargs):
+    """The `mmSolverSceneGraph` command (src/mmSolver/cmd/MMSolverSceneGraphCmd.cpp:140-208): can
+    the scene of these cameras / markers / attributes / frames be built for the given scene graph
+    mode?  The reference's Python API asks this before it picks sceneGraphMode = 2
+    (`construct_scene_graph`); maya_dag (1) always answers True.  Here the scene already is a flat
+    scene: the answer is whether the library's own scene checks (the host half of
+    mmb_problem_create, through the host-only mmb_affects) accept it.  A scene that cannot be
+    built answers False, it does not raise -- as the command does."""
+    if mode != "debugConstruct":
+        raise RuntimeError("mmSolverSceneGraph: Mode value is invalid: mode=%r" % (mode,))
+    options, rest = _options_from_kwargs(kwargs)
+    sgm = int(options.get("scene_graph_mode", SCENE_GRAPH_MODE_MAYA_DAG))   # the command's default
+    if sgm == SCENE_GRAPH_MODE_MAYA_DAG:
+        return True
+    if sgm != SCENE_GRAPH_MODE_MM_SCENE_GRAPH:
+        raise RuntimeError("mmSolverSceneGraph: Scene Graph Mode value is invalid: value=%d" % sgm)
+    objects = {}
+    for key, value in rest.items():
+        long_name = {v: k for k, v in _OBJECT_FLAGS.items()}.get(key, key)
+        if long_name in _OBJECT_FLAGS:
+            objects[long_name] = value
+    from .problem import affects
+    from ._capi import MmbError
+    try:
+        sb = select_scene(scene, **objects) if objects else scene
+        affects(sb)
+    except (MmbError, ValueError, KeyError, IndexError):
+        return False
+    return True
+
+
 def mmSolver(scene, write_back=True, device=0, **kwargs):
     """-> list of `key=value` strings, as `maya.cmds.mmSolver` returns them."""
     opts, rest = _options_from_kwargs(kwargs)

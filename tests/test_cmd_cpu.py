@@ -162,3 +162,24 @@ def test_mmSolverType_mirrors_the_reference_test(monkeypatch):
     assert cmd.mmSolverType(query=True, default=True) == "1=cminpack_lmdif"
     monkeypatch.setenv("MMSOLVER_DEFAULT_SOLVER", "ceres")   # not in this build: the default stays
     assert cmd.mmSolverType(q=True, idx=True, n=False, **{"def": True}) == 2
+
+
+def test_mmSolverSceneGraph_answers_whether_the_scene_can_be_built():
+    """src/mmSolver/cmd/MMSolverSceneGraphCmd.cpp:140-208: maya_dag always True; mm scene graph:
+    True / False (never an exception) from the scene checks; other modes are errors"""
+    from mayamatchmovesolver_b200 import synth
+    sb, _ = synth.make_scene(F=4, B=5, seed=1)
+    assert cmd.mmSolverSceneGraph(sb) is True                                        # default mode: maya_dag
+    assert cmd.mmSolverSceneGraph(sb, sceneGraphMode=cmd.SCENE_GRAPH_MODE_MM_SCENE_GRAPH) is True
+    assert cmd.mmSolverSceneGraph(sb, sgm=2, frame=list(sb.frames)[:2]) is True        # short flag, object flags
+    import copy
+    bad = copy.deepcopy(sb)
+    bad._arrays_cache = None
+    bad.mkr_bnd[0] = 10 ** 6          # a marker whose bundle does not exist
+    assert cmd.mmSolverSceneGraph(bad, sceneGraphMode=2) is False
+    assert cmd.mmSolverSceneGraph(bad, sceneGraphMode=1) is True
+    assert cmd.mmSolverSceneGraph(sb, sceneGraphMode=2, frame=[10 ** 6]) is False      # a frame the scene does not have
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverSceneGraph(sb, mode="construct")
+    with pytest.raises(RuntimeError):
+        cmd.mmSolverSceneGraph(sb, sceneGraphMode=3)
